@@ -1,0 +1,272 @@
+/*
+ * tracer_b200.h -- C ABI of libtracer_b200.so (sm_100a).
+ *
+ * This is the drop-in boundary for the Monte-Carlo bounce loop of
+ * casselineau/Tracer.  The reference has no FFI (it is pure NumPy), so each
+ * entry point below names the reference *Python* interface it replaces
+ * (paths relative to the reference tree).  All pointers named `d_*` are DEVICE
+ * pointers owned by the caller (torch CUDA tensors in the Python host layer);
+ * the library never allocates, frees or retains them.  Scene handles own small
+ * device tables and are freed by trc_scene_destroy().
+ *
+ * Ray bundles are SoA float64 exactly as the reference's RayBundle
+ * (tracer/ray_bundle.py:6-63): vertices (3,n) and directions (3,n) row-major
+ * with a row stride `ld` (elements), energy (n,), parents (n,) int64.
+ *
+ * Every function returns 0 on success or a negative TrcStatus; the message is
+ * available from trc_last_error() (thread-local).  No C++ exception crosses
+ * this boundary.  All work is enqueued on the given CUDA stream
+ * (a cudaStream_t passed as void*; NULL = legacy default stream).
+ */
+#ifndef TRACER_B200_H
+#define TRACER_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TRC_ABI_VERSION 1
+
+typedef enum TrcStatus {
+    TRC_OK = 0,
+    TRC_ERR_BAD_ARGUMENT = -1,
+    TRC_ERR_UNSUPPORTED_KIND = -2,
+    TRC_ERR_CUDA = -3,
+    TRC_ERR_CAPACITY = -4
+} TrcStatus;
+
+/* Geometry-manager kinds: one per reference GeometryManager subclass on the
+ * hot path. */
+typedef enum TrcGeomKind {
+    TRC_G_FLAT_INFINITE = 0,   /* FlatGeometryManager        flat_surface.py:11   */
+    TRC_G_RECT_PLATE = 1,      /* RectPlateGM                flat_surface.py:181  gp: hx, hy */
+    TRC_G_RECT_EXTRUDED = 2,   /* ExtrudedRectPlateGM        flat_surface.py:253  gp: hx, hy, cx, cy, ehx, ehy */
+    TRC_G_ROUND_PLATE = 3,     /* RoundPlateGM / StraightCut flat_surface.py:457,548  gp: Re, Ri(<0 none), x_cut(+inf none) */
+    TRC_G_TRIANGLE = 4,        /* TriangularFace             triangular_face.py:12 gp: v0x v0y v0z v1x v1y v1z */
+    TRC_G_PARABOLOID = 5,      /* Paraboloid                 paraboloid.py:11     gp: a, b */
+    TRC_G_PARAB_DISH = 6,      /* ParabolicDishGM            paraboloid.py:71     gp: a, b, h */
+    TRC_G_PARAB_HEX = 7,       /* HexagonalParabolicDishGM   paraboloid.py:174    gp: a, b, R */
+    TRC_G_PARAB_RECT = 8,      /* RectangularParabolicDishGM paraboloid.py:225    gp: a, b, hw, hh */
+    TRC_G_PARAB_CYL = 9,       /* ParabolicCylinder          paraboloid.py:328    gp: a */
+    TRC_G_PARAB_TROUGH = 10,   /* ParabolicTroughGM          paraboloid.py:386    gp: a, hl, h */
+    TRC_G_SPHERE = 11,         /* SphericalGM                sphere_surface.py:9  gp: r */
+    TRC_G_HEMISPHERE = 12,     /* HemisphereGM               sphere_surface.py:117 gp: r */
+    TRC_G_SPHERE_RECT = 13,    /* SphericalRectFacet         sphere_surface.py:206 gp: r, lx/2, ly/2 */
+    TRC_G_CONE_INFINITE = 14,  /* InfiniteCone               cone.py:7            gp: c, a */
+    TRC_G_CONE_FINITE = 15,    /* FiniteCone                 cone.py:74           gp: c, a(=0), h */
+    TRC_G_FRUSTUM = 16,        /* ConicalFrustum             cone.py:261          gp: c, a, zmin, zmax */
+    TRC_G_FRUSTUM_RECT = 17,   /* RectCutConicalFrustum      cone.py:356          gp: c, a, zmin, zmax, hw, hh */
+    TRC_G_CYL_INFINITE = 18,   /* InfiniteCylinder           cylinder.py:12       gp: R */
+    TRC_G_CYL_FINITE = 19,     /* FiniteCylinder             cylinder.py:59       gp: R, half_h, ang0, ang1 */
+    TRC_G_CYL_RECT = 20,       /* RectCutCylinder            cylinder.py:161      gp: R, half_h, hw, hh */
+    TRC_G_QUADRIC_FLAT = 21,   /* FlatQuadricSurfaceGM       quadratic_surface.py:4   gp: a b c d e f */
+    TRC_G_QUADRIC_RECT = 22,   /* RectFlatQuadricSurfaceGM   quadratic_surface.py:63  gp: a b c d e f hw hh */
+    TRC_G_SPHERE_CUT = 23,     /* CutSphereGM + BoundarySphere sphere_surface.py:168, boundary_shape.py:89-111
+                                  gp: r, cx, cy, cz (bound centre, global), R_bound */
+    TRC_G_KIND_COUNT = 24
+} TrcGeomKind;
+
+/* Optics kinds: the base optics class behind the accountant wrapper
+ * (optics_callables.py). */
+typedef enum TrcOpticsKind {
+    TRC_O_TRANSPARENT = 0,        /* Transparent         optics_callables.py:93  */
+    TRC_O_REFLECTIVE = 1,         /* Reflective          :116  op: abs */
+    TRC_O_REAL_REFLECTIVE = 2,    /* RealReflective      :214  op: abs, sigma, bi_var */
+    TRC_O_LAMBERTIAN = 3,         /* Lambertian          :143  op: abs, ang_range */
+    TRC_O_LAMBERTIAN_SPECULAR = 4,/* LambertianSpecular  :553  op: abs, specularity */
+    TRC_O_LAMB_DIRECTIONAL = 5,   /* Lambertian_directional_axisymmetric_piecewise :331
+                                     table = (thetas, abs_th); always diffuse */
+    TRC_O_REFLECTIVE_SPECTRAL = 6,/* Reflective_spectral :178  table = (wavelengths, absorptances) */
+    TRC_O_LAMBSPEC_DIRECTIONAL = 7,/* LambertianSpecular_directional_axisymmetric_piecewise :427
+                                     op: specularity; table = (thetas, abs_th) */
+    TRC_O_LAMB_DIRECTIONAL_SPECTRAL = 8, /* Lambertian_directional_axisymmetric_piecewise_spectral :359
+                                     op[1] = n_wavelengths; table = thetas[table_len],
+                                     wavelengths[n_wl], absorptance[table_len*n_wl] (bilinear) */
+    TRC_O_KIND_COUNT = 9
+} TrcOpticsKind;
+
+/* Surface flag bits. */
+#define TRC_F_ONE_SIDED   1u   /* OneSidedReflective / OneSidedRealReflective (:195,:492): E'=0 where d.up>0 */
+#define TRC_F_UNBOUNDED   2u   /* no finite AABB: tested for every ray, outside the BVH */
+
+/* One record per surface in Assembly.get_surfaces() order (assembly.py:60-77).
+ * frame = rows 0..2 of Surface._temp_frame (has_frame.py:75), inv = rows 0..2
+ * of numpy.linalg.inv(frame) computed on the host with the same routine the
+ * reference uses (flat_surface.py:160).  Row-major, 4 columns. */
+typedef struct TrcSurfaceRec {
+    double frame[12];
+    double inv[12];
+    double gp[12];       /* geometry parameters, see TrcGeomKind */
+    double op[4];        /* optics parameters, see TrcOpticsKind */
+    int32_t gkind;
+    int32_t okind;
+    uint32_t flags;
+    int32_t table_off;   /* offset (in doubles) into the scene's optics table pool, -1 = none */
+    int32_t table_len;   /* number of (x, y) knots */
+    int32_t pad_[3];
+} TrcSurfaceRec;         /* 352 bytes */
+
+/* Binary BVH node over per-surface global AABBs.  Replaces the relevance
+ * mask produced by KdTree.traversal (accel_tree.py:213-312): instead of
+ * materialising an (S, N) boolean matrix, the nearest-hit kernel walks this
+ * tree per ray.  Leaf: count > 0, `first` indexes the leaf-surface list.
+ * Inner: count == 0, children at `first` and `first + 1`. */
+typedef struct TrcBvhNode {
+    double lo[3];
+    double hi[3];
+    int32_t first;
+    int32_t count;
+    int32_t pad_[2];
+} TrcBvhNode;            /* 64 bytes */
+
+typedef struct TrcScene TrcScene;
+
+int trc_abi_version(void);
+const char *trc_last_error(void);
+
+/* Replaces the per-trace Python walk over Assembly.get_surfaces()
+ * (tracer_engine.py:165-166): uploads the compiled surface table.
+ * `tables` is a pool of float64 (x..., y...) interpolation tables for the
+ * directional / spectral optics (may be NULL when n_table == 0). */
+int trc_scene_create(const TrcSurfaceRec *surfaces, int32_t n_surfaces,
+                     const double *tables, int32_t n_table,
+                     TrcScene **out);
+/* After Assembly.transform_children / HeliostatField.track_sun
+ * (assembly.py:137-147, models/heliostat_field.py:89): refresh frames only. */
+int trc_scene_update_frames(TrcScene *scene, const double *frames12,
+                            const double *inv12, int32_t n_surfaces);
+/* Acceleration structure.  Replaces KdTree.__init__/build_tree output
+ * (accel_tree.py:20-146).  nodes[0] is the root.  leaf_surfaces lists the
+ * surface indices referenced by leaves; `unbounded` lists the always-relevant
+ * surfaces (accel_tree.py:59-73). */
+int trc_scene_set_bvh(TrcScene *scene, const TrcBvhNode *nodes, int32_t n_nodes,
+                      const int32_t *leaf_surfaces, int32_t n_leaf_surfaces,
+                      const int32_t *unbounded, int32_t n_unbounded);
+int trc_scene_destroy(TrcScene *scene);
+int32_t trc_scene_num_surfaces(const TrcScene *scene);
+
+/* Nearest hit across all surfaces for every ray.  Replaces
+ * TracerEngine.intersect_ray (tracer_engine.py:27-64) together with every
+ * GeometryManager.find_intersections it calls and,
+ * when use_bvh != 0, KdTree.traversal (accel_tree.py:213-312).
+ * d_hit_surf[i] = index of the first surface hit by ray i (lowest index wins
+ * ties, strict '<' at tracer_engine.py:59), or -1. */
+int trc_nearest_hit(const TrcScene *scene, int64_t n_rays,
+                    const double *d_vertices, const double *d_directions, int64_t ld,
+                    int32_t use_bvh, int32_t *d_hit_surf, void *stream);
+
+/* Stable counting/radix sort of (key, value) pairs by key; keys < 0 are
+ * dropped.  With keys = d_hit_surf and values = NULL (meaning 0..n-1) this is
+ * the surface-major, ray-minor child ordering of the optics loop +
+ * concatenate_rays (tracer_engine.py:218-266, ray_bundle.py:197-223).
+ * With keys = cull flags it is the "survivors first, weak rays at the back"
+ * order of tracer_engine.py:268-274.
+ * d_work must hold trc_sort_work_bytes(n, n_keys) bytes.  The number of kept
+ * pairs is written to d_count[0] (int64, device). */
+int64_t trc_sort_work_bytes(int64_t n, int32_t n_keys);
+int trc_sort_pairs(int64_t n, int32_t n_keys,
+                   const int32_t *d_keys_in, const int32_t *d_vals_in,
+                   int32_t *d_keys_out, int32_t *d_vals_out,
+                   int64_t *d_count, void *d_work, void *stream);
+
+/* Segment offsets of a sorted key array holding *d_count (<= n_max) entries:
+ * d_offsets[k] = first position whose key >= k, for k in [0, n_keys]; i.e.
+ * surface k owns slots [off[k], off[k+1]).  This is what the optics loop's
+ * per-surface `intersections` masks encode (tracer_engine.py:218-228). */
+int trc_segment_offsets_dyn(const int64_t *d_count, int64_t n_max, int32_t n_keys,
+                            const int32_t *d_sorted_keys, int64_t *d_offsets, void *stream);
+
+/* Optics + accounting for the h sorted hits of one bounce.  Replaces the body
+ * of the optics loop: Surface.select_rays / get_outgoing (surface.py:72-94),
+ * GM.get_normals / get_intersection_points_global, every optics __call__
+ * (optics_callables.py:93-627) and the Accountant.count calls
+ * (optics_callables.py:1949-1961).
+ *   slot q reads parent ray d_slot_parent[q] hit on surface d_slot_surf[q].
+ *   child q: vertex = hit point, direction per optics, energy, parent index.
+ *   d_draws[k] (k < 3) are injected random draws in slot order (NULL => the
+ *   kernel draws from Philox4x32-10 keyed by (seed, bounce, slot)).
+ *   Optional tallies (NULL to skip): d_absorbed[q] = E_in - E_out
+ *   (AbsorptionAccountant :1638-1643), d_normals (3,h) (NormalAccountant).
+ *   d_cull[q] = 1 where child energy <= min_energy (tracer_engine.py:242). */
+typedef struct TrcOpticsArgs {
+    int64_t h;
+    const int32_t *d_slot_parent;
+    const int32_t *d_slot_surf;
+    const double *d_vertices;     /* parent bundle */
+    const double *d_directions;
+    const double *d_energy;
+    const double *d_wavelengths;  /* nullable: per-ray wavelength (spectral optics) */
+    int64_t ld_in;
+    double *d_out_vertices;       /* child bundle, slot order */
+    double *d_out_directions;
+    double *d_out_energy;
+    int64_t *d_out_parents;
+    int64_t ld_out;
+    const double *d_draws[3];
+    uint64_t seed;
+    uint32_t bounce;
+    uint32_t pad_;
+    double min_energy;
+    double *d_absorbed;           /* nullable */
+    double *d_normals;            /* nullable, (3,h) with stride ld_out */
+    int32_t *d_cull;              /* nullable; int32 so it can key trc_sort_pairs */
+} TrcOpticsArgs;
+int trc_optics(const TrcScene *scene, const TrcOpticsArgs *args, void *stream);
+
+/* Row gather: out[r, j] = in[r, idx[j]] for r < n_rows (float64 rows) and
+ * optionally an int64 row.  Applies the cull permutation to a child bundle
+ * (RayBundle.inherit with an index selector, ray_bundle.py:117-143). */
+int trc_gather_rows(int64_t n_out, const int32_t *d_idx,
+                    int32_t n_rows, const double *d_in, int64_t ld_in,
+                    double *d_out, int64_t ld_out,
+                    const int64_t *d_in_i64, int64_t *d_out_i64, void *stream);
+
+/* Sources (tracer/sources.py).  All draw from Philox4x32-10 keyed by
+ * (seed, first_ray + i); rot_dir / rot_pos are the 3x3 row-major matrices
+ * returned by rotation_to_z (spatial_geometry.py:24-48) for the ray direction
+ * and the source-plane normal.
+ *   trc_source_pillbox_disk: disk_bundle (sources.py:175-239)
+ *   trc_source_buie_disk:    buie_sunshape (sources.py:412-464) with the
+ *                            Buie_directions_sampling tables (:330-384)
+ *                            precomputed on the host (n_seg = 210). */
+int trc_source_pillbox_disk(int64_t n, int64_t first_ray, uint64_t seed,
+                            const double *center3, const double *rot_dir9, const double *rot_pos9,
+                            double radius_in, double radius, double ang0, double ang1,
+                            double ang_range, double ray_energy,
+                            double *d_vertices, double *d_directions, double *d_energy,
+                            int64_t ld, void *stream);
+typedef struct TrcBuieTables {
+    int32_t n_seg;            /* 210 */
+    int32_t has_aureole;      /* CSR > 0 */
+    double cdf[212];          /* CDF_DNI[0..n_seg] */
+    double theta[212];        /* theta_int[0..n_seg] */
+    double w[212];            /* phi_dni*cos*sin at theta_int[i] */
+    double sum_integ_dni;
+    double gamma, kappa, theta_dni, theta_tot;
+} TrcBuieTables;
+int trc_source_buie_disk(int64_t n, int64_t first_ray, uint64_t seed,
+                         const TrcBuieTables *tables,
+                         const double *center3, const double *rot_dir9, const double *rot_pos9,
+                         double radius, double ray_energy,
+                         double *d_vertices, double *d_directions, double *d_energy,
+                         int64_t ld, void *stream);
+
+/* Flux-map binning on device.  Replaces Surface.global_to_local
+ * (surface.py:114-126) + RectPlateGM.get_fluxmap's histogram2d
+ * (flat_surface.py:237-251): d_bins (nx*ny, row-major [ix][iy]) += energy. */
+int trc_fluxmap_rect(int64_t n, const double *d_hits, int64_t ld, const double *d_energy,
+                     const double *proj12 /* host, rows 0..2 of rounded inverse frame */,
+                     double hx, double hy, int32_t nx, int32_t ny,
+                     double *d_bins, void *stream);
+
+/* Per-surface energy totals: d_totals[s] += sum of d_values over slots of
+ * surface s (segment offsets from trc_segment_offsets). */
+int trc_segment_sums(int32_t n_keys, const int64_t *d_offsets, const double *d_values,
+                     double *d_totals, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TRACER_B200_H */

@@ -1,0 +1,96 @@
+"""Generate the golden vectors of tests/golden/*.npz by running the REAL reference
+(imported from /root/reference through oracle/ref_import.py).  Run here, in the
+build container, whenever a scene in tests/scenes.py changes:
+
+    python tests/golden/make_golden.py
+
+The .npz files are committed; the GPU box never runs this script.
+"""
+import os
+import sys
+import warnings
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+from oracle import ref_import  # noqa: E402
+from tests import scenes  # noqa: E402
+
+# name -> (builder, kwargs, seed, reps, min_energy)
+TRACE_CASES = {
+    'c1_flat': (scenes.c1_flat_mirror, dict(n_rays=2000), 11, 3, 1e-10),
+    'c2_dish_bivar': (scenes.c2_dish, dict(n_rays=1500, bi_var=True), 12, 3, 1e-10),
+    'c2_dish_conical': (scenes.c2_dish, dict(n_rays=1500, bi_var=False), 13, 3, 1e-10),
+    'c3_nsttf': (scenes.c3_nsttf, dict(n_rays=20000), 14, 3, 1e-10),
+    'c3_nsttf_dense': (scenes.c3_nsttf, dict(n_rays=4000, n_hstats=40, dense=True), 15, 3, 1e-10),
+    'c4_cavity': (scenes.c4_cavity, dict(n_rays=1500, n_theta=8, n_z=4), 16, 5, 1e-3 * 1000. * np.pi * 0.81 / 1500),
+    'c5_cavity': (scenes.c5_cavity, dict(n_rays=1500), 17, 6, 1e-10),
+    'c5_cavity_spectral': (scenes.c5_cavity, dict(n_rays=1500, spectral=True), 18, 6, 1e-10),
+}
+ZOO_RAYS = 4000
+ZOO_SEED = 99
+
+
+def trace_reference(name):
+    import logging
+    T = scenes.NS('tracer')
+    builder, kw, seed, reps, min_energy = TRACE_CASES[name]
+    np.random.seed(seed)
+    asm, source = builder(T, **kw)
+    bundle = source()
+    from tracer.tracer_engine import TracerEngine
+    eng = TracerEngine(asm, loglevel=logging.DEBUG)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        eng.ray_tracer(bundle, reps=reps, min_energy=min_energy, tree=True)
+    out = {'n_tree': eng.tree.num_bunds(), 'seed': seed, 'reps': reps, 'min_energy': min_energy}
+    for k in range(eng.tree.num_bunds()):
+        b = eng.tree[k]
+        out['v%d' % k] = b.get_vertices()
+        out['d%d' % k] = b.get_directions()
+        out['e%d' % k] = b.get_energy()
+        if k > 0:
+            out['p%d' % k] = b.get_parents()
+    for s, surf in enumerate(asm.get_surfaces()):
+        opt = surf.get_optics_manager()
+        if hasattr(opt, 'get_all_hits'):
+            for j, arr in enumerate(opt.get_all_hits()):
+                out['acc_%d_%d' % (s, j)] = arr
+    return out
+
+
+def zoo_reference():
+    """find_intersections / normals / hit points of every GM class on fixed rays."""
+    T = scenes.NS('tracer')
+    out = {}
+    for name, (make, frame) in scenes.gm_zoo(T).items():
+        rays = scenes.zoo_rays(T, ZOO_RAYS, ZOO_SEED)
+        gm = make()
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            prm = np.array(gm.find_intersections(frame, rays), dtype=float)
+            hit = np.nonzero(np.isfinite(prm) & (prm != 0.))[0]
+            out[name + '_params'] = prm
+            if len(hit) and name != 'flat':
+                gm.select_rays(hit)
+                out[name + '_normals'] = np.array(gm.get_normals())
+                out[name + '_points'] = np.array(gm.get_intersection_points_global())
+    return out
+
+
+def main():
+    ref_import.enable()
+    for name in TRACE_CASES:
+        data = trace_reference(name)
+        np.savez_compressed(os.path.join(HERE, name + '.npz'), **data)
+        print(name, 'bundles:', [data['v%d' % k].shape[1] for k in range(data['n_tree'])])
+    z = zoo_reference()
+    np.savez_compressed(os.path.join(HERE, 'gm_zoo.npz'), **z)
+    print('gm_zoo', {k[:-7]: int(np.isfinite(v).sum()) for k, v in z.items() if k.endswith('_params')})
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,234 @@
+"""Scene builders shared by the golden-vector generator (real reference classes,
+``pkg='tracer'``) and the tests (``pkg='tracer_b200'``).  Every builder returns
+(assembly, source_factory) where source_factory() draws the source bundle from
+numpy.random in the reference's order.  Scenes follow SURVEY.md section 8(d).
+"""
+import importlib
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+HSTAT_CSV = os.path.join(HERE, 'golden', 'sandia_hstat_coordinates.csv')
+
+
+class NS(object):
+    """Lazy namespace: NS('tracer').flat_surface.RectPlateGM etc."""
+
+    def __init__(self, pkg):
+        self.pkg = pkg
+
+    def __getattr__(self, mod):
+        m = importlib.import_module(self.pkg + '.' + mod)
+        if hasattr(m, '__path__'):          # sub-package (tracer.models)
+            m = NS(self.pkg + '.' + mod)
+        setattr(self, mod, m)
+        return m
+
+
+def c1_flat_mirror(T, n_rays=2000):
+    """Config 1: flat mirror + flat receiver, pillbox disk source."""
+    mirror = T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(2., 2.),
+                                                               T.optics_callables.Reflective(0.05))])
+    recv = T.object.AssembledObject(
+        surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(4., 4.), T.optics_callables.ReflectiveReceiver(1.))],
+        transform=np.dot(T.spatial_geometry.translate(0, 0, 5.), T.spatial_geometry.rotx(np.pi)))
+    asm = T.assembly.Assembly(objects=[mirror, recv])
+
+    def source():
+        return T.sources.disk_bundle(n_rays, np.c_[[0., 0., 4.]], np.r_[0., 0., -1.], 0.8, 4.65e-3, flux=1000.)
+    return asm, source
+
+
+def c2_dish(T, n_rays=2000, bi_var=True, sigma=2e-3):
+    """Config 2: parabolic dish with slope error + flat receiver, Buie sunshape."""
+    dish = T.object.AssembledObject(surfs=[T.surface.Surface(
+        T.paraboloid.ParabolicDishGM(5., 3.), T.optics_callables.RealReflective(0.06, sigma, bi_var=bi_var))])
+    recv = T.object.AssembledObject(
+        surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(0.3, 0.3), T.optics_callables.ReflectiveReceiver(1.))],
+        transform=np.dot(T.spatial_geometry.translate(0, 0, 3.), T.spatial_geometry.rotx(np.pi)))
+    asm = T.assembly.Assembly(objects=[dish, recv])
+
+    def source():
+        return T.sources.buie_sunshape(n_rays, np.c_[[0., 0., 10.]], np.r_[0., 0., -1.], 2.5, 0.05, flux=1000.)
+    return asm, source
+
+
+def nsttf_positions(n_hstats=None):
+    pos = np.loadtxt(HSTAT_CSV, delimiter=',')
+    pos[:, 1] -= 4.       # examples/Sandia_NSTTF_field example.py:98
+    return pos if n_hstats is None else pos[:n_hstats].copy()
+
+
+def sun_vector(azimuth, zenith):
+    az = np.pi / 2. - azimuth
+    return np.r_[np.sin(zenith) * np.cos(az), np.sin(zenith) * np.sin(az), np.cos(zenith)]
+
+
+def c3_nsttf(T, n_rays=5000, n_hstats=None, dense=False, sigma=1e-3):
+    """Config 3: Sandia NSTTF heliostat field + tower receiver, Buie CSR 0.01."""
+    pos = nsttf_positions(n_hstats)
+    hf = T.models.heliostat_field
+    field = hf.HeliostatField(pos, 6.1, 6.1, absorptivity=0.04, sigma=sigma, bi_var=True, MCRT_option='fast')
+    zenith = np.radians(35.05)
+    field.track_sun(0., zenith, aim_points=np.tile(np.r_[0., 0., 60.], (len(pos), 1)))
+    recv = T.models.one_sided_mirror.one_sided_receiver(11., 11., 1.)
+    recv.set_transform(np.dot(T.spatial_geometry.translate(0., 0., 60.), T.spatial_geometry.rotx(-np.pi / 2.)))
+    asm = T.assembly.Assembly(objects=[recv], subassemblies=[field])
+    sun = sun_vector(0., zenith)
+    lo, hi = pos.min(axis=0), pos.max(axis=0)
+    centre = 0.5 * (lo + hi)
+    radius = 1.1 * 0.5 * np.sqrt(np.sum((hi[:2] - lo[:2]) ** 2))
+    if dense:
+        radius = 0.25 * radius
+
+    def source():
+        return T.sources.buie_sunshape(n_rays, np.vstack(300. * sun + centre), -sun, radius, 0.01, flux=1000.,
+                                       pre_process_CSR=False)
+    return asm, source
+
+
+def cylinder_mesh(n_theta, n_z, radius=1., length=2.):
+    """Closed triangulated cavity: side wall + back cap at z = length; open at z=0.
+    Returns a list of (p0, p1, p2) global triangles with inward-facing CCW order."""
+    tris = []
+    th = np.linspace(0., 2. * np.pi, n_theta + 1)
+    zs = np.linspace(0., length, n_z + 1)
+    for i in range(n_theta):
+        for j in range(n_z):
+            a = np.r_[radius * np.cos(th[i]), radius * np.sin(th[i]), zs[j]]
+            b = np.r_[radius * np.cos(th[i + 1]), radius * np.sin(th[i + 1]), zs[j]]
+            c = np.r_[radius * np.cos(th[i + 1]), radius * np.sin(th[i + 1]), zs[j + 1]]
+            d = np.r_[radius * np.cos(th[i]), radius * np.sin(th[i]), zs[j + 1]]
+            tris += [(a, c, b), (a, d, c)]
+    centre = np.r_[0., 0., length]
+    for i in range(n_theta):
+        b = np.r_[radius * np.cos(th[i]), radius * np.sin(th[i]), length]
+        c = np.r_[radius * np.cos(th[i + 1]), radius * np.sin(th[i + 1]), length]
+        tris.append((centre, c, b))
+    return tris
+
+
+def triangle_object(T, p0, p1, p2, optics):
+    """One AssembledObject per triangle, as ray_trace_utils/stl_utils.py:213-227:
+    frame with origin p0, x along p1-p0, z along the normal; BoundaryBox = AABB."""
+    e0, e1 = p1 - p0, p2 - p0
+    z = np.cross(e0, e1)
+    z /= np.sqrt(np.sum(z ** 2))
+    x = e0 / np.sqrt(np.sum(e0 ** 2))
+    y = np.cross(z, x)
+    rot = np.vstack((x, y, z)).T
+    frame = np.eye(4)
+    frame[:3, :3] = rot
+    frame[:3, 3] = p0
+    verts = np.dot(rot.T, np.vstack((e0, e1)).T)
+    verts[2] = 0.
+    surf = T.surface.Surface(T.triangular_face.TriangularFace(verts), optics)
+    pts = np.vstack((p0, p1, p2))
+    local = np.dot(rot.T, (pts - p0).T)
+    box = T.boundary_shape.BoundaryBox(np.array([local.min(axis=1) - 1e-9, local.max(axis=1) + 1e-9]))
+    return T.object.AssembledObject(surfs=[surf], bounds=[box], transform=frame)
+
+
+def c4_cavity(T, n_rays=2000, n_theta=8, n_z=4, absorptivity=0.7):
+    """Config 4 (reduced): triangulated cylindrical cavity, Lambertian multi-bounce."""
+    objs = [triangle_object(T, p0, p1, p2, T.optics_callables.LambertianReceiver(absorptivity))
+            for (p0, p1, p2) in cylinder_mesh(n_theta, n_z)]
+    asm = T.assembly.Assembly(objects=objs)
+
+    def source():
+        return T.sources.disk_bundle(n_rays, np.c_[[0., 0., -0.01]], np.r_[0., 0., 1.], 0.9, np.pi / 4., flux=1000.)
+    return asm, source
+
+
+def c5_cavity(T, n_rays=2000, spectral=False):
+    """Config 5 (one pass): Holman ex. 8.17-like cylinder cavity made of quadric
+    surfaces: aperture disk, three cylinder sections, flat back
+    (emissive_losses/emissive_losses_test.py:38).  Rays are emitted from the
+    aperture into the cavity.  ``spectral`` puts directional-spectral optics on the walls."""
+    oc = T.optics_callables
+    R, depth = 0.01, 0.01
+    if spectral:
+        thetas = np.linspace(0., np.pi / 2., 10)
+        wls = np.linspace(0.3e-6, 2.5e-6, 12)
+        table = 0.5 + 0.4 * np.outer(np.cos(thetas), np.linspace(1., 0.5, 12))
+
+        def wall():
+            return oc.Lambertian_directional_axisymmetric_piecewise_spectralReceiver(thetas, table, wls)
+    else:
+        def wall():
+            return oc.LambertianReceiver(1.)
+    objs = [T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RoundPlateGM(R), oc.LambertianReceiver(1.))],
+                                     transform=T.spatial_geometry.rotx(np.pi))]
+    for k in range(3):
+        objs.append(T.object.AssembledObject(
+            surfs=[T.surface.Surface(T.cylinder.FiniteCylinder(2. * R, depth), wall())],
+            transform=T.spatial_geometry.translate(0., 0., (k + 0.5) * depth)))
+    objs.append(T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RoundPlateGM(R), wall())],
+                                         transform=T.spatial_geometry.translate(0., 0., 3. * depth)))
+    asm = T.assembly.Assembly(objects=objs)
+
+    def source():
+        b = T.sources.disk_bundle(n_rays, np.c_[[0., 0., 1e-6]], np.r_[0., 0., 1.], R, np.pi / 2., flux=1.)
+        if spectral:
+            wl = np.random.uniform(0.3e-6, 2.5e-6, size=n_rays)
+            b = T.ray_bundle.RayBundle(vertices=b.get_vertices(), directions=b.get_directions(),
+                                       energy=b.get_energy(), wavelengths=wl)
+        return b
+    return asm, source
+
+
+def gm_zoo(T):
+    """name -> (geometry manager factory, frame) covering every supported GM kind."""
+    sg = T.spatial_geometry
+    tilt = np.dot(sg.translate(0.1, -0.2, 0.3), np.dot(sg.rotx(0.3), sg.roty(-0.2)))
+    F, P, S, C, Y, Q = T.flat_surface, T.paraboloid, T.sphere_surface, T.cone, T.cylinder, T.quadratic_surface
+    return {
+        'flat': (lambda: F.FlatGeometryManager(), tilt),
+        'rect': (lambda: F.RectPlateGM(1.5, 1.), tilt),
+        'rect_extruded': (lambda: F.ExtrudedRectPlateGM(1.5, 1., np.c_[[0.1, 0.05]], 0.4, 0.3), tilt),
+        'round': (lambda: F.RoundPlateGM(0.9, 0.3), tilt),
+        'round_cut': (lambda: F.StraightCutRoundPlateGM(0.9, 0.4), tilt),
+        'triangle': (lambda: T.triangular_face.TriangularFace(np.array([[1., 0.2], [0., 0.9], [0., 0.]])), tilt),
+        'paraboloid': (lambda: P.Paraboloid(1.5, 2.), tilt),
+        'dish': (lambda: P.ParabolicDishGM(2., 1.), tilt),
+        'hex_dish': (lambda: P.HexagonalParabolicDishGM(2., 1.), tilt),
+        'rect_dish': (lambda: P.RectangularParabolicDishGM(1.5, 1., 1.), tilt),
+        'parab_cyl': (lambda: P.ParabolicCylinder(1.5), tilt),
+        'trough': (lambda: P.ParabolicTroughGM(2., 1., 1.5), tilt),
+        'sphere': (lambda: S.SphericalGM(0.8), tilt),
+        'hemisphere': (lambda: S.HemisphereGM(0.8), tilt),
+        'cut_sphere': (lambda: S.CutSphereGM(0.8, T.boundary_shape.BoundarySphere(radius=1.6, location=np.r_[0.1, -0.2, -1.1])), tilt),
+        'sphere_rect': (lambda: S.SphericalRectFacet(0.8, 0.9, 0.7), tilt),
+        'cone_inf': (lambda: C.InfiniteCone(0.5, 0.1), tilt),
+        'cone': (lambda: C.FiniteCone(0.7, 1.2), tilt),
+        'frustum': (lambda: C.ConicalFrustum(0.1, 0.3, 0.9, 0.8), tilt),
+        'frustum_rect': (lambda: C.RectCutConicalFrustum(0.1, 0.5, 0.9, 0.9, 1.2, 1.5), tilt),
+        'cyl_inf': (lambda: Y.InfiniteCylinder(1.2), tilt),
+        'cyl': (lambda: Y.FiniteCylinder(1.2, 1., [0.3, 5.5]), tilt),
+        'cyl_rect': (lambda: Y.RectCutCylinder(1.2, 1., 1.0, 1.1), tilt),
+        'quadric_flat': (lambda: Q.FlatQuadricSurfaceGM(0.2, 0.1, 0.05, 0.02, -0.03, 0.01), tilt),
+        'quadric_rect': (lambda: Q.RectFlatQuadricSurfaceGM(1.5, 1., 0.2, 0.1, 0.05, 0.02, -0.03, 0.01), tilt),
+    }
+
+
+def zoo_scene(T, name, optics=None):
+    make, frame = gm_zoo(T)[name]
+    opt = optics if optics is not None else T.optics_callables.ReflectiveReceiver(0.1)
+    # ReflectiveReceiver exists in both packages; add normals through a second accountant class
+    obj = T.object.AssembledObject(surfs=[T.surface.Surface(make(), opt)], transform=frame.copy())
+    return T.assembly.Assembly(objects=[obj])
+
+
+def zoo_rays(T, n, seed):
+    """Rays from a shell of radius ~3 around the origin aimed at a jittered
+    point near the surface, plus rays starting inside the shapes."""
+    rng = np.random.RandomState(seed)
+    p = rng.normal(size=(3, n))
+    p = 3. * p / np.sqrt(np.sum(p ** 2, axis=0))
+    inside = rng.rand(n) < 0.25
+    p[:, inside] = rng.uniform(-0.5, 0.5, size=(3, int(inside.sum())))
+    target = rng.uniform(-0.8, 0.8, size=(3, n)) + np.c_[[0.1, -0.2, 0.3]]
+    d = target - p
+    d /= np.sqrt(np.sum(d ** 2, axis=0))
+    return T.ray_bundle.RayBundle(vertices=p, directions=d, energy=np.ones(n))

@@ -1,0 +1,215 @@
+// Optics + accounting kernel, row gather, per-surface sums, flux-map binning.
+#include "common.cuh"
+#include "geom.cuh"
+#include "optics.cuh"
+#include "philox.cuh"
+
+using namespace trc;
+
+namespace {
+
+struct OpticsParams {
+    int64_t h;
+    const int32_t *slot_parent;
+    const int32_t *slot_surf;
+    const double *vert, *dir, *energy, *wavelengths;
+    int64_t ld_in;
+    double *o_vert, *o_dir, *o_energy;
+    int64_t *o_parents;
+    int64_t ld_out;
+    const double *draws[3];
+    uint64_t seed;
+    uint32_t bounce;
+    double min_energy;
+    double *absorbed;
+    double *normals;
+    int32_t *cull;
+};
+
+// Philox draws in the units the reference's numpy calls produce
+// (normal(scale=sigma), uniform(0, 2pi), uniform(0, 1)) for one slot.
+__device__ __forceinline__ void philox_draws(const TrcSurfaceRec *s, uint64_t seed, uint32_t bounce, uint64_t q,
+                                             double *u) {
+    const double two_pi = 2.0 * M_PI;
+    switch (s->okind) {
+    case TRC_O_REAL_REFLECTIVE: {
+        if (!(s->op[1] > 0.0)) break;
+        double a, b;
+        normal2(seed, q, bounce, 0, a, b);
+        if (s->op[2] != 0.0) { u[0] = a * s->op[1]; u[1] = b * s->op[1]; }
+        else {
+            double c, e;
+            uniform2(seed, q, bounce, 1, c, e);
+            u[0] = a * s->op[1]; u[1] = two_pi * c;
+        }
+        break;
+    }
+    case TRC_O_LAMBERTIAN: case TRC_O_LAMB_DIRECTIONAL: case TRC_O_LAMB_DIRECTIONAL_SPECTRAL: {
+        double a, b;
+        uniform2(seed, q, bounce, 0, a, b);
+        u[0] = two_pi * a; u[1] = b;
+        break;
+    }
+    case TRC_O_LAMBERTIAN_SPECULAR: case TRC_O_LAMBSPEC_DIRECTIONAL: {
+        double a, b, c, e;
+        uniform2(seed, q, bounce, 0, a, b);
+        uniform2(seed, q, bounce, 1, c, e);
+        u[0] = a; u[1] = two_pi * b; u[2] = c;
+        break;
+    }
+    default: break;
+    }
+}
+
+// One thread per child slot q (surface-major, parent-minor order).  Gathers the
+// parent ray, recomputes the hit on the known surface (same arithmetic as the
+// nearest-hit kernel, hence the same bits), applies the optics and writes the
+// child coalesced.  Replaces Surface.select_rays/get_outgoing (surface.py:72-94)
+// for every surface at once.
+__global__ void __launch_bounds__(256)
+optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict__ tables, OpticsParams p) {
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= p.h) return;
+    int64_t r = p.slot_parent[q];
+    int sidx = p.slot_surf[q];
+    const TrcSurfaceRec *s = &surfs[sidx];
+    V3 v = mk(p.vert[r], p.vert[p.ld_in + r], p.vert[2 * p.ld_in + r]);
+    V3 d = mk(p.dir[r], p.dir[p.ld_in + r], p.dir[2 * p.ld_in + r]);
+    double e_in = p.energy[r];
+    double wl = p.wavelengths ? p.wavelengths[r] : 0.0;
+    double t = intersect(s, v, d);
+    V3 hit = axpy(v, t, d);
+    V3 n = surface_normal(s, hit, d);
+    double u[3] = {0.0, 0.0, 0.0};
+    if (p.draws[0]) {
+        u[0] = p.draws[0][q];
+        if (p.draws[1]) u[1] = p.draws[1][q];
+        if (p.draws[2]) u[2] = p.draws[2][q];
+    } else {
+        philox_draws(s, p.seed, p.bounce, (uint64_t)q, u);
+    }
+    OpticsOut o = apply_optics(s, tables, d, n, e_in, wl, u);
+    if (s->flags & TRC_F_ONE_SIDED) {
+        // OneSided*: rays arriving along +z of the surface lose all energy
+        // (optics_callables.py:201-212, :498-504)
+        const double *f = s->frame;
+        double proj = d.x * f[2] + d.y * f[6] + d.z * f[10];
+        if (proj > 0.0) o.energy = 0.0;
+    }
+    p.o_vert[q] = hit.x; p.o_vert[p.ld_out + q] = hit.y; p.o_vert[2 * p.ld_out + q] = hit.z;
+    p.o_dir[q] = o.dir.x; p.o_dir[p.ld_out + q] = o.dir.y; p.o_dir[2 * p.ld_out + q] = o.dir.z;
+    p.o_energy[q] = o.energy;
+    p.o_parents[q] = r;
+    if (p.absorbed) p.absorbed[q] = e_in - o.energy;
+    if (p.normals) { p.normals[q] = n.x; p.normals[p.ld_out + q] = n.y; p.normals[2 * p.ld_out + q] = n.z; }
+    if (p.cull) p.cull[q] = (o.energy <= p.min_energy) ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(int64_t n_out, const int32_t *__restrict__ idx, int n_rows,
+                   const double *__restrict__ in, int64_t ld_in, double *__restrict__ out, int64_t ld_out,
+                   const int64_t *__restrict__ in_i64, int64_t *__restrict__ out_i64) {
+    int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_out) return;
+    int64_t src = idx[j];
+    for (int r = 0; r < n_rows; ++r) out[(int64_t)r * ld_out + j] = in[(int64_t)r * ld_in + src];
+    if (in_i64) out_i64[j] = in_i64[src];
+}
+
+// one warp per surface segment
+__global__ void segment_sums_kernel(int32_t n_keys, const int64_t *__restrict__ off,
+                                    const double *__restrict__ values, double *__restrict__ totals) {
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= n_keys) return;
+    int64_t a = off[warp], b = off[warp + 1];
+    double acc = 0.0;
+    for (int64_t i = a + lane; i < b; i += 32) acc += values[i];
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if (lane == 0 && b > a) totals[warp] += acc;
+}
+
+struct Proj { double m[12]; };
+
+// histogram2d semantics: bins [e_k, e_{k+1}) with the last bin closed, edges
+// from linspace(-h, h, n+1) (flat_surface.py:241-244).
+__device__ __forceinline__ int bin_index(double x, double half, int nb) {
+    if (x < -half || x > half) return -1;
+    double w = 2.0 * half / nb;
+    int k = (int)floor((x + half) / w);
+    if (k >= nb) k = nb - 1;
+    if (k < 0) k = 0;
+    return k;
+}
+
+__global__ void __launch_bounds__(256)
+fluxmap_rect_kernel(int64_t n, const double *__restrict__ hits, int64_t ld, const double *__restrict__ energy,
+                    Proj pr, double hx, double hy, int nx, int ny, double *__restrict__ bins) {
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        V3 g = mk(hits[i], hits[ld + i], hits[2 * ld + i]);
+        double lx = pr.m[0] * g.x + pr.m[1] * g.y + pr.m[2] * g.z + pr.m[3];
+        double ly = pr.m[4] * g.x + pr.m[5] * g.y + pr.m[6] * g.z + pr.m[7];
+        int ix = bin_index(lx, hx, nx), iy = bin_index(ly, hy, ny);
+        if (ix < 0 || iy < 0) continue;
+        atomicAdd(&bins[ix * ny + iy], energy[i]);
+    }
+}
+
+}  // namespace
+
+extern "C" int trc_optics(const TrcScene *sc, const TrcOpticsArgs *a, void *stream) {
+    if (!sc || !a || a->h < 0) return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: bad argument%s");
+    if (a->h == 0) return TRC_OK;
+    if (!a->d_slot_parent || !a->d_slot_surf || !a->d_vertices || !a->d_directions || !a->d_energy ||
+        !a->d_out_vertices || !a->d_out_directions || !a->d_out_energy || !a->d_out_parents || a->ld_out < a->h)
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: null buffer or bad stride%s");
+    OpticsParams p;
+    p.h = a->h; p.slot_parent = a->d_slot_parent; p.slot_surf = a->d_slot_surf;
+    p.vert = a->d_vertices; p.dir = a->d_directions; p.energy = a->d_energy; p.wavelengths = a->d_wavelengths;
+    p.ld_in = a->ld_in;
+    p.o_vert = a->d_out_vertices; p.o_dir = a->d_out_directions; p.o_energy = a->d_out_energy;
+    p.o_parents = a->d_out_parents; p.ld_out = a->ld_out;
+    for (int k = 0; k < 3; ++k) p.draws[k] = a->d_draws[k];
+    p.seed = a->seed; p.bounce = a->bounce; p.min_energy = a->min_energy;
+    p.absorbed = a->d_absorbed; p.normals = a->d_normals; p.cull = a->d_cull;
+    int64_t blocks = (a->h + 255) / 256;
+    optics_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(sc->d_surfaces, sc->d_tables, p);
+    return check_launch("optics");
+}
+
+extern "C" int trc_gather_rows(int64_t n_out, const int32_t *d_idx, int32_t n_rows, const double *d_in,
+                               int64_t ld_in, double *d_out, int64_t ld_out, const int64_t *d_in_i64,
+                               int64_t *d_out_i64, void *stream) {
+    if (n_out < 0 || n_rows < 0 || (n_out > 0 && (!d_idx || (n_rows > 0 && (!d_in || !d_out)))))
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_gather_rows: bad argument%s");
+    if (n_out == 0) return TRC_OK;
+    int64_t blocks = (n_out + 255) / 256;
+    gather_rows_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(n_out, d_idx, n_rows, d_in, ld_in, d_out,
+                                                                           ld_out, d_in_i64, d_out_i64);
+    return check_launch("gather_rows");
+}
+
+extern "C" int trc_segment_sums(int32_t n_keys, const int64_t *d_offsets, const double *d_values,
+                                double *d_totals, void *stream) {
+    if (n_keys < 1 || !d_offsets || !d_values || !d_totals)
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_segment_sums: bad argument%s");
+    int64_t threads = (int64_t)n_keys * 32;
+    segment_sums_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n_keys, d_offsets,
+                                                                                             d_values, d_totals);
+    return check_launch("segment_sums");
+}
+
+extern "C" int trc_fluxmap_rect(int64_t n, const double *d_hits, int64_t ld, const double *d_energy,
+                                const double *proj12, double hx, double hy, int32_t nx, int32_t ny,
+                                double *d_bins, void *stream) {
+    if (n < 0 || !proj12 || nx < 1 || ny < 1 || !d_bins || (n > 0 && (!d_hits || !d_energy)))
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_fluxmap_rect: bad argument%s");
+    if (n == 0) return TRC_OK;
+    Proj pr;
+    for (int k = 0; k < 12; ++k) pr.m[k] = proj12[k];
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    fluxmap_rect_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(n, d_hits, ld, d_energy, pr, hx, hy, nx,
+                                                                            ny, d_bins);
+    return check_launch("fluxmap_rect");
+}

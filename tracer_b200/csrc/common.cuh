@@ -1,0 +1,44 @@
+// Shared host-side helpers of the C ABI translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/tracer_b200.h"
+
+// thread-local last-error text, defined in tracer_b200.cu
+char *trc_err_buf();
+static const int TRC_ERR_BUF = 512;
+
+static inline int fail(int code, const char *fmt, const char *detail = "") {
+    snprintf(trc_err_buf(), TRC_ERR_BUF, fmt, detail);
+    return code;
+}
+#define TRC_CUDA(call)                                                         \
+    do {                                                                       \
+        cudaError_t e_ = (call);                                               \
+        if (e_ != cudaSuccess) return fail(TRC_ERR_CUDA, #call ": %s", cudaGetErrorString(e_)); \
+    } while (0)
+
+static inline int check_launch(const char *what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        snprintf(trc_err_buf(), TRC_ERR_BUF, "%s launch: %s", what, cudaGetErrorString(e));
+        return TRC_ERR_CUDA;
+    }
+    return TRC_OK;
+}
+
+// Device-side scene tables; owned by the library (trc_scene_create/destroy).
+struct TrcScene {
+    int32_t n_surfaces = 0;
+    TrcSurfaceRec *d_surfaces = nullptr;
+    double *d_tables = nullptr;
+    int32_t n_table = 0;
+    TrcBvhNode *d_nodes = nullptr;
+    int32_t n_nodes = 0;
+    int32_t *d_leaf_surfaces = nullptr;
+    int32_t n_leaf_surfaces = 0;
+    int32_t *d_unbounded = nullptr;
+    int32_t n_unbounded = 0;
+    int num_sms = 148;
+};

@@ -1,0 +1,171 @@
+// Optics callables on device: given the incoming direction, the surface normal
+// at the hit and up to three random draws, produce the outgoing direction and
+// energy.  Mirrors the semantics (not the structure) of optics.reflections
+// (optics.py:145-157) and the optics classes of optics_callables.py:93-627.
+#pragma once
+#include "geom.cuh"
+
+namespace trc {
+
+// optics.reflections: d - 2 (d.n) n
+__device__ __forceinline__ V3 reflect(V3 d, V3 n) {
+    double k = dot(d, n);
+    return mk(d.x - 2.0 * (k * n.x), d.y - 2.0 * (k * n.y), d.z - 2.0 * (k * n.z));
+}
+
+// numpy.round(x, 14) as used by general_axis_rotation (spatial_geometry.py:18)
+__device__ __forceinline__ double round14(double x) { return rint(x * 1e14) / 1e14; }
+
+// rotate_z_to_normal (ray_trace_utils/vector_manipulations.py:56-74): the
+// minimal rotation taking +z to `n`, applied to `e`.  Axis = z x n normalised
+// (x-hat when degenerate), angle = acos(n.z), Rodrigues matrix with sin/cos
+// rounded to 14 decimals, identity when the angle is exactly 0.
+__device__ __forceinline__ V3 rotate_z_to_normal(V3 e, V3 n) {
+    double ax = -n.y, ay = n.x;
+    double len = sqrt(ax * ax + ay * ay);
+    ax /= len; ay /= len;
+    if (!(ax == ax)) { ax = 1.0; ay = 0.0; }
+    double ang = acos(n.z);
+    if (ang == 0.0) return e;
+    double s = round14(sin(ang)), c = round14(cos(ang)), w = 1.0 - c;
+    // R = outer(a,a) w + I c + [a]x s with a = (ax, ay, 0)
+    double r00 = ax * ax * w + c, r01 = ax * ay * w,     r02 = ay * s;
+    double r10 = ay * ax * w,     r11 = ay * ay * w + c, r12 = -ax * s;
+    double r20 = -ay * s,         r21 = ax * s,          r22 = c;
+    return mk(r00 * e.x + r01 * e.y + r02 * e.z,
+              r10 * e.x + r11 * e.y + r12 * e.z,
+              r20 * e.x + r21 * e.y + r22 * e.z);
+}
+
+// rotation_to_z(n) applied to a local direction a (spatial_geometry.py:24-48
+// as used by Lambertian.__call__, optics_callables.py:163-165):
+// x' = (n.y, -n.x, 0)/|.| (x-hat if degenerate), y' = n x x', z' = n.
+__device__ __forceinline__ V3 rotation_to_z_apply(V3 n, V3 a) {
+    double px = n.y, py = -n.x;
+    if (px == 0.0 && py == 0.0) { px = 1.0; py = 0.0; }
+    double len = sqrt(px * px + py * py);
+    px /= len; py /= len;
+    // y' = n x (px, py, 0)
+    double qx = n.y * 0.0 - n.z * py;
+    double qy = n.z * px - n.x * 0.0;
+    double qz = n.x * py - n.y * px;
+    return mk(px * a.x + qx * a.y + n.x * a.z,
+              py * a.x + qy * a.y + n.y * a.z,
+              0.0 * a.x + qz * a.y + n.z * a.z);
+}
+
+// pillbox_sunshape_directions / Lambertian_directions (sources.py:88-117):
+// xi1 in [0, 2pi), xi2 in [0, 1).
+__device__ __forceinline__ V3 pillbox_direction(double xi1, double xi2, double ang_range) {
+    if (ang_range == 0.0) return mk(0.0, 0.0, 1.0);
+    double ss = sin(ang_range) * sqrt(xi2);
+    return mk(cos(xi1) * ss, sin(xi1) * ss, sqrt(1.0 - ss * ss));
+}
+
+// numpy.interp(x, xp, fp) for increasing xp (clamped at the ends).
+__device__ __forceinline__ double interp1(double x, const double *xp, const double *fp, int n) {
+    if (x <= xp[0]) return fp[0];
+    if (x >= xp[n - 1]) return fp[n - 1];
+    int lo = 0, hi = n - 1;
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (xp[mid] <= x) lo = mid; else hi = mid;
+    }
+    double slope = (fp[lo + 1] - fp[lo]) / (xp[lo + 1] - xp[lo]);
+    return slope * (x - xp[lo]) + fp[lo];
+}
+
+// Bilinear lookup on a regular (theta, wavelength) grid, the "linear" method of
+// scipy.interpolate.RegularGridInterpolator used at optics_callables.py:371.
+// Layout at xp: thetas[nth], wavelengths[nwl], values[nth*nwl] (row-major).
+__device__ __forceinline__ int grid_cell(double x, const double *g, int n) {
+    int lo = 0, hi = n - 1;
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (g[mid] <= x) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+__device__ __forceinline__ double interp2(double th, double wl, const double *xp, int nth, int nwl) {
+    const double *gt = xp, *gw = xp + nth, *val = xp + nth + nwl;
+    int i = grid_cell(th, gt, nth), j = grid_cell(wl, gw, nwl);
+    double a = (th - gt[i]) / (gt[i + 1] - gt[i]);
+    double b = (wl - gw[j]) / (gw[j + 1] - gw[j]);
+    double v00 = val[i * nwl + j], v01 = val[i * nwl + j + 1];
+    double v10 = val[(i + 1) * nwl + j], v11 = val[(i + 1) * nwl + j + 1];
+    return (1.0 - a) * ((1.0 - b) * v00 + b * v01) + a * ((1.0 - b) * v10 + b * v11);
+}
+
+struct OpticsOut { V3 dir; double energy; };
+
+// u[0..2]: draws already in the reference's units: normal(scale=sigma) values,
+// uniform(0, 2pi) angles, uniform(0,1) variates (see TrcOpticsArgs).
+__device__ __forceinline__ OpticsOut apply_optics(const TrcSurfaceRec *s, const double *tables,
+                                                  V3 d, V3 n, double e_in, double wavelength,
+                                                  const double *u) {
+    OpticsOut o;
+    const double *op = s->op;
+    switch (s->okind) {
+    case TRC_O_TRANSPARENT:
+        o.dir = d; o.energy = e_in; break;
+    case TRC_O_REFLECTIVE:
+        o.dir = reflect(d, n); o.energy = e_in * (1.0 - op[0]); break;
+    case TRC_O_REAL_REFLECTIVE: {
+        V3 rn = n;
+        if (op[1] > 0.0) {
+            V3 e;
+            if (op[2] != 0.0) {  // bi-variate slope error (optics_callables.py:235-243)
+                double tx = tan(u[0]), ty = tan(u[1]);
+                double ez = sqrt(1.0 / (1.0 + tx * tx + ty * ty));
+                e = mk(tx * ez, ty * ez, ez);
+            } else {             // conical (:245-250)
+                double st = sin(u[0]);
+                e = mk(st * cos(u[1]), st * sin(u[1]), cos(u[0]));
+            }
+            rn = rotate_z_to_normal(e, n);
+            double len = sqrt(rn.x * rn.x + rn.y * rn.y + rn.z * rn.z);
+            rn = mk(rn.x / len, rn.y / len, rn.z / len);
+        }
+        o.dir = reflect(d, rn); o.energy = e_in * (1.0 - op[0]); break;
+    }
+    case TRC_O_LAMBERTIAN: {
+        V3 a = pillbox_direction(u[0], u[1], op[1]);
+        o.dir = rotation_to_z_apply(n, a); o.energy = e_in * (1.0 - op[0]); break;
+    }
+    case TRC_O_LAMBERTIAN_SPECULAR: {
+        if (u[0] < op[1]) o.dir = reflect(d, n);
+        else o.dir = rotation_to_z_apply(n, pillbox_direction(u[1], u[2], M_PI / 2.0));
+        o.energy = e_in * (1.0 - op[0]); break;
+    }
+    case TRC_O_LAMB_DIRECTIONAL: case TRC_O_LAMBSPEC_DIRECTIONAL: case TRC_O_LAMB_DIRECTIONAL_SPECTRAL: {
+        // optics_callables.py:340-358, :370-388, :437-455: absorptance looked up
+        // by the incidence angle acos(|(d.n) n|).
+        const double *xp = tables + s->table_off;
+        int nth = s->table_len;
+        double k = dot(d, n);
+        V3 vert = mk(k * n.x, k * n.y, k * n.z);
+        double th = acos(sqrt(vert.x * vert.x + vert.y * vert.y + vert.z * vert.z));
+        double ab;
+        if (s->okind == TRC_O_LAMB_DIRECTIONAL_SPECTRAL) ab = interp2(th, wavelength, xp, nth, (int)op[1]);
+        else ab = interp1(th, xp, xp + nth, nth);
+        if (s->okind == TRC_O_LAMBSPEC_DIRECTIONAL) {
+            if (u[0] < op[0]) o.dir = reflect(d, n);
+            else o.dir = rotation_to_z_apply(n, pillbox_direction(u[1], u[2], M_PI / 2.0));
+        } else {
+            o.dir = rotation_to_z_apply(n, pillbox_direction(u[0], u[1], M_PI / 2.0));
+        }
+        o.energy = e_in * (1.0 - ab); break;
+    }
+    case TRC_O_REFLECTIVE_SPECTRAL: {
+        const double *xp = tables + s->table_off;
+        const double *fp = xp + s->table_len;
+        o.dir = reflect(d, n);
+        o.energy = e_in * (1.0 - interp1(wavelength, xp, fp, s->table_len)); break;
+    }
+    default:
+        o.dir = d; o.energy = e_in; break;
+    }
+    return o;
+}
+
+}  // namespace trc

@@ -1,0 +1,279 @@
+"""Optics-manager descriptions and accountants with the reference's names.
+
+Reference: tracer/optics_callables.py.  There, each class is a callable doing
+NumPy work per surface per bounce, and a factory (:1942-2092) generates ~20 000
+``<Optics><Accountants...>`` classes at import.  Here the optics run inside the
+CUDA optics kernel (csrc/optics.cuh); these classes hold parameters only, and
+accountant-composed classes are synthesised on demand from their *name* by the
+module-level ``__getattr__`` (PEP 562), using the reference's naming rules:
+
+    <Optics> + shorthands in the order Absorber, Attenuator, Receptor,
+    Scatterer, Polychromatic, Spectral, Location, Directional, Normal
+    aliases: Receiver = Location+Absorber, Detector = Directional+Location+
+    Absorber, Transmitter = Location+Scatterer   (optics_callables.py:2063-2074)
+
+e.g. ``ReflectiveReceiver``, ``LambertianReceiver``, ``OneSidedReflectiveReceiver``,
+``OneSidedRealReflectiveDetector``.  ``get_all_hits()`` returns the accountants'
+data in the reference's order (energy, spectral, location, directions, normals).
+The GPU engine appends one array per bounce to the accountants' lists
+(``_absorbed``, ``_hits`` ...), exactly what Accountant.count would have stored.
+"""
+import sys
+from copy import deepcopy
+
+import numpy as np
+
+
+def copy_optical_manager(opt):
+    newopt = deepcopy(opt)
+    if hasattr(newopt, 'reset'):
+        newopt.reset()
+    return newopt
+
+
+class _OpticsDescription(object):
+    """Common base: optics are evaluated on the GPU, never called on the host."""
+
+    def __call__(self, geometry, rays, selector):
+        raise TypeError(
+            f"{type(self).__name__} is a description; optics run on the GPU through "
+            "TracerEngine.ray_tracer (no CPU path)")
+
+
+class Transparent(_OpticsDescription):
+    """Passes rays through unchanged (optics_callables.py:93)."""
+
+    def __init__(self):
+        pass
+
+
+class Reflective(_OpticsDescription):
+    """Specular, opaque, grey absorptivity (optics_callables.py:116)."""
+
+    def __init__(self, absorptivity):
+        self._abs = absorptivity
+
+
+class Lambertian(_OpticsDescription):
+    """Ideal diffuse reflector within ``ang_range`` of the normal (:143)."""
+
+    def __init__(self, absorptivity=0., ang_range=np.pi / 2.):
+        self._abs = absorptivity
+        self._ang_range = ang_range
+
+
+class Reflective_spectral(_OpticsDescription):
+    """Specular with absorptance interpolated in wavelength (:178)."""
+
+    def __init__(self, absorptances, wavelengths):
+        self._wavelengths = wavelengths
+        self._absorptances = absorptances
+
+
+class OneSidedReflective(Reflective):
+    """Reflective from +z; rays arriving from behind lose their energy (:195)."""
+
+
+class RealReflective(_OpticsDescription):
+    """Specular with Gaussian slope error, bi-variate or conical (:214)."""
+
+    def __init__(self, absorptivity, sigma, bi_var=False):
+        self._abs = absorptivity
+        self._sig = sigma
+        self.bi_var = bi_var
+
+
+class OneSidedRealReflective(RealReflective):
+    """(:492)"""
+
+
+class LambertianSpecular(_OpticsDescription):
+    """Per-ray choice between specular and diffuse reflection (:553)."""
+
+    def __init__(self, absorptivity=0., specularity=0.5):
+        self._abs = absorptivity
+        self.specularity = specularity
+
+
+class Lambertian_directional_axisymmetric_piecewise(_OpticsDescription):
+    """Diffuse; absorptance interpolated in the incidence angle (:331)."""
+
+    def __init__(self, thetas, absorptance_th, specularity=0.):
+        self.thetas = thetas
+        self.abs_th = absorptance_th
+        self.specularity = specularity
+
+
+class LambertianSpecular_directional_axisymmetric_piecewise(_OpticsDescription):
+    """Specular/diffuse mix; absorptance interpolated in the incidence angle (:427)."""
+
+    def __init__(self, thetas, absorptance_th, specularity=0.):
+        self.thetas = thetas
+        self.abs_th = absorptance_th
+        self.specularity = specularity
+
+
+class Lambertian_directional_axisymmetric_piecewise_spectral(_OpticsDescription):
+    """Diffuse; absorptance bilinear in (incidence angle, wavelength) (:359)."""
+
+    def __init__(self, thetas, absorptance, wavelengths):
+        self.thetas, self.wavelengths = np.unique(thetas), np.unique(wavelengths)
+        self.absorptance = np.reshape(absorptance, (len(self.thetas), len(self.wavelengths)))
+
+
+perfect_mirror = Reflective(0)
+
+_BASE_OPTICS = {c.__name__: c for c in (
+    Transparent, Reflective, Lambertian, Reflective_spectral, OneSidedReflective, RealReflective,
+    OneSidedRealReflective, LambertianSpecular, Lambertian_directional_axisymmetric_piecewise,
+    LambertianSpecular_directional_axisymmetric_piecewise,
+    Lambertian_directional_axisymmetric_piecewise_spectral)}
+
+# Optics of the reference that are outside the north-star path (SURVEY 8a row
+# O8 / 8f N4): constructing them says so instead of silently mis-tracing.
+_UNSUPPORTED = (
+    'Refractive', 'RefractiveHomogenous', 'RefractiveAbsorbantHomogenous', 'RefractiveScattering',
+    'RefractiveScatteringHomogenous', 'Scattering', 'ScatteringPeriodicBoundary', 'PeriodicBoundary',
+    'Absorbant', 'LambertianAbsorbant', 'FresnelConductorHomogenous', 'SemiLambertian', 'BiFacial',
+    'Reflective_IAM', 'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM',
+    'Lambertian_directional_axisymmetric_piecewise_Polychromatic',
+    'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise')
+
+
+# ------------------------------------------------------------ accountants
+class Accountant(object):
+    """Per-surface result store (optics_callables.py:1577-1595).  ``field`` is
+    the list attribute the engine appends per-bounce arrays to."""
+    shorthand = None
+    field = None
+    vector = False
+
+    def __init__(self):
+        self.reset()
+
+    def reset(self):
+        setattr(self, self.field, [])
+
+    def get_data(self):
+        chunks = getattr(self, self.field)
+        if self.vector:
+            chunks = [c for c in chunks if c.shape[1]]
+            return np.hstack(chunks) if chunks else np.array([]).reshape(3, 0)
+        chunks = [c for c in chunks if len(c)]
+        return np.hstack(chunks) if chunks else np.array([])
+
+
+class AbsorptionAccountant(Accountant):
+    shorthand, field = 'Absorber', '_absorbed'
+
+
+class AttenuationAccountant(Accountant):
+    shorthand, field = 'Attenuator', '_attenuated'
+
+
+class ReceptionAccountant(Accountant):
+    shorthand, field = 'Receptor', '_received'
+
+
+class ScatteringAccountant(Accountant):
+    shorthand, field = 'Scatterer', '_scattered'
+
+
+class PolychromaticAccountant(Accountant):
+    shorthand, field = 'Polychromatic', '_spectra'
+
+
+class SpectralAccountant(Accountant):
+    shorthand, field = 'Spectral', '_wavelengths'
+
+
+class LocationAccountant(Accountant):
+    shorthand, field, vector = 'Location', '_hits', True
+
+
+class DirectionAccountant(Accountant):
+    shorthand, field, vector = 'Directional', '_directions', True
+
+
+class NormalAccountant(Accountant):
+    shorthand, field, vector = 'Normal', '_normals', True
+
+
+# canonical order = get_all_hits() order (optics_callables.py:2063-2068)
+_ACCOUNTANTS = (AbsorptionAccountant, AttenuationAccountant, ReceptionAccountant, ScatteringAccountant,
+                PolychromaticAccountant, SpectralAccountant, LocationAccountant, DirectionAccountant,
+                NormalAccountant)
+_ALIASES = {'Receiver': ('Location', 'Absorber'),
+            'Detector': ('Directional', 'Location', 'Absorber'),
+            'Transmitter': ('Location', 'Scatterer')}
+
+
+class OpticsCallable(_OpticsDescription):
+    """Wrapper pairing a base optics description (``_opt``) with accountants
+    (``accountants``), as produced by make_mixed_accountant_class (:1942-1972)."""
+    optics_class = None
+    accountant_classes = ()
+
+    def __init__(self, *args, **kwargs):
+        self._opt = self.optics_class(*args, **kwargs)
+        self.accountants = [a() for a in self.accountant_classes]
+
+    def reset(self):
+        for a in self.accountants:
+            a.reset()
+
+    def get_all_hits(self):
+        return [a.get_data() for a in self.accountants]
+
+
+def _parse_accountant_suffix(suffix):
+    """'DirectionalReceiver' -> tuple of accountant classes in canonical order, or None."""
+    wanted = set()
+    for alias, parts in _ALIASES.items():
+        if suffix.endswith(alias):
+            wanted.update(parts)
+            suffix = suffix[:-len(alias)]
+            break
+    pos = 0
+    for acc in _ACCOUNTANTS:          # explicit shorthands must come in canonical order
+        if suffix.startswith(acc.shorthand, pos):
+            wanted.add(acc.shorthand)
+            pos += len(acc.shorthand)
+    if pos != len(suffix) or not wanted:
+        return None
+    return tuple(a for a in _ACCOUNTANTS if a.shorthand in wanted)
+
+
+_generated = {}
+
+
+def _make_class(name):
+    best = None
+    for base_name, base in _BASE_OPTICS.items():
+        if name.startswith(base_name) and (best is None or len(base_name) > len(best[0])):
+            accs = _parse_accountant_suffix(name[len(base_name):])
+            if accs is not None:
+                best = (base_name, base, accs)
+    if best is None:
+        return None
+    _, base, accs = best
+    return type(name, (OpticsCallable,), {'optics_class': base, 'accountant_classes': accs,
+                                          '__module__': __name__})
+
+
+def __getattr__(name):
+    if name.startswith('__'):
+        raise AttributeError(name)
+    if name in _generated:
+        return _generated[name]
+    for bad in _UNSUPPORTED:
+        if name.startswith(bad) and not any(name.startswith(b) and len(b) > len(bad) for b in _BASE_OPTICS):
+            raise NotImplementedError(
+                f"optics class {name!r} (base {bad!r}) is outside the GPU bounce-loop scope "
+                "(SURVEY.md section 8f row N4); no CPU fallback is provided")
+    cls = _make_class(name)
+    if cls is None:
+        raise AttributeError(f"module {__name__!r} has no attribute {name!r}")
+    _generated[name] = cls
+    setattr(sys.modules[__name__], name, cls)
+    return cls

@@ -1,0 +1,400 @@
+"""Scene compiler: Assembly -> flat device tables.
+
+Walks ``Assembly.get_surfaces()`` once (the reference does this per trace at
+tracer_engine.py:165-166 and then loops over the Python objects twice per
+bounce) and emits one TrcSurfaceRec per surface: global frame, host-inverted
+frame, geometry kind + parameters, optics kind + parameters, flags; plus a
+global AABB per bounded surface for the BVH.  Works on this package's
+description classes *and* on the reference's own classes (dispatch is by class
+name along the MRO and by the reference's attribute names), so a scene built
+with ``tracer.*`` traces unchanged.
+
+Unknown geometry/optics classes, overridden object relevance hooks and
+accountants that have no device counterpart raise NotImplementedError naming
+the class: there is no CPU fallback.
+"""
+import numpy as np
+
+from . import _lib as L
+
+
+def _mro_names(obj):
+    return [c.__name__ for c in type(obj).__mro__]
+
+
+def _scalar(x, what):
+    a = np.asarray(x, dtype=float)
+    if a.size != 1:
+        raise NotImplementedError(f"{what} must be a scalar for the GPU engine (got shape {a.shape})")
+    return float(a.reshape(-1)[0])
+
+
+# --------------------------------------------------------------- geometry
+def _geom_record(gm, surface):
+    """-> (kind, gp list, local bbox (lo, hi) or None for unbounded)."""
+    names = _mro_names(gm)
+    name = names[0]
+    inf = np.inf
+
+    def box(x, y, z0, z1):
+        return (np.array([-x, -y, z0], float), np.array([x, y, z1], float))
+
+    for name in names:
+        if name == 'PerforatedRectPlateGM':
+            break
+        if name == 'ExtrudedRectPlateGM':
+            hx, hy = np.asarray(gm._half_dims, float).reshape(-1)
+            cx, cy = np.asarray(gm.extr_center, float).reshape(-1)[:2]
+            ex, ey = np.asarray(gm.extr_half_dims, float).reshape(-1)
+            return L.G_RECT_EXTRUDED, [hx, hy, cx, cy, ex, ey], box(hx, hy, 0., 0.)
+        if name == 'RectPlateGM':
+            hx, hy = np.asarray(gm._half_dims, float).reshape(-1)
+            return L.G_RECT_PLATE, [hx, hy], box(hx, hy, 0., 0.)
+        if name in ('StraightCutRoundPlateGM', 'RoundPlateGM'):
+            re = float(gm._Re)
+            ri = -1.0 if gm._Ri is None else float(gm._Ri)
+            xc = getattr(gm, 'x_cut', None)
+            xc = inf if xc is None else float(xc)
+            return L.G_ROUND_PLATE, [re, ri, xc], box(re, re, 0., 0.)
+        if name == 'TriangularFace':
+            v = np.asarray(gm._verts, float)
+            if v.shape != (3, 2):
+                raise ValueError("TriangularFace vertices must be a 3x2 array")
+            pts = np.stack([np.zeros(3), v[:, 0], v[:, 1]], axis=1)
+            return L.G_TRIANGLE, list(v[:, 0]) + list(v[:, 1]), (pts.min(axis=1), pts.max(axis=1))
+        if name in ('FlatGeometryManager', 'FiniteFlatGM'):
+            return L.G_FLAT_INFINITE, [], None
+        if name == 'ParabolicDishGM':
+            return L.G_PARAB_DISH, [gm.a, gm.b, gm._h], box(gm._R, gm._R, 0., gm._h)
+        if name == 'HexagonalParabolicDishGM':
+            r = float(gm._R)
+            return L.G_PARAB_HEX, [gm.a, gm.b, r], box(r, r, 0., max(gm.a, gm.b) * 2 * r * r)
+        if name == 'RectangularParabolicDishGM':
+            if getattr(gm, '_off_axis_normal', None) is not None:
+                break
+            w, h = float(gm._w), float(gm._h)
+            return L.G_PARAB_RECT, [gm.a, gm.b, w, h], box(w, h, 0., gm.a * w * w + gm.b * h * h)
+        if name == 'ParabolicTroughGM':
+            hl, h = gm._l / 2., float(gm._h)
+            return L.G_PARAB_TROUGH, [gm.a, hl, h], box(np.sqrt(h / gm.a), hl, 0., h)
+        if name == 'ParabolicCylinder':
+            return L.G_PARAB_CYL, [gm.a], None
+        if name == 'Paraboloid':
+            return L.G_PARABOLOID, [gm.a, gm.b], None
+        if name == 'SphericalRectFacet':
+            r = float(gm._rad)
+            return L.G_SPHERE_RECT, [r, gm.lx / 2., gm.ly / 2.], box(min(r, gm.lx / 2.), min(r, gm.ly / 2.), -r, 0.)
+        if name == 'HemisphereGM':
+            r = float(gm._rad)
+            return L.G_HEMISPHERE, [r], box(r, r, -r, 0.)
+        if name == 'CutSphereGM':
+            r = float(gm._rad)
+            bound = gm._bound
+            if bound is None:
+                return L.G_SPHERE, [r], box(r, r, -r, r)
+            if 'BoundarySphere' not in _mro_names(bound):
+                raise NotImplementedError(
+                    f"CutSphereGM bounding volume {type(bound).__name__} is not supported on the GPU "
+                    "(only BoundarySphere)")
+            # BoundarySphere never moves its centre with the frame (boundary_shape.py:101)
+            c = np.asarray(bound._temp_loc, float)[:3]
+            rb = float(bound._radius)
+            return L.G_SPHERE_CUT, [r] + list(c) + [rb], ('global', c - rb, c + rb)
+        if name == 'SphericalGM':
+            r = float(gm._rad)
+            return L.G_SPHERE, [r], box(r, r, -r, r)
+        if name == 'FiniteCone':
+            return L.G_CONE_FINITE, [gm.c, gm.a, gm.h], box(gm.r, gm.r, 0., gm.h)
+        if name == 'RectCutConicalFrustum':
+            rm = max(gm.r1, gm.r2)
+            hw, hh = np.asarray(gm.half_dims, float)
+            return (L.G_FRUSTUM_RECT, [gm.c, gm.a, gm.zmin, gm.zmax, hw, hh],
+                    (np.array([-min(rm, hw), -min(rm, hh), gm.zmin]), np.array([min(rm, hw), min(rm, hh), gm.zmax])))
+        if name == 'ConicalFrustum':
+            rm = max(gm.r1, gm.r2)
+            return L.G_FRUSTUM, [gm.c, gm.a, gm.zmin, gm.zmax], box(rm, rm, gm.zmin, gm.zmax)
+        if name == 'InfiniteCone':
+            return L.G_CONE_INFINITE, [gm.c, gm.a], None
+        if name == 'RectCutCylinder':
+            r, hh_ = float(gm._R), float(gm._half_h)
+            hw, hh = np.asarray(gm.half_dims, float)
+            return L.G_CYL_RECT, [r, hh_, hw, hh], box(min(r, hw), min(r, hh), -hh_, hh_)
+        if name == 'FiniteCylinder':
+            r, hh_ = float(gm._R), float(gm._half_h)
+            return L.G_CYL_FINITE, [r, hh_, float(gm._ang_range[0]), float(gm._ang_range[1])], box(r, r, -hh_, hh_)
+        if name == 'InfiniteCylinder':
+            return L.G_CYL_INFINITE, [float(gm._R)], None
+        if name == 'RectFlatQuadricSurfaceGM':
+            w, h = float(gm._w), float(gm._h)
+            m = abs(gm.a) * w * w + abs(gm.b) * h * h + abs(gm.c) * w * h + abs(gm.d) * w + abs(gm.e) * h
+            return (L.G_QUADRIC_RECT, [gm.a, gm.b, gm.c, gm.d, gm.e, gm.f, w, h], box(w, h, gm.f - m, gm.f + m))
+        if name == 'FlatQuadricSurfaceGM':
+            return L.G_QUADRIC_FLAT, [gm.a, gm.b, gm.c, gm.d, gm.e, gm.f], None
+    raise NotImplementedError(
+        f"geometry manager {type(gm).__name__} has no GPU kernel (no CPU fallback); "
+        "see SURVEY.md section 8 for the supported classes")
+
+
+def _global_aabb(frame, local_box):
+    if local_box is None:
+        return None
+    if len(local_box) == 3 and isinstance(local_box[0], str):
+        lo, hi = local_box[1], local_box[2]
+    else:
+        lo, hi = local_box
+        c = np.ones((4, 8))
+        for k in range(8):
+            c[0, k] = hi[0] if k & 1 else lo[0]
+            c[1, k] = hi[1] if k & 2 else lo[1]
+            c[2, k] = hi[2] if k & 4 else lo[2]
+        g = np.dot(frame, c)[:3]
+        lo, hi = g.min(axis=1), g.max(axis=1)
+    pad = 1e-6 * (1.0 + np.abs(np.concatenate([lo, hi])).max())
+    return lo - pad, hi + pad
+
+
+# ----------------------------------------------------------------- optics
+_ACC_FIELDS = {  # shorthand -> (list attribute on the accountant, source)
+    'Absorber': ('_absorbed', 'absorbed'),
+    'Receptor': ('_received', 'e_in'),
+    'Scatterer': ('_scattered', 'e_out'),
+    'Location': ('_hits', 'hits'),
+    'Directional': ('_directions', 'dirs_in'),
+    'Normal': ('_normals', 'normals'),
+    'Spectral': ('_wavelengths', 'wavelengths'),
+}
+
+
+def _optics_record(opt):
+    """-> dict(okind, op, flags, table, accountants, draws)"""
+    accountants = []
+    base = opt
+    if hasattr(opt, 'accountants') and hasattr(opt, '_opt'):
+        base = opt._opt
+        for a in opt.accountants:
+            sh = getattr(a, 'shorthand', None)
+            if sh not in _ACC_FIELDS:
+                raise NotImplementedError(
+                    f"accountant {type(a).__name__} of {type(opt).__name__} has no GPU counterpart")
+            accountants.append((a,) + _ACC_FIELDS[sh])
+    elif hasattr(opt, 'get_all_hits'):
+        raise NotImplementedError(f"optics manager {type(opt).__name__}: unknown accounting wrapper")
+    rec = dict(okind=None, op=[0., 0., 0., 0.], flags=0, table=None, accountants=accountants,
+               needs_wavelengths=False, instance=opt)
+    for name in _mro_names(base):
+        if name == 'Transparent':
+            rec['okind'] = L.O_TRANSPARENT
+        elif name in ('OneSidedReflective', 'Reflective'):
+            rec['okind'] = L.O_REFLECTIVE
+            rec['op'][0] = _scalar(base._abs, 'absorptivity')
+        elif name in ('OneSidedRealReflective', 'RealReflective'):
+            rec['okind'] = L.O_REAL_REFLECTIVE
+            rec['op'][:3] = [_scalar(base._abs, 'absorptivity'), _scalar(base._sig, 'sigma'),
+                             1.0 if base.bi_var == True else 0.0]  # noqa: E712 (reference compares with ==)
+        elif name == 'Lambertian':
+            rec['okind'] = L.O_LAMBERTIAN
+            rec['op'][:2] = [_scalar(base._abs, 'absorptivity'), _scalar(base._ang_range, 'ang_range')]
+        elif name == 'LambertianSpecular':
+            rec['okind'] = L.O_LAMBERTIAN_SPECULAR
+            rec['op'][:2] = [_scalar(base._abs, 'absorptivity'), _scalar(base.specularity, 'specularity')]
+        elif name == 'Lambertian_directional_axisymmetric_piecewise':
+            rec['okind'] = L.O_LAMB_DIRECTIONAL
+            rec['table'] = (np.asarray(base.thetas, float), np.asarray(base.abs_th, float))
+        elif name == 'LambertianSpecular_directional_axisymmetric_piecewise':
+            rec['okind'] = L.O_LAMBSPEC_DIRECTIONAL
+            rec['op'][0] = _scalar(base.specularity, 'specularity')
+            rec['table'] = (np.asarray(base.thetas, float), np.asarray(base.abs_th, float))
+        elif name == 'Lambertian_directional_axisymmetric_piecewise_spectral':
+            rec['okind'] = L.O_LAMB_DIRECTIONAL_SPECTRAL
+            if hasattr(base, 'interpolator'):      # reference object: scipy RegularGridInterpolator
+                th, wl = [np.asarray(g, float) for g in base.interpolator.grid]
+                val = np.asarray(base.interpolator.values, float)
+            else:
+                th, wl, val = base.thetas, base.wavelengths, base.absorptance
+            rec['op'][1] = float(len(wl))
+            rec['table'] = (np.asarray(th, float), np.concatenate([np.asarray(wl, float), np.ravel(val)]))
+            rec['needs_wavelengths'] = True
+        elif name == 'Reflective_spectral':
+            rec['okind'] = L.O_REFLECTIVE_SPECTRAL
+            rec['table'] = (np.asarray(base._wavelengths, float), np.asarray(base._absorptances, float))
+            rec['needs_wavelengths'] = True
+        else:
+            continue
+        if name.startswith('OneSided') or 'OneSidedReflective' in _mro_names(base) \
+                or 'OneSidedRealReflective' in _mro_names(base):
+            rec['flags'] |= L.F_ONE_SIDED
+        return rec
+    raise NotImplementedError(
+        f"optics manager {type(base).__name__} has no GPU kernel (no CPU fallback); "
+        "see SURVEY.md section 8 for the supported classes")
+
+
+# -------------------------------------------------------------------- BVH
+def build_bvh(lo, hi, leaf_size=2):
+    """Balanced object-median BVH over n AABBs, built level by level with
+    vectorised NumPy sorts.  Level-order layout: children of node i are 2i+1
+    and 2i+2.  Returns (nodes structured array, leaf order int32)."""
+    n = lo.shape[0]
+    depth = 0
+    while -(-n // (1 << depth)) > leaf_size:
+        depth += 1
+    order = np.arange(n)
+    cent = 0.5 * (lo + hi)
+    bounds = [(np.array([0]), np.array([n]))]       # per level: (starts, ends)
+    for level in range(depth):
+        starts, ends = bounds[-1]
+        counts = ends - starts
+        node_of = np.repeat(np.arange(len(starts)), counts)
+        c = cent[order]
+        cmin = np.full((len(starts), 3), np.inf)
+        cmax = np.full((len(starts), 3), -np.inf)
+        nz = counts > 0
+        if n:
+            cmin[nz] = np.minimum.reduceat(c, starts[nz], axis=0)
+            cmax[nz] = np.maximum.reduceat(c, starts[nz], axis=0)
+        axis = np.argmax(np.where(nz[:, None], cmax - cmin, 0.0), axis=1)
+        key = c[np.arange(n), axis[node_of]]
+        perm = np.lexsort((key, node_of))
+        order = order[perm]
+        mid = starts + (counts + 1) // 2
+        bounds.append((np.stack([starts, mid], 1).reshape(-1), np.stack([mid, ends], 1).reshape(-1)))
+    n_nodes = (1 << (depth + 1)) - 1
+    nodes = np.zeros(n_nodes, dtype=L.BVH_NODE_DTYPE)
+    # leaves
+    starts, ends = bounds[-1]
+    first_leaf = (1 << depth) - 1
+    counts = ends - starts
+    llo = np.full((len(starts), 3), np.inf)
+    lhi = np.full((len(starts), 3), -np.inf)
+    nz = counts > 0
+    if n:
+        llo[nz] = np.minimum.reduceat(lo[order], starts[nz], axis=0)
+        lhi[nz] = np.maximum.reduceat(hi[order], starts[nz], axis=0)
+        # reduceat runs to the next start; empty-leaf gaps cannot occur between non-empty ones
+    nodes['lo'][first_leaf:] = llo
+    nodes['hi'][first_leaf:] = lhi
+    nodes['first'][first_leaf:] = starts
+    nodes['count'][first_leaf:] = np.maximum(counts, 0)
+    # an empty leaf must never be entered: give it an inverted box and count 0 -> treat as leaf via count=-1
+    empty = np.nonzero(~nz)[0] + first_leaf
+    nodes['count'][empty] = -1
+    for level in range(depth - 1, -1, -1):
+        a, b = (1 << level) - 1, (1 << (level + 1)) - 1
+        idx = np.arange(a, b)
+        left, right = 2 * idx + 1, 2 * idx + 2
+        nodes['lo'][idx] = np.minimum(nodes['lo'][left], nodes['lo'][right])
+        nodes['hi'][idx] = np.maximum(nodes['hi'][left], nodes['hi'][right])
+        nodes['first'][idx] = left
+        nodes['count'][idx] = 0
+    return nodes, order.astype(np.int32)
+
+
+class CompiledScene(object):
+    """Flat tables for one Assembly + the device handle."""
+
+    def __init__(self, assembly, leaf_size=2):
+        self.assembly = assembly
+        surfaces = assembly.get_surfaces()
+        if len(surfaces) == 0:
+            raise ValueError("assembly has no surfaces")
+        self._check_objects(assembly)
+        self.surfaces = surfaces
+        S = len(surfaces)
+        recs = np.zeros(S, dtype=L.SURFACE_DTYPE)
+        tables = []
+        table_len = 0
+        self.optics = []
+        self.aabb_lo = np.full((S, 3), np.nan)
+        self.aabb_hi = np.full((S, 3), np.nan)
+        seen_opt = {}
+        for i, s in enumerate(surfaces):
+            frame = np.asarray(s._temp_frame, dtype=float)
+            kind, gp, lbox = _geom_record(s._geom, s)
+            orec = _optics_record(s._opt)
+            if orec['accountants'] and id(s._opt) in seen_opt:
+                raise NotImplementedError(
+                    f"optics manager instance shared by surfaces {seen_opt[id(s._opt)]} and {i}: "
+                    "accountant data would be merged (optics_callables.py:82); use copy_optical_manager")
+            seen_opt[id(s._opt)] = i
+            r = recs[i]
+            r['frame'] = frame[:3].reshape(-1)
+            r['inv'] = np.linalg.inv(frame)[:3].reshape(-1)
+            r['gp'][:len(gp)] = gp
+            r['op'] = orec['op']
+            r['gkind'], r['okind'] = kind, orec['okind']
+            flags = orec['flags']
+            box = _global_aabb(frame, lbox)
+            if box is None:
+                flags |= L.F_UNBOUNDED
+            else:
+                self.aabb_lo[i], self.aabb_hi[i] = box
+            r['flags'] = flags
+            r['table_off'], r['table_len'] = -1, 0
+            if orec['table'] is not None:
+                x, y = orec['table']
+                r['table_off'], r['table_len'] = table_len, len(x)
+                tables += [x, y]
+                table_len += len(x) + len(y)
+            self.optics.append(orec)
+        self.records = recs
+        self.tables = np.concatenate(tables) if tables else np.zeros(0)
+        self.needs_wavelengths = any(o['needs_wavelengths'] for o in self.optics)
+        self.has_accountants = any(o['accountants'] for o in self.optics)
+        self.unbounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) != 0)[0].astype(np.int32)
+        self.bounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) == 0)[0].astype(np.int32)
+        self.leaf_size = leaf_size
+        self.handle = None
+        self.bvh_nodes = None
+        self._upload()
+
+    @staticmethod
+    def _check_objects(assembly):
+        for obj in assembly.get_objects():
+            for hook in ('own_rays', 'surfaces_for_next_iteration'):
+                fn = getattr(obj, hook, None)
+                qual = getattr(getattr(fn, '__func__', fn), '__qualname__', '')
+                if fn is not None and qual != 'AssembledObject.' + hook:
+                    raise NotImplementedError(
+                        f"{type(obj).__name__} overrides {hook}(): per-object relevance hooks "
+                        "(object.py:81-112) are not honoured by the GPU engine")
+
+    def _upload(self):
+        import ctypes as C
+        lib = L.load()
+        h = C.c_void_p()
+        tab = self.tables
+        L.check(lib.trc_scene_create(self.records.ctypes.data_as(C.c_void_p), len(self.records),
+                                     tab.ctypes.data_as(C.c_void_p) if tab.size else None, int(tab.size),
+                                     C.byref(h)))
+        self.handle = h
+        self._upload_bvh()
+
+    def _upload_bvh(self):
+        import ctypes as C
+        lib = L.load()
+        if len(self.bounded):
+            nodes, order = build_bvh(self.aabb_lo[self.bounded], self.aabb_hi[self.bounded], self.leaf_size)
+            leaf_surfs = np.ascontiguousarray(self.bounded[order])
+        else:
+            nodes, leaf_surfs = np.zeros(0, dtype=L.BVH_NODE_DTYPE), np.zeros(0, np.int32)
+        self.bvh_nodes, self.bvh_leaf_surfaces = nodes, leaf_surfs
+        unb = np.ascontiguousarray(self.unbounded)
+        L.check(lib.trc_scene_set_bvh(
+            self.handle, nodes.ctypes.data_as(C.c_void_p) if len(nodes) else None, len(nodes),
+            leaf_surfs.ctypes.data_as(C.c_void_p) if len(leaf_surfs) else None, len(leaf_surfs),
+            unb.ctypes.data_as(C.c_void_p) if len(unb) else None, len(unb)))
+
+    @property
+    def num_surfaces(self):
+        return len(self.records)
+
+    def close(self):
+        if self.handle is not None:
+            L.load().trc_scene_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,256 @@
+"""Scene graph with the reference's public API: frames, assemblies, objects,
+surfaces and boundary boxes.
+
+These are *descriptions* only.  The reference's classes (tracer/has_frame.py,
+assembly.py, object.py, surface.py, boundary_shape.py) also carry the per-bounce
+protocol state (register_incoming/select_rays/get_outgoing/done,
+surface.py:55-112); here that work happens on the GPU, so a Surface just pairs a
+geometry description with an optics description and knows its global frame.
+The scene compiler (tracer_b200/scene.py) reads ``Assembly.get_surfaces()``,
+``Surface._temp_frame``, ``Surface._geom`` and ``Surface._opt`` -- the same
+attribute names the reference uses, so reference-built scenes compile too.
+"""
+import numpy as np
+
+
+class HasFrame(object):
+    """Location + rotation relative to the parent, and the resolved global frame.
+
+    API of has_frame.py:3-83: get/set_location, get/set_rotation,
+    get/set_transform, transform_frame; ``_temp_frame`` is the 4x4 global frame.
+    """
+
+    def __init__(self, location=None, rotation=None):
+        self._transform = np.eye(4)
+        self.set_location(np.zeros(3) if location is None else location)
+        self.set_rotation(np.eye(3) if rotation is None else rotation)
+        self._temp_frame = self._transform
+
+    def get_location(self):
+        return self._loc
+
+    def get_rotation(self):
+        return self._rot
+
+    def get_transform(self):
+        return self._transform
+
+    def set_location(self, location):
+        location = np.asarray(location)
+        if location.shape != (3,):
+            raise ValueError("location must be a 1D 3-component array")
+        self._loc = location
+        self._transform[:3, 3] = location
+
+    def set_rotation(self, rotation):
+        rotation = np.asarray(rotation)
+        if rotation.shape != (3, 3):
+            raise ValueError("rotation must be a 3x3 array")
+        self._rot = rotation
+        self._transform[:3, :3] = rotation
+
+    def set_transform(self, transform):
+        self._transform = transform
+        self._loc = transform[:3, 3]
+        self._rot = transform[:3, :3]
+
+    def transform_frame(self, transform):
+        """Resolve the global frame given the parent's global transform."""
+        self._temp_frame = np.dot(transform, self._transform)
+
+    def _to_local(self, points):
+        # the reference rounds the inverse to 9 decimals (surface.py:125, assembly.py:44)
+        proj = np.round(np.linalg.inv(self._temp_frame), decimals=9)
+        return np.dot(proj, np.vstack((points, np.ones(points.shape[1]))))
+
+
+class Surface(HasFrame):
+    """A geometry manager + an optics manager placed in an object (surface.py:12-53)."""
+
+    def __init__(self, geometry, optics, location=None, rotation=None, fixed_color=False):
+        HasFrame.__init__(self, location, rotation)
+        self._geom = geometry
+        self._opt = optics
+        self._fixed_color = fixed_color[:3] if fixed_color else fixed_color
+        self._transparency = fixed_color[-1] if (fixed_color and len(fixed_color) == 4) else 0
+
+    def get_optics_manager(self):
+        return self._opt
+
+    def get_geometry_manager(self):
+        return self._geom
+
+    def global_to_local(self, points):
+        """(3,n) global points -> (4,n) homogeneous local coordinates (surface.py:114-126)."""
+        return self._to_local(points)
+
+    def get_fluxmap(self, eners, local_coords, resolution):
+        return self._geom.get_fluxmap(eners, local_coords, resolution)
+
+
+class BoundaryShape(HasFrame):
+    def in_bounds(self, points):
+        raise TypeError("Virtual function in_bounds() called. Implement this in a derived class")
+
+
+class BoundaryBox(BoundaryShape):
+    """Axis-aligned box given in the owner's local frame; its global AABB
+    (``_minpoint``/``_maxpoint``) is refreshed on every transform
+    (boundary_shape.py:58-87).  Feeds the acceleration structure."""
+
+    def __init__(self, aabb, location=None, rotation=None):
+        BoundaryShape.__init__(self, location, rotation)
+        self._aabb = np.array(aabb, dtype=float)
+        self._AABB = np.array(aabb, dtype=float)
+
+    def update_AABB(self):
+        lo, hi = self._aabb
+        corners = np.ones((4, 8))
+        for k in range(8):
+            corners[0, k] = hi[0] if k & 1 else lo[0]
+            corners[1, k] = hi[1] if k & 2 else lo[1]
+            corners[2, k] = hi[2] if k & 4 else lo[2]
+        glob = np.dot(self._temp_frame, corners)[:3]
+        self._minpoint, self._maxpoint = glob.min(axis=1), glob.max(axis=1)
+        self._AABB = np.array([self._minpoint, self._maxpoint])
+
+    def in_bounds(self, bund_vertices):
+        lo, hi = self._minpoint, self._maxpoint
+        if bund_vertices.ndim == 2:
+            lo, hi = lo[:, None], hi[:, None]
+        return np.logical_and(bund_vertices > lo, bund_vertices < hi).all(axis=0)
+
+    def transform_frame(self, transform):
+        BoundaryShape.transform_frame(self, transform)
+        self.update_AABB()
+
+
+class BoundarySphere(BoundaryShape):
+    """Sphere used by CutSphereGM to keep only part of a spherical surface
+    (boundary_shape.py:89-111).  As in the reference the centre is the location
+    given at construction and does not follow later frame transforms."""
+
+    def __init__(self, location=None, radius=1.):
+        BoundaryShape.__init__(self, location, None)
+        self._temp_loc = self._loc
+        self._radius = radius
+
+    def in_bounds(self, bund_vertices):
+        return self._radius ** 2 >= ((bund_vertices - self._temp_loc[:3]) ** 2).sum(axis=1)
+
+
+class Assembly(HasFrame):
+    """Tree of objects and sub-assemblies (assembly.py:7-151)."""
+
+    def __init__(self, objects=None, subassemblies=None, location=None, rotation=None):
+        self._objects = [] if objects is None else objects
+        self._assemblies = [] if subassemblies is None else subassemblies
+        HasFrame.__init__(self, location, rotation)
+
+    # -- queries
+    def get_local_objects(self):
+        return self._objects
+
+    def get_assemblies(self):
+        return self._assemblies
+
+    def get_objects(self):
+        """Objects of the sub-assemblies first (depth first), then the local ones
+        (same order as assembly.py:60-65, which defines surface indices)."""
+        out = []
+        for asm in self._assemblies:
+            out.extend(asm.get_objects())
+        out.extend(self._objects)
+        return out
+
+    def get_surfaces(self):
+        return [s for obj in self.get_objects() for s in obj.get_surfaces()]
+
+    def global_to_local(self, points):
+        return self._to_local(points)
+
+    # -- mutation
+    def add_object(self, object, transform=None):
+        self._objects.append(object)
+        if transform is not None:
+            object.set_transform(transform)
+        self.transform_children()
+
+    def add_assembly(self, assembly, transform=None):
+        self._assemblies.append(assembly)
+        if transform is not None:
+            assembly.set_transform(transform)
+        self.transform_children()
+
+    def set_rotation(self, rotation):
+        HasFrame.set_rotation(self, rotation)
+        self.transform_children()
+
+    def set_location(self, location):
+        HasFrame.set_location(self, location)
+        self.transform_children()
+
+    def set_transform(self, transform):
+        HasFrame.set_transform(self, transform)
+        self.transform_children()
+
+    def transform_children(self, assembly_transform=np.eye(4)):
+        mine = np.dot(assembly_transform, self.get_transform())
+        for child in self._assemblies + self._objects:
+            child.transform_children(mine)
+
+    def reset_all_optics(self):
+        for s in self.get_surfaces():
+            if hasattr(s.get_optics_manager(), 'reset'):
+                s.get_optics_manager().reset()
+
+
+class AssembledObject(Assembly):
+    """A rigid group of surfaces (+ optional boundary boxes) (object.py:8-79)."""
+
+    def __init__(self, surfs=None, bounds=None, location=None, rotation=None, transform=None):
+        self.surfaces = [] if surfs is None else surfs
+        self.boundaries = [] if bounds is None else bounds
+        if not hasattr(self.surfaces, '__len__'):
+            self.surfaces = [self.surfaces]
+        if not hasattr(self.boundaries, '__len__'):
+            self.boundaries = [self.boundaries]
+        if transform is None:
+            transform = np.eye(4)
+            if location is not None:
+                transform[:3, 3] = location
+            if rotation is not None:
+                transform[:3, :3] = rotation
+        self.set_transform(transform)
+
+    def get_objects(self):
+        return [self]
+
+    def get_surfaces(self):
+        return self.surfaces
+
+    def get_boundaries(self):
+        if self.boundaries is None:
+            self.boundaries = []
+        return self.boundaries
+
+    def add_surface(self, surface):
+        self.surfaces.append(surface)
+        self.transform_children()
+
+    def add_boundary(self, boundary):
+        self.boundaries.append(boundary)
+        self.transform_children()
+
+    def transform_children(self, assembly_transform=np.eye(4)):
+        mine = np.dot(assembly_transform, self.get_transform())
+        for child in self.surfaces + self.boundaries:
+            child.transform_frame(mine)
+
+    # Legacy relevance hooks (object.py:81-112).  Only the defaults are honoured
+    # by the GPU engine; overriding them raises at compile time.
+    def own_rays(self, rays, surface_id):
+        return np.zeros(rays.get_num_rays(), dtype=bool)
+
+    def surfaces_for_next_iteration(self, rays, surface_id):
+        return np.ones((len(self.surfaces), rays.get_num_rays()), dtype=bool)

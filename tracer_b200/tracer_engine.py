@@ -1,0 +1,354 @@
+"""TracerEngine: the reference's driver API (tracer/tracer_engine.py:11-295) on
+top of the sm_100a kernels.
+
+``TracerEngine(assembly).ray_tracer(bundle, reps, min_energy, tree, accel,
+Kd_Tree)`` keeps the reference signature, return value and side effects
+(``self.tree``, accountant data behind ``get_all_hits()``, log messages) but the
+per-bounce work -- every find_intersections, the nearest-hit reduction, the
+optics callables, accountants, culling and child-bundle concatenation -- runs on
+the GPU through libtracer_b200.so.  Python only sizes buffers (torch CUDA
+tensors) and sequences ~10 launches per bounce.
+
+Random draws: ``rng='philox'`` (default) draws on device, keyed by
+(seed, bounce, child slot).  ``rng='numpy'`` draws on the host from
+``numpy.random`` in exactly the reference's order (bounce -> surface ->
+draw kind -> hit) and injects them, so a trace with the
+same ``numpy.random.seed`` reproduces the reference bundle for bundle.
+"""
+import ctypes as C
+import logging
+
+import numpy as np
+
+from . import _lib as L
+from .ray_bundle import RayBundle, _DeviceColumns
+from .scene import CompiledScene
+from .trace_tree import RayTree
+
+
+class _LazyRows(object):
+    """Device-resident chunk of accountant data; looks like an ndarray to
+    numpy.hstack (shape, len, __array__) and is copied to the host on demand."""
+
+    def __init__(self, tensor):
+        self.t = tensor
+        self.shape = tuple(tensor.shape)
+        self.ndim = tensor.dim()
+        self._host = None
+
+    def __len__(self):
+        return self.shape[0]
+
+    def __array__(self, dtype=None, copy=None):
+        if self._host is None:
+            self._host = self.t.cpu().numpy()
+            self.t = None
+        return self._host if dtype is None else self._host.astype(dtype)
+
+
+class _DevBundle(object):
+    """Engine-internal view of a bundle living in HBM."""
+    __slots__ = ('V', 'D', 'E', 'W', 'n')
+
+    def __init__(self, V, D, E, W=None):
+        self.V, self.D, self.E, self.W = V, D, E, W
+        self.n = int(V.shape[1])
+
+
+class TracerEngine(object):
+    def __init__(self, parent_assembly, loglevel=logging.DEBUG, device=None, rng='philox', seed=0,
+                 device_accel='auto', leaf_size=2):
+        """
+        parent_assembly - the top-level Assembly (reference's or this package's).
+        loglevel        - level of the per-bounce log lines (as the reference).
+        device          - torch device (default: current CUDA device).
+        rng             - 'philox' (device draws) or 'numpy' (host draws in the
+                          reference's order, injected into the kernels).
+        seed            - Philox seed.
+        device_accel    - 'auto' | 'brute' | 'bvh': how the nearest-hit kernel
+                          finds candidates.  Results are identical.
+        """
+        import torch
+        L.load()  # fail loudly when the CUDA library is missing
+        if not torch.cuda.is_available():
+            raise RuntimeError("tracer_b200 needs a CUDA device: the bounce loop has no CPU path")
+        self._asm = parent_assembly
+        self.loglevel = loglevel
+        self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+        if rng not in ('philox', 'numpy'):
+            raise ValueError("rng must be 'philox' or 'numpy'")
+        self.rng = rng
+        self.seed = int(seed)
+        if device_accel not in ('auto', 'brute', 'bvh'):
+            raise ValueError("device_accel must be 'auto', 'brute' or 'bvh'")
+        self.device_accel = device_accel
+        self.leaf_size = leaf_size
+        self._scene = None
+        self._frames_key = None
+        self.stats = {}
+
+    # ------------------------------------------------------------ scene
+    def compile(self, force=False):
+        """(Re)compile the assembly into device tables when it changed."""
+        surfaces = self._asm.get_surfaces()
+        frames = np.stack([np.asarray(s._temp_frame, float) for s in surfaces]) if surfaces else np.zeros((0, 4, 4))
+        key = (tuple(id(s) for s in surfaces), frames.tobytes())
+        if force or self._scene is None or key != self._frames_key:
+            if self._scene is not None:
+                self._scene.close()
+            self._scene = CompiledScene(self._asm, leaf_size=self.leaf_size)
+            self._frames_key = key
+        return self._scene
+
+    # ----------------------------------------------------------- bundles
+    def _to_device(self, bundle):
+        import torch
+
+        def col(name, required=True):
+            if not bundle.has_property(name) or not getattr(bundle, 'is_set', lambda n: True)(name):
+                if required:
+                    raise ValueError(f"bundle has no {name}")
+                return None
+            raw = bundle._props.get(name) if hasattr(bundle, '_props') else None
+            if isinstance(raw, _DeviceColumns):
+                t = raw.pieces[0] if len(raw.pieces) == 1 else torch.cat(raw.pieces, dim=-1)
+                return t.to(self.device)
+            try:
+                arr = getattr(bundle, 'get_' + name)()
+            except (KeyError, AttributeError):
+                if required:
+                    raise ValueError(f"bundle has no {name}")
+                return None
+            arr = np.ascontiguousarray(arr, dtype=np.float64)
+            return torch.from_numpy(arr).to(self.device, non_blocking=True)
+
+        V, D, E = col('vertices'), col('directions'), col('energy')
+        W = col('wavelengths', required=False) if bundle.has_property('wavelengths') else None
+        if V.dim() != 2 or V.shape[0] != 3 or D.shape != V.shape or E.shape[0] != V.shape[1]:
+            raise ValueError("bundle arrays must be vertices (3,n), directions (3,n), energy (n,)")
+        return _DevBundle(V.contiguous(), D.contiguous(), E.contiguous(), None if W is None else W.contiguous())
+
+    # ------------------------------------------------------------ draws
+    def _numpy_draws(self, scene, seg, H):
+        """Host draws in the reference's consumption order; returns 3 device arrays or None."""
+        import torch
+        draws = None
+        counts = np.diff(seg)
+        for s in np.nonzero(counts)[0]:
+            n = int(counts[s])
+            a, b = int(seg[s]), int(seg[s + 1])
+            rec = scene.records[s]
+            k = rec['okind']
+            vals = [None, None, None]
+            if k == L.O_REAL_REFLECTIVE:
+                sig = rec['op'][1]
+                if sig > 0.:
+                    if rec['op'][2] != 0.:
+                        vals[0] = np.random.normal(scale=sig, size=(n,))
+                        vals[1] = np.random.normal(scale=sig, size=(n,))
+                    else:
+                        vals[0] = np.random.normal(scale=sig, size=(n,))
+                        vals[1] = np.random.uniform(low=0., high=2. * np.pi, size=(n,))
+            elif k in (L.O_LAMBERTIAN, L.O_LAMB_DIRECTIONAL, L.O_LAMB_DIRECTIONAL_SPECTRAL):
+                ang = rec['op'][1] if k == L.O_LAMBERTIAN else np.pi / 2.
+                vals[0] = np.random.uniform(low=0., high=2. * np.pi, size=n)
+                if ang != 0.:
+                    vals[1] = np.random.uniform(size=n)
+            elif k in (L.O_LAMBERTIAN_SPECULAR, L.O_LAMBSPEC_DIRECTIONAL):
+                spec = rec['op'][1] if k == L.O_LAMBERTIAN_SPECULAR else rec['op'][0]
+                r = np.random.rand(n)
+                diffuse = ~(r < spec)
+                nd = int(diffuse.sum())
+                vals[0] = r
+                vals[1], vals[2] = np.zeros(n), np.zeros(n)
+                vals[1][diffuse] = np.random.uniform(low=0., high=2. * np.pi, size=nd)
+                vals[2][diffuse] = np.random.uniform(size=nd)
+            if any(v is not None for v in vals):
+                if draws is None:
+                    draws = np.zeros((3, H))
+                for j in range(3):
+                    if vals[j] is not None:
+                        draws[j, a:b] = vals[j]
+        if draws is None:
+            draws = np.zeros((3, H))
+        return torch.from_numpy(draws).to(self.device)
+
+    # ------------------------------------------------------------ bounce
+    def _bounce(self, scene, cur, bounce, min_energy, use_bvh):
+        """One iteration of the reference loop body (tracer_engine.py:193-274).
+        Returns (record tensors dict, n_survivors, H)."""
+        import torch
+        lib = L.load()
+        dev = self.device
+        st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        n, S = cur.n, scene.num_surfaces
+        i32, i64, f64 = torch.int32, torch.int64, torch.float64
+        hit = torch.empty(n, dtype=i32, device=dev)
+        L.check(lib.trc_nearest_hit(scene.handle, n, L.dptr(cur.V), L.dptr(cur.D), cur.V.stride(0),
+                                    1 if use_bvh else 0, L.dptr(hit), st))
+        slot_surf = torch.empty(n, dtype=i32, device=dev)
+        slot_parent = torch.empty(n, dtype=i32, device=dev)
+        count = torch.zeros(1, dtype=i64, device=dev)
+        work = torch.empty(int(lib.trc_sort_work_bytes(n, S)), dtype=torch.uint8, device=dev)
+        L.check(lib.trc_sort_pairs(n, S, L.dptr(hit), None, L.dptr(slot_surf), L.dptr(slot_parent),
+                                   L.dptr(count), L.dptr(work), st))
+        seg = torch.empty(S + 1, dtype=i64, device=dev)
+        L.check(lib.trc_segment_offsets_dyn(L.dptr(count), n, S, L.dptr(slot_surf), L.dptr(seg), st))
+        H = int(count.item())
+        del hit, work
+        if H == 0:
+            return None, 0, 0
+        need_seg_host = scene.has_accountants or self.rng == 'numpy'
+        seg_host = seg.cpu().numpy() if need_seg_host else None
+
+        oV = torch.empty((3, H), dtype=f64, device=dev)
+        oD = torch.empty((3, H), dtype=f64, device=dev)
+        oE = torch.empty(H, dtype=f64, device=dev)
+        oP = torch.empty(H, dtype=i64, device=dev)
+        cull = torch.empty(H, dtype=i32, device=dev)
+        want = set(src for o in scene.optics for (_, _, src) in o['accountants'])
+        absorbed = torch.empty(H, dtype=f64, device=dev) if 'absorbed' in want else None
+        normals = torch.empty((3, H), dtype=f64, device=dev) if 'normals' in want else None
+        draws = self._numpy_draws(scene, seg_host, H) if self.rng == 'numpy' else None
+
+        a = L.OpticsArgs()
+        a.h = H
+        a.d_slot_parent, a.d_slot_surf = slot_parent.data_ptr(), slot_surf.data_ptr()
+        a.d_vertices, a.d_directions, a.d_energy = cur.V.data_ptr(), cur.D.data_ptr(), cur.E.data_ptr()
+        a.d_wavelengths = cur.W.data_ptr() if cur.W is not None else None
+        a.ld_in = cur.V.stride(0)
+        a.d_out_vertices, a.d_out_directions = oV.data_ptr(), oD.data_ptr()
+        a.d_out_energy, a.d_out_parents, a.ld_out = oE.data_ptr(), oP.data_ptr(), H
+        for j in range(3):
+            a.d_draws[j] = draws[j].data_ptr() if draws is not None else None
+        a.seed, a.bounce, a.min_energy = self.seed, bounce, float(min_energy)
+        a.d_absorbed = absorbed.data_ptr() if absorbed is not None else None
+        a.d_normals = normals.data_ptr() if normals is not None else None
+        a.d_cull = cull.data_ptr()
+        L.check(lib.trc_optics(scene.handle, C.byref(a), st))
+
+        oW = cur.W.index_select(0, slot_parent[:H].long()) if cur.W is not None else None
+        if scene.has_accountants:
+            self._account(scene, cur, seg_host, slot_parent, oV, oE, absorbed, normals)
+
+        n_cull = int(cull.sum().item())
+        rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
+        if n_cull and n_cull < H:
+            # survivors first, weak rays at the back (tracer_engine.py:242-245, 268-274)
+            k2 = torch.empty(H, dtype=i32, device=dev)
+            perm = torch.empty(H, dtype=i32, device=dev)
+            work = torch.empty(int(lib.trc_sort_work_bytes(H, 2)), dtype=torch.uint8, device=dev)
+            L.check(lib.trc_sort_pairs(H, 2, L.dptr(cull), None, L.dptr(k2), L.dptr(perm), L.dptr(count),
+                                       L.dptr(work), st))
+            pV, pD = torch.empty_like(oV), torch.empty_like(oD)
+            pE, pP = torch.empty_like(oE), torch.empty_like(oP)
+            L.check(lib.trc_gather_rows(H, L.dptr(perm), 3, L.dptr(oV), H, L.dptr(pV), H, None, None, st))
+            L.check(lib.trc_gather_rows(H, L.dptr(perm), 3, L.dptr(oD), H, L.dptr(pD), H, None, None, st))
+            L.check(lib.trc_gather_rows(H, L.dptr(perm), 1, L.dptr(oE), H, L.dptr(pE), H, L.dptr(oP), L.dptr(pP), st))
+            pW = oW.index_select(0, perm.long()) if oW is not None else None
+            rec = dict(V=pV, D=pD, E=pE, P=pP, W=pW)
+        rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
+        return rec, H - n_cull, H
+
+    def _account(self, scene, cur, seg, slot_parent, oV, oE, absorbed, normals):
+        """What Accountant.count() stores, one chunk per surface per bounce
+        (optics_callables.py:1597-1790), kept in HBM until read."""
+        for s, orec in enumerate(scene.optics):
+            if not orec['accountants']:
+                continue
+            a, b = int(seg[s]), int(seg[s + 1])
+            if b == a:
+                continue
+            par = None
+            for acc, field, src in orec['accountants']:
+                if src == 'hits':
+                    chunk = oV[:, a:b].clone()
+                elif src == 'absorbed':
+                    chunk = absorbed[a:b].clone()
+                elif src == 'e_out':
+                    chunk = oE[a:b].clone()
+                elif src == 'normals':
+                    chunk = normals[:, a:b].clone()
+                else:
+                    if par is None:
+                        par = slot_parent[a:b].long()
+                    if src == 'e_in':
+                        chunk = cur.E.index_select(0, par)
+                    elif src == 'dirs_in':
+                        chunk = cur.D.index_select(1, par)
+                    elif src == 'wavelengths':
+                        if cur.W is None:
+                            raise ValueError("Spectral accountant needs a 'wavelengths' bundle property")
+                        chunk = cur.W.index_select(0, par)
+                getattr(acc, field).append(_LazyRows(chunk))
+
+    @staticmethod
+    def _as_bundle(rec, n=None):
+        def cols(t):
+            if t is None:
+                return None
+            return _DeviceColumns([t if n is None else t[..., :n]])
+        kw = {}
+        if rec.get('W') is not None:
+            kw['wavelengths'] = cols(rec['W'])
+        return RayBundle(vertices=cols(rec['V']), directions=cols(rec['D']), energy=cols(rec['E']),
+                         parents=cols(rec['P']), **kw)
+
+    # ------------------------------------------------------------- trace
+    def ray_tracer(self, bundle, reps=100, min_energy=1e-10, tree=True, accel=False, Kd_Tree=None, **kwargs):
+        """Trace ``bundle`` through the assembly; same contract as
+        tracer_engine.py:124-295.  Returns (vertices, directions) of the last
+        live bundle as NumPy arrays."""
+        import torch
+        self.reps = reps
+        self.minener = min_energy
+        self.tree = RayTree()
+        if tree is True:
+            self.tree.append(bundle)
+        scene = self.compile()
+        self.Kd_Tree = Kd_Tree if Kd_Tree is not None else (scene if accel else None)
+        if self.device_accel == 'bvh' or accel:
+            use_bvh = True
+        elif self.device_accel == 'brute':
+            use_bvh = False
+        else:
+            use_bvh = scene.num_surfaces > 16
+        if scene.needs_wavelengths and not bundle.has_property('wavelengths'):
+            raise ValueError("scene has spectral optics but the bundle carries no 'wavelengths'")
+
+        with torch.cuda.device(self.device):
+            cur = self._to_device(bundle)
+            e0 = cur.E.sum() if cur.n else None
+            ray_bounces = 0
+            per_bounce = []
+            last_rec = None
+            for i in range(reps):
+                ray_bounces += cur.n
+                rec, n_surv, H = self._bounce(scene, cur, i, min_energy, use_bvh)
+                per_bounce.append((cur.n, H, n_surv))
+                if rec is None:
+                    last_rec = None
+                    cur = _DevBundle(cur.V[:, :0], cur.D[:, :0], cur.E[:0], None if cur.W is None else cur.W[:0])
+                    logging.log(self.loglevel, 'Ray bundle depleted')
+                    break
+                last_rec = rec
+                if tree:
+                    full = dict(rec)
+                    full.pop('pre_cull')
+                    self.tree.append(self._as_bundle(full))
+                W = rec['W'][:n_surv] if rec['W'] is not None else None
+                cur = _DevBundle(rec['V'][:, :n_surv], rec['D'][:, :n_surv], rec['E'][:n_surv], W)
+                if cur.n == 0:
+                    logging.log(self.loglevel, 'Ray bundle depleted')
+                    break
+            if not tree:
+                # only the last record, in pre-cull order (tracer_engine.py:288-291)
+                self.tree.append(self._as_bundle(last_rec['pre_cull']) if last_rec is not None
+                                 else RayBundle.empty_bund())
+            self.stats = dict(ray_bounces=ray_bounces, per_bounce=per_bounce, surfaces=scene.num_surfaces,
+                              use_bvh=use_bvh)
+            if cur.n != 0:
+                logging.warning(f'{cur.n} rays left at the end of the simulation')
+                frac = float((cur.E.sum() / e0).item()) * 100.
+                logging.warning(f'Remaining energy in last bundle: {frac}%')
+            return cur.V.contiguous().cpu().numpy(), cur.D.contiguous().cpu().numpy()
