@@ -1,0 +1,215 @@
+"""CPU: host-side logic -- C ABI surface, scene compiler, BVH builder, the
+API mirror (RayBundle, optics name factory, scene graph)."""
+import os
+import re
+import warnings
+
+import numpy as np
+import pytest
+
+from tests import scenes
+from tests.golden.make_golden import ZOO_RAYS, ZOO_SEED
+
+T = scenes.NS('tracer_b200')
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    """The shared library loads and exports each function of include/tracer_b200.h
+    (no compute call: there is no GPU here)."""
+    from tracer_b200 import _lib
+    header = open(os.path.join(ROOT, 'include', 'tracer_b200.h')).read()
+    header = re.sub(r'/\*.*?\*/', '', header, flags=re.S)
+    declared = set(re.findall(r'\b(trc_[a-z0-9_]+)\s*\(', header))
+    assert declared, 'no declarations parsed'
+    lib = _lib.load()
+    for name in sorted(declared):
+        assert hasattr(lib, name), f'{name} declared in the header but not exported'
+    assert declared == set(_lib.SIGNATURES), 'ctypes SIGNATURES out of sync with the header'
+    assert lib.trc_abi_version() == _lib.ABI_VERSION
+    assert _lib.SURFACE_DTYPE.itemsize == 352 and _lib.BVH_NODE_DTYPE.itemsize == 64
+
+
+def test_bad_arguments_return_status_not_crash():
+    from tracer_b200 import _lib
+    lib = _lib.load()
+    assert lib.trc_sort_work_bytes(-1, 4) == -1
+    assert lib.trc_sort_work_bytes(1000, 219) > 0
+    with pytest.raises(ValueError):
+        _lib.check(lib.trc_nearest_hit(None, 10, None, None, 10, 0, None, None))
+    assert b'trc_nearest_hit' in lib.trc_last_error()
+
+
+@pytest.mark.parametrize('name', sorted(scenes.gm_zoo(T)))
+def test_compiled_aabb_is_conservative(name):
+    """Every oracle hit point of a bounded surface lies inside its compiled AABB,
+    so BVH culling can never drop a real hit."""
+    from oracle.numpy_engine import find_intersections
+    from tracer_b200.scene import CompiledScene
+    asm = scenes.zoo_scene(T, name)
+    sc = CompiledScene(asm, upload=False)
+    rays = scenes.zoo_rays(T, ZOO_RAYS, ZOO_SEED)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        prm, points, _ = find_intersections(asm.get_surfaces()[0], rays.get_vertices(), rays.get_directions())
+    hit = np.nonzero(np.isfinite(prm))[0]
+    assert len(hit) > 50
+    if len(sc.unbounded):
+        assert name in ('flat', 'paraboloid', 'parab_cyl', 'cone_inf', 'cyl_inf', 'quadric_flat')
+        return
+    p = points(hit)
+    assert np.all(p >= sc.aabb_lo[0][:, None]) and np.all(p <= sc.aabb_hi[0][:, None])
+
+
+def _bvh_reach(nodes, leaf_surfs):
+    seen = []
+    stack = [0]
+    while stack:
+        i = stack.pop()
+        nd = nodes[i]
+        if nd['count'] != 0:
+            for k in range(max(nd['count'], 0)):
+                seen.append(int(leaf_surfs[nd['first'] + k]))
+        else:
+            for c in (nd['first'], nd['first'] + 1):
+                ch = nodes[c]
+                if ch['count'] >= 0:
+                    assert np.all(ch['lo'] >= nd['lo']) and np.all(ch['hi'] <= nd['hi'])
+                stack.append(int(c))
+    return seen
+
+
+@pytest.mark.parametrize('n,leaf', [(1, 2), (2, 2), (3, 1), (5, 2), (219, 2), (1000, 4)])
+def test_bvh_builder_invariants(n, leaf):
+    from tracer_b200.scene import build_bvh
+    rng = np.random.RandomState(n)
+    c = rng.uniform(-10, 10, size=(n, 3))
+    half = rng.uniform(0.1, 1.0, size=(n, 3))
+    nodes, order = build_bvh(c - half, c + half, leaf)
+    seen = _bvh_reach(nodes, order)
+    assert sorted(seen) == list(range(n)), 'every box in exactly one leaf'
+    for nd in nodes:
+        if nd['count'] > 0:
+            idx = order[nd['first']:nd['first'] + nd['count']]
+            assert np.all((c - half)[idx] >= nd['lo']) and np.all((c + half)[idx] <= nd['hi'])
+            assert nd['count'] <= leaf
+
+
+def test_nsttf_scene_compiles_like_the_survey_says():
+    from tracer_b200 import _lib as L
+    from tracer_b200.scene import CompiledScene
+    asm, _ = scenes.c3_nsttf(T, n_rays=10)
+    assert len(asm.get_objects()) == 655
+    sc = CompiledScene(asm, upload=False)
+    assert sc.num_surfaces == 219
+    r = sc.records
+    # receiver first? no: sub-assemblies come first (assembly.py:60-65) -> heliostats 0..217, receiver 218
+    assert np.all(r['gkind'] == L.G_RECT_PLATE)
+    assert np.all(r['okind'][:218] == L.O_REAL_REFLECTIVE) and r['okind'][218] == L.O_REFLECTIVE
+    assert np.all(r['flags'] & L.F_ONE_SIDED)
+    assert sc.optics[218]['accountants'] and not sc.optics[0]['accountants']
+    inv = r['inv'].reshape(-1, 3, 4)
+    fr = r['frame'].reshape(-1, 3, 4)
+    for k in (0, 100, 218):
+        f4 = np.vstack((fr[k], [0, 0, 0, 1]))
+        assert np.allclose(np.vstack((inv[k], [0, 0, 0, 1])) @ f4, np.eye(4), atol=1e-12)
+
+
+def test_optics_name_factory():
+    oc = T.optics_callables
+    r = oc.ReflectiveReceiver(0.3)
+    assert [type(a).__name__ for a in r.accountants] == ['AbsorptionAccountant', 'LocationAccountant']
+    d = oc.OneSidedRealReflectiveDetector(0.1, 1e-3, True)
+    assert [a.shorthand for a in d.accountants] == ['Absorber', 'Location', 'Directional']
+    assert type(d._opt).__name__ == 'OneSidedRealReflective' and d._opt.bi_var is True
+    t = oc.LambertianTransmitter(0.2)
+    assert [a.shorthand for a in t.accountants] == ['Scatterer', 'Location']
+    x = oc.LambertianSpecularDirectionalReceiver(0.1, 0.5)
+    assert type(x._opt).__name__ == 'LambertianSpecular'
+    assert [a.shorthand for a in x.accountants] == ['Absorber', 'Location', 'Directional']
+    assert r.get_all_hits()[0].shape == (0,) and r.get_all_hits()[1].shape == (3, 0)
+    with pytest.raises(AttributeError):
+        oc.NoSuchOpticsReceiver
+    with pytest.raises(NotImplementedError):
+        oc.RefractiveHomogenous
+    with pytest.raises(TypeError):
+        r(None, None, None)            # descriptions are not callable on the host
+
+
+def test_unknown_classes_and_hooks_raise_at_compile_time():
+    from tracer_b200.scene import CompiledScene
+
+    class Weird(T.geometry_manager.GeometryManager):
+        pass
+
+    def asm_with(gm, opt):
+        return T.assembly.Assembly(objects=[T.object.AssembledObject(surfs=[T.surface.Surface(gm, opt)])])
+    with pytest.raises(NotImplementedError, match='Weird'):
+        CompiledScene(asm_with(Weird(), T.optics_callables.Reflective(0.)), upload=False)
+
+    class WeirdOptics(object):
+        pass
+    with pytest.raises(NotImplementedError, match='WeirdOptics'):
+        CompiledScene(asm_with(T.flat_surface.RectPlateGM(1, 1), WeirdOptics()), upload=False)
+
+    class Owner(T.object.AssembledObject):
+        def own_rays(self, rays, surface_id):
+            return np.ones(rays.get_num_rays(), dtype=bool)
+    a = T.assembly.Assembly(objects=[Owner(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(1, 1),
+                                                                    T.optics_callables.Reflective(0.))])])
+    with pytest.raises(NotImplementedError, match='own_rays'):
+        CompiledScene(a, upload=False)
+    shared = T.optics_callables.ReflectiveReceiver(0.)
+    objs = [T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(1, 1), shared)])
+            for _ in range(2)]
+    with pytest.raises(NotImplementedError, match='shared'):
+        CompiledScene(T.assembly.Assembly(objects=objs), upload=False)
+
+
+def test_constructor_validation_matches_reference_errors():
+    with pytest.raises(ValueError):
+        T.flat_surface.RectPlateGM(-1, 1)
+    with pytest.raises(ValueError):
+        T.flat_surface.RoundPlateGM(1., 2.)
+    with pytest.raises(ValueError):
+        T.sphere_surface.SphericalGM(0)
+    with pytest.raises(AttributeError):
+        T.cone.FiniteCone(0, 1)
+    with pytest.raises(AttributeError):
+        T.cone.ConicalFrustum(0, 1, 0, 2)
+    with pytest.raises(ValueError):
+        T.surface.Surface(T.flat_surface.RectPlateGM(1, 1), None, location=np.zeros(2))
+
+
+def test_ray_bundle_api():
+    RB = T.ray_bundle.RayBundle
+    v = np.arange(12.).reshape(3, 4)
+    b = RB(vertices=v, directions=v + 1, energy=np.arange(4.), wavelengths=np.arange(4.) * 1e-6)
+    assert b.get_num_rays() == 4 and b.has_property('wavelengths') and b.has_property('parents')
+    with pytest.raises(KeyError):
+        b.get_parents()
+    c = b.inherit(np.array([2, 0]), energy=np.array([9., 8.]), parents=np.array([2, 0]))
+    assert np.array_equal(c.get_vertices(), v[:, [2, 0]]) and np.array_equal(c.get_energy(), [9., 8.])
+    assert np.array_equal(c.get_wavelengths(), [2e-6, 0.])
+    d = b.delete_rays(np.array([1]))
+    assert d.get_num_rays() == 3 and np.array_equal(d.get_energy(), [0., 2., 3.])
+    s = b + b
+    assert s.get_num_rays() == 8
+    cat = T.ray_bundle.concatenate_rays([b, d])
+    assert cat.get_num_rays() == 7
+    assert T.ray_bundle.concatenate_rays([]).get_num_rays() == 0
+    b.set_energy(5., selector=np.array([0]))
+    assert b.get_energy()[0] == 5.
+    assert b.get_energy(selector=np.array([1, 2])).shape == (2,)
+
+
+def test_ray_tree_history():
+    RT, RB = T.trace_tree.RayTree, T.ray_bundle.RayBundle
+    t = RT()
+    z = np.zeros((3, 4))
+    t.append(RB(vertices=z, directions=z, energy=np.ones(4)))
+    t.append(RB(vertices=z, directions=z, energy=np.ones(4), parents=np.array([1, 0, 3, 2])))
+    t.append(RB(vertices=z[:, :2], directions=z[:, :2], energy=np.ones(2), parents=np.array([2, 1])))
+    assert t.num_bunds() == 3
+    assert [list(p) for p in t.ordered_parents()] == [[1, 0, 3, 2], [2, 1]]
+    assert list(t.ray_history(0)) == [0, 2, 3]

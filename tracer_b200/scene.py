@@ -292,8 +292,9 @@ def build_bvh(lo, hi, leaf_size=2):
 class CompiledScene(object):
     """Flat tables for one Assembly + the device handle."""
 
-    def __init__(self, assembly, leaf_size=2):
+    def __init__(self, assembly, leaf_size=2, upload=True):
         self.assembly = assembly
+        self.handle = None
         surfaces = assembly.get_surfaces()
         if len(surfaces) == 0:
             raise ValueError("assembly has no surfaces")
@@ -343,9 +344,15 @@ class CompiledScene(object):
         self.unbounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) != 0)[0].astype(np.int32)
         self.bounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) == 0)[0].astype(np.int32)
         self.leaf_size = leaf_size
-        self.handle = None
         self.bvh_nodes = None
-        self._upload()
+        if len(self.bounded):
+            self.bvh_nodes, order = build_bvh(self.aabb_lo[self.bounded], self.aabb_hi[self.bounded], leaf_size)
+            self.bvh_leaf_surfaces = np.ascontiguousarray(self.bounded[order])
+        else:
+            self.bvh_nodes = np.zeros(0, dtype=L.BVH_NODE_DTYPE)
+            self.bvh_leaf_surfaces = np.zeros(0, np.int32)
+        if upload:
+            self._upload()
 
     @staticmethod
     def _check_objects(assembly):
@@ -372,12 +379,7 @@ class CompiledScene(object):
     def _upload_bvh(self):
         import ctypes as C
         lib = L.load()
-        if len(self.bounded):
-            nodes, order = build_bvh(self.aabb_lo[self.bounded], self.aabb_hi[self.bounded], self.leaf_size)
-            leaf_surfs = np.ascontiguousarray(self.bounded[order])
-        else:
-            nodes, leaf_surfs = np.zeros(0, dtype=L.BVH_NODE_DTYPE), np.zeros(0, np.int32)
-        self.bvh_nodes, self.bvh_leaf_surfaces = nodes, leaf_surfs
+        nodes, leaf_surfs = self.bvh_nodes, self.bvh_leaf_surfaces
         unb = np.ascontiguousarray(self.unbounded)
         L.check(lib.trc_scene_set_bvh(
             self.handle, nodes.ctypes.data_as(C.c_void_p) if len(nodes) else None, len(nodes),
