@@ -1,0 +1,151 @@
+"""GPU arm of bench.py (kept separate so `bench.py --impl reference` never imports torch.cuda)."""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+
+from bench import (ALGO_BYTES_PER_RAY_HIT_KERNEL, FLUX_RES, METRIC, REPS, UNIT, ClockSampler, cpu_baseline,
+                   nsttf_source_geometry)
+from tests import scenes
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from tracer_b200 import _lib as L
+    from tracer_b200.fluxmap import receiver_energy_bins
+    from tracer_b200.tracer_engine_mp import TracerEngineMP
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = L.load()
+    T = scenes.NS("tracer_b200")
+    asm, _ = scenes.c3_nsttf(T, n_rays=10)
+    surfaces = asm.get_surfaces()
+    recv = surfaces[-1]
+    eng = TracerEngineMP(asm, rng="philox", seed=1234 + rank, device_accel=args.accel)
+    centre, direction, radius = nsttf_source_geometry()
+    n = args.rays
+    src = T.sources.buie_sunshape_device(n, centre, direction, radius, 0.01, flux=1000., pre_process_CSR=False,
+                                         seed=99, first_ray=rank * n, total_rays=n * world, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(bundle, read_back=False):
+        asm.reset_all_optics()
+        eng.ray_tracer(bundle, reps=REPS, min_energy=1e-10, tree=True)
+        bins = receiver_energy_bins(recv, FLUX_RES, device=dev)
+        absorbed, hits, bins = eng.reduce_tallies(bins)
+        if read_back:
+            return bins.cpu().numpy(), eng.stats["ray_bounces"]
+        return bins, eng.stats["ray_bounces"]
+
+    def timed(bundle, steps, warmup, read_back=False, sample_clocks=False):
+        sampler = ClockSampler(local) if sample_clocks else None
+        if sampler:
+            sampler.start()          # nvidia-smi needs ~1 s to start: begin before the warm-up
+        for _ in range(warmup):
+            step(bundle, read_back)
+        barrier()
+        l0 = lib.trc_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        bounces, last = 0, None
+        for _ in range(steps):
+            last, b = step(bundle, read_back)
+            bounces += b
+        e1.record()
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        tot = torch.tensor([float(bounces)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        return float(ms.item()), float(tot.item()), lib.trc_launch_count() - l0, clocks, last
+
+    ms, bounces, launches, clocks, bins = timed(src, args.steps, args.warmup, sample_clocks=True)
+    value = bounces / (ms * 1e-3)
+    per_bounce = eng.stats["per_bounce"]
+    tests_equiv = sum(nb[0] for nb in per_bounce) * len(surfaces) * world * args.steps / (ms * 1e-3)
+
+    # dominant kernel alone, on the stream it is launched on
+    V, D = src._props["vertices"].pieces[0], src._props["directions"].pieces[0]
+    hit = torch.empty(n, dtype=torch.int32, device=dev)
+    scene = eng.compile()
+    st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    use_bvh = 1 if args.accel == "bvh" else 0
+    for _ in range(3):
+        L.check(lib.trc_nearest_hit(scene.handle, n, L.dptr(V), L.dptr(D), V.stride(0), use_bvh, L.dptr(hit), st))
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    k0.record()
+    reps_k = 5
+    for _ in range(reps_k):
+        L.check(lib.trc_nearest_hit(scene.handle, n, L.dptr(V), L.dptr(D), V.stride(0), use_bvh, L.dptr(hit), st))
+    k1.record()
+    torch.cuda.synchronize()
+    k_ms = k0.elapsed_time(k1) / reps_k
+    peak, peak_src = _peaks()
+    achieved = ALGO_BYTES_PER_RAY_HIT_KERNEL * n / (k_ms * 1e-3) / 1e9
+    del hit
+
+    e2e = None
+    if not args.no_e2e:
+        hV = torch.empty((3, n), dtype=torch.float64, pin_memory=True)
+        hD = torch.empty((3, n), dtype=torch.float64, pin_memory=True)
+        hE = torch.empty(n, dtype=torch.float64, pin_memory=True)
+        hV.copy_(V); hD.copy_(D); hE.copy_(src._props["energy"].pieces[0])
+        host = T.ray_bundle.RayBundle(vertices=hV.numpy(), directions=hD.numpy(), energy=hE.numpy())
+        e_steps = max(1, min(args.steps, 3))
+        e_ms, e_b, _, _, _ = timed(host, e_steps, 1, read_back=True)
+        e2e = {"value": e_b / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 56 * n,
+               "d2h_bytes_per_step": FLUX_RES * FLUX_RES * 8, "ms_per_step": e_ms / e_steps}
+        del hV, hD, hE, host
+
+    cpu = None
+    if rank == 0 and not args.no_cpu:
+        procs = max(1, min(os.cpu_count() or 1, 64))
+        v, b, wall = cpu_baseline(args.cpu_rays, procs)
+        cpu = {"value": v, "unit": UNIT, "cores": procs, "kind": "port",
+               "sample": "%d processes x %d rays of the same NSTTF scene, reps=%d, %.1f s wall" % (procs, args.cpu_rays, REPS, wall)}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C3 NSTTF heliostat field (218 heliostats + receiver), Buie CSR 0.01, reps=3",
+                       "rays_per_gpu_per_step": n, "surfaces": len(surfaces), "accel": args.accel,
+                       "rng": "philox", "tree": True, "flux_map": "%dx%d on device" % (FLUX_RES, FLUX_RES),
+                       "l2": "inputs (5.6 GB/GPU at 1e8 rays) larger than L2",
+                       "per_bounce_rays_in_hits_survivors": per_bounce},
+            "ray_surface_tests_per_s_brute_equivalent": tests_equiv,
+            "receiver_power_W": float(bins.sum().item()) if hasattr(bins, "sum") else None,
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "kernel": "nearest_hit_%s_kernel" % args.accel,
+                         "kernel_ms": k_ms, "bytes_per_ray": ALGO_BYTES_PER_RAY_HIT_KERNEL, "peak_source": peak_src},
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()

@@ -125,6 +125,8 @@ typedef struct TrcScene TrcScene;
 
 int trc_abi_version(void);
 const char *trc_last_error(void);
+/* Number of CUDA kernels this library has launched in the process so far. */
+uint64_t trc_launch_count(void);
 
 /* Replaces the per-trace Python walk over Assembly.get_surfaces()
  * (tracer_engine.py:165-166): uploads the compiled surface table.

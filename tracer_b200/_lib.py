@@ -74,6 +74,7 @@ _DP = C.POINTER(C.c_double)
 SIGNATURES = {
     "trc_abi_version": (C.c_int, []),
     "trc_last_error": (C.c_char_p, []),
+    "trc_launch_count": (C.c_uint64, []),
     "trc_scene_create": (C.c_int, [_P, _I32, _P, _I32, C.POINTER(_P)]),
     "trc_scene_update_frames": (C.c_int, [_P, _P, _P, _I32]),
     "trc_scene_set_bvh": (C.c_int, [_P, _P, _I32, _P, _I32, _P, _I32]),

@@ -19,7 +19,11 @@ static inline int fail(int code, const char *fmt, const char *detail = "") {
         if (e_ != cudaSuccess) return fail(TRC_ERR_CUDA, #call ": %s", cudaGetErrorString(e_)); \
     } while (0)
 
-static inline int check_launch(const char *what) {
+// process-wide count of kernels launched by this library (bench.py's gpu_launches)
+void trc_note_launches(int n);
+
+static inline int check_launch(const char *what, int n_kernels = 1) {
+    trc_note_launches(n_kernels);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(trc_err_buf(), TRC_ERR_BUF, "%s launch: %s", what, cudaGetErrorString(e));

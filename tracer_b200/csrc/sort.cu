@@ -165,15 +165,6 @@ scan_apply_kernel(uint32_t *__restrict__ data, int64_t n, const uint32_t *__rest
     }
 }
 
-__global__ void copy_pairs_kernel(const int32_t *ki, const int32_t *vi, int32_t *ko, int32_t *vo,
-                                  const int64_t *count) {
-    int64_t n = *count;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        ko[i] = ki[i];
-        vo[i] = vi[i];
-    }
-}
-
 int key_bits(int32_t n_keys) {
     int bits = 1;
     while (bits < 31 && (1LL << bits) < (long long)n_keys) ++bits;
@@ -253,7 +244,7 @@ extern "C" int trc_sort_pairs(int64_t n, int32_t n_keys, const int32_t *d_keys_i
                                                                           w.n_tiles, hist, ko, vo);
         ki = ko; vi = vo;
     }
-    return check_launch("sort_pairs");
+    return check_launch("sort_pairs", 5 * passes);
 }
 
 // ------------------------------------------------------- segment offsets

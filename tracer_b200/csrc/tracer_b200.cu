@@ -25,6 +25,11 @@ using namespace trc;
 static thread_local char g_err[TRC_ERR_BUF] = "";
 char *trc_err_buf() { return g_err; }
 
+#include <atomic>
+static std::atomic<unsigned long long> g_launches{0};
+void trc_note_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+extern "C" uint64_t trc_launch_count(void) { return (uint64_t)g_launches.load(std::memory_order_relaxed); }
+
 extern "C" int trc_abi_version(void) { return TRC_ABI_VERSION; }
 extern "C" const char *trc_last_error(void) { return g_err; }
 

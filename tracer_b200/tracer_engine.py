@@ -207,7 +207,7 @@ class TracerEngine(object):
         oP = torch.empty(H, dtype=i64, device=dev)
         cull = torch.empty(H, dtype=i32, device=dev)
         want = set(src for o in scene.optics for (_, _, src) in o['accountants'])
-        absorbed = torch.empty(H, dtype=f64, device=dev) if 'absorbed' in want else None
+        absorbed = torch.empty(H, dtype=f64, device=dev)   # always: feeds the per-surface totals
         normals = torch.empty((3, H), dtype=f64, device=dev) if 'normals' in want else None
         draws = self._numpy_draws(scene, seg_host, H) if self.rng == 'numpy' else None
 
@@ -227,6 +227,10 @@ class TracerEngine(object):
         a.d_cull = cull.data_ptr()
         L.check(lib.trc_optics(scene.handle, C.byref(a), st))
 
+        # per-surface absorbed energy and hit counts, kept on device: the payload of
+        # the multi-GPU all-reduce (tracer_engine_mp.py) and a tally for 'fast' optics
+        L.check(lib.trc_segment_sums(S, L.dptr(seg), L.dptr(absorbed), L.dptr(self.absorbed_per_surface), st))
+        self.hits_per_surface += seg[1:] - seg[:-1]
         oW = cur.W.index_select(0, slot_parent[:H].long()) if cur.W is not None else None
         if scene.has_accountants:
             self._account(scene, cur, seg_host, slot_parent, oV, oE, absorbed, normals)
@@ -319,6 +323,8 @@ class TracerEngine(object):
         with torch.cuda.device(self.device):
             cur = self._to_device(bundle)
             e0 = cur.E.sum() if cur.n else None
+            self.absorbed_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.float64, device=self.device)
+            self.hits_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.int64, device=self.device)
             ray_bounces = 0
             per_bounce = []
             last_rec = None
