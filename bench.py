@@ -160,6 +160,7 @@ def main():
     ap.add_argument("--rays", type=float, default=1e8, help="rays per GPU per step")
     ap.add_argument("--cpu-rays", type=float, default=2e5, help="rays per host process for the CPU baseline")
     ap.add_argument("--accel", default="bvh", choices=["bvh", "brute"])
+    ap.add_argument("--leaf-size", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

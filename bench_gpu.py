@@ -38,7 +38,7 @@ def run_gpu(args):
     asm, _ = scenes.c3_nsttf(T, n_rays=10)
     surfaces = asm.get_surfaces()
     recv = surfaces[-1]
-    eng = TracerEngineMP(asm, rng="philox", seed=1234 + rank, device_accel=args.accel)
+    eng = TracerEngineMP(asm, rng="philox", seed=1234 + rank, device_accel=args.accel, leaf_size=args.leaf_size)
     centre, direction, radius = nsttf_source_geometry()
     n = args.rays
     src = T.sources.buie_sunshape_device(n, centre, direction, radius, 0.01, flux=1000., pre_process_CSR=False,

@@ -263,9 +263,11 @@ int trc_fluxmap_rect(int64_t n, const double *d_hits, int64_t ld, const double *
                      double hx, double hy, int32_t nx, int32_t ny,
                      double *d_bins, void *stream);
 
-/* Per-surface energy totals: d_totals[s] += sum of d_values over slots of
- * surface s (segment offsets from trc_segment_offsets). */
-int trc_segment_sums(int32_t n_keys, const int64_t *d_offsets, const double *d_values,
+/* Per-surface energy totals: d_totals[k] += sum of d_values[q] over the h slots
+ * whose (sorted) key d_sorted_keys[q] == k.  Feeds the absorbed-energy tally that
+ * is all-reduced across GPUs (the merge of tracer_engine_mp.py:64-119 reduced to
+ * its sums). */
+int trc_segment_sums(int64_t h, const int32_t *d_sorted_keys, const double *d_values,
                      double *d_totals, void *stream);
 
 #ifdef __cplusplus

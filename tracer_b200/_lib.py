@@ -91,7 +91,7 @@ SIGNATURES = {
     "trc_source_buie_disk": (C.c_int, [_I64, _I64, C.c_uint64, C.POINTER(BuieTables), _DP, _DP, _DP, _D, _D,
                                        _P, _P, _P, _I64, _P]),
     "trc_fluxmap_rect": (C.c_int, [_I64, _P, _I64, _P, _DP, _D, _D, _I32, _I32, _P, _P]),
-    "trc_segment_sums": (C.c_int, [_I32, _P, _P, _P, _P]),
+    "trc_segment_sums": (C.c_int, [_I64, _P, _P, _P, _P]),
 }
 
 

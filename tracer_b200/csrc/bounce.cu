@@ -116,16 +116,36 @@ gather_rows_kernel(int64_t n_out, const int32_t *__restrict__ idx, int n_rows,
     if (in_i64) out_i64[j] = in_i64[src];
 }
 
-// one warp per surface segment
-__global__ void segment_sums_kernel(int32_t n_keys, const int64_t *__restrict__ off,
-                                    const double *__restrict__ values, double *__restrict__ totals) {
-    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (warp >= n_keys) return;
-    int64_t a = off[warp], b = off[warp + 1];
+// Sum of `values` per key over a key-sorted slot array.  Each thread folds 8
+// consecutive slots (flushing on a key change), then the warp does a segmented
+// shuffle reduction so that one atomicAdd per (warp, key) reaches memory -- the
+// work is spread over all slots even when every hit is on one surface.
+constexpr int kSumItems = 8;
+__global__ void __launch_bounds__(256)
+segment_sums_kernel(int64_t h, const int32_t *__restrict__ keys, const double *__restrict__ values,
+                    double *__restrict__ totals) {
+    const int lane = threadIdx.x & 31;
+    int64_t first = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * kSumItems;
+    int key = -1;
     double acc = 0.0;
-    for (int64_t i = a + lane; i < b; i += 32) acc += values[i];
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
-    if (lane == 0 && b > a) totals[warp] += acc;
+    for (int k = 0; k < kSumItems; ++k) {
+        int64_t i = first + k;
+        if (i >= h) break;
+        int kk = keys[i];
+        if (kk != key) {
+            if (key >= 0) atomicAdd(&totals[key], acc);
+            key = kk; acc = 0.0;
+        }
+        acc += values[i];
+    }
+    // segmented reduction across the warp (keys are non-decreasing with the lane)
+    for (int o = 1; o < 32; o <<= 1) {
+        double other = __shfl_down_sync(0xffffffffu, acc, o);
+        int okey = __shfl_down_sync(0xffffffffu, key, o);
+        if (lane + o < 32 && okey == key) acc += other;
+    }
+    int prev = __shfl_up_sync(0xffffffffu, key, 1);
+    if (key >= 0 && (lane == 0 || prev != key)) atomicAdd(&totals[key], acc);
 }
 
 struct Proj { double m[12]; };
@@ -189,12 +209,13 @@ extern "C" int trc_gather_rows(int64_t n_out, const int32_t *d_idx, int32_t n_ro
     return check_launch("gather_rows");
 }
 
-extern "C" int trc_segment_sums(int32_t n_keys, const int64_t *d_offsets, const double *d_values,
+extern "C" int trc_segment_sums(int64_t h, const int32_t *d_sorted_keys, const double *d_values,
                                 double *d_totals, void *stream) {
-    if (n_keys < 1 || !d_offsets || !d_values || !d_totals)
+    if (h < 0 || !d_totals || (h > 0 && (!d_sorted_keys || !d_values)))
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_segment_sums: bad argument%s");
-    int64_t threads = (int64_t)n_keys * 32;
-    segment_sums_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n_keys, d_offsets,
+    if (h == 0) return TRC_OK;
+    int64_t threads = (h + kSumItems - 1) / kSumItems;
+    segment_sums_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(h, d_sorted_keys,
                                                                                              d_values, d_totals);
     return check_launch("segment_sums");
 }

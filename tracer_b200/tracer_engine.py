@@ -229,7 +229,7 @@ class TracerEngine(object):
 
         # per-surface absorbed energy and hit counts, kept on device: the payload of
         # the multi-GPU all-reduce (tracer_engine_mp.py) and a tally for 'fast' optics
-        L.check(lib.trc_segment_sums(S, L.dptr(seg), L.dptr(absorbed), L.dptr(self.absorbed_per_surface), st))
+        L.check(lib.trc_segment_sums(H, L.dptr(slot_surf), L.dptr(absorbed), L.dptr(self.absorbed_per_surface), st))
         self.hits_per_surface += seg[1:] - seg[:-1]
         oW = cur.W.index_select(0, slot_parent[:H].long()) if cur.W is not None else None
         if scene.has_accountants:
