@@ -121,6 +121,9 @@ typedef struct TrcBvhNode {
     int32_t pad_[2];
 } TrcBvhNode;            /* 64 bytes */
 
+/* Largest leaf the tree walk accepts (bounds its candidate queue). */
+#define TRC_BVH_MAX_LEAF 4
+
 typedef struct TrcScene TrcScene;
 
 int trc_abi_version(void);
@@ -143,6 +146,15 @@ int trc_scene_update_frames(TrcScene *scene, const double *frames12,
  * (accel_tree.py:20-146).  nodes[0] is the root.  leaf_surfaces lists the
  * surface indices referenced by leaves; `unbounded` lists the always-relevant
  * surfaces (accel_tree.py:59-73). */
+/* Host-only binned-SAH builder over n global AABBs (lo3/hi3: n x 3 float64).
+ * Replaces KdTree.build_tree + determine_split (accel_tree.py:42-204); the
+ * layout is free because results do not depend on it.  Writes at
+ * most 2n nodes (node_capacity >= 2n), the node count and the leaf ordering
+ * (leaf k of a node covers leaf_order[first .. first+count)).  1 <= leaf_size
+ * <= TRC_BVH_MAX_LEAF.  Needs no GPU. */
+int trc_bvh_build(const double *lo3, const double *hi3, int32_t n, int32_t leaf_size,
+                  TrcBvhNode *nodes, int32_t node_capacity, int32_t *n_nodes_out,
+                  int32_t *leaf_order);
 int trc_scene_set_bvh(TrcScene *scene, const TrcBvhNode *nodes, int32_t n_nodes,
                       const int32_t *leaf_surfaces, int32_t n_leaf_surfaces,
                       const int32_t *unbounded, int32_t n_unbounded);

@@ -25,6 +25,7 @@ ABI_VERSION = 1
  O_LAMB_DIRECTIONAL_SPECTRAL) = range(9)
 F_ONE_SIDED = 1
 F_UNBOUNDED = 2
+BVH_MAX_LEAF = 4
 
 # numpy mirror of struct TrcSurfaceRec (352 bytes)
 SURFACE_DTYPE = np.dtype([
@@ -77,6 +78,7 @@ SIGNATURES = {
     "trc_launch_count": (C.c_uint64, []),
     "trc_scene_create": (C.c_int, [_P, _I32, _P, _I32, C.POINTER(_P)]),
     "trc_scene_update_frames": (C.c_int, [_P, _P, _P, _I32]),
+    "trc_bvh_build": (C.c_int, [_P, _P, _I32, _I32, _P, _I32, C.POINTER(_I32), _P]),
     "trc_scene_set_bvh": (C.c_int, [_P, _P, _I32, _P, _I32, _P, _I32]),
     "trc_scene_destroy": (C.c_int, [_P]),
     "trc_scene_num_surfaces": (_I32, [_P]),

@@ -32,14 +32,28 @@ static inline int check_launch(const char *what, int n_kernels = 1) {
     return TRC_OK;
 }
 
+// Tree node as the walk reads it: 32 bytes, the two children of an inner node
+// are adjacent and 64-byte aligned (root at 0, slot 1 unused, pairs from 2).
+// Leaf: count > 0, `first` indexes the leaf-surface list; inner: count == 0,
+// children at `first`, `first + 1`.  Empty leaf: inverted box.
+struct TrcNode32 {
+    float lo[3];
+    float hi[3];
+    int32_t first;
+    int32_t count;
+};
+
 // Device-side scene tables; owned by the library (trc_scene_create/destroy).
 struct TrcScene {
     int32_t n_surfaces = 0;
     TrcSurfaceRec *d_surfaces = nullptr;
     double *d_tables = nullptr;
     int32_t n_table = 0;
-    TrcBvhNode *d_nodes = nullptr;
+    TrcBvhNode *d_nodes = nullptr;     // float64 boxes as uploaded (kept for inspection)
     int32_t n_nodes = 0;
+    TrcNode32 *d_nodes32 = nullptr;    // float32 outward-rounded boxes walked by the kernel (n_nodes + 1 entries)
+    float extent[3] = {0.f, 0.f, 0.f}; // max |coordinate| of the root box per axis
+    unsigned long long *d_chunk_counter = nullptr;   // dynamic work distribution of the tree walk
     int32_t *d_leaf_surfaces = nullptr;
     int32_t n_leaf_surfaces = 0;
     int32_t *d_unbounded = nullptr;

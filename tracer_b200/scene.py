@@ -231,62 +231,22 @@ def _optics_record(opt):
 
 # -------------------------------------------------------------------- BVH
 def build_bvh(lo, hi, leaf_size=2):
-    """Balanced object-median BVH over n AABBs, built level by level with
-    vectorised NumPy sorts.  Level-order layout: children of node i are 2i+1
-    and 2i+2.  Returns (nodes structured array, leaf order int32)."""
+    """Binned-SAH binary BVH over n AABBs, built by the native host builder
+    (csrc/bvh_build.cu; no GPU needed).  Children of an inner node are adjacent
+    (``first``, ``first + 1``).  Returns (nodes structured array, leaf order int32)."""
+    import ctypes as C
+    lib = L.load()
+    lo = np.ascontiguousarray(lo, dtype=np.float64)
+    hi = np.ascontiguousarray(hi, dtype=np.float64)
     n = lo.shape[0]
-    depth = 0
-    while -(-n // (1 << depth)) > leaf_size:
-        depth += 1
-    order = np.arange(n)
-    cent = 0.5 * (lo + hi)
-    bounds = [(np.array([0]), np.array([n]))]       # per level: (starts, ends)
-    for level in range(depth):
-        starts, ends = bounds[-1]
-        counts = ends - starts
-        node_of = np.repeat(np.arange(len(starts)), counts)
-        c = cent[order]
-        cmin = np.full((len(starts), 3), np.inf)
-        cmax = np.full((len(starts), 3), -np.inf)
-        nz = counts > 0
-        if n:
-            cmin[nz] = np.minimum.reduceat(c, starts[nz], axis=0)
-            cmax[nz] = np.maximum.reduceat(c, starts[nz], axis=0)
-        axis = np.argmax(np.where(nz[:, None], cmax - cmin, 0.0), axis=1)
-        key = c[np.arange(n), axis[node_of]]
-        perm = np.lexsort((key, node_of))
-        order = order[perm]
-        mid = starts + (counts + 1) // 2
-        bounds.append((np.stack([starts, mid], 1).reshape(-1), np.stack([mid, ends], 1).reshape(-1)))
-    n_nodes = (1 << (depth + 1)) - 1
-    nodes = np.zeros(n_nodes, dtype=L.BVH_NODE_DTYPE)
-    # leaves
-    starts, ends = bounds[-1]
-    first_leaf = (1 << depth) - 1
-    counts = ends - starts
-    llo = np.full((len(starts), 3), np.inf)
-    lhi = np.full((len(starts), 3), -np.inf)
-    nz = counts > 0
-    if n:
-        llo[nz] = np.minimum.reduceat(lo[order], starts[nz], axis=0)
-        lhi[nz] = np.maximum.reduceat(hi[order], starts[nz], axis=0)
-        # reduceat runs to the next start; empty-leaf gaps cannot occur between non-empty ones
-    nodes['lo'][first_leaf:] = llo
-    nodes['hi'][first_leaf:] = lhi
-    nodes['first'][first_leaf:] = starts
-    nodes['count'][first_leaf:] = np.maximum(counts, 0)
-    # an empty leaf must never be entered: give it an inverted box and count 0 -> treat as leaf via count=-1
-    empty = np.nonzero(~nz)[0] + first_leaf
-    nodes['count'][empty] = -1
-    for level in range(depth - 1, -1, -1):
-        a, b = (1 << level) - 1, (1 << (level + 1)) - 1
-        idx = np.arange(a, b)
-        left, right = 2 * idx + 1, 2 * idx + 2
-        nodes['lo'][idx] = np.minimum(nodes['lo'][left], nodes['lo'][right])
-        nodes['hi'][idx] = np.maximum(nodes['hi'][left], nodes['hi'][right])
-        nodes['first'][idx] = left
-        nodes['count'][idx] = 0
-    return nodes, order.astype(np.int32)
+    nodes = np.zeros(2 * n, dtype=L.BVH_NODE_DTYPE)
+    order = np.zeros(n, dtype=np.int32)
+    n_nodes = C.c_int32(0)
+    L.check(lib.trc_bvh_build(lo.ctypes.data_as(C.c_void_p), hi.ctypes.data_as(C.c_void_p), n,
+                              int(min(max(leaf_size, 1), L.BVH_MAX_LEAF)),
+                              nodes.ctypes.data_as(C.c_void_p), len(nodes), C.byref(n_nodes),
+                              order.ctypes.data_as(C.c_void_p)))
+    return nodes[:n_nodes.value].copy(), order
 
 
 class CompiledScene(object):
