@@ -32,16 +32,18 @@ static inline int check_launch(const char *what, int n_kernels = 1) {
     return TRC_OK;
 }
 
-// Tree node as the walk reads it: 32 bytes, the two children of an inner node
-// are adjacent and 64-byte aligned (root at 0, slot 1 unused, pairs from 2).
-// Leaf: count > 0, `first` indexes the leaf-surface list; inner: count == 0,
-// children at `first`, `first + 1`.  Empty leaf: inverted box.
-struct TrcNode32 {
-    float lo[3];
-    float hi[3];
-    int32_t first;
-    int32_t count;
-};
+// The tree as the walk reads it: one 32-byte record per INNER node holding the
+// boxes of its two children quantised to 16 bits on the grid of the root box
+// (rounded outward), split into two 16-byte halves kept in separate arrays so
+// that random per-lane fetches spread over all shared-memory bank groups:
+//   a = { c0.lo0|c0.lo1<<16, c0.lo2|c0.hi0<<16, c0.hi1|c0.hi2<<16, c1.lo0|c1.lo1<<16 }
+//   b = { c1.lo2|c1.hi0<<16, c1.hi1|c1.hi2<<16, meta0, meta1 }
+// meta: bits 28..30 = leaf surface count (0 = inner node, 7 = empty leaf), bits 0..27 =
+// pair index of the child (inner) or first entry in the candidate list (leaf).
+// Pairs are numbered breadth-first from the root (pair 0 = the root's children).
+struct TrcPairHalf { uint32_t w[4]; };
+#define TRC_META_COUNT(m) (((m) >> 28) & 7u)
+#define TRC_META_INDEX(m) ((m) & 0x0fffffffu)
 
 // Device-side scene tables; owned by the library (trc_scene_create/destroy).
 struct TrcScene {
@@ -51,12 +53,19 @@ struct TrcScene {
     int32_t n_table = 0;
     TrcBvhNode *d_nodes = nullptr;     // float64 boxes as uploaded (kept for inspection)
     int32_t n_nodes = 0;
-    TrcNode32 *d_nodes32 = nullptr;    // float32 outward-rounded boxes walked by the kernel (n_nodes + 1 entries)
+    TrcPairHalf *d_pair_a = nullptr;   // quantised children boxes, first halves  (n_pairs)
+    TrcPairHalf *d_pair_b = nullptr;   // second halves + child metadata          (n_pairs)
+    int32_t n_pairs = 0;
+    uint32_t root_meta = 0;            // meta word of the root node itself
+    float root_lo[3] = {0.f, 0.f, 0.f};   // root box (float32, rounded outward) = quantisation grid origin
+    float root_hi[3] = {0.f, 0.f, 0.f};
+    float qstep[3] = {0.f, 0.f, 0.f};  // grid step per axis: plane = root_lo + q * qstep
     float extent[3] = {0.f, 0.f, 0.f}; // max |coordinate| of the root box per axis
     unsigned long long *d_chunk_counter = nullptr;   // dynamic work distribution of the tree walk
     int32_t *d_leaf_surfaces = nullptr;
     int32_t n_leaf_surfaces = 0;
     int32_t *d_unbounded = nullptr;
     int32_t n_unbounded = 0;
+    int32_t *d_cand = nullptr;         // leaf surfaces followed by unbounded surfaces (the walk's candidate list)
     int num_sms = 148;
 };

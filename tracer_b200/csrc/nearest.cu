@@ -25,6 +25,7 @@
 #include <cuda_runtime.h>
 #include <float.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "geom.cuh"
@@ -71,30 +72,45 @@ nearest_hit_brute_kernel(const TrcSurfaceRec *__restrict__ surfs, int n_surf, in
     if (live) hit_surf[i] = best_s;
 }
 
-// ------------------------------------------------------------------ tree walk
-constexpr int kWalkWarps = 4;                 // warps per CTA
-constexpr int kChunk = 256;                   // consecutive rays owned by a warp at a time
-constexpr int kListCap = 64;                  // active list: filled while < 32, by <= 32 at a time
-constexpr int kQueueCap = 31 + 32 * 2 * TRC_BVH_MAX_LEAF;   // leftover + one visit of every lane
-constexpr int kStack = 64;
-constexpr int kListFields = 10;               // inv[3], ovl[3], ovh[3], slot
 
-struct WalkShared {
+// ------------------------------------------------------------------ tree walk
+constexpr int kWalkWarps = 8;                 // warps per CTA
+constexpr int kChunk = 256;                   // consecutive rays owned by a warp at a time (slot fits 8 bits)
+constexpr int kListCap = 64;                  // active list: filled while < 32, by <= 32 at a time
+constexpr int kQueueCap = 32 + 32 * 2;        // leftover + one visit (two leaf children) of every lane
+constexpr int kStack = 64;
+constexpr int kRing = 3;                       // ray batches in flight per warp (cp.async), 1.5 KB each
+constexpr int kListFields = 10;               // A[3], Bl[3], Bh[3], slot
+constexpr int kSmemPairs = 512;               // top of the tree (breadth-first) cached per CTA: 16 KB
+// queue entry = slot << 24 | (count - 1) << 22 | first candidate-list index: one entry per leaf
+constexpr unsigned kCandMask = 0x003fffffu;
+
+struct WalkWarpShared {
     unsigned long long best_t[kChunk];        // bits of the best float64 t (+inf = none)
     int best_s[kChunk];                       // its surface index (INT_MAX = none)
     float list[kListFields][kListCap];        // SoA: lanes read consecutive entries conflict-free
-    int2 queue[kQueueCap];                    // (slot, surface)
-    int qn;                                   // queue fill
+    unsigned queue[kQueueCap];                // packed (slot, leaf)
+    long long fifo[4];                        // chunk ids in consumption order (written by the prefetcher)
+    double ring[kRing][6][32];                // cp.async landing zone: vertex + direction rows of 32 rays
+};
+
+struct WalkShared {
+    uint4 pair_a[kSmemPairs];                 // TrcPairHalf arrays (see common.cuh)
+    uint4 pair_b[kSmemPairs];
+    WalkWarpShared w[kWalkWarps];
 };
 
 struct WalkParams {
     const TrcSurfaceRec *surfs;
-    const TrcNode32 *nodes;
-    const int32_t *leaf_surfs;
-    const int32_t *unbounded;
-    int n_unbounded;
+    const uint4 *pair_a, *pair_b;
+    int n_pairs;
+    unsigned root_meta;
+    const int32_t *cand;                      // candidate list: leaf surfaces, then unbounded surfaces
+    int unbounded_first, n_unbounded;
     int has_tree;
-    float extent[3];
+    int debug;                                // TRC_WALK_DEBUG experiment bits (timing only)
+    int refill_at;                            // leave the walk loop to refill when <= this many lanes are active
+    float root_lo[3], root_hi[3], qstep[3], extent[3];
     int64_t n;
     const double *vert, *dir;
     int64_t ld;
@@ -103,169 +119,249 @@ struct WalkParams {
 };
 
 #define TRC_INF_BITS 0x7ff0000000000000ULL
+#define TRC_FINF (__int_as_float(0x7f800000))
 
-// Per-ray float32 walk state: t(box plane) = fma(plane, inv, nov).  The box is
-// widened per ray by pad_k = 1e-6 (|v_k| + extent_k): that covers the rounding
-// of the origin and of 1/d to float32 and of the two FMAs, all of which are
-// <= a few 2^-24 (|v_k| + |plane|) in position units.  `lo` planes use the
-// origin moved by +pad, `hi` planes by -pad, which widens the slab for either
-// sign of d.  1/d is clamped to +-1e20 so an axis-parallel ray gives a huge
-// finite interval instead of 0 * inf.
+// Per-ray float32 walk state.  A box plane sits at root_lo + q * qstep (q a
+// 16-bit integer); its ray parameter is
+//     t = (root_lo + q qstep - v) / d = q A + B,   A = qstep / d,  B = (root_lo - v) / d.
+// q enters the FMA as the float 2^23 + q built with one byte-permute
+// (0x4B000000 | q), so B carries the -2^23 A term.  The box is widened per ray by
+//     pad_k = 1e-6 (|v_k| + extent_k) + 1.5 qstep_k
+// which covers the rounding of v and 1/d to float32 and of the FMA (a few 2^-24
+// of |v_k| + |plane|) and the half-step error of folding 2^23 A into B.  `lo`
+// planes use the origin moved by +pad, `hi` planes by -pad, which widens the
+// slab for either sign of d.  1/d is clamped to +-1e20 so an axis-parallel ray
+// gives a huge finite interval instead of 0 * inf.
 struct RayF {
-    float inv[3], novl[3], novh[3];
+    float A[3], Bl[3], Bh[3];
 };
 
-__device__ __forceinline__ void ray_setup(V3 v, V3 d, const float *extent, RayF &r) {
+__device__ __forceinline__ void ray_setup(V3 v, V3 d, const WalkParams &p, RayF &r) {
     const float dv[3] = {(float)d.x, (float)d.y, (float)d.z};
     const float ov[3] = {(float)v.x, (float)v.y, (float)v.z};
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         float inv = fabsf(dv[k]) < 1e-20f ? copysignf(1e20f, dv[k]) : __fdividef(1.0f, dv[k]);
-        float pad = 1e-6f * (fabsf(ov[k]) + extent[k]);
-        r.inv[k] = inv;
-        r.novl[k] = -(ov[k] + pad) * inv;
-        r.novh[k] = -(ov[k] - pad) * inv;
+        float pad = fmaf(1e-6f, fabsf(ov[k]) + p.extent[k], 1.5f * p.qstep[k]);
+        float a = p.qstep[k] * inv;
+        float shift = 8388608.0f * a;
+        r.A[k] = a;
+        r.Bl[k] = (p.root_lo[k] - (ov[k] + pad)) * inv - shift;
+        r.Bh[k] = (p.root_lo[k] - (ov[k] - pad)) * inv - shift;
     }
 }
 
-#define TRC_FINF (__int_as_float(0x7f800000))
+// 2^23 + (low / high 16 bits of w) as a float
+__device__ __forceinline__ float q_lo(unsigned w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7610)); }
+__device__ __forceinline__ float q_hi(unsigned w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7632)); }
 
-// Conservative entry distance of the ray into a node box, +inf when the box is
-// missed or lies beyond tbest.  a = (lo0, lo1, lo2, hi0), b = (hi1, hi2, first, count).
-__device__ __forceinline__ float slab32(float4 a, float4 b, const RayF &r, float tbest) {
-    float t1 = fmaf(a.x, r.inv[0], r.novl[0]), t2 = fmaf(a.w, r.inv[0], r.novh[0]);
+// Conservative entry distance into the box with planes (2^23 + q): lo0,lo1,lo2,hi0,hi1,hi2;
+// +inf when the box is missed or lies beyond tbest.
+__device__ __forceinline__ float slab16(float l0, float l1, float l2, float h0, float h1, float h2,
+                                        const RayF &r, float tbest) {
+    float t1 = fmaf(l0, r.A[0], r.Bl[0]), t2 = fmaf(h0, r.A[0], r.Bh[0]);
     float tmin = fminf(t1, t2), tmax = fmaxf(t1, t2);
-    t1 = fmaf(a.y, r.inv[1], r.novl[1]); t2 = fmaf(b.x, r.inv[1], r.novh[1]);
+    t1 = fmaf(l1, r.A[1], r.Bl[1]); t2 = fmaf(h1, r.A[1], r.Bh[1]);
     tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
-    t1 = fmaf(a.z, r.inv[2], r.novl[2]); t2 = fmaf(b.y, r.inv[2], r.novh[2]);
+    t1 = fmaf(l2, r.A[2], r.Bl[2]); t2 = fmaf(h2, r.A[2], r.Bh[2]);
     tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
     tmin = fmaxf(tmin, 0.0f);
     return (tmin <= tmax && tmin <= tbest) ? tmin : TRC_FINF;
+}
+
+// root box test in plain float32 (same widening)
+__device__ __forceinline__ bool root_hit(V3 v, V3 d, const WalkParams &p) {
+    const float dv[3] = {(float)d.x, (float)d.y, (float)d.z};
+    const float ov[3] = {(float)v.x, (float)v.y, (float)v.z};
+    float tmin = 0.0f, tmax = TRC_FINF;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float inv = fabsf(dv[k]) < 1e-20f ? copysignf(1e20f, dv[k]) : __fdividef(1.0f, dv[k]);
+        float pad = fmaf(1e-6f, fabsf(ov[k]) + p.extent[k], 1.5f * p.qstep[k]);
+        float t1 = (p.root_lo[k] - (ov[k] + pad)) * inv, t2 = (p.root_hi[k] - (ov[k] - pad)) * inv;
+        tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
+    }
+    return tmin <= tmax;
 }
 
 __device__ __forceinline__ float best_as_float(unsigned long long bits) {
     return __double2float_ru(__longlong_as_double((long long)bits));
 }
 
-// Stage C: test queued (slot, surface) candidates in float64, 32 at a time, and
+// Stage C: test queued (slot, leaf) candidates in float64, 32 at a time, and
 // fold them into the per-slot best (t, surface).  `all` drains the queue.
-__device__ __forceinline__ void flush_queue(WalkShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
-                                            bool all) {
-    int qn = sh.qn;
+__device__ __noinline__ int flush_queue(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
+                                        int qn, bool all) {
+    __syncwarp();
+    if (p.debug & 1) qn = 0;
     while (qn >= 32 || (all && qn > 0)) {
         int take = min(32, qn);
         int base = qn - take;
         bool has = lane < take;
-        int2 e = has ? sh.queue[base + lane] : make_int2(0, 0);
+        unsigned e = has ? sh.queue[base + lane] : 0u;
+        const int slot = (int)(e >> 24);
+        const int first = (int)(e & kCandMask);
+        const int cnt = has ? (int)((e >> 22) & 3u) + 1 : 0;
+        // nearest of the leaf's surfaces for this ray (ties: lowest surface index)
         double t = TRC_INF;
+        int surf = INT_MAX;
         if (has) {
-            int64_t ray = chunk_base + e.x;
+            int64_t ray = chunk_base + slot;
             V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
             V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
-            t = intersect(&p.surfs[e.y], v, d);
+            for (int k = 0; k < cnt; ++k) {
+                int s = __ldg(&p.cand[first + k]);
+                double tk = intersect(&p.surfs[s], v, d);
+                if (tk < t || (tk == t && s < surf && tk != TRC_INF)) { t = tk; surf = s; }
+            }
         }
         unsigned long long tb = (unsigned long long)__double_as_longlong(t);
         bool cand = has && tb < TRC_INF_BITS;
-        unsigned long long before = cand ? sh.best_t[e.x] : 0ULL;
+        unsigned long long before = cand ? sh.best_t[slot] : 0ULL;
         __syncwarp();
-        if (cand) atomicMin(&sh.best_t[e.x], tb);
+        if (cand) atomicMin(&sh.best_t[slot], tb);
         __syncwarp();
-        bool win = cand && sh.best_t[e.x] == tb;
-        if (win && tb < before) sh.best_s[e.x] = INT_MAX;     // the old index belonged to a larger t
+        bool win = cand && sh.best_t[slot] == tb;
+        if (win && tb < before) sh.best_s[slot] = INT_MAX;     // the old index belonged to a larger t
         __syncwarp();
-        if (win) atomicMin(&sh.best_s[e.x], e.y);              // ties: lowest surface index
+        if (win) atomicMin(&sh.best_s[slot], surf);            // ties: lowest surface index
         __syncwarp();
         qn = base;
     }
-    if (lane == 0) sh.qn = qn;
-    __syncwarp();
+    return qn;
 }
 
-__global__ void __launch_bounds__(kWalkWarps * 32)
+__device__ __forceinline__ void cp_async8(void *smem_dst, const void *gmem_src) {
+    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+
+__global__ void __launch_bounds__(kWalkWarps * 32, 2)
 nearest_hit_walk_kernel(WalkParams p) {
-    __shared__ WalkShared shared[kWalkWarps];
-    WalkShared &sh = shared[threadIdx.x >> 5];
+    extern __shared__ __align__(16) unsigned char walk_smem[];
+    WalkShared &S = *reinterpret_cast<WalkShared *>(walk_smem);
+    WalkWarpShared &sh = S.w[threadIdx.x >> 5];
     const int lane = threadIdx.x & 31;
     const unsigned full = 0xffffffffu;
     const unsigned lt_mask = (1u << lane) - 1u;
     const int64_t n_chunks = (p.n + kChunk - 1) / kChunk;
 
-    // root of the tree (uniform loads)
-    float4 root_a = make_float4(0.f, 0.f, 0.f, 0.f), root_b = root_a;
-    int root_first = 0, root_count = -1;
-    if (p.has_tree) {
-        const float4 *np = reinterpret_cast<const float4 *>(p.nodes);
-        root_a = __ldg(np); root_b = __ldg(np + 1);
-        root_first = __float_as_int(root_b.z); root_count = __float_as_int(root_b.w);
+    // top of the tree -> shared memory (breadth-first order: the first kSmemPairs pairs)
+    {
+        int np = min(p.n_pairs, kSmemPairs);
+        for (int k = threadIdx.x; k < np; k += blockDim.x) {
+            S.pair_a[k] = __ldg(p.pair_a + k);
+            S.pair_b[k] = __ldg(p.pair_b + k);
+        }
     }
+    __syncthreads();
+    const int root_count = p.has_tree ? (int)TRC_META_COUNT(p.root_meta) : 7;   // 0 inner, 1..4 leaf, 7 nothing
     int stack[kStack];
 
+    // ---- ray prefetcher: the warp streams batches of 32 rays (chunk after chunk, chunk
+    // ids from the global counter) into a ring of kRing shared-memory slots with
+    // cp.async, always kRing - 1 batches ahead of stage A, so a ray is read from HBM
+    // exactly once and stage A never waits for DRAM.
+    int64_t pc;            // chunk being prefetched           (warp-uniform)
+    int poff = 0;          // next ray offset in that chunk
+    int fifo_w = 0, fifo_r = 0, ring_w = 0, ring_r = 0;
+    auto fetch_chunk = [&]() -> int64_t {
+        unsigned long long c = 0;
+        if (lane == 0) c = atomicAdd(p.chunk_counter, 1ULL);
+        c = __shfl_sync(full, c, 0);
+        if (lane == 0) sh.fifo[fifo_w & 3] = (long long)c;
+        ++fifo_w;
+        __syncwarp();
+        return (int64_t)c;
+    };
+    auto issue_batch = [&]() {
+        if (pc < n_chunks) {
+            int64_t ray = pc * kChunk + poff + lane;
+            if (ray < p.n) {
+                double *dst = &sh.ring[ring_w % kRing][0][lane];
+                cp_async8(dst, p.vert + ray);
+                cp_async8(dst + 32, p.vert + p.ld + ray);
+                cp_async8(dst + 64, p.vert + 2 * p.ld + ray);
+                cp_async8(dst + 96, p.dir + ray);
+                cp_async8(dst + 128, p.dir + p.ld + ray);
+                cp_async8(dst + 160, p.dir + 2 * p.ld + ray);
+            }
+            poff += 32;
+            if (pc * kChunk + poff >= p.n || poff >= kChunk) { pc = fetch_chunk(); poff = 0; }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");      // possibly empty: keeps the group count uniform
+        ++ring_w;
+    };
+    pc = fetch_chunk();
+#pragma unroll
+    for (int k = 0; k < kRing - 1; ++k) issue_batch();
+
     for (;;) {
-        unsigned long long c64 = 0;
-        if (lane == 0) c64 = atomicAdd(p.chunk_counter, 1ULL);
-        c64 = __shfl_sync(full, c64, 0);
-        if ((int64_t)c64 >= n_chunks) break;
-        const int64_t chunk_base = (int64_t)c64 * kChunk;
+        const int64_t c_cur = (int64_t)sh.fifo[fifo_r & 3];
+        ++fifo_r;
+        if (c_cur >= n_chunks) break;
+        const int64_t chunk_base = c_cur * kChunk;
         const int chunk_n = (int)min((int64_t)kChunk, p.n - chunk_base);
 
         for (int i = lane; i < kChunk; i += 32) { sh.best_t[i] = TRC_INF_BITS; sh.best_s[i] = INT_MAX; }
-        if (lane == 0) sh.qn = 0;
         __syncwarp();
 
         int next = 0;          // rays of the chunk already through stage A   (warp-uniform)
         int list_n = 0;        // active-list fill                              (warp-uniform)
+        int qn = 0;            // candidate-queue fill                          (warp-uniform)
         bool active = false;   // this lane is walking a ray
         RayF r;
-        int slot = 0, cur = 0, sp = 0;
+        int cur = 0, sp = 0;   // cur = pair index
+        unsigned tag = 0;      // slot << 24
         float tbest = TRC_FINF;
 
         for (;;) {
             // ---------------- stage A: produce survivors until the list can feed a full refill
+#pragma unroll 1
             while (list_n < 32 && next < chunk_n) {
                 int j = next + lane;
                 bool valid = j < chunk_n;
                 next += 32;
+                issue_batch();
+                asm volatile("cp.async.wait_group %0;" ::"n"(kRing - 1) : "memory");
                 RayF nr;
                 bool surv = false;
                 if (valid) {
-                    int64_t ray = chunk_base + j;
-                    V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
-                    V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
-                    ray_setup(v, d, p.extent, nr);
-                    surv = p.has_tree && slab32(root_a, root_b, nr, TRC_FINF) < TRC_FINF;
+                    const double *src = &sh.ring[ring_r % kRing][0][lane];   // this lane's own copies
+                    V3 v = mk(src[0], src[32], src[64]);
+                    V3 d = mk(src[96], src[128], src[160]);
+                    surv = root_count != 7 && root_hit(v, d, p) && !(p.debug & 2);
+                    ray_setup(v, d, p, nr);
                 }
+                ++ring_r;
+                unsigned m = __ballot_sync(full, surv);
                 if (root_count > 0) {
                     // the whole tree is one leaf: its surfaces are candidates of every surviving ray
-                    for (int k = 0; k < root_count; ++k) {
-                        unsigned m = __ballot_sync(full, surv);
-                        int qn = sh.qn;
-                        if (surv) sh.queue[qn + __popc(m & lt_mask)] = make_int2(j, __ldg(&p.leaf_surfs[root_first + k]));
-                        __syncwarp();
-                        if (lane == 0) sh.qn = qn + __popc(m);
-                        __syncwarp();
-                        flush_queue(sh, p, chunk_base, lane, false);
+                    if (root_count != 7) {
+                        if (surv) sh.queue[qn + __popc(m & lt_mask)] =
+                            ((unsigned)j << 24) | ((unsigned)(root_count - 1) << 22) | TRC_META_INDEX(p.root_meta);
+                        qn += __popc(m);
+                        if (qn >= 32) qn = flush_queue(sh, p, chunk_base, lane, qn, false);
                     }
                 } else {
-                    unsigned m = __ballot_sync(full, surv);
                     if (surv) {
                         int e = list_n + __popc(m & lt_mask);
 #pragma unroll
                         for (int k = 0; k < 3; ++k) {
-                            sh.list[k][e] = nr.inv[k]; sh.list[3 + k][e] = nr.novl[k]; sh.list[6 + k][e] = nr.novh[k];
+                            sh.list[k][e] = nr.A[k]; sh.list[3 + k][e] = nr.Bl[k]; sh.list[6 + k][e] = nr.Bh[k];
                         }
                         sh.list[9][e] = __int_as_float(j);
                     }
                     list_n += __popc(m);
                 }
                 // surfaces without a finite box are candidates of every ray (accel_tree.py:59-73)
-                for (int k = 0; k < p.n_unbounded; ++k) {
-                    unsigned m = __ballot_sync(full, valid);
-                    int qn = sh.qn;
-                    if (valid) sh.queue[qn + __popc(m & lt_mask)] = make_int2(j, __ldg(&p.unbounded[k]));
-                    __syncwarp();
-                    if (lane == 0) sh.qn = qn + __popc(m);
-                    __syncwarp();
-                    flush_queue(sh, p, chunk_base, lane, false);
+                if (p.n_unbounded) {
+                    unsigned mv = __ballot_sync(full, valid);
+                    for (int k = 0; k < p.n_unbounded; ++k) {
+                        if (valid) sh.queue[qn + __popc(mv & lt_mask)] = ((unsigned)j << 24) | (unsigned)(p.unbounded_first + k);
+                        qn += __popc(mv);
+                        if (qn >= 32) qn = flush_queue(sh, p, chunk_base, lane, qn, false);
+                    }
                 }
                 __syncwarp();
             }
@@ -277,10 +373,11 @@ nearest_hit_walk_kernel(WalkParams p) {
                     int e = list_n - 1 - rk;
 #pragma unroll
                     for (int k = 0; k < 3; ++k) {
-                        r.inv[k] = sh.list[k][e]; r.novl[k] = sh.list[3 + k][e]; r.novh[k] = sh.list[6 + k][e];
+                        r.A[k] = sh.list[k][e]; r.Bl[k] = sh.list[3 + k][e]; r.Bh[k] = sh.list[6 + k][e];
                     }
-                    slot = __float_as_int(sh.list[9][e]);
-                    cur = root_first; sp = 0; active = true;
+                    int slot = __float_as_int(sh.list[9][e]);
+                    tag = (unsigned)slot << 24;
+                    cur = 0; sp = 0; active = true;
                     tbest = best_as_float(sh.best_t[slot]);
                 }
                 list_n -= min(__popc(idle), list_n);
@@ -289,45 +386,59 @@ nearest_hit_walk_kernel(WalkParams p) {
             if (__ballot_sync(full, active) == 0u) break;   // list empty and chunk exhausted
 
             // ---------------- stage B: walk until enough lanes are idle to be worth a refill
+#pragma unroll 1
             for (;;) {
+                bool l0 = false, l1 = false;
+                unsigned e0 = 0, e1 = 0;
                 if (active) {
-                    const float4 *np = reinterpret_cast<const float4 *>(p.nodes + cur);
-                    float4 a0 = __ldg(np), b0 = __ldg(np + 1), a1 = __ldg(np + 2), b1 = __ldg(np + 3);
-                    float t0 = slab32(a0, b0, r, tbest), t1 = slab32(a1, b1, r, tbest);
-                    int f0 = __float_as_int(b0.z), c0 = __float_as_int(b0.w);
-                    int f1 = __float_as_int(b1.z), c1 = __float_as_int(b1.w);
-                    bool h0 = t0 < TRC_FINF && c0 >= 0, h1 = t1 < TRC_FINF && c1 >= 0;
-                    int m0 = h0 ? c0 : 0, m1 = h1 ? c1 : 0;
-                    if (m0 + m1) {
-                        int pos = atomicAdd(&sh.qn, m0 + m1);
-                        for (int k = 0; k < m0; ++k) sh.queue[pos++] = make_int2(slot, __ldg(&p.leaf_surfs[f0 + k]));
-                        for (int k = 0; k < m1; ++k) sh.queue[pos++] = make_int2(slot, __ldg(&p.leaf_surfs[f1 + k]));
-                    }
-                    bool i0 = h0 && c0 == 0, i1 = h1 && c1 == 0;
+                    uint4 a, b;
+                    if (cur < kSmemPairs) { a = S.pair_a[cur]; b = S.pair_b[cur]; }
+                    else { a = __ldg(p.pair_a + cur); b = __ldg(p.pair_b + cur); }
+                    float t0 = slab16(q_lo(a.x), q_hi(a.x), q_lo(a.y), q_hi(a.y), q_lo(a.z), q_hi(a.z), r, tbest);
+                    float t1 = slab16(q_lo(a.w), q_hi(a.w), q_lo(b.x), q_hi(b.x), q_lo(b.y), q_hi(b.y), r, tbest);
+                    unsigned c0 = TRC_META_COUNT(b.z), c1 = TRC_META_COUNT(b.w);
+                    bool h0 = t0 < TRC_FINF && c0 != 7u, h1 = t1 < TRC_FINF && c1 != 7u;
+                    l0 = h0 && c0 != 0u; l1 = h1 && c1 != 0u;
+                    e0 = tag | ((c0 - 1u) << 22) | TRC_META_INDEX(b.z);
+                    e1 = tag | ((c1 - 1u) << 22) | TRC_META_INDEX(b.w);
+                    bool i0 = h0 && c0 == 0u, i1 = h1 && c1 == 0u;
+                    int f0 = (int)b.z, f1 = (int)b.w;        // inner: meta == pair index
                     if (i0 && i1) {
                         bool swap = t1 < t0;
                         cur = swap ? f1 : f0;
                         stack[sp++] = swap ? f0 : f1;
-                    } else if (i0) cur = f0;
-                    else if (i1) cur = f1;
-                    else if (sp > 0) cur = stack[--sp];
-                    else active = false;
+                    } else if (i0 || i1) {
+                        cur = i0 ? f0 : f1;
+                    } else if (sp > 0) {
+                        cur = stack[--sp];
+                    } else {
+                        active = false;
+                    }
                 }
-                __syncwarp();
-                if (sh.qn >= 32) {
-                    flush_queue(sh, p, chunk_base, lane, false);
-                    if (active) tbest = best_as_float(sh.best_t[slot]);
+                // leaves reached in this step -> candidate queue (positions from ballots, no atomics)
+                unsigned m0 = __ballot_sync(full, l0), m1 = __ballot_sync(full, l1);
+                if (m0 | m1) {
+                    if (l0) sh.queue[qn + __popc(m0 & lt_mask)] = e0;
+                    qn += __popc(m0);
+                    if (l1) sh.queue[qn + __popc(m1 & lt_mask)] = e1;
+                    qn += __popc(m1);
+                    if (qn >= 32) {
+                        qn = flush_queue(sh, p, chunk_base, lane, qn, false);
+                        if (active) tbest = best_as_float(sh.best_t[tag >> 24]);
+                    }
                 }
                 int n_active = __popc(__ballot_sync(full, active));
                 if (n_active == 0) break;
-                if (n_active <= 28 && (list_n > 0 || next < chunk_n)) break;
+                if (n_active <= p.refill_at && (list_n > 0 || next < chunk_n)) break;
             }
         }
-        flush_queue(sh, p, chunk_base, lane, true);
+        flush_queue(sh, p, chunk_base, lane, qn, true);
+        __syncwarp();
         for (int i = lane; i < chunk_n; i += 32)
             p.hit_surf[chunk_base + i] = sh.best_t[i] == TRC_INF_BITS ? -1 : sh.best_s[i];
         __syncwarp();
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
 }  // namespace
@@ -345,18 +456,32 @@ extern "C" int trc_nearest_hit(const TrcScene *sc, int64_t n, const double *d_ve
                                                                    ld, d_hit_surf);
         return check_launch("nearest_hit_brute");
     }
-    if ((sc->n_nodes == 0 && sc->n_unbounded == 0) || !sc->d_chunk_counter)
+    if ((sc->n_nodes == 0 && sc->n_unbounded == 0) || !sc->d_chunk_counter || !sc->d_cand)
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: use_bvh set but no BVH uploaded%s");
     static int occ = 0;
+    static int g_refill_at = 24;
     if (occ == 0) {
-        TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, nearest_hit_walk_kernel, kWalkWarps * 32, 0));
+        const char *env = getenv("TRC_WALK_REFILL_AT");      // tuning knob (0..31)
+        if (env) { int v = atoi(env); if (v >= 0 && v < 32) g_refill_at = v; }
+        TRC_CUDA(cudaFuncSetAttribute(nearest_hit_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(WalkShared)));
+        TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, nearest_hit_walk_kernel, kWalkWarps * 32,
+                                                               sizeof(WalkShared)));
         if (occ < 1) occ = 1;
     }
     WalkParams p;
-    p.surfs = sc->d_surfaces; p.nodes = sc->d_nodes32; p.leaf_surfs = sc->d_leaf_surfaces;
-    p.unbounded = sc->d_unbounded; p.n_unbounded = sc->n_unbounded;
+    p.surfs = sc->d_surfaces;
+    p.pair_a = reinterpret_cast<const uint4 *>(sc->d_pair_a);
+    p.pair_b = reinterpret_cast<const uint4 *>(sc->d_pair_b);
+    p.n_pairs = sc->n_pairs; p.root_meta = sc->root_meta;
+    p.cand = sc->d_cand; p.unbounded_first = sc->n_leaf_surfaces; p.n_unbounded = sc->n_unbounded;
     p.has_tree = sc->n_nodes > 0 ? 1 : 0;
-    for (int k = 0; k < 3; ++k) p.extent[k] = sc->extent[k];
+    p.refill_at = g_refill_at;
+    { const char *dbg = getenv("TRC_WALK_DEBUG"); p.debug = dbg ? atoi(dbg) : 0; }
+    for (int k = 0; k < 3; ++k) {
+        p.root_lo[k] = sc->root_lo[k]; p.root_hi[k] = sc->root_hi[k];
+        p.qstep[k] = sc->qstep[k]; p.extent[k] = sc->extent[k];
+    }
     p.n = n; p.vert = d_vert; p.dir = d_dir; p.ld = ld; p.hit_surf = d_hit_surf;
     p.chunk_counter = sc->d_chunk_counter;
     int64_t n_chunks = (n + kChunk - 1) / kChunk;
@@ -364,6 +489,6 @@ extern "C" int trc_nearest_hit(const TrcScene *sc, int64_t n, const double *d_ve
     int64_t resident = (int64_t)sc->num_sms * occ;
     if (blocks > resident) blocks = resident;
     TRC_CUDA(cudaMemsetAsync(sc->d_chunk_counter, 0, sizeof(unsigned long long), st));
-    nearest_hit_walk_kernel<<<(unsigned)blocks, kWalkWarps * 32, 0, st>>>(p);
+    nearest_hit_walk_kernel<<<(unsigned)blocks, kWalkWarps * 32, sizeof(WalkShared), st>>>(p);
     return check_launch("nearest_hit_walk");
 }

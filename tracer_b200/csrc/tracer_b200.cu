@@ -72,7 +72,9 @@ extern "C" int trc_scene_destroy(TrcScene *sc) {
     cudaFree(sc->d_surfaces);
     cudaFree(sc->d_tables);
     cudaFree(sc->d_nodes);
-    cudaFree(sc->d_nodes32);
+    cudaFree(sc->d_pair_a);
+    cudaFree(sc->d_pair_b);
+    cudaFree(sc->d_cand);
     cudaFree(sc->d_chunk_counter);
     cudaFree(sc->d_leaf_surfaces);
     cudaFree(sc->d_unbounded);
@@ -113,47 +115,103 @@ extern "C" int trc_scene_set_bvh(TrcScene *sc, const TrcBvhNode *nodes, int32_t 
     if (!sc || n_nodes < 0 || n_leaf_surfaces < 0 || n_unbounded < 0)
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_scene_set_bvh: bad argument%s");
     cudaFree(sc->d_nodes); sc->d_nodes = nullptr; sc->n_nodes = 0;
-    cudaFree(sc->d_nodes32); sc->d_nodes32 = nullptr;
+    cudaFree(sc->d_pair_a); sc->d_pair_a = nullptr;
+    cudaFree(sc->d_pair_b); sc->d_pair_b = nullptr; sc->n_pairs = 0;
     cudaFree(sc->d_leaf_surfaces); sc->d_leaf_surfaces = nullptr; sc->n_leaf_surfaces = 0;
     cudaFree(sc->d_unbounded); sc->d_unbounded = nullptr; sc->n_unbounded = 0;
     if (n_nodes > 0) {
         TRC_CUDA(cudaMalloc(&sc->d_nodes, sizeof(TrcBvhNode) * (size_t)n_nodes));
         TRC_CUDA(cudaMemcpy(sc->d_nodes, nodes, sizeof(TrcBvhNode) * (size_t)n_nodes, cudaMemcpyHostToDevice));
         sc->n_nodes = n_nodes;
-        // float32 walk copy: boxes rounded outward, children pairs shifted to even slots
-        std::vector<TrcNode32> n32((size_t)n_nodes + 1);
-        memset(n32.data(), 0, sizeof(TrcNode32) * n32.size());
-        for (int k = 0; k < 3; ++k) sc->extent[k] = 0.f;
-        for (int32_t i = 0; i < n_nodes; ++i) {
-            TrcNode32 &o = n32[i == 0 ? 0 : (size_t)i + 1];
-            const TrcBvhNode &nd = nodes[i];
-            if (nd.count < 0 || (nd.count > 0 && nd.count > TRC_BVH_MAX_LEAF)) {
-                if (nd.count > 0) return fail(TRC_ERR_BAD_ARGUMENT, "trc_scene_set_bvh: leaf larger than TRC_BVH_MAX_LEAF%s");
-                for (int k = 0; k < 3; ++k) { o.lo[k] = INFINITY; o.hi[k] = -INFINITY; }
-                o.first = 0; o.count = 1;      // empty leaf: the inverted box is never entered
-                continue;
-            }
-            for (int k = 0; k < 3; ++k) {
-                float l = (float)nd.lo[k], h = (float)nd.hi[k];
-                if ((double)l > nd.lo[k]) l = nextafterf(l, -INFINITY);
-                if ((double)h < nd.hi[k]) h = nextafterf(h, INFINITY);
-                o.lo[k] = l; o.hi[k] = h;
-            }
-            o.count = nd.count;
-            if (nd.count == 0) {
-                if (nd.first < 1 || nd.first + 1 >= n_nodes)
-                    return fail(TRC_ERR_BAD_ARGUMENT, "trc_scene_set_bvh: child index out of range%s");
-                o.first = nd.first + 1;
-            } else {
-                if (nd.first < 0 || nd.first + nd.count > n_leaf_surfaces)
+        // Walk copy: inner nodes renumbered breadth-first as "pairs" (the top of the
+        // tree is what the kernel caches in shared memory); children boxes quantised
+        // to 16 bits on the grid of the root box, rounded outward.
+        if (nodes[0].count > TRC_BVH_MAX_LEAF)
+            return fail(TRC_ERR_BAD_ARGUMENT, "trc_scene_set_bvh: leaf larger than TRC_BVH_MAX_LEAF%s");
+        double step[3];
+        for (int k = 0; k < 3; ++k) {
+            float l = (float)nodes[0].lo[k], hh = (float)nodes[0].hi[k];
+            if ((double)l > nodes[0].lo[k]) l = nextafterf(l, -INFINITY);
+            if ((double)hh < nodes[0].hi[k]) hh = nextafterf(hh, INFINITY);
+            sc->root_lo[k] = l; sc->root_hi[k] = hh;
+            float st = (float)(((double)hh - (double)l) / 65535.0 * (1.0 + 1e-6));
+            st = nextafterf(st, INFINITY);
+            if (!(st > 1e-30f)) st = 1e-30f;
+            sc->qstep[k] = st; step[k] = (double)st;
+            sc->extent[k] = fmaxf(fabsf(l), fabsf(hh));
+        }
+        auto meta_of = [&](const TrcBvhNode &nd, int32_t pair_index) -> uint32_t {
+            if (nd.count < 0) return 7u << 28;                       // empty leaf
+            if (nd.count == 0) return (uint32_t)pair_index;          // inner
+            return ((uint32_t)nd.count << 28) | (uint32_t)nd.first;  // leaf
+        };
+        std::vector<int32_t> pair_of((size_t)n_nodes, -1), order;   // inner node -> pair index
+        order.reserve((size_t)n_nodes);
+        if (nodes[0].count == 0) { pair_of[0] = 0; order.push_back(0); }
+        for (size_t h = 0; h < order.size(); ++h) {
+            const TrcBvhNode &nd = nodes[order[h]];
+            if (nd.first < 1 || nd.first + 1 >= n_nodes)
+                return fail(TRC_ERR_BAD_ARGUMENT, "trc_scene_set_bvh: child index out of range%s");
+            for (int c = 0; c < 2; ++c) {
+                int32_t ci = nd.first + c;
+                const TrcBvhNode &ch = nodes[ci];
+                if (ch.count > TRC_BVH_MAX_LEAF)
+                    return fail(TRC_ERR_BAD_ARGUMENT, "trc_scene_set_bvh: leaf larger than TRC_BVH_MAX_LEAF%s");
+                if (ch.count > 0 && (ch.first < 0 || ch.first + ch.count > n_leaf_surfaces))
                     return fail(TRC_ERR_BAD_ARGUMENT, "trc_scene_set_bvh: leaf range out of bounds%s");
-                o.first = nd.first;
+                if (ch.count == 0) {
+                    if (pair_of[ci] >= 0 || order.size() >= (size_t)n_nodes)
+                        return fail(TRC_ERR_BAD_ARGUMENT, "trc_scene_set_bvh: node referenced twice%s");
+                    pair_of[ci] = (int32_t)order.size();
+                    order.push_back(ci);
+                }
             }
         }
-        for (int k = 0; k < 3; ++k)
-            sc->extent[k] = fmaxf(fabsf(n32[0].lo[k]), fabsf(n32[0].hi[k]));
-        TRC_CUDA(cudaMalloc(&sc->d_nodes32, sizeof(TrcNode32) * n32.size()));
-        TRC_CUDA(cudaMemcpy(sc->d_nodes32, n32.data(), sizeof(TrcNode32) * n32.size(), cudaMemcpyHostToDevice));
+        if (order.size() >= (1u << 28)) return fail(TRC_ERR_CAPACITY, "trc_scene_set_bvh: too many nodes%s");
+        sc->n_pairs = (int32_t)order.size();
+        sc->root_meta = meta_of(nodes[0], 0);
+        std::vector<TrcPairHalf> pa(order.size() + 1), pb(order.size() + 1);
+        for (size_t h = 0; h < order.size(); ++h) {
+            const TrcBvhNode &nd = nodes[order[h]];
+            uint32_t q[12];
+            uint32_t meta[2];
+            for (int c = 0; c < 2; ++c) {
+                const TrcBvhNode &ch = nodes[nd.first + c];
+                meta[c] = meta_of(ch, ch.count == 0 ? pair_of[nd.first + c] : 0);
+                for (int k = 0; k < 3; ++k) {
+                    double ql = floor((ch.lo[k] - (double)sc->root_lo[k]) / step[k]);
+                    double qh = ceil((ch.hi[k] - (double)sc->root_lo[k]) / step[k]);
+                    if (!(ql >= 0.0)) ql = 0.0;
+                    if (ql > 65535.0) ql = 65535.0;
+                    if (!(qh <= 65535.0)) qh = 65535.0;
+                    if (qh < 0.0) qh = 0.0;
+                    q[6 * c + k] = (uint32_t)ql;
+                    q[6 * c + 3 + k] = (uint32_t)qh;
+                }
+            }
+            pa[h].w[0] = q[0] | (q[1] << 16); pa[h].w[1] = q[2] | (q[3] << 16);
+            pa[h].w[2] = q[4] | (q[5] << 16); pa[h].w[3] = q[6] | (q[7] << 16);
+            pb[h].w[0] = q[8] | (q[9] << 16); pb[h].w[1] = q[10] | (q[11] << 16);
+            pb[h].w[2] = meta[0]; pb[h].w[3] = meta[1];
+        }
+        TRC_CUDA(cudaMalloc(&sc->d_pair_a, sizeof(TrcPairHalf) * pa.size()));
+        TRC_CUDA(cudaMalloc(&sc->d_pair_b, sizeof(TrcPairHalf) * pb.size()));
+        TRC_CUDA(cudaMemcpy(sc->d_pair_a, pa.data(), sizeof(TrcPairHalf) * pa.size(), cudaMemcpyHostToDevice));
+        TRC_CUDA(cudaMemcpy(sc->d_pair_b, pb.data(), sizeof(TrcPairHalf) * pb.size(), cudaMemcpyHostToDevice));
+    }
+    if ((int64_t)n_leaf_surfaces + n_unbounded >= (1 << 22))
+        return fail(TRC_ERR_CAPACITY, "trc_scene_set_bvh: more than 2^22 candidate entries%s");
+    cudaFree(sc->d_cand); sc->d_cand = nullptr;
+    {
+        std::vector<int32_t> cand;
+        cand.reserve((size_t)n_leaf_surfaces + (size_t)n_unbounded + 1);
+        for (int32_t i = 0; i < n_leaf_surfaces; ++i) cand.push_back(leaf_surfaces[i]);
+        for (int32_t i = 0; i < n_unbounded; ++i) cand.push_back(unbounded[i]);
+        for (int32_t v : cand)
+            if (v < 0 || v >= sc->n_surfaces) return fail(TRC_ERR_BAD_ARGUMENT, "trc_scene_set_bvh: surface index out of range%s");
+        if (cand.empty()) cand.push_back(0);
+        TRC_CUDA(cudaMalloc(&sc->d_cand, sizeof(int32_t) * cand.size()));
+        TRC_CUDA(cudaMemcpy(sc->d_cand, cand.data(), sizeof(int32_t) * cand.size(), cudaMemcpyHostToDevice));
     }
     if (!sc->d_chunk_counter) TRC_CUDA(cudaMalloc(&sc->d_chunk_counter, sizeof(unsigned long long)));
     if (n_leaf_surfaces > 0) {
