@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 1
+#define TRC_ABI_VERSION 2
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -192,27 +192,65 @@ int trc_sort_pairs(int64_t n, int32_t n_keys,
 int trc_segment_offsets_dyn(const int64_t *d_count, int64_t n_max, int32_t n_keys,
                             const int32_t *d_sorted_keys, int64_t *d_offsets, void *stream);
 
-/* Optics + accounting for the h sorted hits of one bounce.  Replaces the body
+/* One hit of a bounce: the parent ray (copied while it is on chip in the
+ * nearest-hit kernel, so the optics kernel never gathers from the multi-GB
+ * parent bundle), its index in the parent bundle and the surface it hit. */
+typedef struct TrcHitRecord {
+    double v[3];
+    double d[3];
+    double energy;
+    int32_t ray;
+    int32_t surf;
+} TrcHitRecord;          /* 64 bytes */
+
+#define TRC_HIT_CHUNK 256 /* rays per chunk of trc_trace_hits */
+
+/* trc_nearest_hit fused with the emission of the hit list.  Rays are processed
+ * in chunks of TRC_HIT_CHUNK consecutive rays; chunk c appends its
+ * d_chunk_cnt[c] records (ascending ray index) at d_records[d_chunk_off[c] ...].
+ * Chunks land in arbitrary order; trc_order_hits restores the reference order.
+ * *d_total (device, zeroed by this call) receives the number of hits; records
+ * beyond `capacity` are dropped (the caller checks total <= capacity and
+ * retries with a larger buffer).  d_hit_surf (n int32, as trc_nearest_hit) is
+ * optional (NULL to skip). */
+int trc_trace_hits(const TrcScene *scene, int64_t n_rays,
+                   const double *d_vertices, const double *d_directions, const double *d_energy, int64_t ld,
+                   int32_t use_bvh, int32_t *d_hit_surf,
+                   TrcHitRecord *d_records, int64_t capacity,
+                   uint32_t *d_chunk_off, uint32_t *d_chunk_cnt, int64_t *d_total, void *stream);
+
+/* Child order of the optics loop + concatenate_rays (tracer_engine.py:218-266,
+ * ray_bundle.py:197-223): surface-major, parent-ray-minor.  From the chunk
+ * table of trc_trace_hits builds, for every slot q < h of that order,
+ * d_slot_surf[q] and d_slot_rec[q] (index of its record in d_records), plus the
+ * per-surface segment offsets d_offsets[0..n_keys] (as trc_segment_offsets_dyn).
+ * d_work must hold trc_order_work_bytes(n_chunks, h, n_keys) bytes. */
+int64_t trc_order_work_bytes(int64_t n_chunks, int64_t h, int32_t n_keys);
+int trc_order_hits(int64_t n_chunks, const uint32_t *d_chunk_off, const uint32_t *d_chunk_cnt,
+                   const TrcHitRecord *d_records, int64_t h, int32_t n_keys,
+                   int32_t *d_slot_surf, int32_t *d_slot_rec, int64_t *d_offsets,
+                   void *d_work, void *stream);
+
+/* Optics + accounting for the h ordered hits of one bounce.  Replaces the body
  * of the optics loop: Surface.select_rays / get_outgoing (surface.py:72-94),
  * GM.get_normals / get_intersection_points_global, every optics __call__
  * (optics_callables.py:93-627) and the Accountant.count calls
  * (optics_callables.py:1949-1961).
- *   slot q reads parent ray d_slot_parent[q] hit on surface d_slot_surf[q].
+ *   slot q reads record d_records[d_slot_rec[q]] (parent ray + surface).
  *   child q: vertex = hit point, direction per optics, energy, parent index.
  *   d_draws[k] (k < 3) are injected random draws in slot order (NULL => the
  *   kernel draws from Philox4x32-10 keyed by (seed, bounce, slot)).
+ *   d_wavelengths: per-PARENT-ray wavelengths (indexed by record.ray), nullable.
  *   Optional tallies (NULL to skip): d_absorbed[q] = E_in - E_out
- *   (AbsorptionAccountant :1638-1643), d_normals (3,h) (NormalAccountant).
+ *   (AbsorptionAccountant :1638-1643), d_normals (3,h) (NormalAccountant),
+ *   d_e_in[q], d_dirs_in (3,h) (Reception / Direction accountants),
+ *   d_out_wavelengths[q] (child wavelength = parent's).
  *   d_cull[q] = 1 where child energy <= min_energy (tracer_engine.py:242). */
 typedef struct TrcOpticsArgs {
     int64_t h;
-    const int32_t *d_slot_parent;
-    const int32_t *d_slot_surf;
-    const double *d_vertices;     /* parent bundle */
-    const double *d_directions;
-    const double *d_energy;
-    const double *d_wavelengths;  /* nullable: per-ray wavelength (spectral optics) */
-    int64_t ld_in;
+    const TrcHitRecord *d_records;
+    const int32_t *d_slot_rec;
+    const double *d_wavelengths;  /* nullable: per-parent-ray wavelength (spectral optics) */
     double *d_out_vertices;       /* child bundle, slot order */
     double *d_out_directions;
     double *d_out_energy;
@@ -225,7 +263,11 @@ typedef struct TrcOpticsArgs {
     double min_energy;
     double *d_absorbed;           /* nullable */
     double *d_normals;            /* nullable, (3,h) with stride ld_out */
+    double *d_e_in;               /* nullable */
+    double *d_dirs_in;            /* nullable, (3,h) with stride ld_out */
+    double *d_out_wavelengths;    /* nullable */
     int32_t *d_cull;              /* nullable; int32 so it can key trc_sort_pairs */
+    int64_t *d_n_cull;            /* nullable: device counter incremented by the number of culled children */
 } TrcOpticsArgs;
 int trc_optics(const TrcScene *scene, const TrcOpticsArgs *args, void *stream);
 

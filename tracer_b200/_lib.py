@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtracer_b200.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # enum TrcGeomKind
 (G_FLAT_INFINITE, G_RECT_PLATE, G_RECT_EXTRUDED, G_ROUND_PLATE, G_TRIANGLE, G_PARABOLOID,
@@ -42,18 +42,22 @@ BVH_NODE_DTYPE = np.dtype([
 assert BVH_NODE_DTYPE.itemsize == 64
 
 
+HIT_CHUNK = 256
+HIT_RECORD_BYTES = 64          # struct TrcHitRecord: v[3], d[3], energy (float64), ray, surf (int32)
+
+
 class OpticsArgs(C.Structure):
     _fields_ = [
         ("h", C.c_int64),
-        ("d_slot_parent", C.c_void_p), ("d_slot_surf", C.c_void_p),
-        ("d_vertices", C.c_void_p), ("d_directions", C.c_void_p), ("d_energy", C.c_void_p),
-        ("d_wavelengths", C.c_void_p), ("ld_in", C.c_int64),
+        ("d_records", C.c_void_p), ("d_slot_rec", C.c_void_p), ("d_wavelengths", C.c_void_p),
         ("d_out_vertices", C.c_void_p), ("d_out_directions", C.c_void_p), ("d_out_energy", C.c_void_p),
         ("d_out_parents", C.c_void_p), ("ld_out", C.c_int64),
         ("d_draws", C.c_void_p * 3),
         ("seed", C.c_uint64), ("bounce", C.c_uint32), ("pad_", C.c_uint32),
         ("min_energy", C.c_double),
-        ("d_absorbed", C.c_void_p), ("d_normals", C.c_void_p), ("d_cull", C.c_void_p),
+        ("d_absorbed", C.c_void_p), ("d_normals", C.c_void_p), ("d_e_in", C.c_void_p),
+        ("d_dirs_in", C.c_void_p), ("d_out_wavelengths", C.c_void_p), ("d_cull", C.c_void_p),
+        ("d_n_cull", C.c_void_p),
     ]
 
 
@@ -83,6 +87,9 @@ SIGNATURES = {
     "trc_scene_destroy": (C.c_int, [_P]),
     "trc_scene_num_surfaces": (_I32, [_P]),
     "trc_nearest_hit": (C.c_int, [_P, _I64, _P, _P, _I64, _I32, _P, _P]),
+    "trc_trace_hits": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _I32, _P, _P, _I64, _P, _P, _P, _P]),
+    "trc_order_work_bytes": (_I64, [_I64, _I64, _I32]),
+    "trc_order_hits": (C.c_int, [_I64, _P, _P, _P, _I64, _I32, _P, _P, _P, _P, _P]),
     "trc_sort_work_bytes": (_I64, [_I64, _I32]),
     "trc_sort_pairs": (C.c_int, [_I64, _I32, _P, _P, _P, _P, _P, _P, _P]),
     "trc_segment_offsets_dyn": (C.c_int, [_P, _I64, _I32, _P, _P, _P]),

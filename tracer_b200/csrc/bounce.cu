@@ -10,10 +10,9 @@ namespace {
 
 struct OpticsParams {
     int64_t h;
-    const int32_t *slot_parent;
-    const int32_t *slot_surf;
-    const double *vert, *dir, *energy, *wavelengths;
-    int64_t ld_in;
+    const TrcHitRecord *records;
+    const int32_t *slot_rec;
+    const double *wavelengths;
     double *o_vert, *o_dir, *o_energy;
     int64_t *o_parents;
     int64_t ld_out;
@@ -23,7 +22,11 @@ struct OpticsParams {
     double min_energy;
     double *absorbed;
     double *normals;
+    double *e_in;
+    double *dirs_in;
+    double *o_wavelengths;
     int32_t *cull;
+    unsigned long long *n_cull;
 };
 
 // Philox draws in the units the reference's numpy calls produce
@@ -61,48 +64,62 @@ __device__ __forceinline__ void philox_draws(const TrcSurfaceRec *s, uint64_t se
     }
 }
 
-// One thread per child slot q (surface-major, parent-minor order).  Gathers the
-// parent ray, recomputes the hit on the known surface (same arithmetic as the
-// nearest-hit kernel, hence the same bits), applies the optics and writes the
-// child coalesced.  Replaces Surface.select_rays/get_outgoing (surface.py:72-94)
-// for every surface at once.
+// One thread per child slot q (surface-major, parent-minor order).  Reads the
+// 64-byte hit record (parent ray + surface) written by the nearest-hit kernel,
+// recomputes the hit on the known surface (same arithmetic as that kernel, hence
+// the same bits), applies the optics and writes the child coalesced.  Replaces
+// Surface.select_rays/get_outgoing (surface.py:72-94) for every surface at once.
 __global__ void __launch_bounds__(256)
 optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict__ tables, OpticsParams p) {
     int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= p.h) return;
-    int64_t r = p.slot_parent[q];
-    int sidx = p.slot_surf[q];
-    const TrcSurfaceRec *s = &surfs[sidx];
-    V3 v = mk(p.vert[r], p.vert[p.ld_in + r], p.vert[2 * p.ld_in + r]);
-    V3 d = mk(p.dir[r], p.dir[p.ld_in + r], p.dir[2 * p.ld_in + r]);
-    double e_in = p.energy[r];
-    double wl = p.wavelengths ? p.wavelengths[r] : 0.0;
-    double t = intersect(s, v, d);
-    V3 hit = axpy(v, t, d);
-    V3 n = surface_normal(s, hit, d);
-    double u[3] = {0.0, 0.0, 0.0};
-    if (p.draws[0]) {
-        u[0] = p.draws[0][q];
-        if (p.draws[1]) u[1] = p.draws[1][q];
-        if (p.draws[2]) u[2] = p.draws[2][q];
-    } else {
-        philox_draws(s, p.seed, p.bounce, (uint64_t)q, u);
+    bool live = q < p.h;
+    bool culled = false;
+    if (live) {
+        const double2 *rec = reinterpret_cast<const double2 *>(p.records + p.slot_rec[q]);
+        double2 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2), r3 = __ldg(rec + 3);
+        V3 v = mk(r0.x, r0.y, r1.x);
+        V3 d = mk(r1.y, r2.x, r2.y);
+        double e_in = r3.x;
+        long long tail = __double_as_longlong(r3.y);
+        int64_t r = (int64_t)(unsigned)(tail & 0xffffffffLL);
+        int sidx = (int)(tail >> 32);
+        const TrcSurfaceRec *s = &surfs[sidx];
+        double wl = p.wavelengths ? p.wavelengths[r] : 0.0;
+        double t = intersect(s, v, d);
+        V3 hit = axpy(v, t, d);
+        V3 n = surface_normal(s, hit, d);
+        double u[3] = {0.0, 0.0, 0.0};
+        if (p.draws[0]) {
+            u[0] = p.draws[0][q];
+            if (p.draws[1]) u[1] = p.draws[1][q];
+            if (p.draws[2]) u[2] = p.draws[2][q];
+        } else {
+            philox_draws(s, p.seed, p.bounce, (uint64_t)q, u);
+        }
+        OpticsOut o = apply_optics(s, tables, d, n, e_in, wl, u);
+        if (s->flags & TRC_F_ONE_SIDED) {
+            // OneSided*: rays arriving along +z of the surface lose all energy
+            // (optics_callables.py:201-212, :498-504)
+            const double *f = s->frame;
+            double proj = d.x * f[2] + d.y * f[6] + d.z * f[10];
+            if (proj > 0.0) o.energy = 0.0;
+        }
+        p.o_vert[q] = hit.x; p.o_vert[p.ld_out + q] = hit.y; p.o_vert[2 * p.ld_out + q] = hit.z;
+        p.o_dir[q] = o.dir.x; p.o_dir[p.ld_out + q] = o.dir.y; p.o_dir[2 * p.ld_out + q] = o.dir.z;
+        p.o_energy[q] = o.energy;
+        p.o_parents[q] = r;
+        if (p.absorbed) p.absorbed[q] = e_in - o.energy;
+        if (p.normals) { p.normals[q] = n.x; p.normals[p.ld_out + q] = n.y; p.normals[2 * p.ld_out + q] = n.z; }
+        if (p.e_in) p.e_in[q] = e_in;
+        if (p.dirs_in) { p.dirs_in[q] = d.x; p.dirs_in[p.ld_out + q] = d.y; p.dirs_in[2 * p.ld_out + q] = d.z; }
+        if (p.o_wavelengths) p.o_wavelengths[q] = wl;
+        culled = o.energy <= p.min_energy;
+        if (p.cull) p.cull[q] = culled ? 1 : 0;
     }
-    OpticsOut o = apply_optics(s, tables, d, n, e_in, wl, u);
-    if (s->flags & TRC_F_ONE_SIDED) {
-        // OneSided*: rays arriving along +z of the surface lose all energy
-        // (optics_callables.py:201-212, :498-504)
-        const double *f = s->frame;
-        double proj = d.x * f[2] + d.y * f[6] + d.z * f[10];
-        if (proj > 0.0) o.energy = 0.0;
+    if (p.n_cull) {
+        unsigned m = __ballot_sync(0xffffffffu, culled);
+        if ((threadIdx.x & 31) == 0 && m) atomicAdd(p.n_cull, (unsigned long long)__popc(m));
     }
-    p.o_vert[q] = hit.x; p.o_vert[p.ld_out + q] = hit.y; p.o_vert[2 * p.ld_out + q] = hit.z;
-    p.o_dir[q] = o.dir.x; p.o_dir[p.ld_out + q] = o.dir.y; p.o_dir[2 * p.ld_out + q] = o.dir.z;
-    p.o_energy[q] = o.energy;
-    p.o_parents[q] = r;
-    if (p.absorbed) p.absorbed[q] = e_in - o.energy;
-    if (p.normals) { p.normals[q] = n.x; p.normals[p.ld_out + q] = n.y; p.normals[2 * p.ld_out + q] = n.z; }
-    if (p.cull) p.cull[q] = (o.energy <= p.min_energy) ? 1 : 0;
 }
 
 __global__ void __launch_bounds__(256)
@@ -161,9 +178,20 @@ __device__ __forceinline__ int bin_index(double x, double half, int nb) {
     return k;
 }
 
+// Each CTA bins into a private shared-memory copy of the map (all hits of a
+// receiver land in a few thousand bins: global atomics would serialise) and
+// adds its non-empty bins to the global map once at the end.
+constexpr int kFluxSmemBins = 4096;
 __global__ void __launch_bounds__(256)
 fluxmap_rect_kernel(int64_t n, const double *__restrict__ hits, int64_t ld, const double *__restrict__ energy,
                     Proj pr, double hx, double hy, int nx, int ny, double *__restrict__ bins) {
+    __shared__ double local[kFluxSmemBins];
+    const int nb = nx * ny;
+    const bool priv = nb <= kFluxSmemBins;
+    if (priv) {
+        for (int k = threadIdx.x; k < nb; k += blockDim.x) local[k] = 0.0;
+        __syncthreads();
+    }
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         V3 g = mk(hits[i], hits[ld + i], hits[2 * ld + i]);
@@ -171,7 +199,15 @@ fluxmap_rect_kernel(int64_t n, const double *__restrict__ hits, int64_t ld, cons
         double ly = pr.m[4] * g.x + pr.m[5] * g.y + pr.m[6] * g.z + pr.m[7];
         int ix = bin_index(lx, hx, nx), iy = bin_index(ly, hy, ny);
         if (ix < 0 || iy < 0) continue;
-        atomicAdd(&bins[ix * ny + iy], energy[i]);
+        if (priv) atomicAdd(&local[ix * ny + iy], energy[i]);
+        else atomicAdd(&bins[ix * ny + iy], energy[i]);
+    }
+    if (priv) {
+        __syncthreads();
+        for (int k = threadIdx.x; k < nb; k += blockDim.x) {
+            double v = local[k];
+            if (v != 0.0) atomicAdd(&bins[k], v);
+        }
     }
 }
 
@@ -180,18 +216,18 @@ fluxmap_rect_kernel(int64_t n, const double *__restrict__ hits, int64_t ld, cons
 extern "C" int trc_optics(const TrcScene *sc, const TrcOpticsArgs *a, void *stream) {
     if (!sc || !a || a->h < 0) return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: bad argument%s");
     if (a->h == 0) return TRC_OK;
-    if (!a->d_slot_parent || !a->d_slot_surf || !a->d_vertices || !a->d_directions || !a->d_energy ||
-        !a->d_out_vertices || !a->d_out_directions || !a->d_out_energy || !a->d_out_parents || a->ld_out < a->h)
+    if (!a->d_records || !a->d_slot_rec || !a->d_out_vertices || !a->d_out_directions || !a->d_out_energy ||
+        !a->d_out_parents || a->ld_out < a->h)
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: null buffer or bad stride%s");
     OpticsParams p;
-    p.h = a->h; p.slot_parent = a->d_slot_parent; p.slot_surf = a->d_slot_surf;
-    p.vert = a->d_vertices; p.dir = a->d_directions; p.energy = a->d_energy; p.wavelengths = a->d_wavelengths;
-    p.ld_in = a->ld_in;
+    p.h = a->h; p.records = a->d_records; p.slot_rec = a->d_slot_rec; p.wavelengths = a->d_wavelengths;
     p.o_vert = a->d_out_vertices; p.o_dir = a->d_out_directions; p.o_energy = a->d_out_energy;
     p.o_parents = a->d_out_parents; p.ld_out = a->ld_out;
     for (int k = 0; k < 3; ++k) p.draws[k] = a->d_draws[k];
     p.seed = a->seed; p.bounce = a->bounce; p.min_energy = a->min_energy;
-    p.absorbed = a->d_absorbed; p.normals = a->d_normals; p.cull = a->d_cull;
+    p.absorbed = a->d_absorbed; p.normals = a->d_normals; p.e_in = a->d_e_in; p.dirs_in = a->d_dirs_in;
+    p.o_wavelengths = a->d_out_wavelengths; p.cull = a->d_cull;
+    p.n_cull = reinterpret_cast<unsigned long long *>(a->d_n_cull);
     int64_t blocks = (a->h + 255) / 256;
     optics_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(sc->d_surfaces, sc->d_tables, p);
     return check_launch("optics");
@@ -229,7 +265,7 @@ extern "C" int trc_fluxmap_rect(int64_t n, const double *d_hits, int64_t ld, con
     Proj pr;
     for (int k = 0; k < 12; ++k) pr.m[k] = proj12[k];
     int64_t blocks = (n + 255) / 256;
-    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks > 148 * 2) blocks = 148 * 2;
     fluxmap_rect_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(n, d_hits, ld, d_energy, pr, hx, hy, nx,
                                                                             ny, d_bins);
     return check_launch("fluxmap_rect");

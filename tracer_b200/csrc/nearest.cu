@@ -41,11 +41,39 @@ __device__ __forceinline__ void consider(const TrcSurfaceRec *s, int idx, V3 v, 
 
 #define TRC_STAGE_SURFS 96
 
+// Optional outputs of both kernels: the int32 hit index per ray and/or the hit
+// list (trc_trace_hits): 64-byte records appended chunk by chunk.
+struct HitSink {
+    int32_t *hit_surf;                 // nullable
+    const double *energy;              // parent energies (read for hits only)
+    TrcHitRecord *records;             // nullable
+    int64_t capacity;
+    uint32_t *chunk_off, *chunk_cnt;
+    unsigned long long *total;
+};
+
+__device__ __forceinline__ void store_record(TrcHitRecord *dst, V3 v, V3 d, double e, int ray, int surf) {
+    double2 *o = reinterpret_cast<double2 *>(dst);
+    o[0] = make_double2(v.x, v.y);
+    o[1] = make_double2(v.z, d.x);
+    o[2] = make_double2(d.y, d.z);
+    double tail;
+    {
+        long long bits = ((long long)(unsigned)surf << 32) | (long long)(unsigned)ray;   // little endian: ray, surf
+        tail = __longlong_as_double(bits);
+    }
+    o[3] = make_double2(e, tail);
+}
+
+static_assert(TRC_HIT_CHUNK == 256, "one brute-force block = one chunk");
+
 __global__ void __launch_bounds__(256)
 nearest_hit_brute_kernel(const TrcSurfaceRec *__restrict__ surfs, int n_surf, int64_t n,
                          const double *__restrict__ vert, const double *__restrict__ dir, int64_t ld,
-                         int32_t *__restrict__ hit_surf) {
+                         HitSink sink) {
     __shared__ TrcSurfaceRec stage[TRC_STAGE_SURFS];
+    __shared__ unsigned warp_cnt[8];
+    __shared__ unsigned long long block_base;
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     bool live = i < n;
     V3 v = mk(0, 0, 0), d = mk(0, 0, 1);
@@ -69,9 +97,28 @@ nearest_hit_brute_kernel(const TrcSurfaceRec *__restrict__ surfs, int n_surf, in
             for (int k = 0; k < cnt; ++k) consider(&stage[k], base + k, v, d, best_t, best_s);
         }
     }
-    if (live) hit_surf[i] = best_s;
+    if (live && sink.hit_surf) sink.hit_surf[i] = best_s;
+    if (sink.records) {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        bool hit = live && best_s >= 0;
+        unsigned m = __ballot_sync(0xffffffffu, hit);
+        if (lane == 0) warp_cnt[warp] = __popc(m);
+        __syncthreads();
+        unsigned before = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { unsigned c = warp_cnt[w]; if (w < warp) before += c; total += c; }
+        if (threadIdx.x == 0) {
+            block_base = atomicAdd(sink.total, (unsigned long long)total);
+            sink.chunk_off[blockIdx.x] = (uint32_t)block_base;
+            sink.chunk_cnt[blockIdx.x] = total;
+        }
+        __syncthreads();
+        if (hit) {
+            unsigned long long pos = block_base + before + __popc(m & ((1u << lane) - 1u));
+            if ((int64_t)pos < sink.capacity) store_record(sink.records + pos, v, d, sink.energy[i], (int)i, best_s);
+        }
+    }
 }
-
 
 // ------------------------------------------------------------------ tree walk
 constexpr int kWalkWarps = 8;                 // warps per CTA
@@ -114,7 +161,7 @@ struct WalkParams {
     int64_t n;
     const double *vert, *dir;
     int64_t ld;
-    int32_t *hit_surf;
+    HitSink sink;
     unsigned long long *chunk_counter;
 };
 
@@ -136,19 +183,32 @@ struct RayF {
     float A[3], Bl[3], Bh[3];
 };
 
-__device__ __forceinline__ void ray_setup(V3 v, V3 d, const WalkParams &p, RayF &r) {
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// Float32 set-up of one ray; returns whether the (widened) root box is hit.
+__device__ __forceinline__ bool ray_setup(V3 v, V3 d, const WalkParams &p, RayF &r) {
     const float dv[3] = {(float)d.x, (float)d.y, (float)d.z};
     const float ov[3] = {(float)v.x, (float)v.y, (float)v.z};
+    float tmin = 0.0f, tmax = TRC_FINF;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        float inv = fabsf(dv[k]) < 1e-20f ? copysignf(1e20f, dv[k]) : __fdividef(1.0f, dv[k]);
+        float inv = fabsf(dv[k]) < 1e-20f ? copysignf(1e20f, dv[k]) : rcp_approx(dv[k]);
         float pad = fmaf(1e-6f, fabsf(ov[k]) + p.extent[k], 1.5f * p.qstep[k]);
         float a = p.qstep[k] * inv;
         float shift = 8388608.0f * a;
+        float bl = (p.root_lo[k] - (ov[k] + pad)) * inv, bh = (p.root_lo[k] - (ov[k] - pad)) * inv;
         r.A[k] = a;
-        r.Bl[k] = (p.root_lo[k] - (ov[k] + pad)) * inv - shift;
-        r.Bh[k] = (p.root_lo[k] - (ov[k] - pad)) * inv - shift;
+        r.Bl[k] = bl - shift;
+        r.Bh[k] = bh - shift;
+        // root box planes: lo = grid origin, hi = root_hi
+        float t2 = (p.root_hi[k] - (ov[k] - pad)) * inv;
+        tmin = fmaxf(tmin, fminf(bl, t2)); tmax = fminf(tmax, fmaxf(bl, t2));
     }
+    return tmin <= tmax;
 }
 
 // 2^23 + (low / high 16 bits of w) as a float
@@ -167,21 +227,6 @@ __device__ __forceinline__ float slab16(float l0, float l1, float l2, float h0, 
     tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
     tmin = fmaxf(tmin, 0.0f);
     return (tmin <= tmax && tmin <= tbest) ? tmin : TRC_FINF;
-}
-
-// root box test in plain float32 (same widening)
-__device__ __forceinline__ bool root_hit(V3 v, V3 d, const WalkParams &p) {
-    const float dv[3] = {(float)d.x, (float)d.y, (float)d.z};
-    const float ov[3] = {(float)v.x, (float)v.y, (float)v.z};
-    float tmin = 0.0f, tmax = TRC_FINF;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        float inv = fabsf(dv[k]) < 1e-20f ? copysignf(1e20f, dv[k]) : __fdividef(1.0f, dv[k]);
-        float pad = fmaf(1e-6f, fabsf(ov[k]) + p.extent[k], 1.5f * p.qstep[k]);
-        float t1 = (p.root_lo[k] - (ov[k] + pad)) * inv, t2 = (p.root_hi[k] - (ov[k] - pad)) * inv;
-        tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
-    }
-    return tmin <= tmax;
 }
 
 __device__ __forceinline__ float best_as_float(unsigned long long bits) {
@@ -236,6 +281,8 @@ __device__ __forceinline__ void cp_async8(void *smem_dst, const void *gmem_src) 
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
 }
 
+// kAllShared: the whole tree fits the shared-memory cache (no global-memory path in the walk)
+template <bool kAllShared>
 __global__ void __launch_bounds__(kWalkWarps * 32, 2)
 nearest_hit_walk_kernel(WalkParams p) {
     extern __shared__ __align__(16) unsigned char walk_smem[];
@@ -330,8 +377,7 @@ nearest_hit_walk_kernel(WalkParams p) {
                     const double *src = &sh.ring[ring_r % kRing][0][lane];   // this lane's own copies
                     V3 v = mk(src[0], src[32], src[64]);
                     V3 d = mk(src[96], src[128], src[160]);
-                    surv = root_count != 7 && root_hit(v, d, p) && !(p.debug & 2);
-                    ray_setup(v, d, p, nr);
+                    surv = ray_setup(v, d, p, nr) && root_count != 7 && !(p.debug & 2);
                 }
                 ++ring_r;
                 unsigned m = __ballot_sync(full, surv);
@@ -389,18 +435,17 @@ nearest_hit_walk_kernel(WalkParams p) {
 #pragma unroll 1
             for (;;) {
                 bool l0 = false, l1 = false;
-                unsigned e0 = 0, e1 = 0;
+                unsigned e0 = 0, e1 = 0;       // meta words of the children (leaf: count | first)
                 if (active) {
                     uint4 a, b;
-                    if (cur < kSmemPairs) { a = S.pair_a[cur]; b = S.pair_b[cur]; }
+                    if (kAllShared || cur < kSmemPairs) { a = S.pair_a[cur]; b = S.pair_b[cur]; }
                     else { a = __ldg(p.pair_a + cur); b = __ldg(p.pair_b + cur); }
                     float t0 = slab16(q_lo(a.x), q_hi(a.x), q_lo(a.y), q_hi(a.y), q_lo(a.z), q_hi(a.z), r, tbest);
                     float t1 = slab16(q_lo(a.w), q_hi(a.w), q_lo(b.x), q_hi(b.x), q_lo(b.y), q_hi(b.y), r, tbest);
                     unsigned c0 = TRC_META_COUNT(b.z), c1 = TRC_META_COUNT(b.w);
                     bool h0 = t0 < TRC_FINF && c0 != 7u, h1 = t1 < TRC_FINF && c1 != 7u;
                     l0 = h0 && c0 != 0u; l1 = h1 && c1 != 0u;
-                    e0 = tag | ((c0 - 1u) << 22) | TRC_META_INDEX(b.z);
-                    e1 = tag | ((c1 - 1u) << 22) | TRC_META_INDEX(b.w);
+                    e0 = b.z; e1 = b.w;
                     bool i0 = h0 && c0 == 0u, i1 = h1 && c1 == 0u;
                     int f0 = (int)b.z, f1 = (int)b.w;        // inner: meta == pair index
                     if (i0 && i1) {
@@ -418,9 +463,10 @@ nearest_hit_walk_kernel(WalkParams p) {
                 // leaves reached in this step -> candidate queue (positions from ballots, no atomics)
                 unsigned m0 = __ballot_sync(full, l0), m1 = __ballot_sync(full, l1);
                 if (m0 | m1) {
-                    if (l0) sh.queue[qn + __popc(m0 & lt_mask)] = e0;
+                    // meta (count << 28 | first) -> entry (slot << 24 | (count - 1) << 22 | first)
+                    if (l0) sh.queue[qn + __popc(m0 & lt_mask)] = tag | (((e0 >> 28) - 1u) << 22) | TRC_META_INDEX(e0);
                     qn += __popc(m0);
-                    if (l1) sh.queue[qn + __popc(m1 & lt_mask)] = e1;
+                    if (l1) sh.queue[qn + __popc(m1 & lt_mask)] = tag | (((e1 >> 28) - 1u) << 22) | TRC_META_INDEX(e1);
                     qn += __popc(m1);
                     if (qn >= 32) {
                         qn = flush_queue(sh, p, chunk_base, lane, qn, false);
@@ -434,8 +480,40 @@ nearest_hit_walk_kernel(WalkParams p) {
         }
         flush_queue(sh, p, chunk_base, lane, qn, true);
         __syncwarp();
-        for (int i = lane; i < chunk_n; i += 32)
-            p.hit_surf[chunk_base + i] = sh.best_t[i] == TRC_INF_BITS ? -1 : sh.best_s[i];
+        if (p.sink.hit_surf) {
+            for (int i = lane; i < chunk_n; i += 32)
+                p.sink.hit_surf[chunk_base + i] = sh.best_t[i] == TRC_INF_BITS ? -1 : sh.best_s[i];
+        }
+        if (p.sink.records) {
+            // append this chunk's hits (ascending ray index) to the hit list
+            int h_c = 0;
+#pragma unroll
+            for (int k = 0; k < kChunk / 32; ++k)
+                h_c += __popc(__ballot_sync(full, sh.best_t[lane + 32 * k] != TRC_INF_BITS));
+            unsigned long long base = 0;
+            if (lane == 0) {
+                base = atomicAdd(p.sink.total, (unsigned long long)h_c);
+                p.sink.chunk_off[c_cur] = (uint32_t)base;
+                p.sink.chunk_cnt[c_cur] = (uint32_t)h_c;
+            }
+            base = __shfl_sync(full, base, 0);
+            if (h_c) {
+                int run = 0;
+                for (int k = 0; k < kChunk / 32; ++k) {
+                    int i = lane + 32 * k;
+                    bool hit = sh.best_t[i] != TRC_INF_BITS;
+                    unsigned m = __ballot_sync(full, hit);
+                    unsigned long long pos = base + run + __popc(m & lt_mask);
+                    run += __popc(m);
+                    if (hit && (int64_t)pos < p.sink.capacity) {
+                        int64_t ray = chunk_base + i;
+                        V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
+                        V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
+                        store_record(p.sink.records + pos, v, d, p.sink.energy[ray], (int)ray, sh.best_s[i]);
+                    }
+                }
+            }
+        }
         __syncwarp();
     }
     asm volatile("cp.async.wait_all;" ::: "memory");
@@ -443,17 +521,15 @@ nearest_hit_walk_kernel(WalkParams p) {
 
 }  // namespace
 
-extern "C" int trc_nearest_hit(const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir,
-                               int64_t ld, int32_t use_bvh, int32_t *d_hit_surf, void *stream) {
-    if (!sc || n < 0 || (n > 0 && (!d_vert || !d_dir || !d_hit_surf)) || ld < n)
-        return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: bad argument%s");
+static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir, int64_t ld,
+                          int32_t use_bvh, HitSink sink, cudaStream_t st) {
+    if (sink.records) TRC_CUDA(cudaMemsetAsync(sink.total, 0, sizeof(unsigned long long), st));
     if (n == 0) return TRC_OK;
-    cudaStream_t st = (cudaStream_t)stream;
+    if (n >= 0x7fffffffLL) return fail(TRC_ERR_CAPACITY, "trc_nearest_hit: more than 2^31-1 rays, chunk the bundle%s");
     if (!use_bvh) {
         int64_t blocks = (n + 255) / 256;
-        if (blocks > 0x7fffffffLL) return fail(TRC_ERR_CAPACITY, "trc_nearest_hit: bundle too large, chunk it%s");
         nearest_hit_brute_kernel<<<(unsigned)blocks, 256, 0, st>>>(sc->d_surfaces, sc->n_surfaces, n, d_vert, d_dir,
-                                                                   ld, d_hit_surf);
+                                                                   ld, sink);
         return check_launch("nearest_hit_brute");
     }
     if ((sc->n_nodes == 0 && sc->n_unbounded == 0) || !sc->d_chunk_counter || !sc->d_cand)
@@ -463,9 +539,11 @@ extern "C" int trc_nearest_hit(const TrcScene *sc, int64_t n, const double *d_ve
     if (occ == 0) {
         const char *env = getenv("TRC_WALK_REFILL_AT");      // tuning knob (0..31)
         if (env) { int v = atoi(env); if (v >= 0 && v < 32) g_refill_at = v; }
-        TRC_CUDA(cudaFuncSetAttribute(nearest_hit_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        TRC_CUDA(cudaFuncSetAttribute(nearest_hit_walk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)sizeof(WalkShared)));
-        TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, nearest_hit_walk_kernel, kWalkWarps * 32,
+        TRC_CUDA(cudaFuncSetAttribute(nearest_hit_walk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(WalkShared)));
+        TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, nearest_hit_walk_kernel<false>, kWalkWarps * 32,
                                                                sizeof(WalkShared)));
         if (occ < 1) occ = 1;
     }
@@ -482,13 +560,37 @@ extern "C" int trc_nearest_hit(const TrcScene *sc, int64_t n, const double *d_ve
         p.root_lo[k] = sc->root_lo[k]; p.root_hi[k] = sc->root_hi[k];
         p.qstep[k] = sc->qstep[k]; p.extent[k] = sc->extent[k];
     }
-    p.n = n; p.vert = d_vert; p.dir = d_dir; p.ld = ld; p.hit_surf = d_hit_surf;
+    p.n = n; p.vert = d_vert; p.dir = d_dir; p.ld = ld; p.sink = sink;
     p.chunk_counter = sc->d_chunk_counter;
     int64_t n_chunks = (n + kChunk - 1) / kChunk;
     int64_t blocks = (n_chunks + kWalkWarps - 1) / kWalkWarps;
     int64_t resident = (int64_t)sc->num_sms * occ;
     if (blocks > resident) blocks = resident;
     TRC_CUDA(cudaMemsetAsync(sc->d_chunk_counter, 0, sizeof(unsigned long long), st));
-    nearest_hit_walk_kernel<<<(unsigned)blocks, kWalkWarps * 32, sizeof(WalkShared), st>>>(p);
+    if (sc->n_pairs <= kSmemPairs)
+        nearest_hit_walk_kernel<true><<<(unsigned)blocks, kWalkWarps * 32, sizeof(WalkShared), st>>>(p);
+    else
+        nearest_hit_walk_kernel<false><<<(unsigned)blocks, kWalkWarps * 32, sizeof(WalkShared), st>>>(p);
     return check_launch("nearest_hit_walk");
+}
+
+extern "C" int trc_nearest_hit(const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir,
+                               int64_t ld, int32_t use_bvh, int32_t *d_hit_surf, void *stream) {
+    if (!sc || n < 0 || (n > 0 && (!d_vert || !d_dir || !d_hit_surf)) || ld < n)
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: bad argument%s");
+    HitSink sink = {d_hit_surf, nullptr, nullptr, 0, nullptr, nullptr, nullptr};
+    return launch_nearest(sc, n, d_vert, d_dir, ld, use_bvh, sink, (cudaStream_t)stream);
+}
+
+extern "C" int trc_trace_hits(const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir,
+                              const double *d_energy, int64_t ld, int32_t use_bvh, int32_t *d_hit_surf,
+                              TrcHitRecord *d_records, int64_t capacity, uint32_t *d_chunk_off,
+                              uint32_t *d_chunk_cnt, int64_t *d_total, void *stream) {
+    if (!sc || n < 0 || capacity < 0 || !d_total || ld < n ||
+        (n > 0 && (!d_vert || !d_dir || !d_energy || !d_chunk_off || !d_chunk_cnt || (capacity > 0 && !d_records))))
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_trace_hits: bad argument%s");
+    static TrcHitRecord dummy_rec;   // never written: capacity 0
+    HitSink sink = {d_hit_surf, d_energy, d_records ? d_records : &dummy_rec, d_records ? capacity : 0, d_chunk_off,
+                    d_chunk_cnt, reinterpret_cast<unsigned long long *>(d_total)};
+    return launch_nearest(sc, n, d_vert, d_dir, ld, use_bvh, sink, (cudaStream_t)stream);
 }

@@ -272,3 +272,94 @@ extern "C" int trc_segment_offsets_dyn(const int64_t *d_count, int64_t n_max, in
     segment_offsets_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(d_count, n_keys, d_sorted_keys, d_offsets);
     return check_launch("segment_offsets");
 }
+
+// ------------------------------------------------------- order the hit list
+// trc_trace_hits appends chunks of hits in arbitrary order; the reference
+// order (surface-major, parent-ray-minor) is recovered by (1) an exclusive scan
+// of the per-chunk counts in chunk (= ray) order, (2) writing (surface, record
+// index) pairs at those positions, (3) one stable radix sort by surface.
+namespace {
+
+__global__ void __launch_bounds__(kThreads)
+copy_u32_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, int64_t n) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[i];
+}
+
+// one warp per chunk
+__global__ void __launch_bounds__(kThreads)
+hit_pairs_kernel(int64_t n_chunks, const uint32_t *__restrict__ chunk_off, const uint32_t *__restrict__ chunk_cnt,
+                 const uint32_t *__restrict__ ord_off, const TrcHitRecord *__restrict__ records, int64_t h,
+                 int32_t *__restrict__ keys, int32_t *__restrict__ vals) {
+    int64_t c = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (c >= n_chunks) return;
+    uint32_t cnt = chunk_cnt[c], src = chunk_off[c], dst = ord_off[c];
+    for (uint32_t i = lane; i < cnt; i += 32) {
+        int64_t q = (int64_t)dst + i;
+        if (q < h) {
+            keys[q] = records[src + i].surf;
+            vals[q] = (int32_t)(src + i);
+        }
+    }
+}
+
+struct OrderLayout {
+    int64_t scan_blocks;
+    size_t off_ord, off_sums, off_keys, off_vals, off_sort, total;
+};
+
+OrderLayout order_layout(int64_t n_chunks, int64_t h, int32_t n_keys) {
+    OrderLayout w;
+    auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    w.scan_blocks = (n_chunks + kScanPerBlock - 1) / kScanPerBlock;
+    if (w.scan_blocks < 1) w.scan_blocks = 1;
+    size_t off = 0;
+    w.off_ord = off; off = align(off + sizeof(uint32_t) * (size_t)(n_chunks + 1));
+    w.off_sums = off; off = align(off + sizeof(uint32_t) * (size_t)w.scan_blocks);
+    w.off_keys = off; off = align(off + sizeof(int32_t) * (size_t)h);
+    w.off_vals = off; off = align(off + sizeof(int32_t) * (size_t)h);
+    w.off_sort = off; off = align(off + (size_t)layout(h > 0 ? h : 1, n_keys).total);
+    w.total = off + 256;
+    return w;
+}
+
+}  // namespace
+
+extern "C" int64_t trc_order_work_bytes(int64_t n_chunks, int64_t h, int32_t n_keys) {
+    if (n_chunks < 0 || h < 0 || n_keys < 1) return -1;
+    return (int64_t)order_layout(n_chunks, h, n_keys).total;
+}
+
+extern "C" int trc_order_hits(int64_t n_chunks, const uint32_t *d_chunk_off, const uint32_t *d_chunk_cnt,
+                              const TrcHitRecord *d_records, int64_t h, int32_t n_keys, int32_t *d_slot_surf,
+                              int32_t *d_slot_rec, int64_t *d_offsets, void *d_work, void *stream) {
+    if (n_chunks < 0 || h < 0 || n_keys < 1 || !d_offsets || !d_work ||
+        (h > 0 && (!d_chunk_off || !d_chunk_cnt || !d_records || !d_slot_surf || !d_slot_rec || n_chunks < 1)))
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_order_hits: bad argument%s");
+    if (h >= 0x7fffffffLL) return fail(TRC_ERR_CAPACITY, "trc_order_hits: more than 2^31-1 hits%s");
+    cudaStream_t st = (cudaStream_t)stream;
+    OrderLayout w = order_layout(n_chunks, h, n_keys);
+    char *wk = (char *)d_work;
+    uint32_t *ord = (uint32_t *)(wk + w.off_ord);
+    uint32_t *sums = (uint32_t *)(wk + w.off_sums);
+    int32_t *keys = (int32_t *)(wk + w.off_keys);
+    int32_t *vals = (int32_t *)(wk + w.off_vals);
+    int64_t *count = (int64_t *)(wk + w.total - 256);
+    if (h == 0) {
+        TRC_CUDA(cudaMemsetAsync(d_offsets, 0, sizeof(int64_t) * (size_t)(n_keys + 1), st));
+        return TRC_OK;
+    }
+    copy_u32_kernel<<<(unsigned)((n_chunks + kThreads - 1) / kThreads), kThreads, 0, st>>>(d_chunk_cnt, ord, n_chunks);
+    scan_reduce_kernel<<<(unsigned)w.scan_blocks, kThreads, 0, st>>>(ord, n_chunks, sums);
+    scan_sums_kernel<<<1, kThreads, 0, st>>>(sums, w.scan_blocks, nullptr);
+    scan_apply_kernel<<<(unsigned)w.scan_blocks, kThreads, 0, st>>>(ord, n_chunks, sums);
+    int64_t warps_per_block = kThreads / 32;
+    hit_pairs_kernel<<<(unsigned)((n_chunks + warps_per_block - 1) / warps_per_block), kThreads, 0, st>>>(
+        n_chunks, d_chunk_off, d_chunk_cnt, ord, d_records, h, keys, vals);
+    int rc = check_launch("order_hits", 5);
+    if (rc != TRC_OK) return rc;
+    rc = trc_sort_pairs(h, n_keys, keys, vals, d_slot_surf, d_slot_rec, count, wk + w.off_sort, stream);
+    if (rc != TRC_OK) return rc;
+    return trc_segment_offsets_dyn(count, h, n_keys, d_slot_surf, d_offsets, stream);
+}

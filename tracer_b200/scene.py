@@ -301,6 +301,7 @@ class CompiledScene(object):
         self.tables = np.concatenate(tables) if tables else np.zeros(0)
         self.needs_wavelengths = any(o['needs_wavelengths'] for o in self.optics)
         self.has_accountants = any(o['accountants'] for o in self.optics)
+        self.accountant_sources = set(src for o in self.optics for (_, _, src) in o['accountants'])
         self.unbounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) != 0)[0].astype(np.int32)
         self.bounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) == 0)[0].astype(np.int32)
         self.leaf_size = leaf_size

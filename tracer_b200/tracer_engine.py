@@ -85,6 +85,7 @@ class TracerEngine(object):
         self.leaf_size = leaf_size
         self._scene = None
         self._frames_key = None
+        self._hit_frac = {}       # bounce -> hit fraction of the previous trace (sizes the hit list)
         self.stats = {}
 
     # ------------------------------------------------------------ scene
@@ -97,6 +98,7 @@ class TracerEngine(object):
             if self._scene is not None:
                 self._scene.close()
             self._scene = CompiledScene(self._asm, leaf_size=self.leaf_size)
+            self._hit_frac = {}
             self._frames_key = key
         return self._scene
 
@@ -176,28 +178,44 @@ class TracerEngine(object):
     # ------------------------------------------------------------ bounce
     def _bounce(self, scene, cur, bounce, min_energy, use_bvh):
         """One iteration of the reference loop body (tracer_engine.py:193-274).
-        Returns (record tensors dict, n_survivors, H)."""
+        Returns (record tensors dict, n_survivors, H).
+
+        Launch sequence: trc_trace_hits (nearest hit fused with the emission of
+        64-byte hit records) -> trc_order_hits (surface-major / ray-minor slots)
+        -> trc_optics -> trc_segment_sums [-> cull sort + gathers].  Two host
+        syncs: the hit count (sizes the child bundle) and the cull count."""
         import torch
         lib = L.load()
         dev = self.device
         st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         n, S = cur.n, scene.num_surfaces
         i32, i64, f64 = torch.int32, torch.int64, torch.float64
-        hit = torch.empty(n, dtype=i32, device=dev)
-        L.check(lib.trc_nearest_hit(scene.handle, n, L.dptr(cur.V), L.dptr(cur.D), cur.V.stride(0),
-                                    1 if use_bvh else 0, L.dptr(hit), st))
-        slot_surf = torch.empty(n, dtype=i32, device=dev)
-        slot_parent = torch.empty(n, dtype=i32, device=dev)
-        count = torch.zeros(1, dtype=i64, device=dev)
-        work = torch.empty(int(lib.trc_sort_work_bytes(n, S)), dtype=torch.uint8, device=dev)
-        L.check(lib.trc_sort_pairs(n, S, L.dptr(hit), None, L.dptr(slot_surf), L.dptr(slot_parent),
-                                   L.dptr(count), L.dptr(work), st))
-        seg = torch.empty(S + 1, dtype=i64, device=dev)
-        L.check(lib.trc_segment_offsets_dyn(L.dptr(count), n, S, L.dptr(slot_surf), L.dptr(seg), st))
-        H = int(count.item())
-        del hit, work
+        n_chunks = (n + L.HIT_CHUNK - 1) // L.HIT_CHUNK
+        chunk_off = torch.empty(n_chunks, dtype=i32, device=dev)
+        chunk_cnt = torch.empty(n_chunks, dtype=i32, device=dev)
+        counters = torch.zeros(2, dtype=i64, device=dev)          # [hits, culled]
+        # capacity of the hit list: the hit fraction seen at this bounce of the previous
+        # trace (+30 %), else every ray; an overflow re-runs the kernel with the exact size
+        frac = self._hit_frac.get(bounce)
+        cap = n if frac is None or n <= (1 << 20) else min(n, int(1.3 * frac * n) + 65536)
+        while True:
+            records = torch.empty((cap, L.HIT_RECORD_BYTES // 8), dtype=f64, device=dev)
+            L.check(lib.trc_trace_hits(scene.handle, n, L.dptr(cur.V), L.dptr(cur.D), L.dptr(cur.E),
+                                       cur.V.stride(0), 1 if use_bvh else 0, None, L.dptr(records), cap,
+                                       L.dptr(chunk_off), L.dptr(chunk_cnt), L.dptr(counters), st))
+            H = int(counters[0].item())
+            if H <= cap:
+                break
+            cap = H
+        self._hit_frac[bounce] = H / float(n) if n else 0.
         if H == 0:
             return None, 0, 0
+        slot_surf = torch.empty(H, dtype=i32, device=dev)
+        slot_rec = torch.empty(H, dtype=i32, device=dev)
+        seg = torch.empty(S + 1, dtype=i64, device=dev)
+        work = torch.empty(int(lib.trc_order_work_bytes(n_chunks, H, S)), dtype=torch.uint8, device=dev)
+        L.check(lib.trc_order_hits(n_chunks, L.dptr(chunk_off), L.dptr(chunk_cnt), L.dptr(records), H, S,
+                                   L.dptr(slot_surf), L.dptr(slot_rec), L.dptr(seg), L.dptr(work), st))
         need_seg_host = scene.has_accountants or self.rng == 'numpy'
         seg_host = seg.cpu().numpy() if need_seg_host else None
 
@@ -206,41 +224,50 @@ class TracerEngine(object):
         oE = torch.empty(H, dtype=f64, device=dev)
         oP = torch.empty(H, dtype=i64, device=dev)
         cull = torch.empty(H, dtype=i32, device=dev)
-        want = set(src for o in scene.optics for (_, _, src) in o['accountants'])
+        want = scene.accountant_sources
         absorbed = torch.empty(H, dtype=f64, device=dev)   # always: feeds the per-surface totals
         normals = torch.empty((3, H), dtype=f64, device=dev) if 'normals' in want else None
+        e_in = torch.empty(H, dtype=f64, device=dev) if 'e_in' in want else None
+        dirs_in = torch.empty((3, H), dtype=f64, device=dev) if 'dirs_in' in want else None
+        if 'wavelengths' in want and cur.W is None:
+            raise ValueError("Spectral accountant needs a 'wavelengths' bundle property")
+        oW = torch.empty(H, dtype=f64, device=dev) if cur.W is not None else None
         draws = self._numpy_draws(scene, seg_host, H) if self.rng == 'numpy' else None
 
         a = L.OpticsArgs()
         a.h = H
-        a.d_slot_parent, a.d_slot_surf = slot_parent.data_ptr(), slot_surf.data_ptr()
-        a.d_vertices, a.d_directions, a.d_energy = cur.V.data_ptr(), cur.D.data_ptr(), cur.E.data_ptr()
+        a.d_records, a.d_slot_rec = records.data_ptr(), slot_rec.data_ptr()
         a.d_wavelengths = cur.W.data_ptr() if cur.W is not None else None
-        a.ld_in = cur.V.stride(0)
         a.d_out_vertices, a.d_out_directions = oV.data_ptr(), oD.data_ptr()
         a.d_out_energy, a.d_out_parents, a.ld_out = oE.data_ptr(), oP.data_ptr(), H
         for j in range(3):
             a.d_draws[j] = draws[j].data_ptr() if draws is not None else None
         a.seed, a.bounce, a.min_energy = self.seed, bounce, float(min_energy)
-        a.d_absorbed = absorbed.data_ptr() if absorbed is not None else None
+        a.d_absorbed = absorbed.data_ptr()
         a.d_normals = normals.data_ptr() if normals is not None else None
+        a.d_e_in = e_in.data_ptr() if e_in is not None else None
+        a.d_dirs_in = dirs_in.data_ptr() if dirs_in is not None else None
+        a.d_out_wavelengths = oW.data_ptr() if oW is not None else None
         a.d_cull = cull.data_ptr()
+        a.d_n_cull = counters[1:].data_ptr()
         L.check(lib.trc_optics(scene.handle, C.byref(a), st))
 
         # per-surface absorbed energy and hit counts, kept on device: the payload of
         # the multi-GPU all-reduce (tracer_engine_mp.py) and a tally for 'fast' optics
         L.check(lib.trc_segment_sums(H, L.dptr(slot_surf), L.dptr(absorbed), L.dptr(self.absorbed_per_surface), st))
         self.hits_per_surface += seg[1:] - seg[:-1]
-        oW = cur.W.index_select(0, slot_parent[:H].long()) if cur.W is not None else None
         if scene.has_accountants:
-            self._account(scene, cur, seg_host, slot_parent, oV, oE, absorbed, normals)
+            self._account(scene, seg_host, dict(hits=oV, absorbed=absorbed, e_out=oE, normals=normals, e_in=e_in,
+                                                dirs_in=dirs_in, wavelengths=oW))
 
-        n_cull = int(cull.sum().item())
+        n_cull = int(counters[1].item())
+        del records, work
         rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
         if n_cull and n_cull < H:
             # survivors first, weak rays at the back (tracer_engine.py:242-245, 268-274)
             k2 = torch.empty(H, dtype=i32, device=dev)
             perm = torch.empty(H, dtype=i32, device=dev)
+            count = torch.zeros(1, dtype=i64, device=dev)
             work = torch.empty(int(lib.trc_sort_work_bytes(H, 2)), dtype=torch.uint8, device=dev)
             L.check(lib.trc_sort_pairs(H, 2, L.dptr(cull), None, L.dptr(k2), L.dptr(perm), L.dptr(count),
                                        L.dptr(work), st))
@@ -254,37 +281,20 @@ class TracerEngine(object):
         rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
         return rec, H - n_cull, H
 
-    def _account(self, scene, cur, seg, slot_parent, oV, oE, absorbed, normals):
+    @staticmethod
+    def _account(scene, seg, src):
         """What Accountant.count() stores, one chunk per surface per bounce
-        (optics_callables.py:1597-1790), kept in HBM until read."""
+        (optics_callables.py:1597-1790), kept in HBM until read.  ``src`` maps a
+        source name to the slot-ordered tensor the optics kernel filled."""
         for s, orec in enumerate(scene.optics):
             if not orec['accountants']:
                 continue
             a, b = int(seg[s]), int(seg[s + 1])
             if b == a:
                 continue
-            par = None
-            for acc, field, src in orec['accountants']:
-                if src == 'hits':
-                    chunk = oV[:, a:b].clone()
-                elif src == 'absorbed':
-                    chunk = absorbed[a:b].clone()
-                elif src == 'e_out':
-                    chunk = oE[a:b].clone()
-                elif src == 'normals':
-                    chunk = normals[:, a:b].clone()
-                else:
-                    if par is None:
-                        par = slot_parent[a:b].long()
-                    if src == 'e_in':
-                        chunk = cur.E.index_select(0, par)
-                    elif src == 'dirs_in':
-                        chunk = cur.D.index_select(1, par)
-                    elif src == 'wavelengths':
-                        if cur.W is None:
-                            raise ValueError("Spectral accountant needs a 'wavelengths' bundle property")
-                        chunk = cur.W.index_select(0, par)
-                getattr(acc, field).append(_LazyRows(chunk))
+            for acc, field, name in orec['accountants']:
+                t = src[name]
+                getattr(acc, field).append(_LazyRows(t[..., a:b].clone()))
 
     @staticmethod
     def _as_bundle(rec, n=None):
@@ -322,7 +332,7 @@ class TracerEngine(object):
 
         with torch.cuda.device(self.device):
             cur = self._to_device(bundle)
-            e0 = cur.E.sum() if cur.n else None
+            source_E = cur.E
             self.absorbed_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.float64, device=self.device)
             self.hits_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.int64, device=self.device)
             ray_bounces = 0
@@ -355,6 +365,6 @@ class TracerEngine(object):
                               use_bvh=use_bvh)
             if cur.n != 0:
                 logging.warning(f'{cur.n} rays left at the end of the simulation')
-                frac = float((cur.E.sum() / e0).item()) * 100.
+                frac = float((cur.E.sum() / source_E.sum()).item()) * 100.
                 logging.warning(f'Remaining energy in last bundle: {frac}%')
             return cur.V.contiguous().cpu().numpy(), cur.D.contiguous().cpu().numpy()
