@@ -10,7 +10,8 @@ scaling: every GPU traces its own ``--rays`` bundle (default 1e8).
   e2e     : same step through the public API with a HOST bundle in pinned
             memory (H2D inside the timed region) and the flux map read back
   roofline: dominant kernel (nearest-hit BVH walk over the source bundle) timed
-            alone with CUDA events; algorithmic bytes = 52 B/ray
+            by CUDA events around its launch inside the timed region;
+            algorithmic bytes = 48 B/ray + 72 B/hit
   cpu_baseline / --impl reference: the NumPy oracle port of the reference
             engine on the host cores, bounded sample of the same workload
 """
@@ -39,7 +40,9 @@ METRIC = "ray-bounces/sec, NSTTF field 1e8 rays"
 UNIT = "ray-bounces/s"
 REPS = 3
 FLUX_RES = 50
-ALGO_BYTES_PER_RAY_HIT_KERNEL = 52      # 48 B read (vertex + direction) + 4 B hit index written
+ALGO_BYTES_PER_RAY_HIT_KERNEL = 48      # vertex + direction read once per ray
+ALGO_BYTES_PER_HIT_HIT_KERNEL = 72      # per hit: 8 B energy read + 64 B hit record written
+TRAFFIC_BYTES_PER_RAY_NCU = 52.9        # (dram read + write) / rays of the ncu --set full capture in profiles/
 
 
 class ClockSampler(object):
@@ -160,7 +163,7 @@ def main():
     ap.add_argument("--rays", type=float, default=1e8, help="rays per GPU per step")
     ap.add_argument("--cpu-rays", type=float, default=2e5, help="rays per host process for the CPU baseline")
     ap.add_argument("--accel", default="bvh", choices=["bvh", "brute"])
-    ap.add_argument("--leaf-size", type=int, default=2)
+    ap.add_argument("--leaf-size", type=int, default=1)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

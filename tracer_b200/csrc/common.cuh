@@ -68,4 +68,5 @@ struct TrcScene {
     int32_t n_unbounded = 0;
     int32_t *d_cand = nullptr;         // leaf surfaces followed by unbounded surfaces (the walk's candidate list)
     int num_sms = 148;
+    bool flat_only = false;            // every surface is of the flat family (kinds <= TRC_G_TRIANGLE)
 };

@@ -121,14 +121,31 @@ nearest_hit_brute_kernel(const TrcSurfaceRec *__restrict__ surfs, int n_surf, in
 }
 
 // ------------------------------------------------------------------ tree walk
-constexpr int kWalkWarps = 8;                 // warps per CTA
+#ifndef TRC_WALK_MIN_CTAS
+#define TRC_WALK_MIN_CTAS 2
+#endif
+#ifndef TRC_WALK_MIN_CTAS_FLAT
+#define TRC_WALK_MIN_CTAS_FLAT 2
+#endif
+#ifndef TRC_WALK_WARPS
+#define TRC_WALK_WARPS 8
+#endif
+constexpr int kWalkWarps = TRC_WALK_WARPS;    // warps per CTA
 constexpr int kChunk = 256;                   // consecutive rays owned by a warp at a time (slot fits 8 bits)
 constexpr int kListCap = 64;                  // active list: filled while < 32, by <= 32 at a time
 constexpr int kQueueCap = 32 + 32 * 2;        // leftover + one visit (two leaf children) of every lane
 constexpr int kStack = 64;
-constexpr int kRing = 3;                       // ray batches in flight per warp (cp.async), 1.5 KB each
+constexpr int kWalkSteps = 4;                  // visits per lane between two warp-level collections
+constexpr unsigned kNoEntry = 0xffffffffu;    // (first < 2^22 - 1, so no real entry is all ones)
+#ifndef TRC_WALK_RING
+#define TRC_WALK_RING 3
+#endif
+constexpr int kRing = TRC_WALK_RING;                       // ray batches in flight per warp (cp.async), 1.5 KB each
 constexpr int kListFields = 10;               // A[3], Bl[3], Bh[3], slot
-constexpr int kSmemPairs = 512;               // top of the tree (breadth-first) cached per CTA: 16 KB
+#ifndef TRC_WALK_SMEM_PAIRS
+#define TRC_WALK_SMEM_PAIRS 512
+#endif
+constexpr int kSmemPairs = TRC_WALK_SMEM_PAIRS;               // top of the tree (breadth-first) cached per CTA: 16 KB
 // queue entry = slot << 24 | (count - 1) << 22 | first candidate-list index: one entry per leaf
 constexpr unsigned kCandMask = 0x003fffffu;
 
@@ -235,8 +252,9 @@ __device__ __forceinline__ float best_as_float(unsigned long long bits) {
 
 // Stage C: test queued (slot, leaf) candidates in float64, 32 at a time, and
 // fold them into the per-slot best (t, surface).  `all` drains the queue.
-__device__ __noinline__ int flush_queue(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
-                                        int qn, bool all) {
+template <bool kFlatOnly>
+__device__ __forceinline__ int flush_queue_body(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
+                                                int qn, bool all) {
     __syncwarp();
     if (p.debug & 1) qn = 0;
     while (qn >= 32 || (all && qn > 0)) {
@@ -256,7 +274,14 @@ __device__ __noinline__ int flush_queue(WalkWarpShared &sh, const WalkParams &p,
             V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
             for (int k = 0; k < cnt; ++k) {
                 int s = __ldg(&p.cand[first + k]);
-                double tk = intersect(&p.surfs[s], v, d);
+                const TrcSurfaceRec *sr = &p.surfs[s];
+                double tk;
+                if (kFlatOnly) {              // scene of flat-family surfaces only: no quadric code, few registers
+                    tk = isect_flat(sr, sr->gkind, v, d);
+                    if (tk == 0.0) tk = TRC_INF;
+                } else {
+                    tk = intersect(sr, v, d);
+                }
                 if (tk < t || (tk == t && s < surf && tk != TRC_INF)) { t = tk; surf = s; }
             }
         }
@@ -276,14 +301,61 @@ __device__ __noinline__ int flush_queue(WalkWarpShared &sh, const WalkParams &p,
     return qn;
 }
 
+// Generic scenes: the float64 tests of all 24 geometry kinds need ~75 registers; kept out of
+// line so that they are not live together with the walk state.  Flat-only scenes (heliostat
+// fields, triangle meshes) inline the short flat-family test instead and run at higher occupancy.
+__device__ __noinline__ int flush_queue_generic(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
+                                                int qn, bool all) {
+    return flush_queue_body<false>(sh, p, chunk_base, lane, qn, all);
+}
+template <bool kFlatOnly>
+__device__ __forceinline__ int flush_queue(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
+                                           int qn, bool all) {
+    if (kFlatOnly) return flush_queue_body<true>(sh, p, chunk_base, lane, qn, all);
+    return flush_queue_generic(sh, p, chunk_base, lane, qn, all);
+}
+
+// Append one chunk's hits (ascending ray index) to the hit list of trc_trace_hits.
+__device__ __noinline__ void emit_chunk_hits(WalkWarpShared &sh, const WalkParams &p, int64_t c_cur,
+                                             int64_t chunk_base, int lane) {
+    const unsigned full = 0xffffffffu;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    int h_c = 0;
+#pragma unroll
+    for (int k = 0; k < kChunk / 32; ++k)
+        h_c += __popc(__ballot_sync(full, sh.best_t[lane + 32 * k] != TRC_INF_BITS));
+    unsigned long long base = 0;
+    if (lane == 0) {
+        base = atomicAdd(p.sink.total, (unsigned long long)h_c);
+        p.sink.chunk_off[c_cur] = (uint32_t)base;
+        p.sink.chunk_cnt[c_cur] = (uint32_t)h_c;
+    }
+    base = __shfl_sync(full, base, 0);
+    if (h_c == 0) return;
+    int run = 0;
+    for (int k = 0; k < kChunk / 32; ++k) {
+        int i = lane + 32 * k;
+        bool hit = sh.best_t[i] != TRC_INF_BITS;
+        unsigned m = __ballot_sync(full, hit);
+        unsigned long long pos = base + run + __popc(m & lt_mask);
+        run += __popc(m);
+        if (hit && (int64_t)pos < p.sink.capacity) {
+            int64_t ray = chunk_base + i;
+            V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
+            V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
+            store_record(p.sink.records + pos, v, d, p.sink.energy[ray], (int)ray, sh.best_s[i]);
+        }
+    }
+}
+
 __device__ __forceinline__ void cp_async8(void *smem_dst, const void *gmem_src) {
     unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
 }
 
 // kAllShared: the whole tree fits the shared-memory cache (no global-memory path in the walk)
-template <bool kAllShared>
-__global__ void __launch_bounds__(kWalkWarps * 32, 2)
+template <bool kAllShared, bool kFlatOnly>
+__global__ void __launch_bounds__(kWalkWarps * 32, kFlatOnly ? TRC_WALK_MIN_CTAS_FLAT : TRC_WALK_MIN_CTAS)
 nearest_hit_walk_kernel(WalkParams p) {
     extern __shared__ __align__(16) unsigned char walk_smem[];
     WalkShared &S = *reinterpret_cast<WalkShared *>(walk_smem);
@@ -356,9 +428,9 @@ nearest_hit_walk_kernel(WalkParams p) {
         int next = 0;          // rays of the chunk already through stage A   (warp-uniform)
         int list_n = 0;        // active-list fill                              (warp-uniform)
         int qn = 0;            // candidate-queue fill                          (warp-uniform)
-        bool active = false;   // this lane is walking a ray
         RayF r;
-        int cur = 0, sp = 0;   // cur = pair index
+        int cur = -1, sp = 0;  // cur = pair index this lane visits next, -1 = the lane is idle
+        unsigned pend0 = kNoEntry, pend1 = kNoEntry;   // leaves reached but not yet queued
         unsigned tag = 0;      // slot << 24
         float tbest = TRC_FINF;
 
@@ -387,7 +459,7 @@ nearest_hit_walk_kernel(WalkParams p) {
                         if (surv) sh.queue[qn + __popc(m & lt_mask)] =
                             ((unsigned)j << 24) | ((unsigned)(root_count - 1) << 22) | TRC_META_INDEX(p.root_meta);
                         qn += __popc(m);
-                        if (qn >= 32) qn = flush_queue(sh, p, chunk_base, lane, qn, false);
+                        if (qn >= 32) qn = flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, false);
                     }
                 } else {
                     if (surv) {
@@ -406,16 +478,16 @@ nearest_hit_walk_kernel(WalkParams p) {
                     for (int k = 0; k < p.n_unbounded; ++k) {
                         if (valid) sh.queue[qn + __popc(mv & lt_mask)] = ((unsigned)j << 24) | (unsigned)(p.unbounded_first + k);
                         qn += __popc(mv);
-                        if (qn >= 32) qn = flush_queue(sh, p, chunk_base, lane, qn, false);
+                        if (qn >= 32) qn = flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, false);
                     }
                 }
                 __syncwarp();
             }
             // ---------------- refill idle lanes from the list
             {
-                unsigned idle = __ballot_sync(full, !active);
+                unsigned idle = __ballot_sync(full, cur < 0);
                 int rk = __popc(idle & lt_mask);
-                if (!active && rk < list_n) {
+                if (cur < 0 && rk < list_n) {
                     int e = list_n - 1 - rk;
 #pragma unroll
                     for (int k = 0; k < 3; ++k) {
@@ -423,97 +495,74 @@ nearest_hit_walk_kernel(WalkParams p) {
                     }
                     int slot = __float_as_int(sh.list[9][e]);
                     tag = (unsigned)slot << 24;
-                    cur = 0; sp = 0; active = true;
+                    cur = 0; sp = 0;
                     tbest = best_as_float(sh.best_t[slot]);
                 }
                 list_n -= min(__popc(idle), list_n);
                 __syncwarp();
             }
-            if (__ballot_sync(full, active) == 0u) break;   // list empty and chunk exhausted
+            if (__ballot_sync(full, cur >= 0) == 0u) break;   // list empty and chunk exhausted
 
-            // ---------------- stage B: walk until enough lanes are idle to be worth a refill
+            // ---------------- stage B: walk.  kWalkSteps visits per lane without any warp-level
+            // coordination (a lane that reaches a leaf parks the leaf in `pend` and waits), then
+            // the warp collects the parked leaves into the candidate queue, flushes it when 32 are
+            // waiting, and leaves the loop when enough lanes are idle to be worth a refill.
 #pragma unroll 1
             for (;;) {
-                bool l0 = false, l1 = false;
-                unsigned e0 = 0, e1 = 0;       // meta words of the children (leaf: count | first)
-                if (active) {
-                    uint4 a, b;
-                    if (kAllShared || cur < kSmemPairs) { a = S.pair_a[cur]; b = S.pair_b[cur]; }
-                    else { a = __ldg(p.pair_a + cur); b = __ldg(p.pair_b + cur); }
-                    float t0 = slab16(q_lo(a.x), q_hi(a.x), q_lo(a.y), q_hi(a.y), q_lo(a.z), q_hi(a.z), r, tbest);
-                    float t1 = slab16(q_lo(a.w), q_hi(a.w), q_lo(b.x), q_hi(b.x), q_lo(b.y), q_hi(b.y), r, tbest);
-                    unsigned c0 = TRC_META_COUNT(b.z), c1 = TRC_META_COUNT(b.w);
-                    bool h0 = t0 < TRC_FINF && c0 != 7u, h1 = t1 < TRC_FINF && c1 != 7u;
-                    l0 = h0 && c0 != 0u; l1 = h1 && c1 != 0u;
-                    e0 = b.z; e1 = b.w;
-                    bool i0 = h0 && c0 == 0u, i1 = h1 && c1 == 0u;
-                    int f0 = (int)b.z, f1 = (int)b.w;        // inner: meta == pair index
-                    if (i0 && i1) {
-                        bool swap = t1 < t0;
-                        cur = swap ? f1 : f0;
-                        stack[sp++] = swap ? f0 : f1;
-                    } else if (i0 || i1) {
-                        cur = i0 ? f0 : f1;
-                    } else if (sp > 0) {
-                        cur = stack[--sp];
-                    } else {
-                        active = false;
+#pragma unroll 1
+                for (int it = 0; it < kWalkSteps; ++it) {
+                    if (cur >= 0 && pend0 == kNoEntry) {
+                        uint4 a, b;
+                        if (kAllShared || cur < kSmemPairs) { a = S.pair_a[cur]; b = S.pair_b[cur]; }
+                        else { a = __ldg(p.pair_a + cur); b = __ldg(p.pair_b + cur); }
+                        float t0 = slab16(q_lo(a.x), q_hi(a.x), q_lo(a.y), q_hi(a.y), q_lo(a.z), q_hi(a.z), r, tbest);
+                        float t1 = slab16(q_lo(a.w), q_hi(a.w), q_lo(b.x), q_hi(b.x), q_lo(b.y), q_hi(b.y), r, tbest);
+                        unsigned c0 = TRC_META_COUNT(b.z), c1 = TRC_META_COUNT(b.w);
+                        bool h0 = t0 < TRC_FINF && c0 != 7u, h1 = t1 < TRC_FINF && c1 != 7u;
+                        bool i0 = h0 && c0 == 0u, i1 = h1 && c1 == 0u;
+                        // meta (count << 28 | first) -> entry (slot << 24 | (count - 1) << 22 | first)
+                        if (h1 && !i1) pend0 = tag | ((c1 - 1u) << 22) | TRC_META_INDEX(b.w);
+                        if (h0 && !i0) { pend1 = pend0; pend0 = tag | ((c0 - 1u) << 22) | TRC_META_INDEX(b.z); }
+                        int f0 = (int)b.z, f1 = (int)b.w;        // inner: meta == pair index
+                        if (i0 && i1) {
+                            bool swap = t1 < t0;
+                            cur = swap ? f1 : f0;
+                            stack[sp++] = swap ? f0 : f1;
+                        } else if (i0 || i1) {
+                            cur = i0 ? f0 : f1;
+                        } else if (sp > 0) {
+                            cur = stack[--sp];
+                        } else {
+                            cur = -1;
+                        }
                     }
                 }
-                // leaves reached in this step -> candidate queue (positions from ballots, no atomics)
-                unsigned m0 = __ballot_sync(full, l0), m1 = __ballot_sync(full, l1);
-                if (m0 | m1) {
-                    // meta (count << 28 | first) -> entry (slot << 24 | (count - 1) << 22 | first)
-                    if (l0) sh.queue[qn + __popc(m0 & lt_mask)] = tag | (((e0 >> 28) - 1u) << 22) | TRC_META_INDEX(e0);
+                // parked leaves -> candidate queue (positions from ballots, no atomics)
+                unsigned m0 = __ballot_sync(full, pend0 != kNoEntry);
+                if (m0) {
+                    unsigned m1 = __ballot_sync(full, pend1 != kNoEntry);
+                    if (pend0 != kNoEntry) sh.queue[qn + __popc(m0 & lt_mask)] = pend0;
                     qn += __popc(m0);
-                    if (l1) sh.queue[qn + __popc(m1 & lt_mask)] = tag | (((e1 >> 28) - 1u) << 22) | TRC_META_INDEX(e1);
+                    if (pend1 != kNoEntry) sh.queue[qn + __popc(m1 & lt_mask)] = pend1;
                     qn += __popc(m1);
+                    pend0 = pend1 = kNoEntry;
                     if (qn >= 32) {
-                        qn = flush_queue(sh, p, chunk_base, lane, qn, false);
-                        if (active) tbest = best_as_float(sh.best_t[tag >> 24]);
+                        qn = flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, false);
+                        if (cur >= 0) tbest = best_as_float(sh.best_t[tag >> 24]);
                     }
                 }
-                int n_active = __popc(__ballot_sync(full, active));
+                int n_active = __popc(__ballot_sync(full, cur >= 0));
                 if (n_active == 0) break;
                 if (n_active <= p.refill_at && (list_n > 0 || next < chunk_n)) break;
             }
         }
-        flush_queue(sh, p, chunk_base, lane, qn, true);
+        flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, true);
         __syncwarp();
         if (p.sink.hit_surf) {
             for (int i = lane; i < chunk_n; i += 32)
                 p.sink.hit_surf[chunk_base + i] = sh.best_t[i] == TRC_INF_BITS ? -1 : sh.best_s[i];
         }
-        if (p.sink.records) {
-            // append this chunk's hits (ascending ray index) to the hit list
-            int h_c = 0;
-#pragma unroll
-            for (int k = 0; k < kChunk / 32; ++k)
-                h_c += __popc(__ballot_sync(full, sh.best_t[lane + 32 * k] != TRC_INF_BITS));
-            unsigned long long base = 0;
-            if (lane == 0) {
-                base = atomicAdd(p.sink.total, (unsigned long long)h_c);
-                p.sink.chunk_off[c_cur] = (uint32_t)base;
-                p.sink.chunk_cnt[c_cur] = (uint32_t)h_c;
-            }
-            base = __shfl_sync(full, base, 0);
-            if (h_c) {
-                int run = 0;
-                for (int k = 0; k < kChunk / 32; ++k) {
-                    int i = lane + 32 * k;
-                    bool hit = sh.best_t[i] != TRC_INF_BITS;
-                    unsigned m = __ballot_sync(full, hit);
-                    unsigned long long pos = base + run + __popc(m & lt_mask);
-                    run += __popc(m);
-                    if (hit && (int64_t)pos < p.sink.capacity) {
-                        int64_t ray = chunk_base + i;
-                        V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
-                        V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
-                        store_record(p.sink.records + pos, v, d, p.sink.energy[ray], (int)ray, sh.best_s[i]);
-                    }
-                }
-            }
-        }
+        if (p.sink.records) emit_chunk_hits(sh, p, c_cur, chunk_base, lane);
         __syncwarp();
     }
     asm volatile("cp.async.wait_all;" ::: "memory");
@@ -534,19 +583,23 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     }
     if ((sc->n_nodes == 0 && sc->n_unbounded == 0) || !sc->d_chunk_counter || !sc->d_cand)
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: use_bvh set but no BVH uploaded%s");
-    static int occ = 0;
+    typedef void (*WalkKernel)(WalkParams);
+    static const WalkKernel kernels[4] = {nearest_hit_walk_kernel<false, false>, nearest_hit_walk_kernel<true, false>,
+                                          nearest_hit_walk_kernel<false, true>, nearest_hit_walk_kernel<true, true>};
+    static int occ[4] = {0, 0, 0, 0};
     static int g_refill_at = 24;
-    if (occ == 0) {
+    if (occ[0] == 0) {
         const char *env = getenv("TRC_WALK_REFILL_AT");      // tuning knob (0..31)
         if (env) { int v = atoi(env); if (v >= 0 && v < 32) g_refill_at = v; }
-        TRC_CUDA(cudaFuncSetAttribute(nearest_hit_walk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(WalkShared)));
-        TRC_CUDA(cudaFuncSetAttribute(nearest_hit_walk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(WalkShared)));
-        TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, nearest_hit_walk_kernel<false>, kWalkWarps * 32,
-                                                               sizeof(WalkShared)));
-        if (occ < 1) occ = 1;
+        for (int k = 0; k < 4; ++k) {
+            TRC_CUDA(cudaFuncSetAttribute(kernels[k], cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)sizeof(WalkShared)));
+            TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[k], kernels[k], kWalkWarps * 32,
+                                                                   sizeof(WalkShared)));
+            if (occ[k] < 1) occ[k] = 1;
+        }
     }
+    const int variant = (sc->n_pairs <= kSmemPairs ? 1 : 0) | (sc->flat_only ? 2 : 0);
     WalkParams p;
     p.surfs = sc->d_surfaces;
     p.pair_a = reinterpret_cast<const uint4 *>(sc->d_pair_a);
@@ -564,13 +617,10 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     p.chunk_counter = sc->d_chunk_counter;
     int64_t n_chunks = (n + kChunk - 1) / kChunk;
     int64_t blocks = (n_chunks + kWalkWarps - 1) / kWalkWarps;
-    int64_t resident = (int64_t)sc->num_sms * occ;
+    int64_t resident = (int64_t)sc->num_sms * occ[variant];
     if (blocks > resident) blocks = resident;
     TRC_CUDA(cudaMemsetAsync(sc->d_chunk_counter, 0, sizeof(unsigned long long), st));
-    if (sc->n_pairs <= kSmemPairs)
-        nearest_hit_walk_kernel<true><<<(unsigned)blocks, kWalkWarps * 32, sizeof(WalkShared), st>>>(p);
-    else
-        nearest_hit_walk_kernel<false><<<(unsigned)blocks, kWalkWarps * 32, sizeof(WalkShared), st>>>(p);
+    kernels[variant]<<<(unsigned)blocks, kWalkWarps * 32, sizeof(WalkShared), st>>>(p);
     return check_launch("nearest_hit_walk");
 }
 

@@ -48,6 +48,9 @@ extern "C" int trc_scene_create(const TrcSurfaceRec *surfaces, int32_t n_surface
     TrcScene *sc = new (std::nothrow) TrcScene();
     if (!sc) return fail(TRC_ERR_CAPACITY, "trc_scene_create: out of host memory%s");
     sc->n_surfaces = n_surfaces;
+    sc->flat_only = true;
+    for (int32_t i = 0; i < n_surfaces; ++i)
+        if (surfaces[i].gkind > TRC_G_TRIANGLE) sc->flat_only = false;
     cudaError_t e = cudaMalloc(&sc->d_surfaces, sizeof(TrcSurfaceRec) * (size_t)n_surfaces);
     if (e == cudaSuccess)
         e = cudaMemcpy(sc->d_surfaces, surfaces, sizeof(TrcSurfaceRec) * (size_t)n_surfaces, cudaMemcpyHostToDevice);

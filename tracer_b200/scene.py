@@ -230,7 +230,7 @@ def _optics_record(opt):
 
 
 # -------------------------------------------------------------------- BVH
-def build_bvh(lo, hi, leaf_size=2):
+def build_bvh(lo, hi, leaf_size=1):
     """Binned-SAH binary BVH over n AABBs, built by the native host builder
     (csrc/bvh_build.cu; no GPU needed).  Children of an inner node are adjacent
     (``first``, ``first + 1``).  Returns (nodes structured array, leaf order int32)."""
@@ -252,7 +252,7 @@ def build_bvh(lo, hi, leaf_size=2):
 class CompiledScene(object):
     """Flat tables for one Assembly + the device handle."""
 
-    def __init__(self, assembly, leaf_size=2, upload=True):
+    def __init__(self, assembly, leaf_size=1, upload=True):
         self.assembly = assembly
         self.handle = None
         surfaces = assembly.get_surfaces()

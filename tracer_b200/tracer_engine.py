@@ -57,7 +57,7 @@ class _DevBundle(object):
 
 class TracerEngine(object):
     def __init__(self, parent_assembly, loglevel=logging.DEBUG, device=None, rng='philox', seed=0,
-                 device_accel='auto', leaf_size=2):
+                 device_accel='auto', leaf_size=1):
         """
         parent_assembly - the top-level Assembly (reference's or this package's).
         loglevel        - level of the per-bounce log lines (as the reference).
@@ -86,6 +86,7 @@ class TracerEngine(object):
         self._scene = None
         self._frames_key = None
         self._hit_frac = {}       # bounce -> hit fraction of the previous trace (sizes the hit list)
+        self.kernel_events = None  # set to a list to collect (bounce, n, H, start, end) CUDA events of trc_trace_hits
         self.stats = {}
 
     # ------------------------------------------------------------ scene
@@ -200,10 +201,17 @@ class TracerEngine(object):
         cap = n if frac is None or n <= (1 << 20) else min(n, int(1.3 * frac * n) + 65536)
         while True:
             records = torch.empty((cap, L.HIT_RECORD_BYTES // 8), dtype=f64, device=dev)
+            if self.kernel_events is not None:
+                ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                ev0.record()
             L.check(lib.trc_trace_hits(scene.handle, n, L.dptr(cur.V), L.dptr(cur.D), L.dptr(cur.E),
                                        cur.V.stride(0), 1 if use_bvh else 0, None, L.dptr(records), cap,
                                        L.dptr(chunk_off), L.dptr(chunk_cnt), L.dptr(counters), st))
+            if self.kernel_events is not None:
+                ev1.record()
             H = int(counters[0].item())
+            if self.kernel_events is not None:
+                self.kernel_events.append((bounce, n, H, ev0, ev1))
             if H <= cap:
                 break
             cap = H
