@@ -316,14 +316,24 @@ __device__ __forceinline__ int flush_queue(WalkWarpShared &sh, const WalkParams 
 }
 
 // Append one chunk's hits (ascending ray index) to the hit list of trc_trace_hits.
-__device__ __noinline__ void emit_chunk_hits(WalkWarpShared &sh, const WalkParams &p, int64_t c_cur,
+// The hit slots are first compacted into shared memory (the active list is empty at this
+// point and lends its storage), so the dependent global loads of the records run once for
+// 32 hits at a time instead of once per 32 slots.
+__device__ __forceinline__ void emit_chunk_hits(WalkWarpShared &sh, const WalkParams &p, int64_t c_cur,
                                              int64_t chunk_base, int lane) {
     const unsigned full = 0xffffffffu;
     const unsigned lt_mask = (1u << lane) - 1u;
+    unsigned char *slots = reinterpret_cast<unsigned char *>(&sh.list[0][0]);
+    static_assert(sizeof(float) * kListFields * kListCap >= kChunk, "slot list borrows the active list");
     int h_c = 0;
 #pragma unroll
-    for (int k = 0; k < kChunk / 32; ++k)
-        h_c += __popc(__ballot_sync(full, sh.best_t[lane + 32 * k] != TRC_INF_BITS));
+    for (int k = 0; k < kChunk / 32; ++k) {
+        int i = lane + 32 * k;
+        bool hit = sh.best_t[i] != TRC_INF_BITS;
+        unsigned m = __ballot_sync(full, hit);
+        if (hit) slots[h_c + __popc(m & lt_mask)] = (unsigned char)i;
+        h_c += __popc(m);
+    }
     unsigned long long base = 0;
     if (lane == 0) {
         base = atomicAdd(p.sink.total, (unsigned long long)h_c);
@@ -331,21 +341,17 @@ __device__ __noinline__ void emit_chunk_hits(WalkWarpShared &sh, const WalkParam
         p.sink.chunk_cnt[c_cur] = (uint32_t)h_c;
     }
     base = __shfl_sync(full, base, 0);
-    if (h_c == 0) return;
-    int run = 0;
-    for (int k = 0; k < kChunk / 32; ++k) {
-        int i = lane + 32 * k;
-        bool hit = sh.best_t[i] != TRC_INF_BITS;
-        unsigned m = __ballot_sync(full, hit);
-        unsigned long long pos = base + run + __popc(m & lt_mask);
-        run += __popc(m);
-        if (hit && (int64_t)pos < p.sink.capacity) {
-            int64_t ray = chunk_base + i;
-            V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
-            V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
-            store_record(p.sink.records + pos, v, d, p.sink.energy[ray], (int)ray, sh.best_s[i]);
-        }
+    __syncwarp();
+    for (int e = lane; e < h_c; e += 32) {
+        unsigned long long pos = base + e;
+        if ((int64_t)pos >= p.sink.capacity) break;       // overflow: the host re-runs with the exact size
+        int i = slots[e];
+        int64_t ray = chunk_base + i;
+        V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
+        V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
+        store_record(p.sink.records + pos, v, d, p.sink.energy[ray], (int)ray, sh.best_s[i]);
     }
+    __syncwarp();
 }
 
 __device__ __forceinline__ void cp_async8(void *smem_dst, const void *gmem_src) {
