@@ -35,15 +35,24 @@ static inline int check_launch(const char *what, int n_kernels = 1) {
 // The tree as the walk reads it: one 32-byte record per INNER node holding the
 // boxes of its two children quantised to 16 bits on the grid of the root box
 // (rounded outward), split into two 16-byte halves kept in separate arrays so
-// that random per-lane fetches spread over all shared-memory bank groups:
-//   a = { c0.lo0|c0.lo1<<16, c0.lo2|c0.hi0<<16, c0.hi1|c0.hi2<<16, c1.lo0|c1.lo1<<16 }
-//   b = { c1.lo2|c1.hi0<<16, c1.hi1|c1.hi2<<16, meta0, meta1 }
-// meta: bits 28..30 = leaf surface count (0 = inner node, 7 = empty leaf), bits 0..27 =
-// pair index of the child (inner) or first entry in the candidate list (leaf).
+// that random per-lane fetches spread over all shared-memory bank groups.  The
+// two planes of an axis share a word (lo | hi << 16), so the walk picks the
+// near / far plane of a ray with one byte-permute whose selector depends only
+// on the sign of the ray direction:
+//   a = { c0.axis0, c0.axis1, c0.axis2, c1.axis0 }
+//   b = { c1.axis1, c1.axis2, child0, child1 }
+// child word: inner node -> its pair index (bit 31 clear);
+//             leaf       -> bit 31 | (surface count - 1) << 22 | first entry in the
+//                           candidate list, i.e. the low 24 bits are a queue entry
+//                           without its ray slot.
 // Pairs are numbered breadth-first from the root (pair 0 = the root's children).
+// root_meta (host side only): bits 28..30 = leaf surface count of the root itself
+// (0 = inner node), bits 0..27 = first candidate.
 struct TrcPairHalf { uint32_t w[4]; };
 #define TRC_META_COUNT(m) (((m) >> 28) & 7u)
 #define TRC_META_INDEX(m) ((m) & 0x0fffffffu)
+#define TRC_CHILD_LEAF 0x80000000u
+#define TRC_CHILD_ENTRY_MASK 0x00ffffffu
 
 // Device-side scene tables; owned by the library (trc_scene_create/destroy).
 struct TrcScene {

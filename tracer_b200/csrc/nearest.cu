@@ -141,7 +141,7 @@ constexpr unsigned kNoEntry = 0xffffffffu;    // (first < 2^22 - 1, so no real e
 #define TRC_WALK_RING 3
 #endif
 constexpr int kRing = TRC_WALK_RING;                       // ray batches in flight per warp (cp.async), 1.5 KB each
-constexpr int kListFields = 10;               // A[3], Bl[3], Bh[3], slot
+constexpr int kListFields = 10;               // A[3], Bn[3], Bf[3], slot | direction signs << 8
 #ifndef TRC_WALK_SMEM_PAIRS
 #define TRC_WALK_SMEM_PAIRS 512
 #endif
@@ -197,7 +197,8 @@ struct WalkParams {
 // slab for either sign of d.  1/d is clamped to +-1e20 so an axis-parallel ray
 // gives a huge finite interval instead of 0 * inf.
 struct RayF {
-    float A[3], Bl[3], Bh[3];
+    float A[3], Bn[3], Bf[3];      // near / far plane: t = fma(2^23 + q, A, B)
+    unsigned sn[3], sf[3];         // byte-permute selectors of the near / far plane of each axis
 };
 
 __device__ __forceinline__ float rcp_approx(float x) {
@@ -206,44 +207,68 @@ __device__ __forceinline__ float rcp_approx(float x) {
     return y;
 }
 
+// selector words: 2^23 + (low / high 16 bits) as a float = prmt(w, 0x4B000000, sel)
+#define TRC_SEL_LO 0x7610u
+#define TRC_SEL_HI 0x7632u
+__device__ __forceinline__ void set_selectors(RayF &r, unsigned signs) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        r.sn[k] = ((signs >> k) & 1u) ? TRC_SEL_HI : TRC_SEL_LO;    // d < 0: the ray enters through the hi plane
+        r.sf[k] = r.sn[k] ^ 0x0022u;
+    }
+}
+
 // Float32 set-up of one ray; returns whether the (widened) root box is hit.
-__device__ __forceinline__ bool ray_setup(V3 v, V3 d, const WalkParams &p, RayF &r) {
+// signs: bit k set when the direction component k is negative.
+__device__ __forceinline__ bool ray_setup(V3 v, V3 d, const WalkParams &p, RayF &r, unsigned &signs) {
     const float dv[3] = {(float)d.x, (float)d.y, (float)d.z};
     const float ov[3] = {(float)v.x, (float)v.y, (float)v.z};
     float tmin = 0.0f, tmax = TRC_FINF;
+    signs = 0u;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         float inv = fabsf(dv[k]) < 1e-20f ? copysignf(1e20f, dv[k]) : rcp_approx(dv[k]);
+        bool neg = inv < 0.0f;
         float pad = fmaf(1e-6f, fabsf(ov[k]) + p.extent[k], 1.5f * p.qstep[k]);
         float a = p.qstep[k] * inv;
         float shift = 8388608.0f * a;
+        // lo planes see the origin moved by +pad, hi planes by -pad: the slab widens for either sign
         float bl = (p.root_lo[k] - (ov[k] + pad)) * inv, bh = (p.root_lo[k] - (ov[k] - pad)) * inv;
         r.A[k] = a;
-        r.Bl[k] = bl - shift;
-        r.Bh[k] = bh - shift;
+        r.Bn[k] = (neg ? bh : bl) - shift;
+        r.Bf[k] = (neg ? bl : bh) - shift;
+        signs |= neg ? (1u << k) : 0u;
         // root box planes: lo = grid origin, hi = root_hi
         float t2 = (p.root_hi[k] - (ov[k] - pad)) * inv;
-        tmin = fmaxf(tmin, fminf(bl, t2)); tmax = fminf(tmax, fmaxf(bl, t2));
+        tmin = fmaxf(tmin, neg ? t2 : bl); tmax = fminf(tmax, neg ? bl : t2);
     }
     return tmin <= tmax;
 }
 
-// 2^23 + (low / high 16 bits of w) as a float
-__device__ __forceinline__ float q_lo(unsigned w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7610)); }
-__device__ __forceinline__ float q_hi(unsigned w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7632)); }
+__device__ __forceinline__ float plane(unsigned w, unsigned sel) {
+    unsigned o;          // raw prmt: __byte_perm would mask the (already clean) selector first
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(o) : "r"(w), "r"(0x4B000000u), "r"(sel));
+    return __uint_as_float(o);
+}
+__device__ __forceinline__ uint4 lds128(unsigned addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
 
-// Conservative entry distance into the box with planes (2^23 + q): lo0,lo1,lo2,hi0,hi1,hi2;
-// +inf when the box is missed or lies beyond tbest.
-__device__ __forceinline__ float slab16(float l0, float l1, float l2, float h0, float h1, float h2,
-                                        const RayF &r, float tbest) {
-    float t1 = fmaf(l0, r.A[0], r.Bl[0]), t2 = fmaf(h0, r.A[0], r.Bh[0]);
-    float tmin = fminf(t1, t2), tmax = fmaxf(t1, t2);
-    t1 = fmaf(l1, r.A[1], r.Bl[1]); t2 = fmaf(h1, r.A[1], r.Bh[1]);
-    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
-    t1 = fmaf(l2, r.A[2], r.Bl[2]); t2 = fmaf(h2, r.A[2], r.Bh[2]);
-    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
-    tmin = fmaxf(tmin, 0.0f);
-    return (tmin <= tmax && tmin <= tbest) ? tmin : TRC_FINF;
+// Conservative entry distance into the child box whose axis words are w0, w1, w2;
+// hit = entered before tbest.
+__device__ __forceinline__ float slab16(unsigned w0, unsigned w1, unsigned w2, const RayF &r, float tbest, bool &hit) {
+    float n0 = fmaf(plane(w0, r.sn[0]), r.A[0], r.Bn[0]);
+    float n1 = fmaf(plane(w1, r.sn[1]), r.A[1], r.Bn[1]);
+    float n2 = fmaf(plane(w2, r.sn[2]), r.A[2], r.Bn[2]);
+    float f0 = fmaf(plane(w0, r.sf[0]), r.A[0], r.Bf[0]);
+    float f1 = fmaf(plane(w1, r.sf[1]), r.A[1], r.Bf[1]);
+    float f2 = fmaf(plane(w2, r.sf[2]), r.A[2], r.Bf[2]);
+    float tmin = fmaxf(fmaxf(n0, n1), fmaxf(n2, 0.0f));
+    float tmax = fminf(fminf(f0, f1), fminf(f2, tbest));
+    hit = tmin <= tmax;
+    return tmin;
 }
 
 __device__ __forceinline__ float best_as_float(unsigned long long bits) {
@@ -380,6 +405,8 @@ nearest_hit_walk_kernel(WalkParams p) {
         }
     }
     __syncthreads();
+    unsigned pair_a_smem = (unsigned)__cvta_generic_to_shared(&S.pair_a[0]);   // pair_b follows pair_a
+    asm volatile("" : "+r"(pair_a_smem));      // keep it in a register (else recomputed from %cluster_ctaid per visit)
     const int root_count = p.has_tree ? (int)TRC_META_COUNT(p.root_meta) : 7;   // 0 inner, 1..4 leaf, 7 nothing
     int stack[kStack];
 
@@ -450,12 +477,13 @@ nearest_hit_walk_kernel(WalkParams p) {
                 issue_batch();
                 asm volatile("cp.async.wait_group %0;" ::"n"(kRing - 1) : "memory");
                 RayF nr;
+                unsigned nsigns = 0u;
                 bool surv = false;
                 if (valid) {
                     const double *src = &sh.ring[ring_r % kRing][0][lane];   // this lane's own copies
                     V3 v = mk(src[0], src[32], src[64]);
                     V3 d = mk(src[96], src[128], src[160]);
-                    surv = ray_setup(v, d, p, nr) && root_count != 7 && !(p.debug & 2);
+                    surv = ray_setup(v, d, p, nr, nsigns) && root_count != 7 && !(p.debug & 2);
                 }
                 ++ring_r;
                 unsigned m = __ballot_sync(full, surv);
@@ -472,9 +500,9 @@ nearest_hit_walk_kernel(WalkParams p) {
                         int e = list_n + __popc(m & lt_mask);
 #pragma unroll
                         for (int k = 0; k < 3; ++k) {
-                            sh.list[k][e] = nr.A[k]; sh.list[3 + k][e] = nr.Bl[k]; sh.list[6 + k][e] = nr.Bh[k];
+                            sh.list[k][e] = nr.A[k]; sh.list[3 + k][e] = nr.Bn[k]; sh.list[6 + k][e] = nr.Bf[k];
                         }
-                        sh.list[9][e] = __int_as_float(j);
+                        sh.list[9][e] = __int_as_float(j | (int)(nsigns << 8));
                     }
                     list_n += __popc(m);
                 }
@@ -497,9 +525,11 @@ nearest_hit_walk_kernel(WalkParams p) {
                     int e = list_n - 1 - rk;
 #pragma unroll
                     for (int k = 0; k < 3; ++k) {
-                        r.A[k] = sh.list[k][e]; r.Bl[k] = sh.list[3 + k][e]; r.Bh[k] = sh.list[6 + k][e];
+                        r.A[k] = sh.list[k][e]; r.Bn[k] = sh.list[3 + k][e]; r.Bf[k] = sh.list[6 + k][e];
                     }
-                    int slot = __float_as_int(sh.list[9][e]);
+                    int word = __float_as_int(sh.list[9][e]);
+                    int slot = word & 0xff;
+                    set_selectors(r, (unsigned)word >> 8);
                     tag = (unsigned)slot << 24;
                     cur = 0; sp = 0;
                     tbest = best_as_float(sh.best_t[slot]);
@@ -519,16 +549,18 @@ nearest_hit_walk_kernel(WalkParams p) {
                 for (int it = 0; it < kWalkSteps; ++it) {
                     if (cur >= 0 && pend0 == kNoEntry) {
                         uint4 a, b;
-                        if (kAllShared || cur < kSmemPairs) { a = S.pair_a[cur]; b = S.pair_b[cur]; }
+                        if (kAllShared || cur < kSmemPairs) {
+                            a = lds128(pair_a_smem + 16u * (unsigned)cur);
+                            b = lds128(pair_a_smem + (unsigned)(sizeof(uint4) * kSmemPairs) + 16u * (unsigned)cur);
+                        }
                         else { a = __ldg(p.pair_a + cur); b = __ldg(p.pair_b + cur); }
-                        float t0 = slab16(q_lo(a.x), q_hi(a.x), q_lo(a.y), q_hi(a.y), q_lo(a.z), q_hi(a.z), r, tbest);
-                        float t1 = slab16(q_lo(a.w), q_hi(a.w), q_lo(b.x), q_hi(b.x), q_lo(b.y), q_hi(b.y), r, tbest);
-                        unsigned c0 = TRC_META_COUNT(b.z), c1 = TRC_META_COUNT(b.w);
-                        bool h0 = t0 < TRC_FINF && c0 != 7u, h1 = t1 < TRC_FINF && c1 != 7u;
-                        bool i0 = h0 && c0 == 0u, i1 = h1 && c1 == 0u;
-                        // meta (count << 28 | first) -> entry (slot << 24 | (count - 1) << 22 | first)
-                        if (h1 && !i1) pend0 = tag | ((c1 - 1u) << 22) | TRC_META_INDEX(b.w);
-                        if (h0 && !i0) { pend1 = pend0; pend0 = tag | ((c0 - 1u) << 22) | TRC_META_INDEX(b.z); }
+                        bool h0, h1;
+                        float t0 = slab16(a.x, a.y, a.z, r, tbest, h0);
+                        float t1 = slab16(a.w, b.x, b.y, r, tbest, h1);
+                        bool i0 = h0 && (int)b.z >= 0, i1 = h1 && (int)b.w >= 0;     // hit inner children
+                        // hit leaves: child word -> queue entry (slot << 24 | (count - 1) << 22 | first)
+                        if (h1 && !i1) pend0 = tag | (b.w & TRC_CHILD_ENTRY_MASK);
+                        if (h0 && !i0) { pend1 = pend0; pend0 = tag | (b.z & TRC_CHILD_ENTRY_MASK); }
                         int f0 = (int)b.z, f1 = (int)b.w;        // inner: meta == pair index
                         if (i0 && i1) {
                             bool swap = t1 < t0;

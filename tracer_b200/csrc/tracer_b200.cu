@@ -143,10 +143,15 @@ extern "C" int trc_scene_set_bvh(TrcScene *sc, const TrcBvhNode *nodes, int32_t 
             sc->qstep[k] = st; step[k] = (double)st;
             sc->extent[k] = fmaxf(fabsf(l), fabsf(hh));
         }
-        auto meta_of = [&](const TrcBvhNode &nd, int32_t pair_index) -> uint32_t {
-            if (nd.count < 0) return 7u << 28;                       // empty leaf
-            if (nd.count == 0) return (uint32_t)pair_index;          // inner
-            return ((uint32_t)nd.count << 28) | (uint32_t)nd.first;  // leaf
+        auto meta_of = [&](const TrcBvhNode &nd) -> uint32_t {      // root word, host side only
+            if (nd.count < 0) return 7u << 28;                       // empty tree
+            if (nd.count == 0) return 0u;                            // inner
+            return ((uint32_t)nd.count << 28) | (uint32_t)nd.first;  // the whole tree is one leaf
+        };
+        auto child_word = [&](const TrcBvhNode &nd, int32_t pair_index) -> uint32_t {
+            if (nd.count == 0) return (uint32_t)pair_index;                                       // inner
+            if (nd.count < 0) return TRC_CHILD_LEAF;      // empty leaf: inverted box, harmless candidate 0
+            return TRC_CHILD_LEAF | ((uint32_t)(nd.count - 1) << 22) | (uint32_t)nd.first;        // leaf
         };
         std::vector<int32_t> pair_of((size_t)n_nodes, -1), order;   // inner node -> pair index
         order.reserve((size_t)n_nodes);
@@ -172,15 +177,15 @@ extern "C" int trc_scene_set_bvh(TrcScene *sc, const TrcBvhNode *nodes, int32_t 
         }
         if (order.size() >= (1u << 28)) return fail(TRC_ERR_CAPACITY, "trc_scene_set_bvh: too many nodes%s");
         sc->n_pairs = (int32_t)order.size();
-        sc->root_meta = meta_of(nodes[0], 0);
+        sc->root_meta = meta_of(nodes[0]);
         std::vector<TrcPairHalf> pa(order.size() + 1), pb(order.size() + 1);
         for (size_t h = 0; h < order.size(); ++h) {
             const TrcBvhNode &nd = nodes[order[h]];
-            uint32_t q[12];
-            uint32_t meta[2];
+            uint32_t ax[6];          // per child and axis: lo | hi << 16
+            uint32_t word[2];
             for (int c = 0; c < 2; ++c) {
                 const TrcBvhNode &ch = nodes[nd.first + c];
-                meta[c] = meta_of(ch, ch.count == 0 ? pair_of[nd.first + c] : 0);
+                word[c] = child_word(ch, ch.count == 0 ? pair_of[nd.first + c] : 0);
                 for (int k = 0; k < 3; ++k) {
                     double ql = floor((ch.lo[k] - (double)sc->root_lo[k]) / step[k]);
                     double qh = ceil((ch.hi[k] - (double)sc->root_lo[k]) / step[k]);
@@ -188,14 +193,12 @@ extern "C" int trc_scene_set_bvh(TrcScene *sc, const TrcBvhNode *nodes, int32_t 
                     if (ql > 65535.0) ql = 65535.0;
                     if (!(qh <= 65535.0)) qh = 65535.0;
                     if (qh < 0.0) qh = 0.0;
-                    q[6 * c + k] = (uint32_t)ql;
-                    q[6 * c + 3 + k] = (uint32_t)qh;
+                    if (ch.count < 0) { ql = 65535.0; qh = 0.0; }      // empty leaf: never entered
+                    ax[3 * c + k] = (uint32_t)ql | ((uint32_t)qh << 16);
                 }
             }
-            pa[h].w[0] = q[0] | (q[1] << 16); pa[h].w[1] = q[2] | (q[3] << 16);
-            pa[h].w[2] = q[4] | (q[5] << 16); pa[h].w[3] = q[6] | (q[7] << 16);
-            pb[h].w[0] = q[8] | (q[9] << 16); pb[h].w[1] = q[10] | (q[11] << 16);
-            pb[h].w[2] = meta[0]; pb[h].w[3] = meta[1];
+            pa[h].w[0] = ax[0]; pa[h].w[1] = ax[1]; pa[h].w[2] = ax[2]; pa[h].w[3] = ax[3];
+            pb[h].w[0] = ax[4]; pb[h].w[1] = ax[5]; pb[h].w[2] = word[0]; pb[h].w[3] = word[1];
         }
         TRC_CUDA(cudaMalloc(&sc->d_pair_a, sizeof(TrcPairHalf) * pa.size()));
         TRC_CUDA(cudaMalloc(&sc->d_pair_b, sizeof(TrcPairHalf) * pb.size()));
