@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 2
+#define TRC_ABI_VERSION 3
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -218,6 +218,22 @@ int trc_trace_hits(const TrcScene *scene, int64_t n_rays,
                    int32_t use_bvh, int32_t *d_hit_surf,
                    TrcHitRecord *d_records, int64_t capacity,
                    uint32_t *d_chunk_off, uint32_t *d_chunk_cnt, int64_t *d_total, void *stream);
+
+/* One slice of a bundle that is still arriving from the host (the engine copies
+ * a host RayBundle in slices on a second stream and traces slice k while slice
+ * k+1 is in flight).  Same as trc_trace_hits for the rays [ray_base, ray_base +
+ * n_rays) of a larger bundle: every pointer addresses the slice's FIRST ray /
+ * first chunk (ray_base must be a multiple of TRC_HIT_CHUNK, `ld` stays the row
+ * stride of the whole bundle), records carry ray = ray_base + local index, and
+ * *d_total is NOT zeroed: the caller zeroes it before the first slice and reads
+ * the total after the last one.  The chunk tables of all slices together are
+ * what trc_order_hits expects. */
+int trc_trace_hits_slice(const TrcScene *scene, int64_t n_rays,
+                         const double *d_vertices, const double *d_directions, const double *d_energy, int64_t ld,
+                         int32_t use_bvh, int32_t *d_hit_surf,
+                         TrcHitRecord *d_records, int64_t capacity,
+                         uint32_t *d_chunk_off, uint32_t *d_chunk_cnt, int64_t *d_total,
+                         int64_t ray_base, void *stream);
 
 /* Child order of the optics loop + concatenate_rays (tracer_engine.py:218-266,
  * ray_bundle.py:197-223): surface-major, parent-ray-minor.  From the chunk

@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtracer_b200.so")
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 # enum TrcGeomKind
 (G_FLAT_INFINITE, G_RECT_PLATE, G_RECT_EXTRUDED, G_ROUND_PLATE, G_TRIANGLE, G_PARABOLOID,
@@ -88,6 +88,7 @@ SIGNATURES = {
     "trc_scene_num_surfaces": (_I32, [_P]),
     "trc_nearest_hit": (C.c_int, [_P, _I64, _P, _P, _I64, _I32, _P, _P]),
     "trc_trace_hits": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _I32, _P, _P, _I64, _P, _P, _P, _P]),
+    "trc_trace_hits_slice": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _I32, _P, _P, _I64, _P, _P, _P, _I64, _P]),
     "trc_order_work_bytes": (_I64, [_I64, _I64, _I32]),
     "trc_order_hits": (C.c_int, [_I64, _P, _P, _P, _I64, _I32, _P, _P, _P, _P, _P]),
     "trc_sort_work_bytes": (_I64, [_I64, _I32]),

@@ -50,6 +50,7 @@ struct HitSink {
     int64_t capacity;
     uint32_t *chunk_off, *chunk_cnt;
     unsigned long long *total;
+    int32_t ray_base;                  // added to the ray index stored in a record (slices of a larger bundle)
 };
 
 __device__ __forceinline__ void store_record(TrcHitRecord *dst, V3 v, V3 d, double e, int ray, int surf) {
@@ -115,7 +116,7 @@ nearest_hit_brute_kernel(const TrcSurfaceRec *__restrict__ surfs, int n_surf, in
         __syncthreads();
         if (hit) {
             unsigned long long pos = block_base + before + __popc(m & ((1u << lane) - 1u));
-            if ((int64_t)pos < sink.capacity) store_record(sink.records + pos, v, d, sink.energy[i], (int)i, best_s);
+            if ((int64_t)pos < sink.capacity) store_record(sink.records + pos, v, d, sink.energy[i], sink.ray_base + (int)i, best_s);
         }
     }
 }
@@ -374,7 +375,7 @@ __device__ __forceinline__ void emit_chunk_hits(WalkWarpShared &sh, const WalkPa
         int64_t ray = chunk_base + i;
         V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
         V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
-        store_record(p.sink.records + pos, v, d, p.sink.energy[ray], (int)ray, sh.best_s[i]);
+        store_record(p.sink.records + pos, v, d, p.sink.energy[ray], p.sink.ray_base + (int)ray, sh.best_s[i]);
     }
     __syncwarp();
 }
@@ -609,8 +610,8 @@ nearest_hit_walk_kernel(WalkParams p) {
 }  // namespace
 
 static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir, int64_t ld,
-                          int32_t use_bvh, HitSink sink, cudaStream_t st) {
-    if (sink.records) TRC_CUDA(cudaMemsetAsync(sink.total, 0, sizeof(unsigned long long), st));
+                          int32_t use_bvh, HitSink sink, cudaStream_t st, bool zero_total = true) {
+    if (sink.records && zero_total) TRC_CUDA(cudaMemsetAsync(sink.total, 0, sizeof(unsigned long long), st));
     if (n == 0) return TRC_OK;
     if (n >= 0x7fffffffLL) return fail(TRC_ERR_CAPACITY, "trc_nearest_hit: more than 2^31-1 rays, chunk the bundle%s");
     if (!use_bvh) {
@@ -666,19 +667,36 @@ extern "C" int trc_nearest_hit(const TrcScene *sc, int64_t n, const double *d_ve
                                int64_t ld, int32_t use_bvh, int32_t *d_hit_surf, void *stream) {
     if (!sc || n < 0 || (n > 0 && (!d_vert || !d_dir || !d_hit_surf)) || ld < n)
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: bad argument%s");
-    HitSink sink = {d_hit_surf, nullptr, nullptr, 0, nullptr, nullptr, nullptr};
+    HitSink sink = {d_hit_surf, nullptr, nullptr, 0, nullptr, nullptr, nullptr, 0};
     return launch_nearest(sc, n, d_vert, d_dir, ld, use_bvh, sink, (cudaStream_t)stream);
+}
+
+static int trace_hits_impl(const char *who, const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir,
+                           const double *d_energy, int64_t ld, int32_t use_bvh, int32_t *d_hit_surf,
+                           TrcHitRecord *d_records, int64_t capacity, uint32_t *d_chunk_off, uint32_t *d_chunk_cnt,
+                           int64_t *d_total, int64_t ray_base, bool zero_total, void *stream) {
+    if (!sc || n < 0 || capacity < 0 || !d_total || ld < n || ray_base < 0 || ray_base % TRC_HIT_CHUNK != 0 ||
+        ray_base + n >= 0x7fffffffLL ||
+        (n > 0 && (!d_vert || !d_dir || !d_energy || !d_chunk_off || !d_chunk_cnt || (capacity > 0 && !d_records))))
+        return fail(TRC_ERR_BAD_ARGUMENT, "%s: bad argument", who);
+    static TrcHitRecord dummy_rec;   // never written: capacity 0
+    HitSink sink = {d_hit_surf, d_energy, d_records ? d_records : &dummy_rec, d_records ? capacity : 0, d_chunk_off,
+                    d_chunk_cnt, reinterpret_cast<unsigned long long *>(d_total), (int32_t)ray_base};
+    return launch_nearest(sc, n, d_vert, d_dir, ld, use_bvh, sink, (cudaStream_t)stream, zero_total);
 }
 
 extern "C" int trc_trace_hits(const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir,
                               const double *d_energy, int64_t ld, int32_t use_bvh, int32_t *d_hit_surf,
                               TrcHitRecord *d_records, int64_t capacity, uint32_t *d_chunk_off,
                               uint32_t *d_chunk_cnt, int64_t *d_total, void *stream) {
-    if (!sc || n < 0 || capacity < 0 || !d_total || ld < n ||
-        (n > 0 && (!d_vert || !d_dir || !d_energy || !d_chunk_off || !d_chunk_cnt || (capacity > 0 && !d_records))))
-        return fail(TRC_ERR_BAD_ARGUMENT, "trc_trace_hits: bad argument%s");
-    static TrcHitRecord dummy_rec;   // never written: capacity 0
-    HitSink sink = {d_hit_surf, d_energy, d_records ? d_records : &dummy_rec, d_records ? capacity : 0, d_chunk_off,
-                    d_chunk_cnt, reinterpret_cast<unsigned long long *>(d_total)};
-    return launch_nearest(sc, n, d_vert, d_dir, ld, use_bvh, sink, (cudaStream_t)stream);
+    return trace_hits_impl("trc_trace_hits", sc, n, d_vert, d_dir, d_energy, ld, use_bvh, d_hit_surf, d_records,
+                           capacity, d_chunk_off, d_chunk_cnt, d_total, 0, true, stream);
+}
+
+extern "C" int trc_trace_hits_slice(const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir,
+                                    const double *d_energy, int64_t ld, int32_t use_bvh, int32_t *d_hit_surf,
+                                    TrcHitRecord *d_records, int64_t capacity, uint32_t *d_chunk_off,
+                                    uint32_t *d_chunk_cnt, int64_t *d_total, int64_t ray_base, void *stream) {
+    return trace_hits_impl("trc_trace_hits_slice", sc, n, d_vert, d_dir, d_energy, ld, use_bvh, d_hit_surf,
+                           d_records, capacity, d_chunk_off, d_chunk_cnt, d_total, ray_base, false, stream);
 }

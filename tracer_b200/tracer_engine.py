@@ -47,12 +47,19 @@ class _LazyRows(object):
 
 
 class _DevBundle(object):
-    """Engine-internal view of a bundle living in HBM."""
-    __slots__ = ('V', 'D', 'E', 'W', 'n')
+    """Engine-internal view of a bundle living in HBM.  ``slices`` is set while a
+    host bundle is still arriving: [(first ray, end ray, CUDA event of its copy)]."""
+    __slots__ = ('V', 'D', 'E', 'W', 'n', 'slices', 'keep')
 
-    def __init__(self, V, D, E, W=None):
+    def __init__(self, V, D, E, W=None, slices=None, keep=None):
         self.V, self.D, self.E, self.W = V, D, E, W
         self.n = int(V.shape[1])
+        self.slices = slices
+        self.keep = keep          # host arrays of the copies in flight
+
+
+STREAM_MIN_RAYS = 1 << 22     # host bundles at least this large are uploaded in slices ...
+STREAM_SLICES = 8             # ... this many, each traced while the next one is copied
 
 
 class TracerEngine(object):
@@ -86,6 +93,7 @@ class TracerEngine(object):
         self._scene = None
         self._frames_key = None
         self._hit_frac = {}       # bounce -> hit fraction of the previous trace (sizes the hit list)
+        self._copy_stream = None
         self.kernel_events = None  # set to a list to collect (bounce, n, H, start, end) CUDA events of trc_trace_hits
         self.stats = {}
 
@@ -125,11 +133,56 @@ class TracerEngine(object):
             arr = np.ascontiguousarray(arr, dtype=np.float64)
             return torch.from_numpy(arr).to(self.device, non_blocking=True)
 
+        streamed = self._upload_in_slices(bundle)
+        if streamed is not None:
+            return streamed
         V, D, E = col('vertices'), col('directions'), col('energy')
         W = col('wavelengths', required=False) if bundle.has_property('wavelengths') else None
         if V.dim() != 2 or V.shape[0] != 3 or D.shape != V.shape or E.shape[0] != V.shape[1]:
             raise ValueError("bundle arrays must be vertices (3,n), directions (3,n), energy (n,)")
         return _DevBundle(V.contiguous(), D.contiguous(), E.contiguous(), None if W is None else W.contiguous())
+
+    def _upload_in_slices(self, bundle):
+        """Large host bundle: allocate it in HBM and enqueue the host->device copy in
+        STREAM_SLICES slices on a second stream, one event per slice; bounce 1 traces
+        slice k (trc_trace_hits_slice) while slice k+1 is on the wire.  Returns None
+        when the bundle is device-backed, small, or carries wavelengths."""
+        import torch
+        props = getattr(bundle, '_props', None)
+        if props is None or bundle.has_property('wavelengths') and bundle.is_set('wavelengths'):
+            return None
+        raw = [props.get(k) for k in ('vertices', 'directions', 'energy')]
+        if any(not isinstance(a, np.ndarray) for a in raw):
+            return None
+        hV, hD, hE = (np.ascontiguousarray(a, dtype=np.float64) for a in raw)
+        if hV.ndim != 2 or hV.shape[0] != 3 or hD.shape != hV.shape or hE.shape != (hV.shape[1],):
+            return None          # the regular path raises the reference's error
+        n = hV.shape[1]
+        if n < STREAM_MIN_RAYS:
+            return None
+        dev = self.device
+        V = torch.empty((3, n), dtype=torch.float64, device=dev)
+        D = torch.empty((3, n), dtype=torch.float64, device=dev)
+        E = torch.empty(n, dtype=torch.float64, device=dev)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+        cs = self._copy_stream
+        cs.wait_stream(torch.cuda.current_stream(dev))       # the blocks may have just been freed by compute work
+        step = -(-n // STREAM_SLICES)
+        step = -(-step // L.HIT_CHUNK) * L.HIT_CHUNK
+        tV, tD, tE = torch.from_numpy(hV), torch.from_numpy(hD), torch.from_numpy(hE)
+        slices = []
+        with torch.cuda.stream(cs):
+            for a in range(0, n, step):
+                b = min(n, a + step)
+                for k in range(3):
+                    V[k, a:b].copy_(tV[k, a:b], non_blocking=True)
+                    D[k, a:b].copy_(tD[k, a:b], non_blocking=True)
+                E[a:b].copy_(tE[a:b], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cs)
+                slices.append((a, b, ev))
+        return _DevBundle(V, D, E, None, slices, keep=(tV, tD, tE))
 
     # ------------------------------------------------------------ draws
     def _numpy_draws(self, scene, seg, H):
@@ -201,6 +254,24 @@ class TracerEngine(object):
         cap = n if frac is None or n <= (1 << 20) else min(n, int(1.3 * frac * n) + 65536)
         while True:
             records = torch.empty((cap, L.HIT_RECORD_BYTES // 8), dtype=f64, device=dev)
+            if cur.slices is not None:
+                # the bundle is still arriving: trace each slice as soon as its copy has landed
+                stream = torch.cuda.current_stream(dev)
+                ld = cur.V.stride(0)
+                for a, b, ev in cur.slices:
+                    stream.wait_event(ev)
+                    c0 = a // L.HIT_CHUNK
+                    L.check(lib.trc_trace_hits_slice(
+                        scene.handle, b - a, cur.V.data_ptr() + 8 * a, cur.D.data_ptr() + 8 * a,
+                        cur.E.data_ptr() + 8 * a, ld, 1 if use_bvh else 0, None, L.dptr(records), cap,
+                        chunk_off.data_ptr() + 4 * c0, chunk_cnt.data_ptr() + 4 * c0, L.dptr(counters), a, st))
+                cur.slices = cur.keep = None   # resident from here on (an overflow re-runs the plain call)
+                H = int(counters[0].item())
+                if H <= cap:
+                    break
+                cap = H
+                counters.zero_()
+                continue
             if self.kernel_events is not None:
                 ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 ev0.record()
