@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 3
+#define TRC_ABI_VERSION 4
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -84,12 +84,22 @@ typedef enum TrcOpticsKind {
     TRC_O_LAMB_DIRECTIONAL_SPECTRAL = 8, /* Lambertian_directional_axisymmetric_piecewise_spectral :359
                                      op[1] = n_wavelengths; table = thetas[table_len],
                                      wavelengths[n_wl], absorptance[table_len*n_wl] (bilinear) */
-    TRC_O_KIND_COUNT = 9
+    TRC_O_LAMB_PIECEWISE_SPEC = 9,/* Lambertian_piecewise_Specular_directional_axisymmetric_piecewise :457
+                                     table = thetas[n], abs_th[n], spec_th[n]: absorptance AND specularity
+                                     interpolated at the incidence angle */
+    TRC_O_LAMBERTIAN_ABSORBANT = 10,/* LambertianAbsorbant :891 (+ Absorbant.attenuate :874-889, imposed
+                                     attenuation coefficient): op: absorptivity, ang_range, a_c, scaling.
+                                     E_att = E exp(-a_c |hit - parent vertex| scaling), E' = E_att (1 - abs) */
+    TRC_O_KIND_COUNT = 11
 } TrcOpticsKind;
 
 /* Surface flag bits. */
 #define TRC_F_ONE_SIDED   1u   /* OneSidedReflective / OneSidedRealReflective (:195,:492): E'=0 where d.up>0 */
 #define TRC_F_UNBOUNDED   2u   /* no finite AABB: tested for every ray, outside the BVH */
+#define TRC_F_IAM         4u   /* Martin-Ruiz incidence-angle modifier (IAM.__call__ :277-282) replaces the
+                                  energy of Lambertian_IAM :303 / RealReflective_IAM :320:
+                                  E' = E (1 - abs) (1 - exp(-cos^c / a_r)) / (1 - exp(-1 / a_r)),
+                                  cos = |(d.n) n|; op[4] = a_r, op[5] = c */
 
 /* One record per surface in Assembly.get_surfaces() order (assembly.py:60-77).
  * frame = rows 0..2 of Surface._temp_frame (has_frame.py:75), inv = rows 0..2
@@ -99,14 +109,14 @@ typedef struct TrcSurfaceRec {
     double frame[12];
     double inv[12];
     double gp[12];       /* geometry parameters, see TrcGeomKind */
-    double op[4];        /* optics parameters, see TrcOpticsKind */
+    double op[8];        /* optics parameters, see TrcOpticsKind (op[4..5]: TRC_F_IAM) */
     int32_t gkind;
     int32_t okind;
     uint32_t flags;
     int32_t table_off;   /* offset (in doubles) into the scene's optics table pool, -1 = none */
     int32_t table_len;   /* number of (x, y) knots */
     int32_t pad_[3];
-} TrcSurfaceRec;         /* 352 bytes */
+} TrcSurfaceRec;         /* 384 bytes */
 
 /* Binary BVH node over per-surface global AABBs.  Replaces the relevance
  * mask produced by KdTree.traversal (accel_tree.py:213-312): instead of
@@ -260,6 +270,7 @@ int trc_order_hits(int64_t n_chunks, const uint32_t *d_chunk_off, const uint32_t
  *   Optional tallies (NULL to skip): d_absorbed[q] = E_in - E_out
  *   (AbsorptionAccountant :1638-1643), d_normals (3,h) (NormalAccountant),
  *   d_e_in[q], d_dirs_in (3,h) (Reception / Direction accountants),
+ *   d_attenuated[q] = E_in - E_att (AttenuationAccountant :1670; 0 for optics without attenuation),
  *   d_out_wavelengths[q] (child wavelength = parent's).
  *   d_cull[q] = 1 where child energy <= min_energy (tracer_engine.py:242). */
 typedef struct TrcOpticsArgs {
@@ -284,6 +295,7 @@ typedef struct TrcOpticsArgs {
     double *d_out_wavelengths;    /* nullable */
     int32_t *d_cull;              /* nullable; int32 so it can key trc_sort_pairs */
     int64_t *d_n_cull;            /* nullable: device counter incremented by the number of culled children */
+    double *d_attenuated;         /* nullable */
 } TrcOpticsArgs;
 int trc_optics(const TrcScene *scene, const TrcOpticsArgs *args, void *stream);
 

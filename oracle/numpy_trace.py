@@ -67,15 +67,70 @@ def _theta_in(d, normals):
     return N.arccos(N.sqrt(N.sum(vertical ** 2, axis=0)))
 
 
-def apply_optics(opt, d, normals, energy, wavelengths, up):
+_KNOWN = ('Transparent', 'OneSidedReflective', 'Reflective', 'OneSidedRealReflective', 'RealReflective',
+          'Lambertian', 'LambertianSpecular', 'Lambertian_directional_axisymmetric_piecewise',
+          'LambertianSpecular_directional_axisymmetric_piecewise',
+          'Lambertian_directional_axisymmetric_piecewise_spectral', 'Reflective_spectral',
+          'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM', 'LambertianAbsorbant',
+          'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise')
+
+
+def _iam(base, d, normals, energy):
+    """IAM.__call__, optics_callables.py:277-282"""
+    vertical = N.sum(d * normals, axis=0) * normals
+    cos_aoi = N.sqrt(N.sum(vertical ** 2, axis=0))
+    return energy * (1. - base._abs) * (1. - N.exp(-cos_aoi ** base.c / base.a_r)) / (1. - N.exp(-1. / base.a_r))
+
+
+def apply_optics(opt, d, normals, energy, wavelengths, up, v_parent=None, hit=None):
     """One optics callable on the selected rays of one surface.
-    Returns (directions (3,h), energy (h,))."""
+    Returns (directions (3,h), energy (h,)); apply_optics.attenuations holds the
+    attenuated energy of the last call (LambertianAbsorbant) or None."""
     base, _ = _unwrap(opt)
     names = _names(base)
     h = d.shape[1]
     one_sided = False
+    apply_optics.attenuations = None
+    for cls in type(base).__mro__:          # a subclass with its own __call__ is not its parent
+        if cls.__name__ in _KNOWN:
+            break
+        if '__call__' in vars(cls) and cls.__name__ != '_OpticsDescription':
+            raise NotImplementedError("oracle: optics %s" % type(base).__name__)
     for name in names:
-        if name == 'Transparent':                                   # optics_callables.py:106-113
+        if name == 'Lambertian_IAM':                                # :303-318
+            out = _lambert(normals, base._ang_range, h), _iam(base, d, normals, energy)
+        elif name == 'RealReflective_IAM':                          # :320-329
+            dirs, _ = apply_optics(_PlainRealReflective(base), d, normals, energy, wavelengths, up)
+            out = dirs, _iam(base, d, normals, energy)
+        elif name == 'LambertianSpecular_IAM':                      # :596-627
+            directs = N.zeros(d.shape)
+            vertical = N.sum(directs * normals, axis=0) * normals     # sic: the zeroed array (:606)
+            cos_aoi = N.sqrt(N.sum(vertical ** 2, axis=0))
+            specular = N.random.rand(h) < base.specularity
+            directs[:, specular] = reflections(d[:, specular], normals[:, specular])
+            directs[:, ~specular] = _lambert(normals[:, ~specular], N.pi / 2., int(N.sum(~specular)))
+            out = directs, energy * (1. - base._abs * (1. - N.exp(-cos_aoi / base.a_r)) / (1. - N.exp(-1. / base.a_r)))
+        elif name == 'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise':   # :466-487
+            th = _theta_in(d, normals)
+            ab = N.interp(th, base.thetas, base.abs_th)
+            spec = N.interp(th, base.thetas, base.spec_th)
+            directs = N.zeros(d.shape)
+            specular = N.random.rand(h) < spec
+            directs[:, specular] = reflections(d[:, specular], normals[:, specular])
+            directs[:, ~specular] = _lambert(normals[:, ~specular], N.pi / 2., int(N.sum(~specular)))
+            out = directs, energy * (1. - ab)
+        elif name == 'LambertianAbsorbant':                         # :901-906 with attenuate :874-889
+            dirs = _lambert(normals, base._ang_range, h)
+            e0 = energy * (1. - 0.)
+            path = N.sqrt(N.sum((hit - v_parent) ** 2, axis=0))
+            if base._scaling != 1.:
+                path = path * base._scaling
+            if len(base.a_c) > 1:
+                raise NotImplementedError("oracle: per-medium attenuation coefficients")
+            e_att = e0 * N.exp(-base.a_c * path)
+            apply_optics.attenuations = energy - e_att
+            out = dirs, e_att * (1. - base._absorptivity)
+        elif name == 'Transparent':                                 # optics_callables.py:106-113
             out = d.copy(), energy.copy()
         elif name in ('Reflective', 'OneSidedReflective'):          # :130-140, :201-212
             out = reflections(d, normals), energy * (1. - base._abs)
@@ -138,7 +193,17 @@ def apply_optics(opt, d, normals, energy, wavelengths, up):
     return dirs, e
 
 
-_ACC = {'Absorber': '_absorbed', 'Receptor': '_received', 'Scatterer': '_scattered', 'Location': '_hits',
+class _PlainRealReflective(object):
+    """View of a RealReflective_IAM object as its RealReflective part."""
+
+    def __init__(self, base):
+        self._abs, self._sig, self.bi_var = base._abs, base._sig, base.bi_var
+
+
+_PlainRealReflective.__name__ = 'RealReflective'
+
+
+_ACC = {'Absorber': '_absorbed', 'Attenuator': '_attenuated', 'Receptor': '_received', 'Scatterer': '_scattered', 'Location': '_hits',
         'Directional': '_directions', 'Normal': '_normals', 'Spectral': '_wavelengths'}
 
 
@@ -199,9 +264,10 @@ class OracleEngine(object):
                 d_in = bund.directions[:, sel]
                 e_in = bund.energy[sel]
                 wl_in = None if bund.wavelengths is None else bund.wavelengths[sel]
-                dirs, e_out = apply_optics(surf._opt, d_in, normals, e_in, wl_in, surf._temp_frame[:3, 2])
+                dirs, e_out = apply_optics(surf._opt, d_in, normals, e_in, wl_in, surf._temp_frame[:3, 2],
+                                           v_parent=bund.vertices[:, sel], hit=hit)
                 child = Bundle(hit, dirs, e_out, sel, wl_in)
-                self._count(s_idx, surf, hit, d_in, normals, e_in, e_out, wl_in)
+                self._count(s_idx, surf, hit, d_in, normals, e_in, e_out, wl_in, apply_optics.attenuations)
                 record.append(child)
                 delete = e_out <= min_energy
                 weak.append(delete)
@@ -218,10 +284,10 @@ class OracleEngine(object):
             self.tree.append(Bundle.concat(record))
         return bund.vertices, bund.directions
 
-    def _count(self, s_idx, surf, hit, d_in, normals, e_in, e_out, wl_in):
+    def _count(self, s_idx, surf, hit, d_in, normals, e_in, e_out, wl_in, attenuated=None):
         """Accountant.count for each accountant (optics_callables.py:1597-1790)."""
         _, accs = _unwrap(surf._opt)
-        data = {'_absorbed': e_in - e_out, '_received': e_in, '_scattered': e_out, '_hits': hit,
+        data = {'_absorbed': e_in - e_out, '_attenuated': attenuated, '_received': e_in, '_scattered': e_out, '_hits': hit,
                 '_directions': d_in, '_normals': normals, '_wavelengths': wl_in}
         t = self.tallies[s_idx]
         for a in accs:

@@ -29,6 +29,7 @@ TRACE_CASES = {
     'c4_cavity': (scenes.c4_cavity, dict(n_rays=1500, n_theta=8, n_z=4), 16, 5, 1e-3 * 1000. * np.pi * 0.81 / 1500),
     'c5_cavity': (scenes.c5_cavity, dict(n_rays=1500), 17, 6, 1e-10),
     'c5_cavity_spectral': (scenes.c5_cavity, dict(n_rays=1500, spectral=True), 18, 6, 1e-10),
+    'c6_optics_zoo': (scenes.c6_optics_zoo, dict(n_rays=3000), 19, 5, 1e-10),
 }
 ZOO_RAYS = 4000
 ZOO_SEED = 99

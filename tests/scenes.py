@@ -178,6 +178,37 @@ def c5_cavity(T, n_rays=2000, spectral=False):
     return asm, source
 
 
+def c6_optics_zoo(T, n_rays=2000):
+    """Five plates under a diffuse lid, one optics class of the IAM / piecewise /
+    attenuating family per plate, each with accountants."""
+    oc = T.optics_callables
+    thetas = np.linspace(0., np.pi / 2., 7)
+    abs_th = np.linspace(0.2, 0.7, 7)
+    spec_th = np.linspace(0.9, 0.1, 7)
+    optics = [
+        oc.Lambertian_IAMReceiver(0.3, 0.16, 1.3),
+        oc.RealReflective_IAMReceiver(0.1, 0.2, 2e-3, True),
+        oc.LambertianSpecular_IAMReceiver(0.2, 0.5, 0.16),
+        oc.Lambertian_piecewise_Specular_directional_axisymmetric_piecewiseReceiver(thetas, abs_th, spec_th),
+        oc.LambertianAbsorbantAbsorberAttenuatorLocation(0.25, [0.4], np.pi / 2., 1.5),
+    ]
+    objs = []
+    for k, opt in enumerate(optics):
+        objs.append(T.object.AssembledObject(
+            surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(1., 3.), opt)],
+            transform=T.spatial_geometry.translate(k - 2., 0., 0.)))
+    objs.append(T.object.AssembledObject(
+        surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(7., 5.), oc.LambertianReceiver(0.3))],
+        transform=np.dot(T.spatial_geometry.translate(0., 0., 1.5), T.spatial_geometry.rotx(np.pi))))
+    asm = T.assembly.Assembly(objects=objs)
+
+    def source():
+        direction = np.r_[0.3, 0.1, -1.]
+        direction = direction / np.sqrt(np.sum(direction ** 2))
+        return T.sources.disk_bundle(n_rays, np.c_[[-0.4, -0.1, 1.4]], direction, 2.4, 0.02, flux=1000.)
+    return asm, source
+
+
 def gm_zoo(T):
     """name -> (geometry manager factory, frame) covering every supported GM kind."""
     sg = T.spatial_geometry

@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, name), f'{name} declared in the header but not exported'
     assert declared == set(_lib.SIGNATURES), 'ctypes SIGNATURES out of sync with the header'
     assert lib.trc_abi_version() == _lib.ABI_VERSION
-    assert _lib.SURFACE_DTYPE.itemsize == 352 and _lib.BVH_NODE_DTYPE.itemsize == 64
+    assert _lib.SURFACE_DTYPE.itemsize == 384 and _lib.BVH_NODE_DTYPE.itemsize == 64
 
 
 def test_bad_arguments_return_status_not_crash():
@@ -151,6 +151,25 @@ def test_unknown_classes_and_hooks_raise_at_compile_time():
         pass
     with pytest.raises(NotImplementedError, match='WeirdOptics'):
         CompiledScene(asm_with(T.flat_surface.RectPlateGM(1, 1), WeirdOptics()), upload=False)
+
+    class TiltedMirror(T.optics_callables.Reflective):          # a subclass that changes the optics ...
+        def __call__(self, geometry, rays, selector):
+            return None
+    with pytest.raises(NotImplementedError, match='TiltedMirror'):  # ... must not be traced as its parent
+        CompiledScene(asm_with(T.flat_surface.RectPlateGM(1, 1), TiltedMirror(0.1)), upload=False)
+
+    class RenamedMirror(T.optics_callables.Reflective):         # same __call__: fine
+        pass
+    sc = CompiledScene(asm_with(T.flat_surface.RectPlateGM(1, 1), RenamedMirror(0.1)), upload=False)
+    assert sc.records[0]['okind'] == 1
+    with pytest.raises(NotImplementedError):
+        T.optics_callables.Reflective_IAM
+    with pytest.raises(NotImplementedError, match='one-element'):
+        CompiledScene(asm_with(T.flat_surface.RectPlateGM(1, 1),
+                               T.optics_callables.LambertianAbsorbant(0.1, [0.1, 0.2])), upload=False)
+    sc = CompiledScene(asm_with(T.flat_surface.RectPlateGM(1, 1),
+                                T.optics_callables.RealReflective_IAM(0.1, 0.16, 1e-3)), upload=False)
+    assert sc.records[0]['flags'] & 4 and sc.records[0]['op'][4] == 0.16 and sc.records[0]['op'][5] == 1.
 
     class Owner(T.object.AssembledObject):
         def own_rays(self, rays, surface_id):

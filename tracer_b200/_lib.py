@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtracer_b200.so")
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 # enum TrcGeomKind
 (G_FLAT_INFINITE, G_RECT_PLATE, G_RECT_EXTRUDED, G_ROUND_PLATE, G_TRIANGLE, G_PARABOLOID,
@@ -22,18 +22,19 @@ ABI_VERSION = 3
 # enum TrcOpticsKind
 (O_TRANSPARENT, O_REFLECTIVE, O_REAL_REFLECTIVE, O_LAMBERTIAN, O_LAMBERTIAN_SPECULAR,
  O_LAMB_DIRECTIONAL, O_REFLECTIVE_SPECTRAL, O_LAMBSPEC_DIRECTIONAL,
- O_LAMB_DIRECTIONAL_SPECTRAL) = range(9)
+ O_LAMB_DIRECTIONAL_SPECTRAL, O_LAMB_PIECEWISE_SPEC, O_LAMBERTIAN_ABSORBANT) = range(11)
 F_ONE_SIDED = 1
 F_UNBOUNDED = 2
+F_IAM = 4
 BVH_MAX_LEAF = 4
 
-# numpy mirror of struct TrcSurfaceRec (352 bytes)
+# numpy mirror of struct TrcSurfaceRec (384 bytes)
 SURFACE_DTYPE = np.dtype([
-    ("frame", "<f8", (12,)), ("inv", "<f8", (12,)), ("gp", "<f8", (12,)), ("op", "<f8", (4,)),
+    ("frame", "<f8", (12,)), ("inv", "<f8", (12,)), ("gp", "<f8", (12,)), ("op", "<f8", (8,)),
     ("gkind", "<i4"), ("okind", "<i4"), ("flags", "<u4"), ("table_off", "<i4"),
     ("table_len", "<i4"), ("pad_", "<i4", (3,)),
 ], align=True)
-assert SURFACE_DTYPE.itemsize == 352
+assert SURFACE_DTYPE.itemsize == 384
 
 # numpy mirror of struct TrcBvhNode (64 bytes)
 BVH_NODE_DTYPE = np.dtype([
@@ -57,7 +58,7 @@ class OpticsArgs(C.Structure):
         ("min_energy", C.c_double),
         ("d_absorbed", C.c_void_p), ("d_normals", C.c_void_p), ("d_e_in", C.c_void_p),
         ("d_dirs_in", C.c_void_p), ("d_out_wavelengths", C.c_void_p), ("d_cull", C.c_void_p),
-        ("d_n_cull", C.c_void_p),
+        ("d_n_cull", C.c_void_p), ("d_attenuated", C.c_void_p),
     ]
 
 

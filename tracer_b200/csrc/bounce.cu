@@ -27,6 +27,7 @@ struct OpticsParams {
     double *o_wavelengths;
     int32_t *cull;
     unsigned long long *n_cull;
+    double *attenuated;
 };
 
 // Philox draws in the units the reference's numpy calls produce
@@ -47,13 +48,14 @@ __device__ __forceinline__ void philox_draws(const TrcSurfaceRec *s, uint64_t se
         }
         break;
     }
-    case TRC_O_LAMBERTIAN: case TRC_O_LAMB_DIRECTIONAL: case TRC_O_LAMB_DIRECTIONAL_SPECTRAL: {
+    case TRC_O_LAMBERTIAN: case TRC_O_LAMB_DIRECTIONAL: case TRC_O_LAMB_DIRECTIONAL_SPECTRAL:
+    case TRC_O_LAMBERTIAN_ABSORBANT: {
         double a, b;
         uniform2(seed, q, bounce, 0, a, b);
         u[0] = two_pi * a; u[1] = b;
         break;
     }
-    case TRC_O_LAMBERTIAN_SPECULAR: case TRC_O_LAMBSPEC_DIRECTIONAL: {
+    case TRC_O_LAMBERTIAN_SPECULAR: case TRC_O_LAMBSPEC_DIRECTIONAL: case TRC_O_LAMB_PIECEWISE_SPEC: {
         double a, b, c, e;
         uniform2(seed, q, bounce, 0, a, b);
         uniform2(seed, q, bounce, 1, c, e);
@@ -96,7 +98,7 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
         } else {
             philox_draws(s, p.seed, p.bounce, (uint64_t)q, u);
         }
-        OpticsOut o = apply_optics(s, tables, d, n, e_in, wl, u);
+        OpticsOut o = apply_optics(s, tables, d, n, e_in, wl, u, v, hit);
         if (s->flags & TRC_F_ONE_SIDED) {
             // OneSided*: rays arriving along +z of the surface lose all energy
             // (optics_callables.py:201-212, :498-504)
@@ -111,6 +113,7 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
         if (p.absorbed) p.absorbed[q] = e_in - o.energy;
         if (p.normals) { p.normals[q] = n.x; p.normals[p.ld_out + q] = n.y; p.normals[2 * p.ld_out + q] = n.z; }
         if (p.e_in) p.e_in[q] = e_in;
+        if (p.attenuated) p.attenuated[q] = o.attenuated;
         if (p.dirs_in) { p.dirs_in[q] = d.x; p.dirs_in[p.ld_out + q] = d.y; p.dirs_in[2 * p.ld_out + q] = d.z; }
         if (p.o_wavelengths) p.o_wavelengths[q] = wl;
         culled = o.energy <= p.min_energy;
@@ -228,6 +231,7 @@ extern "C" int trc_optics(const TrcScene *sc, const TrcOpticsArgs *a, void *stre
     p.absorbed = a->d_absorbed; p.normals = a->d_normals; p.e_in = a->d_e_in; p.dirs_in = a->d_dirs_in;
     p.o_wavelengths = a->d_out_wavelengths; p.cull = a->d_cull;
     p.n_cull = reinterpret_cast<unsigned long long *>(a->d_n_cull);
+    p.attenuated = a->d_attenuated;
     int64_t blocks = (a->h + 255) / 256;
     optics_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(sc->d_surfaces, sc->d_tables, p);
     return check_launch("optics");

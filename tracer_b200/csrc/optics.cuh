@@ -96,14 +96,22 @@ __device__ __forceinline__ double interp2(double th, double wl, const double *xp
     return (1.0 - a) * ((1.0 - b) * v00 + b * v01) + a * ((1.0 - b) * v10 + b * v11);
 }
 
-struct OpticsOut { V3 dir; double energy; };
+struct OpticsOut { V3 dir; double energy; double attenuated; };
+
+// |(d.n) n|: the cosine of the incidence angle as the reference forms it
+__device__ __forceinline__ double cos_incidence(V3 d, V3 n) {
+    double k = dot(d, n);
+    V3 vert = mk(k * n.x, k * n.y, k * n.z);
+    return sqrt(vert.x * vert.x + vert.y * vert.y + vert.z * vert.z);
+}
 
 // u[0..2]: draws already in the reference's units: normal(scale=sigma) values,
 // uniform(0, 2pi) angles, uniform(0,1) variates (see TrcOpticsArgs).
 __device__ __forceinline__ OpticsOut apply_optics(const TrcSurfaceRec *s, const double *tables,
                                                   V3 d, V3 n, double e_in, double wavelength,
-                                                  const double *u) {
+                                                  const double *u, V3 v_parent, V3 hit) {
     OpticsOut o;
+    o.attenuated = 0.0;
     const double *op = s->op;
     switch (s->okind) {
     case TRC_O_TRANSPARENT:
@@ -156,6 +164,29 @@ __device__ __forceinline__ OpticsOut apply_optics(const TrcSurfaceRec *s, const 
         }
         o.energy = e_in * (1.0 - ab); break;
     }
+    case TRC_O_LAMB_PIECEWISE_SPEC: {
+        // optics_callables.py:466-487: absorptance and specularity both follow the incidence angle
+        const double *xp = tables + s->table_off;
+        int nth = s->table_len;
+        double th = acos(cos_incidence(d, n));
+        double ab = interp1(th, xp, xp + nth, nth);
+        double spec = interp1(th, xp, xp + 2 * nth, nth);
+        if (u[0] < spec) o.dir = reflect(d, n);
+        else o.dir = rotation_to_z_apply(n, pillbox_direction(u[1], u[2], M_PI / 2.0));
+        o.energy = e_in * (1.0 - ab); break;
+    }
+    case TRC_O_LAMBERTIAN_ABSORBANT: {
+        // LambertianAbsorbant.__call__ (:901-906): Lambertian with zero absorptivity, then
+        // Absorbant.attenuate (:874-889) over the path from the parent vertex, then absorption
+        o.dir = rotation_to_z_apply(n, pillbox_direction(u[0], u[1], op[1]));
+        double e0 = e_in * (1.0 - 0.0);
+        double dx = hit.x - v_parent.x, dy = hit.y - v_parent.y, dz = hit.z - v_parent.z;
+        double path = sqrt(dx * dx + dy * dy + dz * dz);
+        if (op[3] != 1.0) path *= op[3];
+        double e_att = e0 * exp(-op[2] * path);
+        o.attenuated = e_in - e_att;
+        o.energy = e_att * (1.0 - op[0]); break;
+    }
     case TRC_O_REFLECTIVE_SPECTRAL: {
         const double *xp = tables + s->table_off;
         const double *fp = xp + s->table_len;
@@ -164,6 +195,11 @@ __device__ __forceinline__ OpticsOut apply_optics(const TrcSurfaceRec *s, const 
     }
     default:
         o.dir = d; o.energy = e_in; break;
+    }
+    if (s->flags & TRC_F_IAM) {
+        // IAM.__call__ (:277-282) overwrites the energy of the base optics
+        double c = cos_incidence(d, n);
+        o.energy = e_in * (1.0 - op[0]) * (1.0 - exp(-(op[5] == 1.0 ? c : pow(c, op[5])) / op[4])) / (1.0 - exp(-1.0 / op[4]));
     }
     return o;
 }

@@ -121,9 +121,65 @@ class Lambertian_directional_axisymmetric_piecewise_spectral(_OpticsDescription)
         self.absorptance = np.reshape(absorptance, (len(self.thetas), len(self.wavelengths)))
 
 
+class Lambertian_IAM(Lambertian):
+    """Lambertian whose energy follows the Martin-Ruiz incidence-angle modifier (:303-318)."""
+
+    def __init__(self, absorptivity, a_r, c=1):
+        Lambertian.__init__(self, absorptivity)
+        self.a_r = a_r
+        self.c = c
+
+
+class RealReflective_IAM(RealReflective):
+    """RealReflective with the incidence-angle modifier, exponent c = 1 (:320-329)."""
+
+    def __init__(self, absorptivity, a_r, sigma, bi_var=False):
+        RealReflective.__init__(self, absorptivity, sigma, bi_var)
+        self.a_r = a_r
+        self.c = 1
+
+
+class LambertianSpecular_IAM(_OpticsDescription):
+    """Specular/diffuse mix (:586-627).  As written in the reference the modifier is
+    evaluated on a zeroed direction array, so cos(AOI) = 0 and the energy is passed on
+    unchanged whatever absorptivity and a_r are; that behaviour is what is reproduced."""
+
+    def __init__(self, absorptivity=0., specularity=0.5, a_r=0.16):
+        self._abs = absorptivity
+        self.specularity = specularity
+        self.a_r = a_r
+
+
+class Lambertian_piecewise_Specular_directional_axisymmetric_piecewise(_OpticsDescription):
+    """Specular/diffuse mix with absorptance and specularity both interpolated in the
+    incidence angle (:457-487)."""
+
+    def __init__(self, thetas, absorptance_th, specularity_th):
+        self.thetas = thetas
+        self.abs_th = absorptance_th
+        self.spec_th = specularity_th
+
+
+class LambertianAbsorbant(Lambertian):
+    """Opaque diffuse wall of an absorbing volume (:891-906): the ray is attenuated over
+    the path from its parent vertex (imposed attenuation coefficient, Absorbant :860-889),
+    then absorbed.  ``attenuation_coefficient`` must be a one-element sequence, as in the
+    reference (its ``len(self.a_c)`` rejects scalars)."""
+
+    def __init__(self, absorptivity=0., attenuation_coefficient=0., ang_range=np.pi / 2., scaling=1.):
+        self._absorptivity = absorptivity
+        Lambertian.__init__(self, absorptivity=0., ang_range=ang_range)
+        self._scaling = scaling
+        self.a_c = attenuation_coefficient
+        if self.a_c is not None:
+            self.a_c = np.array(attenuation_coefficient)
+
+
 perfect_mirror = Reflective(0)
 
 _BASE_OPTICS = {c.__name__: c for c in (
+    Lambertian_IAM, RealReflective_IAM, LambertianSpecular_IAM, LambertianAbsorbant,
+    Lambertian_piecewise_Specular_directional_axisymmetric_piecewise,
     Transparent, Reflective, Lambertian, Reflective_spectral, OneSidedReflective, RealReflective,
     OneSidedRealReflective, LambertianSpecular, Lambertian_directional_axisymmetric_piecewise,
     LambertianSpecular_directional_axisymmetric_piecewise,
@@ -134,10 +190,8 @@ _BASE_OPTICS = {c.__name__: c for c in (
 _UNSUPPORTED = (
     'Refractive', 'RefractiveHomogenous', 'RefractiveAbsorbantHomogenous', 'RefractiveScattering',
     'RefractiveScatteringHomogenous', 'Scattering', 'ScatteringPeriodicBoundary', 'PeriodicBoundary',
-    'Absorbant', 'LambertianAbsorbant', 'FresnelConductorHomogenous', 'SemiLambertian', 'BiFacial',
-    'Reflective_IAM', 'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM',
-    'Lambertian_directional_axisymmetric_piecewise_Polychromatic',
-    'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise')
+    'Absorbant', 'FresnelConductorHomogenous', 'SemiLambertian', 'BiFacial', 'Reflective_IAM',
+    'Lambertian_directional_axisymmetric_piecewise_Polychromatic')
 
 
 # ------------------------------------------------------------ accountants

@@ -156,6 +156,7 @@ def _global_aabb(frame, local_box):
 # ----------------------------------------------------------------- optics
 _ACC_FIELDS = {  # shorthand -> (list attribute on the accountant, source)
     'Absorber': ('_absorbed', 'absorbed'),
+    'Attenuator': ('_attenuated', 'attenuated'),
     'Receptor': ('_received', 'e_in'),
     'Scatterer': ('_scattered', 'e_out'),
     'Location': ('_hits', 'hits'),
@@ -179,10 +180,56 @@ def _optics_record(opt):
             accountants.append((a,) + _ACC_FIELDS[sh])
     elif hasattr(opt, 'get_all_hits'):
         raise NotImplementedError(f"optics manager {type(opt).__name__}: unknown accounting wrapper")
-    rec = dict(okind=None, op=[0., 0., 0., 0.], flags=0, table=None, accountants=accountants,
+    rec = dict(okind=None, op=[0.] * 8, flags=0, table=None, table_len=None, accountants=accountants,
                needs_wavelengths=False, instance=opt)
+    # classes whose __call__ the kernels reproduce; anything deriving from one of them with
+    # its own __call__ (e.g. Reflective_IAM, SemiLambertian, a user subclass) must not be
+    # traced as its parent
+    known = ('Transparent', 'OneSidedReflective', 'Reflective', 'OneSidedRealReflective', 'RealReflective',
+             'Lambertian', 'LambertianSpecular', 'Lambertian_directional_axisymmetric_piecewise',
+             'LambertianSpecular_directional_axisymmetric_piecewise',
+             'Lambertian_directional_axisymmetric_piecewise_spectral', 'Reflective_spectral',
+             'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM', 'LambertianAbsorbant',
+             'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise')
+    for cls in type(base).__mro__:
+        if cls.__name__ in known:
+            break
+        if '__call__' in vars(cls) and cls.__name__ != '_OpticsDescription':
+            raise NotImplementedError(
+                f"optics manager {type(base).__name__}: {cls.__name__}.__call__ has no GPU kernel "
+                "(no CPU fallback); see SURVEY.md section 8 for the supported classes")
     for name in _mro_names(base):
-        if name == 'Transparent':
+        if name == 'Lambertian_IAM':
+            rec['okind'] = L.O_LAMBERTIAN
+            rec['op'][:2] = [_scalar(base._abs, 'absorptivity'), _scalar(base._ang_range, 'ang_range')]
+            rec['op'][4:6] = [_scalar(base.a_r, 'a_r'), _scalar(base.c, 'c')]
+            rec['flags'] |= L.F_IAM
+        elif name == 'RealReflective_IAM':
+            rec['okind'] = L.O_REAL_REFLECTIVE
+            rec['op'][:3] = [_scalar(base._abs, 'absorptivity'), _scalar(base._sig, 'sigma'),
+                             1.0 if base.bi_var == True else 0.0]  # noqa: E712
+            rec['op'][4:6] = [_scalar(base.a_r, 'a_r'), _scalar(base.c, 'c')]
+            rec['flags'] |= L.F_IAM
+        elif name == 'LambertianSpecular_IAM':
+            # optics_callables.py:606-607: the modifier sees a zeroed direction array, cos(AOI) = 0,
+            # so the energy factor is exactly 1 whatever absorptivity and a_r are
+            rec['okind'] = L.O_LAMBERTIAN_SPECULAR
+            rec['op'][:2] = [0., _scalar(base.specularity, 'specularity')]
+        elif name == 'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise':
+            rec['okind'] = L.O_LAMB_PIECEWISE_SPEC
+            th = np.asarray(base.thetas, float)
+            rec['table'] = (th, np.concatenate([np.asarray(base.abs_th, float), np.asarray(base.spec_th, float)]))
+            rec['table_len'] = len(th)
+        elif name == 'LambertianAbsorbant':
+            a_c = base.a_c
+            if a_c is None or np.ndim(a_c) != 1 or len(a_c) != 1:
+                raise NotImplementedError(
+                    "LambertianAbsorbant: only one imposed attenuation coefficient (a one-element sequence) "
+                    "is supported; per-medium coefficients need the refractive family (SURVEY 8f N4)")
+            rec['okind'] = L.O_LAMBERTIAN_ABSORBANT
+            rec['op'][:4] = [_scalar(base._absorptivity, 'absorptivity'), _scalar(base._ang_range, 'ang_range'),
+                             float(a_c[0]), _scalar(base._scaling, 'scaling')]
+        elif name == 'Transparent':
             rec['okind'] = L.O_TRANSPARENT
         elif name in ('OneSidedReflective', 'Reflective'):
             rec['okind'] = L.O_REFLECTIVE
@@ -301,6 +348,7 @@ class CompiledScene(object):
         self.tables = np.concatenate(tables) if tables else np.zeros(0)
         self.needs_wavelengths = any(o['needs_wavelengths'] for o in self.optics)
         self.has_accountants = any(o['accountants'] for o in self.optics)
+        self.needs_theta_for_draws = any(o['okind'] == L.O_LAMB_PIECEWISE_SPEC for o in self.optics)
         self.accountant_sources = set(src for o in self.optics for (_, _, src) in o['accountants'])
         self.unbounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) != 0)[0].astype(np.int32)
         self.bounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) == 0)[0].astype(np.int32)

@@ -185,8 +185,10 @@ class TracerEngine(object):
         return _DevBundle(V, D, E, None, slices, keep=(tV, tD, tE))
 
     # ------------------------------------------------------------ draws
-    def _numpy_draws(self, scene, seg, H):
-        """Host draws in the reference's consumption order; returns 3 device arrays or None."""
+    def _numpy_draws(self, scene, seg, H, theta_in=None):
+        """Host draws in the reference's consumption order; returns 3 device arrays or None.
+        ``theta_in`` (host, slot order) is needed by optics whose specular/diffuse split
+        depends on the incidence angle."""
         import torch
         draws = None
         counts = np.diff(seg)
@@ -205,8 +207,19 @@ class TracerEngine(object):
                     else:
                         vals[0] = np.random.normal(scale=sig, size=(n,))
                         vals[1] = np.random.uniform(low=0., high=2. * np.pi, size=(n,))
-            elif k in (L.O_LAMBERTIAN, L.O_LAMB_DIRECTIONAL, L.O_LAMB_DIRECTIONAL_SPECTRAL):
-                ang = rec['op'][1] if k == L.O_LAMBERTIAN else np.pi / 2.
+            elif k == L.O_LAMB_PIECEWISE_SPEC:
+                th_tab, rest = scene.optics[s]['table']
+                spec = np.interp(theta_in[a:b], th_tab, rest[len(th_tab):])
+                r = np.random.rand(n)
+                diffuse = ~(r < spec)
+                nd = int(diffuse.sum())
+                vals[0] = r
+                vals[1], vals[2] = np.zeros(n), np.zeros(n)
+                vals[1][diffuse] = np.random.uniform(low=0., high=2. * np.pi, size=nd)
+                vals[2][diffuse] = np.random.uniform(size=nd)
+            elif k in (L.O_LAMBERTIAN, L.O_LAMB_DIRECTIONAL, L.O_LAMB_DIRECTIONAL_SPECTRAL,
+                       L.O_LAMBERTIAN_ABSORBANT):
+                ang = rec['op'][1] if k in (L.O_LAMBERTIAN, L.O_LAMBERTIAN_ABSORBANT) else np.pi / 2.
                 vals[0] = np.random.uniform(low=0., high=2. * np.pi, size=n)
                 if ang != 0.:
                     vals[1] = np.random.uniform(size=n)
@@ -308,24 +321,38 @@ class TracerEngine(object):
         normals = torch.empty((3, H), dtype=f64, device=dev) if 'normals' in want else None
         e_in = torch.empty(H, dtype=f64, device=dev) if 'e_in' in want else None
         dirs_in = torch.empty((3, H), dtype=f64, device=dev) if 'dirs_in' in want else None
+        attenuated = torch.empty(H, dtype=f64, device=dev) if 'attenuated' in want else None
         if 'wavelengths' in want and cur.W is None:
             raise ValueError("Spectral accountant needs a 'wavelengths' bundle property")
         oW = torch.empty(H, dtype=f64, device=dev) if cur.W is not None else None
-        draws = self._numpy_draws(scene, seg_host, H) if self.rng == 'numpy' else None
-
         a = L.OpticsArgs()
         a.h = H
         a.d_records, a.d_slot_rec = records.data_ptr(), slot_rec.data_ptr()
         a.d_wavelengths = cur.W.data_ptr() if cur.W is not None else None
         a.d_out_vertices, a.d_out_directions = oV.data_ptr(), oD.data_ptr()
         a.d_out_energy, a.d_out_parents, a.ld_out = oE.data_ptr(), oP.data_ptr(), H
+        a.seed, a.bounce, a.min_energy = self.seed, bounce, float(min_energy)
+        draws = None
+        if self.rng == 'numpy':
+            theta_in = None
+            if scene.needs_theta_for_draws:
+                # the specular/diffuse split of these optics follows the incidence angle: a first
+                # pass of the kernel (draws unused for normals) provides it to the host
+                tn = torch.empty((3, H), dtype=f64, device=dev)
+                td = torch.empty((3, H), dtype=f64, device=dev)
+                a.d_normals, a.d_dirs_in = tn.data_ptr(), td.data_ptr()
+                L.check(lib.trc_optics(scene.handle, C.byref(a), st))
+                hn, hd = tn.cpu().numpy(), td.cpu().numpy()
+                vertical = np.sum(hd * hn, axis=0) * hn          # optics_callables.py:469-472
+                theta_in = np.arccos(np.sqrt(np.sum(vertical ** 2, axis=0)))
+            draws = self._numpy_draws(scene, seg_host, H, theta_in)
         for j in range(3):
             a.d_draws[j] = draws[j].data_ptr() if draws is not None else None
-        a.seed, a.bounce, a.min_energy = self.seed, bounce, float(min_energy)
         a.d_absorbed = absorbed.data_ptr()
         a.d_normals = normals.data_ptr() if normals is not None else None
         a.d_e_in = e_in.data_ptr() if e_in is not None else None
         a.d_dirs_in = dirs_in.data_ptr() if dirs_in is not None else None
+        a.d_attenuated = attenuated.data_ptr() if attenuated is not None else None
         a.d_out_wavelengths = oW.data_ptr() if oW is not None else None
         a.d_cull = cull.data_ptr()
         a.d_n_cull = counters[1:].data_ptr()
@@ -337,7 +364,7 @@ class TracerEngine(object):
         self.hits_per_surface += seg[1:] - seg[:-1]
         if scene.has_accountants:
             self._account(scene, seg_host, dict(hits=oV, absorbed=absorbed, e_out=oE, normals=normals, e_in=e_in,
-                                                dirs_in=dirs_in, wavelengths=oW))
+                                                dirs_in=dirs_in, wavelengths=oW, attenuated=attenuated))
 
         n_cull = int(counters[1].item())
         del records, work
