@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 4
+#define TRC_ABI_VERSION 5
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -90,7 +90,10 @@ typedef enum TrcOpticsKind {
     TRC_O_LAMBERTIAN_ABSORBANT = 10,/* LambertianAbsorbant :891 (+ Absorbant.attenuate :874-889, imposed
                                      attenuation coefficient): op: absorptivity, ang_range, a_c, scaling.
                                      E_att = E exp(-a_c |hit - parent vertex| scaling), E' = E_att (1 - abs) */
-    TRC_O_KIND_COUNT = 11
+    TRC_O_PERIODIC = 11,          /* PeriodicBoundary :690-723: op: period.  TWO children per hit: a
+                                     zero-energy stub at the hit, then the live ray moved by period * normal
+                                     (block A, block B of the surface's segment; see TrcOpticsArgs) */
+    TRC_O_KIND_COUNT = 12
 } TrcOpticsKind;
 
 /* Surface flag bits. */
@@ -296,6 +299,15 @@ typedef struct TrcOpticsArgs {
     int32_t *d_cull;              /* nullable; int32 so it can key trc_sort_pairs */
     int64_t *d_n_cull;            /* nullable: device counter incremented by the number of culled children */
     double *d_attenuated;         /* nullable */
+    /* Scenes with TRC_O_PERIODIC surfaces (NULL otherwise => child index == slot).  The child
+     * bundle then has more entries than hits: with c_s = hits on surface s and m_s = 1 or 2
+     * children per hit, surface s owns children [d_child_off[s], d_child_off[s+1]) and the j-th
+     * hit of the surface writes child d_child_off[s] + j (and + c_s + j for its second child).
+     * d_slot_surf / d_seg are the outputs of trc_order_hits; ld_out >= d_child_off[n_surfaces];
+     * the child arrays, d_cull and d_out_wavelengths are indexed by child, every other tally by slot. */
+    const int32_t *d_slot_surf;
+    const int64_t *d_seg;
+    const int64_t *d_child_off;
 } TrcOpticsArgs;
 int trc_optics(const TrcScene *scene, const TrcOpticsArgs *args, void *stream);
 

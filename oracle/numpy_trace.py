@@ -72,7 +72,7 @@ _KNOWN = ('Transparent', 'OneSidedReflective', 'Reflective', 'OneSidedRealReflec
           'LambertianSpecular_directional_axisymmetric_piecewise',
           'Lambertian_directional_axisymmetric_piecewise_spectral', 'Reflective_spectral',
           'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM', 'LambertianAbsorbant',
-          'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise')
+          'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise', 'PeriodicBoundary')
 
 
 def _iam(base, d, normals, energy):
@@ -264,6 +264,16 @@ class OracleEngine(object):
                 d_in = bund.directions[:, sel]
                 e_in = bund.energy[sel]
                 wl_in = None if bund.wavelengths is None else bund.wavelengths[sel]
+                base_opt, _ = _unwrap(surf._opt)
+                if 'PeriodicBoundary' in _names(base_opt):          # optics_callables.py:703-721
+                    stub = Bundle(hit, d_in.copy(), N.zeros(len(sel)), sel, wl_in)
+                    moved = Bundle(hit + base_opt.period * normals, d_in.copy(), e_in.copy(), sel, wl_in)
+                    child = Bundle.concat([stub, moved])
+                    record.append(child)
+                    delete = child.energy <= min_energy
+                    weak.append(delete)
+                    outg.append(child.take(N.nonzero(~delete)[0]) if delete.any() else child)
+                    continue
                 dirs, e_out = apply_optics(surf._opt, d_in, normals, e_in, wl_in, surf._temp_frame[:3, 2],
                                            v_parent=bund.vertices[:, sel], hit=hit)
                 child = Bundle(hit, dirs, e_out, sel, wl_in)

@@ -209,6 +209,31 @@ def c6_optics_zoo(T, n_rays=2000):
     return asm, source
 
 
+def c7_periodic_cell(T, n_rays=2000):
+    """A unit cell: Lambertian floor, PeriodicBoundary side walls (period 1 along x and y),
+    oblique pillbox source above.  Rays leaving through a wall re-enter from the opposite one."""
+    oc = T.optics_callables
+    sg = T.spatial_geometry
+    objs = [T.object.AssembledObject(
+        surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(1., 1.), oc.LambertianReceiver(0.6))])]
+    walls = [
+        np.dot(sg.translate(0.5, 0., 0.5), sg.roty(np.pi / 2.)),
+        np.dot(sg.translate(-0.5, 0., 0.5), sg.roty(-np.pi / 2.)),
+        np.dot(sg.translate(0., 0.5, 0.5), sg.rotx(-np.pi / 2.)),
+        np.dot(sg.translate(0., -0.5, 0.5), sg.rotx(np.pi / 2.)),
+    ]
+    for frame in walls:
+        objs.append(T.object.AssembledObject(
+            surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(1., 1.), oc.PeriodicBoundary(1.))], transform=frame))
+    asm = T.assembly.Assembly(objects=objs)
+
+    def source():
+        direction = np.r_[0.7, 0.35, -1.]
+        direction = direction / np.sqrt(np.sum(direction ** 2))
+        return T.sources.disk_bundle(n_rays, np.c_[[0., 0., 0.95]], direction, 0.45, 0.3, flux=1000.)
+    return asm, source
+
+
 def gm_zoo(T):
     """name -> (geometry manager factory, frame) covering every supported GM kind."""
     sg = T.spatial_geometry

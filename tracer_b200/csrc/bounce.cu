@@ -28,6 +28,8 @@ struct OpticsParams {
     int32_t *cull;
     unsigned long long *n_cull;
     double *attenuated;
+    const int32_t *slot_surf;
+    const int64_t *seg, *child_off;
 };
 
 // Philox draws in the units the reference's numpy calls produce
@@ -106,18 +108,40 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
             double proj = d.x * f[2] + d.y * f[6] + d.z * f[10];
             if (proj > 0.0) o.energy = 0.0;
         }
-        p.o_vert[q] = hit.x; p.o_vert[p.ld_out + q] = hit.y; p.o_vert[2 * p.ld_out + q] = hit.z;
-        p.o_dir[q] = o.dir.x; p.o_dir[p.ld_out + q] = o.dir.y; p.o_dir[2 * p.ld_out + q] = o.dir.z;
-        p.o_energy[q] = o.energy;
-        p.o_parents[q] = r;
+        // child index: the slot itself, unless some surface of the scene emits two children per hit
+        int64_t c = q, c2 = -1;
+        if (p.child_off) {
+            int64_t first = p.seg[sidx];
+            c = p.child_off[sidx] + (q - first);
+            if (s->okind == TRC_O_PERIODIC) c2 = c + (p.seg[sidx + 1] - first);
+        }
+        double e_first = o.energy;
+        if (c2 >= 0) {
+            // PeriodicBoundary (:703-721): block A = zero-energy stubs at the hit, block B = the
+            // rays themselves moved by period * normal
+            e_first = 0.0;
+            V3 moved = mk(hit.x + s->op[0] * n.x, hit.y + s->op[0] * n.y, hit.z + s->op[0] * n.z);
+            p.o_vert[c2] = moved.x; p.o_vert[p.ld_out + c2] = moved.y; p.o_vert[2 * p.ld_out + c2] = moved.z;
+            p.o_dir[c2] = d.x; p.o_dir[p.ld_out + c2] = d.y; p.o_dir[2 * p.ld_out + c2] = d.z;
+            p.o_energy[c2] = e_in;
+            p.o_parents[c2] = r;
+            if (p.o_wavelengths) p.o_wavelengths[c2] = wl;
+            bool weak2 = e_in <= p.min_energy;
+            if (p.cull) p.cull[c2] = weak2 ? 1 : 0;
+            if (weak2 && p.n_cull) atomicAdd(p.n_cull, 1ULL);
+        }
+        p.o_vert[c] = hit.x; p.o_vert[p.ld_out + c] = hit.y; p.o_vert[2 * p.ld_out + c] = hit.z;
+        p.o_dir[c] = o.dir.x; p.o_dir[p.ld_out + c] = o.dir.y; p.o_dir[2 * p.ld_out + c] = o.dir.z;
+        p.o_energy[c] = e_first;
+        p.o_parents[c] = r;
         if (p.absorbed) p.absorbed[q] = e_in - o.energy;
         if (p.normals) { p.normals[q] = n.x; p.normals[p.ld_out + q] = n.y; p.normals[2 * p.ld_out + q] = n.z; }
         if (p.e_in) p.e_in[q] = e_in;
         if (p.attenuated) p.attenuated[q] = o.attenuated;
         if (p.dirs_in) { p.dirs_in[q] = d.x; p.dirs_in[p.ld_out + q] = d.y; p.dirs_in[2 * p.ld_out + q] = d.z; }
-        if (p.o_wavelengths) p.o_wavelengths[q] = wl;
-        culled = o.energy <= p.min_energy;
-        if (p.cull) p.cull[q] = culled ? 1 : 0;
+        if (p.o_wavelengths) p.o_wavelengths[c] = wl;
+        culled = e_first <= p.min_energy;
+        if (p.cull) p.cull[c] = culled ? 1 : 0;
     }
     if (p.n_cull) {
         unsigned m = __ballot_sync(0xffffffffu, culled);
@@ -232,6 +256,8 @@ extern "C" int trc_optics(const TrcScene *sc, const TrcOpticsArgs *a, void *stre
     p.o_wavelengths = a->d_out_wavelengths; p.cull = a->d_cull;
     p.n_cull = reinterpret_cast<unsigned long long *>(a->d_n_cull);
     p.attenuated = a->d_attenuated;
+    p.slot_surf = a->d_slot_surf; p.seg = a->d_seg; p.child_off = a->d_child_off;
+    if (p.child_off && !p.seg) return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: d_child_off needs d_seg%s");
     int64_t blocks = (a->h + 255) / 256;
     optics_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(sc->d_surfaces, sc->d_tables, p);
     return check_launch("optics");

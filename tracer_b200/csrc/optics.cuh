@@ -114,7 +114,7 @@ __device__ __forceinline__ OpticsOut apply_optics(const TrcSurfaceRec *s, const 
     o.attenuated = 0.0;
     const double *op = s->op;
     switch (s->okind) {
-    case TRC_O_TRANSPARENT:
+    case TRC_O_TRANSPARENT: case TRC_O_PERIODIC:     // periodic: the energy leaves with the second child
         o.dir = d; o.energy = e_in; break;
     case TRC_O_REFLECTIVE:
         o.dir = reflect(d, n); o.energy = e_in * (1.0 - op[0]); break;

@@ -175,9 +175,18 @@ class LambertianAbsorbant(Lambertian):
             self.a_c = np.array(attenuation_coefficient)
 
 
+class PeriodicBoundary(_OpticsDescription):
+    """Periodic boundary condition (:690-723): every hit leaves a zero-energy stub at the
+    hit point and re-emits the ray, unchanged, from hit + period * normal."""
+
+    def __init__(self, period):
+        self.period = period
+
+
 perfect_mirror = Reflective(0)
 
 _BASE_OPTICS = {c.__name__: c for c in (
+    PeriodicBoundary,
     Lambertian_IAM, RealReflective_IAM, LambertianSpecular_IAM, LambertianAbsorbant,
     Lambertian_piecewise_Specular_directional_axisymmetric_piecewise,
     Transparent, Reflective, Lambertian, Reflective_spectral, OneSidedReflective, RealReflective,
@@ -189,7 +198,7 @@ _BASE_OPTICS = {c.__name__: c for c in (
 # O8 / 8f N4): constructing them says so instead of silently mis-tracing.
 _UNSUPPORTED = (
     'Refractive', 'RefractiveHomogenous', 'RefractiveAbsorbantHomogenous', 'RefractiveScattering',
-    'RefractiveScatteringHomogenous', 'Scattering', 'ScatteringPeriodicBoundary', 'PeriodicBoundary',
+    'RefractiveScatteringHomogenous', 'Scattering', 'ScatteringPeriodicBoundary',
     'Absorbant', 'FresnelConductorHomogenous', 'SemiLambertian', 'BiFacial', 'Reflective_IAM',
     'Lambertian_directional_axisymmetric_piecewise_Polychromatic')
 

@@ -190,7 +190,7 @@ def _optics_record(opt):
              'LambertianSpecular_directional_axisymmetric_piecewise',
              'Lambertian_directional_axisymmetric_piecewise_spectral', 'Reflective_spectral',
              'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM', 'LambertianAbsorbant',
-             'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise')
+             'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise', 'PeriodicBoundary')
     for cls in type(base).__mro__:
         if cls.__name__ in known:
             break
@@ -229,6 +229,13 @@ def _optics_record(opt):
             rec['okind'] = L.O_LAMBERTIAN_ABSORBANT
             rec['op'][:4] = [_scalar(base._absorptivity, 'absorptivity'), _scalar(base._ang_range, 'ang_range'),
                              float(a_c[0]), _scalar(base._scaling, 'scaling')]
+        elif name == 'PeriodicBoundary':
+            if accountants:
+                raise NotImplementedError(
+                    "PeriodicBoundary with accountants: the reference's Accountant.count sees 2 children per "
+                    "hit and fails on the shape mismatch; not reproduced")
+            rec['okind'] = L.O_PERIODIC
+            rec['op'][0] = _scalar(base.period, 'period')
         elif name == 'Transparent':
             rec['okind'] = L.O_TRANSPARENT
         elif name in ('OneSidedReflective', 'Reflective'):
@@ -348,6 +355,8 @@ class CompiledScene(object):
         self.tables = np.concatenate(tables) if tables else np.zeros(0)
         self.needs_wavelengths = any(o['needs_wavelengths'] for o in self.optics)
         self.has_accountants = any(o['accountants'] for o in self.optics)
+        self.children_per_hit = np.array([2 if o['okind'] == L.O_PERIODIC else 1 for o in self.optics], dtype=np.int64)
+        self.has_split = bool((self.children_per_hit > 1).any())
         self.needs_theta_for_draws = any(o['okind'] == L.O_LAMB_PIECEWISE_SPEC for o in self.optics)
         self.accountant_sources = set(src for o in self.optics for (_, _, src) in o['accountants'])
         self.unbounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) != 0)[0].astype(np.int32)

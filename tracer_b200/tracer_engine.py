@@ -308,29 +308,38 @@ class TracerEngine(object):
         work = torch.empty(int(lib.trc_order_work_bytes(n_chunks, H, S)), dtype=torch.uint8, device=dev)
         L.check(lib.trc_order_hits(n_chunks, L.dptr(chunk_off), L.dptr(chunk_cnt), L.dptr(records), H, S,
                                    L.dptr(slot_surf), L.dptr(slot_rec), L.dptr(seg), L.dptr(work), st))
-        need_seg_host = scene.has_accountants or self.rng == 'numpy'
+        need_seg_host = scene.has_accountants or self.rng == 'numpy' or scene.has_split
         seg_host = seg.cpu().numpy() if need_seg_host else None
+        # children: one per hit, or (PeriodicBoundary) two -- then child index != slot
+        Hc, child_off, child_off_host = H, None, None
+        if scene.has_split:
+            counts = np.diff(seg_host)
+            child_off_host = np.concatenate([[0], np.cumsum(counts * scene.children_per_hit)]).astype(np.int64)
+            Hc = int(child_off_host[-1])
+            child_off = torch.from_numpy(child_off_host).to(dev)
 
-        oV = torch.empty((3, H), dtype=f64, device=dev)
-        oD = torch.empty((3, H), dtype=f64, device=dev)
-        oE = torch.empty(H, dtype=f64, device=dev)
-        oP = torch.empty(H, dtype=i64, device=dev)
-        cull = torch.empty(H, dtype=i32, device=dev)
+        oV = torch.empty((3, Hc), dtype=f64, device=dev)
+        oD = torch.empty((3, Hc), dtype=f64, device=dev)
+        oE = torch.empty(Hc, dtype=f64, device=dev)
+        oP = torch.empty(Hc, dtype=i64, device=dev)
+        cull = torch.empty(Hc, dtype=i32, device=dev)
         want = scene.accountant_sources
         absorbed = torch.empty(H, dtype=f64, device=dev)   # always: feeds the per-surface totals
-        normals = torch.empty((3, H), dtype=f64, device=dev) if 'normals' in want else None
+        normals = torch.empty((3, Hc), dtype=f64, device=dev) if 'normals' in want else None   # row stride = ld_out
         e_in = torch.empty(H, dtype=f64, device=dev) if 'e_in' in want else None
-        dirs_in = torch.empty((3, H), dtype=f64, device=dev) if 'dirs_in' in want else None
+        dirs_in = torch.empty((3, Hc), dtype=f64, device=dev) if 'dirs_in' in want else None
         attenuated = torch.empty(H, dtype=f64, device=dev) if 'attenuated' in want else None
         if 'wavelengths' in want and cur.W is None:
             raise ValueError("Spectral accountant needs a 'wavelengths' bundle property")
-        oW = torch.empty(H, dtype=f64, device=dev) if cur.W is not None else None
+        oW = torch.empty(Hc, dtype=f64, device=dev) if cur.W is not None else None
         a = L.OpticsArgs()
         a.h = H
         a.d_records, a.d_slot_rec = records.data_ptr(), slot_rec.data_ptr()
         a.d_wavelengths = cur.W.data_ptr() if cur.W is not None else None
         a.d_out_vertices, a.d_out_directions = oV.data_ptr(), oD.data_ptr()
-        a.d_out_energy, a.d_out_parents, a.ld_out = oE.data_ptr(), oP.data_ptr(), H
+        a.d_out_energy, a.d_out_parents, a.ld_out = oE.data_ptr(), oP.data_ptr(), Hc
+        if child_off is not None:
+            a.d_slot_surf, a.d_seg, a.d_child_off = slot_surf.data_ptr(), seg.data_ptr(), child_off.data_ptr()
         a.seed, a.bounce, a.min_energy = self.seed, bounce, float(min_energy)
         draws = None
         if self.rng == 'numpy':
@@ -338,11 +347,11 @@ class TracerEngine(object):
             if scene.needs_theta_for_draws:
                 # the specular/diffuse split of these optics follows the incidence angle: a first
                 # pass of the kernel (draws unused for normals) provides it to the host
-                tn = torch.empty((3, H), dtype=f64, device=dev)
-                td = torch.empty((3, H), dtype=f64, device=dev)
+                tn = torch.empty((3, Hc), dtype=f64, device=dev)
+                td = torch.empty((3, Hc), dtype=f64, device=dev)
                 a.d_normals, a.d_dirs_in = tn.data_ptr(), td.data_ptr()
                 L.check(lib.trc_optics(scene.handle, C.byref(a), st))
-                hn, hd = tn.cpu().numpy(), td.cpu().numpy()
+                hn, hd = tn[:, :H].cpu().numpy(), td[:, :H].cpu().numpy()
                 vertical = np.sum(hd * hn, axis=0) * hn          # optics_callables.py:469-472
                 theta_in = np.arccos(np.sqrt(np.sum(vertical ** 2, axis=0)))
             draws = self._numpy_draws(scene, seg_host, H, theta_in)
@@ -364,34 +373,37 @@ class TracerEngine(object):
         self.hits_per_surface += seg[1:] - seg[:-1]
         if scene.has_accountants:
             self._account(scene, seg_host, dict(hits=oV, absorbed=absorbed, e_out=oE, normals=normals, e_in=e_in,
-                                                dirs_in=dirs_in, wavelengths=oW, attenuated=attenuated))
+                                                dirs_in=dirs_in, wavelengths=oW, attenuated=attenuated),
+                          child_off_host)
 
         n_cull = int(counters[1].item())
         del records, work
         rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
-        if n_cull and n_cull < H:
+        if n_cull and n_cull < Hc:
             # survivors first, weak rays at the back (tracer_engine.py:242-245, 268-274)
-            k2 = torch.empty(H, dtype=i32, device=dev)
-            perm = torch.empty(H, dtype=i32, device=dev)
+            k2 = torch.empty(Hc, dtype=i32, device=dev)
+            perm = torch.empty(Hc, dtype=i32, device=dev)
             count = torch.zeros(1, dtype=i64, device=dev)
-            work = torch.empty(int(lib.trc_sort_work_bytes(H, 2)), dtype=torch.uint8, device=dev)
-            L.check(lib.trc_sort_pairs(H, 2, L.dptr(cull), None, L.dptr(k2), L.dptr(perm), L.dptr(count),
+            work = torch.empty(int(lib.trc_sort_work_bytes(Hc, 2)), dtype=torch.uint8, device=dev)
+            L.check(lib.trc_sort_pairs(Hc, 2, L.dptr(cull), None, L.dptr(k2), L.dptr(perm), L.dptr(count),
                                        L.dptr(work), st))
             pV, pD = torch.empty_like(oV), torch.empty_like(oD)
             pE, pP = torch.empty_like(oE), torch.empty_like(oP)
-            L.check(lib.trc_gather_rows(H, L.dptr(perm), 3, L.dptr(oV), H, L.dptr(pV), H, None, None, st))
-            L.check(lib.trc_gather_rows(H, L.dptr(perm), 3, L.dptr(oD), H, L.dptr(pD), H, None, None, st))
-            L.check(lib.trc_gather_rows(H, L.dptr(perm), 1, L.dptr(oE), H, L.dptr(pE), H, L.dptr(oP), L.dptr(pP), st))
+            L.check(lib.trc_gather_rows(Hc, L.dptr(perm), 3, L.dptr(oV), Hc, L.dptr(pV), Hc, None, None, st))
+            L.check(lib.trc_gather_rows(Hc, L.dptr(perm), 3, L.dptr(oD), Hc, L.dptr(pD), Hc, None, None, st))
+            L.check(lib.trc_gather_rows(Hc, L.dptr(perm), 1, L.dptr(oE), Hc, L.dptr(pE), Hc, L.dptr(oP), L.dptr(pP), st))
             pW = oW.index_select(0, perm.long()) if oW is not None else None
             rec = dict(V=pV, D=pD, E=pE, P=pP, W=pW)
         rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
-        return rec, H - n_cull, H
+        return rec, Hc - n_cull, H
 
     @staticmethod
-    def _account(scene, seg, src):
+    def _account(scene, seg, src, child_off=None):
         """What Accountant.count() stores, one chunk per surface per bounce
         (optics_callables.py:1597-1790), kept in HBM until read.  ``src`` maps a
-        source name to the slot-ordered tensor the optics kernel filled."""
+        source name to the tensor the optics kernel filled: slot order, except the
+        child columns (hit points, outgoing energy) which follow ``child_off`` when
+        some surface of the scene emits two children per hit."""
         for s, orec in enumerate(scene.optics):
             if not orec['accountants']:
                 continue
@@ -400,7 +412,11 @@ class TracerEngine(object):
                 continue
             for acc, field, name in orec['accountants']:
                 t = src[name]
-                getattr(acc, field).append(_LazyRows(t[..., a:b].clone()))
+                if child_off is not None and name in ('hits', 'e_out', 'wavelengths'):
+                    lo = int(child_off[s])
+                    getattr(acc, field).append(_LazyRows(t[..., lo:lo + (b - a)].clone()))
+                else:
+                    getattr(acc, field).append(_LazyRows(t[..., a:b].clone()))
 
     @staticmethod
     def _as_bundle(rec, n=None):
