@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 5
+#define TRC_ABI_VERSION 6
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -356,6 +356,26 @@ int trc_fluxmap_rect(int64_t n, const double *d_hits, int64_t ld, const double *
                      const double *proj12 /* host, rows 0..2 of rounded inverse frame */,
                      double hx, double hy, int32_t nx, int32_t ny,
                      double *d_bins, void *stream);
+
+/* Flux-map binning in the mesh coordinates of the other geometry managers
+ * (get_fluxmap of RoundPlateGM flat_surface.py:524, ParabolicDishGM paraboloid.py:151,
+ * FiniteCylinder cylinder.py:139, SphericalGM sphere_surface.py:100, and RectPlateGM with
+ * explicit edges): local = proj12 . [hit; 1] (Surface.global_to_local, surface.py:114-126),
+ * (u, v) by `coord`, weights d_energy summed into d_bins[iu * nv + iv] (caller zeroes it)
+ * with numpy.histogram2d's rule on the explicit edge arrays d_edges_u[0..nu], d_edges_v[0..nv]
+ * (device memory; [e_i, e_i+1), last bin closed).  The host divides by the bin areas. */
+typedef enum TrcFluxCoord {
+    TRC_FLUX_XY = 0,         /* u = x, v = y */
+    TRC_FLUX_R_ATAN_XY = 1,  /* u = sqrt(x^2+y^2), v = atan2(x, y) wrapped to [0, 2pi)  (RoundPlateGM) */
+    TRC_FLUX_R_ATAN_YX = 2,  /* u = sqrt(x^2+y^2), v = atan2(y, x) wrapped             (dishes) */
+    TRC_FLUX_Z_PHI = 3,      /* u = z, v = atan2(y, x) wrapped                         (cylinders) */
+    TRC_FLUX_THETA_PHI = 4,  /* u = acos(z / param), v = atan2(y, x) wrapped; param = radius (spheres) */
+    TRC_FLUX_COORD_COUNT = 5
+} TrcFluxCoord;
+int trc_fluxmap_binned(int32_t coord, int64_t n, const double *d_hits, int64_t ld, const double *d_energy,
+                       const double *proj12, double param,
+                       const double *d_edges_u, int32_t nu, const double *d_edges_v, int32_t nv,
+                       double *d_bins, void *stream);
 
 /* Per-surface energy totals: d_totals[k] += sum of d_values[q] over the h slots
  * whose (sorted) key d_sorted_keys[q] == k.  Feeds the absorbed-energy tally that

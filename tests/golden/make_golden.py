@@ -83,12 +83,29 @@ def zoo_reference():
     return out
 
 
+def fluxmap_reference():
+    """get_fluxmap of the reference's geometry managers on fixed hit points."""
+    T = scenes.NS('tracer')
+    out = {}
+    for name, (gm, frame, res, local) in scenes.fluxmap_cases(T).items():
+        surf = T.surface.Surface(gm, T.optics_callables.Reflective(0.))
+        surf._temp_frame = frame
+        hits = np.dot(frame, np.vstack([local, np.ones(local.shape[1])]))[:3]
+        eners = np.random.RandomState(5).uniform(0.5, 1.5, size=local.shape[1])
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            flux = gm.get_fluxmap(eners.copy(), surf.global_to_local(hits)[:3], res)
+        out[name + '_hits'], out[name + '_eners'], out[name + '_flux'] = hits, eners, np.asarray(flux)
+    return out
+
+
 def main():
     ref_import.enable()
     for name in TRACE_CASES:
         data = trace_reference(name)
         np.savez_compressed(os.path.join(HERE, name + '.npz'), **data)
         print(name, 'bundles:', [data['v%d' % k].shape[1] for k in range(data['n_tree'])])
+    np.savez_compressed(os.path.join(HERE, 'fluxmaps.npz'), **fluxmap_reference())
     z = zoo_reference()
     np.savez_compressed(os.path.join(HERE, 'gm_zoo.npz'), **z)
     print('gm_zoo', {k[:-7]: int(np.isfinite(v).sum()) for k, v in z.items() if k.endswith('_params')})

@@ -288,3 +288,29 @@ def zoo_rays(T, n, seed):
     d = target - p
     d /= np.sqrt(np.sum(d ** 2, axis=0))
     return T.ray_bundle.RayBundle(vertices=p, directions=d, energy=np.ones(n))
+
+
+def fluxmap_cases(T):
+    """name -> (geometry manager, frame, resolution, (3,n) local sample points) for the
+    get_fluxmap meshes: rectangle, annulus, dish, cylinder sector, sphere."""
+    sg = T.spatial_geometry
+    rng = np.random.RandomState(77)
+    n = 20000
+    frame = np.dot(sg.translate(0.3, -1.2, 2.), np.dot(sg.rotx(0.4), sg.rotz(1.1)))
+    cases = {}
+    xy = rng.uniform(-1.1, 1.1, size=(2, n)) * np.c_[[1.5, 1.0]]
+    cases['rect'] = (T.flat_surface.RectPlateGM(3., 2.), frame, 12, np.vstack([xy, np.zeros(n)]))
+    r, a = rng.uniform(0.3, 1.3, n), rng.uniform(0, 2 * np.pi, n)
+    cases['annulus'] = (T.flat_surface.RoundPlateGM(1.2, 0.4), frame, 9, np.vstack([r * np.cos(a), r * np.sin(a), np.zeros(n)]))
+    cases['disk'] = (T.flat_surface.RoundPlateGM(1.2), frame, 10, np.vstack([r * np.cos(a), r * np.sin(a), np.zeros(n)]))
+    dish = T.paraboloid.ParabolicDishGM(2.4, 1.5)
+    rd = rng.uniform(0., 1.25, n)
+    x, y = rd * np.cos(a), rd * np.sin(a)
+    cases['dish'] = (dish, frame, 8, np.vstack([x, y, dish.a * x ** 2 + dish.b * y ** 2]))
+    cyl = T.cylinder.FiniteCylinder(2., 1.5, ang_range=[0.5, 4.])
+    ac = rng.uniform(0., 2 * np.pi, n)
+    cases['cylinder'] = (cyl, frame, 11, np.vstack([np.cos(ac), np.sin(ac), rng.uniform(-0.8, 0.8, n)]))
+    d = rng.normal(size=(3, n))
+    d /= np.sqrt(np.sum(d ** 2, axis=0))
+    cases['sphere'] = (T.sphere_surface.SphericalGM(0.7), frame, 6, 0.7 * d)
+    return cases

@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtracer_b200.so")
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 # enum TrcGeomKind
 (G_FLAT_INFINITE, G_RECT_PLATE, G_RECT_EXTRUDED, G_ROUND_PLATE, G_TRIANGLE, G_PARABOLOID,
@@ -26,6 +26,8 @@ ABI_VERSION = 5
 F_ONE_SIDED = 1
 F_UNBOUNDED = 2
 F_IAM = 4
+# enum TrcFluxCoord
+(FLUX_XY, FLUX_R_ATAN_XY, FLUX_R_ATAN_YX, FLUX_Z_PHI, FLUX_THETA_PHI) = range(5)
 BVH_MAX_LEAF = 4
 
 # numpy mirror of struct TrcSurfaceRec (384 bytes)
@@ -103,6 +105,7 @@ SIGNATURES = {
     "trc_source_buie_disk": (C.c_int, [_I64, _I64, C.c_uint64, C.POINTER(BuieTables), _DP, _DP, _DP, _D, _D,
                                        _P, _P, _P, _I64, _P]),
     "trc_fluxmap_rect": (C.c_int, [_I64, _P, _I64, _P, _DP, _D, _D, _I32, _I32, _P, _P]),
+    "trc_fluxmap_binned": (C.c_int, [_I32, _I64, _P, _I64, _P, _DP, _D, _P, _I32, _P, _I32, _P, _P]),
     "trc_segment_sums": (C.c_int, [_I64, _P, _P, _P, _P]),
 }
 

@@ -238,6 +238,67 @@ fluxmap_rect_kernel(int64_t n, const double *__restrict__ hits, int64_t ld, cons
     }
 }
 
+// numpy.histogramdd's bin of x on explicit edges e[0..n]: searchsorted(e, x, 'right') - 1,
+// values equal to the last edge fall in the last bin, anything else outside -> -1.
+__device__ __forceinline__ int edge_bin(double x, const double *e, int n) {
+    if (!(x >= e[0]) || !(x <= e[n])) return -1;
+    if (x == e[n]) return n - 1;
+    int lo = 0, hi = n;              // invariant: e[lo] <= x < e[hi]
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (e[mid] <= x) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// Flux-map binning in the surface's own mesh coordinates (the get_fluxmap methods of the
+// geometry managers): local = proj . [hit; 1], (u, v) per TrcFluxCoord, weights summed per
+// (u, v) bin on explicit edges.  Edges are staged in shared memory; bins are privatised per
+// block when they fit.
+constexpr int kFluxMaxEdges = 1000;   // static shared memory: 32 KB of bins + 2 x 8 KB of edges < 48 KB
+__global__ void __launch_bounds__(256)
+fluxmap_binned_kernel(int coord, int64_t n, const double *__restrict__ hits, int64_t ld,
+                      const double *__restrict__ energy, Proj pr, double param,
+                      const double *__restrict__ edges_u, int nu, const double *__restrict__ edges_v, int nv,
+                      double *__restrict__ bins) {
+    __shared__ double local[kFluxSmemBins];
+    __shared__ double eu[kFluxMaxEdges], ev[kFluxMaxEdges];
+    const int nb = nu * nv;
+    const bool priv = nb <= kFluxSmemBins;
+    for (int k = threadIdx.x; k <= nu; k += blockDim.x) eu[k] = edges_u[k];
+    for (int k = threadIdx.x; k <= nv; k += blockDim.x) ev[k] = edges_v[k];
+    if (priv)
+        for (int k = threadIdx.x; k < nb; k += blockDim.x) local[k] = 0.0;
+    __syncthreads();
+    const double two_pi = 2.0 * M_PI;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        V3 g = mk(hits[i], hits[ld + i], hits[2 * ld + i]);
+        double lx = pr.m[0] * g.x + pr.m[1] * g.y + pr.m[2] * g.z + pr.m[3];
+        double ly = pr.m[4] * g.x + pr.m[5] * g.y + pr.m[6] * g.z + pr.m[7];
+        double lz = pr.m[8] * g.x + pr.m[9] * g.y + pr.m[10] * g.z + pr.m[11];
+        double u, v;
+        switch (coord) {
+        case TRC_FLUX_XY: u = lx; v = ly; break;
+        case TRC_FLUX_R_ATAN_XY: u = sqrt(lx * lx + ly * ly); v = atan2(lx, ly); if (v < 0.0) v += two_pi; break;
+        case TRC_FLUX_R_ATAN_YX: u = sqrt(lx * lx + ly * ly); v = atan2(ly, lx); if (v < 0.0) v += two_pi; break;
+        case TRC_FLUX_Z_PHI: u = lz; v = atan2(ly, lx); if (v < 0.0) v += two_pi; break;
+        default: u = acos(lz / param); v = atan2(ly, lx); if (v < 0.0) v += two_pi; break;   // TRC_FLUX_THETA_PHI
+        }
+        int iu = edge_bin(u, eu, nu), iv = edge_bin(v, ev, nv);
+        if (iu < 0 || iv < 0) continue;
+        if (priv) atomicAdd(&local[iu * nv + iv], energy[i]);
+        else atomicAdd(&bins[iu * nv + iv], energy[i]);
+    }
+    if (priv) {
+        __syncthreads();
+        for (int k = threadIdx.x; k < nb; k += blockDim.x) {
+            double w = local[k];
+            if (w != 0.0) atomicAdd(&bins[k], w);
+        }
+    }
+}
+
 }  // namespace
 
 extern "C" int trc_optics(const TrcScene *sc, const TrcOpticsArgs *a, void *stream) {
@@ -299,4 +360,21 @@ extern "C" int trc_fluxmap_rect(int64_t n, const double *d_hits, int64_t ld, con
     fluxmap_rect_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(n, d_hits, ld, d_energy, pr, hx, hy, nx,
                                                                             ny, d_bins);
     return check_launch("fluxmap_rect");
+}
+
+extern "C" int trc_fluxmap_binned(int32_t coord, int64_t n, const double *d_hits, int64_t ld, const double *d_energy,
+                                  const double *proj12, double param, const double *d_edges_u, int32_t nu,
+                                  const double *d_edges_v, int32_t nv, double *d_bins, void *stream) {
+    if (coord < 0 || coord >= TRC_FLUX_COORD_COUNT || n < 0 || !proj12 || !d_edges_u || !d_edges_v || !d_bins ||
+        nu < 1 || nv < 1 || nu >= kFluxMaxEdges || nv >= kFluxMaxEdges || (n > 0 && (!d_hits || !d_energy || ld < n)))
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_fluxmap_binned: bad argument%s");
+    if (n == 0) return TRC_OK;
+    Proj pr;
+    for (int k = 0; k < 12; ++k) pr.m[k] = proj12[k];
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 2) blocks = 148 * 2;
+    fluxmap_binned_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(coord, n, d_hits, ld, d_energy, pr,
+                                                                              param, d_edges_u, nu, d_edges_v, nv,
+                                                                              d_bins);
+    return check_launch("fluxmap_binned");
 }

@@ -49,3 +49,102 @@ def bin_area(surface, resolution):
     gm = surface.get_geometry_manager()
     hx, hy = np.asarray(gm._half_dims, float).reshape(-1)
     return (2. * hx / resolution) * (2. * hy / resolution)
+
+
+# ---------------------------------------------------------------- all mesh kinds
+def _mesh(gm, resolution):
+    """(coord kind, param, u edges, v edges, bin areas (nu, nv)) of the mesh the
+    reference's ``get_fluxmap`` of this geometry manager uses."""
+    N = np
+    names = [c.__name__ for c in type(gm).__mro__]
+    if 'StraightCutRoundPlateGM' in names or 'ExtrudedRectPlateGM' in names:
+        raise NotImplementedError(f"flux map of {type(gm).__name__}: multi-region mesh not implemented")
+    if 'RectPlateGM' in names:                                        # flat_surface.py:237-251
+        xs = N.linspace(-gm._half_dims[0, 0], gm._half_dims[0, 0], resolution + 1)
+        ys = N.linspace(-gm._half_dims[1, 0], gm._half_dims[1, 0], resolution + 1)
+        dxs = N.tile(N.abs(xs[1:] - xs[:-1]), (len(ys) - 1, 1))
+        dys = N.tile(N.abs(ys[1:] - ys[:-1]), (len(xs) - 1, 1)).T
+        return L.FLUX_XY, 0., xs, ys, dxs * dys
+    if 'RoundPlateGM' in names:                                       # flat_surface.py:524-545
+        if resolution is None:
+            resolution = 40
+        angs = N.r_[0.:2. * N.pi + 2. * N.pi / resolution:2. * N.pi / resolution]
+        if gm._Ri is not None:
+            rs = gm._Ri + (gm._Re - gm._Ri) / resolution * N.arange(0, resolution + 1)
+        else:
+            rs = gm._Re / resolution * N.arange(0, resolution + 1)
+        drs = N.tile(N.abs(rs[1:] - rs[:-1]), (len(angs) - 1, 1)).T
+        ravgs = N.tile((rs[1:] + rs[:-1]) / 2., (len(angs) - 1, 1)).T
+        dangs = N.tile(N.abs(angs[1:] - angs[:-1]), (len(rs) - 1, 1))
+        return L.FLUX_R_ATAN_XY, 0., rs, angs, drs * ravgs * dangs
+    if 'ParabolicDishGM' in names:                                    # paraboloid.py:151-172
+        r_end = gm._R * (1. + 1. / resolution)
+        r = N.r_[0:r_end:gm._R / resolution]
+        ang_end = 2. * N.pi * (1 + 1. / resolution)
+        ang = N.r_[0:ang_end:2 * N.pi / resolution][:resolution + 1]
+        rs = N.tile(r, (len(ang) - 1, 1)).T
+        dangs = N.repeat(N.vstack(ang[1:] - ang[:-1]), len(r) - 1, axis=1)
+        areas = dangs * ((4. * gm.a ** 2 * rs[1:] ** 2 + 1.) ** (3. / 2.) - (4. * gm.a ** 2 * rs[:-1] ** 2 + 1.) ** (3. / 2.))
+        return L.FLUX_R_ATAN_YX, 0., r, ang, areas
+    if 'FiniteCylinder' in names:                                     # cylinder.py:139-159
+        h_bins = N.linspace(-gm._half_h, gm._half_h, resolution + 1)
+        ang_bins = N.linspace(gm._ang_range[0], gm._ang_range[1], resolution + 1)
+        dh = N.abs(N.repeat(N.vstack(h_bins[1:] - h_bins[:-1]), len(ang_bins) - 1, axis=1)).T
+        dangs = N.repeat(N.vstack(ang_bins[1:] - ang_bins[:-1]), len(h_bins) - 1, axis=1)
+        return L.FLUX_Z_PHI, 0., h_bins, ang_bins, dangs * gm._R * dh
+    if 'SphericalGM' in names:                                        # sphere_surface.py:100-115
+        ths_bin = N.linspace(0., N.pi, resolution + 1)
+        phis_bin = N.linspace(0., 2. * N.pi, resolution * 2 + 1)
+        tb = N.vstack(ths_bin)
+        dphi = phis_bin[1:] - phis_bin[:-1]
+        areas = gm._rad ** 2. * dphi * (N.cos(tb[:-1]) - N.cos(tb[1:]))
+        return L.FLUX_THETA_PHI, float(gm._rad), ths_bin, phis_bin, areas
+    raise NotImplementedError(f"{type(gm).__name__} has no get_fluxmap in the reference")
+
+
+def binned_energy(surface, hits, energy, resolution, device=None):
+    """Energy per mesh bin, (nu, nv) float64 CUDA tensor, of hit points (3,n, global
+    coordinates) weighted by ``energy`` (n,), both CUDA tensors or host arrays.
+    Returns (bins, areas)."""
+    import torch
+    lib = L.load()
+    dev = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+    coord, param, eu, ev, areas = _mesh(surface.get_geometry_manager(), resolution)
+    proj = np.round(np.linalg.inv(surface._temp_frame), decimals=9)[:3]   # surface.py:125
+    _, pp = L.host_doubles(proj, 12)
+    nu, nv = len(eu) - 1, len(ev) - 1
+    bins = torch.zeros((nu, nv), dtype=torch.float64, device=dev)
+    d_eu = torch.from_numpy(np.ascontiguousarray(eu, dtype=np.float64)).to(dev)
+    d_ev = torch.from_numpy(np.ascontiguousarray(ev, dtype=np.float64)).to(dev)
+    with torch.cuda.device(dev):
+        st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        chunks = zip(hits, energy) if isinstance(hits, (list, tuple)) else [(hits, energy)]
+        for h, e in chunks:
+            th = h if torch.is_tensor(h) else torch.from_numpy(np.ascontiguousarray(h, dtype=np.float64))
+            te = e if torch.is_tensor(e) else torch.from_numpy(np.ascontiguousarray(e, dtype=np.float64))
+            th, te = th.to(dev).contiguous(), te.to(dev).contiguous()
+            n = int(te.shape[0])
+            if n == 0:
+                continue
+            L.check(lib.trc_fluxmap_binned(coord, n, L.dptr(th), th.stride(0), L.dptr(te), pp, float(param),
+                                           L.dptr(d_eu), nu, L.dptr(d_ev), nv, L.dptr(bins), st))
+    return bins, areas
+
+
+def surface_fluxmap(surface, resolution, device=None):
+    """What ``GM.get_fluxmap(absorbed, Surface.global_to_local(hits), resolution)`` returns in
+    the reference (flat_surface.py:237,524; paraboloid.py:151; cylinder.py:139;
+    sphere_surface.py:100) -- the flattened flux array -- computed from the accountant
+    data of the last trace while it is still in HBM; only the map is copied to the host."""
+    opt = surface.get_optics_manager()
+    accs = {a.shorthand: a for a in opt.accountants}
+    if 'Location' not in accs or not any(k in accs for k in ('Absorber', 'Receptor', 'Scatterer')):
+        raise ValueError("surface_fluxmap needs a Location accountant and an energy accountant")
+    from .scene import _ACC_FIELDS
+    en = accs.get('Absorber') or accs.get('Receptor') or accs.get('Scatterer')
+    hits = [c.t if getattr(c, 't', None) is not None else np.asarray(c) for c in _chunks(accs['Location']._hits)]
+    ener = [c.t if getattr(c, 't', None) is not None else np.asarray(c)
+            for c in _chunks(getattr(en, _ACC_FIELDS[en.shorthand][0]))]
+    bins, areas = binned_energy(surface, hits, ener, resolution, device)
+    flux = bins.cpu().numpy() / areas
+    return np.hstack(flux)
