@@ -295,7 +295,7 @@ def fluxmap_cases(T):
     get_fluxmap meshes: rectangle, annulus, dish, cylinder sector, sphere."""
     sg = T.spatial_geometry
     rng = np.random.RandomState(77)
-    n = 20000
+    n = 6000
     frame = np.dot(sg.translate(0.3, -1.2, 2.), np.dot(sg.rotx(0.4), sg.rotz(1.1)))
     cases = {}
     xy = rng.uniform(-1.1, 1.1, size=(2, n)) * np.c_[[1.5, 1.0]]
