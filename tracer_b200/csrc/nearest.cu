@@ -136,7 +136,10 @@ constexpr int kChunk = 256;                   // consecutive rays owned by a war
 constexpr int kListCap = 64;                  // active list: filled while < 32, by <= 32 at a time
 constexpr int kQueueCap = 32 + 32 * 2;        // leftover + one visit (two leaf children) of every lane
 constexpr int kStack = 64;
-constexpr int kWalkSteps = 4;                  // visits per lane between two warp-level collections
+#ifndef TRC_WALK_STEPS
+#define TRC_WALK_STEPS 3
+#endif
+constexpr int kWalkSteps = TRC_WALK_STEPS;                  // visits per lane between two warp-level collections
 constexpr unsigned kNoEntry = 0xffffffffu;    // (first < 2^22 - 1, so no real entry is all ones)
 #ifndef TRC_WALK_RING
 #define TRC_WALK_RING 3
