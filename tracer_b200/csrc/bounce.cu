@@ -73,7 +73,10 @@ __device__ __forceinline__ void philox_draws(const TrcSurfaceRec *s, uint64_t se
 // recomputes the hit on the known surface (same arithmetic as that kernel, hence
 // the same bits), applies the optics and writes the child coalesced.  Replaces
 // Surface.select_rays/get_outgoing (surface.py:72-94) for every surface at once.
-__global__ void __launch_bounds__(256)
+#ifndef TRC_OPTICS_MIN_CTAS
+#define TRC_OPTICS_MIN_CTAS 4
+#endif
+__global__ void __launch_bounds__(256, TRC_OPTICS_MIN_CTAS)
 optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict__ tables, OpticsParams p) {
     int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     bool live = q < p.h;

@@ -101,14 +101,18 @@ class TracerEngine(object):
     def compile(self, force=False):
         """(Re)compile the assembly into device tables when it changed."""
         surfaces = self._asm.get_surfaces()
-        frames = np.stack([np.asarray(s._temp_frame, float) for s in surfaces]) if surfaces else np.zeros((0, 4, 4))
-        key = (tuple(id(s) for s in surfaces), frames.tobytes())
+        # Every transform of the scene graph assigns a NEW frame array to each surface
+        # (has_frame.py / reference has_frame.py:75), so object identity is a cheap change
+        # detector; the arrays are kept referenced so that their ids cannot be recycled.
+        frames = [s._temp_frame for s in surfaces]
+        key = (tuple(map(id, surfaces)), tuple(map(id, frames)))
         if force or self._scene is None or key != self._frames_key:
             if self._scene is not None:
                 self._scene.close()
             self._scene = CompiledScene(self._asm, leaf_size=self.leaf_size)
             self._hit_frac = {}
             self._frames_key = key
+            self._frames_ref = (surfaces, frames)
         return self._scene
 
     # ----------------------------------------------------------- bundles
