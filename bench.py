@@ -42,7 +42,7 @@ REPS = 3
 FLUX_RES = 50
 ALGO_BYTES_PER_RAY_HIT_KERNEL = 48      # vertex + direction read once per ray
 ALGO_BYTES_PER_HIT_HIT_KERNEL = 72      # per hit: 8 B energy read + 64 B hit record written
-TRAFFIC_BYTES_PER_RAY_NCU = 52.9        # (dram read + write) / rays of the ncu --set full capture in profiles/
+TRAFFIC_BYTES_PER_RAY_NCU = 57.8        # (dram read + write) / rays of the ncu --set full capture in profiles/
 
 
 class ClockSampler(object):

@@ -113,8 +113,8 @@ def run_gpu(args):
         host = T.ray_bundle.RayBundle(vertices=hV.numpy(), directions=hD.numpy(), energy=hE.numpy())
         e_steps = max(1, min(args.steps, 3))
         e_ms, e_b, _, _, _ = timed(host, e_steps, 1, read_back=True)
-        e2e = {"value": e_b / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 56 * n,
-               "d2h_bytes_per_step": FLUX_RES * FLUX_RES * 8, "ms_per_step": e_ms / e_steps}
+        e2e = {"value": e_b / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 56 * n * world,
+               "d2h_bytes_per_step": FLUX_RES * FLUX_RES * 8 * world, "ms_per_step": e_ms / e_steps}
         del hV, hD, hE, host
 
     cpu = None

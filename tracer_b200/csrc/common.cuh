@@ -44,7 +44,8 @@ static inline int check_launch(const char *what, int n_kernels = 1) {
 // child word: inner node -> its pair index (bit 31 clear);
 //             leaf       -> bit 31 | (surface count - 1) << 22 | first entry in the
 //                           candidate list, i.e. the low 24 bits are a queue entry
-//                           without its ray slot.
+//                           without its ray slot; a leaf of ONE surface carries the
+//                           surface index itself instead of a list position.
 // Pairs are numbered breadth-first from the root (pair 0 = the root's children).
 // root_meta (host side only): bits 28..30 = leaf surface count of the root itself
 // (0 = inner node), bits 0..27 = first candidate.

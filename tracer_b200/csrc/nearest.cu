@@ -302,7 +302,7 @@ __device__ __forceinline__ int flush_queue_body(WalkWarpShared &sh, const WalkPa
             V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
             V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
             for (int k = 0; k < cnt; ++k) {
-                int s = __ldg(&p.cand[first + k]);
+                int s = cnt == 1 ? first : __ldg(&p.cand[first + k]);     // single-surface entries hold the index
                 const TrcSurfaceRec *sr = &p.surfs[s];
                 double tk;
                 if (kFlatOnly) {              // scene of flat-family surfaces only: no quadric code, few registers
@@ -412,6 +412,9 @@ nearest_hit_walk_kernel(WalkParams p) {
     unsigned pair_a_smem = (unsigned)__cvta_generic_to_shared(&S.pair_a[0]);   // pair_b follows pair_a
     asm volatile("" : "+r"(pair_a_smem));      // keep it in a register (else recomputed from %cluster_ctaid per visit)
     const int root_count = p.has_tree ? (int)TRC_META_COUNT(p.root_meta) : 7;   // 0 inner, 1..4 leaf, 7 nothing
+    // entry payload of a tree that is a single leaf: list position, or the surface index itself for one surface
+    const unsigned root_first = root_count == 1 ? (unsigned)__ldg(&p.cand[TRC_META_INDEX(p.root_meta)])
+                                                : (unsigned)TRC_META_INDEX(p.root_meta);
     int stack[kStack];
 
     // ---- ray prefetcher: the warp streams batches of 32 rays (chunk after chunk, chunk
@@ -495,7 +498,7 @@ nearest_hit_walk_kernel(WalkParams p) {
                     // the whole tree is one leaf: its surfaces are candidates of every surviving ray
                     if (root_count != 7) {
                         if (surv) sh.queue[qn + __popc(m & lt_mask)] =
-                            ((unsigned)j << 24) | ((unsigned)(root_count - 1) << 22) | TRC_META_INDEX(p.root_meta);
+                            ((unsigned)j << 24) | ((unsigned)(root_count - 1) << 22) | root_first;
                         qn += __popc(m);
                         if (qn >= 32) qn = flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, false);
                     }
@@ -514,7 +517,8 @@ nearest_hit_walk_kernel(WalkParams p) {
                 if (p.n_unbounded) {
                     unsigned mv = __ballot_sync(full, valid);
                     for (int k = 0; k < p.n_unbounded; ++k) {
-                        if (valid) sh.queue[qn + __popc(mv & lt_mask)] = ((unsigned)j << 24) | (unsigned)(p.unbounded_first + k);
+                        const unsigned s_unb = (unsigned)__ldg(&p.cand[p.unbounded_first + k]);   // entry = surface index
+                        if (valid) sh.queue[qn + __popc(mv & lt_mask)] = ((unsigned)j << 24) | s_unb;
                         qn += __popc(mv);
                         if (qn >= 32) qn = flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, false);
                     }

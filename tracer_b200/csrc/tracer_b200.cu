@@ -151,6 +151,8 @@ extern "C" int trc_scene_set_bvh(TrcScene *sc, const TrcBvhNode *nodes, int32_t 
         auto child_word = [&](const TrcBvhNode &nd, int32_t pair_index) -> uint32_t {
             if (nd.count == 0) return (uint32_t)pair_index;                                       // inner
             if (nd.count < 0) return TRC_CHILD_LEAF;      // empty leaf: inverted box, harmless candidate 0
+            if (nd.count == 1)                  // one surface: its index itself, no candidate-list lookup
+                return TRC_CHILD_LEAF | (uint32_t)leaf_surfaces[nd.first];
             return TRC_CHILD_LEAF | ((uint32_t)(nd.count - 1) << 22) | (uint32_t)nd.first;        // leaf
         };
         std::vector<int32_t> pair_of((size_t)n_nodes, -1), order;   // inner node -> pair index
@@ -205,7 +207,7 @@ extern "C" int trc_scene_set_bvh(TrcScene *sc, const TrcBvhNode *nodes, int32_t 
         TRC_CUDA(cudaMemcpy(sc->d_pair_a, pa.data(), sizeof(TrcPairHalf) * pa.size(), cudaMemcpyHostToDevice));
         TRC_CUDA(cudaMemcpy(sc->d_pair_b, pb.data(), sizeof(TrcPairHalf) * pb.size(), cudaMemcpyHostToDevice));
     }
-    if ((int64_t)n_leaf_surfaces + n_unbounded >= (1 << 22))
+    if ((int64_t)n_leaf_surfaces + n_unbounded >= (1 << 22) || sc->n_surfaces >= (1 << 22))
         return fail(TRC_ERR_CAPACITY, "trc_scene_set_bvh: more than 2^22 candidate entries%s");
     cudaFree(sc->d_cand); sc->d_cand = nullptr;
     {
