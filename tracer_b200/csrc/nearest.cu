@@ -162,9 +162,11 @@ struct WalkWarpShared {
     double ring[kRing][6][32];                // cp.async landing zone: vertex + direction rows of 32 rays
 };
 
+// Dynamic shared memory of a CTA: the per-warp blocks, then the cached top of the tree,
+// pair_a[n_cached] followed by pair_b[n_cached] (TrcPairHalf arrays, see common.cuh) with
+// n_cached = min(n_pairs, kSmemPairs) rounded up to 8.  Only what the tree needs is
+// allocated: every KB not carved out for shared memory stays L1 for the float64 stage.
 struct WalkShared {
-    uint4 pair_a[kSmemPairs];                 // TrcPairHalf arrays (see common.cuh)
-    uint4 pair_b[kSmemPairs];
     WalkWarpShared w[kWalkWarps];
 };
 
@@ -178,6 +180,7 @@ struct WalkParams {
     int has_tree;
     int debug;                                // TRC_WALK_DEBUG experiment bits (timing only)
     int refill_at;                            // leave the walk loop to refill when <= this many lanes are active
+    int n_cached;                             // pairs cached in shared memory
     float root_lo[3], root_hi[3], qstep[3], extent[3];
     int64_t n;
     const double *vert, *dir;
@@ -402,15 +405,17 @@ nearest_hit_walk_kernel(WalkParams p) {
 
     // top of the tree -> shared memory (breadth-first order: the first kSmemPairs pairs)
     {
-        int np = min(p.n_pairs, kSmemPairs);
+        uint4 *cache = reinterpret_cast<uint4 *>(walk_smem + sizeof(WalkShared));
+        int np = min(p.n_pairs, p.n_cached);
         for (int k = threadIdx.x; k < np; k += blockDim.x) {
-            S.pair_a[k] = __ldg(p.pair_a + k);
-            S.pair_b[k] = __ldg(p.pair_b + k);
+            cache[k] = __ldg(p.pair_a + k);
+            cache[p.n_cached + k] = __ldg(p.pair_b + k);
         }
     }
     __syncthreads();
-    unsigned pair_a_smem = (unsigned)__cvta_generic_to_shared(&S.pair_a[0]);   // pair_b follows pair_a
-    asm volatile("" : "+r"(pair_a_smem));      // keep it in a register (else recomputed from %cluster_ctaid per visit)
+    unsigned pair_a_smem = (unsigned)__cvta_generic_to_shared(walk_smem + sizeof(WalkShared));
+    unsigned pair_b_smem = pair_a_smem + 16u * (unsigned)p.n_cached;             // pair_b follows pair_a
+    asm volatile("" : "+r"(pair_a_smem), "+r"(pair_b_smem));   // keep them in registers (else recomputed per visit)
     const int root_count = p.has_tree ? (int)TRC_META_COUNT(p.root_meta) : 7;   // 0 inner, 1..4 leaf, 7 nothing
     // entry payload of a tree that is a single leaf: list position, or the surface index itself for one surface
     const unsigned root_first = root_count == 1 ? (unsigned)__ldg(&p.cand[TRC_META_INDEX(p.root_meta)])
@@ -557,9 +562,9 @@ nearest_hit_walk_kernel(WalkParams p) {
                 for (int it = 0; it < kWalkSteps; ++it) {
                     if (cur >= 0 && pend0 == kNoEntry) {
                         uint4 a, b;
-                        if (kAllShared || cur < kSmemPairs) {
+                        if (kAllShared || cur < p.n_cached) {
                             a = lds128(pair_a_smem + 16u * (unsigned)cur);
-                            b = lds128(pair_a_smem + (unsigned)(sizeof(uint4) * kSmemPairs) + 16u * (unsigned)cur);
+                            b = lds128(pair_b_smem + 16u * (unsigned)cur);
                         }
                         else { a = __ldg(p.pair_a + cur); b = __ldg(p.pair_b + cur); }
                         bool h0, h1;
@@ -632,19 +637,20 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     typedef void (*WalkKernel)(WalkParams);
     static const WalkKernel kernels[4] = {nearest_hit_walk_kernel<false, false>, nearest_hit_walk_kernel<true, false>,
                                           nearest_hit_walk_kernel<false, true>, nearest_hit_walk_kernel<true, true>};
-    static int occ[4] = {0, 0, 0, 0};
-    static int g_refill_at = 24;
-    if (occ[0] == 0) {
+    static int g_refill_at = -1;
+    static bool attr_set = false;
+    if (!attr_set) {
         const char *env = getenv("TRC_WALK_REFILL_AT");      // tuning knob (0..31)
+        g_refill_at = 24;
         if (env) { int v = atoi(env); if (v >= 0 && v < 32) g_refill_at = v; }
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < 4; ++k)
             TRC_CUDA(cudaFuncSetAttribute(kernels[k], cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)sizeof(WalkShared)));
-            TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[k], kernels[k], kWalkWarps * 32,
-                                                                   sizeof(WalkShared)));
-            if (occ[k] < 1) occ[k] = 1;
-        }
+                                          (int)(sizeof(WalkShared) + 32 * kSmemPairs)));
+        attr_set = true;
     }
+    int n_cached = sc->n_pairs < kSmemPairs ? sc->n_pairs : kSmemPairs;
+    n_cached = (n_cached + 7) & ~7;
+    const size_t smem = sizeof(WalkShared) + 32 * (size_t)n_cached;
     const int variant = (sc->n_pairs <= kSmemPairs ? 1 : 0) | (sc->flat_only ? 2 : 0);
     WalkParams p;
     p.surfs = sc->d_surfaces;
@@ -654,6 +660,7 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     p.cand = sc->d_cand; p.unbounded_first = sc->n_leaf_surfaces; p.n_unbounded = sc->n_unbounded;
     p.has_tree = sc->n_nodes > 0 ? 1 : 0;
     p.refill_at = g_refill_at;
+    p.n_cached = n_cached;
     { const char *dbg = getenv("TRC_WALK_DEBUG"); p.debug = dbg ? atoi(dbg) : 0; }
     for (int k = 0; k < 3; ++k) {
         p.root_lo[k] = sc->root_lo[k]; p.root_hi[k] = sc->root_hi[k];
@@ -663,10 +670,13 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     p.chunk_counter = sc->d_chunk_counter;
     int64_t n_chunks = (n + kChunk - 1) / kChunk;
     int64_t blocks = (n_chunks + kWalkWarps - 1) / kWalkWarps;
-    int64_t resident = (int64_t)sc->num_sms * occ[variant];
+    int occ = 0;
+    TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernels[variant], kWalkWarps * 32, smem));
+    if (occ < 1) occ = 1;
+    int64_t resident = (int64_t)sc->num_sms * occ;
     if (blocks > resident) blocks = resident;
     TRC_CUDA(cudaMemsetAsync(sc->d_chunk_counter, 0, sizeof(unsigned long long), st));
-    kernels[variant]<<<(unsigned)blocks, kWalkWarps * 32, sizeof(WalkShared), st>>>(p);
+    kernels[variant]<<<(unsigned)blocks, kWalkWarps * 32, smem, st>>>(p);
     return check_launch("nearest_hit_walk");
 }
 
