@@ -125,3 +125,25 @@ def test_nsttf_walk_equals_brute_1e6():
     b1 = eng.tree[1]
     _compare(asm, b1.get_vertices(), b1.get_directions())
     torch.cuda.synchronize()
+
+
+def test_triangle_cavity_20k_faces_walk_equals_brute_multi_bounce():
+    """Config 4 at reduced scale (2e4 triangular faces: the tree no longer fits the
+    shared-memory cache, leaves come from global memory): identical per-bounce bundle
+    sizes and per-surface hit counts with and without the tree over 5 Lambertian bounces."""
+    from tracer_b200.tracer_engine import TracerEngine
+    np.random.seed(4)
+    asm, source = scenes.c4_cavity(T, n_rays=200000, n_theta=200, n_z=50)
+    bundle = source()
+    out = []
+    for accel in ('bvh', 'brute'):
+        asm.reset_all_optics()
+        eng = TracerEngine(asm, rng='philox', seed=9, device_accel=accel)
+        eng.ray_tracer(bundle, reps=5, min_energy=1e-6, tree=True)
+        out.append((eng.stats['per_bounce'], eng.hits_per_surface.cpu().numpy(),
+                    eng.absorbed_per_surface.cpu().numpy(), eng.tree[3].get_parents().copy()))
+    assert out[0][0] == out[1][0]
+    assert len(out[0][0]) == 5 and out[0][0][4][1] > 10000          # still bouncing after 5 iterations
+    assert np.array_equal(out[0][1], out[1][1])
+    np.testing.assert_allclose(out[0][2], out[1][2], rtol=1e-12)
+    assert np.array_equal(out[0][3], out[1][3])
