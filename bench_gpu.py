@@ -97,7 +97,7 @@ def run_gpu(args):
 
     # dominant kernel: trc_trace_hits of bounce 1 (nearest hit over the whole source bundle +
     # emission of the hit records), CUDA events recorded around it inside the timed region
-    ev = [(e[1], e[2], e[3].elapsed_time(e[4])) for e in kernel_events if e[0] == 0]
+    ev = [(e[1], e[2], e[3]()) for e in kernel_events if e[0] == 0]
     k_ms = float(np.mean([t for _, _, t in ev]))
     k_hits = float(np.mean([h for _, h, _ in ev]))
     algo_bytes = ALGO_BYTES_PER_RAY_HIT_KERNEL * n + ALGO_BYTES_PER_HIT_HIT_KERNEL * k_hits

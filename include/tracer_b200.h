@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 6
+#define TRC_ABI_VERSION 7
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -310,6 +310,67 @@ typedef struct TrcOpticsArgs {
     const int64_t *d_child_off;
 } TrcOpticsArgs;
 int trc_optics(const TrcScene *scene, const TrcOpticsArgs *args, void *stream);
+
+/* One whole iteration of the reference loop body (tracer_engine.py:193-274) in one call:
+ * trc_trace_hits -> hit count -> trc_order_hits -> trc_optics (Philox draws) ->
+ * trc_segment_sums + per-surface hit counts -> cull count -> survivors-first reorder when
+ * some but not all children are weak.  Same kernels, same results as the step-by-step
+ * entry points; the host sequencing just lives in C++ (two stream synchronisations:
+ * the hit count and the cull count).  Not for scenes with TRC_O_PERIODIC surfaces nor
+ * for injected draws -- those use the step-by-step entry points.
+ *
+ * Memory: two caller-owned device arenas sized with trc_bounce_keep_bytes /
+ * trc_bounce_scratch_bytes for `capacity` hits.  d_scratch may be reused or freed after
+ * the call; d_keep holds every output at the byte offsets returned in TrcBounceResult
+ * (-1 = absent), laid out for the ACTUAL hit count: rows of `ld` = hits elements.
+ * Returns TRC_ERR_CAPACITY with result->hits set when hits > capacity (nothing else is
+ * valid then; call again with larger arenas). */
+#define TRC_COL_NORMALS    1u
+#define TRC_COL_E_IN       2u
+#define TRC_COL_DIRS_IN    4u
+#define TRC_COL_ATTENUATED 8u
+typedef struct TrcBounceArgs {
+    int64_t n;                        /* rays entering the bounce */
+    const double *d_vertices;         /* (3,n) rows of stride ld */
+    const double *d_directions;
+    const double *d_energy;
+    int64_t ld;
+    const double *d_wavelengths;      /* nullable, per ray */
+    int32_t use_bvh;
+    uint32_t bounce;
+    uint64_t seed;
+    double min_energy;
+    uint32_t columns;                 /* TRC_COL_*: accountant columns to produce besides `absorbed` */
+    int32_t time_trace;               /* non-zero: bracket the nearest-hit kernel with CUDA events (ev_start/ev_stop) */
+    int64_t capacity;                 /* hits the arenas are sized for */
+    void *d_keep;
+    int64_t keep_bytes;
+    void *d_scratch;
+    int64_t scratch_bytes;
+    int64_t *h_seg;                   /* nullable HOST buffer (n_surfaces + 1): per-surface slot offsets */
+    double *d_absorbed_per_surface;   /* (n_surfaces) running totals, updated */
+    int64_t *d_hits_per_surface;      /* (n_surfaces) running totals, updated */
+} TrcBounceArgs;
+typedef struct TrcBounceResult {
+    int64_t hits;                     /* children = rays that hit something */
+    int64_t culled;                   /* children with energy <= min_energy */
+    int64_t ld;                       /* row stride of every (3,h) array below = hits */
+    /* children in slot order (surface-major, parent-minor): float64 (3,h), (3,h), (h), int64 (h), float64 (h) */
+    int64_t off_vertices, off_directions, off_energy, off_parents, off_wavelengths;
+    /* the same with survivors first and weak rays at the back; -1 when the slot order already is that order
+     * (nothing or everything culled) */
+    int64_t off_sorted_vertices, off_sorted_directions, off_sorted_energy, off_sorted_parents, off_sorted_wavelengths;
+    /* accountant columns, slot order */
+    int64_t off_absorbed, off_normals, off_e_in, off_dirs_in, off_attenuated;
+    int64_t off_seg;                  /* int64 (n_surfaces + 1): surface s owns slots [seg[s], seg[s+1]) */
+    void *ev_start, *ev_stop;         /* CUDA events around the nearest-hit kernel when time_trace; release them
+                                         with trc_event_elapsed_ms */
+} TrcBounceResult;
+int64_t trc_bounce_keep_bytes(int64_t capacity, uint32_t columns, int32_t has_wavelengths, int32_t n_surfaces);
+int64_t trc_bounce_scratch_bytes(int64_t n_rays, int64_t capacity, int32_t n_surfaces);
+int trc_bounce(const TrcScene *scene, const TrcBounceArgs *args, TrcBounceResult *result, void *stream);
+/* Waits for ev_stop, returns the elapsed time and destroys both events. */
+int trc_event_elapsed_ms(void *ev_start, void *ev_stop, float *ms);
 
 /* Row gather: out[r, j] = in[r, idx[j]] for r < n_rows (float64 rows) and
  * optionally an int64 row.  Applies the cull permutation to a child bundle

@@ -21,9 +21,11 @@ def enable():
     if not available():
         raise ImportError("reference tree not present at %s" % REFERENCE_ROOT)
     shim = os.path.join(os.path.dirname(os.path.abspath(__file__)), "refshim")
+    # appended, not prepended: the reference has top-level packages named like ours
+    # (tests/), and child processes spawned by the tests inherit sys.path
     for p in (shim, REFERENCE_ROOT):
         if p not in sys.path:
-            sys.path.insert(0, p)
+            sys.path.append(p)
     if not hasattr(builtins, "xrange"):
         builtins.xrange = range
     import tracer  # noqa: F401

@@ -182,3 +182,35 @@ def test_philox_energy_conservation_and_statistics():
     # reflected ray deviates by twice the normal error: std of each transverse component ~ 2 sigma
     sx, sy = dirs[0].std(), dirs[1].std()
     assert abs(sx - 2 * sig) < 0.02 * 2 * sig and abs(sy - 2 * sig) < 0.02 * 2 * sig
+
+
+@pytest.mark.parametrize('name', ['c3_nsttf', 'c5_cavity_spectral', 'c6_optics_zoo'])
+def test_fused_bounce_equals_step_by_step(name):
+    """trc_bounce (the library sequences the bounce) and the step-by-step entry points driven
+    from Python give identical trees, tallies and accountant data (Philox draws)."""
+    builder, kw, seed, reps, min_energy = TRACE_CASES[name]
+    out = []
+    for fused in (True, False):
+        np.random.seed(seed)
+        asm, source = builder(T, **kw)
+        bundle = source()
+        eng = _engine(asm, rng='philox', seed=21)
+        eng.fused_bounce = fused
+        eng.ray_tracer(bundle, reps=reps, min_energy=min_energy, tree=True)
+        tree = [(eng.tree[k].get_vertices(), eng.tree[k].get_directions(), eng.tree[k].get_energy(),
+                 eng.tree[k].get_parents()) for k in range(1, eng.tree.num_bunds())]
+        accs = [s.get_optics_manager().get_all_hits() for s in asm.get_surfaces()
+                if hasattr(s.get_optics_manager(), 'get_all_hits')]
+        out.append((eng.stats['per_bounce'], tree, accs, eng.hits_per_surface.cpu().numpy(),
+                    eng.absorbed_per_surface.cpu().numpy()))
+    assert out[0][0] == out[1][0]
+    assert len(out[0][1]) == len(out[1][1]) >= 2
+    for a, b in zip(out[0][1], out[1][1]):
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
+    for a, b in zip(out[0][2], out[1][2]):
+        assert len(a) == len(b)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
+    assert np.array_equal(out[0][3], out[1][3])
+    np.testing.assert_allclose(out[0][4], out[1][4], rtol=1e-12)

@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtracer_b200.so")
 
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 # enum TrcGeomKind
 (G_FLAT_INFINITE, G_RECT_PLATE, G_RECT_EXTRUDED, G_ROUND_PLATE, G_TRIANGLE, G_PARABOLOID,
@@ -65,6 +65,30 @@ class OpticsArgs(C.Structure):
     ]
 
 
+COL_NORMALS, COL_E_IN, COL_DIRS_IN, COL_ATTENUATED = 1, 2, 4, 8
+
+
+class BounceArgs(C.Structure):
+    _fields_ = [
+        ("n", C.c_int64), ("d_vertices", C.c_void_p), ("d_directions", C.c_void_p), ("d_energy", C.c_void_p),
+        ("ld", C.c_int64), ("d_wavelengths", C.c_void_p),
+        ("use_bvh", C.c_int32), ("bounce", C.c_uint32), ("seed", C.c_uint64), ("min_energy", C.c_double),
+        ("columns", C.c_uint32), ("time_trace", C.c_int32), ("capacity", C.c_int64),
+        ("d_keep", C.c_void_p), ("keep_bytes", C.c_int64), ("d_scratch", C.c_void_p), ("scratch_bytes", C.c_int64),
+        ("h_seg", C.c_void_p), ("d_absorbed_per_surface", C.c_void_p), ("d_hits_per_surface", C.c_void_p),
+    ]
+
+
+class BounceResult(C.Structure):
+    _fields_ = [(k, C.c_int64) for k in (
+        "hits", "culled", "ld",
+        "off_vertices", "off_directions", "off_energy", "off_parents", "off_wavelengths",
+        "off_sorted_vertices", "off_sorted_directions", "off_sorted_energy", "off_sorted_parents",
+        "off_sorted_wavelengths",
+        "off_absorbed", "off_normals", "off_e_in", "off_dirs_in", "off_attenuated", "off_seg")] + [
+        ("ev_start", C.c_void_p), ("ev_stop", C.c_void_p)]
+
+
 class BuieTables(C.Structure):
     _fields_ = [
         ("n_seg", C.c_int32), ("has_aureole", C.c_int32),
@@ -105,6 +129,10 @@ SIGNATURES = {
     "trc_source_buie_disk": (C.c_int, [_I64, _I64, C.c_uint64, C.POINTER(BuieTables), _DP, _DP, _DP, _D, _D,
                                        _P, _P, _P, _I64, _P]),
     "trc_fluxmap_rect": (C.c_int, [_I64, _P, _I64, _P, _DP, _D, _D, _I32, _I32, _P, _P]),
+    "trc_bounce_keep_bytes": (_I64, [_I64, C.c_uint32, _I32, _I32]),
+    "trc_bounce_scratch_bytes": (_I64, [_I64, _I64, _I32]),
+    "trc_bounce": (C.c_int, [_P, _P, _P, _P]),
+    "trc_event_elapsed_ms": (C.c_int, [_P, _P, C.POINTER(C.c_float)]),
     "trc_fluxmap_binned": (C.c_int, [_I32, _I64, _P, _I64, _P, _DP, _D, _P, _I32, _P, _I32, _P, _P]),
     "trc_segment_sums": (C.c_int, [_I64, _P, _P, _P, _P]),
 }

@@ -94,6 +94,7 @@ class TracerEngine(object):
         self._frames_key = None
         self._hit_frac = {}       # bounce -> hit fraction of the previous trace (sizes the hit list)
         self._copy_stream = None
+        self.fused_bounce = True   # sequence a bounce inside the library (trc_bounce) when the configuration allows
         self.kernel_events = None  # set to a list to collect (bounce, n, H, start, end) CUDA events of trc_trace_hits
         self.stats = {}
 
@@ -256,6 +257,8 @@ class TracerEngine(object):
         -> trc_optics -> trc_segment_sums [-> cull sort + gathers].  Two host
         syncs: the hit count (sizes the child bundle) and the cull count."""
         import torch
+        if self.fused_bounce and self.rng == 'philox' and not scene.has_split and cur.slices is None:
+            return self._bounce_fused(scene, cur, bounce, min_energy, use_bvh)
         lib = L.load()
         dev = self.device
         st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
@@ -299,7 +302,7 @@ class TracerEngine(object):
                 ev1.record()
             H = int(counters[0].item())
             if self.kernel_events is not None:
-                self.kernel_events.append((bounce, n, H, ev0, ev1))
+                self.kernel_events.append((bounce, n, H, lambda a=ev0, b=ev1: a.elapsed_time(b)))
             if H <= cap:
                 break
             cap = H
@@ -400,6 +403,83 @@ class TracerEngine(object):
             rec = dict(V=pV, D=pD, E=pE, P=pP, W=pW)
         rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
         return rec, Hc - n_cull, H
+
+    def _bounce_fused(self, scene, cur, bounce, min_energy, use_bvh):
+        """The same iteration through trc_bounce: the launch sequence, the two count read-backs
+        and the buffer carving happen inside the library; Python allocates two arenas and wraps
+        views.  Philox draws, no two-children optics, bundle resident in HBM."""
+        import torch
+        lib = L.load()
+        dev = self.device
+        st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        n, S = cur.n, scene.num_surfaces
+        want = scene.accountant_sources
+        if 'wavelengths' in want and cur.W is None:
+            raise ValueError("Spectral accountant needs a 'wavelengths' bundle property")
+        cols = ((L.COL_NORMALS if 'normals' in want else 0) | (L.COL_E_IN if 'e_in' in want else 0) |
+                (L.COL_DIRS_IN if 'dirs_in' in want else 0) | (L.COL_ATTENUATED if 'attenuated' in want else 0))
+        has_w = 1 if cur.W is not None else 0
+        frac = self._hit_frac.get(bounce)
+        cap = n if frac is None or n <= (1 << 20) else min(n, int(1.3 * frac * n) + 65536)
+        h_seg = np.zeros(S + 1, dtype=np.int64) if scene.has_accountants else None
+        a, r = L.BounceArgs(), L.BounceResult()
+        a.n, a.ld = n, cur.V.stride(0)
+        a.d_vertices, a.d_directions, a.d_energy = cur.V.data_ptr(), cur.D.data_ptr(), cur.E.data_ptr()
+        a.d_wavelengths = cur.W.data_ptr() if has_w else None
+        a.use_bvh, a.bounce, a.seed, a.min_energy = (1 if use_bvh else 0), bounce, self.seed, float(min_energy)
+        a.columns, a.time_trace = cols, (1 if self.kernel_events is not None else 0)
+        a.h_seg = h_seg.ctypes.data if h_seg is not None else None
+        a.d_absorbed_per_surface = self.absorbed_per_surface.data_ptr()
+        a.d_hits_per_surface = self.hits_per_surface.data_ptr()
+        while True:
+            keep = torch.empty(int(lib.trc_bounce_keep_bytes(cap, cols, has_w, S)), dtype=torch.uint8, device=dev)
+            scratch = torch.empty(int(lib.trc_bounce_scratch_bytes(n, cap, S)), dtype=torch.uint8, device=dev)
+            a.capacity = cap
+            a.d_keep, a.keep_bytes = keep.data_ptr(), keep.numel()
+            a.d_scratch, a.scratch_bytes = scratch.data_ptr(), scratch.numel()
+            rc = lib.trc_bounce(scene.handle, C.byref(a), C.byref(r), st)
+            if a.time_trace and r.ev_start:
+                ev = (r.ev_start, r.ev_stop)
+
+                def elapsed(ev=ev):
+                    ms = C.c_float(0.)
+                    L.check(lib.trc_event_elapsed_ms(ev[0], ev[1], C.byref(ms)))
+                    return ms.value
+                if rc == 0:
+                    self.kernel_events.append((bounce, n, int(r.hits), elapsed))
+                else:
+                    elapsed()              # releases the events of the attempt that overflowed
+            if rc == -4 and r.hits > cap:      # TRC_ERR_CAPACITY: more hits than the arenas hold
+                cap = int(r.hits)
+                continue
+            L.check(rc)
+            break
+        H, n_cull = int(r.hits), int(r.culled)
+        self._hit_frac[bounce] = H / float(n) if n else 0.
+        if H == 0:
+            return None, 0, 0
+        f64, i64 = torch.float64, torch.int64
+
+        def view(off, dtype, rows):
+            if off < 0:
+                return None
+            nbytes = 8 * H * (rows or 1)
+            t = keep[off:off + nbytes].view(dtype)
+            return t.view(rows, H) if rows else t
+        oV, oD = view(r.off_vertices, f64, 3), view(r.off_directions, f64, 3)
+        oE, oP, oW = view(r.off_energy, f64, 0), view(r.off_parents, i64, 0), view(r.off_wavelengths, f64, 0)
+        if scene.has_accountants:
+            self._account(scene, h_seg, dict(
+                hits=oV, absorbed=view(r.off_absorbed, f64, 0), e_out=oE, normals=view(r.off_normals, f64, 3),
+                e_in=view(r.off_e_in, f64, 0), dirs_in=view(r.off_dirs_in, f64, 3), wavelengths=oW,
+                attenuated=view(r.off_attenuated, f64, 0)))
+        rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
+        if r.off_sorted_vertices >= 0:
+            rec = dict(V=view(r.off_sorted_vertices, f64, 3), D=view(r.off_sorted_directions, f64, 3),
+                       E=view(r.off_sorted_energy, f64, 0), P=view(r.off_sorted_parents, i64, 0),
+                       W=view(r.off_sorted_wavelengths, f64, 0))
+        rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
+        return rec, H - n_cull, H
 
     @staticmethod
     def _account(scene, seg, src, child_off=None):
