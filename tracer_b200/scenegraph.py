@@ -139,12 +139,20 @@ class BoundarySphere(BoundaryShape):
         return self._radius ** 2 >= ((bund_vertices - self._temp_loc[:3]) ** 2).sum(axis=1)
 
 
+# Bumped by every structural change made through the API of any Assembly / AssembledObject;
+# get_surfaces() results are cached against it (a heliostat field is ~650 objects and the
+# engine asks for the surface list at the start of every trace).
+_STRUCTURE_VERSION = [0]
+
+
 class Assembly(HasFrame):
     """Tree of objects and sub-assemblies (assembly.py:7-151)."""
 
     def __init__(self, objects=None, subassemblies=None, location=None, rotation=None):
         self._objects = [] if objects is None else objects
         self._assemblies = [] if subassemblies is None else subassemblies
+        self._surfaces_cache = None
+        _STRUCTURE_VERSION[0] += 1
         HasFrame.__init__(self, location, rotation)
 
     # -- queries
@@ -164,19 +172,26 @@ class Assembly(HasFrame):
         return out
 
     def get_surfaces(self):
-        return [s for obj in self.get_objects() for s in obj.get_surfaces()]
+        key = (_STRUCTURE_VERSION[0], len(self._objects), len(self._assemblies))
+        cache = self.__dict__.get('_surfaces_cache')
+        if cache is None or cache[0] != key:
+            cache = (key, [s for obj in self.get_objects() for s in obj.get_surfaces()])
+            self._surfaces_cache = cache
+        return list(cache[1])
 
     def global_to_local(self, points):
         return self._to_local(points)
 
     # -- mutation
     def add_object(self, object, transform=None):
+        _STRUCTURE_VERSION[0] += 1
         self._objects.append(object)
         if transform is not None:
             object.set_transform(transform)
         self.transform_children()
 
     def add_assembly(self, assembly, transform=None):
+        _STRUCTURE_VERSION[0] += 1
         self._assemblies.append(assembly)
         if transform is not None:
             assembly.set_transform(transform)
@@ -209,6 +224,7 @@ class AssembledObject(Assembly):
     """A rigid group of surfaces (+ optional boundary boxes) (object.py:8-79)."""
 
     def __init__(self, surfs=None, bounds=None, location=None, rotation=None, transform=None):
+        _STRUCTURE_VERSION[0] += 1
         self.surfaces = [] if surfs is None else surfs
         self.boundaries = [] if bounds is None else bounds
         if not hasattr(self.surfaces, '__len__'):
@@ -235,6 +251,7 @@ class AssembledObject(Assembly):
         return self.boundaries
 
     def add_surface(self, surface):
+        _STRUCTURE_VERSION[0] += 1
         self.surfaces.append(surface)
         self.transform_children()
 
