@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 7
+#define TRC_ABI_VERSION 8
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -407,6 +407,20 @@ int trc_source_buie_disk(int64_t n, int64_t first_ray, uint64_t seed,
                          const TrcBuieTables *tables,
                          const double *center3, const double *rot_dir9, const double *rot_pos9,
                          double radius, double ray_energy,
+                         double *d_vertices, double *d_directions, double *d_energy,
+                         int64_t ld, void *stream);
+/* Rectangular source planes: rect_bundle / oblique_solar_rect_bundle (sources.py:241-302) and
+ * rect_buie_sunshape (:466-515).  Start points uniform in [-half_x, half_x] x [-half_y, half_y]
+ * of the source plane's local frame (rot_pos), directions as the disk variants. */
+int trc_source_pillbox_rect(int64_t n, int64_t first_ray, uint64_t seed,
+                            const double *center3, const double *rot_dir9, const double *rot_pos9,
+                            double half_x, double half_y, double ang_range, double ray_energy,
+                            double *d_vertices, double *d_directions, double *d_energy,
+                            int64_t ld, void *stream);
+int trc_source_buie_rect(int64_t n, int64_t first_ray, uint64_t seed,
+                         const TrcBuieTables *tables,
+                         const double *center3, const double *rot_dir9, const double *rot_pos9,
+                         double half_x, double half_y, double ray_energy,
                          double *d_vertices, double *d_directions, double *d_energy,
                          int64_t ld, void *stream);
 

@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtracer_b200.so")
 
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 # enum TrcGeomKind
 (G_FLAT_INFINITE, G_RECT_PLATE, G_RECT_EXTRUDED, G_ROUND_PLATE, G_TRIANGLE, G_PARABOLOID,
@@ -126,6 +126,9 @@ SIGNATURES = {
     "trc_gather_rows": (C.c_int, [_I64, _P, _I32, _P, _I64, _P, _I64, _P, _P, _P]),
     "trc_source_pillbox_disk": (C.c_int, [_I64, _I64, C.c_uint64, _DP, _DP, _DP, _D, _D, _D, _D, _D, _D,
                                           _P, _P, _P, _I64, _P]),
+    "trc_source_pillbox_rect": (C.c_int, [_I64, _I64, C.c_uint64, _DP, _DP, _DP, _D, _D, _D, _D, _P, _P, _P, _I64, _P]),
+    "trc_source_buie_rect": (C.c_int, [_I64, _I64, C.c_uint64, C.POINTER(BuieTables), _DP, _DP, _DP, _D, _D, _D,
+                                       _P, _P, _P, _I64, _P]),
     "trc_source_buie_disk": (C.c_int, [_I64, _I64, C.c_uint64, C.POINTER(BuieTables), _DP, _DP, _DP, _D, _D,
                                        _P, _P, _P, _I64, _P]),
     "trc_fluxmap_rect": (C.c_int, [_I64, _P, _I64, _P, _DP, _D, _D, _I32, _I32, _P, _P]),

@@ -30,6 +30,7 @@ __device__ __forceinline__ void store_ray(double *vert, double *dir, double *ene
 __global__ void __launch_bounds__(256)
 pillbox_disk_kernel(int64_t n, int64_t first, uint64_t seed, Vec3h center, Mat3 rot_dir, Mat3 rot_pos,
                     double r_in, double r_out, double ang0, double ang1, double ang_range, double ray_energy,
+                    double rect_hx, double rect_hy,
                     double *__restrict__ vert, double *__restrict__ dir, double *__restrict__ energy, int64_t ld) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -39,9 +40,14 @@ pillbox_disk_kernel(int64_t n, int64_t first, uint64_t seed, Vec3h center, Mat3 
     uniform2(seed, id, 0x50494c4cu, 1, u2, u3);   // position draws
     V3 a = pillbox_direction(2.0 * M_PI * u0, u1, ang_range);
     V3 d = mat_apply(rot_dir, a);
-    double th = ang0 + (ang1 - ang0) * u3;
-    double rs = sqrt(r_in * r_in + u2 * (r_out * r_out - r_in * r_in));
-    V3 pl = mk(rs * cos(th), rs * sin(th), 0.0);
+    V3 pl;
+    if (rect_hx > 0.0) {          // rectangular source (rect_bundle, sources.py:241-264): uniform in +-hx, +-hy
+        pl = mk((2.0 * u2 - 1.0) * rect_hx, (2.0 * u3 - 1.0) * rect_hy, 0.0);
+    } else {
+        double th = ang0 + (ang1 - ang0) * u3;
+        double rs = sqrt(r_in * r_in + u2 * (r_out * r_out - r_in * r_in));
+        pl = mk(rs * cos(th), rs * sin(th), 0.0);
+    }
     V3 p = mat_apply(rot_pos, pl);
     store_ray(vert, dir, energy, ld, i, mk(p.x + center.v[0], p.y + center.v[1], p.z + center.v[2]), d, ray_energy);
 }
@@ -49,6 +55,7 @@ pillbox_disk_kernel(int64_t n, int64_t first, uint64_t seed, Vec3h center, Mat3 
 __global__ void __launch_bounds__(256)
 buie_disk_kernel(int64_t n, int64_t first, uint64_t seed, const TrcBuieTables *__restrict__ tb,
                  Vec3h center, Mat3 rot_dir, Mat3 rot_pos, double radius, double ray_energy,
+                 double rect_hx, double rect_hy,
                  double *__restrict__ vert, double *__restrict__ dir, double *__restrict__ energy, int64_t ld) {
     __shared__ double s_cdf[212], s_th[212], s_w[212];
     const int nseg = tb->n_seg;
@@ -60,9 +67,14 @@ buie_disk_kernel(int64_t n, int64_t first, uint64_t seed, const TrcBuieTables *_
     double xv1, uphi, rth, uxi;
     uniform2(seed, id, 0x42554945u, 0, xv1, uphi);   // start position
     uniform2(seed, id, 0x42554945u, 1, rth, uxi);    // polar / azimuth of the direction
-    double phiv = 2.0 * M_PI * uphi;
-    double rs = radius * sqrt(xv1);
-    V3 p = mat_apply(rot_pos, mk(rs * cos(phiv), rs * sin(phiv), 0.0));
+    V3 p;
+    if (rect_hx > 0.0) {          // rect_buie_sunshape (sources.py:487-488): width * (u - 0.5), height * (u' - 0.5)
+        p = mat_apply(rot_pos, mk((2.0 * xv1 - 1.0) * rect_hx, (2.0 * uphi - 1.0) * rect_hy, 0.0));
+    } else {
+        double phiv = 2.0 * M_PI * uphi;
+        double rs = radius * sqrt(xv1);
+        p = mat_apply(rot_pos, mk(rs * cos(phiv), rs * sin(phiv), 0.0));
+    }
     double theta = 0.0;
     if (rth >= s_cdf[nseg]) {
         if (tb->has_aureole) {
@@ -95,30 +107,49 @@ thread_local BuieCache g_buie = {{}, nullptr, false};
 
 }  // namespace
 
-extern "C" int trc_source_pillbox_disk(int64_t n, int64_t first_ray, uint64_t seed, const double *center3,
-                                       const double *rot_dir9, const double *rot_pos9, double radius_in,
-                                       double radius, double ang0, double ang1, double ang_range,
-                                       double ray_energy, double *d_vert, double *d_dir, double *d_energy,
-                                       int64_t ld, void *stream) {
+static int source_pillbox(int64_t n, int64_t first_ray, uint64_t seed, const double *center3,
+                          const double *rot_dir9, const double *rot_pos9, double radius_in,
+                          double radius, double ang0, double ang1, double ang_range,
+                          double ray_energy, double rect_hx, double rect_hy, double *d_vert, double *d_dir,
+                          double *d_energy, int64_t ld, void *stream) {
     if (n < 0 || !center3 || !rot_dir9 || !rot_pos9 || (n > 0 && (!d_vert || !d_dir || !d_energy)) || ld < n)
-        return fail(TRC_ERR_BAD_ARGUMENT, "trc_source_pillbox_disk: bad argument%s");
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_source_pillbox: bad argument%s");
     if (n == 0) return TRC_OK;
     Vec3h c; Mat3 rd, rp;
     for (int k = 0; k < 3; ++k) c.v[k] = center3[k];
     for (int k = 0; k < 9; ++k) { rd.m[k] = rot_dir9[k]; rp.m[k] = rot_pos9[k]; }
     pillbox_disk_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-        n, first_ray, seed, c, rd, rp, radius_in, radius, ang0, ang1, ang_range, ray_energy, d_vert, d_dir,
-        d_energy, ld);
-    return check_launch("source_pillbox_disk");
+        n, first_ray, seed, c, rd, rp, radius_in, radius, ang0, ang1, ang_range, ray_energy, rect_hx, rect_hy,
+        d_vert, d_dir, d_energy, ld);
+    return check_launch("source_pillbox");
 }
 
-extern "C" int trc_source_buie_disk(int64_t n, int64_t first_ray, uint64_t seed, const TrcBuieTables *tables,
-                                    const double *center3, const double *rot_dir9, const double *rot_pos9,
-                                    double radius, double ray_energy, double *d_vert, double *d_dir,
-                                    double *d_energy, int64_t ld, void *stream) {
+extern "C" int trc_source_pillbox_disk(int64_t n, int64_t first_ray, uint64_t seed, const double *center3,
+                                       const double *rot_dir9, const double *rot_pos9, double radius_in,
+                                       double radius, double ang0, double ang1, double ang_range,
+                                       double ray_energy, double *d_vert, double *d_dir, double *d_energy,
+                                       int64_t ld, void *stream) {
+    return source_pillbox(n, first_ray, seed, center3, rot_dir9, rot_pos9, radius_in, radius, ang0, ang1, ang_range,
+                          ray_energy, 0.0, 0.0, d_vert, d_dir, d_energy, ld, stream);
+}
+
+extern "C" int trc_source_pillbox_rect(int64_t n, int64_t first_ray, uint64_t seed, const double *center3,
+                                       const double *rot_dir9, const double *rot_pos9, double half_x,
+                                       double half_y, double ang_range, double ray_energy, double *d_vert,
+                                       double *d_dir, double *d_energy, int64_t ld, void *stream) {
+    if (!(half_x > 0.0) || !(half_y > 0.0))
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_source_pillbox_rect: half extents must be positive%s");
+    return source_pillbox(n, first_ray, seed, center3, rot_dir9, rot_pos9, 0.0, 0.0, 0.0, 0.0, ang_range, ray_energy,
+                          half_x, half_y, d_vert, d_dir, d_energy, ld, stream);
+}
+
+static int source_buie(int64_t n, int64_t first_ray, uint64_t seed, const TrcBuieTables *tables,
+                       const double *center3, const double *rot_dir9, const double *rot_pos9,
+                       double radius, double ray_energy, double rect_hx, double rect_hy, double *d_vert,
+                       double *d_dir, double *d_energy, int64_t ld, void *stream) {
     if (n < 0 || !tables || tables->n_seg < 1 || tables->n_seg > 210 || !center3 || !rot_dir9 || !rot_pos9 ||
         (n > 0 && (!d_vert || !d_dir || !d_energy)) || ld < n)
-        return fail(TRC_ERR_BAD_ARGUMENT, "trc_source_buie_disk: bad argument%s");
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_source_buie: bad argument%s");
     if (n == 0) return TRC_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (!g_buie.valid || memcmp(&g_buie.host, tables, sizeof(TrcBuieTables)) != 0) {
@@ -134,6 +165,25 @@ extern "C" int trc_source_buie_disk(int64_t n, int64_t first_ray, uint64_t seed,
     for (int k = 0; k < 3; ++k) c.v[k] = center3[k];
     for (int k = 0; k < 9; ++k) { rd.m[k] = rot_dir9[k]; rp.m[k] = rot_pos9[k]; }
     buie_disk_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, first_ray, seed, g_buie.dev, c, rd, rp, radius,
-                                                                  ray_energy, d_vert, d_dir, d_energy, ld);
-    return check_launch("source_buie_disk");
+                                                                  ray_energy, rect_hx, rect_hy, d_vert, d_dir,
+                                                                  d_energy, ld);
+    return check_launch("source_buie");
+}
+
+extern "C" int trc_source_buie_disk(int64_t n, int64_t first_ray, uint64_t seed, const TrcBuieTables *tables,
+                                    const double *center3, const double *rot_dir9, const double *rot_pos9,
+                                    double radius, double ray_energy, double *d_vert, double *d_dir,
+                                    double *d_energy, int64_t ld, void *stream) {
+    return source_buie(n, first_ray, seed, tables, center3, rot_dir9, rot_pos9, radius, ray_energy, 0.0, 0.0, d_vert,
+                       d_dir, d_energy, ld, stream);
+}
+
+extern "C" int trc_source_buie_rect(int64_t n, int64_t first_ray, uint64_t seed, const TrcBuieTables *tables,
+                                    const double *center3, const double *rot_dir9, const double *rot_pos9,
+                                    double half_x, double half_y, double ray_energy, double *d_vert,
+                                    double *d_dir, double *d_energy, int64_t ld, void *stream) {
+    if (!(half_x > 0.0) || !(half_y > 0.0))
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_source_buie_rect: half extents must be positive%s");
+    return source_buie(n, first_ray, seed, tables, center3, rot_dir9, rot_pos9, 0.0, ray_energy, half_x, half_y,
+                       d_vert, d_dir, d_energy, ld, stream);
 }

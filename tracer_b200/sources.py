@@ -96,6 +96,32 @@ def rect_bundle(num_rays, center, direction, x, y, ang_range, flux=None, procs=1
     return b
 
 
+def oblique_solar_rect_bundle(num_rays, center, source_direction, rays_direction, x, y, ang_range, flux=None,
+                              procs=1, wavelength=None, ref_index=None):
+    """Rectangular pillbox source whose rays leave along ``rays_direction`` while the source
+    plane faces ``source_direction`` (sources.py:268-302)."""
+    a = pillbox_sunshape_directions(num_rays, ang_range)
+    directions = _apply(rotation_to_z(rays_direction), a)
+    xs = np.random.uniform(low=-x / 2., high=x / 2., size=num_rays)
+    ys = np.random.uniform(low=-y / 2., high=y / 2., size=num_rays)
+    if (np.asarray(source_direction) == np.array([0, 0, -1])).all():
+        xs, ys = ys, xs
+    vertices_local = np.vstack((ys, xs, np.zeros(num_rays)))
+    vertices_global = np.dot(rotation_to_z(source_direction), vertices_local)
+    kw = {}
+    if wavelength is not None:
+        kw['wavelengths'] = np.ones(num_rays) * wavelength
+    if ref_index is not None:
+        kw['ref_index'] = np.ones(num_rays) * ref_index
+    rayb = RayBundle(vertices=vertices_global + center, directions=directions, **kw)
+    if flux is not None:
+        cosangle = 2. * np.arcsin(0.5 * np.sqrt(np.sum((np.asarray(rays_direction) - np.asarray(source_direction)) ** 2)))
+        rayb.set_energy(x * y / num_rays * flux * np.ones(num_rays) * np.cos(cosangle))
+    else:
+        rayb.set_energy(np.ones(num_rays) / float(num_rays) / procs)
+    return rayb
+
+
 def buie_tables(CSR, pre_process_CSR=True):
     """Piecewise-linear solar-disk CDF + aureole constants of Buie et al. (2003)
     as used by Buie_directions_sampling (sources.py:330-362).  Returns a dict."""
@@ -244,4 +270,78 @@ def buie_sunshape_device(num_rays, center, direction, radius, CSR, flux=None, pr
         st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         L.check(lib.trc_source_buie_disk(num_rays, first_ray, seed, C.byref(t), c, rd, rp, float(radius), float(e),
                                          L.dptr(V), L.dptr(D), L.dptr(E), num_rays, st))
+    return _wrap(V, D, E)
+
+
+def _rect_local_half_extents(x, y, plane_normal):
+    """Half extents along the local axes of the source plane: the reference lays the points
+    out as (ys, xs, 0) and swaps the two when the plane faces straight down
+    (sources.py:251-257, 278-284)."""
+    if (np.asarray(plane_normal) == np.array([0, 0, -1])).all():
+        return x / 2., y / 2.
+    return y / 2., x / 2.
+
+
+def rect_bundle_device(num_rays, center, direction, x, y, ang_range, flux=None, procs=1, seed=0, first_ray=0,
+                       total_rays=None, device=None, rays_direction=None):
+    """``rect_bundle`` (and, with ``rays_direction``, ``oblique_solar_rect_bundle``) generated in
+    HBM by the Philox pillbox kernel."""
+    import torch
+    from . import _lib as L
+    lib = L.load()
+    direction = np.asarray(direction, float)
+    if rays_direction is None:
+        rays_direction = direction
+    rays_direction = np.asarray(rays_direction, float)
+    total = total_rays or num_rays
+    if flux is not None:
+        cosangle = 2. * np.arcsin(0.5 * np.sqrt(np.sum((rays_direction - direction) ** 2)))
+        e = x * y / total * flux * np.cos(cosangle)
+    else:
+        e = 1. / float(total) / procs
+    hx, hy = _rect_local_half_extents(x, y, direction)
+    dev, V, D, E = _device_bundle_buffers(num_rays, device)
+    _, c = L.host_doubles(center, 3)
+    _, rd = L.host_doubles(rotation_to_z(rays_direction), 9)
+    _, rp = L.host_doubles(rotation_to_z(direction), 9)
+    with torch.cuda.device(dev):
+        st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        L.check(lib.trc_source_pillbox_rect(num_rays, first_ray, seed, c, rd, rp, float(hx), float(hy),
+                                            float(ang_range), float(e), L.dptr(V), L.dptr(D), L.dptr(E), num_rays, st))
+    return _wrap(V, D, E)
+
+
+def oblique_solar_rect_bundle_device(num_rays, center, source_direction, rays_direction, x, y, ang_range, flux=None,
+                                     procs=1, seed=0, first_ray=0, total_rays=None, device=None):
+    return rect_bundle_device(num_rays, center, source_direction, x, y, ang_range, flux=flux, procs=procs, seed=seed,
+                              first_ray=first_ray, total_rays=total_rays, device=device,
+                              rays_direction=rays_direction)
+
+
+def rect_buie_sunshape_device(num_rays, center, direction, width, height, CSR, flux=None, pre_process_CSR=True,
+                              rays_direction=None, seed=0, first_ray=0, total_rays=None, device=None):
+    """``rect_buie_sunshape`` (sources.py:466-515) generated in HBM by the Philox Buie kernel."""
+    import torch
+    from . import _lib as L
+    lib = L.load()
+    direction = np.asarray(direction, float)
+    if rays_direction is None:
+        rays_direction = direction
+    tb = buie_tables(CSR, pre_process_CSR)
+    t = L.BuieTables()
+    t.n_seg, t.has_aureole = BUIE_SEGMENTS, int(tb['CSR'] > 0.)
+    for k in range(BUIE_SEGMENTS + 1):
+        t.cdf[k], t.theta[k], t.w[k] = tb['cdf'][k], tb['theta'][k], tb['w'][k]
+    t.sum_integ_dni, t.gamma, t.kappa = tb['sum_integ'], tb['gamma'], tb['kappa']
+    t.theta_dni, t.theta_tot = THETA_DNI, THETA_TOT
+    ang = 2. * np.sin(np.sqrt(np.sum((rays_direction - direction) ** 2)) / 2.)
+    e = flux * width * height / (total_rays or num_rays) * np.cos(ang)
+    dev, V, D, E = _device_bundle_buffers(num_rays, device)
+    _, c = L.host_doubles(center, 3)
+    _, rd = L.host_doubles(rotation_to_z(rays_direction), 9)
+    _, rp = L.host_doubles(rotation_to_z(direction), 9)
+    with torch.cuda.device(dev):
+        st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        L.check(lib.trc_source_buie_rect(num_rays, first_ray, seed, C.byref(t), c, rd, rp, float(width) / 2.,
+                                         float(height) / 2., float(e), L.dptr(V), L.dptr(D), L.dptr(E), num_rays, st))
     return _wrap(V, D, E)
