@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 8
+#define TRC_ABI_VERSION 9
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -93,7 +93,11 @@ typedef enum TrcOpticsKind {
     TRC_O_PERIODIC = 11,          /* PeriodicBoundary :690-723: op: period.  TWO children per hit: a
                                      zero-energy stub at the hit, then the live ray moved by period * normal
                                      (block A, block B of the surface's segment; see TrcOpticsArgs) */
-    TRC_O_KIND_COUNT = 12
+    TRC_O_FRESNEL_CONDUCTOR = 12, /* FresnelConductorHomogenous :1523-1558 with optics.fresnel_conductor /
+                                     fresnel_to_attenuating (optics.py:41-81): op: n1; table = wavelengths[n],
+                                     n2[n], k2[n] (complex index of the conductor, linear in wavelength);
+                                     specular, E' = E (R_p + R_s) / 2; NaN outside the table's range */
+    TRC_O_KIND_COUNT = 13
 } TrcOpticsKind;
 
 /* Surface flag bits. */

@@ -72,7 +72,8 @@ _KNOWN = ('Transparent', 'OneSidedReflective', 'Reflective', 'OneSidedRealReflec
           'LambertianSpecular_directional_axisymmetric_piecewise',
           'Lambertian_directional_axisymmetric_piecewise_spectral', 'Reflective_spectral',
           'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM', 'LambertianAbsorbant',
-          'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise', 'PeriodicBoundary')
+          'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise', 'PeriodicBoundary',
+          'FresnelConductorHomogenous')
 
 
 def _iam(base, d, normals, energy):
@@ -130,6 +131,16 @@ def apply_optics(opt, d, normals, energy, wavelengths, up, v_parent=None, hit=No
             e_att = e0 * N.exp(-base.a_c * path)
             apply_optics.attenuations = energy - e_att
             out = dirs, e_att * (1. - base._absorptivity)
+        elif name == 'FresnelConductorHomogenous':                  # :1536-1558, optics.py:41-81
+            m2 = base._material.m(wavelengths)
+            th1 = N.arccos(N.abs((normals * d).sum(axis=0)))
+            n1 = base._n1
+            b = (m2.real ** 2 - m2.imag ** 2 - (n1 * N.sin(th1)) ** 2)
+            a = N.sqrt(b ** 2 + 4. * (m2.real * m2.imag) ** 2)
+            p, q = N.sqrt(0.5 * (a + b)), N.sqrt(0.5 * (a - b))
+            R_s = ((n1 * N.cos(th1) - p) ** 2 + q ** 2) / ((n1 * N.cos(th1) + p) ** 2 + q ** 2)
+            R_p = ((p - n1 * N.sin(th1) * N.tan(th1)) ** 2 + q ** 2) / ((p + n1 * N.sin(th1) * N.tan(th1)) ** 2 + q ** 2) * R_s
+            out = reflections(d, normals), energy * ((R_p + R_s) / 2.)
         elif name == 'Transparent':                                 # optics_callables.py:106-113
             out = d.copy(), energy.copy()
         elif name in ('Reflective', 'OneSidedReflective'):          # :130-140, :201-212

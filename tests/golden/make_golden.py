@@ -31,6 +31,7 @@ TRACE_CASES = {
     'c5_cavity_spectral': (scenes.c5_cavity, dict(n_rays=1500, spectral=True), 18, 6, 1e-10),
     'c6_optics_zoo': (scenes.c6_optics_zoo, dict(n_rays=3000), 19, 5, 1e-10),
     'c7_periodic_cell': (scenes.c7_periodic_cell, dict(n_rays=2000), 20, 6, 1e-10),
+    'c8_fresnel_conductor': (scenes.c8_fresnel_conductor, dict(n_rays=2000), 21, 6, 1e-10),
 }
 ZOO_RAYS = 4000
 ZOO_SEED = 99

@@ -234,6 +234,40 @@ def c7_periodic_cell(T, n_rays=2000):
     return asm, source
 
 
+def _optical_constants(T):
+    """The reference keeps its materials outside the tracer package."""
+    if T.pkg == 'tracer':
+        return importlib.import_module('ray_trace_utils.optical_constants')
+    return T.optical_constants
+
+
+def c8_fresnel_conductor(T, n_rays=2000):
+    """A metal plate (Fresnel reflectance from tabulated n, k) under a spectrally selective
+    mirror lid; the source bundle carries one wavelength per ray."""
+    oc = T.optics_callables
+    here = os.path.dirname(os.path.abspath(__file__))
+    metal = _optical_constants(T).OpticalMaterialFromFile(os.path.join(here, 'golden', 'conductor_nk.csv'))
+    wls = np.linspace(3e-7, 2.5e-6, 9)
+    lid_abs = np.linspace(0.05, 0.6, 9)
+    objs = [
+        T.object.AssembledObject(surfs=[T.surface.Surface(
+            T.flat_surface.RectPlateGM(4., 4.), oc.FresnelConductorHomogenousReceiver(1., metal))]),
+        T.object.AssembledObject(
+            surfs=[T.surface.Surface(T.flat_surface.RoundPlateGM(3.), oc.Reflective_spectralReceiver(lid_abs, wls))],
+            transform=np.dot(T.spatial_geometry.translate(0., 0., 1.), T.spatial_geometry.rotx(np.pi))),
+    ]
+    asm = T.assembly.Assembly(objects=objs)
+
+    def source():
+        direction = np.r_[0.5, 0.2, -1.]
+        direction = direction / np.sqrt(np.sum(direction ** 2))
+        b = T.sources.disk_bundle(n_rays, np.c_[[-0.4, -0.15, 0.9]], direction, 0.8, 0.3, flux=1000.)
+        wl = np.random.uniform(3.2e-7, 2.4e-6, size=n_rays)
+        return T.ray_bundle.RayBundle(vertices=b.get_vertices(), directions=b.get_directions(),
+                                      energy=b.get_energy(), wavelengths=wl)
+    return asm, source
+
+
 def gm_zoo(T):
     """name -> (geometry manager factory, frame) covering every supported GM kind."""
     sg = T.spatial_geometry

@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtracer_b200.so")
 
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 # enum TrcGeomKind
 (G_FLAT_INFINITE, G_RECT_PLATE, G_RECT_EXTRUDED, G_ROUND_PLATE, G_TRIANGLE, G_PARABOLOID,
@@ -22,7 +22,8 @@ ABI_VERSION = 8
 # enum TrcOpticsKind
 (O_TRANSPARENT, O_REFLECTIVE, O_REAL_REFLECTIVE, O_LAMBERTIAN, O_LAMBERTIAN_SPECULAR,
  O_LAMB_DIRECTIONAL, O_REFLECTIVE_SPECTRAL, O_LAMBSPEC_DIRECTIONAL,
- O_LAMB_DIRECTIONAL_SPECTRAL, O_LAMB_PIECEWISE_SPEC, O_LAMBERTIAN_ABSORBANT, O_PERIODIC) = range(12)
+ O_LAMB_DIRECTIONAL_SPECTRAL, O_LAMB_PIECEWISE_SPEC, O_LAMBERTIAN_ABSORBANT, O_PERIODIC,
+ O_FRESNEL_CONDUCTOR) = range(13)
 F_ONE_SIDED = 1
 F_UNBOUNDED = 2
 F_IAM = 4

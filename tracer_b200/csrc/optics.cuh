@@ -187,6 +187,27 @@ __device__ __forceinline__ OpticsOut apply_optics(const TrcSurfaceRec *s, const 
         o.attenuated = e_in - e_att;
         o.energy = e_att * (1.0 - op[0]); break;
     }
+    case TRC_O_FRESNEL_CONDUCTOR: {
+        // optics.py:41-81 (Modest ch. 2: perfect dielectric n1 -> absorbing medium m2 = n2 + i k2)
+        const double *xp = tables + s->table_off;
+        int nw = s->table_len;
+        o.dir = reflect(d, n);
+        if (!(wavelength >= xp[0]) || !(wavelength <= xp[nw - 1])) {     // optical_material.check_valid: NaN
+            o.energy = e_in * nan(""); break;
+        }
+        double n2 = interp1(wavelength, xp, xp + nw, nw), k2 = interp1(wavelength, xp, xp + 2 * nw, nw);
+        double n1 = op[0];
+        double th1 = acos(fabs(n.x * d.x + n.y * d.y + n.z * d.z));
+        double s1 = n1 * sin(th1), c1 = n1 * cos(th1);
+        double b = n2 * n2 - k2 * k2 - s1 * s1;
+        double nk = n2 * k2;
+        double a = sqrt(b * b + 4.0 * (nk * nk));
+        double pp = sqrt(0.5 * (a + b)), qq = sqrt(0.5 * (a - b));
+        double rs = ((c1 - pp) * (c1 - pp) + qq * qq) / ((c1 + pp) * (c1 + pp) + qq * qq);
+        double st = s1 * tan(th1);
+        double rp = ((pp - st) * (pp - st) + qq * qq) / ((pp + st) * (pp + st) + qq * qq) * rs;
+        o.energy = e_in * ((rp + rs) / 2.0); break;
+    }
     case TRC_O_REFLECTIVE_SPECTRAL: {
         const double *xp = tables + s->table_off;
         const double *fp = xp + s->table_len;

@@ -175,6 +175,16 @@ class LambertianAbsorbant(Lambertian):
             self.a_c = np.array(attenuation_coefficient)
 
 
+class FresnelConductorHomogenous(_OpticsDescription):
+    """Specular reflection off a conductor seen from a perfect dielectric of index ``n1``;
+    reflectance from the Fresnel equations with the complex index of ``material`` at the
+    ray's wavelength (:1523-1558)."""
+
+    def __init__(self, n1, material):
+        self._n1 = n1
+        self._material = material
+
+
 class PeriodicBoundary(_OpticsDescription):
     """Periodic boundary condition (:690-723): every hit leaves a zero-energy stub at the
     hit point and re-emits the ray, unchanged, from hit + period * normal."""
@@ -186,7 +196,7 @@ class PeriodicBoundary(_OpticsDescription):
 perfect_mirror = Reflective(0)
 
 _BASE_OPTICS = {c.__name__: c for c in (
-    PeriodicBoundary,
+    PeriodicBoundary, FresnelConductorHomogenous,
     Lambertian_IAM, RealReflective_IAM, LambertianSpecular_IAM, LambertianAbsorbant,
     Lambertian_piecewise_Specular_directional_axisymmetric_piecewise,
     Transparent, Reflective, Lambertian, Reflective_spectral, OneSidedReflective, RealReflective,
@@ -199,7 +209,7 @@ _BASE_OPTICS = {c.__name__: c for c in (
 _UNSUPPORTED = (
     'Refractive', 'RefractiveHomogenous', 'RefractiveAbsorbantHomogenous', 'RefractiveScattering',
     'RefractiveScatteringHomogenous', 'Scattering', 'ScatteringPeriodicBoundary',
-    'Absorbant', 'FresnelConductorHomogenous', 'SemiLambertian', 'BiFacial', 'Reflective_IAM',
+    'Absorbant', 'SemiLambertian', 'BiFacial', 'Reflective_IAM',
     'Lambertian_directional_axisymmetric_piecewise_Polychromatic')
 
 

@@ -166,6 +166,25 @@ _ACC_FIELDS = {  # shorthand -> (list attribute on the accountant, source)
 }
 
 
+def _material_table(material):
+    """(wavelengths, [n..., k...]) knots of a material's complex index.  Materials that
+    interpolate a table (scipy interp1d in the reference, OpticalMaterialTable here) give
+    their own knots, so the kernel reproduces them exactly; analytic models are sampled."""
+    if hasattr(material, 'lambdas') and hasattr(material, 'n') and hasattr(material, 'k'):
+        wl, n, k = material.lambdas, material.n, material.k
+    elif hasattr(material, 'm_func') and hasattr(material.m_func, 'x'):
+        wl = np.asarray(material.m_func.x, float)
+        m = np.asarray(material.m_func.y)
+        n, k = m.real, m.imag
+    else:
+        wl = np.linspace(material.l_min, material.l_max, 4096)
+        m = np.asarray(material.m(wl))
+        n, k = m.real, m.imag
+    wl = np.asarray(wl, float)
+    order = np.argsort(wl)
+    return wl[order], np.concatenate([np.asarray(n, float)[order], np.asarray(k, float)[order]])
+
+
 def _optics_record(opt):
     """-> dict(okind, op, flags, table, accountants, draws)"""
     accountants = []
@@ -190,7 +209,8 @@ def _optics_record(opt):
              'LambertianSpecular_directional_axisymmetric_piecewise',
              'Lambertian_directional_axisymmetric_piecewise_spectral', 'Reflective_spectral',
              'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM', 'LambertianAbsorbant',
-             'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise', 'PeriodicBoundary')
+             'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise', 'PeriodicBoundary',
+             'FresnelConductorHomogenous')
     for cls in type(base).__mro__:
         if cls.__name__ in known:
             break
@@ -229,6 +249,11 @@ def _optics_record(opt):
             rec['okind'] = L.O_LAMBERTIAN_ABSORBANT
             rec['op'][:4] = [_scalar(base._absorptivity, 'absorptivity'), _scalar(base._ang_range, 'ang_range'),
                              float(a_c[0]), _scalar(base._scaling, 'scaling')]
+        elif name == 'FresnelConductorHomogenous':
+            rec['okind'] = L.O_FRESNEL_CONDUCTOR
+            rec['op'][0] = _scalar(base._n1, 'n1')
+            rec['table'] = _material_table(base._material)
+            rec['needs_wavelengths'] = True
         elif name == 'PeriodicBoundary':
             if accountants:
                 raise NotImplementedError(
