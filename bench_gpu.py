@@ -58,10 +58,10 @@ def run_gpu(args):
             return bins.cpu().numpy(), eng.stats["ray_bounces"]
         return bins, eng.stats["ray_bounces"]
 
-    def timed(bundle, steps, warmup, read_back=False, sample_clocks=False, after_warmup=None):
-        sampler = ClockSampler(local) if sample_clocks else None
-        if sampler:
-            sampler.start()          # nvidia-smi needs ~1 s to start: begin before the warm-up
+    sampler = ClockSampler(local)
+    sampler.start()                  # nvidia-smi needs ~1 s to start; it samples both timed regions (value and e2e)
+
+    def timed(bundle, steps, warmup, read_back=False, after_warmup=None):
         for _ in range(warmup):
             step(bundle, read_back)
         if after_warmup:
@@ -76,20 +76,18 @@ def run_gpu(args):
             bounces += b
         e1.record()
         barrier()
-        clocks = sampler.stop() if sampler else None
         ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
         tot = torch.tensor([float(bounces)], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
             dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-        return float(ms.item()), float(tot.item()), lib.trc_launch_count() - l0, clocks, last
+        return float(ms.item()), float(tot.item()), lib.trc_launch_count() - l0, last
 
     kernel_events = []
 
     def start_events():
         eng.kernel_events = kernel_events
-    ms, bounces, launches, clocks, bins = timed(src, args.steps, args.warmup, sample_clocks=True,
-                                                after_warmup=start_events)
+    ms, bounces, launches, bins = timed(src, args.steps, args.warmup, after_warmup=start_events)
     eng.kernel_events = None
     value = bounces / (ms * 1e-3)
     per_bounce = eng.stats["per_bounce"]
@@ -112,11 +110,12 @@ def run_gpu(args):
         hV.copy_(V); hD.copy_(D); hE.copy_(src._props["energy"].pieces[0])
         host = T.ray_bundle.RayBundle(vertices=hV.numpy(), directions=hD.numpy(), energy=hE.numpy())
         e_steps = max(1, min(args.steps, 3))
-        e_ms, e_b, _, _, _ = timed(host, e_steps, 1, read_back=True)
+        e_ms, e_b, _, _ = timed(host, e_steps, 1, read_back=True)
         e2e = {"value": e_b / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 56 * n * world,
                "d2h_bytes_per_step": FLUX_RES * FLUX_RES * 8 * world, "ms_per_step": e_ms / e_steps}
         del hV, hD, hE, host
 
+    clocks = sampler.stop()
     cpu = None
     if rank == 0 and not args.no_cpu:
         procs = max(1, min(os.cpu_count() or 1, 64))
