@@ -214,3 +214,31 @@ def test_fused_bounce_equals_step_by_step(name):
             assert np.array_equal(x, y)
     assert np.array_equal(out[0][3], out[1][3])
     np.testing.assert_allclose(out[0][4], out[1][4], rtol=1e-12)
+
+
+@pytest.mark.parametrize('fused', [True, False])
+def test_hit_list_overflow_is_retried(fused):
+    """The hit list is sized from the hit fraction of the previous trace; a bundle that hits
+    far more than the last one overflows it and the bounce is re-run with the exact size."""
+    n = (1 << 21) + 1234
+    asm, _ = scenes.c1_flat_mirror(T, n_rays=10)
+    centre, down = np.c_[[0., 0., 4.]], np.r_[0., 0., -1.]
+    sparse = T.sources.disk_bundle_device(n, centre, down, 12., 4.65e-3, flux=1000., seed=1)    # ~3 % hit the mirror
+    dense = T.sources.disk_bundle_device(n, centre, down, 0.8, 4.65e-3, flux=1000., seed=2)     # all hit
+    eng = _engine(asm, rng='philox', seed=3)
+    eng.fused_bounce = fused
+    eng.ray_tracer(sparse, reps=3, min_energy=1e-10, tree=False)
+    assert eng.stats['per_bounce'][0][1] < 0.1 * n
+    asm.reset_all_optics()
+    eng.ray_tracer(dense, reps=3, min_energy=1e-10, tree=True)
+    got = (eng.stats['per_bounce'], eng.hits_per_surface.cpu().numpy(), eng.absorbed_per_surface.cpu().numpy(),
+           eng.tree[1].get_parents().copy())
+    assert got[0][0][1] == n
+    asm.reset_all_optics()
+    fresh = _engine(asm, rng='philox', seed=3)
+    fresh.fused_bounce = fused
+    fresh.ray_tracer(dense, reps=3, min_energy=1e-10, tree=True)
+    assert got[0] == fresh.stats['per_bounce']
+    assert np.array_equal(got[1], fresh.hits_per_surface.cpu().numpy())
+    np.testing.assert_allclose(got[2], fresh.absorbed_per_surface.cpu().numpy(), rtol=1e-12)
+    assert np.array_equal(got[3], fresh.tree[1].get_parents())
