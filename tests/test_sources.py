@@ -22,7 +22,7 @@ def _ref():
 
 
 @pytest.mark.skipif(not HAVE_REF, reason='reference tree only exists in the build container')
-@pytest.mark.parametrize('case', ['disk', 'rect', 'rect_down', 'oblique', 'buie', 'rect_buie'])
+@pytest.mark.parametrize('case', ['disk', 'rect', 'rect_down', 'oblique', 'buie', 'rect_buie', 'vf_frustum', 'vf_cylinder'])
 def test_host_sources_equal_live_reference(case):
     R = _ref()
     d = np.r_[0.3, -0.2, -1.]
@@ -44,6 +44,10 @@ def test_host_sources_equal_live_reference(case):
             return s.oblique_solar_rect_bundle(500, c, d, rd, 3., 2., 0.01, flux=900., wavelength=5e-7)
         if case == 'buie':
             return s.buie_sunshape(500, c, d, 2.5, 0.05, flux=900.)
+        if case == 'vf_frustum':
+            return s.vf_frustum_bundle(300, 0.5, 1.2, 0.8, c, d, rays_in=False, angular_span=[0.3, 4.])
+        if case == 'vf_cylinder':
+            return s.vf_cylinder_bundle(300, 0.7, 1.5, c, d, flux=3., rays_in=True)
         return s.rect_buie_sunshape(500, c, d, 3., 2., 0.05, flux=900., rays_direction=rd)
     a, b = make(T), make(R)
     assert np.array_equal(a.get_vertices(), b.get_vertices())

@@ -1,0 +1,95 @@
+"""View-factor driver.  CPU: the online statistics of RTVF.test_precision
+against the reference's own method (its class body is executed from
+emissive_losses/view_factors_3D.py when the reference tree is present -- the module itself
+cannot be imported: it pulls in the Coin3D renderer).  GPU: a closed cylinder traced to
+convergence reproduces the analytic view factors, the summation rule and reciprocity."""
+import os
+
+import numpy as np
+import pytest
+
+from tests import scenes
+
+T = scenes.NS('tracer_b200')
+REF_FILE = '/root/reference/emissive_losses/view_factors_3D.py'
+
+
+def _reference_rtvf_class():
+    src = open(REF_FILE).read().replace('\r', '')
+    start = src.index('class RTVF()')
+    end = src.index('class FONaR_RTVF')
+    ns = {'N': np}
+    exec(compile(src[start:end], REF_FILE, 'exec'), ns)
+    return ns['RTVF']
+
+
+@pytest.mark.skipif(not os.path.isfile(REF_FILE), reason='reference tree only exists in the build container')
+@pytest.mark.parametrize('option', ['absolute', 'relative'])
+def test_precision_statistics_equal_reference(option):
+    from tracer_b200.view_factors import RTVF
+    Ref = _reference_rtvf_class()
+    rng = np.random.RandomState(1)
+    n = 4
+    areas = np.array([1., 2., 0.5, 3.])
+    true = rng.uniform(0.05, 0.4, size=(n, n))
+    true /= true.sum(axis=1, keepdims=True)
+    mine, ref = RTVF(1000, 0.02, option), Ref(1000, 0.02, option)
+    for obj in (mine, ref):
+        obj.areas = areas
+        obj.VF = np.zeros((n, n))
+        obj.VF_esperance, obj.Qsum = np.zeros((n, n)), np.zeros((n, n))
+        obj.stdev_VF = np.zeros((n, n))
+        obj.p = np.zeros(n)
+    for it in range(6):
+        counts = np.array([1000., 1000., 0. if it % 2 else 1000., 1000.])
+        sample = true + rng.normal(scale=0.02, size=(n, n))
+        for obj in (mine, ref):
+            obj.ray_counts = counts.copy()
+            obj.p = obj.p + counts
+            obj.VF = sample.copy()
+            with np.errstate(all='ignore'):
+                obj.test_precision()
+        np.testing.assert_array_equal(mine.VF_esperance, ref.VF_esperance)
+        np.testing.assert_array_equal(mine.stdev_VF, ref.stdev_VF)
+        np.testing.assert_array_equal(mine.VF_reciprocity, ref.VF_reciprocity)
+        np.testing.assert_array_equal(mine.progress, ref.progress)
+    assert not np.isnan(mine.VF_esperance).any()
+
+
+@pytest.mark.gpu
+def test_closed_cylinder_view_factors():
+    from tracer_b200.view_factors import AssemblyRTVF
+    oc, sg = T.optics_callables, T.spatial_geometry
+    r, h = 1., 2.
+    objs = [
+        T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RoundPlateGM(r), oc.LambertianReceiver(1.))]),
+        T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RoundPlateGM(r), oc.LambertianReceiver(1.))],
+                                 transform=np.dot(sg.translate(0., 0., h), sg.rotx(np.pi))),
+        T.object.AssembledObject(surfs=[T.surface.Surface(T.cylinder.FiniteCylinder(2. * r, h), oc.LambertianReceiver(1.))],
+                                 transform=sg.translate(0., 0., h / 2.)),
+    ]
+    asm = T.assembly.Assembly(objects=objs)
+    areas = [np.pi * r ** 2, np.pi * r ** 2, 2. * np.pi * r * h]
+    state = {'k': 0}
+
+    def emit(i, n):
+        state['k'] += 1
+        if i == 0:
+            return T.sources.disk_bundle_device(n, np.c_[[0., 0., 0.]], np.r_[0., 0., 1.], r, np.pi / 2., seed=state['k'])
+        if i == 1:
+            return T.sources.disk_bundle_device(n, np.c_[[0., 0., h]], np.r_[0., 0., -1.], r, np.pi / 2., seed=state['k'])
+        np.random.seed(state['k'])
+        return T.sources.vf_cylinder_bundle(n, r, h, np.c_[[0., 0., h / 2.]], np.r_[0., 0., 1.], rays_in=True)
+    vf = AssemblyRTVF(asm, [0, 1, 2], areas, emit, num_rays=40000, precision=0.01, seed=5)
+    F, sd = vf.run(max_passes=40)
+    R = r / h
+    X = 1. + (1. + R ** 2) / R ** 2
+    f01 = 0.5 * (X - np.sqrt(X ** 2 - 4.))
+    f20 = areas[0] * (1. - f01) / areas[2]
+    exact = np.array([[0., f01, 1. - f01], [f01, 0., 1. - f01], [f20, f20, 1. - 2. * f20]])
+    assert vf.passes >= 2 and not vf.progress.any()
+    assert np.abs(F - exact).max() < 0.01, (F, exact)
+    assert np.abs(F.sum(axis=1) - 1.).max() < 0.01               # summation rule (closed cavity)
+    AF = F * np.vstack(areas)
+    assert np.abs(AF - AF.T).max() < 0.02                        # reciprocity
+    assert (sd <= 0.005 + 1e-12).all()

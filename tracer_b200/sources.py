@@ -122,6 +122,63 @@ def oblique_solar_rect_bundle(num_rays, center, source_direction, rays_direction
     return rayb
 
 
+def vf_frustum_bundle(num_rays, r0, r1, depth, center, direction, flux=None, rays_in=True,
+                      angular_span=[0., 2. * np.pi], angular_range=np.pi / 2.):
+    """Lambertian emission from the lateral surface of a conical frustum, for view-factor
+    ray traces (sources.py:644-714).  Draw order: directions, radius variate, azimuth."""
+    from .spatial_geometry import roty, rotz
+    r0, r1, depth, num_rays = float(r0), float(r1), float(depth), int(num_rays)
+    dir_flat = pillbox_sunshape_directions(num_rays, angular_range)
+    c = (r1 - r0) / depth
+    R = np.random.uniform(size=num_rays)
+    rs = np.sqrt((r1 ** 2. - r0 ** 2.) * R + r0 ** 2.)
+    zs = (rs - r0) / ((r1 - r0) / depth)
+    phi_s = np.random.uniform(low=angular_span[0], high=angular_span[1], size=num_rays)
+    xs, ys = rs * np.cos(phi_s), rs * np.sin(phi_s)
+    yrot = roty(-np.pi / 2. + np.arctan(c))[:3, :3]
+    local_unit = np.zeros(np.shape(dir_flat))
+    for t in range(num_rays):
+        local_unit[:, t] = np.dot(rotz(phi_s[t])[:3, :3], np.dot(yrot, dir_flat[:, t]))
+    if rays_in == False:  # noqa: E712 (reference spelling)
+        local_unit = -1. * local_unit
+    perp_rot = rotation_to_z(direction)
+    vertices_global = np.dot(perp_rot, np.vstack((xs, ys, zs)))
+    directions = np.dot(perp_rot, local_unit)
+    if flux is None:
+        energy = np.ones(num_rays) / float(num_rays)
+    else:
+        area = (angular_span[1] - angular_span[0]) * (r1 + r0) / 2. * np.sqrt(abs(r1 - r0) ** 2. + depth ** 2.)
+        energy = np.ones(num_rays) * flux * area / float(num_rays)
+    return RayBundle(vertices=vertices_global + center, directions=directions, energy=energy)
+
+
+def vf_cylinder_bundle(num_rays, rc, lc, center, direction, flux=None, rays_in=True,
+                       angular_span=[0., 2. * np.pi], ang_range=np.pi / 2.):
+    """Lambertian emission from the lateral surface of a cylinder (sources.py:716-767).
+    Draw order: height, azimuth, directions."""
+    from .spatial_geometry import roty, rotz
+    rc, lc, num_rays = float(rc), float(lc), int(num_rays)
+    zs = lc * np.random.uniform(size=num_rays) - lc / 2.
+    phi_s = np.random.uniform(low=angular_span[0], high=angular_span[1], size=num_rays)
+    xs, ys = rc * np.cos(phi_s), rc * np.sin(phi_s)
+    dir_flat = pillbox_sunshape_directions(num_rays, ang_range)
+    yrot = roty(-np.pi / 2.)[:3, :3]
+    local_unit = np.zeros(np.shape(dir_flat))
+    for t in range(num_rays):
+        local_unit[:, t] = np.dot(np.dot(rotz(phi_s[t])[:3, :3], yrot), dir_flat[:, t])
+    if rays_in == False:  # noqa: E712
+        local_unit = -local_unit
+    perp_rot = rotation_to_z(direction)
+    vertices_global = np.dot(perp_rot, np.vstack((xs, ys, zs)))
+    directions = np.dot(perp_rot, local_unit)
+    if flux is None:
+        energy = np.ones(num_rays) / float(num_rays)
+    else:
+        area = rc * (angular_span[1] - angular_span[0]) * lc
+        energy = np.ones(num_rays) * flux * area / float(num_rays)
+    return RayBundle(vertices=vertices_global + center, directions=directions, energy=energy)
+
+
 def buie_tables(CSR, pre_process_CSR=True):
     """Piecewise-linear solar-disk CDF + aureole constants of Buie et al. (2003)
     as used by Buie_directions_sampling (sources.py:330-362).  Returns a dict."""
