@@ -93,3 +93,47 @@ def test_closed_cylinder_view_factors():
     AF = F * np.vstack(areas)
     assert np.abs(AF - AF.T).max() < 0.02                        # reciprocity
     assert (sd <= 0.005 + 1e-12).all()
+
+
+def _cylinder_vf(r=1., h=2.):
+    R = r / h
+    X = 1. + (1. + R ** 2) / R ** 2
+    f01 = 0.5 * (X - np.sqrt(X ** 2 - 4.))
+    a = np.array([np.pi * r ** 2, np.pi * r ** 2, 2. * np.pi * r * h])
+    f20 = a[0] * (1. - f01) / a[2]
+    return np.array([[0., f01, 1. - f01], [f01, 0., 1. - f01], [f20, f20, 1. - 2. * f20]]), a
+
+
+def test_radiosity_energy_balance():
+    from tracer_b200.emissive_losses import radiosity_RTVF
+    VF, areas = _cylinder_vf()
+    eps = np.array([1., 0.8, 0.6])
+    AA, bb, J, E, T, q, Q = radiosity_RTVF(VF, areas, eps, T=np.array([300., 900., 1100.]))
+    assert abs(Q.sum()) < 1e-9 * np.abs(Q).max()          # closed cavity: net exchange sums to zero
+    assert Q[0] < 0 and Q[2] > 0                          # the cold black end receives, the hot wall gives
+    # isothermal cavity: no net exchange anywhere
+    Q_iso = radiosity_RTVF(VF, areas, eps, T=np.array([700., 700., 700.]))[-1]
+    assert np.abs(Q_iso).max() < 1e-9 * 5.6677e-8 * 700. ** 4
+
+
+@pytest.mark.skipif(not os.path.isfile(REF_FILE), reason='reference tree only exists in the build container')
+def test_radiosity_equals_reference():
+    import importlib.util
+    from tracer_b200.emissive_losses import radiosity_RTVF
+    spec = importlib.util.spec_from_file_location('_ref_emissive_losses', os.path.join(os.path.dirname(REF_FILE), 'emissive_losses.py'))
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    VF, areas = _cylinder_vf()
+    eps = np.array([1., 0.8, 0.6])
+    cases = [dict(T=np.array([300., 900., 1100.])),
+             dict(T=np.array([np.nan, np.nan, np.nan]), inc_radiation=np.array([2e4, 5e4, 1e4])),
+             dict(T=np.array([300., np.nan, np.nan]), inc_radiation=np.array([np.nan, 5e4, 1e4]))]
+    for k_case, kw in enumerate(cases):
+        F = VF * 0.9 if k_case == 1 else VF              # all-flux rows on a closed cavity are singular: open it
+        mine = radiosity_RTVF(F, areas, eps, **{k: v.copy() for k, v in kw.items()})
+        theirs = ref.radiosity_RTVF(F, areas, eps, **{k: v.copy() for k, v in kw.items()})
+        for a, b in zip(mine, theirs):
+            np.testing.assert_array_equal(a, b)
+    for bad in (dict(), dict(T=np.array([300., np.nan, 1.]), inc_radiation=np.array([np.nan, np.nan, 1.]))):
+        with pytest.raises(AttributeError):
+            radiosity_RTVF(VF, areas, eps, **bad)
