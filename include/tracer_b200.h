@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 9
+#define TRC_ABI_VERSION 10
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -65,8 +65,17 @@ typedef enum TrcGeomKind {
     TRC_G_QUADRIC_RECT = 22,   /* RectFlatQuadricSurfaceGM   quadratic_surface.py:63  gp: a b c d e f hw hh */
     TRC_G_SPHERE_CUT = 23,     /* CutSphereGM + BoundarySphere sphere_surface.py:168, boundary_shape.py:89-111
                                   gp: r, cx, cy, cz (bound centre, global), R_bound */
-    TRC_G_KIND_COUNT = 24
+    TRC_G_ELLIPSOID = 24,      /* EllipsoidGM                ellipsoid.py:5,63    gp: 1/a^2, 1/b^2, 1/c^2, xlo, xhi, ylo,
+                                  yhi, zlo, zhi (-inf / +inf where there is no limit) */
+    TRC_G_RECT_PERFORATED = 25,/* PerforatedRectPlateGM      flat_surface.py:357  gp: hx, hy, pool offset, n_holes;
+                                  pool: (cx, cy, r) per hole */
+    TRC_G_POLYGON = 26,        /* FlatSimplePolygonGM / PerforatedPolygonGM  polygon.py:7,139
+                                  gp: pool offset, n_vertices, n_holes; pool: xs[nv+1], ys[nv+1] (closed
+                                  profile), then (cx, cy, r) per hole */
+    TRC_G_KIND_COUNT = 27
 } TrcGeomKind;
+/* "pool" = the scene's float64 table pool (trc_scene_create `tables`), shared with the optics
+ * tables; offsets are counted in doubles and stored in gp as exact small integers. */
 
 /* Optics kinds: the base optics class behind the accountant wrapper
  * (optics_callables.py). */

@@ -111,8 +111,34 @@ def find_intersections(surface, v, d):
     raise NotImplementedError("oracle: geometry manager %s" % type(gm).__name__)
 
 
-_FLAT = ('ExtrudedRectPlateGM', 'RectPlateGM', 'StraightCutRoundPlateGM', 'RoundPlateGM', 'TriangularFace',
+_FLAT = ('PerforatedRectPlateGM', 'PerforatedPolygonGM', 'FlatSimplePolygonGM', 'ExtrudedRectPlateGM', 'RectPlateGM', 'StraightCutRoundPlateGM', 'RoundPlateGM', 'TriangularFace',
          'FlatGeometryManager', 'FiniteFlatGM')
+
+
+def _in_a_hole(gm, local):
+    """Strictly inside one of the circular perforations (centres (n,2), radii (n,))."""
+    c = N.asarray(gm.extr_centers, float).reshape(-1, 2)
+    dist = N.sqrt((local[0][:, None] - c[:, 0]) ** 2 + (local[1][:, None] - c[:, 1]) ** 2)
+    return N.any(dist < N.asarray(gm.extr_radii, float).reshape(-1), axis=1)
+
+
+def _in_polygon(profile, px, py):
+    """Crossing number of FlatSimplePolygonGM.in_poly / intersect (polygon.py:31-63), edge by edge."""
+    xs = N.append(profile[0], profile[0, 0])
+    ys = N.append(profile[1], profile[1, 0])
+    crossings = N.zeros(len(px), dtype=N.int64)
+    for k in range(len(xs) - 1):
+        xp0, xp1 = px <= xs[k], px <= xs[k + 1]
+        yp0, yp1 = py <= ys[k], py <= ys[k + 1]
+        across_y = yp0 ^ yp1
+        hit = xp0 & xp1 & across_y
+        doubt = (xp0 ^ xp1) & across_y
+        if doubt.any():
+            a = (ys[k + 1] - ys[k]) / (xs[k + 1] - xs[k])
+            y0 = ys[k] - a * xs[k]
+            hit = hit | (doubt & ((py - y0) / a >= px))
+        crossings += hit
+    return (crossings % 2).astype(bool)
 
 
 def _find_flat(name, gm, frame, v, d):
@@ -122,10 +148,16 @@ def _find_flat(name, gm, frame, v, d):
     if name not in ('FlatGeometryManager', 'FiniteFlatGM'):
         with N.errstate(invalid='ignore'):
             local = _to_local(frame, glob)                  # :160-164
-            if name in ('RectPlateGM', 'ExtrudedRectPlateGM'):
+            if name in ('RectPlateGM', 'ExtrudedRectPlateGM', 'PerforatedRectPlateGM'):
                 params[N.any(N.abs(local[:2]) > gm._half_dims, axis=0)] = N.inf          # :209
+                if name == 'PerforatedRectPlateGM':
+                    params[_in_a_hole(gm, local)] = N.inf                                # :372-373
                 if name == 'ExtrudedRectPlateGM':
                     params[N.all(N.abs(local[:2] - gm.extr_center) < gm.extr_half_dims, axis=0)] = N.inf   # :272
+            elif name in ('FlatSimplePolygonGM', 'PerforatedPolygonGM'):                 # polygon.py:20-29, :150-160
+                params[~_in_polygon(N.asarray(gm.profile, float), local[0], local[1])] = N.inf
+                if name == 'PerforatedPolygonGM':
+                    params[_in_a_hole(gm, local)] = N.inf
             elif name in ('RoundPlateGM', 'StraightCutRoundPlateGM'):
                 r2 = N.sum(local[:2] ** 2., axis=0)
                 params[r2 > gm._Re ** 2.] = N.inf                                        # :488
@@ -156,7 +188,8 @@ def _find_flat(name, gm, frame, v, d):
 _QUADRIC = ('ParabolicDishGM', 'HexagonalParabolicDishGM', 'RectangularParabolicDishGM', 'ParabolicTroughGM',
             'ParabolicCylinder', 'Paraboloid', 'SphericalRectFacet', 'HemisphereGM', 'CutSphereGM', 'SphericalGM',
             'FiniteCone', 'RectCutConicalFrustum', 'ConicalFrustum', 'InfiniteCone', 'RectCutCylinder',
-            'FiniteCylinder', 'InfiniteCylinder', 'RectFlatQuadricSurfaceGM', 'FlatQuadricSurfaceGM')
+            'FiniteCylinder', 'InfiniteCylinder', 'RectFlatQuadricSurfaceGM', 'FlatQuadricSurfaceGM',
+            'EllipsoidGM', 'Ellipsoid')
 _PARAB = ('ParabolicDishGM', 'HexagonalParabolicDishGM', 'RectangularParabolicDishGM', 'Paraboloid')
 _PCYL = ('ParabolicTroughGM', 'ParabolicCylinder')
 _SPH = ('SphericalRectFacet', 'HemisphereGM', 'CutSphereGM', 'SphericalGM')
@@ -189,6 +222,10 @@ def _abc(name, gm, frame, v, d):
         A = N.sum(dl[:2] ** 2, axis=0)
         B = 2. * N.sum(dl[:2] * vl[:2], axis=0)
         C = N.sum(vl[:2] ** 2, axis=0) - gm._R ** 2
+    elif name in ('EllipsoidGM', 'Ellipsoid'):              # ellipsoid.py:20-34
+        A = gm.a * dl[0] ** 2 + gm.b * dl[1] ** 2 + gm.c * dl[2] ** 2
+        B = 2 * gm.a * dl[0] * vl[0] + 2 * gm.b * dl[1] * vl[1] + 2 * gm.c * dl[2] * vl[2]
+        C = gm.a * vl[0] ** 2 + gm.b * vl[1] ** 2 + gm.c * vl[2] ** 2 - 1
     else:                                                   # quadratic_surface.py:46-61
         A = gm.a * dl[0] ** 2. + gm.b * dl[1] ** 2. + gm.c * dl[0] * dl[1]
         B = 2. * gm.a * dl[0] * vl[0] + 2. * gm.b * dl[1] * vl[1] + gm.c * (vl[0] * dl[1] + vl[1] * dl[0]) \
@@ -240,7 +277,7 @@ def _refine_select(select, inside, sphere_family=False):
 def _select(name, gm, frame, coords, prm):
     """The per-class _select_coords overrides; coords (2,3,n) global, prm (2,n)."""
     if name in ('Paraboloid', 'SphericalGM', 'InfiniteCone', 'InfiniteCylinder', 'FlatQuadricSurfaceGM',
-                'ParabolicCylinder'):
+                'ParabolicCylinder', 'Ellipsoid'):
         return _default_select(prm)
     if name == 'CutSphereGM':                               # sphere_surface.py:188-204
         select = _default_select(prm)
@@ -284,6 +321,12 @@ def _select(name, gm, frame, coords, prm):
     if name == 'RectCutCylinder':                           # cylinder.py:171-199
         inside = (-gm._half_h <= z) & (z <= gm._half_h) & (N.abs(x) <= gm.half_dims[0]) & (N.abs(y) <= gm.half_dims[1])
         return _hitting_select(inside & (prm > 1e-6))
+    if name == 'EllipsoidGM':                               # ellipsoid.py:77-116
+        good = prm > 1e-7
+        for coord, lim in ((x, gm.xlim), (y, gm.ylim), (z, gm.zlim)):
+            if gm.truncated and lim is not None:
+                good = good & (coord >= lim[0]) & (coord <= lim[1])
+        return _hitting_select(good)
     if name == 'RectFlatQuadricSurfaceGM':                  # quadratic_surface.py:75-105
         outside = (N.abs(x) > gm._w) | (N.abs(y) > gm._h)
         return _refine_select(_default_select(prm), (~outside) & (prm > 1e-6))
@@ -315,6 +358,8 @@ def _quadric_normals(name, gm, frame, hits, directs):
     elif name in _CONE:
         ln = N.vstack((2. * hit[0], 2. * hit[1], -2. * (hit[2] - gm.a) * gm.c ** 2.))
         eps, apex = 1e-9, (hit[2] == gm.a)
+    elif name in ('EllipsoidGM', 'Ellipsoid'):              # ellipsoid.py:36-61
+        ln = N.vstack((2 * hit[0] * gm.a, 2 * hit[1] * gm.b, 2 * hit[2] * gm.c))
     else:
         ln = N.vstack((2. * hit[0] * gm.a + gm.c * hit[1] + gm.d, 2. * hit[1] * gm.b + gm.c * hit[0] + gm.e,
                        -1 * N.ones(n)))

@@ -299,7 +299,20 @@ def gm_zoo(T):
         'cyl_rect': (lambda: Y.RectCutCylinder(1.2, 1., 1.0, 1.1), tilt),
         'quadric_flat': (lambda: Q.FlatQuadricSurfaceGM(0.2, 0.1, 0.05, 0.02, -0.03, 0.01), tilt),
         'quadric_rect': (lambda: Q.RectFlatQuadricSurfaceGM(1.5, 1., 0.2, 0.1, 0.05, 0.02, -0.03, 0.01), tilt),
+        'rect_perforated': (lambda: F.PerforatedRectPlateGM(1.8, 1.4, np.array([[0.3, 0.2], [-0.4, -0.3], [0.5, -0.4]]),
+                                                           np.array([0.25, 0.2, 0.12])), tilt),
+        'polygon': (lambda: T.polygon.FlatSimplePolygonGM(_STAR), tilt),
+        'polygon_perforated': (lambda: T.polygon.PerforatedPolygonGM(_STAR, np.array([[0.1, 0.1], [-0.3, 0.35]]),
+                                                                     np.array([0.2, 0.1])), tilt),
+        'ellipsoid': (lambda: T.ellipsoid.EllipsoidGM(0.9, 0.6, 0.75), tilt),
+        'ellipsoid_cut': (lambda: T.ellipsoid.EllipsoidGM(0.9, 0.6, 0.75, xlim=[-0.5, 0.7], zlim=[-0.6, 0.2]), tilt),
+        'ellipsoid_all_limits': (lambda: T.ellipsoid.EllipsoidGM(0.9, 0.6, 0.75, [-0.2, 0.2], [-0.2, 0.2], [-0.2, 0.2]), tilt),
     }
+
+
+# a concave 8-vertex star, clockwise, with one vertical and one horizontal edge
+_STAR = np.array([[0.0, 0.3, 0.9, 0.35, 0.5, 0.0, -0.8, -0.8],
+                  [0.9, 0.3, 0.2, -0.2, -0.8, -0.35, -0.6, 0.4]])
 
 
 def zoo_scene(T, name, optics=None):

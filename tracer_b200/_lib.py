@@ -12,13 +12,14 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtracer_b200.so")
 
-ABI_VERSION = 9
+ABI_VERSION = 10
 
 # enum TrcGeomKind
 (G_FLAT_INFINITE, G_RECT_PLATE, G_RECT_EXTRUDED, G_ROUND_PLATE, G_TRIANGLE, G_PARABOLOID,
  G_PARAB_DISH, G_PARAB_HEX, G_PARAB_RECT, G_PARAB_CYL, G_PARAB_TROUGH, G_SPHERE, G_HEMISPHERE,
  G_SPHERE_RECT, G_CONE_INFINITE, G_CONE_FINITE, G_FRUSTUM, G_FRUSTUM_RECT, G_CYL_INFINITE,
- G_CYL_FINITE, G_CYL_RECT, G_QUADRIC_FLAT, G_QUADRIC_RECT, G_SPHERE_CUT) = range(24)
+ G_CYL_FINITE, G_CYL_RECT, G_QUADRIC_FLAT, G_QUADRIC_RECT, G_SPHERE_CUT, G_ELLIPSOID, G_RECT_PERFORATED,
+ G_POLYGON) = range(27)
 # enum TrcOpticsKind
 (O_TRANSPARENT, O_REFLECTIVE, O_REAL_REFLECTIVE, O_LAMBERTIAN, O_LAMBERTIAN_SPECULAR,
  O_LAMB_DIRECTIONAL, O_REFLECTIVE_SPECTRAL, O_LAMBSPEC_DIRECTIONAL,

@@ -92,7 +92,7 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
         int sidx = (int)(tail >> 32);
         const TrcSurfaceRec *s = &surfs[sidx];
         double wl = p.wavelengths ? p.wavelengths[r] : 0.0;
-        double t = intersect(s, v, d);
+        double t = intersect(s, v, d, tables);
         V3 hit = axpy(v, t, d);
         V3 n = surface_normal(s, hit, d);
         double u[3] = {0.0, 0.0, 0.0};

@@ -89,6 +89,62 @@ __device__ __forceinline__ double isect_flat(const TrcSurfaceRec *s, int kind, V
     return t;
 }
 
+// Circular perforations: the hit is void when strictly inside any hole
+// (flat_surface.py:372-373, polygon.py:155-158).  h = (cx, cy, r) triples.
+__device__ __forceinline__ bool in_a_hole(const double *h, int n, double lx, double ly) {
+    for (int k = 0; k < n; ++k) {
+        double dx = lx - h[3 * k], dy = ly - h[3 * k + 1];
+        if (sqrt(dx * dx + dy * dy) < h[3 * k + 2]) return true;
+    }
+    return false;
+}
+
+// FlatSimplePolygonGM.in_poly (polygon.py:31-53): crossing number of the ray from
+// the point towards +x against the closed profile xs[0..nv], ys[0..nv].  An edge
+// wholly at x >= px counts when its ends straddle py; an edge straddling both px and
+// py counts when the crossing abscissa (:55-63) is >= px.
+__device__ __forceinline__ bool in_polygon(const double *xs, const double *ys, int nv, double px, double py) {
+    int crossings = 0;
+    bool xp0 = px <= xs[0], yp0 = py <= ys[0];
+    for (int k = 0; k < nv; ++k) {
+        bool xp1 = px <= xs[k + 1], yp1 = py <= ys[k + 1];
+        if (yp0 != yp1) {
+            if (xp0 && xp1) {
+                ++crossings;
+            } else if (xp0 != xp1) {
+                double a = (ys[k + 1] - ys[k]) / (xs[k + 1] - xs[k]);
+                double y0 = ys[k] - a * xs[k];
+                if ((py - y0) / a >= px) ++crossings;
+            }
+        }
+        xp0 = xp1; yp0 = yp1;
+    }
+    return (crossings & 1) != 0;
+}
+
+// Flat kinds whose aperture lives in the table pool (TRC_G_RECT_PERFORATED, TRC_G_POLYGON).
+// Kept out of isect_flat so that the flat-only tree walk stays small.
+static __device__ __noinline__ double isect_flat_pool(const TrcSurfaceRec *s, int kind, V3 v, V3 d, const double *pool) {
+    double t = isect_flat(s, TRC_G_FLAT_INFINITE, v, d);
+    if (t == TRC_INF) return t;
+    V3 g = axpy(v, t, d);
+    const double *iv = s->inv;
+    const double *gp = s->gp;
+    double lx = iv[0] * g.x + iv[1] * g.y + iv[2] * g.z + iv[3];
+    double ly = iv[4] * g.x + iv[5] * g.y + iv[6] * g.z + iv[7];
+    if (kind == TRC_G_RECT_PERFORATED) {
+        if (fabs(lx) > gp[0] || fabs(ly) > gp[1]) return TRC_INF;
+        if (in_a_hole(pool + (int)gp[2], (int)gp[3], lx, ly)) return TRC_INF;
+        return t;
+    }
+    // TRC_G_POLYGON
+    const double *xs = pool + (int)gp[0];
+    const int nv = (int)gp[1];
+    if (!in_polygon(xs, xs + nv + 1, nv, lx, ly)) return TRC_INF;
+    if (in_a_hole(xs + 2 * (nv + 1), (int)gp[2], lx, ly)) return TRC_INF;
+    return t;
+}
+
 // Flat normal always opposes the incoming ray (flat_surface.py:58-60, 84-91).
 __device__ __forceinline__ V3 normal_flat(const TrcSurfaceRec *s, V3 d) {
     const double *f = s->frame;
@@ -102,7 +158,7 @@ __device__ __forceinline__ V3 normal_flat(const TrcSurfaceRec *s, V3 d) {
 // _select_coords predicates (quadric.py:115-144, paraboloid.py:89-119,
 // :193-223, :257-294, :411-443, sphere_surface.py:122-139, :211-228,
 // cone.py:94-120, :285-320, :365-395, cylinder.py:71-110, :171-199,
-// quadratic_surface.py:75-105).  `dflt` reports whether the class falls back
+// quadratic_surface.py:75-105, ellipsoid.py:77-116).  `dflt` reports whether the class falls back
 // to QuadricGM's default choice when both roots pass.
 __device__ __forceinline__ bool quadric_root_ok(const TrcSurfaceRec *s, int kind, V3 p, double t) {
     const double *gp = s->gp;
@@ -151,6 +207,9 @@ __device__ __forceinline__ bool quadric_root_ok(const TrcSurfaceRec *s, int kind
         return -gp[1] <= l.z && l.z <= gp[1] && fabs(l.x) <= gp[2] && fabs(l.y) <= gp[3] && t > 1e-6;
     case TRC_G_QUADRIC_RECT:
         return !(fabs(l.x) > gp[6] || fabs(l.y) > gp[7]) && t > 1e-6;
+    case TRC_G_ELLIPSOID:         // ellipsoid.py:93-110 (1e-7, limits inclusive)
+        return t > 1e-7 && l.x >= gp[3] && l.x <= gp[4] && l.y >= gp[5] && l.y <= gp[6] &&
+               l.z >= gp[7] && l.z <= gp[8];
     }
     return false;
 }
@@ -198,6 +257,13 @@ __device__ __forceinline__ double isect_quadric(const TrcSurfaceRec *s, int kind
             A = dl.x * dl.x + dl.y * dl.y;
             B = 2.0 * (dl.x * vl.x + dl.y * vl.y);
             C = (vl.x * vl.x + vl.y * vl.y) - gp[0] * gp[0];
+            break;
+        }
+        case TRC_G_ELLIPSOID: {   // ellipsoid.py:20-34
+            double a = gp[0], b = gp[1], c = gp[2];
+            A = a * (dl.x * dl.x) + b * (dl.y * dl.y) + c * (dl.z * dl.z);
+            B = 2.0 * a * dl.x * vl.x + 2.0 * b * dl.y * vl.y + 2.0 * c * dl.z * vl.z;
+            C = a * (vl.x * vl.x) + b * (vl.y * vl.y) + c * (vl.z * vl.z) - 1.0;
             break;
         }
         default: {  // TRC_G_QUADRIC_FLAT / TRC_G_QUADRIC_RECT
@@ -273,6 +339,8 @@ __device__ __forceinline__ V3 normal_quadric(const TrcSurfaceRec *s, int kind, V
         if (ln.x * dl.x + ln.y * dl.y > 0.0) ln = mk(-ln.x, -ln.y, -0.0);
         return rot_to_global(f, ln);
     }
+    case TRC_G_ELLIPSOID:         // ellipsoid.py:36-61
+        n = mk(2.0 * h.x * gp[0], 2.0 * h.y * gp[1], 2.0 * h.z * gp[2]); break;
     default:
         n = mk(2.0 * h.x * gp[0] + gp[2] * h.y + gp[3], 2.0 * h.y * gp[1] + gp[2] * h.x + gp[4], -1.0); break;
     }
@@ -283,13 +351,17 @@ __device__ __forceinline__ V3 normal_quadric(const TrcSurfaceRec *s, int kind, V
     return rot_to_global(f, n);
 }
 
-__device__ __forceinline__ bool kind_is_flat(int kind) { return kind <= TRC_G_TRIANGLE; }
+__device__ __forceinline__ bool kind_is_flat_pool(int kind) { return kind == TRC_G_RECT_PERFORATED || kind == TRC_G_POLYGON; }
+__device__ __forceinline__ bool kind_is_flat(int kind) { return kind <= TRC_G_TRIANGLE || kind_is_flat_pool(kind); }
 
 // GeometryManager.find_intersections for any kind, plus the engine's
 // "t == 0 -> inf" rule (tracer_engine.py:58).
-__device__ __forceinline__ double intersect(const TrcSurfaceRec *s, V3 v, V3 d) {
+// `pool` = the scene's table pool (apertures of the TRC_G_RECT_PERFORATED / TRC_G_POLYGON kinds).
+__device__ __forceinline__ double intersect(const TrcSurfaceRec *s, V3 v, V3 d, const double *pool) {
     int kind = s->gkind;
-    double t = kind_is_flat(kind) ? isect_flat(s, kind, v, d) : isect_quadric(s, kind, v, d);
+    double t = kind <= TRC_G_TRIANGLE ? isect_flat(s, kind, v, d)
+             : kind_is_flat_pool(kind) ? isect_flat_pool(s, kind, v, d, pool)
+                                       : isect_quadric(s, kind, v, d);
     if (t == 0.0) t = TRC_INF;
     return t;
 }

@@ -34,8 +34,9 @@ using namespace trc;
 
 namespace {
 
-__device__ __forceinline__ void consider(const TrcSurfaceRec *s, int idx, V3 v, V3 d, double &best_t, int &best_s) {
-    double t = intersect(s, v, d);
+__device__ __forceinline__ void consider(const TrcSurfaceRec *s, int idx, V3 v, V3 d, const double *pool,
+                                         double &best_t, int &best_s) {
+    double t = intersect(s, v, d, pool);
     if (t < best_t || (t == best_t && idx < best_s && t != TRC_INF)) { best_t = t; best_s = idx; }
 }
 
@@ -69,7 +70,7 @@ __device__ __forceinline__ void store_record(TrcHitRecord *dst, V3 v, V3 d, doub
 static_assert(TRC_HIT_CHUNK == 256, "one brute-force block = one chunk");
 
 __global__ void __launch_bounds__(256)
-nearest_hit_brute_kernel(const TrcSurfaceRec *__restrict__ surfs, int n_surf, int64_t n,
+nearest_hit_brute_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict__ pool, int n_surf, int64_t n,
                          const double *__restrict__ vert, const double *__restrict__ dir, int64_t ld,
                          HitSink sink) {
     __shared__ TrcSurfaceRec stage[TRC_STAGE_SURFS];
@@ -95,7 +96,7 @@ nearest_hit_brute_kernel(const TrcSurfaceRec *__restrict__ surfs, int n_surf, in
         }
         __syncthreads();
         if (live) {
-            for (int k = 0; k < cnt; ++k) consider(&stage[k], base + k, v, d, best_t, best_s);
+            for (int k = 0; k < cnt; ++k) consider(&stage[k], base + k, v, d, pool, best_t, best_s);
         }
     }
     if (live && sink.hit_surf) sink.hit_surf[i] = best_s;
@@ -172,6 +173,7 @@ struct WalkShared {
 
 struct WalkParams {
     const TrcSurfaceRec *surfs;
+    const double *pool;                       // scene table pool (apertures of the pool-based flat kinds)
     const uint4 *pair_a, *pair_b;
     int n_pairs;
     unsigned root_meta;
@@ -312,7 +314,7 @@ __device__ __forceinline__ int flush_queue_body(WalkWarpShared &sh, const WalkPa
                     tk = isect_flat(sr, sr->gkind, v, d);
                     if (tk == 0.0) tk = TRC_INF;
                 } else {
-                    tk = intersect(sr, v, d);
+                    tk = intersect(sr, v, d, p.pool);
                 }
                 if (tk < t || (tk == t && s < surf && tk != TRC_INF)) { t = tk; surf = s; }
             }
@@ -628,7 +630,7 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     if (n >= 0x7fffffffLL) return fail(TRC_ERR_CAPACITY, "trc_nearest_hit: more than 2^31-1 rays, chunk the bundle%s");
     if (!use_bvh) {
         int64_t blocks = (n + 255) / 256;
-        nearest_hit_brute_kernel<<<(unsigned)blocks, 256, 0, st>>>(sc->d_surfaces, sc->n_surfaces, n, d_vert, d_dir,
+        nearest_hit_brute_kernel<<<(unsigned)blocks, 256, 0, st>>>(sc->d_surfaces, sc->d_tables, sc->n_surfaces, n, d_vert, d_dir,
                                                                    ld, sink);
         return check_launch("nearest_hit_brute");
     }
@@ -654,6 +656,7 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     const int variant = (sc->n_pairs <= kSmemPairs ? 1 : 0) | (sc->flat_only ? 2 : 0);
     WalkParams p;
     p.surfs = sc->d_surfaces;
+    p.pool = sc->d_tables;
     p.pair_a = reinterpret_cast<const uint4 *>(sc->d_pair_a);
     p.pair_b = reinterpret_cast<const uint4 *>(sc->d_pair_b);
     p.n_pairs = sc->n_pairs; p.root_meta = sc->root_meta;

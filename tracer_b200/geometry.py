@@ -11,7 +11,8 @@ Reference classes: flat_surface.py (FlatGeometryManager :11, FiniteFlatGM :115,
 RectPlateGM :181, ExtrudedRectPlateGM :253, RoundPlateGM :457,
 StraightCutRoundPlateGM :548), triangular_face.py:12, paraboloid.py (:11, :71,
 :174, :225, :328, :386), sphere_surface.py (:9, :117, :168, :206), cone.py (:7,
-:74, :261, :356), cylinder.py (:12, :59, :161), quadratic_surface.py (:4, :63).
+:74, :261, :356), cylinder.py (:12, :59, :161), quadratic_surface.py (:4, :63),
+flat_surface.py PerforatedRectPlateGM :357, ellipsoid.py (:5, :63), polygon.py (:7, :139).
 """
 import numpy as np
 
@@ -64,6 +65,34 @@ class ExtrudedRectPlateGM(RectPlateGM):
         self.extr_center = extr_center
         self.extr_half_dims = np.c_[[extr_width, extr_height]] / 2.
         assert ((extr_center + self.extr_half_dims) < self._half_dims).all()
+
+
+class PerforatedRectPlateGM(RectPlateGM):
+    """Rectangle with circular holes (flat_surface.py:357-377).  ``extr_centers`` is an (n, 2)
+    array, one hole centre per row (that is how find_intersections :372 reads it, whatever the
+    reference docstring says), ``extr_radii`` an (n,) array."""
+
+    def __init__(self, width, height, extr_centers, extr_radii):
+        RectPlateGM.__init__(self, width, height)
+        self.extr_centers = extr_centers
+        self.extr_radii = extr_radii
+
+
+class FlatSimplePolygonGM(FiniteFlatGM):
+    """Simple polygon in the local XY plane, crossing-number test (polygon.py:7-63).
+    ``profile`` = [[xs], [ys]], vertices in sequence."""
+
+    def __init__(self, profile):
+        self.profile = profile
+
+
+class PerforatedPolygonGM(FlatSimplePolygonGM):
+    """Polygon with circular holes (polygon.py:139-162); centres (n, 2), radii (n,)."""
+
+    def __init__(self, profile, extr_centers, extr_radii):
+        self.extr_centers = extr_centers
+        self.extr_radii = extr_radii
+        FlatSimplePolygonGM.__init__(self, profile)
 
 
 class RoundPlateGM(FiniteFlatGM):
@@ -149,6 +178,31 @@ class ParabolicTroughGM(ParabolicCylinder):
         self._l = length
         self._w = float(aperture)
         self._h = float((aperture / 2. / par_param) ** 2)
+
+
+class Ellipsoid(QuadricGM):
+    """(x/a)^2 + (y/b)^2 + (z/c)^2 = 1; holds the inverse squares like ellipsoid.py:16-18."""
+
+    def __init__(self, a, b, c):
+        self.a = 1. / (a ** 2)
+        self.b = 1. / (b ** 2)
+        self.c = 1. / (c ** 2)
+
+
+class EllipsoidGM(Ellipsoid):
+    """Ellipsoid truncated along the local axes (ellipsoid.py:63-118).  As in the reference
+    (:70-75) the limits only act when at least one of them is None; with all three given they
+    are replaced by the full extent."""
+
+    def __init__(self, a, b, c, xlim=None, ylim=None, zlim=None):
+        Ellipsoid.__init__(self, a, b, c)
+        if any(lim is None for lim in (xlim, ylim, zlim)):
+            self.xlim, self.ylim, self.zlim = xlim, ylim, zlim
+            self.truncated = True
+        else:
+            self.xlim, self.ylim, self.zlim = [-a, a], [-b, b], [-c, c]
+            self.truncated = False
+        self._semi_axes = (float(a), float(b), float(c))
 
 
 class SphericalGM(QuadricGM):

@@ -39,9 +39,35 @@ def _geom_record(gm, surface):
     def box(x, y, z0, z1):
         return (np.array([-x, -y, z0], float), np.array([x, y, z1], float))
 
+    def holes():
+        c = np.asarray(gm.extr_centers, float).reshape(-1, 2)
+        r = np.asarray(gm.extr_radii, float).reshape(-1)
+        if len(c) != len(r):
+            raise ValueError("extr_centers needs one (x, y) row per entry of extr_radii")
+        return np.column_stack([c, r]).reshape(-1), len(r)
+
     for name in names:
         if name == 'PerforatedRectPlateGM':
-            break
+            hx, hy = np.asarray(gm._half_dims, float).reshape(-1)
+            pool, n_holes = holes()
+            return L.G_RECT_PERFORATED, ([hx, hy, 0., n_holes], pool, 2), box(hx, hy, 0., 0.)
+        if name in ('PerforatedPolygonGM', 'FlatSimplePolygonGM'):
+            prof = np.asarray(gm.profile, float)
+            if prof.ndim != 2 or prof.shape[0] != 2 or prof.shape[1] < 3:
+                raise ValueError("polygon profile must be a (2, n >= 3) array")
+            closed = np.concatenate((prof, prof[:, :1]), axis=1)
+            pool, n_holes = holes() if name == 'PerforatedPolygonGM' else (np.zeros(0), 0)
+            lo, hi = prof.min(axis=1), prof.max(axis=1)
+            return (L.G_POLYGON, ([0., prof.shape[1], n_holes], np.concatenate((closed[0], closed[1], pool)), 0),
+                    (np.array([lo[0], lo[1], 0.]), np.array([hi[0], hi[1], 0.])))
+        if name in ('EllipsoidGM', 'Ellipsoid'):
+            semi = 1. / np.sqrt(np.array([gm.a, gm.b, gm.c], float))
+            lims = []
+            for k, lim in enumerate((getattr(gm, 'xlim', None), getattr(gm, 'ylim', None), getattr(gm, 'zlim', None))):
+                lims += [-inf, inf] if lim is None else [float(lim[0]), float(lim[1])]
+            lims = np.array(lims).reshape(3, 2)
+            lo, hi = np.maximum(-semi, lims[:, 0]), np.minimum(semi, lims[:, 1])
+            return L.G_ELLIPSOID, [gm.a, gm.b, gm.c] + list(lims.reshape(-1)), (lo, np.maximum(lo, hi))
         if name == 'ExtrudedRectPlateGM':
             hx, hy = np.asarray(gm._half_dims, float).reshape(-1)
             cx, cy = np.asarray(gm.extr_center, float).reshape(-1)[:2]
@@ -359,6 +385,11 @@ class CompiledScene(object):
             r = recs[i]
             r['frame'] = frame[:3].reshape(-1)
             r['inv'] = np.linalg.inv(frame)[:3].reshape(-1)
+            if isinstance(gp, tuple):                   # aperture data in the table pool: gp[slot] = its offset
+                gp, pool, slot = gp
+                gp[slot] = float(table_len)
+                tables.append(np.asarray(pool, float))
+                table_len += len(pool)
             r['gp'][:len(gp)] = gp
             r['op'] = orec['op']
             r['gkind'], r['okind'] = kind, orec['okind']
