@@ -141,6 +141,45 @@ def c4_cavity(T, n_rays=2000, n_theta=8, n_z=4, absorptivity=0.7):
     return asm, source
 
 
+def cylinder_mesh_array(n_theta, n_z, radius=1., length=2.):
+    """cylinder_mesh as one (n,3,3) array [face, vertex, xyz], built without Python loops
+    (1e6 faces in a fraction of a second); same faces, side wall first (theta-major) then cap."""
+    th = np.linspace(0., 2. * np.pi, n_theta + 1)
+    zs = np.linspace(0., length, n_z + 1)
+    x, y = radius * np.cos(th), radius * np.sin(th)
+    i, j = np.meshgrid(np.arange(n_theta), np.arange(n_z), indexing='ij')
+    i, j = i.ravel(), j.ravel()
+    a = np.stack([x[i], y[i], zs[j]], axis=1)
+    b = np.stack([x[i + 1], y[i + 1], zs[j]], axis=1)
+    c = np.stack([x[i + 1], y[i + 1], zs[j + 1]], axis=1)
+    d = np.stack([x[i], y[i], zs[j + 1]], axis=1)
+    side = np.stack([np.stack([a, c, b], axis=1), np.stack([a, d, c], axis=1)], axis=1).reshape(-1, 3, 3)
+    k = np.arange(n_theta)
+    centre = np.tile(np.r_[0., 0., length], (n_theta, 1))
+    cap = np.stack([centre, np.stack([x[k + 1], y[k + 1], np.full(n_theta, length)], axis=1),
+                    np.stack([x[k], y[k], np.full(n_theta, length)], axis=1)], axis=1)
+    return np.concatenate([side, cap])
+
+
+def c4_cavity_mesh(T, n_rays=2000, n_theta=8, n_z=4, absorptivity=0.7, per_face_objects=False):
+    """Config 4 through the STL route (ray_trace_utils/stl_utils.py:213): the cavity of
+    c4_cavity as ONE mesh object, or (per_face_objects) as one Surface per face built from
+    the same per-face frames -- the two must trace identically."""
+    tris = cylinder_mesh_array(n_theta, n_z)
+    opt = T.optics_callables.LambertianReceiver
+    if per_face_objects:
+        geoms, locs, rots = T.stl_utils.stl_to_tracer_geom(tris, option='triangle')
+        surfs = [T.surface.Surface(g, opt(absorptivity), location=l, rotation=r) for g, l, r in zip(geoms, locs, rots)]
+        obj = T.object.AssembledObject(surfs=surfs)
+    else:
+        obj = T.stl_utils.make_stl_tracer_object(tris, opt, dict(absorptivity=absorptivity), option='triangle')
+    asm = T.assembly.Assembly(objects=[obj])
+
+    def source():
+        return T.sources.disk_bundle(n_rays, np.c_[[0., 0., -0.01]], np.r_[0., 0., 1.], 0.9, np.pi / 4., flux=1000.)
+    return asm, source
+
+
 def c5_cavity(T, n_rays=2000, spectral=False):
     """Config 5 (one pass): Holman ex. 8.17-like cylinder cavity made of quadric
     surfaces: aperture disk, three cylinder sections, flat back

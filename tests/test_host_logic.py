@@ -232,3 +232,53 @@ def test_ray_tree_history():
     assert t.num_bunds() == 3
     assert [list(p) for p in t.ordered_parents()] == [[1, 0, 3, 2], [2, 1]]
     assert list(t.ray_history(0)) == [0, 2, 3]
+
+
+def test_triangle_mesh_object_compiles_like_one_surface_per_face():
+    """stl_utils.TriangleMeshObject (array route) gives the scene compiler the records that one
+    Surface per face gives it, under a tilted assembly transform and next to an ordinary
+    object; its boxes are the exact face boxes (inside the per-surface ones); surfaces made on
+    demand carry the frames of the per-face objects."""
+    from tracer_b200.scene import CompiledScene
+    from tracer_b200.spatial_geometry import rotx, roty
+    scn = []
+    tilt = np.dot(rotx(0.3), roty(-0.4))
+    tilt[:3, 3] = [0.5, -1., 2.]
+    for per_face in (False, True):
+        asm, _ = scenes.c4_cavity_mesh(T, n_theta=12, n_z=5, per_face_objects=per_face)
+        plate = T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(1., 1.),
+                                                                  T.optics_callables.ReflectiveReceiver(0.2))],
+                                         transform=tilt)
+        asm.add_object(plate)
+        asm.set_transform(tilt)
+        scn.append((asm, CompiledScene(asm, upload=False)))
+    (asm_m, m), (asm_o, o) = scn
+    assert len(m.records) == len(o.records) == 12 * 5 * 2 + 12 + 1
+    assert m.mesh_segments[0][:2] == (0, 132) and o.mesh_segments == []
+    for f in ('gkind', 'okind', 'flags', 'table_off', 'table_len', 'op'):
+        assert np.array_equal(m.records[f], o.records[f]), f
+    for f in ('frame', 'inv', 'gp'):
+        np.testing.assert_allclose(m.records[f], o.records[f], rtol=0, atol=1e-14)
+    assert np.all(m.aabb_lo >= o.aabb_lo - 1e-12) and np.all(m.aabb_hi <= o.aabb_hi + 1e-12)
+    assert m.account_list == [132] and o.account_list == list(range(133))
+    surfs_m, surfs_o = asm_m.get_surfaces(), asm_o.get_surfaces()
+    assert len(surfs_m) == 133
+    for i in (0, 57, 131, 132, -1):
+        np.testing.assert_allclose(surfs_m[i]._temp_frame, surfs_o[i]._temp_frame, atol=1e-14)
+        assert type(surfs_m[i].get_geometry_manager()).__name__ == type(surfs_o[i].get_geometry_manager()).__name__
+    with pytest.raises(ValueError):
+        T.stl_utils.make_stl_tracer_object(np.zeros((2, 3, 3)), T.optics_callables.LambertianReceiver, {})
+
+
+def test_load_stl_binary_and_ascii(tmp_path):
+    tris = scenes.cylinder_mesh_array(5, 2).astype('<f4')
+    rec = np.zeros(len(tris), dtype=np.dtype([('n', '<f4', 3), ('v', '<f4', (3, 3)), ('a', '<u2')]))
+    rec['v'] = tris
+    p = tmp_path / 'm.stl'
+    p.write_bytes(b' ' * 80 + np.uint32(len(tris)).tobytes() + rec.tobytes())
+    assert np.array_equal(T.stl_utils.load_stl(str(p)), tris.astype(float))
+    q = tmp_path / 'a.stl'
+    q.write_text('solid x\n' + ''.join(
+        'facet normal 0 0 0\n outer loop\n' + ''.join('  vertex %r %r %r\n' % tuple(float(c) for c in v) for v in t) +
+        ' endloop\nendfacet\n' for t in tris) + 'endsolid x\n')
+    assert np.array_equal(T.stl_utils.load_stl(str(q)), tris.astype(float))

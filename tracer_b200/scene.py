@@ -367,54 +367,45 @@ class CompiledScene(object):
         self.surfaces = surfaces
         S = len(surfaces)
         recs = np.zeros(S, dtype=L.SURFACE_DTYPE)
-        tables = []
-        table_len = 0
+        self._tables = []
+        self._table_len = 0
         self.optics = []
         self.aabb_lo = np.full((S, 3), np.nan)
         self.aabb_hi = np.full((S, 3), np.nan)
-        seen_opt = {}
-        for i, s in enumerate(surfaces):
-            frame = np.asarray(s._temp_frame, dtype=float)
-            kind, gp, lbox = _geom_record(s._geom, s)
-            orec = _optics_record(s._opt)
-            if orec['accountants'] and id(s._opt) in seen_opt:
-                raise NotImplementedError(
-                    f"optics manager instance shared by surfaces {seen_opt[id(s._opt)]} and {i}: "
-                    "accountant data would be merged (optics_callables.py:82); use copy_optical_manager")
-            seen_opt[id(s._opt)] = i
-            r = recs[i]
-            r['frame'] = frame[:3].reshape(-1)
-            r['inv'] = np.linalg.inv(frame)[:3].reshape(-1)
-            if isinstance(gp, tuple):                   # aperture data in the table pool: gp[slot] = its offset
-                gp, pool, slot = gp
-                gp[slot] = float(table_len)
-                tables.append(np.asarray(pool, float))
-                table_len += len(pool)
-            r['gp'][:len(gp)] = gp
-            r['op'] = orec['op']
-            r['gkind'], r['okind'] = kind, orec['okind']
-            flags = orec['flags']
-            box = _global_aabb(frame, lbox)
-            if box is None:
-                flags |= L.F_UNBOUNDED
-            else:
-                self.aabb_lo[i], self.aabb_hi[i] = box
-            r['flags'] = flags
-            r['table_off'], r['table_len'] = -1, 0
-            if orec['table'] is not None:
-                x, y = orec['table']
-                r['table_off'], r['table_len'] = table_len, len(x)
-                tables += [x, y]
-                table_len += len(x) + len(y)
-            self.optics.append(orec)
+        self.mesh_segments = []          # (first surface, one past the last, TriangleMeshObject)
+        self._seen_opt = {}
+        objs = assembly.get_objects()
+        if any(getattr(o, 'is_triangle_mesh', False) for o in objs):
+            i = 0
+            for obj in objs:
+                if getattr(obj, 'is_triangle_mesh', False):
+                    n = obj.num_triangles()
+                    self._fill_mesh(recs, i, obj)
+                    self.mesh_segments.append((i, i + n, obj))
+                    i += n
+                else:
+                    for s in obj.get_surfaces():
+                        self._fill_one(recs, i, s)
+                        i += 1
+            assert i == S
+        else:
+            for i, s in enumerate(surfaces):
+                self._fill_one(recs, i, s)
+        tables = self._tables
+        in_mesh = np.zeros(S, dtype=bool)
+        for a, b, _ in self.mesh_segments:
+            in_mesh[a:b] = True
+        # surfaces whose accountants are fed one by one (TracerEngine._account); a mesh gets one chunk per bounce
+        self.account_list = [i for i in np.nonzero(~in_mesh)[0] if self.optics[i]['accountants']]
         self.records = recs
         self.tables = np.concatenate(tables) if tables else np.zeros(0)
-        self.needs_wavelengths = any(o['needs_wavelengths'] for o in self.optics)
-        self.has_accountants = any(o['accountants'] for o in self.optics)
-        self.children_per_hit = np.array([2 if o['okind'] == L.O_PERIODIC else 1 for o in self.optics], dtype=np.int64)
+        uniq = list({id(o): o for o in self.optics}.values())        # a mesh shares one record
+        self.needs_wavelengths = any(o['needs_wavelengths'] for o in uniq)
+        self.has_accountants = any(o['accountants'] for o in uniq)
+        self.children_per_hit = np.where(recs['okind'] == L.O_PERIODIC, 2, 1).astype(np.int64)
         self.has_split = bool((self.children_per_hit > 1).any())
-        self.needs_theta_for_draws = any(o['okind'] == L.O_LAMB_PIECEWISE_SPEC for o in self.optics)
-        self.accountant_sources = set(src for o in self.optics for (_, _, src) in o['accountants'])
+        self.needs_theta_for_draws = any(o['okind'] == L.O_LAMB_PIECEWISE_SPEC for o in uniq)
+        self.accountant_sources = set(src for o in uniq for (_, _, src) in o['accountants'])
         self.unbounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) != 0)[0].astype(np.int32)
         self.bounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) == 0)[0].astype(np.int32)
         self.leaf_size = leaf_size
@@ -427,6 +418,79 @@ class CompiledScene(object):
             self.bvh_leaf_surfaces = np.zeros(0, np.int32)
         if upload:
             self._upload()
+
+    def _add_table(self, arr):
+        off = self._table_len
+        arr = np.asarray(arr, float)
+        self._tables.append(arr)
+        self._table_len += len(arr)
+        return off
+
+    def _fill_one(self, recs, i, s):
+        frame = np.asarray(s._temp_frame, dtype=float)
+        kind, gp, lbox = _geom_record(s._geom, s)
+        orec = _optics_record(s._opt)
+        seen_opt = self._seen_opt
+        if orec['accountants'] and id(s._opt) in seen_opt:
+            raise NotImplementedError(
+                f"optics manager instance shared by surfaces {seen_opt[id(s._opt)]} and {i}: "
+                "accountant data would be merged (optics_callables.py:82); use copy_optical_manager")
+        seen_opt[id(s._opt)] = i
+        r = recs[i]
+        r['frame'] = frame[:3].reshape(-1)
+        r['inv'] = np.linalg.inv(frame)[:3].reshape(-1)
+        if isinstance(gp, tuple):                   # aperture data in the table pool: gp[slot] = its offset
+            gp, pool, slot = gp
+            gp[slot] = float(self._add_table(pool))
+        r['gp'][:len(gp)] = gp
+        r['op'] = orec['op']
+        r['gkind'], r['okind'] = kind, orec['okind']
+        flags = orec['flags']
+        box = _global_aabb(frame, lbox)
+        if box is None:
+            flags |= L.F_UNBOUNDED
+        else:
+            self.aabb_lo[i], self.aabb_hi[i] = box
+        r['flags'] = flags
+        r['table_off'], r['table_len'] = -1, 0
+        if orec['table'] is not None:
+            x, y = orec['table']
+            r['table_off'], r['table_len'] = self._add_table(x), len(x)
+            self._add_table(y)
+        self.optics.append(orec)
+
+    def _fill_mesh(self, recs, i0, mesh):
+        """Records of a whole TriangleMeshObject with array operations (same content as
+        _fill_one on each of its faces: TRC_G_TRIANGLE, the mesh's optics on every face)."""
+        frames = np.asarray(mesh.mesh_frames(), dtype=float)
+        verts = np.asarray(mesh.mesh_vertices(), dtype=float)
+        n = len(frames)
+        orec = _optics_record(mesh.mesh_optics())
+        if orec['okind'] == L.O_PERIODIC:
+            raise NotImplementedError("PeriodicBoundary optics on a TriangleMeshObject")
+        orec['mesh'] = mesh
+        sl = slice(i0, i0 + n)
+        recs['frame'][sl] = frames[:, :3, :].reshape(n, 12)
+        recs['inv'][sl] = np.linalg.inv(frames)[:, :3, :].reshape(n, 12)
+        recs['gp'][sl, 0:3] = verts[:, :, 0]
+        recs['gp'][sl, 3:6] = verts[:, :, 1]
+        recs['op'][sl] = np.asarray(orec['op'], float)
+        recs['gkind'][sl] = L.G_TRIANGLE
+        recs['okind'][sl] = orec['okind']
+        recs['flags'][sl] = orec['flags']
+        recs['table_off'][sl], recs['table_len'][sl] = -1, 0
+        if orec['table'] is not None:               # one copy of the table serves every face
+            x, y = orec['table']
+            recs['table_off'][sl], recs['table_len'][sl] = self._add_table(x), len(x)
+            self._add_table(y)
+        rot, p0 = frames[:, :3, :3], frames[:, :3, 3]
+        p1 = p0 + np.einsum('nij,nj->ni', rot, verts[:, :, 0])
+        p2 = p0 + np.einsum('nij,nj->ni', rot, verts[:, :, 1])
+        lo = np.minimum(np.minimum(p0, p1), p2)
+        hi = np.maximum(np.maximum(p0, p1), p2)
+        pad = 1e-6 * (1.0 + np.maximum(np.abs(lo).max(axis=1), np.abs(hi).max(axis=1)))[:, None]
+        self.aabb_lo[sl], self.aabb_hi[sl] = lo - pad, hi + pad
+        self.optics.extend([orec] * n)
 
     @staticmethod
     def _check_objects(assembly):

@@ -145,6 +145,34 @@ class BoundarySphere(BoundaryShape):
 _STRUCTURE_VERSION = [0]
 
 
+class SurfaceSeq(object):
+    """Read-only concatenation of per-object surface sequences, some of which make their
+    Surface objects on demand; indexable and iterable like the list get_surfaces() returns."""
+
+    def __init__(self, parts):
+        self.parts = parts
+        self._starts = np.concatenate(([0], np.cumsum([len(p) for p in parts]))).astype(np.int64)
+
+    def __len__(self):
+        return int(self._starts[-1])
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[k] for k in range(*i.indices(len(self)))]
+        n = len(self)
+        if i < 0:
+            i += n
+        if not 0 <= i < n:
+            raise IndexError("surface index out of range")
+        k = int(np.searchsorted(self._starts, i, side='right')) - 1
+        return self.parts[k][int(i - self._starts[k])]
+
+    def __iter__(self):
+        for p in self.parts:
+            for s in p:
+                yield s
+
+
 class Assembly(HasFrame):
     """Tree of objects and sub-assemblies (assembly.py:7-151)."""
 
@@ -175,9 +203,14 @@ class Assembly(HasFrame):
         key = (_STRUCTURE_VERSION[0], len(self._objects), len(self._assemblies))
         cache = self.__dict__.get('_surfaces_cache')
         if cache is None or cache[0] != key:
-            cache = (key, [s for obj in self.get_objects() for s in obj.get_surfaces()])
+            objs = self.get_objects()
+            if any(getattr(obj, 'is_triangle_mesh', False) for obj in objs):
+                # a mesh object's surfaces only exist when indexed (stl_utils.TriangleMeshObject)
+                cache = (key, SurfaceSeq([obj.get_surfaces() for obj in objs]))
+            else:
+                cache = (key, [s for obj in objs for s in obj.get_surfaces()])
             self._surfaces_cache = cache
-        return list(cache[1])
+        return cache[1] if isinstance(cache[1], SurfaceSeq) else list(cache[1])
 
     def global_to_local(self, points):
         return self._to_local(points)
@@ -215,9 +248,13 @@ class Assembly(HasFrame):
             child.transform_children(mine)
 
     def reset_all_optics(self):
-        for s in self.get_surfaces():
-            if hasattr(s.get_optics_manager(), 'reset'):
-                s.get_optics_manager().reset()
+        for obj in self.get_objects():
+            if getattr(obj, 'is_triangle_mesh', False):
+                obj.reset_optics()
+                continue
+            for s in obj.get_surfaces():
+                if hasattr(s.get_optics_manager(), 'reset'):
+                    s.get_optics_manager().reset()
 
 
 class AssembledObject(Assembly):

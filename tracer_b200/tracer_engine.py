@@ -105,7 +105,11 @@ class TracerEngine(object):
         # Every transform of the scene graph assigns a NEW frame array to each surface
         # (has_frame.py / reference has_frame.py:75), so object identity is a cheap change
         # detector; the arrays are kept referenced so that their ids cannot be recycled.
-        frames = [s._temp_frame for s in surfaces]
+        if hasattr(surfaces, 'parts'):        # SurfaceSeq: a mesh object is one entry (its frame array is re-made
+            surfaces = [s for p in surfaces.parts for s in (p if isinstance(p, list) else [p._mesh])]   # on transform)
+            frames = [s._global_frames if hasattr(s, '_global_frames') else s._temp_frame for s in surfaces]
+        else:
+            frames = [s._temp_frame for s in surfaces]
         key = (tuple(map(id, surfaces)), tuple(map(id, frames)))
         if force or self._scene is None or key != self._frames_key:
             if self._scene is not None:
@@ -488,9 +492,16 @@ class TracerEngine(object):
         source name to the tensor the optics kernel filled: slot order, except the
         child columns (hit points, outgoing energy) which follow ``child_off`` when
         some surface of the scene emits two children per hit."""
-        for s, orec in enumerate(scene.optics):
-            if not orec['accountants']:
+        for i0, i1, mesh in scene.mesh_segments:           # one chunk per bounce for a whole mesh
+            a, b = int(seg[i0]), int(seg[i1])
+            names = set(name for _, _, name in scene.optics[i0]['accountants'])
+            if b == a or not names:
                 continue
+            if child_off is not None:
+                raise NotImplementedError("TriangleMeshObject in a scene with two-children optics")
+            mesh._add_chunk(np.array(seg[i0:i1 + 1], dtype=np.int64), {k: src[k][..., a:b].clone() for k in names})
+        for s in scene.account_list:
+            orec = scene.optics[s]
             a, b = int(seg[s]), int(seg[s + 1])
             if b == a:
                 continue
