@@ -79,4 +79,7 @@ struct TrcScene {
     int32_t *d_cand = nullptr;         // leaf surfaces followed by unbounded surfaces (the walk's candidate list)
     int num_sms = 148;
     bool flat_only = false;            // every surface is of the flat family (kinds <= TRC_G_TRIANGLE)
+    float4 *d_tri32 = nullptr;         // float32 copies of the triangles (3 x float4 per surface) for the walk's
+                                       // conservative pre-test; null unless the scene is flat-only and has triangles
+    int32_t n_triangles = 0;
 };

@@ -159,6 +159,8 @@ struct WalkWarpShared {
     int best_s[kChunk];                       // its surface index (INT_MAX = none)
     float list[kListFields][kListCap];        // SoA: lanes read consecutive entries conflict-free
     unsigned queue[kQueueCap];                // packed (slot, leaf)
+    unsigned queue2[64];                      // candidates that passed the float32 triangle pre-test
+    int q2n;                                  // its fill (warp-uniform, kept here to spare a register)
     long long fifo[4];                        // chunk ids in consumption order (written by the prefetcher)
     double ring[kRing][6][32];                // cp.async landing zone: vertex + direction rows of 32 rays
 };
@@ -174,6 +176,7 @@ struct WalkShared {
 struct WalkParams {
     const TrcSurfaceRec *surfs;
     const double *pool;                       // scene table pool (apertures of the pool-based flat kinds)
+    const float4 *tri32;                      // float32 triangles for the pre-test, or null (see tri_prefilter)
     const uint4 *pair_a, *pair_b;
     int n_pairs;
     unsigned root_meta;
@@ -287,15 +290,15 @@ __device__ __forceinline__ float best_as_float(unsigned long long bits) {
 // Stage C: test queued (slot, leaf) candidates in float64, 32 at a time, and
 // fold them into the per-slot best (t, surface).  `all` drains the queue.
 template <bool kFlatOnly>
-__device__ __forceinline__ int flush_queue_body(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
-                                                int qn, bool all) {
+__device__ __forceinline__ int flush_queue_body(WalkWarpShared &sh, const unsigned *queue, const WalkParams &p,
+                                                int64_t chunk_base, int lane, int qn, bool all) {
     __syncwarp();
     if (p.debug & 1) qn = 0;
     while (qn >= 32 || (all && qn > 0)) {
         int take = min(32, qn);
         int base = qn - take;
         bool has = lane < take;
-        unsigned e = has ? sh.queue[base + lane] : 0u;
+        unsigned e = has ? queue[base + lane] : 0u;
         const int slot = (int)(e >> 24);
         const int first = (int)(e & kCandMask);
         const int cnt = has ? (int)((e >> 22) & 3u) + 1 : 0;
@@ -340,12 +343,82 @@ __device__ __forceinline__ int flush_queue_body(WalkWarpShared &sh, const WalkPa
 // fields, triangle meshes) inline the short flat-family test instead and run at higher occupancy.
 __device__ __noinline__ int flush_queue_generic(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
                                                 int qn, bool all) {
-    return flush_queue_body<false>(sh, p, chunk_base, lane, qn, all);
+    return flush_queue_body<false>(sh, sh.queue, p, chunk_base, lane, qn, all);
 }
+
+// Conservative float32 ray/triangle test (Moeller-Trumbore with running error bounds): false only
+// when the ray certainly misses the triangle, so that the float64 test of the reference
+// (triangular_face.py:59-72) would give inf as well.  With eps = 2^-24, A = |o|_1 + |p0|_1 and
+// |x|_1 the 1-norm: the numerators of u and v carry an absolute error below
+// K eps A |e1|_1 |d|_1 and K eps A |e0|_1 |d|_1, the determinant below K eps |e0|_1 |e1|_1 |d|_1
+// (rounding of origin, vertices and direction to float32, of the differences and of the
+// products; K = 16 leaves a factor > 2 over the first-order sums).  A determinant inside its
+// own error band decides nothing.  The plane distance t is not used: the float64 stage rules on it.
+__device__ __forceinline__ bool tri_prefilter(const float4 *tri, V3 v, V3 d) {
+    const float4 a = __ldg(tri), b = __ldg(tri + 1), c = __ldg(tri + 2);
+    if (c.y == 0.f) return true;                                 // not a triangle
+    const float ox = (float)v.x, oy = (float)v.y, oz = (float)v.z;
+    const float dx = (float)d.x, dy = (float)d.y, dz = (float)d.z;
+    const float e0x = a.w, e0y = b.x, e0z = b.y, e1x = b.z, e1y = b.w, e1z = c.x;
+    const float tx = ox - a.x, ty = oy - a.y, tz = oz - a.z;
+    const float px = dy * e1z - dz * e1y, py = dz * e1x - dx * e1z, pz = dx * e1y - dy * e1x;
+    const float det = e0x * px + e0y * py + e0z * pz;
+    const float qx = ty * e0z - tz * e0y, qy = tz * e0x - tx * e0z, qz = tx * e0y - ty * e0x;
+    const float sgn = det < 0.f ? -1.f : 1.f;
+    const float nu = sgn * (tx * px + ty * py + tz * pz);
+    const float nv = sgn * (dx * qx + dy * qy + dz * qz);
+    const float ad = fabsf(det);
+    const float keps = 16.f * 5.9604645e-8f;
+    const float A = fabsf(ox) + fabsf(oy) + fabsf(oz) + fabsf(a.x) + fabsf(a.y) + fabsf(a.z);
+    const float n0 = fabsf(e0x) + fabsf(e0y) + fabsf(e0z), n1 = fabsf(e1x) + fabsf(e1y) + fabsf(e1z);
+    const float nd = fabsf(dx) + fabsf(dy) + fabsf(dz);
+    const float err_u = keps * A * n1 * nd, err_v = keps * A * n0 * nd, err_d = keps * n0 * n1 * nd;
+    if (!(ad > 2.f * err_d)) return true;                        // grazing / degenerate / NaN: undecided
+    if (nu < -err_u || nv < -err_v) return false;
+    if (nu + nv - ad > err_u + err_v + err_d) return false;
+    return true;
+}
+
+// Flat-only scenes with triangles: queue entries first take the float32 pre-test, 32 at a time;
+// the few that pass wait in queue2 for the float64 stage.
+__device__ __forceinline__ int prefilter_queue(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
+                                               int qn, bool all) {
+    const unsigned lt_mask = (1u << lane) - 1u;
+    __syncwarp();
+    int q2n = sh.q2n;
+    while (qn >= 32 || (all && qn > 0)) {
+        int take = min(32, qn);
+        int base = qn - take;
+        bool has = lane < take;
+        unsigned e = has ? sh.queue[base + lane] : 0u;
+        bool pass = has;
+        if (has && ((e >> 22) & 3u) == 0u) {                     // single-surface entry holds the surface index
+            int64_t ray = chunk_base + (int)(e >> 24);
+            V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
+            V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
+            pass = tri_prefilter(p.tri32 + 3 * (size_t)(e & kCandMask), v, d);
+        }
+        if (q2n >= 32)                                           // leaves < 32: room for 32 more
+            q2n = flush_queue_body<true>(sh, sh.queue2, p, chunk_base, lane, q2n, false);
+        unsigned m = __ballot_sync(0xffffffffu, pass);
+        if (pass) sh.queue2[q2n + __popc(m & lt_mask)] = e;
+        q2n += __popc(m);
+        __syncwarp();
+        qn = base;
+    }
+    if (q2n >= 32 || (all && q2n > 0)) q2n = flush_queue_body<true>(sh, sh.queue2, p, chunk_base, lane, q2n, all);
+    if (lane == 0) sh.q2n = q2n;
+    __syncwarp();
+    return qn;
+}
+
 template <bool kFlatOnly>
 __device__ __forceinline__ int flush_queue(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
                                            int qn, bool all) {
-    if (kFlatOnly) return flush_queue_body<true>(sh, p, chunk_base, lane, qn, all);
+    if (kFlatOnly) {
+        if (p.tri32) return prefilter_queue(sh, p, chunk_base, lane, qn, all);
+        return flush_queue_body<true>(sh, sh.queue, p, chunk_base, lane, qn, all);
+    }
     return flush_queue_generic(sh, p, chunk_base, lane, qn, all);
 }
 
@@ -470,6 +543,7 @@ nearest_hit_walk_kernel(WalkParams p) {
         const int chunk_n = (int)min((int64_t)kChunk, p.n - chunk_base);
 
         for (int i = lane; i < kChunk; i += 32) { sh.best_t[i] = TRC_INF_BITS; sh.best_s[i] = INT_MAX; }
+        if (lane == 0) sh.q2n = 0;
         __syncwarp();
 
         int next = 0;          // rays of the chunk already through stage A   (warp-uniform)
@@ -657,6 +731,7 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     WalkParams p;
     p.surfs = sc->d_surfaces;
     p.pool = sc->d_tables;
+    p.tri32 = sc->d_tri32;
     p.pair_a = reinterpret_cast<const uint4 *>(sc->d_pair_a);
     p.pair_b = reinterpret_cast<const uint4 *>(sc->d_pair_b);
     p.n_pairs = sc->n_pairs; p.root_meta = sc->root_meta;

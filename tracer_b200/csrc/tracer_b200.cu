@@ -11,6 +11,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <math.h>
 #include <new>
@@ -36,6 +37,7 @@ extern "C" int trc_abi_version(void) { return TRC_ABI_VERSION; }
 extern "C" const char *trc_last_error(void) { return g_err; }
 
 // ------------------------------------------------------------------- scene
+static cudaError_t build_tri32(TrcScene *sc);
 extern "C" int trc_scene_create(const TrcSurfaceRec *surfaces, int32_t n_surfaces,
                                 const double *tables, int32_t n_table, TrcScene **out) {
     if (!surfaces || n_surfaces <= 0 || !out) return fail(TRC_ERR_BAD_ARGUMENT, "trc_scene_create: bad argument%s");
@@ -59,6 +61,12 @@ extern "C" int trc_scene_create(const TrcSurfaceRec *surfaces, int32_t n_surface
         e = cudaMalloc(&sc->d_tables, sizeof(double) * (size_t)n_table);
         if (e == cudaSuccess) e = cudaMemcpy(sc->d_tables, tables, sizeof(double) * (size_t)n_table, cudaMemcpyHostToDevice);
     }
+    for (int32_t i = 0; i < n_surfaces; ++i)
+        if (surfaces[i].gkind == TRC_G_TRIANGLE) ++sc->n_triangles;
+    if (e == cudaSuccess && sc->flat_only && sc->n_triangles > 0 && !getenv("TRC_NO_TRI_PREFILTER")) {
+        e = cudaMalloc(&sc->d_tri32, sizeof(float4) * 3 * (size_t)n_surfaces);
+        if (e == cudaSuccess) e = build_tri32(sc);
+    }
     int dev = 0;
     if (e == cudaSuccess) e = cudaGetDevice(&dev);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sc->num_sms, cudaDevAttrMultiProcessorCount, dev);
@@ -74,6 +82,7 @@ extern "C" int trc_scene_destroy(TrcScene *sc) {
     if (!sc) return TRC_OK;
     cudaFree(sc->d_surfaces);
     cudaFree(sc->d_tables);
+    cudaFree(sc->d_tri32);
     cudaFree(sc->d_nodes);
     cudaFree(sc->d_pair_a);
     cudaFree(sc->d_pair_b);
@@ -86,6 +95,33 @@ extern "C" int trc_scene_destroy(TrcScene *sc) {
 }
 
 extern "C" int32_t trc_scene_num_surfaces(const TrcScene *sc) { return sc ? sc->n_surfaces : 0; }
+
+// Float32 copy of every triangle for the tree walk's pre-test (nearest.cu, tri_prefilter):
+// [p0.x p0.y p0.z e0.x] [e0.y e0.z e1.x e1.y] [e1.z flag - -], p0 = frame origin, e = R * verts
+// (triangular_face.py:60-61), flag = 1 for a triangle, 0 for any other kind (never pre-tested).
+__global__ void build_tri32_kernel(const TrcSurfaceRec *s, float4 *out, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double *f = s[i].frame, *gp = s[i].gp;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a, c = a;
+    if (s[i].gkind == TRC_G_TRIANGLE) {
+        double e0[3], e1[3];
+        for (int k = 0; k < 3; ++k) {
+            e0[k] = f[4 * k] * gp[0] + f[4 * k + 1] * gp[1] + f[4 * k + 2] * gp[2];
+            e1[k] = f[4 * k] * gp[3] + f[4 * k + 1] * gp[4] + f[4 * k + 2] * gp[5];
+        }
+        a = make_float4((float)f[3], (float)f[7], (float)f[11], (float)e0[0]);
+        b = make_float4((float)e0[1], (float)e0[2], (float)e1[0], (float)e1[1]);
+        c = make_float4((float)e1[2], 1.f, 0.f, 0.f);
+    }
+    out[3 * (size_t)i] = a; out[3 * (size_t)i + 1] = b; out[3 * (size_t)i + 2] = c;
+}
+
+static cudaError_t build_tri32(TrcScene *sc) {
+    if (!sc->d_tri32) return cudaSuccess;
+    build_tri32_kernel<<<(sc->n_surfaces + 255) / 256, 256>>>(sc->d_surfaces, sc->d_tri32, sc->n_surfaces);
+    return cudaDeviceSynchronize();
+}
 
 __global__ void update_frames_kernel(TrcSurfaceRec *s, const double *fr, const double *iv, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -106,6 +142,7 @@ extern "C" int trc_scene_update_frames(TrcScene *sc, const double *frames12, con
     if (e == cudaSuccess) {
         update_frames_kernel<<<(n * 12 + 255) / 256, 256>>>(sc->d_surfaces, tmp, tmp + 12 * (size_t)n, n);
         e = cudaDeviceSynchronize();
+        if (e == cudaSuccess) e = build_tri32(sc);
     }
     cudaFree(tmp);
     if (e != cudaSuccess) return fail(TRC_ERR_CUDA, "trc_scene_update_frames: %s", cudaGetErrorString(e));
