@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 10
+#define TRC_ABI_VERSION 11
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -106,7 +106,19 @@ typedef enum TrcOpticsKind {
                                      fresnel_to_attenuating (optics.py:41-81): op: n1; table = wavelengths[n],
                                      n2[n], k2[n] (complex index of the conductor, linear in wavelength);
                                      specular, E' = E (R_p + R_s) / 2; NaN outside the table's range */
-    TRC_O_KIND_COUNT = 13
+    TRC_O_REFRACTIVE = 13,        /* RefractiveHomogenous :1186-1296 (+ Refractive :726-858, optics.refractions /
+                                     optics.fresnel optics.py:13-39,159-192) and RefractiveTransmissiveHomogenous
+                                     :1323-1345 (Absorbant.attenuate :874-889 with imposed coefficients).
+                                     op: n_a, n_b (the two indices, _ref_idxs), single_ray (1/0), sigma (< 0: None),
+                                     n_att (0 none, 1 or 2 imposed attenuation coefficients), a_c[0], a_c[1], scaling.
+                                     Needs the parent bundle's ref_index column (d_ref_index).  Per hit, with
+                                     m1 = the ray's index and m2 = the other one: TWO child slots, block A = the
+                                     reflected ray, block B = the refracted ray (as TRC_O_PERIODIC lays them out).
+                                     single_ray: the ray goes to A when draw <= R (R = 1 under total internal
+                                     reflection) else to B, and the other slot is VOID; otherwise A gets E R and
+                                     B gets E (1 - R), B void under total internal reflection.  Void slots carry
+                                     d_cull = 2 and are not children: the caller drops them. */
+    TRC_O_KIND_COUNT = 14
 } TrcOpticsKind;
 
 /* Surface flag bits. */
@@ -321,6 +333,13 @@ typedef struct TrcOpticsArgs {
     const int32_t *d_slot_surf;
     const int64_t *d_seg;
     const int64_t *d_child_off;
+    /* RayBundle.ref_index (ray_bundle.py:33): the refractive index each parent ray travels in, and the
+     * same column of the children (inherited, or the medium entered by a refracted ray).  Both NULL
+     * unless the bundle carries the property; TRC_O_REFRACTIVE surfaces need them.  d_n_void counts the
+     * void child slots (d_cull = 2) left by TRC_O_REFRACTIVE surfaces. */
+    const double *d_ref_index;
+    double *d_out_ref_index;
+    int64_t *d_n_void;
 } TrcOpticsArgs;
 int trc_optics(const TrcScene *scene, const TrcOpticsArgs *args, void *stream);
 

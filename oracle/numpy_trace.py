@@ -11,9 +11,9 @@ from .numpy_engine import (_names, find_intersections, reflections, rotation_to_
 class Bundle(object):
     """Minimal SoA bundle of the oracle (tracer/ray_bundle.py:6-63)."""
 
-    def __init__(self, vertices, directions, energy, parents=None, wavelengths=None):
+    def __init__(self, vertices, directions, energy, parents=None, wavelengths=None, ref_index=None):
         self.vertices, self.directions, self.energy = vertices, directions, energy
-        self.parents, self.wavelengths = parents, wavelengths
+        self.parents, self.wavelengths, self.ref_index = parents, wavelengths, ref_index
 
     @property
     def n(self):
@@ -22,15 +22,17 @@ class Bundle(object):
     def take(self, idx):
         return Bundle(self.vertices[:, idx], self.directions[:, idx], self.energy[idx],
                       None if self.parents is None else self.parents[idx],
-                      None if self.wavelengths is None else self.wavelengths[idx])
+                      None if self.wavelengths is None else self.wavelengths[idx],
+                      None if self.ref_index is None else self.ref_index[idx])
 
     @staticmethod
     def concat(bs):
         if not bs:
             return Bundle(N.zeros((3, 0)), N.zeros((3, 0)), N.array([]), N.array([], dtype=int))
         wl = None if bs[0].wavelengths is None else N.hstack([b.wavelengths for b in bs])
+        ri = None if bs[0].ref_index is None else N.hstack([b.ref_index for b in bs])
         return Bundle(N.hstack([b.vertices for b in bs]), N.hstack([b.directions for b in bs]),
-                      N.hstack([b.energy for b in bs]), N.hstack([b.parents for b in bs]), wl)
+                      N.hstack([b.energy for b in bs]), N.hstack([b.parents for b in bs]), wl, ri)
 
     # reference-style getters so tests can treat oracle and engine bundles alike
     def get_vertices(self):
@@ -44,6 +46,9 @@ class Bundle(object):
 
     def get_parents(self):
         return self.parents
+
+    def get_ref_index(self):
+        return self.ref_index
 
     def get_num_rays(self):
         return self.n
@@ -74,6 +79,83 @@ _KNOWN = ('Transparent', 'OneSidedReflective', 'Reflective', 'OneSidedRealReflec
           'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM', 'LambertianAbsorbant',
           'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise', 'PeriodicBoundary',
           'FresnelConductorHomogenous')
+
+
+def fresnel(ray_dirs, normals, n1, n2):
+    """optics.fresnel, optics.py:13-39"""
+    theta_in = N.arccos(N.abs((normals * ray_dirs).sum(axis=0)))
+    foo = N.cos(theta_in)
+    bar = N.sqrt(1 - (n1 / n2 * N.sin(theta_in)) ** 2)
+    Rs = ((n1 * foo - n2 * bar) / (n1 * foo + n2 * bar)) ** 2
+    Rp = ((n1 * bar - n2 * foo) / (n1 * bar + n2 * foo)) ** 2
+    return (Rs + Rp) / 2
+
+
+def refractions(n1, n2, ray_dirs, normals):
+    """optics.refractions, optics.py:159-192: (mask of rays not totally reflected, their new directions)"""
+    n = N.broadcast_arrays(n2 / n1, ray_dirs[0])[0]
+    cos1 = (normals * ray_dirs).sum(axis=0)
+    refracted = cos1 ** 2 >= 1. - n ** 2
+    cos1, ray_dirs, normals, n = cos1[refracted], ray_dirs[:, refracted], normals[:, refracted], n[refracted]
+    refr_dirs = (ray_dirs - cos1 * normals) / n
+    cos2 = N.sqrt(1 - 1. / n ** 2 * (1. - cos1 ** 2))
+    refr_dirs += normals * cos2 * N.where(cos1 < 0., -1, 1)
+    return refracted, refr_dirs
+
+
+def refractive_children(base, hit, d, normals, energy, sel, wl, m1, v_parent, all_wl, all_ri):
+    """RefractiveHomogenous.__call__ (optics_callables.py:842-858 through :1222-1296) and, for
+    RefractiveTransmissiveHomogenous (:1342-1345), Absorbant.attenuate (:874-889) with imposed
+    coefficients.  Returns the child Bundle in [reflected][refracted] order.
+
+    In single_ray mode the reference inherits the columns it does not set (ref_index of the
+    reflected rays, wavelengths of both kinds) through ``rays.inherit(sel_refl, ...)`` where
+    sel_refl = argwhere(refl) counts positions WITHIN the surface's selection (:1257-1258) but
+    indexes the whole incoming bundle; ``all_wl`` / ``all_ri`` are those whole-bundle columns."""
+    h = len(sel)
+    normals = normals.copy()
+    if base._sigma is not None:                                    # :1229-1241
+        th = N.random.normal(scale=base._sigma, size=h)
+        phi = N.random.uniform(low=0., high=2. * N.pi, size=h)
+        errors = N.vstack((N.sin(th) * N.cos(phi), N.sin(th) * N.sin(phi), N.cos(th)))
+        rots = rotation_to_z(normals.T)
+        if rots.ndim == 2:
+            rots = [rots]
+        for i in range(h):
+            normals[:, i] = N.dot(rots[i], errors[:, i])
+    n2 = N.where(m1 == base._ref_idxs[0], base._ref_idxs[1], base._ref_idxs[0])     # :1217-1218
+    refr, out_dirs = refractions(m1, n2, d, normals)
+    R = N.ones(h)
+    R[refr] = fresnel(d[:, refr], normals[:, refr], m1[refr], n2[refr])             # :841-843
+    take = (lambda a, m: None if a is None else a[m])
+    if base._single_ray:                                           # :1252-1281
+        refl = N.random.uniform(size=R.shape) <= R
+        dirs_refr = N.zeros((3, h))
+        dirs_refr[:, refr] = out_dirs
+        parts = []
+        sel_refl, sel_refr = N.argwhere(refl).flatten(), N.argwhere(~refl).flatten()
+        if refl.any():
+            parts.append(Bundle(hit[:, refl], reflections(d[:, refl], normals[:, refl]), energy[refl], sel[refl],
+                                take(all_wl, sel_refl), all_ri[sel_refl]))
+        if (~refl).any():
+            parts.append(Bundle(hit[:, ~refl], dirs_refr[:, ~refl], energy[~refl], sel[~refl],
+                                take(all_wl, sel_refr), n2[~refl]))
+    else:                                                          # :1284-1294
+        parts = [Bundle(hit, reflections(d, normals), energy * R, sel, wl, m1),
+                 Bundle(hit[:, refr], out_dirs, energy[refr] * (1. - R[refr]), sel[refr], take(wl, refr), n2[refr])]
+    child = Bundle.concat(parts)
+    if getattr(base, 'a_c', None) is not None:                     # attenuate :874-889
+        # parents index the incoming bundle; v_parent / m1 are given per selected ray, so map back
+        pos = N.searchsorted(sel, child.parents)
+        path = N.sqrt(N.sum((child.vertices - v_parent[:, pos]) ** 2, axis=0))
+        if base._scaling != 1.:
+            path = path * base._scaling
+        if len(base.a_c) > 1:
+            a_c = base.a_c[N.array(m1[pos] == base._ref_idxs[1], dtype=int)]
+        else:
+            a_c = base.a_c
+        child.energy = child.energy * N.exp(-a_c * path)
+    return child
 
 
 def _iam(base, d, normals, energy):
@@ -253,8 +335,14 @@ class OracleEngine(object):
                 wl = N.asarray(bundle.get_wavelengths())
             except (KeyError, AttributeError):
                 wl = None
+        ri = None
+        if hasattr(bundle, 'has_property') and bundle.has_property('ref_index'):
+            try:
+                ri = N.asarray(bundle.get_ref_index(), float)
+            except (KeyError, AttributeError):
+                ri = None
         bund = Bundle(N.asarray(bundle.get_vertices(), float), N.asarray(bundle.get_directions(), float),
-                      N.asarray(bundle.get_energy(), float), None, wl)
+                      N.asarray(bundle.get_energy(), float), None, wl, ri)
         self.tree = [bund] if tree else []
         self.front_surfs = []
         self.tallies = [dict() for _ in surfaces]
@@ -277,9 +365,19 @@ class OracleEngine(object):
                 wl_in = None if bund.wavelengths is None else bund.wavelengths[sel]
                 base_opt, _ = _unwrap(surf._opt)
                 if 'PeriodicBoundary' in _names(base_opt):          # optics_callables.py:703-721
-                    stub = Bundle(hit, d_in.copy(), N.zeros(len(sel)), sel, wl_in)
-                    moved = Bundle(hit + base_opt.period * normals, d_in.copy(), e_in.copy(), sel, wl_in)
+                    ri_in = None if bund.ref_index is None else bund.ref_index[sel]
+                    stub = Bundle(hit, d_in.copy(), N.zeros(len(sel)), sel, wl_in, ri_in)
+                    moved = Bundle(hit + base_opt.period * normals, d_in.copy(), e_in.copy(), sel, wl_in, ri_in)
                     child = Bundle.concat([stub, moved])
+                    record.append(child)
+                    delete = child.energy <= min_energy
+                    weak.append(delete)
+                    outg.append(child.take(N.nonzero(~delete)[0]) if delete.any() else child)
+                    continue
+                if 'RefractiveHomogenous' in _names(base_opt):      # row O8
+                    child = refractive_children(base_opt, hit, d_in, normals, e_in, sel, wl_in,
+                                                bund.ref_index[sel], bund.vertices[:, sel],
+                                                bund.wavelengths, bund.ref_index)
                     record.append(child)
                     delete = child.energy <= min_energy
                     weak.append(delete)
@@ -287,7 +385,7 @@ class OracleEngine(object):
                     continue
                 dirs, e_out = apply_optics(surf._opt, d_in, normals, e_in, wl_in, surf._temp_frame[:3, 2],
                                            v_parent=bund.vertices[:, sel], hit=hit)
-                child = Bundle(hit, dirs, e_out, sel, wl_in)
+                child = Bundle(hit, dirs, e_out, sel, wl_in, None if bund.ref_index is None else bund.ref_index[sel])
                 self._count(s_idx, surf, hit, d_in, normals, e_in, e_out, wl_in, apply_optics.attenuations)
                 record.append(child)
                 delete = e_out <= min_energy

@@ -32,6 +32,7 @@ TRACE_CASES = {
     'c6_optics_zoo': (scenes.c6_optics_zoo, dict(n_rays=3000), 19, 5, 1e-10),
     'c7_periodic_cell': (scenes.c7_periodic_cell, dict(n_rays=2000), 20, 6, 1e-10),
     'c8_fresnel_conductor': (scenes.c8_fresnel_conductor, dict(n_rays=2000), 21, 6, 1e-10),
+    'c9_refractive': (scenes.c9_refractive, dict(n_rays=2000), 22, 7, 1e-3 * 1000. * np.pi * 1.21 / 2000),
 }
 ZOO_RAYS = 4000
 ZOO_SEED = 99
@@ -57,6 +58,8 @@ def trace_reference(name):
         out['e%d' % k] = b.get_energy()
         if k > 0:
             out['p%d' % k] = b.get_parents()
+        if name == 'c9_refractive':
+            out['r%d' % k] = b.get_ref_index()
     for s, surf in enumerate(asm.get_surfaces()):
         opt = surf.get_optics_manager()
         if hasattr(opt, 'get_all_hits'):
@@ -102,10 +105,13 @@ def fluxmap_reference():
 
 def main():
     ref_import.enable()
-    for name in TRACE_CASES:
+    only = sys.argv[1:]          # optional: names of the trace cases to (re)generate, nothing else
+    for name in (only or TRACE_CASES):
         data = trace_reference(name)
         np.savez_compressed(os.path.join(HERE, name + '.npz'), **data)
         print(name, 'bundles:', [data['v%d' % k].shape[1] for k in range(data['n_tree'])])
+    if only:
+        return
     np.savez_compressed(os.path.join(HERE, 'fluxmaps.npz'), **fluxmap_reference())
     z = zoo_reference()
     np.savez_compressed(os.path.join(HERE, 'gm_zoo.npz'), **z)

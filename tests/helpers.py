@@ -37,6 +37,8 @@ def compare_tree(gold, tree, n_levels=None, rtol=RTOL):
         close(b.get_vertices(), gold['v%d' % k], rtol, f'level {k} vertices')
         close(b.get_directions(), gold['d%d' % k], rtol, f'level {k} directions')
         close(b.get_energy(), gold['e%d' % k], rtol, f'level {k} energy')
+        if 'r%d' % k in gold.files:
+            assert np.array_equal(np.asarray(b.get_ref_index()), gold['r%d' % k]), f'level {k}: ref_index differs'
 
 
 def golden_accountants(gold):

@@ -273,6 +273,43 @@ def c7_periodic_cell(T, n_rays=2000):
     return asm, source
 
 
+def c9_refractive(T, n_rays=2000):
+    """Refraction: a glass slab that splits every ray into a reflected and a
+    refracted child (single_ray=False), a glass ball that picks one of them per ray with a
+    rough surface (single_ray=True, sigma), an absorbing slab (RefractiveTransmissiveHomogenous,
+    one attenuation coefficient per medium) and a diffuse receiver underneath.  The source
+    bundle carries ref_index = 1 (air)."""
+    oc = T.optics_callables
+    sg = T.spatial_geometry
+    slab = T.object.AssembledObject(surfs=[
+        T.surface.Surface(T.flat_surface.RectPlateGM(1.2, 2.), oc.RefractiveHomogenous(1., 1.5, single_ray=False)),
+        T.surface.Surface(T.flat_surface.RectPlateGM(1.2, 2.), oc.RefractiveHomogenous(1., 1.5, single_ray=False),
+                          location=np.r_[0., 0., -0.3])],
+        transform=sg.translate(-0.7, 0., 0.))
+    ball = T.object.AssembledObject(surfs=[
+        T.surface.Surface(T.sphere_surface.SphericalGM(0.35), oc.RefractiveHomogenous(1., 1.33, single_ray=True, sigma=2e-3))],
+        transform=sg.translate(0.45, 0.5, -0.1))
+    tinted = T.object.AssembledObject(surfs=[
+        T.surface.Surface(T.flat_surface.RectPlateGM(0.9, 0.9),
+                          oc.RefractiveTransmissiveHomogenous(1., 1.45, [0.05, 2.5], single_ray=True)),
+        T.surface.Surface(T.flat_surface.RectPlateGM(0.9, 0.9),
+                          oc.RefractiveTransmissiveHomogenous(1., 1.45, [0.05, 2.5], single_ray=True),
+                          location=np.r_[0., 0., -0.25])],
+        transform=np.dot(sg.translate(0.5, -0.55, 0.), sg.rotx(0.1)))
+    floor = T.object.AssembledObject(
+        surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(4., 4.), oc.LambertianReceiver(0.7))],
+        transform=sg.translate(0., 0., -0.8))
+    asm = T.assembly.Assembly(objects=[slab, ball, tinted, floor])
+
+    def source():
+        direction = np.r_[0.25, -0.1, -1.]
+        direction = direction / np.sqrt(np.sum(direction ** 2))
+        b = T.sources.disk_bundle(n_rays, np.c_[[-0.2, 0.05, 0.9]], direction, 1.1, 0.2, flux=1000.)
+        return T.ray_bundle.RayBundle(vertices=b.get_vertices(), directions=b.get_directions(),
+                                      energy=b.get_energy(), ref_index=np.ones(n_rays))
+    return asm, source
+
+
 def _optical_constants(T):
     """The reference keeps its materials outside the tracer package."""
     if T.pkg == 'tracer':

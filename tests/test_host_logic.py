@@ -131,7 +131,11 @@ def test_optics_name_factory():
     with pytest.raises(AttributeError):
         oc.NoSuchOpticsReceiver
     with pytest.raises(NotImplementedError):
-        oc.RefractiveHomogenous
+        oc.RefractiveScatteringHomogenous
+    rh = oc.RefractiveHomogenous(1., 1.5, single_ray=False, sigma=1e-3)
+    assert rh._ref_idxs == (1., 1.5) and rh._single_ray is False and rh._sigma == 1e-3
+    rt = oc.RefractiveTransmissiveHomogenous(1., 1.5, [0.1, 2.])
+    assert isinstance(rt, oc.RefractiveHomogenous) and list(rt.a_c) == [0.1, 2.] and rt._scaling == 1.
     with pytest.raises(TypeError):
         r(None, None, None)            # descriptions are not callable on the host
 
@@ -282,3 +286,32 @@ def test_load_stl_binary_and_ascii(tmp_path):
         'facet normal 0 0 0\n outer loop\n' + ''.join('  vertex %r %r %r\n' % tuple(float(c) for c in v) for v in t) +
         ' endloop\nendfacet\n' for t in tris) + 'endsolid x\n')
     assert np.array_equal(T.stl_utils.load_stl(str(q)), tris.astype(float))
+
+
+def test_refractive_records():
+    """Scene compiler, row O8: op = n_a, n_b, single_ray, sigma (-1 = None), n_att, a_c0, a_c1, scaling;
+    two child slots per hit; accountants and complex indices are refused."""
+    from tracer_b200 import _lib as L
+    from tracer_b200.scene import CompiledScene
+    oc = T.optics_callables
+    flat = T.flat_surface.RectPlateGM
+
+    def scene(*optics):
+        objs = [T.object.AssembledObject(surfs=[T.surface.Surface(flat(1., 1.), o, location=np.r_[0., 0., -float(k)])])
+                for k, o in enumerate(optics)]
+        return CompiledScene(T.assembly.Assembly(objects=objs), upload=False)
+    sc = scene(oc.RefractiveHomogenous(1., 1.5), oc.RefractiveHomogenous(1.33, 1., single_ray=False, sigma=2e-3),
+               oc.RefractiveTransmissiveHomogenous(1., 1.45, [0.05, 2.5], scaling=10.), oc.Reflective(0.1))
+    r = sc.records
+    assert list(r['okind']) == [L.O_REFRACTIVE] * 3 + [L.O_REFLECTIVE]
+    assert list(r['op'][0]) == [1., 1.5, 1., -1., 0., 0., 0., 0.]
+    assert list(r['op'][1]) == [1.33, 1., 0., 2e-3, 0., 0., 0., 0.]
+    assert list(r['op'][2]) == [1., 1.45, 1., -1., 2., 0.05, 2.5, 10.]
+    assert list(sc.children_per_hit) == [2, 2, 2, 1] and sc.has_split and sc.has_refractive
+    assert not scene(oc.Reflective(0.1)).has_refractive
+    with pytest.raises(NotImplementedError):
+        scene(oc.RefractiveHomogenousReceiver(1., 1.5))
+    with pytest.raises(NotImplementedError):
+        scene(oc.RefractiveHomogenous(1., 1.5 + 0.1j))
+    with pytest.raises(NotImplementedError):
+        scene(oc.RefractiveTransmissiveHomogenous(1., 1.5, None))

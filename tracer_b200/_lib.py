@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtracer_b200.so")
 
-ABI_VERSION = 10
+ABI_VERSION = 11
 
 # enum TrcGeomKind
 (G_FLAT_INFINITE, G_RECT_PLATE, G_RECT_EXTRUDED, G_ROUND_PLATE, G_TRIANGLE, G_PARABOLOID,
@@ -24,7 +24,7 @@ ABI_VERSION = 10
 (O_TRANSPARENT, O_REFLECTIVE, O_REAL_REFLECTIVE, O_LAMBERTIAN, O_LAMBERTIAN_SPECULAR,
  O_LAMB_DIRECTIONAL, O_REFLECTIVE_SPECTRAL, O_LAMBSPEC_DIRECTIONAL,
  O_LAMB_DIRECTIONAL_SPECTRAL, O_LAMB_PIECEWISE_SPEC, O_LAMBERTIAN_ABSORBANT, O_PERIODIC,
- O_FRESNEL_CONDUCTOR) = range(13)
+ O_FRESNEL_CONDUCTOR, O_REFRACTIVE) = range(14)
 F_ONE_SIDED = 1
 F_UNBOUNDED = 2
 F_IAM = 4
@@ -64,6 +64,7 @@ class OpticsArgs(C.Structure):
         ("d_dirs_in", C.c_void_p), ("d_out_wavelengths", C.c_void_p), ("d_cull", C.c_void_p),
         ("d_n_cull", C.c_void_p), ("d_attenuated", C.c_void_p),
         ("d_slot_surf", C.c_void_p), ("d_seg", C.c_void_p), ("d_child_off", C.c_void_p),
+        ("d_ref_index", C.c_void_p), ("d_out_ref_index", C.c_void_p), ("d_n_void", C.c_void_p),
     ]
 
 

@@ -30,6 +30,9 @@ struct OpticsParams {
     double *attenuated;
     const int32_t *slot_surf;
     const int64_t *seg, *child_off;
+    const double *ref_index;
+    double *o_ref_index;
+    unsigned long long *n_void;
 };
 
 // Philox draws in the units the reference's numpy calls produce
@@ -64,8 +67,58 @@ __device__ __forceinline__ void philox_draws(const TrcSurfaceRec *s, uint64_t se
         u[0] = a; u[1] = two_pi * b; u[2] = c;
         break;
     }
+    case TRC_O_REFRACTIVE: {
+        double a, b, c, e;
+        normal2(seed, q, bounce, 0, a, b);
+        uniform2(seed, q, bounce, 1, c, e);
+        u[0] = a * (s->op[3] > 0.0 ? s->op[3] : 0.0); u[1] = two_pi * c; u[2] = e;
+        break;
+    }
     default: break;
     }
+}
+
+// TRC_O_REFRACTIVE: two child slots per hit (block A reflected, block B refracted), either of
+// which may be void (d_cull = 2).  Out of line: keeps the common optics path at its register count.
+__device__ __noinline__ void refractive_slot(const OpticsParams &p, const TrcSurfaceRec *s, int64_t q, int sidx,
+                                             int64_t r, V3 v, V3 d, double e_in, double wl, V3 hit, V3 n,
+                                             const double *u) {
+    double m1 = p.ref_index[r];
+    RefractOut ro = apply_refractive(s, d, n, e_in, m1, u, v, hit);
+    int64_t first = p.seg[sidx];
+    // single_ray mode inherits the columns it does not set from bundle position (rank of the hit
+    // among the surface's hits), not from the parent ray: rays.inherit(argwhere(refl), ...) at
+    // optics_callables.py:1257-1278 -- reproduced as the reference behaves
+    double m_inherit = m1;
+    if (s->op[2] != 0.0) {
+        m_inherit = p.ref_index[q - first];
+        if (p.wavelengths) wl = p.wavelengths[q - first];
+    }
+    int64_t ca = p.child_off[sidx] + (q - first), cb = ca + (p.seg[sidx + 1] - first);
+    int n_weak = 0, n_gone = 0;
+    for (int side = 0; side < 2; ++side) {
+        int64_t c = side ? cb : ca;
+        bool has = side ? ro.has_refr : ro.has_refl;
+        V3 od = side ? ro.dir_refr : ro.dir_refl;
+        double oe = has ? (side ? ro.e_refr : ro.e_refl) : 0.0;
+        p.o_vert[c] = hit.x; p.o_vert[p.ld_out + c] = hit.y; p.o_vert[2 * p.ld_out + c] = hit.z;
+        p.o_dir[c] = od.x; p.o_dir[p.ld_out + c] = od.y; p.o_dir[2 * p.ld_out + c] = od.z;
+        p.o_energy[c] = oe;
+        p.o_parents[c] = r;
+        p.o_ref_index[c] = side ? ro.m2 : m_inherit;
+        if (p.o_wavelengths) p.o_wavelengths[c] = wl;
+        bool weak = has && oe <= p.min_energy;
+        if (p.cull) p.cull[c] = has ? (weak ? 1 : 0) : 2;
+        n_weak += weak ? 1 : 0;
+        n_gone += has ? 0 : 1;
+    }
+    if (p.absorbed) p.absorbed[q] = e_in - ((ro.has_refl ? ro.e_refl : 0.0) + (ro.has_refr ? ro.e_refr : 0.0));
+    if (p.normals) { p.normals[q] = n.x; p.normals[p.ld_out + q] = n.y; p.normals[2 * p.ld_out + q] = n.z; }
+    if (p.e_in) p.e_in[q] = e_in;
+    if (p.attenuated) p.attenuated[q] = 0.0;
+    if (p.dirs_in) { p.dirs_in[q] = d.x; p.dirs_in[p.ld_out + q] = d.y; p.dirs_in[2 * p.ld_out + q] = d.z; }
+    if (n_weak && p.n_cull) atomicAdd(p.n_cull, (unsigned long long)n_weak);
+    if (n_gone && p.n_void) atomicAdd(p.n_void, (unsigned long long)n_gone);
 }
 
 // One thread per child slot q (surface-major, parent-minor order).  Reads the
@@ -76,6 +129,8 @@ __device__ __forceinline__ void philox_draws(const TrcSurfaceRec *s, uint64_t se
 #ifndef TRC_OPTICS_MIN_CTAS
 #define TRC_OPTICS_MIN_CTAS 4
 #endif
+// kRefractive: the scene has TRC_O_REFRACTIVE surfaces (the common instantiation does not carry that code).
+template <bool kRefractive>
 __global__ void __launch_bounds__(256, TRC_OPTICS_MIN_CTAS)
 optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict__ tables, OpticsParams p) {
     int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -103,6 +158,9 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
         } else {
             philox_draws(s, p.seed, p.bounce, (uint64_t)q, u);
         }
+        if (kRefractive && s->okind == TRC_O_REFRACTIVE) {
+            refractive_slot(p, s, q, sidx, r, v, d, e_in, wl, hit, n, u);
+        } else {
         OpticsOut o = apply_optics(s, tables, d, n, e_in, wl, u, v, hit);
         if (s->flags & TRC_F_ONE_SIDED) {
             // OneSided*: rays arriving along +z of the surface lose all energy
@@ -128,6 +186,7 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
             p.o_dir[c2] = d.x; p.o_dir[p.ld_out + c2] = d.y; p.o_dir[2 * p.ld_out + c2] = d.z;
             p.o_energy[c2] = e_in;
             p.o_parents[c2] = r;
+            if (p.o_ref_index) p.o_ref_index[c2] = p.ref_index[r];
             if (p.o_wavelengths) p.o_wavelengths[c2] = wl;
             bool weak2 = e_in <= p.min_energy;
             if (p.cull) p.cull[c2] = weak2 ? 1 : 0;
@@ -137,6 +196,7 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
         p.o_dir[c] = o.dir.x; p.o_dir[p.ld_out + c] = o.dir.y; p.o_dir[2 * p.ld_out + c] = o.dir.z;
         p.o_energy[c] = e_first;
         p.o_parents[c] = r;
+        if (p.o_ref_index) p.o_ref_index[c] = p.ref_index[r];
         if (p.absorbed) p.absorbed[q] = e_in - o.energy;
         if (p.normals) { p.normals[q] = n.x; p.normals[p.ld_out + q] = n.y; p.normals[2 * p.ld_out + q] = n.z; }
         if (p.e_in) p.e_in[q] = e_in;
@@ -145,6 +205,7 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
         if (p.o_wavelengths) p.o_wavelengths[c] = wl;
         culled = e_first <= p.min_energy;
         if (p.cull) p.cull[c] = culled ? 1 : 0;
+        }
     }
     if (p.n_cull) {
         unsigned m = __ballot_sync(0xffffffffu, culled);
@@ -321,9 +382,19 @@ extern "C" int trc_optics(const TrcScene *sc, const TrcOpticsArgs *a, void *stre
     p.n_cull = reinterpret_cast<unsigned long long *>(a->d_n_cull);
     p.attenuated = a->d_attenuated;
     p.slot_surf = a->d_slot_surf; p.seg = a->d_seg; p.child_off = a->d_child_off;
+    p.ref_index = a->d_ref_index; p.o_ref_index = a->d_out_ref_index;
+    p.n_void = reinterpret_cast<unsigned long long *>(a->d_n_void);
+    if ((p.ref_index == nullptr) != (p.o_ref_index == nullptr))
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: d_ref_index and d_out_ref_index go together%s");
+    if (sc->has_refractive && (!p.ref_index || !p.child_off))
+        return fail(TRC_ERR_BAD_ARGUMENT,
+                    "trc_optics: a scene with TRC_O_REFRACTIVE surfaces needs d_ref_index and d_child_off%s");
     if (p.child_off && !p.seg) return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: d_child_off needs d_seg%s");
     int64_t blocks = (a->h + 255) / 256;
-    optics_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(sc->d_surfaces, sc->d_tables, p);
+    if (sc->has_refractive)
+        optics_kernel<true><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(sc->d_surfaces, sc->d_tables, p);
+    else
+        optics_kernel<false><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(sc->d_surfaces, sc->d_tables, p);
     return check_launch("optics");
 }
 

@@ -82,4 +82,6 @@ struct TrcScene {
     float4 *d_tri32 = nullptr;         // float32 copies of the triangles (3 x float4 per surface) for the walk's
                                        // conservative pre-test; null unless the scene is flat-only and has triangles
     int32_t n_triangles = 0;
+    bool has_refractive = false;       // some surface is TRC_O_REFRACTIVE: the optics need the ref_index column
+    bool has_split = false;            // some surface emits two child slots per hit (periodic / refractive)
 };

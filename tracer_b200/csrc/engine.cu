@@ -86,6 +86,9 @@ extern "C" int trc_bounce(const TrcScene *sc, const TrcBounceArgs *a, TrcBounceR
     if (!sc || !a || !r || a->n < 0 || a->capacity < 0 || !a->d_keep || !a->d_scratch ||
         !a->d_absorbed_per_surface || !a->d_hits_per_surface)
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_bounce: bad argument%s");
+    if (sc->has_split)
+        return fail(TRC_ERR_UNSUPPORTED_KIND,
+                    "trc_bounce: scenes with two-children optics (periodic, refractive) use the step-by-step calls%s");
     cudaStream_t st = (cudaStream_t)stream;
     const int32_t S = sc->n_surfaces;
     const int64_t n = a->n, cap = a->capacity;

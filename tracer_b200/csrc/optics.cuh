@@ -96,6 +96,67 @@ __device__ __forceinline__ double interp2(double th, double wl, const double *xp
     return (1.0 - a) * ((1.0 - b) * v00 + b * v01) + a * ((1.0 - b) * v10 + b * v11);
 }
 
+// RefractiveHomogenous / RefractiveTransmissiveHomogenous (optics_callables.py:1186-1296, :1323-1345)
+// for one hit: the (possibly perturbed) normal, Snell's law in vector form with the total-internal-
+// reflection test (optics.refractions, optics.py:159-192), the unpolarised Fresnel reflectance
+// (optics.fresnel, optics.py:13-39), the reflect-or-refract draw of single_ray mode and the
+// path-length attenuation of Absorbant.attenuate (:874-889) with imposed coefficients.
+// u[0] = normal(scale=sigma), u[1] = uniform(0, 2 pi), u[2] = uniform(0, 1).
+struct RefractOut {
+    V3 dir_refl, dir_refr;
+    double e_refl, e_refr;     // energies of the two children
+    double m2;                 // index of the medium a refracted ray enters
+    bool has_refl, has_refr;   // which of the two child slots exist
+};
+__device__ __forceinline__ RefractOut apply_refractive(const TrcSurfaceRec *s, V3 d, V3 n, double e_in, double m1,
+                                                        const double *u, V3 v_parent, V3 hit) {
+    const double *op = s->op;
+    RefractOut r;
+    if (op[3] >= 0.0) {        // _refract_dirs :1229-1241: normal = rotation_to_z(normal) . error vector
+        double st = sin(u[0]);
+        n = rotation_to_z_apply(n, mk(st * cos(u[1]), st * sin(u[1]), cos(u[0])));
+    }
+    double m2 = (m1 == op[0]) ? op[1] : op[0];          // toggle_ref_idx :1204-1219
+    r.m2 = m2;
+    double nn = m2 / m1;
+    double cos1 = n.x * d.x + n.y * d.y + n.z * d.z;
+    bool refr = cos1 * cos1 >= 1.0 - nn * nn;
+    double R = 1.0;
+    r.dir_refr = mk(0.0, 0.0, 0.0);
+    if (refr) {
+        double cos2 = sqrt(1.0 - 1.0 / (nn * nn) * (1.0 - cos1 * cos1));
+        double sg = cos1 < 0.0 ? -1.0 : 1.0;
+        r.dir_refr = mk((d.x - cos1 * n.x) / nn + n.x * cos2 * sg,
+                        (d.y - cos1 * n.y) / nn + n.y * cos2 * sg,
+                        (d.z - cos1 * n.z) / nn + n.z * cos2 * sg);
+        double th = acos(fabs(cos1));
+        double foo = cos(th);
+        double q = m1 / m2 * sin(th);
+        double bar = sqrt(1.0 - q * q);
+        double rs = (m1 * foo - m2 * bar) / (m1 * foo + m2 * bar);
+        double rp = (m1 * bar - m2 * foo) / (m1 * bar + m2 * foo);
+        R = (rs * rs + rp * rp) / 2.0;
+    }
+    r.dir_refl = reflect(d, n);
+    if (op[2] != 0.0) {        // single_ray :1252-1281
+        bool refl = u[2] <= R;
+        r.has_refl = refl; r.has_refr = !refl;
+        r.e_refl = e_in; r.e_refr = e_in;
+    } else {                   // :1284-1294
+        r.has_refl = true; r.has_refr = refr;
+        r.e_refl = e_in * R; r.e_refr = e_in * (1.0 - R);
+    }
+    if (op[4] != 0.0) {        // Absorbant.attenuate :874-889 on every outgoing ray
+        double dx = hit.x - v_parent.x, dy = hit.y - v_parent.y, dz = hit.z - v_parent.z;
+        double path = sqrt(dx * dx + dy * dy + dz * dz);
+        if (op[7] != 1.0) path *= op[7];
+        double a_c = (op[4] > 1.0 && m1 == op[1]) ? op[6] : op[5];
+        double f = exp(-a_c * path);
+        r.e_refl *= f; r.e_refr *= f;
+    }
+    return r;
+}
+
 struct OpticsOut { V3 dir; double energy; double attenuated; };
 
 // |(d.n) n|: the cosine of the incidence angle as the reference forms it

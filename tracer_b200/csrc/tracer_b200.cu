@@ -51,8 +51,11 @@ extern "C" int trc_scene_create(const TrcSurfaceRec *surfaces, int32_t n_surface
     if (!sc) return fail(TRC_ERR_CAPACITY, "trc_scene_create: out of host memory%s");
     sc->n_surfaces = n_surfaces;
     sc->flat_only = true;
-    for (int32_t i = 0; i < n_surfaces; ++i)
+    for (int32_t i = 0; i < n_surfaces; ++i) {
         if (surfaces[i].gkind > TRC_G_TRIANGLE) sc->flat_only = false;
+        if (surfaces[i].okind == TRC_O_REFRACTIVE) sc->has_refractive = sc->has_split = true;
+        if (surfaces[i].okind == TRC_O_PERIODIC) sc->has_split = true;
+    }
     cudaError_t e = cudaMalloc(&sc->d_surfaces, sizeof(TrcSurfaceRec) * (size_t)n_surfaces);
     if (e == cudaSuccess)
         e = cudaMemcpy(sc->d_surfaces, surfaces, sizeof(TrcSurfaceRec) * (size_t)n_surfaces, cudaMemcpyHostToDevice);

@@ -193,9 +193,37 @@ class PeriodicBoundary(_OpticsDescription):
         self.period = period
 
 
+class RefractiveHomogenous(_OpticsDescription):
+    """Interface between two homogenous media of refractive indices ``n1`` and ``n2``
+    (:1186-1296).  The rays must carry a ``ref_index`` property; a ray travelling in one index
+    enters the other.  ``single_ray=True`` picks reflection or refraction per ray from the
+    Fresnel reflectance, ``False`` emits both children; ``sigma`` (None = smooth) perturbs the
+    normal with a conical Gaussian error."""
+
+    def __init__(self, n1, n2, single_ray=True, sigma=None):
+        self._ref_idxs = (n1, n2)
+        self._materials = [n1, n2]
+        self._single_ray = single_ray
+        self._sigma = sigma
+
+
+class RefractiveTransmissiveHomogenous(RefractiveHomogenous):
+    """RefractiveHomogenous followed by Absorbant.attenuate (:1323-1345, :874-889): the outgoing
+    rays are attenuated over the path from the parent vertex with the imposed
+    ``attenuation_coefficients`` (one value, or one per medium in the order n1, n2)."""
+
+    def __init__(self, n1, n2, attenuation_coefficients, single_ray=True, sigma=None, scaling=1.):
+        RefractiveHomogenous.__init__(self, n1, n2, single_ray, sigma)
+        self._scaling = scaling
+        self.a_c = attenuation_coefficients
+        if self.a_c is not None:
+            self.a_c = np.array(attenuation_coefficients)
+
+
 perfect_mirror = Reflective(0)
 
 _BASE_OPTICS = {c.__name__: c for c in (
+    RefractiveHomogenous, RefractiveTransmissiveHomogenous,
     PeriodicBoundary, FresnelConductorHomogenous,
     Lambertian_IAM, RealReflective_IAM, LambertianSpecular_IAM, LambertianAbsorbant,
     Lambertian_piecewise_Specular_directional_axisymmetric_piecewise,
@@ -207,7 +235,7 @@ _BASE_OPTICS = {c.__name__: c for c in (
 # Optics of the reference that are outside the north-star path (SURVEY 8a row
 # O8 / 8f N4): constructing them says so instead of silently mis-tracing.
 _UNSUPPORTED = (
-    'Refractive', 'RefractiveHomogenous', 'RefractiveAbsorbantHomogenous', 'RefractiveScattering',
+    'Refractive', 'RefractiveAbsorbantHomogenous', 'RefractiveScattering',
     'RefractiveScatteringHomogenous', 'Scattering', 'ScatteringPeriodicBoundary',
     'Absorbant', 'SemiLambertian', 'BiFacial', 'Reflective_IAM',
     'Lambertian_directional_axisymmetric_piecewise_Polychromatic')

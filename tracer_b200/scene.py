@@ -236,7 +236,7 @@ def _optics_record(opt):
              'Lambertian_directional_axisymmetric_piecewise_spectral', 'Reflective_spectral',
              'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM', 'LambertianAbsorbant',
              'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise', 'PeriodicBoundary',
-             'FresnelConductorHomogenous')
+             'FresnelConductorHomogenous', 'RefractiveHomogenous', 'RefractiveTransmissiveHomogenous')
     for cls in type(base).__mro__:
         if cls.__name__ in known:
             break
@@ -280,6 +280,32 @@ def _optics_record(opt):
             rec['op'][0] = _scalar(base._n1, 'n1')
             rec['table'] = _material_table(base._material)
             rec['needs_wavelengths'] = True
+        elif name in ('RefractiveTransmissiveHomogenous', 'RefractiveHomogenous'):
+            if accountants:
+                raise NotImplementedError(
+                    "refractive optics with accountants: Accountant.count compares the incoming rays with a "
+                    "child bundle in [reflected][refracted] order (and of another length when rays split); "
+                    "not reproduced")
+            n_a, n_b = base._ref_idxs
+            if np.iscomplexobj(np.asarray([n_a, n_b])):
+                raise NotImplementedError("refractive optics: complex refractive indices (attenuation from the "
+                                          "imaginary part) are outside the GPU path")
+            rec['okind'] = L.O_REFRACTIVE
+            sigma = base._sigma
+            rec['op'][:4] = [_scalar(n_a, 'n1'), _scalar(n_b, 'n2'), 1.0 if base._single_ray else 0.0,
+                             -1.0 if sigma is None else _scalar(sigma, 'sigma')]
+            if sigma is not None and sigma < 0.:
+                raise ValueError("sigma must not be negative")
+            if name == 'RefractiveTransmissiveHomogenous':
+                a_c = base.a_c
+                if a_c is None or np.ndim(a_c) != 1 or len(a_c) not in (1, 2):
+                    raise NotImplementedError(
+                        "RefractiveTransmissiveHomogenous: one or two imposed attenuation coefficients are "
+                        "supported (attenuation from complex indices and wavelengths is not)")
+                rec['op'][4] = float(len(a_c))
+                rec['op'][5] = float(a_c[0])
+                rec['op'][6] = float(a_c[-1])
+                rec['op'][7] = _scalar(base._scaling, 'scaling')
         elif name == 'PeriodicBoundary':
             if accountants:
                 raise NotImplementedError(
@@ -402,7 +428,9 @@ class CompiledScene(object):
         uniq = list({id(o): o for o in self.optics}.values())        # a mesh shares one record
         self.needs_wavelengths = any(o['needs_wavelengths'] for o in uniq)
         self.has_accountants = any(o['accountants'] for o in uniq)
-        self.children_per_hit = np.where(recs['okind'] == L.O_PERIODIC, 2, 1).astype(np.int64)
+        self.children_per_hit = np.where((recs['okind'] == L.O_PERIODIC) | (recs['okind'] == L.O_REFRACTIVE),
+                                         2, 1).astype(np.int64)
+        self.has_refractive = bool((recs['okind'] == L.O_REFRACTIVE).any())
         self.has_split = bool((self.children_per_hit > 1).any())
         self.needs_theta_for_draws = any(o['okind'] == L.O_LAMB_PIECEWISE_SPEC for o in uniq)
         self.accountant_sources = set(src for o in uniq for (_, _, src) in o['accountants'])
@@ -466,8 +494,8 @@ class CompiledScene(object):
         verts = np.asarray(mesh.mesh_vertices(), dtype=float)
         n = len(frames)
         orec = _optics_record(mesh.mesh_optics())
-        if orec['okind'] == L.O_PERIODIC:
-            raise NotImplementedError("PeriodicBoundary optics on a TriangleMeshObject")
+        if orec['okind'] in (L.O_PERIODIC, L.O_REFRACTIVE):
+            raise NotImplementedError("two-children optics (periodic, refractive) on a TriangleMeshObject")
         orec['mesh'] = mesh
         sl = slice(i0, i0 + n)
         recs['frame'][sl] = frames[:, :3, :].reshape(n, 12)

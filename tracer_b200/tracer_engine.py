@@ -49,10 +49,11 @@ class _LazyRows(object):
 class _DevBundle(object):
     """Engine-internal view of a bundle living in HBM.  ``slices`` is set while a
     host bundle is still arriving: [(first ray, end ray, CUDA event of its copy)]."""
-    __slots__ = ('V', 'D', 'E', 'W', 'n', 'slices', 'keep')
+    __slots__ = ('V', 'D', 'E', 'W', 'R', 'n', 'slices', 'keep')
 
-    def __init__(self, V, D, E, W=None, slices=None, keep=None):
+    def __init__(self, V, D, E, W=None, slices=None, keep=None, R=None):
         self.V, self.D, self.E, self.W = V, D, E, W
+        self.R = R                # ref_index column (refractive scenes), else None
         self.n = int(V.shape[1])
         self.slices = slices
         self.keep = keep          # host arrays of the copies in flight
@@ -161,9 +162,13 @@ class TracerEngine(object):
             return streamed
         V, D, E = col('vertices'), col('directions'), col('energy')
         W = col('wavelengths', required=False) if bundle.has_property('wavelengths') else None
+        R = col('ref_index', required=False) if bundle.has_property('ref_index') else None
+        if R is not None and R.shape != E.shape:
+            raise ValueError("bundle ref_index must be (n,)")
         if V.dim() != 2 or V.shape[0] != 3 or D.shape != V.shape or E.shape[0] != V.shape[1]:
             raise ValueError("bundle arrays must be vertices (3,n), directions (3,n), energy (n,)")
-        return _DevBundle(V.contiguous(), D.contiguous(), E.contiguous(), None if W is None else W.contiguous())
+        return _DevBundle(V.contiguous(), D.contiguous(), E.contiguous(), None if W is None else W.contiguous(),
+                          R=None if R is None else R.contiguous())
 
     def _upload_in_slices(self, bundle):
         """Large host bundle: allocate it in HBM and enqueue the host->device copy in
@@ -173,6 +178,8 @@ class TracerEngine(object):
         import torch
         props = getattr(bundle, '_props', None)
         if props is None or bundle.has_property('wavelengths') and bundle.is_set('wavelengths'):
+            return None
+        if props.get('ref_index') is not None:
             return None
         raw = [props.get(k) for k in ('vertices', 'directions', 'energy')]
         if any(not isinstance(a, np.ndarray) for a in raw):
@@ -240,6 +247,13 @@ class TracerEngine(object):
                 vals[1], vals[2] = np.zeros(n), np.zeros(n)
                 vals[1][diffuse] = np.random.uniform(low=0., high=2. * np.pi, size=nd)
                 vals[2][diffuse] = np.random.uniform(size=nd)
+            elif k == L.O_REFRACTIVE:
+                # _refract_dirs (:1229-1231) then _make_output_refraction_bundles (:1255)
+                if rec['op'][3] >= 0.:
+                    vals[0] = np.random.normal(scale=rec['op'][3], size=n)
+                    vals[1] = np.random.uniform(low=0., high=2. * np.pi, size=n)
+                if rec['op'][2] != 0.:
+                    vals[2] = np.random.uniform(size=n)
             elif k in (L.O_LAMBERTIAN, L.O_LAMB_DIRECTIONAL, L.O_LAMB_DIRECTIONAL_SPECTRAL,
                        L.O_LAMBERTIAN_ABSORBANT):
                 ang = rec['op'][1] if k in (L.O_LAMBERTIAN, L.O_LAMBERTIAN_ABSORBANT) else np.pi / 2.
@@ -275,7 +289,8 @@ class TracerEngine(object):
         -> trc_optics -> trc_segment_sums [-> cull sort + gathers].  Two host
         syncs: the hit count (sizes the child bundle) and the cull count."""
         import torch
-        if self.fused_bounce and self.rng == 'philox' and not scene.has_split and cur.slices is None:
+        if self.fused_bounce and self.rng == 'philox' and not scene.has_split and cur.slices is None \
+                and cur.R is None:
             return self._bounce_fused(scene, cur, bounce, min_energy, use_bvh)
         lib = L.load()
         dev = self.device
@@ -285,7 +300,7 @@ class TracerEngine(object):
         n_chunks = (n + L.HIT_CHUNK - 1) // L.HIT_CHUNK
         chunk_off = torch.empty(n_chunks, dtype=i32, device=dev)
         chunk_cnt = torch.empty(n_chunks, dtype=i32, device=dev)
-        counters = torch.zeros(2, dtype=i64, device=dev)          # [hits, culled]
+        counters = torch.zeros(3, dtype=i64, device=dev)          # [hits, culled, void child slots]
         # capacity of the hit list: the hit fraction seen at this bounce of the previous
         # trace (+30 %), else every ray; an overflow re-runs the kernel with the exact size
         frac = self._hit_frac.get(bounce)
@@ -357,6 +372,7 @@ class TracerEngine(object):
         if 'wavelengths' in want and cur.W is None:
             raise ValueError("Spectral accountant needs a 'wavelengths' bundle property")
         oW = torch.empty(Hc, dtype=f64, device=dev) if cur.W is not None else None
+        oR = torch.empty(Hc, dtype=f64, device=dev) if cur.R is not None else None
         a = L.OpticsArgs()
         a.h = H
         a.d_records, a.d_slot_rec = records.data_ptr(), slot_rec.data_ptr()
@@ -366,6 +382,8 @@ class TracerEngine(object):
         if child_off is not None:
             a.d_slot_surf, a.d_seg, a.d_child_off = slot_surf.data_ptr(), seg.data_ptr(), child_off.data_ptr()
         a.seed, a.bounce, a.min_energy = self.seed, bounce, float(min_energy)
+        if cur.R is not None:
+            a.d_ref_index, a.d_out_ref_index = cur.R.data_ptr(), oR.data_ptr()
         draws = None
         if self.rng == 'numpy':
             theta_in = None
@@ -390,6 +408,7 @@ class TracerEngine(object):
         a.d_out_wavelengths = oW.data_ptr() if oW is not None else None
         a.d_cull = cull.data_ptr()
         a.d_n_cull = counters[1:].data_ptr()
+        a.d_n_void = counters[2:].data_ptr()
         L.check(lib.trc_optics(scene.handle, C.byref(a), st))
 
         # per-surface absorbed energy and hit counts, kept on device: the payload of
@@ -401,25 +420,44 @@ class TracerEngine(object):
                                                 dirs_in=dirs_in, wavelengths=oW, attenuated=attenuated),
                           child_off_host)
 
-        n_cull = int(counters[1].item())
+        n_cull, n_void = (int(x) for x in counters[1:].tolist())
         del records, work
-        rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
-        if n_cull and n_cull < Hc:
-            # survivors first, weak rays at the back (tracer_engine.py:242-245, 268-274)
+
+        def reorder(keys, n_keys):
+            # stable counting sort of the children by key through the library's radix passes
             k2 = torch.empty(Hc, dtype=i32, device=dev)
             perm = torch.empty(Hc, dtype=i32, device=dev)
             count = torch.zeros(1, dtype=i64, device=dev)
-            work = torch.empty(int(lib.trc_sort_work_bytes(Hc, 2)), dtype=torch.uint8, device=dev)
-            L.check(lib.trc_sort_pairs(Hc, 2, L.dptr(cull), None, L.dptr(k2), L.dptr(perm), L.dptr(count),
-                                       L.dptr(work), st))
+            w = torch.empty(int(lib.trc_sort_work_bytes(Hc, n_keys)), dtype=torch.uint8, device=dev)
+            L.check(lib.trc_sort_pairs(Hc, n_keys, L.dptr(keys), None, L.dptr(k2), L.dptr(perm), L.dptr(count),
+                                       L.dptr(w), st))
             pV, pD = torch.empty_like(oV), torch.empty_like(oD)
             pE, pP = torch.empty_like(oE), torch.empty_like(oP)
             L.check(lib.trc_gather_rows(Hc, L.dptr(perm), 3, L.dptr(oV), Hc, L.dptr(pV), Hc, None, None, st))
             L.check(lib.trc_gather_rows(Hc, L.dptr(perm), 3, L.dptr(oD), Hc, L.dptr(pD), Hc, None, None, st))
             L.check(lib.trc_gather_rows(Hc, L.dptr(perm), 1, L.dptr(oE), Hc, L.dptr(pE), Hc, L.dptr(oP), L.dptr(pP), st))
             pW = oW.index_select(0, perm.long()) if oW is not None else None
-            rec = dict(V=pV, D=pD, E=pE, P=pP, W=pW)
-        rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
+            pR = oR.index_select(0, perm.long()) if oR is not None else None
+            return pV, pD, pE, pP, pW, pR, perm
+
+        if n_void:
+            # refractive surfaces leave void child slots (cull code 2): drop them, keeping the order
+            is_void = (cull == 2).to(i32)
+            pV, pD, pE, pP, pW, pR, perm = reorder(is_void, 2)
+            Hc -= n_void
+            cull = cull.index_select(0, perm[:Hc].long()).contiguous()
+            oV, oD = pV[:, :Hc].contiguous(), pD[:, :Hc].contiguous()
+            oE, oP = pE[:Hc].contiguous(), pP[:Hc].contiguous()
+            oW = pW[:Hc].contiguous() if pW is not None else None
+            oR = pR[:Hc].contiguous() if pR is not None else None
+            if Hc == 0:
+                return None, 0, H
+        rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR)
+        if n_cull and n_cull < Hc:
+            # survivors first, weak rays at the back (tracer_engine.py:242-245, 268-274)
+            pV, pD, pE, pP, pW, pR, _ = reorder(cull, 2)
+            rec = dict(V=pV, D=pD, E=pE, P=pP, W=pW, R=pR)
+        rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR)
         return rec, Hc - n_cull, H
 
     def _bounce_fused(self, scene, cur, bounce, min_energy, use_bvh):
@@ -536,6 +574,8 @@ class TracerEngine(object):
         kw = {}
         if rec.get('W') is not None:
             kw['wavelengths'] = cols(rec['W'])
+        if rec.get('R') is not None:
+            kw['ref_index'] = cols(rec['R'])
         return RayBundle(vertices=cols(rec['V']), directions=cols(rec['D']), energy=cols(rec['E']),
                          parents=cols(rec['P']), **kw)
 
@@ -563,6 +603,8 @@ class TracerEngine(object):
 
         with torch.cuda.device(self.device):
             cur = self._to_device(bundle)
+            if scene.has_refractive and cur.R is None:
+                raise ValueError("scene has refractive optics but the bundle carries no 'ref_index'")
             source_E = cur.E
             self.absorbed_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.float64, device=self.device)
             self.hits_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.int64, device=self.device)
@@ -584,7 +626,8 @@ class TracerEngine(object):
                     full.pop('pre_cull')
                     self.tree.append(self._as_bundle(full))
                 W = rec['W'][:n_surv] if rec['W'] is not None else None
-                cur = _DevBundle(rec['V'][:, :n_surv], rec['D'][:, :n_surv], rec['E'][:n_surv], W)
+                R = rec['R'][:n_surv] if rec.get('R') is not None else None
+                cur = _DevBundle(rec['V'][:, :n_surv], rec['D'][:, :n_surv], rec['E'][:n_surv], W, R=R)
                 if cur.n == 0:
                     logging.log(self.loglevel, 'Ray bundle depleted')
                     break
