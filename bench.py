@@ -40,6 +40,7 @@ METRIC = "ray-bounces/sec, NSTTF field 1e8 rays"
 UNIT = "ray-bounces/s"
 REPS = 3
 FLUX_RES = 50
+FLUX_CMP_RES = 10                       # bins per side of the flux-map comparison with the CPU reference
 ALGO_BYTES_PER_RAY_HIT_KERNEL = 48      # vertex + direction read once per ray
 ALGO_BYTES_PER_HIT_HIT_KERNEL = 72      # per hit: 8 B energy read + 64 B hit record written
 TRAFFIC_BYTES_PER_RAY_NCU = 57.8        # (dram read + write) / rays of the ncu --set full capture in profiles/
@@ -111,7 +112,15 @@ def _cpu_worker(args):
     with warnings.catch_warnings():
         warnings.simplefilter('ignore')
         eng.ray_tracer(bundle, reps=REPS, min_energy=1e-10, tree=True)
-    return eng.ray_bounces, time.perf_counter() - t0
+    wall = time.perf_counter() - t0
+    # receiver flux map of this process (outside the timed region): absorbed energy per bin
+    recv_idx = len(asm.get_surfaces()) - 1
+    recv = asm.get_surfaces()[recv_idx]
+    absorbed, hits = eng.get_all_hits(recv_idx)
+    hx, hy = np.asarray(recv.get_geometry_manager()._half_dims, float).reshape(-1)
+    local = np.dot(np.linalg.inv(recv._temp_frame), np.vstack([hits, np.ones(hits.shape[1])]))
+    fmap, _, _ = np.histogram2d(local[0], local[1], bins=FLUX_CMP_RES, range=[[-hx, hx], [-hy, hy]], weights=absorbed)
+    return eng.ray_bounces, wall, fmap
 
 
 def cpu_baseline(rays_per_proc, procs, seed=0):
@@ -124,7 +133,28 @@ def cpu_baseline(rays_per_proc, procs, seed=0):
     wall = time.perf_counter() - t0
     bounces = sum(r[0] for r in res)
     trace_wall = max(r[1] for r in res)
+    cpu_baseline.maps = np.array([r[2] for r in res])     # one independent flux map per process
     return bounces / trace_wall, bounces, wall
+
+
+def fluxmap_l2_vs_ref(gpu_bins, cpu_maps):
+    """BASELINE metric "flux-map L2 vs ref": relative L2 distance between the receiver map of
+    the GPU trace (Philox) and the map of the CPU reference port (numpy.random), both as energy
+    per bin on FLUX_CMP_RES^2 bins, next to the distance Monte-Carlo noise of the CPU sample
+    alone explains (standard error over its independent processes)."""
+    g = np.asarray(gpu_bins, float)
+    f = g.shape[0] // FLUX_CMP_RES
+    g = g.reshape(FLUX_CMP_RES, f, FLUX_CMP_RES, f).sum(axis=(1, 3))
+    mean = cpu_maps.mean(axis=0)
+    norm = np.sqrt(np.sum(mean ** 2))
+    out = {"l2_rel": float(np.sqrt(np.sum((g - mean) ** 2)) / norm), "bins": "%dx%d" % (FLUX_CMP_RES, FLUX_CMP_RES),
+           "ref": "CPU port, %d independent processes" % len(cpu_maps)}
+    if len(cpu_maps) > 1:
+        sem = cpu_maps.std(axis=0, ddof=1) / np.sqrt(len(cpu_maps))
+        out["l2_rel_expected_from_mc_noise"] = float(np.sqrt(np.sum(sem ** 2)) / norm)
+        live = sem > 0
+        out["max_bin_z"] = float(np.max(np.abs(g - mean)[live] / sem[live]))
+    return out
 
 
 def run_reference(args, rank):

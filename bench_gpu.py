@@ -5,7 +5,7 @@ import os
 
 import numpy as np
 
-from bench import (TRAFFIC_BYTES_PER_RAY_NCU, ALGO_BYTES_PER_HIT_HIT_KERNEL, ALGO_BYTES_PER_RAY_HIT_KERNEL, FLUX_RES, METRIC, REPS, UNIT, ClockSampler, cpu_baseline,
+from bench import (fluxmap_l2_vs_ref, TRAFFIC_BYTES_PER_RAY_NCU, ALGO_BYTES_PER_HIT_HIT_KERNEL, ALGO_BYTES_PER_RAY_HIT_KERNEL, FLUX_RES, METRIC, REPS, UNIT, ClockSampler, cpu_baseline,
                    nsttf_source_geometry)
 from tests import scenes
 
@@ -116,12 +116,16 @@ def run_gpu(args):
         del hV, hD, hE, host
 
     clocks = sampler.stop()
-    cpu = None
+    cpu, flux_cmp = None, None
     if rank == 0 and not args.no_cpu:
         procs = max(1, min(os.cpu_count() or 1, 64))
         v, b, wall = cpu_baseline(args.cpu_rays, procs)
         cpu = {"value": v, "unit": UNIT, "cores": procs, "kind": "port",
                "sample": "%d processes x %d rays of the same NSTTF scene, reps=%d, %.1f s wall" % (procs, args.cpu_rays, REPS, wall)}
+        # the all-reduced GPU map is the map of ONE source sharded over the ranks (energy per ray = flux x area /
+        # (rays x world)), the same total power as each CPU process traces
+        gpu_map = bins.cpu().numpy() if hasattr(bins, "cpu") else np.asarray(bins)
+        flux_cmp = fluxmap_l2_vs_ref(gpu_map, cpu_baseline.maps)
 
     if rank == 0:
         line = {
@@ -144,7 +148,7 @@ def run_gpu(args):
                          "bytes_per_ray": ALGO_BYTES_PER_RAY_HIT_KERNEL, "bytes_per_hit": ALGO_BYTES_PER_HIT_HIT_KERNEL,
                          "hits": k_hits, "peak_source": peak_src + ", burst (kernel timed by its own events)",
                          "traffic_source": "ncu dram__bytes_read+write per ray of profiles/ (2e7-ray capture) x rays"},
-            "cpu_baseline": cpu,
+            "cpu_baseline": cpu, "flux_map_vs_ref": flux_cmp,
         }
         print(json.dumps(line))
     if world > 1:

@@ -48,3 +48,22 @@ def golden_accountants(gold):
             _, s, j = key.split('_')
             out.setdefault(int(s), {})[int(j)] = gold[key]
     return {s: [v[j] for j in sorted(v)] for s, v in out.items()}
+
+
+def fluxmap_agreement(mean_a, sem_a, mean_b, sem_b):
+    """Two Monte-Carlo estimates of the same flux map from independent random numbers
+    (BASELINE metric "flux-map L2 vs ref").  Returns (z_max, l2, l2_expected):
+    the largest per-bin deviation in units of the combined standard error, the relative L2
+    distance of the maps and the L2 distance pure Monte-Carlo noise would produce."""
+    sigma = np.sqrt(np.asarray(sem_a, float) ** 2 + np.asarray(sem_b, float) ** 2)
+    diff = np.asarray(mean_a, float) - np.asarray(mean_b, float)
+    live = sigma > 0
+    z_max = float(np.max(np.abs(diff[live]) / sigma[live])) if live.any() else 0.
+    norm = np.sqrt(np.sum(np.asarray(mean_b, float) ** 2))
+    return z_max, float(np.sqrt(np.sum(diff ** 2)) / norm), float(np.sqrt(np.sum(sigma ** 2)) / norm)
+
+
+def batch_stats(maps):
+    """Mean map and its standard error from per-batch maps (B, nx, ny)."""
+    maps = np.asarray(maps, float)
+    return maps.mean(axis=0), maps.std(axis=0, ddof=1) / np.sqrt(maps.shape[0])
