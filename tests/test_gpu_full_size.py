@@ -115,3 +115,54 @@ def test_walk_equals_brute_on_tallies_at_2e7():
     assert np.array_equal(walk.hits_per_surface.cpu().numpy(), brute.hits_per_surface.cpu().numpy())
     np.testing.assert_allclose(walk.absorbed_per_surface.cpu().numpy(), brute.absorbed_per_surface.cpu().numpy(),
                                rtol=1e-12)
+
+
+def test_c2_dish_full_size_properties():
+    """Config 2 at BASELINE size: 1e7 Buie rays (CSR 0.05) onto the 5 m paraboloid dish with 2 mrad
+    bi-variate slope error and the 0.3 m receiver at the focus.  Size-independent checks: energy
+    bookkeeping per bounce, the dish's reflectance exactly 1 - 0.06 ray by ray, parents ascending per
+    surface, the receiver's shadow on the dish (its area fraction of the source disk) and the
+    intercept of the focal spot; generic-kind kernels (quadric + flat) with brute = tree walk."""
+    import torch
+    from tracer_b200.tracer_engine import TracerEngine
+    n = 10000000
+    asm, _ = scenes.c2_dish(T, n_rays=10)
+    src = T.sources.buie_sunshape_device(n, np.c_[[0., 0., 10.]], np.r_[0., 0., -1.], 2.5, 0.05, flux=1000.,
+                                         seed=21)
+    e_ray = float(src._props['energy'].pieces[0][0].item())
+    np.testing.assert_allclose(e_ray * n, 1000. * np.pi * 2.5 ** 2, rtol=1e-12)
+    eng = TracerEngine(asm, rng='philox', seed=3, device_accel='brute')
+    eng.ray_tracer(src, reps=3, min_energy=1e-10, tree=True)
+    pb = eng.stats['per_bounce']
+    hits = eng.hits_per_surface.cpu().numpy()
+    absorbed = eng.absorbed_per_surface.cpu().numpy()
+    assert pb[0][0] == n and hits.sum() == sum(h for _, h, _ in pb)
+    b1 = eng.tree[1]
+    E1, P1 = b1._props['energy'].pieces[0], b1._props['parents'].pieces[0]
+    # bounce 1: rays hit the dish (surface 0) or the back of the receiver (surface 1, shadowing the dish)
+    shadow = 0.3 * 0.3 / (np.pi * 2.5 ** 2)
+    first_recv = pb[0][1] - int((E1 == e_ray * (1. - 0.06)).sum().item())
+    assert abs(first_recv / float(n) - shadow) < 5. * np.sqrt(shadow / n)
+    assert 0.985 * n < pb[0][1] < n                   # the source disk is the dish aperture; rays of the rim tilted
+                                                      # outward by the sunshape (10 m x ~2.5 mrad) miss: ~1 %
+    dish_children = E1[:pb[0][1] - first_recv]
+    assert bool((dish_children == e_ray * (1. - 0.06)).all()), 'dish children carry (1 - absorptivity) E'
+    assert bool((P1[1:pb[0][1] - first_recv] > P1[:pb[0][1] - first_recv - 1]).all()), 'parents ascend per surface'
+    # energy: everything that hit is either absorbed or leaves with the children, bounce by bounce
+    e_in, e_children = pb[0][1] * e_ray, float(E1.sum().item())
+    for k in range(2, eng.tree.num_bunds()):
+        bk = eng.tree[k]
+        prev = eng.tree[k - 1]._props['energy'].pieces[0]
+        e_in += float(prev[bk._props['parents'].pieces[0]].sum().item())
+        e_children += float(bk._props['energy'].pieces[0].sum().item())
+    np.testing.assert_allclose(absorbed.sum() + e_children, e_in, rtol=1e-9)
+    # focal spot: 2 mrad slope error + Buie disk on a 0.3 m target 3 m away -> most reflected rays arrive
+    intercept = (hits[1] - first_recv) / float(pb[0][1] - first_recv)
+    assert 0.97 < intercept <= 1.0
+    # the tree walk gives the same tallies
+    eng2 = TracerEngine(asm, rng='philox', seed=3, device_accel='bvh')
+    eng2.ray_tracer(src, reps=3, min_energy=1e-10, tree=False)
+    assert eng2.stats['per_bounce'] == pb
+    assert np.array_equal(eng2.hits_per_surface.cpu().numpy(), hits)
+    np.testing.assert_allclose(eng2.absorbed_per_surface.cpu().numpy(), absorbed, rtol=1e-12)
+    torch.cuda.empty_cache()
