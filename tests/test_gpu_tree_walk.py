@@ -147,3 +147,22 @@ def test_triangle_cavity_20k_faces_walk_equals_brute_multi_bounce():
     assert np.array_equal(out[0][1], out[1][1])
     np.testing.assert_allclose(out[0][2], out[1][2], rtol=1e-12)
     assert np.array_equal(out[0][3], out[1][3])
+
+
+def test_prebuilt_kdtree_handle_selects_the_walk():
+    """ray_tracer(accel=True, Kd_Tree=KdTree(assembly)) as in the reference (tracer_engine.py:171-185)."""
+    from tracer_b200.tracer_engine import TracerEngine
+    np.random.seed(8)
+    asm, source = scenes.c3_nsttf(T, n_rays=20000, n_hstats=40, dense=True)
+    bundle = source()
+    kd = T.accel_tree.KdTree(asm)
+    a = TracerEngine(asm, rng='philox', seed=4, device_accel='auto')
+    a.ray_tracer(bundle, reps=3, min_energy=1e-10, accel=True, Kd_Tree=kd)
+    assert a.Kd_Tree is kd and a.stats['use_bvh']
+    asm.reset_all_optics()
+    b = TracerEngine(asm, rng='philox', seed=4, device_accel='brute')
+    b.ray_tracer(bundle, reps=3, min_energy=1e-10)
+    assert not b.stats['use_bvh'] and a.stats['per_bounce'] == b.stats['per_bounce']
+    for k in range(1, a.tree.num_bunds()):
+        assert np.array_equal(a.tree[k].get_parents(), b.tree[k].get_parents())
+        assert np.array_equal(a.tree[k].get_vertices(), b.tree[k].get_vertices())

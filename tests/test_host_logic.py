@@ -315,3 +315,25 @@ def test_refractive_records():
         scene(oc.RefractiveHomogenous(1., 1.5 + 0.1j))
     with pytest.raises(NotImplementedError):
         scene(oc.RefractiveTransmissiveHomogenous(1., 1.5, None))
+
+
+def test_kdtree_handle():
+    """accel_tree.KdTree keeps the reference's constructor and root-box test; the tree is the BVH the
+    nearest-hit kernel walks."""
+    asm, _ = scenes.c3_nsttf(T, n_rays=10, n_hstats=40)
+    kd = T.accel_tree.KdTree(asm, min_leaf=1, t_isec=500.)
+    assert kd.n_surfs == 41 and len(kd.nodes) == 2 * 41 - 1 and kd.always_relevant == []
+    assert sorted(kd.leaf_surfaces.tolist()) == list(range(41)) and 6 <= kd.depth() <= 12
+    root = kd.nodes[0]
+    assert np.allclose(root['lo'], kd.minpoint) and np.allclose(root['hi'], kd.maxpoint)
+    poss = np.c_[[0., 40., 100.], [0., 40., 100.], [500., 40., 30.], [0., 40., 30.]]
+    dirs = np.c_[[0., 0., -1.], [0., 0., 1.], [0., 1., 0.], [1., 0., 0.]]
+    hit, t0, t1 = kd.intersect_bounds(poss, dirs)
+    assert hit.tolist() == [True, False, False, True]
+    assert t0[0] == pytest.approx(100. - kd.maxpoint[2]) and t0[3] == 0. and t1[3] == pytest.approx(kd.maxpoint[0])
+    with pytest.raises(NotImplementedError):
+        kd.traversal(None)
+    flat = T.assembly.Assembly(objects=[T.object.AssembledObject(
+        surfs=[T.surface.Surface(T.flat_surface.FlatGeometryManager(), T.optics_callables.Reflective(0.))])])
+    with pytest.raises(Exception, match='No boundary defined'):
+        T.accel_tree.KdTree(flat)
