@@ -83,5 +83,6 @@ struct TrcScene {
                                        // conservative pre-test; null unless the scene is flat-only and has triangles
     int32_t n_triangles = 0;
     bool has_refractive = false;       // some surface is TRC_O_REFRACTIVE: the optics need the ref_index column
-    bool has_split = false;            // some surface emits two child slots per hit (periodic / refractive)
+    bool has_split = false;
+    int64_t *h_pinned = nullptr;       // page-locked host words for the count read-backs of trc_bounce: [hits, culled, seg(S+1)]            // some surface emits two child slots per hit (periodic / refractive)
 };

@@ -116,7 +116,10 @@ extern "C" int trc_bounce(const TrcScene *sc, const TrcBounceArgs *a, TrcBounceR
         TRC_CUDA(cudaEventRecord(ev1, st));
         r->ev_start = ev0; r->ev_stop = ev1;
     }
-    int64_t h_counts[2] = {0, 0};
+    // counts come back through page-locked words of the scene (a pageable destination makes the driver
+    // stage the copy: ~60 us of idle GPU per read-back on the timeline)
+    int64_t *h_counts = sc->h_pinned;
+    h_counts[0] = h_counts[1] = 0;
     TRC_CUDA(cudaMemcpyAsync(&h_counts[0], counters, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
     TRC_CUDA(cudaStreamSynchronize(st));
     const int64_t H = h_counts[0];
@@ -162,8 +165,9 @@ extern "C" int trc_bounce(const TrcScene *sc, const TrcBounceArgs *a, TrcBounceR
 
     TRC_CUDA(cudaMemcpyAsync(&h_counts[1], counters + 1, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
     if (a->h_seg)
-        TRC_CUDA(cudaMemcpyAsync(a->h_seg, seg, sizeof(int64_t) * (size_t)(S + 1), cudaMemcpyDeviceToHost, st));
+        TRC_CUDA(cudaMemcpyAsync(h_counts + 2, seg, sizeof(int64_t) * (size_t)(S + 1), cudaMemcpyDeviceToHost, st));
     TRC_CUDA(cudaStreamSynchronize(st));
+    if (a->h_seg) memcpy(a->h_seg, h_counts + 2, sizeof(int64_t) * (size_t)(S + 1));
     const int64_t n_cull = h_counts[1];
     r->culled = n_cull;
     r->off_vertices = kl.off_v; r->off_directions = kl.off_d; r->off_energy = kl.off_e; r->off_parents = kl.off_p;

@@ -70,6 +70,7 @@ extern "C" int trc_scene_create(const TrcSurfaceRec *surfaces, int32_t n_surface
         e = cudaMalloc(&sc->d_tri32, sizeof(float4) * 3 * (size_t)n_surfaces);
         if (e == cudaSuccess) e = build_tri32(sc);
     }
+    if (e == cudaSuccess) e = cudaHostAlloc((void **)&sc->h_pinned, sizeof(int64_t) * (size_t)(n_surfaces + 3), cudaHostAllocDefault);
     int dev = 0;
     if (e == cudaSuccess) e = cudaGetDevice(&dev);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sc->num_sms, cudaDevAttrMultiProcessorCount, dev);
@@ -93,6 +94,7 @@ extern "C" int trc_scene_destroy(TrcScene *sc) {
     cudaFree(sc->d_chunk_counter);
     cudaFree(sc->d_leaf_surfaces);
     cudaFree(sc->d_unbounded);
+    if (sc->h_pinned) cudaFreeHost(sc->h_pinned);
     delete sc;
     return TRC_OK;
 }
