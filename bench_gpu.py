@@ -2,6 +2,7 @@
 import ctypes as C
 import json
 import os
+import sys
 
 import numpy as np
 
@@ -26,6 +27,11 @@ def run_gpu(args):
     from tracer_b200.fluxmap import receiver_energy_bins
     from tracer_b200.tracer_engine_mp import TracerEngineMP
 
+    # stdout carries exactly one JSON line: anything libraries print meanwhile (NCCL's version banner
+    # under NCCL_DEBUG, warnings) goes to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -150,6 +156,9 @@ def run_gpu(args):
                          "traffic_source": "ncu dram__bytes_read+write per ray of profiles/ (2e7-ray capture) x rays"},
             "cpu_baseline": cpu, "flux_map_vs_ref": flux_cmp,
         }
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
     if world > 1:
         dist.destroy_process_group()

@@ -1,5 +1,5 @@
 """GPU timeline of bench steps from torch.profiler (CUPTI): warm per-kernel time, idle gaps.
-    python scripts/timeline_probe.py [rays]"""
+    python scripts/timeline_probe.py [rays] [c3|c4]"""
 import json, os, sys, tempfile
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -9,16 +9,24 @@ from bench import nsttf_source_geometry, REPS, FLUX_RES
 from tracer_b200 import tracer_engine as TE
 from tracer_b200.fluxmap import receiver_energy_bins
 T = scenes.NS("tracer_b200")
-asm, _ = scenes.c3_nsttf(T, n_rays=10)
-recv = asm.get_surfaces()[-1]
-eng = TE.TracerEngine(asm, rng="philox", seed=1, device_accel="bvh")
-centre, direction, radius = nsttf_source_geometry()
 n = int(float(sys.argv[1])) if len(sys.argv) > 1 else 100000000
-src = T.sources.buie_sunshape_device(n, centre, direction, radius, 0.01, flux=1000., pre_process_CSR=False, seed=99)
-def step():
-    asm.reset_all_optics()
-    eng.ray_tracer(src, reps=REPS, min_energy=1e-10, tree=True)
-    return receiver_energy_bins(recv, FLUX_RES)
+if len(sys.argv) > 2 and sys.argv[2] == 'c4':
+    asm, _ = scenes.c4_cavity_mesh(T, n_theta=1000, n_z=500)
+    eng = TE.TracerEngine(asm, rng="philox", seed=9, device_accel="bvh")
+    src = T.sources.disk_bundle_device(n, np.c_[[0., 0., -0.01]], np.r_[0., 0., 1.], 0.9, np.pi / 4., flux=1000., seed=5)
+    def step():
+        asm.reset_all_optics()
+        eng.ray_tracer(src, reps=5, min_energy=1e-12, tree=False)
+else:
+    asm, _ = scenes.c3_nsttf(T, n_rays=10)
+    recv = asm.get_surfaces()[-1]
+    eng = TE.TracerEngine(asm, rng="philox", seed=1, device_accel="bvh")
+    centre, direction, radius = nsttf_source_geometry()
+    src = T.sources.buie_sunshape_device(n, centre, direction, radius, 0.01, flux=1000., pre_process_CSR=False, seed=99)
+    def step():
+        asm.reset_all_optics()
+        eng.ray_tracer(src, reps=REPS, min_energy=1e-10, tree=True)
+        return receiver_energy_bins(recv, FLUX_RES)
 for _ in range(3): step()
 torch.cuda.synchronize()
 STEPS = 4

@@ -337,3 +337,31 @@ def test_kdtree_handle():
         surfs=[T.surface.Surface(T.flat_surface.FlatGeometryManager(), T.optics_callables.Reflective(0.))])])
     with pytest.raises(Exception, match='No boundary defined'):
         T.accel_tree.KdTree(flat)
+
+
+HAVE_REF = os.path.isdir('/root/reference/tracer')
+
+
+@pytest.mark.skipif(not HAVE_REF, reason='reference tree only exists in the build container')
+@pytest.mark.parametrize('name', ['c1_flat', 'c2_dish_bivar', 'c3_nsttf_dense', 'c4_cavity', 'c5_cavity_spectral',
+                                  'c6_optics_zoo', 'c7_periodic_cell', 'c8_fresnel_conductor', 'c9_refractive'])
+def test_reference_built_scene_compiles_to_the_same_tables(name):
+    """The drop-in claim: an Assembly built with the REFERENCE's own classes (tracer.*) goes through the
+    scene compiler unchanged and yields the device tables of the same scene built with this package."""
+    from oracle import ref_import
+    from tests.golden.make_golden import TRACE_CASES
+    from tracer_b200.scene import CompiledScene
+    ref_import.enable()
+    builder, kw, seed, _, _ = TRACE_CASES[name]
+    small = dict(kw)
+    small['n_rays'] = 10
+    ours, _ = builder(T, **small)
+    theirs, _ = builder(scenes.NS('tracer'), **small)
+    a, b = CompiledScene(ours, upload=False), CompiledScene(theirs, upload=False)
+    assert a.num_surfaces == b.num_surfaces
+    for field in a.records.dtype.names:
+        assert np.array_equal(a.records[field], b.records[field]), field
+    assert np.array_equal(a.tables, b.tables)
+    assert np.array_equal(a.children_per_hit, b.children_per_hit)
+    assert a.accountant_sources == b.accountant_sources
+    assert np.array_equal(a.bvh_leaf_surfaces, b.bvh_leaf_surfaces)

@@ -232,8 +232,10 @@ _BASE_OPTICS = {c.__name__: c for c in (
     LambertianSpecular_directional_axisymmetric_piecewise,
     Lambertian_directional_axisymmetric_piecewise_spectral)}
 
-# Optics of the reference that are outside the north-star path (SURVEY 8a row
-# O8 / 8f N4): constructing them says so instead of silently mis-tracing.
+# Optics of the reference without a GPU counterpart (DESIGN.md 4.4 gives the reason for each: the
+# scattering family, Reflective_IAM and SemiLambertian raise inside the reference itself; the others
+# need complex indices, per-ray spectra or two optics per surface): constructing them says so
+# instead of silently mis-tracing.
 _UNSUPPORTED = (
     'Refractive', 'RefractiveAbsorbantHomogenous', 'RefractiveScattering',
     'RefractiveScatteringHomogenous', 'Scattering', 'ScatteringPeriodicBoundary',
