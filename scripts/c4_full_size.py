@@ -1,6 +1,6 @@
 """Configuration 4 at full size on one GPU: 1 001 000-face cylinder cavity (TriangleMeshObject),
 Lambertian receiver, pillbox disk source; prints one JSON line with the per-bounce
-nearest-hit kernel times.  Usage: python scripts/c4_full_size.py [rays] [reps] [n_theta] [n_z]"""
+nearest-hit kernel times.  Usage: python scripts/c4_full_size.py [rays] [reps] [n_theta] [n_z] [leaf_size]"""
 import json
 import os
 import sys
@@ -19,11 +19,12 @@ def main():
     reps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
     n_theta = int(sys.argv[3]) if len(sys.argv) > 3 else 1000
     n_z = int(sys.argv[4]) if len(sys.argv) > 4 else 500
+    leaf = int(sys.argv[5]) if len(sys.argv) > 5 else 1
     T = scenes.NS('tracer_b200')
     t0 = time.time()
     asm, _ = scenes.c4_cavity_mesh(T, n_theta=n_theta, n_z=n_z)
     t_build = time.time() - t0
-    eng = TracerEngine(asm, rng='philox', seed=9, device_accel='bvh')
+    eng = TracerEngine(asm, rng='philox', seed=9, device_accel='bvh', leaf_size=leaf)
     t0 = time.time()
     eng.compile()
     t_compile = time.time() - t0
@@ -44,7 +45,7 @@ def main():
                         kernel_ms=[round(e[3](), 3) for e in eng.kernel_events], per_bounce=pb))
     best = min(out, key=lambda o: o['ms'])
     print(json.dumps(dict(workload='C4 cylinder cavity mesh, LambertianReceiver(0.7)', faces=len(asm.get_surfaces()),
-                          rays=n, reps=reps, host_build_s=round(t_build, 2), host_compile_upload_s=round(t_compile, 2),
+                          rays=n, reps=reps, leaf_size=leaf, host_build_s=round(t_build, 2), host_compile_upload_s=round(t_compile, 2),
                           **best)))
 
 

@@ -65,6 +65,8 @@ struct TrcScene {
     int32_t n_nodes = 0;
     TrcPairHalf *d_pair_a = nullptr;   // quantised children boxes, first halves  (n_pairs)
     TrcPairHalf *d_pair_b = nullptr;   // second halves + child metadata          (n_pairs)
+    TrcPairHalf *d_pair_ab = nullptr;  // the same pairs interleaved (a0 b0 a1 b1 ...): one 32 B sector per visit for the
+                                       // part of the tree that is walked from global memory / L2
     int32_t n_pairs = 0;
     uint32_t root_meta = 0;            // meta word of the root node itself
     float root_lo[3] = {0.f, 0.f, 0.f};   // root box (float32, rounded outward) = quantisation grid origin

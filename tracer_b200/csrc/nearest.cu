@@ -178,6 +178,7 @@ struct WalkParams {
     const double *pool;                       // scene table pool (apertures of the pool-based flat kinds)
     const float4 *tri32;                      // float32 triangles for the pre-test, or null (see tri_prefilter)
     const uint4 *pair_a, *pair_b;
+    const uint4 *pair_ab;                     // interleaved copy for the walk outside the shared-memory cache
     int n_pairs;
     unsigned root_meta;
     const int32_t *cand;                      // candidate list: leaf surfaces, then unbounded surfaces
@@ -642,7 +643,7 @@ nearest_hit_walk_kernel(WalkParams p) {
                             a = lds128(pair_a_smem + 16u * (unsigned)cur);
                             b = lds128(pair_b_smem + 16u * (unsigned)cur);
                         }
-                        else { a = __ldg(p.pair_a + cur); b = __ldg(p.pair_b + cur); }
+                        else { a = __ldg(p.pair_ab + 2 * cur); b = __ldg(p.pair_ab + 2 * cur + 1); }
                         bool h0, h1;
                         float t0 = slab16(a.x, a.y, a.z, r, tbest, h0);
                         float t1 = slab16(a.w, b.x, b.y, r, tbest, h1);
@@ -734,6 +735,7 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     p.tri32 = sc->d_tri32;
     p.pair_a = reinterpret_cast<const uint4 *>(sc->d_pair_a);
     p.pair_b = reinterpret_cast<const uint4 *>(sc->d_pair_b);
+    p.pair_ab = reinterpret_cast<const uint4 *>(sc->d_pair_ab);
     p.n_pairs = sc->n_pairs; p.root_meta = sc->root_meta;
     p.cand = sc->d_cand; p.unbounded_first = sc->n_leaf_surfaces; p.n_unbounded = sc->n_unbounded;
     p.has_tree = sc->n_nodes > 0 ? 1 : 0;

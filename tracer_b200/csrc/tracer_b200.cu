@@ -90,6 +90,7 @@ extern "C" int trc_scene_destroy(TrcScene *sc) {
     cudaFree(sc->d_nodes);
     cudaFree(sc->d_pair_a);
     cudaFree(sc->d_pair_b);
+    cudaFree(sc->d_pair_ab);
     cudaFree(sc->d_cand);
     cudaFree(sc->d_chunk_counter);
     cudaFree(sc->d_leaf_surfaces);
@@ -162,6 +163,7 @@ extern "C" int trc_scene_set_bvh(TrcScene *sc, const TrcBvhNode *nodes, int32_t 
     cudaFree(sc->d_nodes); sc->d_nodes = nullptr; sc->n_nodes = 0;
     cudaFree(sc->d_pair_a); sc->d_pair_a = nullptr;
     cudaFree(sc->d_pair_b); sc->d_pair_b = nullptr; sc->n_pairs = 0;
+    cudaFree(sc->d_pair_ab); sc->d_pair_ab = nullptr;
     cudaFree(sc->d_leaf_surfaces); sc->d_leaf_surfaces = nullptr; sc->n_leaf_surfaces = 0;
     cudaFree(sc->d_unbounded); sc->d_unbounded = nullptr; sc->n_unbounded = 0;
     if (n_nodes > 0) {
@@ -248,6 +250,12 @@ extern "C" int trc_scene_set_bvh(TrcScene *sc, const TrcBvhNode *nodes, int32_t 
         TRC_CUDA(cudaMalloc(&sc->d_pair_b, sizeof(TrcPairHalf) * pb.size()));
         TRC_CUDA(cudaMemcpy(sc->d_pair_a, pa.data(), sizeof(TrcPairHalf) * pa.size(), cudaMemcpyHostToDevice));
         TRC_CUDA(cudaMemcpy(sc->d_pair_b, pb.data(), sizeof(TrcPairHalf) * pb.size(), cudaMemcpyHostToDevice));
+        {
+            std::vector<TrcPairHalf> ab(2 * pa.size());
+            for (size_t k = 0; k < pa.size(); ++k) { ab[2 * k] = pa[k]; ab[2 * k + 1] = pb[k]; }
+            TRC_CUDA(cudaMalloc(&sc->d_pair_ab, sizeof(TrcPairHalf) * ab.size()));
+            TRC_CUDA(cudaMemcpy(sc->d_pair_ab, ab.data(), sizeof(TrcPairHalf) * ab.size(), cudaMemcpyHostToDevice));
+        }
     }
     if ((int64_t)n_leaf_surfaces + n_unbounded >= (1 << 22) || sc->n_surfaces >= (1 << 22))
         return fail(TRC_ERR_CAPACITY, "trc_scene_set_bvh: more than 2^22 candidate entries%s");
