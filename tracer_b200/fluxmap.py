@@ -38,7 +38,8 @@ def receiver_energy_bins(surface, resolution, device=None):
         for hits, absorbed in zip(_chunks(accs['Location']._hits), _chunks(accs['Absorber']._absorbed)):
             th = hits.t if getattr(hits, 't', None) is not None else torch.from_numpy(np.asarray(hits)).to(dev)
             te = absorbed.t if getattr(absorbed, 't', None) is not None else torch.from_numpy(np.asarray(absorbed)).to(dev)
-            th, te = th.contiguous(), te.contiguous()
+            th = th if th.stride(-1) == 1 else th.contiguous()      # rows may be strided views of a bounce arena
+            te = te.contiguous()
             n = int(te.shape[0])
             L.check(lib.trc_fluxmap_rect(n, L.dptr(th), th.stride(0), L.dptr(te), pp, float(hx), float(hy),
                                          resolution, resolution, L.dptr(bins), st))

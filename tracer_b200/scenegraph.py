@@ -248,6 +248,14 @@ class Assembly(HasFrame):
             child.transform_children(mine)
 
     def reset_all_optics(self):
+        self.get_surfaces()                           # fills / validates the cached surface list
+        cached = self._surfaces_cache[1]
+        if not isinstance(cached, SurfaceSeq):        # plain scenes: no walk over the object tree per trace
+            for s in cached:
+                reset = getattr(s._opt, 'reset', None)
+                if reset is not None:
+                    reset()
+            return
         for obj in self.get_objects():
             if getattr(obj, 'is_triangle_mesh', False):
                 obj.reset_optics()

@@ -95,6 +95,7 @@ class TracerEngine(object):
         self._frames_key = None
         self._hit_frac = {}       # bounce -> hit fraction of the previous trace (sizes the hit list)
         self._copy_stream = None
+        self._keep_tree = False
         self.fused_bounce = True   # sequence a bounce inside the library (trc_bounce) when the configuration allows
         self.kernel_events = None  # set to a list to collect (bounce, n, H, start, end) CUDA events of trc_trace_hits
         self.stats = {}
@@ -528,7 +529,7 @@ class TracerEngine(object):
             self._account(scene, h_seg, dict(
                 hits=oV, absorbed=view(r.off_absorbed, f64, 0), e_out=oE, normals=view(r.off_normals, f64, 3),
                 e_in=view(r.off_e_in, f64, 0), dirs_in=view(r.off_dirs_in, f64, 3), wavelengths=oW,
-                attenuated=view(r.off_attenuated, f64, 0)))
+                attenuated=view(r.off_attenuated, f64, 0)), copy=not self._keep_tree)
         rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
         if r.off_sorted_vertices >= 0:
             rec = dict(V=view(r.off_sorted_vertices, f64, 3), D=view(r.off_sorted_directions, f64, 3),
@@ -538,12 +539,14 @@ class TracerEngine(object):
         return rec, H - n_cull, H
 
     @staticmethod
-    def _account(scene, seg, src, child_off=None):
+    def _account(scene, seg, src, child_off=None, copy=True):
         """What Accountant.count() stores, one chunk per surface per bounce
         (optics_callables.py:1597-1790), kept in HBM until read.  ``src`` maps a
         source name to the tensor the optics kernel filled: slot order, except the
         child columns (hit points, outgoing energy) which follow ``child_off`` when
-        some surface of the scene emits two children per hit."""
+        some surface of the scene emits two children per hit.  ``copy=False`` stores views of the
+        bounce's arena instead of copies (used when the ray tree keeps that arena alive anyway)."""
+        take = (lambda t: t.clone()) if copy else (lambda t: t)
         for i0, i1, mesh in scene.mesh_segments:           # one chunk per bounce for a whole mesh
             a, b = int(seg[i0]), int(seg[i1])
             names = set(name for _, _, name in scene.optics[i0]['accountants'])
@@ -551,7 +554,7 @@ class TracerEngine(object):
                 continue
             if child_off is not None:
                 raise NotImplementedError("TriangleMeshObject in a scene with two-children optics")
-            mesh._add_chunk(np.array(seg[i0:i1 + 1], dtype=np.int64), {k: src[k][..., a:b].clone() for k in names})
+            mesh._add_chunk(np.array(seg[i0:i1 + 1], dtype=np.int64), {k: take(src[k][..., a:b]) for k in names})
         for s in scene.account_list:
             orec = scene.optics[s]
             a, b = int(seg[s]), int(seg[s + 1])
@@ -561,9 +564,9 @@ class TracerEngine(object):
                 t = src[name]
                 if child_off is not None and name in ('hits', 'e_out', 'wavelengths'):
                     lo = int(child_off[s])
-                    getattr(acc, field).append(_LazyRows(t[..., lo:lo + (b - a)].clone()))
+                    getattr(acc, field).append(_LazyRows(take(t[..., lo:lo + (b - a)])))
                 else:
-                    getattr(acc, field).append(_LazyRows(t[..., a:b].clone()))
+                    getattr(acc, field).append(_LazyRows(take(t[..., a:b])))
 
     @staticmethod
     def _as_bundle(rec, n=None):
@@ -587,6 +590,7 @@ class TracerEngine(object):
         import torch
         self.reps = reps
         self.minener = min_energy
+        self._keep_tree = bool(tree)      # the tree's bundles view the per-bounce arenas: accountant rows may too
         self.tree = RayTree()
         if tree is True:
             self.tree.append(bundle)
