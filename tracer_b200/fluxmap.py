@@ -29,8 +29,13 @@ def receiver_energy_bins(surface, resolution, device=None):
         raise ValueError("receiver_energy_bins needs Absorber and Location accountants")
     gm = surface.get_geometry_manager()
     hx, hy = np.asarray(gm._half_dims, float).reshape(-1)
-    proj = np.round(np.linalg.inv(surface._temp_frame), decimals=9)[:3]   # surface.py:125
-    _, pp = L.host_doubles(proj, 12)
+    frame = surface._temp_frame
+    cached = surface.__dict__.get('_b200_proj')          # frames are replaced, never edited in place (has_frame.py:75)
+    if cached is None or cached[0] is not frame:
+        proj = np.round(np.linalg.inv(frame), decimals=9)[:3]   # surface.py:125
+        cached = (frame, L.host_doubles(proj, 12))
+        surface.__dict__['_b200_proj'] = cached
+    _, pp = cached[1]
     dev = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
     bins = torch.zeros((resolution, resolution), dtype=torch.float64, device=dev)
     with torch.cuda.device(dev):
