@@ -1,0 +1,212 @@
+"""The reference's own known-answer tests of the bounce loop, restated against (a) the
+NumPy oracle on the CPU and (b) the CUDA path on the GPU.  Each case cites the reference test it
+comes from; expected values are the ones written in the reference's test files, tolerances theirs
+(assert_array_almost_equal, 6 decimals unless stated).
+
+  tests/test_tracer_engine.py  TestTraceProtocol1 / 3 / 4 / 5 / 6   (lines 26-232)
+  tests/test_objects.py        TestObjectBuilding1 / 2, TestAssemblyBuilding4   (lines 20-170)
+  tests/test_tracer_tree.py    TestTraceTree... final order / absorbed to back (lines 106-153) are in
+                               tests/test_gpu_parity.py::test_culling_and_parent_bookkeeping
+  tests/test_opt_callable.py, test_tracer_engine.py nested lens: tests/test_gpu_refractive.py
+"""
+import math
+
+import numpy as np
+import pytest
+
+from tests import scenes
+
+T = scenes.NS('tracer_b200')
+
+
+def _planes(*rotations):
+    sg = T.spatial_geometry
+    obj = T.object.AssembledObject()
+    for rot in rotations:
+        kw = {} if rot is None else dict(rotation=sg.general_axis_rotation([1, 0, 0], rot))
+        obj.add_surface(T.surface.Surface(T.flat_surface.FlatGeometryManager(), T.optics_callables.perfect_mirror, **kw))
+    asm = T.assembly.Assembly()
+    asm.add_object(obj)
+    return asm
+
+
+def case_protocol1():
+    """TestTraceProtocol1.test_ray_tracer (:26-62): one flat mirror, one iteration."""
+    d = np.array([[1, 1, -1], [-1, 1, -1], [-1, -1, -1], [1, -1, -1]]).T / math.sqrt(3)
+    pos = np.c_[[0, 0, 1], [1, -1, 1], [1, 1, 1], [-1, 1, 1]].astype(float)
+    correct = np.zeros((3, 4))
+    correct[:2, 0] = 1
+    return _planes(None), T.ray_bundle.RayBundle(pos, d, energy=np.ones(4)), 1, correct, 6
+
+
+def case_protocol3():
+    """TestTraceProtocol3.test_ray_tracer1 (:97-135): two planes at +-45 degrees."""
+    x = 1 / math.sqrt(2)
+    b = T.ray_bundle.RayBundle(np.c_[[0, 0, 1.], [0, 0, 1.]], np.c_[[0, x, -x], [0, 1., 0]], energy=np.ones(2))
+    return _planes(np.pi / 4, np.pi / (-4)), b, 1, np.c_[[0, .5, .5], [0, 1, 1]], 6
+
+
+def _protocol4(reps, correct):
+    x = 1 / math.sqrt(2)
+    b = T.ray_bundle.RayBundle(np.c_[[0, 2., 1.], [0, 2., 1.]], np.c_[[0, -x, x], [0, 0, -1.]], energy=np.ones(2))
+    return _planes(np.pi / 4, None), b, reps, correct, 6
+
+
+def case_protocol4_one():
+    """TestTraceProtocol4.test_ray_tracer1 (:137-164): the rays hit different surfaces."""
+    return _protocol4(1, np.c_[[0, 1.5, 1.5], [0, 2, 0]])
+
+
+def case_protocol4_two():
+    """TestTraceProtocol4.test_ray_tracer2 (:166-170)."""
+    return _protocol4(2, np.c_[[0, 2, 2], [0, 3, 0]])
+
+
+def case_protocol4_escape():
+    """TestTraceProtocol4.test_too_much_intersections (:172-177): the tracer stops when every ray escapes."""
+    return _protocol4(42, np.array([]).reshape(3, 0))
+
+
+def case_protocol5():
+    """TestTraceProtocol5.test_ray_tracer1 (:179-200): a hemisphere seen from inside and outside, 3 decimals."""
+    sg = T.spatial_geometry
+    surf = T.surface.Surface(T.sphere_surface.HemisphereGM(1.), T.optics_callables.perfect_mirror,
+                             rotation=sg.general_axis_rotation(np.r_[1, 0, 0], np.pi))
+    b = T.ray_bundle.RayBundle(energy=np.ones(3))
+    b.set_directions(np.c_[[0, 1., 0], [0, 1., 0], [0, -1., 0]])
+    b.set_vertices(np.c_[[0, -2., 0.001], [0, 0, 0.001], [0, 2, 0.001]])
+    obj = T.object.AssembledObject()
+    obj.add_surface(surf)
+    asm = T.assembly.Assembly()
+    asm.add_object(obj)
+    return asm, b, 1, np.c_[[0, -1, 0], [0, 1, 0], [0, 1, 0]], 3
+
+
+def case_protocol6():
+    """TestTraceProtocol6.test_ray_tracers1 (:202-232): two facing hemispheres in two objects."""
+    sg = T.spatial_geometry
+    s1 = T.surface.Surface(T.sphere_surface.HemisphereGM(2.), T.optics_callables.perfect_mirror,
+                           rotation=sg.general_axis_rotation(np.r_[1, 0, 0], np.pi / 2.))
+    s2 = T.surface.Surface(T.sphere_surface.HemisphereGM(2.), T.optics_callables.perfect_mirror,
+                           location=np.array([0, -2., 0]), rotation=sg.general_axis_rotation(np.r_[1, 0, 0], -np.pi / 2.))
+    b = T.ray_bundle.RayBundle()
+    b.set_directions(np.c_[[0, 1., 0]])
+    b.set_vertices(np.c_[[0, -1., 0]])
+    b.set_energy(np.r_[[1.]])
+    b.set_ref_index(np.r_[[1.]])
+    asm = T.assembly.Assembly()
+    for s in (s1, s2):
+        obj = T.object.AssembledObject()
+        obj.add_surface(s)
+        asm.add_object(obj)
+    return asm, b, 1, np.c_[[0, 2, 0]], 6
+
+
+def _two_hemispheres():
+    sg = T.spatial_geometry
+    s1 = T.surface.Surface(T.sphere_surface.HemisphereGM(3.), T.optics_callables.perfect_mirror,
+                           location=np.array([0, 0, -1.]), rotation=sg.general_axis_rotation(np.r_[1, 0, 0], np.pi))
+    s2 = T.surface.Surface(T.sphere_surface.HemisphereGM(3.), T.optics_callables.perfect_mirror,
+                           location=np.array([0, 0, 1.]))
+    obj = T.object.AssembledObject()
+    obj.add_surface(s1)
+    obj.add_surface(s2)
+    asm = T.assembly.Assembly()
+    asm.add_object(obj)
+    return asm
+
+
+def case_objects_hemispheres():
+    """test_objects.py TestObjectBuilding1.test_object (:20-46): two hemispheres in one object."""
+    b = T.ray_bundle.RayBundle(np.c_[[0, 0, -3.], [0, 0, -1.]], np.c_[[0, 0, 1.], [0, 0, 1.]], energy=np.ones(2))
+    return _two_hemispheres(), b, 1, np.c_[[0, 0, 2], [0, 0, -2]], 6
+
+
+def case_objects_translated():
+    """TestObjectBuilding1.test_translation (:48-58): the assembly moved by transform_children."""
+    asm = _two_hemispheres()
+    asm.transform_children(np.array([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, 1, 1], [0, 0, 0, 1.]]))
+    b = T.ray_bundle.RayBundle(np.c_[[0, 0, -3.], [0, 0, -1.]], np.c_[[0, 0, 1.], [0, 0, 1.]], energy=np.ones(2))
+    return asm, b, 1, np.c_[[0, 0, 3], [0, 0, -1]], 6
+
+
+def case_objects_rotated_and_translated():
+    """TestObjectBuilding1.test_rotation_and_translation (:60-76)."""
+    asm = _two_hemispheres()
+    asm.transform_children(T.spatial_geometry.generate_transform(np.r_[[1, 0, 0]], np.pi / 2, np.c_[[0, 0, 1]]))
+    b = T.ray_bundle.RayBundle()
+    b.set_vertices(np.c_[[0, -5., 1], [0, 5., 1]])
+    b.set_directions(np.c_[[0, 1., 0], [0, 1., 0]])
+    b.set_energy(np.r_[[1., 1.]])
+    b.set_ref_index(np.r_[[1., 1.]])
+    return asm, b, 1, np.c_[[0, -2, 1]], 6
+
+
+def case_objects_paraboloid():
+    """TestAssemblyBuilding4.test_paraboloid1 (:152-170): the default Paraboloid."""
+    x = 1. / math.sqrt(2)
+    obj = T.object.AssembledObject()
+    obj.add_surface(T.surface.Surface(T.paraboloid.Paraboloid(), T.optics_callables.perfect_mirror))
+    asm = T.assembly.Assembly()
+    asm.add_object(obj)
+    b = T.ray_bundle.RayBundle(np.c_[[0, 0, 1.], [0, 0, 1.]], np.c_[[0, 0, -1.], [0, x, -x]], energy=np.ones(2),
+                               ref_index=np.ones(2))
+    return asm, b, 1, np.c_[[0, 0, 0], [0, 0.618033989, 0.381966011]], 6
+
+
+def _glass_slab():
+    """TestObjectBuilding2 (:78-110): two refractive planes; the expected angles are those of both children
+    of every ray (the test predates single_ray mode)."""
+    oc = T.optics_callables
+    s1 = T.surface.Surface(T.flat_surface.FlatGeometryManager(), oc.RefractiveHomogenous(1., 1.5, single_ray=False),
+                           location=np.array([0, 0, -1.]))
+    s2 = T.surface.Surface(T.flat_surface.FlatGeometryManager(), oc.RefractiveHomogenous(1.5, 1., single_ray=False),
+                           location=np.array([0, 0, 1.]))
+    asm = T.assembly.Assembly()
+    asm.add_object(T.object.AssembledObject(surfs=[s1, s2]))
+    x = 1 / math.sqrt(2)
+    b = T.ray_bundle.RayBundle(np.c_[[0, 1., -2.]], np.c_[[0, -x, x]], energy=np.r_[1.], ref_index=np.r_[1.])
+    return asm, b
+
+
+REFRACTION_CASES = [(1, np.r_[0.785398163, -.4908826]), (2, np.r_[-0.7853981])]
+
+
+@pytest.mark.parametrize('reps,angles', REFRACTION_CASES, ids=['refraction1', 'refraction2'])
+def test_oracle_refraction_angles(reps, angles):
+    from oracle.numpy_trace import OracleEngine
+    asm, bundle = _glass_slab()
+    d = OracleEngine(asm).ray_tracer(bundle, reps, .05)[1]
+    np.testing.assert_array_almost_equal(np.arctan(d[1] / d[2]), angles)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('reps,angles', REFRACTION_CASES, ids=['refraction1', 'refraction2'])
+def test_gpu_refraction_angles(reps, angles):
+    from tracer_b200.tracer_engine import TracerEngine
+    asm, bundle = _glass_slab()
+    d = TracerEngine(asm).ray_tracer(bundle, reps, .05)[1]
+    np.testing.assert_array_almost_equal(np.arctan(d[1] / d[2]), angles)
+
+
+CASES = [case_protocol1, case_protocol3, case_protocol4_one, case_protocol4_two, case_protocol4_escape,
+         case_protocol5, case_protocol6, case_objects_hemispheres, case_objects_translated,
+         case_objects_rotated_and_translated, case_objects_paraboloid]
+
+
+@pytest.mark.parametrize('case', CASES, ids=lambda c: c.__name__[5:])
+def test_oracle_reproduces_the_references_known_answers(case):
+    from oracle.numpy_trace import OracleEngine
+    asm, bundle, reps, correct, decimal = case()
+    params = OracleEngine(asm).ray_tracer(bundle, reps, .05)[0]
+    np.testing.assert_array_almost_equal(params, correct, decimal=decimal)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('accel', ['brute', 'bvh'])
+@pytest.mark.parametrize('case', CASES, ids=lambda c: c.__name__[5:])
+def test_gpu_reproduces_the_references_known_answers(case, accel):
+    from tracer_b200.tracer_engine import TracerEngine
+    asm, bundle, reps, correct, decimal = case()
+    params = TracerEngine(asm, device_accel=accel).ray_tracer(bundle, reps, .05)[0]
+    np.testing.assert_array_almost_equal(params, correct, decimal=decimal)
