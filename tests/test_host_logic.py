@@ -365,3 +365,35 @@ def test_reference_built_scene_compiles_to_the_same_tables(name):
     assert np.array_equal(a.children_per_hit, b.children_per_hit)
     assert a.accountant_sources == b.accountant_sources
     assert np.array_equal(a.bvh_leaf_surfaces, b.bvh_leaf_surfaces)
+
+
+def test_ray_bundle_known_answers_of_the_reference():
+    """tests/test_ray_bundle.py:12-99 of the reference: inheritance (empty, full, positional overrides,
+    partial), delete_rays, extra properties through inherit and concatenate_rays."""
+    RB = T.ray_bundle
+    RB.RayBundle().inherit()
+    pos, d, energy, ref_ind, prn = np.ones((3, 4)), np.zeros((3, 4)), np.ones(4), np.zeros(4), np.ones(4)
+    father = RB.RayBundle(pos, d, energy, prn, ref_ind)
+    child = father.inherit()
+    for got, want in ((child.get_vertices(), pos), (child.get_directions(), d), (child.get_energy(), energy),
+                      (child.get_ref_index(), ref_ind), (child.get_parents(), prn)):
+        np.testing.assert_array_equal(got, want)
+    child = father.inherit(np.s_[:], d, pos, prn, energy, np.ones(4) * 5)
+    np.testing.assert_array_equal(child.get_vertices(), d)
+    np.testing.assert_array_equal(child.get_directions(), pos)
+    np.testing.assert_array_equal(child.get_energy(), prn)
+    np.testing.assert_array_equal(child.get_ref_index(), np.ones(4) * 5)
+    np.testing.assert_array_equal(child.get_parents(), energy)
+    child = RB.RayBundle(pos, d).inherit(selector=np.r_[0, 1], direction=np.ones((3, 2)))
+    np.testing.assert_array_equal(child.get_vertices(), pos[:, [0, 1]])
+    np.testing.assert_array_equal(child.get_directions(), np.ones((3, 2)))
+    child = RB.RayBundle(pos, d, parents=np.arange(4)).delete_rays(np.r_[0])
+    np.testing.assert_array_equal(child.get_vertices(), np.ones((3, 3)))
+    np.testing.assert_array_equal(child.get_parents(), np.arange(1, 4))
+    child = RB.RayBundle(pos, d, wavelength=np.arange(4)).inherit()
+    np.testing.assert_array_equal(child.get_wavelength(), np.arange(4))
+    con = RB.concatenate_rays((RB.RayBundle(np.ones((3, 4)), np.ones((3, 4)), wavelen=np.ones((3, 4))),
+                               RB.RayBundle(np.zeros((3, 4)), np.zeros((3, 4)), wavelen=np.zeros((3, 4)))))
+    correct = np.hstack((np.ones((3, 4)), np.zeros((3, 4))))
+    np.testing.assert_array_equal(con.get_vertices(), correct)
+    np.testing.assert_array_equal(con.get_wavelen(), correct)
