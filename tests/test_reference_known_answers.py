@@ -5,6 +5,7 @@ comes from; expected values are the ones written in the reference's test files, 
 
   tests/test_tracer_engine.py  TestTraceProtocol1 / 3 / 4 / 5 / 6   (lines 26-232)
   tests/test_objects.py        TestObjectBuilding1 / 2, TestAssemblyBuilding4   (lines 20-170)
+  tests/models/test_one_sided_mirror.py  TestRectOneSided (lines 10-52)
   tests/test_tracer_tree.py    TestTraceTree... final order / absorbed to back (lines 106-153) are in
                                tests/test_gpu_parity.py::test_culling_and_parent_bookkeeping
   tests/test_opt_callable.py, test_tracer_engine.py nested lens: tests/test_gpu_refractive.py
@@ -215,3 +216,47 @@ def test_gpu_reproduces_the_references_known_answers(case, accel):
     asm, bundle, reps, correct, decimal = case()
     params = TracerEngine(asm, device_accel=accel).ray_tracer(bundle, reps, .05)[0]
     np.testing.assert_array_almost_equal(params, correct, decimal=decimal)
+
+
+def _one_sided_case(rotated):
+    """tests/models/test_one_sided_mirror.py TestRectOneSided (:10-52): rays from above are reflected with
+    10 % of their energy (absorptivity 0.9), rays from below lose everything, rays beside the plate miss."""
+    mirror = T.models.one_sided_mirror.rect_one_sided_mirror(1.5, 1.5, 0.9)
+    if rotated:
+        mirror.set_transform(T.spatial_geometry.roty(np.pi / 4.))
+    pos = np.zeros((3, 8))
+    pos[0] = np.tile(np.r_[0, 0.5, 2, -2], 2)
+    pos[2] = np.repeat(np.r_[1, -1], 4)
+    d = np.zeros((3, 8))
+    d[2] = np.repeat(np.r_[-1, 1], 4)
+    b = T.ray_bundle.RayBundle()
+    b.set_vertices(pos)
+    b.set_directions(d)
+    b.set_energy(np.ones(8) * 1000)
+    b.set_ref_index(np.ones(8))
+    verts = np.array([[0., 0.5], [0., 0.], [0., -0.5]]) if rotated else np.array([[0., 0.5], [0., 0.], [0., 0.]])
+    return T.assembly.Assembly(objects=[mirror]), b, verts
+
+
+def _check_one_sided(outg, verts):
+    np.testing.assert_array_almost_equal(outg.get_vertices()[:, outg.get_energy() > 0], verts)
+    np.testing.assert_array_almost_equal(outg.get_energy(), np.r_[100., 100., 0, 0])
+
+
+@pytest.mark.parametrize('rotated', [False, True], ids=['regular', 'rotated'])
+def test_oracle_one_sided_mirror(rotated):
+    from oracle.numpy_trace import OracleEngine
+    asm, b, verts = _one_sided_case(rotated)
+    e = OracleEngine(asm)
+    e.ray_tracer(b, 1, 0.05)
+    _check_one_sided(e.tree[-1], verts)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('rotated', [False, True], ids=['regular', 'rotated'])
+def test_gpu_one_sided_mirror(rotated):
+    from tracer_b200.tracer_engine import TracerEngine
+    asm, b, verts = _one_sided_case(rotated)
+    e = TracerEngine(asm)
+    e.ray_tracer(b, 1, 0.05)
+    _check_one_sided(e.tree[-1], verts)
