@@ -1,5 +1,6 @@
 """Known answers of the reference's geometry-manager tests -- ray parameters, hit points and
-normals written in tests/test_hemisphere_gm.py, test_paraboloid_gm.py, test_cylinder.py of the reference
+normals written in tests/test_hemisphere_gm.py, test_paraboloid_gm.py, test_cylinder.py,
+test_flat_geometry_manager.py, test_rect_plate.py, test_round_plate.py, test_triangular_face.py of the reference
 -- against the oracle's find_intersections (CPU) and the CUDA kernels (GPU: a one-bounce trace whose
 Location / Normal accountants and child vertices carry what the kernels computed).  These vectors come on
 top of tests/golden/gm_zoo.npz (4000 random rays per geometry kind, recorded from the reference)."""
@@ -80,8 +81,86 @@ def case_cylinder_rotated():
     return (lambda: T.cylinder.InfiniteCylinder(diameter=1.)), T.spatial_geometry.rotx(np.pi / 6), pos, d, prm, pts, nrm
 
 
+def case_flat():
+    """tests/test_flat_geometry_manager.py:10-52: prm = sqrt(3), normals +z, all points at the origin but one."""
+    d = np.c_[[1, 1, -1], [-1, 1, -1], [-1, -1, -1], [1, -1, -1]] / np.sqrt(3)
+    pos = np.c_[[0, 0, 1], [1, -1, 1], [1, 1, 1], [-1, 1, 1]].astype(float)
+    pts = np.zeros((3, 4))
+    pts[:2, 0] = 1
+    return (lambda: T.flat_surface.FlatGeometryManager()), np.eye(4), pos, d, np.full(4, np.sqrt(3)), pts, \
+        np.tile(np.c_[[0, 0, 1.]], (1, 4))
+
+
+def case_flat_tilted():
+    """tests/test_flat_geometry_manager.py:54-107: the plane rotated by -45 degrees about x."""
+    s2 = np.sqrt(2)
+    d = np.c_[[1, 0, -s2], [-1, 0, -s2], [-1, -s2, 0], [1, -s2, 0]] / np.sqrt(3)
+    pos = np.c_[[0, 1 / s2, 1 / s2], [1, 0, s2], [1, s2, 0], [-1, s2, 0]]
+    pts = np.zeros((3, 4))
+    pts[:, 0] = np.r_[1, 1 / s2, -1 / s2]
+    frame = T.spatial_geometry.generate_transform(np.r_[1., 0, 0], -np.pi / 4., np.zeros((3, 1)))
+    return (lambda: T.flat_surface.FlatGeometryManager()), frame, pos, d, np.full(4, np.sqrt(3)), pts, \
+        np.tile(np.c_[[0, 1 / s2, 1 / s2]], (1, 4))
+
+
+def _down_rays(xs):
+    pos = np.zeros((3, len(xs)))
+    pos[0] = xs
+    pos[2] = 1.
+    return pos, np.tile(np.c_[[0, 0, -1.]], (1, len(xs)))
+
+
+def _mask_case(make, frame, pos, d, misses):
+    prm = np.where(misses, np.inf, np.nan)          # nan: hit, parameter not stated by the reference test
+    return make, frame, pos, d, prm, None, None
+
+
+def case_rect_plate():
+    """tests/test_rect_plate.py:17-27: misses = [F, F, T, T]."""
+    pos, d = _down_rays(np.r_[0, 0.5, 2, -2])
+    return _mask_case(lambda: T.flat_surface.RectPlateGM(1, 0.25), np.eye(4), pos, d, np.r_[False, False, True, True])
+
+
+def case_rect_plate_extruded():
+    """tests/test_rect_plate.py:43-55: a ray inside the rectangular hole misses."""
+    pos, d = _down_rays(np.r_[0, 0.05, 0.2, -0.3])
+    make = (lambda: T.flat_surface.ExtrudedRectPlateGM(width=1, height=1, extr_center=np.vstack([0.2, 0.1]),
+                                                       extr_width=0.2, extr_height=0.4))
+    return _mask_case(make, np.eye(4), pos, d, np.r_[False, False, True, False])
+
+
+def case_round_plate():
+    """tests/test_round_plate.py:17-27."""
+    pos, d = _down_rays(np.r_[0, 0.5, 2, -2])
+    return _mask_case(lambda: T.flat_surface.RoundPlateGM(1), np.eye(4), pos, d, np.r_[False, False, True, True])
+
+
+def _triangle(frame):
+    x, y = np.mgrid[-1:1:2j, -1:1:3j]
+    pos = np.vstack((x.flatten(), y.flatten(), np.ones(6) * 10))
+    pos[1] -= 10.
+    d = np.tile(np.c_[[0., 10., -10.]], (1, 6))
+    verts = np.zeros((3, 2))
+    verts[1] = 2.
+    verts[0] = np.r_[4., -4.]
+    return _mask_case(lambda: T.triangular_face.TriangularFace(verts), frame, pos, d,
+                      ~np.r_[False, False, True, False, False, True])
+
+
+def case_triangle():
+    """tests/test_triangular_face.py:9-29: exclusion by the barycentric test, global frame."""
+    return _triangle(np.eye(4))
+
+
+def case_triangle_transformed():
+    """tests/test_triangular_face.py:31-37."""
+    sg = T.spatial_geometry
+    return _triangle(np.dot(sg.translate(0, -1, 0.5), sg.rotx(np.pi / 4.)))
+
+
 CASES = [case_hemisphere, case_paraboloid, case_dish_circular, case_dish_hexagonal, case_cylinder_vertical,
-         case_cylinder_rotated]
+         case_cylinder_rotated, case_flat, case_flat_tilted, case_rect_plate, case_rect_plate_extruded,
+         case_round_plate, case_triangle, case_triangle_transformed]
 
 
 def _surface(make, frame, optics):
@@ -96,8 +175,11 @@ def test_oracle_geometry_known_answers(case):
     make, frame, pos, d, prm, pts, nrm = case()
     _, surf = _surface(make, frame, T.optics_callables.Reflective(0.))
     got, points, normals = find_intersections(surf, pos, d)
-    np.testing.assert_array_almost_equal(got, prm)
-    hit = np.nonzero(np.isfinite(prm))[0]
+    got = np.where(got == 0., np.inf, got)
+    assert np.array_equal(np.isinf(got), np.isinf(prm)), 'hit / miss pattern'
+    stated = np.isfinite(prm)
+    np.testing.assert_array_almost_equal(got[stated], prm[stated])
+    hit = np.nonzero(~np.isinf(prm))[0]
     if pts is not None:
         np.testing.assert_array_almost_equal(points(hit), pts[:, hit])
     if nrm is not None:
@@ -114,10 +196,12 @@ def test_gpu_geometry_known_answers(case):
     bundle = T.ray_bundle.RayBundle(pos.copy(), d.copy(), energy=np.ones(pos.shape[1]))
     eng = TracerEngine(asm, device_accel='brute')
     eng.ray_tracer(bundle, reps=1, min_energy=-1., tree=True)
-    hit = np.nonzero(np.isfinite(prm))[0]
+    hit = np.nonzero(~np.isinf(prm))[0]
     child = eng.tree[1]
     assert np.array_equal(child.get_parents(), hit)
-    np.testing.assert_array_almost_equal(child.get_vertices(), pos[:, hit] + prm[hit] * d[:, hit])
+    stated = np.isfinite(prm[hit])
+    np.testing.assert_array_almost_equal(child.get_vertices()[:, stated],
+                                         (pos[:, hit] + prm[hit] * d[:, hit])[:, stated])
     _, where, normals = opt.get_all_hits()
     if pts is not None:
         np.testing.assert_array_almost_equal(where, pts[:, hit])
