@@ -1,6 +1,7 @@
 """Known answers of the reference's geometry-manager tests -- ray parameters, hit points and
 normals written in tests/test_hemisphere_gm.py, test_paraboloid_gm.py, test_cylinder.py,
-test_flat_geometry_manager.py, test_rect_plate.py, test_round_plate.py, test_triangular_face.py of the reference
+test_flat_geometry_manager.py, test_rect_plate.py, test_round_plate.py, test_triangular_face.py, test_cut_sphere.py, test_parab_dish.py of the
+reference
 -- against the oracle's find_intersections (CPU) and the CUDA kernels (GPU: a one-bounce trace whose
 Location / Normal accountants and child vertices carry what the kernels computed).  These vectors come on
 top of tests/golden/gm_zoo.npz (4000 random rays per geometry kind, recorded from the reference)."""
@@ -158,9 +159,38 @@ def case_triangle_transformed():
     return _triangle(np.dot(sg.translate(0, -1, 0.5), sg.rotx(np.pi / 4.)))
 
 
+def case_cut_sphere():
+    """tests/test_cut_sphere.py:10-43: a bounding sphere placed so that the lower hemisphere remains."""
+    pos, d = _ring()
+    prm = np.full(10, 1 + 2 * np.sin(np.pi / 3))
+    pts = np.vstack((pos[:2], np.full(10, -2 * np.sin(np.pi / 3))))
+    make = (lambda: T.sphere_surface.CutSphereGM(
+        2., T.boundary_shape.BoundarySphere(radius=4., location=np.r_[0., 0., -4 * np.sqrt(3) / 2.])))
+    return make, np.eye(4), pos, d, prm, pts, None
+
+
+def _dish_selection(frame):
+    pos = np.zeros((3, 4))
+    pos[0] = np.r_[0, 0.5, 2, -2]
+    pos[2] = 2.
+    d = np.tile(np.c_[[0, 0, -1.]], (1, 4))
+    return _mask_case(lambda: T.paraboloid.ParabolicDishGM(2., 1.), frame, pos, d, np.r_[False, False, True, True])
+
+
+def case_parab_dish_selection():
+    """tests/test_parab_dish.py:11-28."""
+    return _dish_selection(np.eye(4))
+
+
+def case_parab_dish_transformed():
+    """tests/test_parab_dish.py:30-36: translated and rotated dish."""
+    return _dish_selection(T.spatial_geometry.generate_transform(np.r_[1., 0., 0.], np.pi / 4., np.c_[[0., 0., 1.]]))
+
+
 CASES = [case_hemisphere, case_paraboloid, case_dish_circular, case_dish_hexagonal, case_cylinder_vertical,
          case_cylinder_rotated, case_flat, case_flat_tilted, case_rect_plate, case_rect_plate_extruded,
-         case_round_plate, case_triangle, case_triangle_transformed]
+         case_round_plate, case_triangle, case_triangle_transformed, case_cut_sphere, case_parab_dish_selection,
+         case_parab_dish_transformed]
 
 
 def _surface(make, frame, optics):
