@@ -260,3 +260,43 @@ def test_gpu_one_sided_mirror(rotated):
     e = TracerEngine(asm)
     e.ray_tracer(b, 1, 0.05)
     _check_one_sided(e.tree[-1], verts)
+
+
+@pytest.mark.gpu
+def test_gpu_surface_trace_protocol():
+    """tests/test_flat_surface.py:12-44 of the reference: Surface.register_incoming / select_rays /
+    get_outgoing on a flat mirror, plus the miss masks of tests/test_rect_plate.py:17-27 and
+    tests/test_parab_dish.py:25-36 obtained through register_incoming."""
+    surf = T.surface.Surface(T.flat_surface.FlatGeometryManager(), T.optics_callables.perfect_mirror)
+    d = np.array([[1, 1, -1], [-1, 1, -1], [-1, -1, -1], [1, -1, -1]]).T / math.sqrt(3)
+    pos = np.c_[[0, 0, 1], [1, -1, 1], [1, 1, 1], [-1, 1, 1]].astype(float)
+    bund = T.ray_bundle.RayBundle(pos, d, energy=np.ones(4) * 100)
+    params = surf.register_incoming(bund)
+    np.testing.assert_array_almost_equal(params, np.r_[[math.sqrt(3)] * 4])
+    surf.select_rays(np.arange(4))
+    outg = surf.get_outgoing()
+    correct_pts = np.zeros((3, 4))
+    correct_pts[:2, 0] = 1
+    np.testing.assert_array_almost_equal(outg.get_vertices(), correct_pts, decimal=12)
+    np.testing.assert_array_almost_equal(
+        outg.get_directions(), np.c_[[1, 1, 1], [-1, 1, 1], [-1, -1, 1], [1, -1, 1]] / np.sqrt(3), decimal=12)
+    np.testing.assert_array_equal(outg.get_energy(), np.ones(4) * 100)
+    np.testing.assert_array_equal(outg.get_parents(), np.arange(4))
+    surf.select_rays(np.r_[3, 1])
+    outg = surf.get_outgoing()
+    np.testing.assert_array_equal(outg.get_parents(), np.r_[3, 1])
+    surf.done()
+    assert not hasattr(surf, '_current_bundle')
+
+    pos = np.zeros((3, 4))
+    pos[0] = np.r_[0, 0.5, 2, -2]
+    pos[2] = 1.
+    down = T.ray_bundle.RayBundle(pos, np.tile(np.c_[[0, 0, -1.]], (1, 4)))
+    rect = T.surface.Surface(T.flat_surface.RectPlateGM(1, 0.25), T.optics_callables.perfect_mirror)
+    np.testing.assert_array_equal(np.isinf(rect.register_incoming(down)), np.r_[False, False, True, True])
+    pos[2] = 2.
+    dish = T.surface.Surface(T.paraboloid.ParabolicDishGM(2., 1.), T.optics_callables.perfect_mirror)
+    high = T.ray_bundle.RayBundle(pos, np.tile(np.c_[[0, 0, -1.]], (1, 4)))
+    np.testing.assert_array_equal(np.isinf(dish.register_incoming(high)), np.r_[False, False, True, True])
+    dish.transform_frame(T.spatial_geometry.generate_transform(np.r_[1., 0., 0.], np.pi / 4., np.c_[[0., 0., 1.]]))
+    np.testing.assert_array_equal(np.isinf(dish.register_incoming(high)), np.r_[False, False, True, True])

@@ -87,6 +87,73 @@ class Surface(HasFrame):
     def get_fluxmap(self, eners, local_coords, resolution):
         return self._geom.get_fluxmap(eners, local_coords, resolution)
 
+    # -- the per-surface trace protocol of the reference (surface.py:55-112), served by the same
+    # -- CUDA kernels: each call runs a one-surface, one-bounce trace on the GPU (no host arithmetic).
+    def _single_surface_trace(self, bundle, optics, rng='philox'):
+        from .tracer_engine import TracerEngine
+        twin = Surface(self._geom, optics)
+        twin._temp_frame = self._temp_frame
+        holder = _ProtocolScene(twin)
+        eng = TracerEngine(holder, device_accel='brute', rng=rng)
+        eng.ray_tracer(bundle, reps=1, min_energy=-np.inf, tree=True)
+        return eng.tree[1] if eng.tree.num_bunds() > 1 else None
+
+    def register_incoming(self, ray_bundle):
+        """Records the bundle and returns the ray parameter of its intersection with this surface,
+        +inf for rays that miss (surface.py:55-70)."""
+        from .optics_callables import Transparent
+        from .ray_bundle import RayBundle
+        self._current_bundle = ray_bundle
+        v = np.asarray(ray_bundle.get_vertices(), float)
+        d = np.asarray(ray_bundle.get_directions(), float)
+        params = np.full(v.shape[1], np.inf)
+        child = self._single_surface_trace(
+            RayBundle(vertices=v, directions=d, energy=np.ones(v.shape[1])), Transparent())
+        if child is not None and child.get_num_rays():
+            hit = np.asarray(child.get_parents(), int)
+            params[hit] = np.sum((child.get_vertices() - v[:, hit]) * d[:, hit], axis=0) / np.sum(d[:, hit] ** 2, axis=0)
+        return params
+
+    def select_rays(self, idxs):
+        self._selected = np.asarray(idxs, int)
+
+    def update_current_bundle(self, bundle):
+        self._current_bundle = bundle
+
+    def get_outgoing(self):
+        """The optics of this surface applied to the selected rays of the registered bundle
+        (surface.py:84-94); draws come from numpy.random in the reference's order."""
+        from .ray_bundle import RayBundle
+        sel = self._selected
+        picked = self._current_bundle.inherit(sel)
+        child = self._single_surface_trace(picked, self._opt, rng='numpy')
+        if child is None:
+            return RayBundle.empty_bund()
+        local = np.asarray(child.get_parents(), int)
+        if len(local) != len(sel) and len(np.unique(local)) == len(local) and len(local) < len(sel):
+            raise ValueError("get_outgoing: a selected ray does not intersect this surface")
+        return child.inherit(parents=sel[local])
+
+    def done(self):
+        if hasattr(self, '_current_bundle'):
+            del self._current_bundle
+
+
+class _ProtocolScene(object):
+    """The smallest thing the scene compiler accepts: one surface already carrying its global frame."""
+
+    def __init__(self, surface):
+        self._surface = surface
+
+    def get_surfaces(self):
+        return [self._surface]
+
+    def get_objects(self):
+        return [self]
+
+    def get_boundaries(self):
+        return []
+
 
 class BoundaryShape(HasFrame):
     def in_bounds(self, points):
