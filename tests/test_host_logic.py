@@ -397,3 +397,30 @@ def test_ray_bundle_known_answers_of_the_reference():
     correct = np.hstack((np.ones((3, 4)), np.zeros((3, 4))))
     np.testing.assert_array_equal(con.get_vertices(), correct)
     np.testing.assert_array_equal(con.get_wavelen(), correct)
+
+
+@pytest.mark.skipif(not HAVE_REF, reason='reference tree only exists in the build container')
+def test_spatial_geometry_equals_live_reference():
+    """Rotations and frames array-equal to tracer/spatial_geometry.py, incl. the 14-decimal
+    rounding of general_axis_rotation and the degenerate rows of rotation_to_z."""
+    from oracle import ref_import
+    ref_import.enable()
+    from tracer import spatial_geometry as ref
+    sg = T.spatial_geometry
+    rs = np.random.RandomState(6)
+    for _ in range(20):
+        axis = rs.normal(size=3)
+        axis /= np.linalg.norm(axis)
+        ang = rs.uniform(-4., 4.)
+        assert np.array_equal(sg.general_axis_rotation(axis, ang), ref.general_axis_rotation(axis, ang))
+        tr = rs.normal(size=(3, 1))
+        assert np.array_equal(sg.generate_transform(axis, ang, tr), ref.generate_transform(axis, ang, tr))
+        for name in ('rotx', 'roty', 'rotz'):
+            assert np.array_equal(getattr(sg, name)(ang), getattr(ref, name)(ang)), name
+        assert np.array_equal(sg.translate(*tr[:, 0]), ref.translate(*tr[:, 0]))
+    vecs = rs.normal(size=(50, 3))
+    vecs /= np.sqrt(np.sum(vecs ** 2, axis=1))[:, None]
+    vecs[3] = [0., 0., 1.]
+    vecs[7] = [0., 0., -1.]
+    assert np.array_equal(sg.rotation_to_z(vecs), ref.rotation_to_z(vecs))
+    assert np.array_equal(sg.rotation_to_z(vecs[5]), ref.rotation_to_z(vecs[5]))
