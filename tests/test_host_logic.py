@@ -424,3 +424,9 @@ def test_spatial_geometry_equals_live_reference():
     vecs[7] = [0., 0., -1.]
     assert np.array_equal(sg.rotation_to_z(vecs), ref.rotation_to_z(vecs))
     assert np.array_equal(sg.rotation_to_z(vecs[5]), ref.rotation_to_z(vecs[5]))
+
+
+def test_boundary_sphere_known_answer():
+    """tests/test_boundary_surface.py:10-19 of the reference (the bound CutSphereGM uses)."""
+    pts = np.array([[0., 0., 0.], [1., 1., 1.], [2., 2., 2.]])
+    np.testing.assert_array_equal(T.boundary_shape.BoundarySphere(radius=2.).in_bounds(pts), [True, True, False])
