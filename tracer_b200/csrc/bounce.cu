@@ -127,7 +127,7 @@ __device__ __noinline__ void refractive_slot(const OpticsParams &p, const TrcSur
 // the same bits), applies the optics and writes the child coalesced.  Replaces
 // Surface.select_rays/get_outgoing (surface.py:72-94) for every surface at once.
 #ifndef TRC_OPTICS_MIN_CTAS
-#define TRC_OPTICS_MIN_CTAS 4
+#define TRC_OPTICS_MIN_CTAS 3
 #endif
 // kRefractive: the scene has TRC_O_REFRACTIVE surfaces (the common instantiation does not carry that code).
 template <bool kRefractive>
