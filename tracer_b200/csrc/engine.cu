@@ -69,6 +69,26 @@ __global__ void add_counts_kernel(const int64_t *__restrict__ seg, int n_surface
     if (s < n_surfaces) hits[s] += seg[s + 1] - seg[s];
 }
 
+// Survivors-first reorder of a whole child bundle in one pass: vertices, directions, energy and
+// parents of child perm[j] move to position j (the three trc_gather_rows calls of the step-by-step
+// path read the permutation three times and cost three launches).
+__global__ void __launch_bounds__(256)
+gather_bundle_kernel(int64_t h, const int32_t *__restrict__ perm, const double *__restrict__ v,
+                     const double *__restrict__ d, const double *__restrict__ e, const int64_t *__restrict__ par,
+                     double *__restrict__ ov, double *__restrict__ od, double *__restrict__ oe,
+                     int64_t *__restrict__ opar) {
+    int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= h) return;
+    int64_t src = perm[j];
+    double v0 = v[src], v1 = v[h + src], v2 = v[2 * h + src];
+    double d0 = d[src], d1 = d[h + src], d2 = d[2 * h + src];
+    double en = e[src];
+    int64_t pp = par[src];
+    ov[j] = v0; ov[h + j] = v1; ov[2 * h + j] = v2;
+    od[j] = d0; od[h + j] = d1; od[2 * h + j] = d2;
+    oe[j] = en; opar[j] = pp;
+}
+
 }  // namespace
 
 extern "C" int64_t trc_bounce_keep_bytes(int64_t capacity, uint32_t columns, int32_t has_wavelengths,
@@ -181,13 +201,11 @@ extern "C" int trc_bounce(const TrcScene *sc, const TrcBounceArgs *a, TrcBounceR
         int32_t *k2 = (int32_t *)(scr + sl.off_k2), *perm = (int32_t *)(scr + sl.off_perm);
         rc = trc_sort_pairs(H, 2, cull, nullptr, k2, perm, counters + 2, scr + sl.off_sort_work, stream);
         if (rc != TRC_OK) return rc;
-        rc = trc_gather_rows(H, perm, 3, o.d_out_vertices, H, (double *)(keep + kl.off_sv), H, nullptr, nullptr, stream);
-        if (rc != TRC_OK) return rc;
-        rc = trc_gather_rows(H, perm, 3, o.d_out_directions, H, (double *)(keep + kl.off_sd), H, nullptr, nullptr,
-                             stream);
-        if (rc != TRC_OK) return rc;
-        rc = trc_gather_rows(H, perm, 1, o.d_out_energy, H, (double *)(keep + kl.off_se), H, o.d_out_parents,
-                             (int64_t *)(keep + kl.off_sp), stream);
+        gather_bundle_kernel<<<(unsigned)((H + 255) / 256), 256, 0, st>>>(
+            H, perm, o.d_out_vertices, o.d_out_directions, o.d_out_energy, o.d_out_parents,
+            (double *)(keep + kl.off_sv), (double *)(keep + kl.off_sd), (double *)(keep + kl.off_se),
+            (int64_t *)(keep + kl.off_sp));
+        rc = check_launch("gather_bundle");
         if (rc != TRC_OK) return rc;
         if (has_w) {
             rc = trc_gather_rows(H, perm, 1, o.d_out_wavelengths, H, (double *)(keep + kl.off_sw), H, nullptr, nullptr,
