@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 11
+#define TRC_ABI_VERSION 12
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -269,7 +269,8 @@ int trc_trace_hits(const TrcScene *scene, int64_t n_rays,
 int trc_trace_hits_slice(const TrcScene *scene, int64_t n_rays,
                          const double *d_vertices, const double *d_directions, const double *d_energy, int64_t ld,
                          int32_t use_bvh, int32_t *d_hit_surf,
-                         TrcHitRecord *d_records, int64_t capacity,
+                         TrcHitRecord *d_records, int32_t *d_keys /* nullable: surface index per record */,
+                         int64_t capacity,
                          uint32_t *d_chunk_off, uint32_t *d_chunk_cnt, int64_t *d_total,
                          int64_t ray_base, void *stream);
 
@@ -293,7 +294,7 @@ int trc_order_hits(int64_t n_chunks, const uint32_t *d_chunk_off, const uint32_t
  *   slot q reads record d_records[d_slot_rec[q]] (parent ray + surface).
  *   child q: vertex = hit point, direction per optics, energy, parent index.
  *   d_draws[k] (k < 3) are injected random draws in slot order (NULL => the
- *   kernel draws from Philox4x32-10 keyed by (seed, bounce, slot)).
+ *   kernel draws from Philox4x32-10 keyed by (seed, source-ray id, bounce, draw slot)).
  *   d_wavelengths: per-PARENT-ray wavelengths (indexed by record.ray), nullable.
  *   Optional tallies (NULL to skip): d_absorbed[q] = E_in - E_out
  *   (AbsorptionAccountant :1638-1643), d_normals (3,h) (NormalAccountant),
@@ -340,69 +341,97 @@ typedef struct TrcOpticsArgs {
     const double *d_ref_index;
     double *d_out_ref_index;
     int64_t *d_n_void;
+    /* Identity of the SOURCE ray each ray descends from: the Philox draws of a hit are keyed by
+     * (seed, source-ray id, bounce, draw slot), so a bundle sharded over several GPUs (sources.py
+     * `.../procs`, tracer_engine_mp.py:19-35) draws exactly what the whole bundle draws.  Parent ray r has
+     * id d_ray_ids[r], or ray_id_base + r when d_ray_ids is NULL (a source bundle); children inherit it
+     * into d_out_ray_ids (nullable; indexed by child).  The two children of a TRC_O_REFRACTIVE split get
+     * (id << 1) and (id << 1) | 1. */
+    const int64_t *d_ray_ids;
+    int64_t ray_id_base;
+    int64_t *d_out_ray_ids;
 } TrcOpticsArgs;
 int trc_optics(const TrcScene *scene, const TrcOpticsArgs *args, void *stream);
 
-/* One whole iteration of the reference loop body (tracer_engine.py:193-274) in one call:
- * trc_trace_hits -> hit count -> trc_order_hits -> trc_optics (Philox draws) ->
- * trc_segment_sums + per-surface hit counts -> cull count -> survivors-first reorder when
- * some but not all children are weak.  Same kernels, same results as the step-by-step
- * entry points; the host sequencing just lives in C++ (two stream synchronisations:
- * the hit count and the cull count).  Not for scenes with TRC_O_PERIODIC surfaces nor
- * for injected draws -- those use the step-by-step entry points.
+/* The reference loop (tracer_engine.py:193-274) for up to TRC_TRACE_MAX_BOUNCES iterations, enqueued back to
+ * back on the stream with NO host synchronisation in between: trc_trace_hits -> child order -> trc_optics
+ * (Philox draws) -> per-surface tallies -> survivors-first reorder, per bounce, then one asynchronous copy of
+ * every count to h_counts.  The caller synchronises the stream once and reads h_counts.  The ray count of
+ * every bounce after the first, the hit counts and the cull counts live in device memory; kernels are launched
+ * on grids sized from `capacity[j]` (hits the buffers of bounce j can hold; a multiple of 256).  A bounce
+ * with more hits than its capacity does nothing (hits is still reported), and nothing after it runs on real
+ * data: the caller enlarges the capacity and traces again from that bounce (its input, the children of the
+ * bounce before, is intact).  Same kernels and the same results as the step-by-step entry points.  Not for
+ * scenes with two-children optics (TRC_O_PERIODIC, TRC_O_REFRACTIVE) nor injected draws.
  *
- * Memory: two caller-owned device arenas sized with trc_bounce_keep_bytes /
- * trc_bounce_scratch_bytes for `capacity` hits.  d_scratch may be reused or freed after
- * the call; d_keep holds every output at the byte offsets returned in TrcBounceResult
- * (-1 = absent), laid out for the ACTUAL hit count: rows of `ld` = hits elements.
- * Returns TRC_ERR_CAPACITY with result->hits set when hits > capacity (nothing else is
- * valid then; call again with larger arenas). */
+ * Memory: two caller-owned device arenas sized by trc_trace_plan.  d_scratch is reused by every bounce and may
+ * be freed after the synchronisation; d_keep holds the outputs of bounce j at plan.bounce[j] (byte offsets, -1 =
+ * absent): rows of `ld` = capacity[j] elements of which the first `hits` are valid.
+ *   children, survivors first and weak rays at the back (tracer_engine.py:242-245, 268-274): off_vertices (3,ld),
+ *     off_directions (3,ld), off_energy, off_parents (int64), off_ray_ids (int64), off_wavelengths;
+ *   off_alt_*: the same children in slot order (surface-major, parent-minor) -- only valid when the bounce's
+ *     `reorder` word is 1 (some but not all children weak); otherwise the slot order IS the first copy;
+ *   accountant columns in slot order: off_absorbed, off_normals, off_e_in, off_dirs_in, off_attenuated;
+ *   off_seg: int64 (n_surfaces + 1), surface s owns slots [seg[s], seg[s+1]).
+ * h_counts (page-locked host memory, plan.counts_words int64): per bounce [rays in, hits, survivors, reorder]
+ * followed, with TRC_TRACE_SEG, by the n_surfaces + 1 words of seg. */
 #define TRC_COL_NORMALS    1u
 #define TRC_COL_E_IN       2u
 #define TRC_COL_DIRS_IN    4u
 #define TRC_COL_ATTENUATED 8u
-typedef struct TrcBounceArgs {
-    int64_t n;                        /* rays entering the bounce */
+#define TRC_TRACE_MAX_BOUNCES 8
+#define TRC_TRACE_TIME_WALK 1   /* bracket the first bounce's nearest-hit kernel with CUDA events (trc_trace_walk_ms) */
+#define TRC_TRACE_WALK_DONE 2   /* the caller ran trc_trace_init and then the first bounce's nearest-hit pass itself
+                                   (trc_trace_hits_slice on a bundle still arriving from the host) into the scratch
+                                   buffers named by the plan */
+#define TRC_TRACE_SEG       4   /* copy seg of every bounce to h_counts (accountants need it on the host) */
+typedef struct TrcTraceArgs {
+    int64_t n;                        /* rays entering the first bounce */
     const double *d_vertices;         /* (3,n) rows of stride ld */
     const double *d_directions;
     const double *d_energy;
     int64_t ld;
     const double *d_wavelengths;      /* nullable, per ray */
+    const int64_t *d_ray_ids;         /* nullable: source-ray ids (see TrcOpticsArgs); else ray_id_base + index */
+    int64_t ray_id_base;
     int32_t use_bvh;
-    uint32_t bounce;
+    uint32_t first_bounce;            /* index of the first bounce in the whole trace (Philox stream) */
+    int32_t n_bounces;
+    int32_t flags;                    /* TRC_TRACE_* */
     uint64_t seed;
     double min_energy;
     uint32_t columns;                 /* TRC_COL_*: accountant columns to produce besides `absorbed` */
-    int32_t time_trace;               /* non-zero: bracket the nearest-hit kernel with CUDA events (ev_start/ev_stop) */
-    int64_t capacity;                 /* hits the arenas are sized for */
+    uint32_t pad_;
+    int64_t capacity[TRC_TRACE_MAX_BOUNCES];
     void *d_keep;
     int64_t keep_bytes;
     void *d_scratch;
     int64_t scratch_bytes;
-    int64_t *h_seg;                   /* nullable HOST buffer (n_surfaces + 1): per-surface slot offsets */
     double *d_absorbed_per_surface;   /* (n_surfaces) running totals, updated */
     int64_t *d_hits_per_surface;      /* (n_surfaces) running totals, updated */
-} TrcBounceArgs;
-typedef struct TrcBounceResult {
-    int64_t hits;                     /* children = rays that hit something */
-    int64_t culled;                   /* children with energy <= min_energy */
-    int64_t ld;                       /* row stride of every (3,h) array below = hits */
-    /* children in slot order (surface-major, parent-minor): float64 (3,h), (3,h), (h), int64 (h), float64 (h) */
-    int64_t off_vertices, off_directions, off_energy, off_parents, off_wavelengths;
-    /* the same with survivors first and weak rays at the back; -1 when the slot order already is that order
-     * (nothing or everything culled) */
-    int64_t off_sorted_vertices, off_sorted_directions, off_sorted_energy, off_sorted_parents, off_sorted_wavelengths;
-    /* accountant columns, slot order */
+    int64_t *h_counts;                /* page-locked host memory */
+} TrcTraceArgs;
+typedef struct TrcTraceBounceLayout {
+    int64_t ld;
+    int64_t off_vertices, off_directions, off_energy, off_parents, off_ray_ids, off_wavelengths;
+    int64_t off_alt_vertices, off_alt_directions, off_alt_energy, off_alt_parents, off_alt_ray_ids, off_alt_wavelengths;
     int64_t off_absorbed, off_normals, off_e_in, off_dirs_in, off_attenuated;
-    int64_t off_seg;                  /* int64 (n_surfaces + 1): surface s owns slots [seg[s], seg[s+1]) */
-    void *ev_start, *ev_stop;         /* CUDA events around the nearest-hit kernel when time_trace; release them
-                                         with trc_event_elapsed_ms */
-} TrcBounceResult;
-int64_t trc_bounce_keep_bytes(int64_t capacity, uint32_t columns, int32_t has_wavelengths, int32_t n_surfaces);
-int64_t trc_bounce_scratch_bytes(int64_t n_rays, int64_t capacity, int32_t n_surfaces);
-int trc_bounce(const TrcScene *scene, const TrcBounceArgs *args, TrcBounceResult *result, void *stream);
-/* Waits for ev_stop, returns the elapsed time and destroys both events. */
-int trc_event_elapsed_ms(void *ev_start, void *ev_stop, float *ms);
+    int64_t off_seg;
+} TrcTraceBounceLayout;
+typedef struct TrcTracePlan {
+    int64_t keep_bytes, scratch_bytes, counts_words;
+    TrcTraceBounceLayout bounce[TRC_TRACE_MAX_BOUNCES];
+    /* byte offsets into d_scratch of the first bounce's hit list, for TRC_TRACE_WALK_DONE callers:
+     * records, keys, chunk tables and the int64 hit total (trc_trace_hits_slice arguments) */
+    int64_t off_records, off_keys, off_chunk_off, off_chunk_cnt, off_total;
+} TrcTracePlan;
+/* Needs n, ld, n_bounces, capacity, columns, flags and whether d_wavelengths is set; no GPU work. */
+int trc_trace_plan(const TrcScene *scene, const TrcTraceArgs *args, TrcTracePlan *plan);
+int trc_trace_init(const TrcScene *scene, const TrcTraceArgs *args, void *stream);
+int trc_trace(const TrcScene *scene, const TrcTraceArgs *args, void *stream);
+/* Device time of the first bounce's nearest-hit kernel of the last trc_trace with TRC_TRACE_TIME_WALK on this
+ * scene (waits for it).  A TrcScene serves one stream / one host thread at a time. */
+int trc_trace_walk_ms(const TrcScene *scene, float *ms);
 
 /* Row gather: out[r, j] = in[r, idx[j]] for r < n_rows (float64 rows) and
  * optionally an int64 row.  Applies the cull permutation to a child bundle

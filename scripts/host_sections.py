@@ -22,7 +22,7 @@ def timed(obj, name, label=None):
         finally:
             acc[label or name] = acc.get(label or name, 0.) + time.perf_counter() - t0
     setattr(obj, name, w)
-for nm in ('_bounce_fused', '_account', '_as_bundle', '_to_host', '_to_device', 'compile'):
+for nm in ('_trace_block', '_account', '_as_bundle', '_to_host', '_to_device', 'compile'):
     timed(eng, nm)
 timed(asm, 'reset_all_optics')
 timed(fluxmap, 'receiver_energy_bins')

@@ -186,7 +186,7 @@ def test_philox_energy_conservation_and_statistics():
 
 @pytest.mark.parametrize('name', ['c3_nsttf', 'c5_cavity_spectral', 'c6_optics_zoo'])
 def test_fused_bounce_equals_step_by_step(name):
-    """trc_bounce (the library sequences the bounce) and the step-by-step entry points driven
+    """trc_trace (device-driven: every bounce enqueued at once) and the step-by-step entry points driven
     from Python give identical trees, tallies and accountant data (Philox draws)."""
     builder, kw, seed, reps, min_energy = TRACE_CASES[name]
     out = []

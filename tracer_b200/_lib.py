@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtracer_b200.so")
 
-ABI_VERSION = 11
+ABI_VERSION = 12
 
 # enum TrcGeomKind
 (G_FLAT_INFINITE, G_RECT_PLATE, G_RECT_EXTRUDED, G_ROUND_PLATE, G_TRIANGLE, G_PARABOLOID,
@@ -65,31 +65,43 @@ class OpticsArgs(C.Structure):
         ("d_n_cull", C.c_void_p), ("d_attenuated", C.c_void_p),
         ("d_slot_surf", C.c_void_p), ("d_seg", C.c_void_p), ("d_child_off", C.c_void_p),
         ("d_ref_index", C.c_void_p), ("d_out_ref_index", C.c_void_p), ("d_n_void", C.c_void_p),
+        ("d_ray_ids", C.c_void_p), ("ray_id_base", C.c_int64), ("d_out_ray_ids", C.c_void_p),
     ]
 
 
 COL_NORMALS, COL_E_IN, COL_DIRS_IN, COL_ATTENUATED = 1, 2, 4, 8
 
 
-class BounceArgs(C.Structure):
+TRACE_MAX_BOUNCES = 8
+TRACE_TIME_WALK, TRACE_WALK_DONE, TRACE_SEG = 1, 2, 4
+
+
+class TraceArgs(C.Structure):
     _fields_ = [
         ("n", C.c_int64), ("d_vertices", C.c_void_p), ("d_directions", C.c_void_p), ("d_energy", C.c_void_p),
-        ("ld", C.c_int64), ("d_wavelengths", C.c_void_p),
-        ("use_bvh", C.c_int32), ("bounce", C.c_uint32), ("seed", C.c_uint64), ("min_energy", C.c_double),
-        ("columns", C.c_uint32), ("time_trace", C.c_int32), ("capacity", C.c_int64),
+        ("ld", C.c_int64), ("d_wavelengths", C.c_void_p), ("d_ray_ids", C.c_void_p), ("ray_id_base", C.c_int64),
+        ("use_bvh", C.c_int32), ("first_bounce", C.c_uint32), ("n_bounces", C.c_int32), ("flags", C.c_int32),
+        ("seed", C.c_uint64), ("min_energy", C.c_double), ("columns", C.c_uint32), ("pad_", C.c_uint32),
+        ("capacity", C.c_int64 * TRACE_MAX_BOUNCES),
         ("d_keep", C.c_void_p), ("keep_bytes", C.c_int64), ("d_scratch", C.c_void_p), ("scratch_bytes", C.c_int64),
-        ("h_seg", C.c_void_p), ("d_absorbed_per_surface", C.c_void_p), ("d_hits_per_surface", C.c_void_p),
+        ("d_absorbed_per_surface", C.c_void_p), ("d_hits_per_surface", C.c_void_p), ("h_counts", C.c_void_p),
     ]
 
 
-class BounceResult(C.Structure):
+class TraceBounceLayout(C.Structure):
     _fields_ = [(k, C.c_int64) for k in (
-        "hits", "culled", "ld",
-        "off_vertices", "off_directions", "off_energy", "off_parents", "off_wavelengths",
-        "off_sorted_vertices", "off_sorted_directions", "off_sorted_energy", "off_sorted_parents",
-        "off_sorted_wavelengths",
-        "off_absorbed", "off_normals", "off_e_in", "off_dirs_in", "off_attenuated", "off_seg")] + [
-        ("ev_start", C.c_void_p), ("ev_stop", C.c_void_p)]
+        "ld",
+        "off_vertices", "off_directions", "off_energy", "off_parents", "off_ray_ids", "off_wavelengths",
+        "off_alt_vertices", "off_alt_directions", "off_alt_energy", "off_alt_parents", "off_alt_ray_ids",
+        "off_alt_wavelengths",
+        "off_absorbed", "off_normals", "off_e_in", "off_dirs_in", "off_attenuated", "off_seg")]
+
+
+class TracePlan(C.Structure):
+    _fields_ = [("keep_bytes", C.c_int64), ("scratch_bytes", C.c_int64), ("counts_words", C.c_int64),
+                ("bounce", TraceBounceLayout * TRACE_MAX_BOUNCES),
+                ("off_records", C.c_int64), ("off_keys", C.c_int64), ("off_chunk_off", C.c_int64),
+                ("off_chunk_cnt", C.c_int64), ("off_total", C.c_int64)]
 
 
 class BuieTables(C.Structure):
@@ -119,7 +131,7 @@ SIGNATURES = {
     "trc_scene_num_surfaces": (_I32, [_P]),
     "trc_nearest_hit": (C.c_int, [_P, _I64, _P, _P, _I64, _I32, _P, _P]),
     "trc_trace_hits": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _I32, _P, _P, _I64, _P, _P, _P, _P]),
-    "trc_trace_hits_slice": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _I32, _P, _P, _I64, _P, _P, _P, _I64, _P]),
+    "trc_trace_hits_slice": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _I32, _P, _P, _P, _I64, _P, _P, _P, _I64, _P]),
     "trc_order_work_bytes": (_I64, [_I64, _I64, _I32]),
     "trc_order_hits": (C.c_int, [_I64, _P, _P, _P, _I64, _I32, _P, _P, _P, _P, _P]),
     "trc_sort_work_bytes": (_I64, [_I64, _I32]),
@@ -135,10 +147,10 @@ SIGNATURES = {
     "trc_source_buie_disk": (C.c_int, [_I64, _I64, C.c_uint64, C.POINTER(BuieTables), _DP, _DP, _DP, _D, _D,
                                        _P, _P, _P, _I64, _P]),
     "trc_fluxmap_rect": (C.c_int, [_I64, _P, _I64, _P, _DP, _D, _D, _I32, _I32, _P, _P]),
-    "trc_bounce_keep_bytes": (_I64, [_I64, C.c_uint32, _I32, _I32]),
-    "trc_bounce_scratch_bytes": (_I64, [_I64, _I64, _I32]),
-    "trc_bounce": (C.c_int, [_P, _P, _P, _P]),
-    "trc_event_elapsed_ms": (C.c_int, [_P, _P, C.POINTER(C.c_float)]),
+    "trc_trace_plan": (C.c_int, [_P, C.POINTER(TraceArgs), C.POINTER(TracePlan)]),
+    "trc_trace_init": (C.c_int, [_P, C.POINTER(TraceArgs), _P]),
+    "trc_trace": (C.c_int, [_P, C.POINTER(TraceArgs), _P]),
+    "trc_trace_walk_ms": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "trc_fluxmap_binned": (C.c_int, [_I32, _I64, _P, _I64, _P, _DP, _D, _P, _I32, _P, _I32, _P, _P]),
     "trc_segment_sums": (C.c_int, [_I64, _P, _P, _P, _P]),
 }

@@ -33,6 +33,19 @@ struct OpticsParams {
     const double *ref_index;
     double *o_ref_index;
     unsigned long long *n_void;
+    // source-ray identity (Philox key): id of parent ray r = ids_in ? ids_in[r] : id_base + r; children inherit it
+    const int64_t *ids_in;
+    int64_t id_base;
+    int64_t *o_ids;
+    // device-driven trace (trace.cu): hit count and bookkeeping live in device memory
+    TrcBounceCtl *ctl;            // nullable; when set h = min(ctl->hits, capacity)
+    TrcBounceCtl *ctl_next;       // nullable: receives n_in = survivors
+    int64_t capacity;
+    uint32_t *cta_surv;           // survivors per CTA -> exclusive scan (last block), read by the partition kernel
+    double *cta_sum;              // absorbed energy per CTA (CTAs whose slots lie on one surface)
+    int32_t *cta_key;             //   its surface, or -1 when the CTA used atomics
+    double *absorbed_per_surface;
+    int64_t *d_counts;            // [n_in, hits, survivors, reorder] of this bounce for the final read-back
 };
 
 // Philox draws in the units the reference's numpy calls produce
@@ -106,6 +119,10 @@ __device__ __noinline__ void refractive_slot(const OpticsParams &p, const TrcSur
         p.o_energy[c] = oe;
         p.o_parents[c] = r;
         p.o_ref_index[c] = side ? ro.m2 : m_inherit;
+        if (p.o_ids) {                  // the two children of a split get distinct ids: (id << 1) | side
+            uint64_t id = (uint64_t)(p.ids_in ? p.ids_in[r] : p.id_base + r);
+            p.o_ids[c] = (int64_t)((id << 1) | (uint64_t)side);
+        }
         if (p.o_wavelengths) p.o_wavelengths[c] = wl;
         bool weak = has && oe <= p.min_energy;
         if (p.cull) p.cull[c] = has ? (weak ? 1 : 0) : 2;
@@ -133,9 +150,17 @@ __device__ __noinline__ void refractive_slot(const OpticsParams &p, const TrcSur
 template <bool kRefractive>
 __global__ void __launch_bounds__(256, TRC_OPTICS_MIN_CTAS)
 optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict__ tables, OpticsParams p) {
+    pdl_wait();
+    pdl_trigger();
     int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p.ctl) {                       // device-driven: the hit count never visited the host
+        long long hraw = (long long)p.ctl->hits;
+        p.h = hraw <= p.capacity ? hraw : 0;       // an overflowed bounce does nothing: the host re-runs it
+    }
     bool live = q < p.h;
     bool culled = false;
+    double a_val = 0.0;                // absorbed energy of this slot and its surface (per-surface sums)
+    int a_key = -1;
     if (live) {
         const double2 *rec = reinterpret_cast<const double2 *>(p.records + p.slot_rec[q]);
         double2 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2), r3 = __ldg(rec + 3);
@@ -156,7 +181,8 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
             if (p.draws[1]) u[1] = p.draws[1][q];
             if (p.draws[2]) u[2] = p.draws[2][q];
         } else {
-            philox_draws(s, p.seed, p.bounce, (uint64_t)q, u);
+            // keyed by the SOURCE ray, not by the child slot: a sharded trace draws what the whole trace draws
+            philox_draws(s, p.seed, p.bounce, (uint64_t)(p.ids_in ? p.ids_in[r] : p.id_base + r), u);
         }
         if (kRefractive && s->okind == TRC_O_REFRACTIVE) {
             refractive_slot(p, s, q, sidx, r, v, d, e_in, wl, hit, n, u);
@@ -197,6 +223,12 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
         p.o_energy[c] = e_first;
         p.o_parents[c] = r;
         if (p.o_ref_index) p.o_ref_index[c] = p.ref_index[r];
+        if (p.o_ids) {
+            int64_t id = p.ids_in ? p.ids_in[r] : p.id_base + r;
+            p.o_ids[c] = id;
+            if (c2 >= 0) p.o_ids[c2] = id;
+        }
+        a_val = e_in - o.energy; a_key = sidx;
         if (p.absorbed) p.absorbed[q] = e_in - o.energy;
         if (p.normals) { p.normals[q] = n.x; p.normals[p.ld_out + q] = n.y; p.normals[2 * p.ld_out + q] = n.z; }
         if (p.e_in) p.e_in[q] = e_in;
@@ -210,6 +242,103 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
     if (p.n_cull) {
         unsigned m = __ballot_sync(0xffffffffu, culled);
         if ((threadIdx.x & 31) == 0 && m) atomicAdd(p.n_cull, (unsigned long long)__popc(m));
+    }
+    if (!p.ctl) return;
+    // ---- device-driven trace: per-CTA survivor counts and per-surface absorbed sums, then the last
+    // block to finish closes the bounce (survivor total, reorder decision, next bounce's ray count).
+    __shared__ unsigned s_cnt[8];
+    __shared__ double s_sum[8];
+    __shared__ int s_first, s_last;
+    __shared__ bool s_is_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t blk0 = (int64_t)blockIdx.x * blockDim.x;
+    const bool blk_live = blk0 < p.h;
+    if (blk_live) {
+        unsigned ms = __ballot_sync(0xffffffffu, live && !culled);
+        if (threadIdx.x == 0) s_first = a_key;
+        if (q == p.h - 1 || (live && threadIdx.x == blockDim.x - 1)) s_last = a_key;
+        // warp-level segmented sum of a_val by key (keys are non-decreasing with the lane: slot order)
+        double acc = a_val;
+        int key = a_key;
+        for (int o = 1; o < 32; o <<= 1) {
+            double other = __shfl_down_sync(0xffffffffu, acc, o);
+            int okey = __shfl_down_sync(0xffffffffu, key, o);
+            if (lane + o < 32 && okey == key) acc += other;
+        }
+        int prev = __shfl_up_sync(0xffffffffu, key, 1);
+        const bool head = key >= 0 && (lane == 0 || prev != key);
+        if (lane == 0) { s_cnt[warp] = __popc(ms); s_sum[warp] = 0.0; }
+        __syncthreads();
+        const bool single = s_first == s_last;          // every slot of the CTA lies on one surface
+        if (head) {
+            if (single) s_sum[warp] = acc;              // one head per warp
+            else atomicAdd(&p.absorbed_per_surface[key], acc);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned c = 0;
+            double t = 0.0;
+            for (int w = 0; w < 8; ++w) { c += s_cnt[w]; t += s_sum[w]; }      // fixed order: deterministic
+            p.cta_surv[blockIdx.x] = c;
+            p.cta_sum[blockIdx.x] = t;
+            p.cta_key[blockIdx.x] = single ? s_first : -1;
+        }
+    }
+    __threadfence();
+    if (threadIdx.x == 0) s_is_last = atomicAdd(&p.ctl->ticket_optics, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_is_last) return;
+    __threadfence();
+    const int64_t nb = (p.h + 255) / 256;
+    // (1) exclusive scan of the per-CTA survivor counts, in place
+    __shared__ unsigned s_scan[256];
+    __shared__ unsigned s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (int64_t start = 0; start < nb; start += 1024) {
+        int64_t i0 = start + 4 * (int64_t)threadIdx.x;
+        unsigned v[4], t = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { v[k] = i0 + k < nb ? __ldcg(&p.cta_surv[i0 + k]) : 0u; t += v[k]; }
+        unsigned incl = t;
+        for (int o = 1; o < 32; o <<= 1) { unsigned x = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += x; }
+        if (lane == 31) s_scan[warp] = incl;
+        __syncthreads();
+        unsigned wbase = 0;
+        for (int w = 0; w < warp; ++w) wbase += s_scan[w];
+        unsigned run = s_carry + wbase + incl - t;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { if (i0 + k < nb) p.cta_surv[i0 + k] = run; run += v[k]; }
+        __syncthreads();
+        if (threadIdx.x == 255) s_carry = run;
+        __syncthreads();
+    }
+    // (2) per-surface absorbed energy from the single-surface CTAs: each thread folds a contiguous run of CTAs
+    {
+        int64_t per = (nb + 255) / 256;
+        int64_t b0 = per * threadIdx.x, b1 = b0 + per < nb ? b0 + per : nb;
+        int key = -1;
+        double acc = 0.0;
+        for (int64_t b = b0; b < b1; ++b) {
+            int kk = __ldcg(&p.cta_key[b]);
+            if (kk != key) {
+                if (key >= 0) atomicAdd(&p.absorbed_per_surface[key], acc);
+                key = kk; acc = 0.0;
+            }
+            if (kk >= 0) acc += __ldcg(&p.cta_sum[b]);
+        }
+        if (key >= 0) atomicAdd(&p.absorbed_per_surface[key], acc);
+    }
+    if (threadIdx.x == 0) {
+        const long long hraw = (long long)p.ctl->hits;
+        const long long n_surv = (long long)s_carry;
+        const unsigned overflow = hraw > p.capacity ? 1u : 0u;
+        const unsigned reorder = (n_surv > 0 && n_surv < p.h) ? 1u : 0u;
+        p.ctl->n_surv = n_surv;
+        p.ctl->reorder = reorder;
+        p.ctl->overflow = overflow;
+        if (p.ctl_next) p.ctl_next->n_in = overflow ? 0 : n_surv;     // an overflowed bounce feeds nothing forward
+        p.d_counts[0] = p.ctl->n_in; p.d_counts[1] = hraw; p.d_counts[2] = n_surv; p.d_counts[3] = reorder;
     }
 }
 
@@ -365,7 +494,9 @@ fluxmap_binned_kernel(int coord, int64_t n, const double *__restrict__ hits, int
 
 }  // namespace
 
-extern "C" int trc_optics(const TrcScene *sc, const TrcOpticsArgs *a, void *stream) {
+// dyn != nullptr: launch of the device-driven trace (trace.cu): a->h is the hit CAPACITY (grid size), the
+// count is read from dyn->ctl->hits, and the last block closes the bounce.
+int trc_optics_dyn(const TrcScene *sc, const TrcOpticsArgs *a, const TrcOpticsDyn *dyn, void *stream) {
     if (!sc || !a || a->h < 0) return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: bad argument%s");
     if (a->h == 0) return TRC_OK;
     if (!a->d_records || !a->d_slot_rec || !a->d_out_vertices || !a->d_out_directions || !a->d_out_energy ||
@@ -384,6 +515,14 @@ extern "C" int trc_optics(const TrcScene *sc, const TrcOpticsArgs *a, void *stre
     p.slot_surf = a->d_slot_surf; p.seg = a->d_seg; p.child_off = a->d_child_off;
     p.ref_index = a->d_ref_index; p.o_ref_index = a->d_out_ref_index;
     p.n_void = reinterpret_cast<unsigned long long *>(a->d_n_void);
+    p.ids_in = a->d_ray_ids; p.id_base = a->ray_id_base; p.o_ids = a->d_out_ray_ids;
+    p.ctl = nullptr; p.ctl_next = nullptr; p.capacity = a->h; p.cta_surv = nullptr; p.cta_sum = nullptr;
+    p.cta_key = nullptr; p.absorbed_per_surface = nullptr; p.d_counts = nullptr;
+    if (dyn) {
+        if (sc->has_split) return fail(TRC_ERR_UNSUPPORTED_KIND, "trc_optics: device-driven trace with two-children optics%s");
+        p.ctl = dyn->ctl; p.ctl_next = dyn->ctl_next; p.cta_surv = dyn->cta_surv; p.cta_sum = dyn->cta_sum;
+        p.cta_key = dyn->cta_key; p.absorbed_per_surface = dyn->absorbed_per_surface; p.d_counts = dyn->d_counts;
+    }
     if ((p.ref_index == nullptr) != (p.o_ref_index == nullptr))
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: d_ref_index and d_out_ref_index go together%s");
     if (sc->has_refractive && (!p.ref_index || !p.child_off))
@@ -391,11 +530,18 @@ extern "C" int trc_optics(const TrcScene *sc, const TrcOpticsArgs *a, void *stre
                     "trc_optics: a scene with TRC_O_REFRACTIVE surfaces needs d_ref_index and d_child_off%s");
     if (p.child_off && !p.seg) return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: d_child_off needs d_seg%s");
     int64_t blocks = (a->h + 255) / 256;
-    if (sc->has_refractive)
+    if (dyn)
+        TRC_CUDA(launch_pdl(optics_kernel<false>, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream,
+                            (const TrcSurfaceRec *)sc->d_surfaces, (const double *)sc->d_tables, p));
+    else if (sc->has_refractive)
         optics_kernel<true><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(sc->d_surfaces, sc->d_tables, p);
     else
         optics_kernel<false><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(sc->d_surfaces, sc->d_tables, p);
     return check_launch("optics");
+}
+
+extern "C" int trc_optics(const TrcScene *sc, const TrcOpticsArgs *a, void *stream) {
+    return trc_optics_dyn(sc, a, nullptr, stream);
 }
 
 extern "C" int trc_gather_rows(int64_t n_out, const int32_t *d_idx, int32_t n_rows, const double *d_in,

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.dirname(HERE)
 LIB = os.path.join(PKG, "libtracer_b200.so")
-SOURCES = ["tracer_b200.cu", "nearest.cu", "bvh_build.cu", "sort.cu", "bounce.cu", "sources.cu", "engine.cu"]
+SOURCES = ["tracer_b200.cu", "nearest.cu", "bvh_build.cu", "sort.cu", "bounce.cu", "sources.cu", "trace.cu"]
 HEADERS = ["common.cuh", "geom.cuh", "optics.cuh", "philox.cuh",
            os.path.join("..", "..", "include", "tracer_b200.h")]
 NVCC_FLAGS = [

@@ -32,6 +32,42 @@ static inline int check_launch(const char *what, int n_kernels = 1) {
     return TRC_OK;
 }
 
+// ---- programmatic dependent launch (sm_90+): every kernel of the device-driven trace starts with
+// pdl_wait() in ALL its threads (before any early exit: "kernel B complete" must imply "kernel A
+// complete" for the kernel after B) and may call pdl_trigger() early so that the next kernel's
+// prologue overlaps this one's tail.  Launched without the attribute both are no-ops.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                     Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+
+// ---- device-side control block of the device-driven trace (trace.cu).  One per bounce; the counts
+// never visit the host between the first launch of a trace and its final read-back.
+struct TrcBounceCtl {
+    long long n_in;                    // rays entering the bounce (bounce 0: host; later: survivors of the previous one)
+    unsigned long long chunk_counter;  // dynamic work distribution of the tree walk
+    unsigned long long hits;           // raw hit count of the nearest-hit kernel (may exceed the capacity)
+    long long n_surv;                  // children with energy > min_energy (optics finalize)
+    unsigned int ticket_order;         // "last block" tickets
+    unsigned int ticket_optics;
+    unsigned int reorder;              // 1: some but not all children are weak -> survivors-first reorder runs
+    unsigned int overflow;             // hits > capacity: results of this and later bounces are void
+    long long pad_[2];
+};                                     // 64 bytes
+static_assert(sizeof(TrcBounceCtl) == 64, "TrcBounceCtl layout");
+
 // The tree as the walk reads it: one 32-byte record per INNER node holding the
 // boxes of its two children quantised to 16 bits on the grid of the root box
 // (rounded outward), split into two 16-byte halves kept in separate arrays so
@@ -80,11 +116,36 @@ struct TrcScene {
     int32_t n_unbounded = 0;
     int32_t *d_cand = nullptr;         // leaf surfaces followed by unbounded surfaces (the walk's candidate list)
     int num_sms = 148;
+    int device = 0;                    // CUDA device the tables live on
+    int walk_occ[4] = {0, 0, 0, 0};    // resident CTAs per SM of each tree-walk instantiation (cached query)
     bool flat_only = false;            // every surface is of the flat family (kinds <= TRC_G_TRIANGLE)
     float4 *d_tri32 = nullptr;         // float32 copies of the triangles (3 x float4 per surface) for the walk's
                                        // conservative pre-test; null unless the scene is flat-only and has triangles
     int32_t n_triangles = 0;
     bool has_refractive = false;       // some surface is TRC_O_REFRACTIVE: the optics need the ref_index column
     bool has_split = false;
-    int64_t *h_pinned = nullptr;       // page-locked host words for the count read-backs of trc_bounce: [hits, culled, seg(S+1)]            // some surface emits two child slots per hit (periodic / refractive)
+    int64_t *h_pinned = nullptr;       // page-locked host words for the count read-backs of trc_bounce: [hits, culled, seg(S+1)]
+    cudaEvent_t ev_walk[2] = {nullptr, nullptr};   // reusable event pair around the bounce-0 nearest-hit kernel (time_trace)
 };
+
+// Optics launch of the device-driven trace (bounce.cu).
+struct TrcOpticsDyn {
+    TrcBounceCtl *ctl, *ctl_next;
+    uint32_t *cta_surv;
+    double *cta_sum;
+    int32_t *cta_key;
+    double *absorbed_per_surface;
+    int64_t *d_counts;
+};
+int trc_optics_dyn(const TrcScene *sc, const TrcOpticsArgs *a, const TrcOpticsDyn *dyn, void *stream);
+
+// Nearest-hit launch of the device-driven trace (nearest.cu): the ray count, the work counter and the hit
+// total live in device memory; n_cap sizes the grid.
+struct TrcNearestDyn {
+    const long long *n_ptr;
+    unsigned long long *chunk_counter;
+    unsigned long long *total;
+};
+int trc_nearest_dyn(const TrcScene *sc, int64_t n_cap, const double *d_vert, const double *d_dir, const double *d_energy,
+                    int64_t ld, int32_t use_bvh, TrcHitRecord *d_records, int32_t *d_keys, int64_t capacity,
+                    uint32_t *d_chunk_off, uint32_t *d_chunk_cnt, const TrcNearestDyn *dyn, cudaStream_t st);

@@ -52,6 +52,8 @@ struct HitSink {
     uint32_t *chunk_off, *chunk_cnt;
     unsigned long long *total;
     int32_t ray_base;                  // added to the ray index stored in a record (slices of a larger bundle)
+    int32_t *keys;                     // nullable: surface index of record k at keys[k] (4-byte sort keys, so that
+                                       // the ordering kernels do not fetch a 32-byte sector per hit for them)
 };
 
 __device__ __forceinline__ void store_record(TrcHitRecord *dst, V3 v, V3 d, double e, int ray, int surf) {
@@ -71,11 +73,16 @@ static_assert(TRC_HIT_CHUNK == 256, "one brute-force block = one chunk");
 
 __global__ void __launch_bounds__(256)
 nearest_hit_brute_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict__ pool, int n_surf, int64_t n,
+                         const long long *__restrict__ n_ptr,
                          const double *__restrict__ vert, const double *__restrict__ dir, int64_t ld,
                          HitSink sink) {
     __shared__ TrcSurfaceRec stage[TRC_STAGE_SURFS];
     __shared__ unsigned warp_cnt[8];
     __shared__ unsigned long long block_base;
+    pdl_wait();
+    pdl_trigger();
+    if (n_ptr) n = *n_ptr;             // device-driven trace: the ray count lives in device memory
+    if ((int64_t)blockIdx.x * blockDim.x >= n) return;      // grid sized for the capacity of the input bundle
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     bool live = i < n;
     V3 v = mk(0, 0, 0), d = mk(0, 0, 1);
@@ -117,7 +124,10 @@ nearest_hit_brute_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *
         __syncthreads();
         if (hit) {
             unsigned long long pos = block_base + before + __popc(m & ((1u << lane) - 1u));
-            if ((int64_t)pos < sink.capacity) store_record(sink.records + pos, v, d, sink.energy[i], sink.ray_base + (int)i, best_s);
+            if ((int64_t)pos < sink.capacity) {
+                store_record(sink.records + pos, v, d, sink.energy[i], sink.ray_base + (int)i, best_s);
+                if (sink.keys) sink.keys[pos] = best_s;
+            }
         }
     }
 }
@@ -171,6 +181,8 @@ struct WalkWarpShared {
 // allocated: every KB not carved out for shared memory stays L1 for the float64 stage.
 struct WalkShared {
     WalkWarpShared w[kWalkWarps];
+    long long n_rays;                         // ray count (read from device memory in a device-driven trace); kept
+    long long pad_;                           // here so that it costs no registers in the walk loop
 };
 
 struct WalkParams {
@@ -189,6 +201,7 @@ struct WalkParams {
     int n_cached;                             // pairs cached in shared memory
     float root_lo[3], root_hi[3], qstep[3], extent[3];
     int64_t n;
+    const long long *n_ptr;                   // non-null: the ray count is read from device memory (device-driven trace)
     const double *vert, *dir;
     int64_t ld;
     HitSink sink;
@@ -457,7 +470,9 @@ __device__ __forceinline__ void emit_chunk_hits(WalkWarpShared &sh, const WalkPa
         int64_t ray = chunk_base + i;
         V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
         V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
-        store_record(p.sink.records + pos, v, d, p.sink.energy[ray], p.sink.ray_base + (int)ray, sh.best_s[i]);
+        const int surf = sh.best_s[i];
+        store_record(p.sink.records + pos, v, d, p.sink.energy[ray], p.sink.ray_base + (int)ray, surf);
+        if (p.sink.keys) p.sink.keys[pos] = surf;
     }
     __syncwarp();
 }
@@ -477,9 +492,9 @@ nearest_hit_walk_kernel(WalkParams p) {
     const int lane = threadIdx.x & 31;
     const unsigned full = 0xffffffffu;
     const unsigned lt_mask = (1u << lane) - 1u;
-    const int64_t n_chunks = (p.n + kChunk - 1) / kChunk;
 
-    // top of the tree -> shared memory (breadth-first order: the first kSmemPairs pairs)
+    // top of the tree -> shared memory (breadth-first order: the first kSmemPairs pairs).  The tree is
+    // constant data, so this prologue runs before the grid dependency resolves (PDL).
     {
         uint4 *cache = reinterpret_cast<uint4 *>(walk_smem + sizeof(WalkShared));
         int np = min(p.n_pairs, p.n_cached);
@@ -488,6 +503,9 @@ nearest_hit_walk_kernel(WalkParams p) {
             cache[p.n_cached + k] = __ldg(p.pair_b + k);
         }
     }
+    pdl_wait();
+    pdl_trigger();
+    if (threadIdx.x == 0) S.n_rays = p.n_ptr ? *p.n_ptr : (long long)p.n;
     __syncthreads();
     unsigned pair_a_smem = (unsigned)__cvta_generic_to_shared(walk_smem + sizeof(WalkShared));
     unsigned pair_b_smem = pair_a_smem + 16u * (unsigned)p.n_cached;             // pair_b follows pair_a
@@ -503,6 +521,7 @@ nearest_hit_walk_kernel(WalkParams p) {
     // cp.async, always kRing - 1 batches ahead of stage A, so a ray is read from HBM
     // exactly once and stage A never waits for DRAM.
     int64_t pc;            // chunk being prefetched           (warp-uniform)
+    int pc_n = 0;          // rays in that chunk (0: past the end of the bundle)
     int poff = 0;          // next ray offset in that chunk
     int fifo_w = 0, fifo_r = 0, ring_w = 0, ring_r = 0;
     auto fetch_chunk = [&]() -> int64_t {
@@ -512,12 +531,14 @@ nearest_hit_walk_kernel(WalkParams p) {
         if (lane == 0) sh.fifo[fifo_w & 3] = (long long)c;
         ++fifo_w;
         __syncwarp();
+        long long rem = S.n_rays - (long long)c * kChunk;
+        pc_n = rem <= 0 ? 0 : (rem < kChunk ? (int)rem : kChunk);
         return (int64_t)c;
     };
     auto issue_batch = [&]() {
-        if (pc < n_chunks) {
+        if (pc_n > 0) {
             int64_t ray = pc * kChunk + poff + lane;
-            if (ray < p.n) {
+            if (poff + lane < pc_n) {
                 double *dst = &sh.ring[ring_w % kRing][0][lane];
                 cp_async8(dst, p.vert + ray);
                 cp_async8(dst + 32, p.vert + p.ld + ray);
@@ -527,7 +548,7 @@ nearest_hit_walk_kernel(WalkParams p) {
                 cp_async8(dst + 160, p.dir + 2 * p.ld + ray);
             }
             poff += 32;
-            if (pc * kChunk + poff >= p.n || poff >= kChunk) { pc = fetch_chunk(); poff = 0; }
+            if (poff >= pc_n) { pc = fetch_chunk(); poff = 0; }
         }
         asm volatile("cp.async.commit_group;" ::: "memory");      // possibly empty: keeps the group count uniform
         ++ring_w;
@@ -539,9 +560,9 @@ nearest_hit_walk_kernel(WalkParams p) {
     for (;;) {
         const int64_t c_cur = (int64_t)sh.fifo[fifo_r & 3];
         ++fifo_r;
-        if (c_cur >= n_chunks) break;
         const int64_t chunk_base = c_cur * kChunk;
-        const int chunk_n = (int)min((int64_t)kChunk, p.n - chunk_base);
+        if (chunk_base >= S.n_rays) break;
+        const int chunk_n = (int)min((int64_t)kChunk, (int64_t)S.n_rays - chunk_base);
 
         for (int i = lane; i < kChunk; i += 32) { sh.best_t[i] = TRC_INF_BITS; sh.best_s[i] = INT_MAX; }
         if (lane == 0) sh.q2n = 0;
@@ -698,15 +719,25 @@ nearest_hit_walk_kernel(WalkParams p) {
 
 }  // namespace
 
+// dyn != nullptr: device-driven trace (trace.cu).  `n` is then the CAPACITY of the input bundle (it
+// sizes the grid), the real count is read from dyn->n_ptr by the kernels, the work counter and the
+// hit total live in the trace's control block (already zeroed) and the launch carries the PDL attribute.
 static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir, int64_t ld,
-                          int32_t use_bvh, HitSink sink, cudaStream_t st, bool zero_total = true) {
-    if (sink.records && zero_total) TRC_CUDA(cudaMemsetAsync(sink.total, 0, sizeof(unsigned long long), st));
+                          int32_t use_bvh, HitSink sink, cudaStream_t st, bool zero_total = true,
+                          const TrcNearestDyn *dyn = nullptr) {
+    if (!dyn && sink.records && zero_total) TRC_CUDA(cudaMemsetAsync(sink.total, 0, sizeof(unsigned long long), st));
     if (n == 0) return TRC_OK;
     if (n >= 0x7fffffffLL) return fail(TRC_ERR_CAPACITY, "trc_nearest_hit: more than 2^31-1 rays, chunk the bundle%s");
+    const long long *n_ptr = dyn ? dyn->n_ptr : nullptr;
     if (!use_bvh) {
         int64_t blocks = (n + 255) / 256;
-        nearest_hit_brute_kernel<<<(unsigned)blocks, 256, 0, st>>>(sc->d_surfaces, sc->d_tables, sc->n_surfaces, n, d_vert, d_dir,
-                                                                   ld, sink);
+        if (dyn) {
+            TRC_CUDA(launch_pdl(nearest_hit_brute_kernel, dim3((unsigned)blocks), dim3(256), 0, st, sc->d_surfaces,
+                                sc->d_tables, sc->n_surfaces, n, n_ptr, d_vert, d_dir, ld, sink));
+        } else {
+            nearest_hit_brute_kernel<<<(unsigned)blocks, 256, 0, st>>>(sc->d_surfaces, sc->d_tables, sc->n_surfaces, n,
+                                                                       n_ptr, d_vert, d_dir, ld, sink);
+        }
         return check_launch("nearest_hit_brute");
     }
     if ((sc->n_nodes == 0 && sc->n_unbounded == 0) || !sc->d_chunk_counter || !sc->d_cand)
@@ -715,15 +746,16 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     static const WalkKernel kernels[4] = {nearest_hit_walk_kernel<false, false>, nearest_hit_walk_kernel<true, false>,
                                           nearest_hit_walk_kernel<false, true>, nearest_hit_walk_kernel<true, true>};
     static int g_refill_at = -1;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};       // cudaFuncSetAttribute is per device
+    if (sc->device < 0 || sc->device >= 64) return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: device index out of range%s");
+    if (!attr_set[sc->device]) {
         const char *env = getenv("TRC_WALK_REFILL_AT");      // tuning knob (0..31)
         g_refill_at = 24;
         if (env) { int v = atoi(env); if (v >= 0 && v < 32) g_refill_at = v; }
         for (int k = 0; k < 4; ++k)
             TRC_CUDA(cudaFuncSetAttribute(kernels[k], cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)(sizeof(WalkShared) + 32 * kSmemPairs)));
-        attr_set = true;
+        attr_set[sc->device] = true;
     }
     int n_cached = sc->n_pairs < kSmemPairs ? sc->n_pairs : kSmemPairs;
     n_cached = (n_cached + 7) & ~7;
@@ -746,39 +778,54 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
         p.root_lo[k] = sc->root_lo[k]; p.root_hi[k] = sc->root_hi[k];
         p.qstep[k] = sc->qstep[k]; p.extent[k] = sc->extent[k];
     }
-    p.n = n; p.vert = d_vert; p.dir = d_dir; p.ld = ld; p.sink = sink;
-    p.chunk_counter = sc->d_chunk_counter;
+    p.n = n; p.n_ptr = n_ptr; p.vert = d_vert; p.dir = d_dir; p.ld = ld; p.sink = sink;
+    p.chunk_counter = dyn ? dyn->chunk_counter : sc->d_chunk_counter;
     int64_t n_chunks = (n + kChunk - 1) / kChunk;
     int64_t blocks = (n_chunks + kWalkWarps - 1) / kWalkWarps;
-    int occ = 0;
-    TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernels[variant], kWalkWarps * 32, smem));
-    if (occ < 1) occ = 1;
+    int occ = sc->walk_occ[variant];
+    if (occ <= 0) {
+        TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernels[variant], kWalkWarps * 32, smem));
+        if (occ < 1) occ = 1;
+        const_cast<TrcScene *>(sc)->walk_occ[variant] = occ;     // per scene: depends on the tree's shared-memory share
+    }
     int64_t resident = (int64_t)sc->num_sms * occ;
     if (blocks > resident) blocks = resident;
-    TRC_CUDA(cudaMemsetAsync(sc->d_chunk_counter, 0, sizeof(unsigned long long), st));
-    kernels[variant]<<<(unsigned)blocks, kWalkWarps * 32, smem, st>>>(p);
+    if (dyn) {
+        TRC_CUDA(launch_pdl(kernels[variant], dim3((unsigned)blocks), dim3(kWalkWarps * 32), smem, st, p));
+    } else {
+        TRC_CUDA(cudaMemsetAsync(sc->d_chunk_counter, 0, sizeof(unsigned long long), st));
+        kernels[variant]<<<(unsigned)blocks, kWalkWarps * 32, smem, st>>>(p);
+    }
     return check_launch("nearest_hit_walk");
+}
+
+int trc_nearest_dyn(const TrcScene *sc, int64_t n_cap, const double *d_vert, const double *d_dir, const double *d_energy,
+                    int64_t ld, int32_t use_bvh, TrcHitRecord *d_records, int32_t *d_keys, int64_t capacity,
+                    uint32_t *d_chunk_off, uint32_t *d_chunk_cnt, const TrcNearestDyn *dyn, cudaStream_t st) {
+    HitSink sink = {nullptr, d_energy, d_records, capacity, d_chunk_off, d_chunk_cnt, dyn->total, 0, d_keys};
+    return launch_nearest(sc, n_cap, d_vert, d_dir, ld, use_bvh, sink, st, false, dyn);
 }
 
 extern "C" int trc_nearest_hit(const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir,
                                int64_t ld, int32_t use_bvh, int32_t *d_hit_surf, void *stream) {
     if (!sc || n < 0 || (n > 0 && (!d_vert || !d_dir || !d_hit_surf)) || ld < n)
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: bad argument%s");
-    HitSink sink = {d_hit_surf, nullptr, nullptr, 0, nullptr, nullptr, nullptr, 0};
+    HitSink sink = {d_hit_surf, nullptr, nullptr, 0, nullptr, nullptr, nullptr, 0, nullptr};
     return launch_nearest(sc, n, d_vert, d_dir, ld, use_bvh, sink, (cudaStream_t)stream);
 }
 
 static int trace_hits_impl(const char *who, const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir,
                            const double *d_energy, int64_t ld, int32_t use_bvh, int32_t *d_hit_surf,
-                           TrcHitRecord *d_records, int64_t capacity, uint32_t *d_chunk_off, uint32_t *d_chunk_cnt,
-                           int64_t *d_total, int64_t ray_base, bool zero_total, void *stream) {
+                           TrcHitRecord *d_records, int32_t *d_keys, int64_t capacity, uint32_t *d_chunk_off,
+                           uint32_t *d_chunk_cnt, int64_t *d_total, int64_t ray_base, bool zero_total, void *stream) {
     if (!sc || n < 0 || capacity < 0 || !d_total || ld < n || ray_base < 0 || ray_base % TRC_HIT_CHUNK != 0 ||
         ray_base + n >= 0x7fffffffLL ||
         (n > 0 && (!d_vert || !d_dir || !d_energy || !d_chunk_off || !d_chunk_cnt || (capacity > 0 && !d_records))))
         return fail(TRC_ERR_BAD_ARGUMENT, "%s: bad argument", who);
     static TrcHitRecord dummy_rec;   // never written: capacity 0
     HitSink sink = {d_hit_surf, d_energy, d_records ? d_records : &dummy_rec, d_records ? capacity : 0, d_chunk_off,
-                    d_chunk_cnt, reinterpret_cast<unsigned long long *>(d_total), (int32_t)ray_base};
+                    d_chunk_cnt, reinterpret_cast<unsigned long long *>(d_total), (int32_t)ray_base,
+                    d_records ? d_keys : nullptr};
     return launch_nearest(sc, n, d_vert, d_dir, ld, use_bvh, sink, (cudaStream_t)stream, zero_total);
 }
 
@@ -787,13 +834,13 @@ extern "C" int trc_trace_hits(const TrcScene *sc, int64_t n, const double *d_ver
                               TrcHitRecord *d_records, int64_t capacity, uint32_t *d_chunk_off,
                               uint32_t *d_chunk_cnt, int64_t *d_total, void *stream) {
     return trace_hits_impl("trc_trace_hits", sc, n, d_vert, d_dir, d_energy, ld, use_bvh, d_hit_surf, d_records,
-                           capacity, d_chunk_off, d_chunk_cnt, d_total, 0, true, stream);
+                           nullptr, capacity, d_chunk_off, d_chunk_cnt, d_total, 0, true, stream);
 }
 
 extern "C" int trc_trace_hits_slice(const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir,
                                     const double *d_energy, int64_t ld, int32_t use_bvh, int32_t *d_hit_surf,
-                                    TrcHitRecord *d_records, int64_t capacity, uint32_t *d_chunk_off,
+                                    TrcHitRecord *d_records, int32_t *d_keys, int64_t capacity, uint32_t *d_chunk_off,
                                     uint32_t *d_chunk_cnt, int64_t *d_total, int64_t ray_base, void *stream) {
     return trace_hits_impl("trc_trace_hits_slice", sc, n, d_vert, d_dir, d_energy, ld, use_bvh, d_hit_surf,
-                           d_records, capacity, d_chunk_off, d_chunk_cnt, d_total, ray_base, false, stream);
+                           d_records, d_keys, capacity, d_chunk_off, d_chunk_cnt, d_total, ray_base, false, stream);
 }

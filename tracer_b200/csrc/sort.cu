@@ -247,6 +247,41 @@ extern "C" int trc_sort_pairs(int64_t n, int32_t n_keys, const int32_t *d_keys_i
     return check_launch("sort_pairs", 5 * passes);
 }
 
+// Passes first_shift, first_shift + 8, ... of the same LSD radix sort over *d_n (<= n_cap) pairs whose lower
+// digits are already sorted (the device-driven trace sorts the low digit itself, trace.cu).  Ping-pongs between
+// (k_a, v_a) -- the input -- and (k_b, v_b); *in_a tells where the result ended up.
+int trc_sort_tail_passes(int64_t n_cap, const int64_t *d_n, int32_t n_keys, int first_shift, int32_t *k_a,
+                         int32_t *v_a, int32_t *k_b, int32_t *v_b, void *d_work, cudaStream_t st, bool *in_a) {
+    WorkLayout w = layout(n_cap, n_keys);
+    char *wk = (char *)d_work;
+    uint32_t *hist = (uint32_t *)(wk + w.off_hist);
+    uint32_t *sums = (uint32_t *)(wk + w.off_sums);
+    const int bits = key_bits(n_keys);
+    int32_t *ki = k_a, *vi = v_a, *ko = k_b, *vo = v_b;
+    bool a_holds = true;
+    int launches = 0;
+    for (int shift = first_shift; shift < bits; shift += 8) {
+        int pb = bits - shift < 8 ? bits - shift : 8;
+        int nbins = 1 << pb;
+        int64_t hist_elems = (int64_t)nbins * w.n_tiles;
+        int64_t scan_blocks = (hist_elems + kScanPerBlock - 1) / kScanPerBlock;
+        radix_tile_kernel<false><<<(unsigned)w.n_tiles, kThreads, 0, st>>>(ki, vi, n_cap, d_n, shift, nbins, false,
+                                                                           w.n_tiles, hist, nullptr, nullptr);
+        scan_reduce_kernel<<<(unsigned)scan_blocks, kThreads, 0, st>>>(hist, hist_elems, sums);
+        scan_sums_kernel<<<1, kThreads, 0, st>>>(sums, scan_blocks, nullptr);
+        scan_apply_kernel<<<(unsigned)scan_blocks, kThreads, 0, st>>>(hist, hist_elems, sums);
+        radix_tile_kernel<true><<<(unsigned)w.n_tiles, kThreads, 0, st>>>(ki, vi, n_cap, d_n, shift, nbins, false,
+                                                                          w.n_tiles, hist, ko, vo);
+        int32_t *t;
+        t = ki; ki = ko; ko = t;
+        t = vi; vi = vo; vo = t;
+        a_holds = !a_holds;
+        launches += 5;
+    }
+    *in_a = a_holds;
+    return launches ? check_launch("sort_tail_passes", launches) : TRC_OK;
+}
+
 // ------------------------------------------------------- segment offsets
 namespace {
 __global__ void segment_offsets_kernel(const int64_t *count, int32_t n_keys, const int32_t *__restrict__ keys,

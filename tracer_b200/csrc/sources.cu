@@ -103,7 +103,8 @@ buie_disk_kernel(int64_t n, int64_t first, uint64_t seed, const TrcBuieTables *_
 // The Buie tables are tiny (5 KB); keep one device copy per call site alive in
 // a small cache keyed by content so repeated source calls do not re-upload.
 struct BuieCache { TrcBuieTables host; TrcBuieTables *dev; bool valid; };
-thread_local BuieCache g_buie = {{}, nullptr, false};
+constexpr int kMaxDevices = 64;
+thread_local BuieCache g_buie_dev[kMaxDevices];     // one cached device copy per CUDA device
 
 }  // namespace
 
@@ -152,6 +153,10 @@ static int source_buie(int64_t n, int64_t first_ray, uint64_t seed, const TrcBui
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_source_buie: bad argument%s");
     if (n == 0) return TRC_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    int dev = 0;
+    TRC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return fail(TRC_ERR_BAD_ARGUMENT, "trc_source_buie: device index out of range%s");
+    BuieCache &g_buie = g_buie_dev[dev];
     if (!g_buie.valid || memcmp(&g_buie.host, tables, sizeof(TrcBuieTables)) != 0) {
         if (!g_buie.dev) TRC_CUDA(cudaMalloc(&g_buie.dev, sizeof(TrcBuieTables)));
         // synchronous copy: the cached device table may still be read by an

@@ -1,0 +1,526 @@
+// trc_trace: several iterations of the reference loop body (tracer_engine.py:193-274) enqueued
+// back to back with NO host synchronisation in between.  Every count a later kernel needs -- rays
+// entering a bounce, hits, survivors -- lives in a device-side control block (TrcBounceCtl); grids are
+// sized from host-side capacities; an overflowing bounce raises a flag, does nothing else and feeds
+// nothing forward.  The caller synchronises once, after the final asynchronous copy of the counts.
+//
+// Kernels of one bounce (each starts with griddepcontrol.wait and is launched with the programmatic
+// stream-serialisation attribute, so its prologue overlaps the tail of the one before):
+//   1. nearest_hit_walk / nearest_hit_brute (nearest.cu)  ray count read from the control block
+//   2. order_hist      per (warp tile, surface) hit counts from the 4-byte key array written next to
+//                      the hit records; the last block scans them -> slot offsets per surface (seg)
+//   3. order_scatter   stable (surface-major, ray-minor) slot -> record index
+//      [scenes with more than 256 surfaces: passes 1.. of the LSD radix sort of sort.cu + segment offsets]
+//   4. optics          (bounce.cu) children in slot order, accountant columns, per-surface absorbed
+//                      sums; the last block closes the bounce (survivors, reorder flag, next ray count)
+//   5. partition, 6. swap   only act when some but not all children are weak: survivors first
+//                      (tracer_engine.py:242-245, 268-274); otherwise they exit at once
+#include <new>
+
+#include "common.cuh"
+
+int trc_sort_tail_passes(int64_t n_cap, const int64_t *d_n, int32_t n_keys, int first_shift, int32_t *k_a,
+                         int32_t *v_a, int32_t *k_b, int32_t *v_b, void *d_work, cudaStream_t st, bool *in_a);
+
+namespace {
+
+inline int64_t up256(int64_t x) { return (x + 255) & ~(int64_t)255; }
+
+constexpr int kOrderWarps = 8;
+constexpr int kMaxBins = 256;
+constexpr int kTargetWarpTiles = 592;      // 4 warp tiles per SM: bounds the (tile, surface) table the last block scans
+
+struct OrderParams {
+    TrcBounceCtl *ctl;
+    int64_t capacity;               // hit capacity: offsets beyond it were never written
+    const uint32_t *chunk_off, *chunk_cnt;
+    const int32_t *keys;            // surface index per record
+    int chunks_per_tile;            // chunks of 256 rays handled by one warp, in ray order
+    int n_tiles;                    // warp tiles covering the capacity of the input bundle
+    int nbins;                      // n_keys when <= 256 (single pass), else 256 (low digit of a radix sort)
+    int n_keys;
+    uint32_t *hist;                 // [n_tiles][nbins]; exclusive-scanned over the tiles by the last block
+    int64_t *bin_off;               // [nbins + 1]: == seg (n_keys + 1) for a single pass
+    int64_t *hits_per_surface;      // single pass: += per-surface counts (nullable)
+    int64_t *h_eff;                 // clamped hit count for the kernels that follow
+    int32_t *out_keys, *out_vals;   // scatter targets: slot -> surface, slot -> record index
+};
+
+// Walk the hits of one warp tile in ray order: chunk after chunk, records of a chunk in ascending ray index.
+// f(key, record index, valid) is called with all 32 lanes converged.
+template <typename F>
+__device__ __forceinline__ void for_each_hit_of_tile(const OrderParams &p, int tile, long long n_chunks, F f) {
+    const int lane = threadIdx.x & 31;
+    const long long c0 = (long long)tile * p.chunks_per_tile;
+    long long c1 = c0 + p.chunks_per_tile;
+    if (c1 > n_chunks) c1 = n_chunks;
+    for (long long cb = c0; cb < c1; cb += 32) {
+        long long c = cb + lane;
+        uint32_t off = 0, cnt = 0;
+        if (c < c1) { off = p.chunk_off[c]; cnt = p.chunk_cnt[c]; }
+        if ((long long)off >= p.capacity) cnt = 0;
+        else if ((long long)off + cnt > p.capacity) cnt = (uint32_t)(p.capacity - off);
+        const int nc = (int)((c1 - cb) < 32 ? (c1 - cb) : 32);
+        for (int k = 0; k < nc; ++k) {
+            const uint32_t o = __shfl_sync(0xffffffffu, off, k), n = __shfl_sync(0xffffffffu, cnt, k);
+            for (uint32_t i = 0; i < n; i += 32) {
+                const bool valid = i + lane < n;
+                const int32_t key = valid ? p.keys[o + i + lane] : -1;
+                f(key, (int32_t)(o + i + lane), valid);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kOrderWarps * 32)
+order_hist_kernel(OrderParams p) {
+    __shared__ uint32_t cnt[kOrderWarps][kMaxBins];
+    __shared__ long long s_tot[kMaxBins];
+    __shared__ bool s_is_last;
+    pdl_wait();
+    pdl_trigger();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long hraw = (long long)p.ctl->hits;
+    const bool overflow = hraw > p.capacity;
+    const long long n = overflow ? 0 : p.ctl->n_in;
+    const long long n_chunks = (n + TRC_HIT_CHUNK - 1) / TRC_HIT_CHUNK;
+    const int tile = blockIdx.x * kOrderWarps + warp;
+    const bool single = p.n_keys <= kMaxBins;
+    if (tile < p.n_tiles) {
+        for (int b = lane; b < p.nbins; b += 32) cnt[warp][b] = 0;
+        __syncwarp();
+        for_each_hit_of_tile(p, tile, n_chunks, [&](int32_t key, int32_t, bool valid) {
+            const int dg = valid ? (single ? key : (key & 255)) : -1;
+            const unsigned peers = __match_any_sync(0xffffffffu, dg);
+            if (valid && (peers & ((1u << lane) - 1u)) == 0u) cnt[warp][dg] += __popc(peers);
+            __syncwarp();
+        });
+        for (int b = lane; b < p.nbins; b += 32) p.hist[(size_t)tile * p.nbins + b] = cnt[warp][b];
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_is_last = atomicAdd(&p.ctl->ticket_order, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_is_last) return;
+    __threadfence();
+    // last block: exclusive scan of every bin's column over the tiles, then of the bin totals
+    long long tot = 0;
+    if ((int)threadIdx.x < p.nbins) {
+        uint32_t run = 0;
+        uint32_t *col = p.hist + threadIdx.x;
+#pragma unroll 8
+        for (int t = 0; t < p.n_tiles; ++t) {
+            uint32_t v = __ldcg(col + (size_t)t * p.nbins);
+            col[(size_t)t * p.nbins] = run;
+            run += v;
+        }
+        tot = run;
+    }
+    s_tot[threadIdx.x] = tot;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        long long run = 0;
+        for (int b = 0; b < p.nbins; ++b) { long long v = s_tot[b]; s_tot[b] = run; run += v; }
+        p.bin_off[p.nbins] = run;
+        *p.h_eff = run;
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < p.nbins) {
+        p.bin_off[threadIdx.x] = s_tot[threadIdx.x];
+        if (single && p.hits_per_surface) p.hits_per_surface[threadIdx.x] += tot;
+    }
+}
+
+__global__ void __launch_bounds__(kOrderWarps * 32)
+order_scatter_kernel(OrderParams p) {
+    __shared__ uint32_t pos[kOrderWarps][kMaxBins];
+    pdl_wait();
+    pdl_trigger();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long hraw = (long long)p.ctl->hits;
+    if (hraw > p.capacity) return;
+    const long long n = p.ctl->n_in;
+    const long long n_chunks = (n + TRC_HIT_CHUNK - 1) / TRC_HIT_CHUNK;
+    const int tile = blockIdx.x * kOrderWarps + warp;
+    const bool single = p.n_keys <= kMaxBins;
+    if (tile >= p.n_tiles) return;
+    for (int b = lane; b < p.nbins; b += 32)
+        pos[warp][b] = (uint32_t)p.bin_off[b] + p.hist[(size_t)tile * p.nbins + b];
+    __syncwarp();
+    for_each_hit_of_tile(p, tile, n_chunks, [&](int32_t key, int32_t rec, bool valid) {
+        const int dg = valid ? (single ? key : (key & 255)) : -1;
+        const unsigned peers = __match_any_sync(0xffffffffu, dg);
+        const unsigned before = __popc(peers & ((1u << lane) - 1u));
+        uint32_t base = 0;
+        if (valid) base = pos[warp][dg];
+        __syncwarp();
+        if (valid && before == 0) pos[warp][dg] = base + __popc(peers);
+        __syncwarp();
+        if (valid) {
+            p.out_keys[base + before] = key;
+            p.out_vals[base + before] = rec;
+        }
+    });
+}
+
+__global__ void add_counts_dyn_kernel(const int64_t *__restrict__ seg, int n_surfaces, int64_t *__restrict__ hits) {
+    pdl_wait();
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < n_surfaces) hits[s] += seg[s + 1] - seg[s];
+}
+
+// ---- survivors first, weak rays to the back (tracer_engine.py:242-245, 268-274)
+struct Columns {
+    double *v, *d, *e;
+    int64_t *par, *ids;
+    double *w;                     // nullable
+    int64_t ld;
+};
+struct PartParams {
+    const TrcBounceCtl *ctl;
+    int64_t capacity;
+    const int32_t *cull;
+    const uint32_t *cta_surv;      // exclusive scan of the survivors per 256-slot block (optics finalize)
+    Columns a, b;                  // a: slot order (written by the optics kernel); b: the other copy
+};
+
+__global__ void __launch_bounds__(256)
+partition_kernel(PartParams p) {
+    __shared__ unsigned s_w[8];
+    pdl_wait();
+    pdl_trigger();
+    if (!p.ctl->reorder) return;
+    const long long hraw = (long long)p.ctl->hits;
+    const long long h = hraw < p.capacity ? hraw : p.capacity;
+    const long long blk0 = (long long)blockIdx.x * 256;
+    if (blk0 >= h) return;
+    const long long q = blk0 + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool live = q < h;
+    const bool surv = live && p.cull[q] == 0;
+    const unsigned m = __ballot_sync(0xffffffffu, surv);
+    if (lane == 0) s_w[warp] = __popc(m);
+    __syncthreads();
+    unsigned before = p.cta_surv[blockIdx.x] + __popc(m & ((1u << lane) - 1u));
+    for (int w = 0; w < warp; ++w) before += s_w[w];
+    if (!live) return;
+    const long long n_surv = p.ctl->n_surv;
+    const long long dst = surv ? (long long)before : n_surv + (q - (long long)before);
+    const Columns &a = p.a, &b = p.b;
+    double v0 = a.v[q], v1 = a.v[a.ld + q], v2 = a.v[2 * a.ld + q];
+    double d0 = a.d[q], d1 = a.d[a.ld + q], d2 = a.d[2 * a.ld + q];
+    double en = a.e[q];
+    int64_t pp = a.par[q], id = a.ids[q];
+    b.v[dst] = v0; b.v[b.ld + dst] = v1; b.v[2 * b.ld + dst] = v2;
+    b.d[dst] = d0; b.d[b.ld + dst] = d1; b.d[2 * b.ld + dst] = d2;
+    b.e[dst] = en; b.par[dst] = pp; b.ids[dst] = id;
+    if (a.w) b.w[dst] = a.w[q];
+}
+
+// After the partition the second copy holds the survivors-first order; the next bounce reads the FIRST copy
+// (its kernels were enqueued with those addresses), so the two copies trade contents.
+__global__ void __launch_bounds__(256)
+swap_kernel(PartParams p) {
+    pdl_wait();
+    pdl_trigger();
+    if (!p.ctl->reorder) return;
+    const long long hraw = (long long)p.ctl->hits;
+    const long long h = hraw < p.capacity ? hraw : p.capacity;
+    const long long q = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (q >= h) return;
+    const Columns &a = p.a, &b = p.b;
+#define TRC_SWAP(x, y) { auto t_ = (x); (x) = (y); (y) = t_; }
+    TRC_SWAP(a.v[q], b.v[q]); TRC_SWAP(a.v[a.ld + q], b.v[b.ld + q]); TRC_SWAP(a.v[2 * a.ld + q], b.v[2 * b.ld + q]);
+    TRC_SWAP(a.d[q], b.d[q]); TRC_SWAP(a.d[a.ld + q], b.d[b.ld + q]); TRC_SWAP(a.d[2 * a.ld + q], b.d[2 * b.ld + q]);
+    TRC_SWAP(a.e[q], b.e[q]); TRC_SWAP(a.par[q], b.par[q]); TRC_SWAP(a.ids[q], b.ids[q]);
+    if (a.w) TRC_SWAP(a.w[q], b.w[q]);
+#undef TRC_SWAP
+}
+
+__global__ void trace_init_kernel(TrcBounceCtl *ctl, int n_ctl, long long n0, int64_t *counts, int n_counts) {
+    pdl_wait();
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    long long *w = reinterpret_cast<long long *>(ctl);
+    const int words = n_ctl * (int)(sizeof(TrcBounceCtl) / 8);
+    if (i < words) w[i] = (i == 0) ? n0 : 0;      // word 0 = ctl[0].n_in
+    if (i < n_counts) counts[i] = 0;
+}
+
+// ---- memory plan
+struct KeepOne {
+    int64_t off[21];
+    int64_t total;
+};
+
+void bounce_layout(int64_t base, int64_t cap, uint32_t columns, int has_w, int32_t n_surfaces, TrcTraceBounceLayout *o,
+                   int64_t *end) {
+    int64_t off = base;
+    auto take = [&](int64_t bytes) { int64_t r = off; off = up256(off + bytes); return r; };
+    o->ld = cap;
+    o->off_vertices = take(24 * cap); o->off_directions = take(24 * cap); o->off_energy = take(8 * cap);
+    o->off_parents = take(8 * cap); o->off_ray_ids = take(8 * cap);
+    o->off_wavelengths = has_w ? take(8 * cap) : -1;
+    o->off_alt_vertices = take(24 * cap); o->off_alt_directions = take(24 * cap); o->off_alt_energy = take(8 * cap);
+    o->off_alt_parents = take(8 * cap); o->off_alt_ray_ids = take(8 * cap);
+    o->off_alt_wavelengths = has_w ? take(8 * cap) : -1;
+    o->off_absorbed = take(8 * cap);
+    o->off_normals = (columns & TRC_COL_NORMALS) ? take(24 * cap) : -1;
+    o->off_e_in = (columns & TRC_COL_E_IN) ? take(8 * cap) : -1;
+    o->off_dirs_in = (columns & TRC_COL_DIRS_IN) ? take(24 * cap) : -1;
+    o->off_attenuated = (columns & TRC_COL_ATTENUATED) ? take(8 * cap) : -1;
+    o->off_seg = take(8 * ((int64_t)n_surfaces + 1));
+    *end = off;
+}
+
+struct ScratchPlan {
+    int64_t off_ctl, off_counts, off_heff, off_records, off_keys, off_chunk_off, off_chunk_cnt, off_slot_surf,
+        off_slot_rec, off_alt_k, off_alt_v, off_hist, off_bin_off, off_sort_work, off_cull, off_cta_surv, off_cta_sum,
+        off_cta_key, total;
+    int64_t cap_max, in_max;
+};
+
+int tiles_for(int64_t n_in_cap, int *chunks_per_tile) {
+    int64_t n_chunks = (n_in_cap + TRC_HIT_CHUNK - 1) / TRC_HIT_CHUNK;
+    if (n_chunks < 1) n_chunks = 1;
+    int64_t g = (n_chunks + kTargetWarpTiles - 1) / kTargetWarpTiles;
+    if (g < 1) g = 1;
+    *chunks_per_tile = (int)g;
+    return (int)((n_chunks + g - 1) / g);
+}
+
+int validate(const TrcScene *sc, const TrcTraceArgs *a, const char *who) {
+    if (!sc || !a || a->n < 0 || a->n_bounces < 1 || a->n_bounces > TRC_TRACE_MAX_BOUNCES || a->ld < a->n)
+        return fail(TRC_ERR_BAD_ARGUMENT, "%s: bad argument", who);
+    if (sc->has_split)
+        return fail(TRC_ERR_UNSUPPORTED_KIND, "%s: scenes with two-children optics (periodic, refractive) use the step-by-step calls", who);
+    if (a->n >= 0x7fffffffLL) return fail(TRC_ERR_CAPACITY, "%s: more than 2^31-1 rays, chunk the bundle", who);
+    for (int j = 0; j < a->n_bounces; ++j)
+        if (a->capacity[j] < 256 || a->capacity[j] % 256 != 0 || a->capacity[j] >= 0x7fffffffLL)
+            return fail(TRC_ERR_BAD_ARGUMENT, "%s: capacities must be positive multiples of 256", who);
+    return TRC_OK;
+}
+
+ScratchPlan scratch_plan(const TrcScene *sc, const TrcTraceArgs *a) {
+    ScratchPlan s;
+    const int32_t S = sc->n_surfaces;
+    int64_t cap_max = 0, in_max = a->n;
+    for (int j = 0; j < a->n_bounces; ++j) {
+        if (a->capacity[j] > cap_max) cap_max = a->capacity[j];
+        if (j + 1 < a->n_bounces && a->capacity[j] > in_max) in_max = a->capacity[j];
+    }
+    s.cap_max = cap_max; s.in_max = in_max;
+    const int64_t n_chunks = (in_max + TRC_HIT_CHUNK - 1) / TRC_HIT_CHUNK + 1;
+    int g;
+    const int64_t tiles = tiles_for(in_max, &g);
+    const int nbins = S <= kMaxBins ? S : kMaxBins;
+    const int64_t nb = (cap_max + 255) / 256;
+    int64_t off = 0;
+    auto take = [&](int64_t bytes) { int64_t r = off; off = up256(off + bytes); return r; };
+    s.off_ctl = take((int64_t)sizeof(TrcBounceCtl) * (TRC_TRACE_MAX_BOUNCES + 1));
+    s.off_counts = take(8 * 4 * TRC_TRACE_MAX_BOUNCES);
+    s.off_heff = take(8 * TRC_TRACE_MAX_BOUNCES);
+    s.off_records = take(64 * cap_max);
+    s.off_keys = take(4 * cap_max);
+    s.off_chunk_off = take(4 * n_chunks);
+    s.off_chunk_cnt = take(4 * n_chunks);
+    s.off_slot_surf = take(4 * cap_max);
+    s.off_slot_rec = take(4 * cap_max);
+    const bool multi = S > kMaxBins;
+    s.off_alt_k = take(multi ? 4 * cap_max : 0);
+    s.off_alt_v = take(multi ? 4 * cap_max : 0);
+    s.off_hist = take(4 * tiles * nbins);
+    s.off_bin_off = take(8 * (nbins + 1));
+    s.off_sort_work = take(multi ? trc_sort_work_bytes(cap_max, S) : 0);
+    s.off_cull = take(4 * cap_max);
+    s.off_cta_surv = take(4 * nb);
+    s.off_cta_sum = take(8 * nb);
+    s.off_cta_key = take(4 * nb);
+    s.total = off;
+    return s;
+}
+
+}  // namespace
+
+extern "C" int trc_trace_plan(const TrcScene *sc, const TrcTraceArgs *a, TrcTracePlan *plan) {
+    if (!plan) return fail(TRC_ERR_BAD_ARGUMENT, "trc_trace_plan: bad argument%s");
+    int rc = validate(sc, a, "trc_trace_plan");
+    if (rc != TRC_OK) return rc;
+    memset(plan, 0, sizeof(*plan));
+    const int has_w = a->d_wavelengths ? 1 : 0;
+    int64_t off = 0;
+    for (int j = 0; j < a->n_bounces; ++j) bounce_layout(off, a->capacity[j], a->columns, has_w, sc->n_surfaces, &plan->bounce[j], &off);
+    plan->keep_bytes = off > 0 ? off : 256;
+    ScratchPlan s = scratch_plan(sc, a);
+    plan->scratch_bytes = s.total;
+    plan->counts_words = (int64_t)a->n_bounces * (4 + ((a->flags & TRC_TRACE_SEG) ? sc->n_surfaces + 1 : 0));
+    plan->off_records = s.off_records; plan->off_keys = s.off_keys; plan->off_chunk_off = s.off_chunk_off;
+    plan->off_chunk_cnt = s.off_chunk_cnt;
+    plan->off_total = s.off_ctl + (int64_t)offsetof(TrcBounceCtl, hits);
+    return TRC_OK;
+}
+
+// Zeroes the control blocks of a trace (and sets the first ray count).  trc_trace does this itself unless the
+// caller runs the first nearest-hit pass (TRC_TRACE_WALK_DONE): then it goes first, before the slices.
+extern "C" int trc_trace_init(const TrcScene *sc, const TrcTraceArgs *a, void *stream) {
+    int rc = validate(sc, a, "trc_trace_init");
+    if (rc != TRC_OK) return rc;
+    if (!a->d_scratch) return fail(TRC_ERR_BAD_ARGUMENT, "trc_trace_init: no scratch arena%s");
+    ScratchPlan s = scratch_plan(sc, a);
+    if (a->scratch_bytes < s.total) return fail(TRC_ERR_BAD_ARGUMENT, "trc_trace_init: scratch arena smaller than planned%s");
+    char *scr = (char *)a->d_scratch;
+    const int words = (TRC_TRACE_MAX_BOUNCES + 1) * (int)(sizeof(TrcBounceCtl) / 8);
+    TRC_CUDA(launch_pdl(trace_init_kernel, dim3((words + 255) / 256), dim3(256), 0, (cudaStream_t)stream,
+                        (TrcBounceCtl *)(scr + s.off_ctl), TRC_TRACE_MAX_BOUNCES + 1, (long long)a->n,
+                        (int64_t *)(scr + s.off_counts), 4 * TRC_TRACE_MAX_BOUNCES));
+    return check_launch("trace_init");
+}
+
+extern "C" int trc_trace(const TrcScene *sc, const TrcTraceArgs *a, void *stream) {
+    int rc = validate(sc, a, "trc_trace");
+    if (rc != TRC_OK) return rc;
+    if (!a->d_keep || !a->d_scratch || !a->d_absorbed_per_surface || !a->d_hits_per_surface || !a->h_counts ||
+        (a->n > 0 && (!a->d_vertices || !a->d_directions || !a->d_energy)))
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_trace: null buffer%s");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int32_t S = sc->n_surfaces;
+    const int has_w = a->d_wavelengths ? 1 : 0;
+    TrcTracePlan plan;
+    rc = trc_trace_plan(sc, a, &plan);
+    if (rc != TRC_OK) return rc;
+    ScratchPlan sp = scratch_plan(sc, a);
+    if (a->keep_bytes < plan.keep_bytes || a->scratch_bytes < plan.scratch_bytes)
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_trace: arena smaller than trc_trace_plan asked for%s");
+    char *scr = (char *)a->d_scratch, *keep = (char *)a->d_keep;
+    TrcBounceCtl *ctl = (TrcBounceCtl *)(scr + sp.off_ctl);
+    int64_t *d_counts = (int64_t *)(scr + sp.off_counts);
+    int64_t *d_heff = (int64_t *)(scr + sp.off_heff);
+    TrcHitRecord *records = (TrcHitRecord *)(scr + sp.off_records);
+    int32_t *keys = (int32_t *)(scr + sp.off_keys);
+    uint32_t *chunk_off = (uint32_t *)(scr + sp.off_chunk_off), *chunk_cnt = (uint32_t *)(scr + sp.off_chunk_cnt);
+    int32_t *slot_surf = (int32_t *)(scr + sp.off_slot_surf), *slot_rec = (int32_t *)(scr + sp.off_slot_rec);
+    int32_t *alt_k = (int32_t *)(scr + sp.off_alt_k), *alt_v = (int32_t *)(scr + sp.off_alt_v);
+    const int nbins = S <= kMaxBins ? S : kMaxBins;
+    const bool multi = S > kMaxBins;
+
+    if (!(a->flags & TRC_TRACE_WALK_DONE)) {
+        rc = trc_trace_init(sc, a, stream);
+        if (rc != TRC_OK) return rc;
+    }
+    // bundle entering the current bounce
+    const double *V = a->d_vertices, *D = a->d_directions, *E = a->d_energy, *W = a->d_wavelengths;
+    const int64_t *ids = a->d_ray_ids;
+    int64_t id_base = a->ray_id_base, ld = a->ld, in_cap = a->n;
+    for (int j = 0; j < a->n_bounces; ++j) {
+        const int64_t cap = a->capacity[j];
+        const TrcTraceBounceLayout &L = plan.bounce[j];
+        TrcBounceCtl *c = ctl + j;
+        // 1. nearest hit + hit records
+        if (!(j == 0 && (a->flags & TRC_TRACE_WALK_DONE)) && in_cap > 0) {
+            const bool timed = j == 0 && (a->flags & TRC_TRACE_TIME_WALK);
+            TrcScene *scw = const_cast<TrcScene *>(sc);
+            if (timed) {
+                if (!scw->ev_walk[0]) {
+                    TRC_CUDA(cudaEventCreate(&scw->ev_walk[0]));
+                    TRC_CUDA(cudaEventCreate(&scw->ev_walk[1]));
+                }
+                TRC_CUDA(cudaEventRecord(scw->ev_walk[0], st));
+            }
+            TrcNearestDyn dyn = {&c->n_in, &c->chunk_counter, &c->hits};
+            rc = trc_nearest_dyn(sc, in_cap, V, D, E, ld, a->use_bvh, records, keys, cap, chunk_off, chunk_cnt, &dyn, st);
+            if (rc != TRC_OK) return rc;
+            if (timed) TRC_CUDA(cudaEventRecord(scw->ev_walk[1], st));
+        }
+        // 2./3. child order
+        int64_t *seg = (int64_t *)(keep + L.off_seg);
+        OrderParams op;
+        op.ctl = c; op.capacity = cap; op.chunk_off = chunk_off; op.chunk_cnt = chunk_cnt; op.keys = keys;
+        op.n_tiles = tiles_for(in_cap > 0 ? in_cap : 1, &op.chunks_per_tile);
+        op.nbins = nbins; op.n_keys = S;
+        op.hist = (uint32_t *)(scr + sp.off_hist);
+        op.bin_off = multi ? (int64_t *)(scr + sp.off_bin_off) : seg;
+        op.hits_per_surface = multi ? nullptr : a->d_hits_per_surface;
+        op.h_eff = d_heff + j;
+        // the low digit lands where an even number of further passes brings the result back to the slot arrays
+        int key_bits = 1;
+        while (key_bits < 31 && (1LL << key_bits) < (long long)S) ++key_bits;
+        const int tail_passes = multi ? (key_bits - 8 + 7) / 8 : 0;
+        const bool first_to_alt = (tail_passes & 1) != 0;
+        op.out_keys = first_to_alt ? alt_k : slot_surf;
+        op.out_vals = first_to_alt ? alt_v : slot_rec;
+        const unsigned oblocks = (unsigned)((op.n_tiles + kOrderWarps - 1) / kOrderWarps);
+        TRC_CUDA(launch_pdl(order_hist_kernel, dim3(oblocks), dim3(kOrderWarps * 32), 0, st, op));
+        TRC_CUDA(launch_pdl(order_scatter_kernel, dim3(oblocks), dim3(kOrderWarps * 32), 0, st, op));
+        rc = check_launch("order", 2);
+        if (rc != TRC_OK) return rc;
+        if (multi) {
+            bool in_first = true;
+            rc = trc_sort_tail_passes(cap, d_heff + j, S, 8, op.out_keys, op.out_vals, first_to_alt ? slot_surf : alt_k,
+                                      first_to_alt ? slot_rec : alt_v, scr + sp.off_sort_work, st, &in_first);
+            if (rc != TRC_OK) return rc;
+            if (in_first != !first_to_alt) return fail(TRC_ERR_BAD_ARGUMENT, "trc_trace: radix pass parity%s");
+            rc = trc_segment_offsets_dyn(d_heff + j, cap, S, slot_surf, seg, stream);
+            if (rc != TRC_OK) return rc;
+            add_counts_dyn_kernel<<<(S + 255) / 256, 256, 0, st>>>(seg, S, a->d_hits_per_surface);
+            rc = check_launch("add_counts");
+            if (rc != TRC_OK) return rc;
+        }
+        // 4. optics, accountant columns, per-surface sums; its last block closes the bounce
+        TrcOpticsArgs o;
+        memset(&o, 0, sizeof(o));
+        o.h = cap; o.d_records = records; o.d_slot_rec = slot_rec; o.d_wavelengths = W;
+        o.d_out_vertices = (double *)(keep + L.off_vertices); o.d_out_directions = (double *)(keep + L.off_directions);
+        o.d_out_energy = (double *)(keep + L.off_energy); o.d_out_parents = (int64_t *)(keep + L.off_parents);
+        o.d_out_ray_ids = (int64_t *)(keep + L.off_ray_ids);
+        o.ld_out = cap;
+        o.seed = a->seed; o.bounce = a->first_bounce + (uint32_t)j; o.min_energy = a->min_energy;
+        o.d_absorbed = (double *)(keep + L.off_absorbed);
+        o.d_normals = L.off_normals >= 0 ? (double *)(keep + L.off_normals) : nullptr;
+        o.d_e_in = L.off_e_in >= 0 ? (double *)(keep + L.off_e_in) : nullptr;
+        o.d_dirs_in = L.off_dirs_in >= 0 ? (double *)(keep + L.off_dirs_in) : nullptr;
+        o.d_attenuated = L.off_attenuated >= 0 ? (double *)(keep + L.off_attenuated) : nullptr;
+        o.d_out_wavelengths = has_w ? (double *)(keep + L.off_wavelengths) : nullptr;
+        o.d_cull = (int32_t *)(scr + sp.off_cull);
+        o.d_ray_ids = ids; o.ray_id_base = id_base;
+        TrcOpticsDyn od = {c, c + 1, (uint32_t *)(scr + sp.off_cta_surv), (double *)(scr + sp.off_cta_sum),
+                           (int32_t *)(scr + sp.off_cta_key), a->d_absorbed_per_surface, d_counts + 4 * j};
+        rc = trc_optics_dyn(sc, &o, &od, stream);
+        if (rc != TRC_OK) return rc;
+        // 5./6. survivors first (acts only when some but not all children are weak)
+        PartParams pp;
+        pp.ctl = c; pp.capacity = cap; pp.cull = o.d_cull; pp.cta_surv = od.cta_surv;
+        pp.a = {o.d_out_vertices, o.d_out_directions, o.d_out_energy, o.d_out_parents, o.d_out_ray_ids,
+                o.d_out_wavelengths, cap};
+        pp.b = {(double *)(keep + L.off_alt_vertices), (double *)(keep + L.off_alt_directions),
+                (double *)(keep + L.off_alt_energy), (int64_t *)(keep + L.off_alt_parents),
+                (int64_t *)(keep + L.off_alt_ray_ids), has_w ? (double *)(keep + L.off_alt_wavelengths) : nullptr, cap};
+        const unsigned pblocks = (unsigned)((cap + 255) / 256);
+        TRC_CUDA(launch_pdl(partition_kernel, dim3(pblocks), dim3(256), 0, st, pp));
+        TRC_CUDA(launch_pdl(swap_kernel, dim3(pblocks), dim3(256), 0, st, pp));
+        rc = check_launch("partition", 2);
+        if (rc != TRC_OK) return rc;
+        // the children (survivors first) are the next bundle
+        V = o.d_out_vertices; D = o.d_out_directions; E = o.d_out_energy; W = o.d_out_wavelengths;
+        ids = o.d_out_ray_ids; id_base = 0; ld = cap; in_cap = cap;
+    }
+    // one read-back for the whole trace
+    const int64_t per = 4 + ((a->flags & TRC_TRACE_SEG) ? S + 1 : 0);
+    if (per == 4) {
+        TRC_CUDA(cudaMemcpyAsync(a->h_counts, d_counts, sizeof(int64_t) * 4 * (size_t)a->n_bounces, cudaMemcpyDeviceToHost, st));
+    } else {
+        for (int j = 0; j < a->n_bounces; ++j) {
+            TRC_CUDA(cudaMemcpyAsync(a->h_counts + per * j, d_counts + 4 * j, sizeof(int64_t) * 4, cudaMemcpyDeviceToHost, st));
+            TRC_CUDA(cudaMemcpyAsync(a->h_counts + per * j + 4, keep + plan.bounce[j].off_seg,
+                                     sizeof(int64_t) * (size_t)(S + 1), cudaMemcpyDeviceToHost, st));
+        }
+    }
+    return TRC_OK;
+}
+
+// Device time of the first bounce's nearest-hit kernel of the last trc_trace that asked for it
+// (TRC_TRACE_TIME_WALK); waits for that kernel.  The event pair belongs to the scene and is reused.
+extern "C" int trc_trace_walk_ms(const TrcScene *sc, float *ms) {
+    if (!sc || !ms || !sc->ev_walk[0]) return fail(TRC_ERR_BAD_ARGUMENT, "trc_trace_walk_ms: no timed trace on this scene%s");
+    TRC_CUDA(cudaEventSynchronize(sc->ev_walk[1]));
+    TRC_CUDA(cudaEventElapsedTime(ms, sc->ev_walk[0], sc->ev_walk[1]));
+    return TRC_OK;
+}

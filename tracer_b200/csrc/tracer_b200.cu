@@ -74,6 +74,7 @@ extern "C" int trc_scene_create(const TrcSurfaceRec *surfaces, int32_t n_surface
     int dev = 0;
     if (e == cudaSuccess) e = cudaGetDevice(&dev);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sc->num_sms, cudaDevAttrMultiProcessorCount, dev);
+    sc->device = dev;
     if (e != cudaSuccess) {
         trc_scene_destroy(sc);
         return fail(TRC_ERR_CUDA, "trc_scene_create: %s", cudaGetErrorString(e));
@@ -96,6 +97,8 @@ extern "C" int trc_scene_destroy(TrcScene *sc) {
     cudaFree(sc->d_leaf_surfaces);
     cudaFree(sc->d_unbounded);
     if (sc->h_pinned) cudaFreeHost(sc->h_pinned);
+    if (sc->ev_walk[0]) cudaEventDestroy(sc->ev_walk[0]);
+    if (sc->ev_walk[1]) cudaEventDestroy(sc->ev_walk[1]);
     delete sc;
     return TRC_OK;
 }

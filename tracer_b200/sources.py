@@ -267,15 +267,26 @@ def _device_bundle_buffers(num_rays, device):
     return dev, V, D, E
 
 
-def _wrap(V, D, E):
-    return RayBundle(vertices=_DeviceColumns([V]), directions=_DeviceColumns([D]), energy=_DeviceColumns([E]))
+def _wrap(V, D, E, first_ray=0):
+    """Device-backed bundle.  ``_ray_id_base`` is the global index of its first ray: the engine keys the
+    optics draws of every descendant by (seed, global source-ray index, bounce), so the shards of one source
+    traced on several GPUs draw exactly what the whole source draws."""
+    b = RayBundle(vertices=_DeviceColumns([V]), directions=_DeviceColumns([D]), energy=_DeviceColumns([E]))
+    b.__dict__['_ray_id_base'] = int(first_ray)
+    return b
+
+
+def _need_flux(flux, who):
+    if flux is None:
+        raise ValueError(who + ": flux (W/m2) is required")
 
 
 def disk_bundle_device(num_rays, center, direction, radius, ang_range, flux=None, radius_in=0.,
                        angular_span=[0., 2. * np.pi], procs=1, rays_direction=None, seed=0, first_ray=0,
-                       device=None):
+                       total_rays=None, device=None):
     """``disk_bundle`` generated in HBM by the Philox pillbox kernel.  ``seed`` and
-    ``first_ray`` (global index of this shard's first ray) fix the bundle."""
+    ``first_ray`` (global index of this shard's first ray) fix the bundle; a source of ``total_rays``
+    sharded over GPUs passes the common total so that the per-ray energy is that of the whole source."""
     import torch
     from . import _lib as L
     lib = L.load()
@@ -285,9 +296,9 @@ def disk_bundle_device(num_rays, center, direction, radius, ang_range, flux=None
     rot = rotation_to_z(rays_direction)
     if flux is not None:
         ang = 2. * np.sin(np.sqrt(np.sum((rays_direction - direction) ** 2)) / 2.)
-        e = np.pi * (float(radius) ** 2. - float(radius_in) ** 2.) / num_rays * flux * np.cos(ang)
+        e = np.pi * (float(radius) ** 2. - float(radius_in) ** 2.) / (total_rays or num_rays) * flux * np.cos(ang)
     else:
-        e = 1. / float(num_rays) / procs
+        e = 1. / float(total_rays or num_rays) / procs
     dev, V, D, E = _device_bundle_buffers(num_rays, device)
     _, c = L.host_doubles(center, 3)
     _, rd = L.host_doubles(rot, 9)
@@ -296,7 +307,7 @@ def disk_bundle_device(num_rays, center, direction, radius, ang_range, flux=None
         L.check(lib.trc_source_pillbox_disk(num_rays, first_ray, seed, c, rd, rd, float(radius_in), float(radius),
                                             float(angular_span[0]), float(angular_span[1]), float(ang_range),
                                             float(e), L.dptr(V), L.dptr(D), L.dptr(E), num_rays, st))
-    return _wrap(V, D, E)
+    return _wrap(V, D, E, first_ray)
 
 
 def buie_sunshape_device(num_rays, center, direction, radius, CSR, flux=None, pre_process_CSR=True,
@@ -307,6 +318,7 @@ def buie_sunshape_device(num_rays, center, direction, radius, CSR, flux=None, pr
     import torch
     from . import _lib as L
     lib = L.load()
+    _need_flux(flux, 'buie_sunshape_device')
     direction = np.asarray(direction, float)
     if rays_direction is None:
         rays_direction = direction
@@ -327,7 +339,7 @@ def buie_sunshape_device(num_rays, center, direction, radius, CSR, flux=None, pr
         st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         L.check(lib.trc_source_buie_disk(num_rays, first_ray, seed, C.byref(t), c, rd, rp, float(radius), float(e),
                                          L.dptr(V), L.dptr(D), L.dptr(E), num_rays, st))
-    return _wrap(V, D, E)
+    return _wrap(V, D, E, first_ray)
 
 
 def _rect_local_half_extents(x, y, plane_normal):
@@ -365,7 +377,7 @@ def rect_bundle_device(num_rays, center, direction, x, y, ang_range, flux=None, 
         st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         L.check(lib.trc_source_pillbox_rect(num_rays, first_ray, seed, c, rd, rp, float(hx), float(hy),
                                             float(ang_range), float(e), L.dptr(V), L.dptr(D), L.dptr(E), num_rays, st))
-    return _wrap(V, D, E)
+    return _wrap(V, D, E, first_ray)
 
 
 def oblique_solar_rect_bundle_device(num_rays, center, source_direction, rays_direction, x, y, ang_range, flux=None,
@@ -381,6 +393,7 @@ def rect_buie_sunshape_device(num_rays, center, direction, width, height, CSR, f
     import torch
     from . import _lib as L
     lib = L.load()
+    _need_flux(flux, 'rect_buie_sunshape_device')
     direction = np.asarray(direction, float)
     if rays_direction is None:
         rays_direction = direction
@@ -401,4 +414,4 @@ def rect_buie_sunshape_device(num_rays, center, direction, width, height, CSR, f
         st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         L.check(lib.trc_source_buie_rect(num_rays, first_ray, seed, C.byref(t), c, rd, rp, float(width) / 2.,
                                          float(height) / 2., float(e), L.dptr(V), L.dptr(D), L.dptr(E), num_rays, st))
-    return _wrap(V, D, E)
+    return _wrap(V, D, E, first_ray)

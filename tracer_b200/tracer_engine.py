@@ -6,11 +6,14 @@ Kd_Tree)`` keeps the reference signature, return value and side effects
 (``self.tree``, accountant data behind ``get_all_hits()``, log messages) but the
 per-bounce work -- every find_intersections, the nearest-hit reduction, the
 optics callables, accountants, culling and child-bundle concatenation -- runs on
-the GPU through libtracer_b200.so.  Python only sizes buffers (torch CUDA
-tensors) and sequences ~10 launches per bounce.
+the GPU through libtracer_b200.so.  With Philox draws the whole loop is device
+driven (``trc_trace``): Python plans buffer capacities from the previous trace,
+enqueues up to eight bounces in one foreign call, synchronises ONCE and reads
+every count back together; no count visits the host in between.
 
 Random draws: ``rng='philox'`` (default) draws on device, keyed by
-(seed, bounce, child slot).  ``rng='numpy'`` draws on the host from
+(seed, source-ray id, bounce, draw slot), so a bundle sharded over GPUs draws
+what the whole bundle draws.  ``rng='numpy'`` draws on the host from
 ``numpy.random`` in exactly the reference's order (bounce -> surface ->
 draw kind -> hit) and injects them, so a trace with the
 same ``numpy.random.seed`` reproduces the reference bundle for bundle.
@@ -49,11 +52,13 @@ class _LazyRows(object):
 class _DevBundle(object):
     """Engine-internal view of a bundle living in HBM.  ``slices`` is set while a
     host bundle is still arriving: [(first ray, end ray, CUDA event of its copy)]."""
-    __slots__ = ('V', 'D', 'E', 'W', 'R', 'n', 'slices', 'keep')
+    __slots__ = ('V', 'D', 'E', 'W', 'R', 'I', 'id_base', 'n', 'slices', 'keep')
 
-    def __init__(self, V, D, E, W=None, slices=None, keep=None, R=None):
+    def __init__(self, V, D, E, W=None, slices=None, keep=None, R=None, I=None, id_base=0):
         self.V, self.D, self.E, self.W = V, D, E, W
         self.R = R                # ref_index column (refractive scenes), else None
+        self.I = I                # source-ray id of each ray (int64), None: id_base + index
+        self.id_base = int(id_base)
         self.n = int(V.shape[1])
         self.slices = slices
         self.keep = keep          # host arrays of the copies in flight
@@ -61,6 +66,12 @@ class _DevBundle(object):
 
 STREAM_MIN_RAYS = 1 << 22     # host bundles at least this large are uploaded in slices ...
 STREAM_SLICES = 8             # ... this many, each traced while the next one is copied
+FULL_CAP_RAYS = 1 << 18       # bundles up to this size get buffers for "every ray hits" (no overflow possible)
+BLIND_BOUNCES = 4             # bounces enqueued per call while the depth of the trace is unknown
+
+
+def _round_cap(x):
+    return max(256, (int(x) + 255) // 256 * 256)
 
 
 class TracerEngine(object):
@@ -94,6 +105,9 @@ class TracerEngine(object):
         self._scene = None
         self._frames_key = None
         self._hit_frac = {}       # bounce -> hit fraction of the previous trace (sizes the hit list)
+        self._hist = {}           # bounce -> (rays in, hits, survivors) of the previous trace (plans trc_trace)
+        self._cap_floor = {}      # bounce -> smallest capacity that is known to fit (set after an overflow)
+        self._counts_host = None  # page-locked int64 words for the one read-back of a trace
         self._copy_stream = None
         self._keep_tree = False
         self.fused_bounce = True   # sequence a bounce inside the library (trc_bounce) when the configuration allows
@@ -132,6 +146,7 @@ class TracerEngine(object):
                 self._scene.close()
             self._scene = CompiledScene(self._asm, leaf_size=self.leaf_size)
             self._hit_frac = {}
+            self._hist, self._cap_floor = {}, {}
             self._frames_key = key
             self._frames_ref = (surfaces, frames)
         return self._scene
@@ -158,8 +173,10 @@ class TracerEngine(object):
             arr = np.ascontiguousarray(arr, dtype=np.float64)
             return torch.from_numpy(arr).to(self.device, non_blocking=True)
 
+        id_base = int(getattr(bundle, '_ray_id_base', 0) or 0)
         streamed = self._upload_in_slices(bundle)
         if streamed is not None:
+            streamed.id_base = id_base
             return streamed
         V, D, E = col('vertices'), col('directions'), col('energy')
         W = col('wavelengths', required=False) if bundle.has_property('wavelengths') else None
@@ -169,7 +186,7 @@ class TracerEngine(object):
         if V.dim() != 2 or V.shape[0] != 3 or D.shape != V.shape or E.shape[0] != V.shape[1]:
             raise ValueError("bundle arrays must be vertices (3,n), directions (3,n), energy (n,)")
         return _DevBundle(V.contiguous(), D.contiguous(), E.contiguous(), None if W is None else W.contiguous(),
-                          R=None if R is None else R.contiguous())
+                          R=None if R is None else R.contiguous(), id_base=id_base)
 
     def _upload_in_slices(self, bundle):
         """Large host bundle: allocate it in HBM and enqueue the host->device copy in
@@ -290,9 +307,6 @@ class TracerEngine(object):
         -> trc_optics -> trc_segment_sums [-> cull sort + gathers].  Two host
         syncs: the hit count (sizes the child bundle) and the cull count."""
         import torch
-        if self.fused_bounce and self.rng == 'philox' and not scene.has_split and cur.slices is None \
-                and cur.R is None:
-            return self._bounce_fused(scene, cur, bounce, min_energy, use_bvh)
         lib = L.load()
         dev = self.device
         st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
@@ -317,7 +331,7 @@ class TracerEngine(object):
                     c0 = a // L.HIT_CHUNK
                     L.check(lib.trc_trace_hits_slice(
                         scene.handle, b - a, cur.V.data_ptr() + 8 * a, cur.D.data_ptr() + 8 * a,
-                        cur.E.data_ptr() + 8 * a, ld, 1 if use_bvh else 0, None, L.dptr(records), cap,
+                        cur.E.data_ptr() + 8 * a, ld, 1 if use_bvh else 0, None, L.dptr(records), None, cap,
                         chunk_off.data_ptr() + 4 * c0, chunk_cnt.data_ptr() + 4 * c0, L.dptr(counters), a, st))
                 cur.slices = cur.keep = None   # resident from here on (an overflow re-runs the plain call)
                 H = int(counters[0].item())
@@ -374,6 +388,7 @@ class TracerEngine(object):
             raise ValueError("Spectral accountant needs a 'wavelengths' bundle property")
         oW = torch.empty(Hc, dtype=f64, device=dev) if cur.W is not None else None
         oR = torch.empty(Hc, dtype=f64, device=dev) if cur.R is not None else None
+        oI = torch.empty(Hc, dtype=i64, device=dev)
         a = L.OpticsArgs()
         a.h = H
         a.d_records, a.d_slot_rec = records.data_ptr(), slot_rec.data_ptr()
@@ -385,6 +400,8 @@ class TracerEngine(object):
         a.seed, a.bounce, a.min_energy = self.seed, bounce, float(min_energy)
         if cur.R is not None:
             a.d_ref_index, a.d_out_ref_index = cur.R.data_ptr(), oR.data_ptr()
+        a.d_ray_ids = cur.I.data_ptr() if cur.I is not None else None
+        a.ray_id_base, a.d_out_ray_ids = cur.id_base, oI.data_ptr()
         draws = None
         if self.rng == 'numpy':
             theta_in = None
@@ -439,104 +456,190 @@ class TracerEngine(object):
             L.check(lib.trc_gather_rows(Hc, L.dptr(perm), 1, L.dptr(oE), Hc, L.dptr(pE), Hc, L.dptr(oP), L.dptr(pP), st))
             pW = oW.index_select(0, perm.long()) if oW is not None else None
             pR = oR.index_select(0, perm.long()) if oR is not None else None
-            return pV, pD, pE, pP, pW, pR, perm
+            pI = oI.index_select(0, perm.long())
+            return pV, pD, pE, pP, pW, pR, pI, perm
 
         if n_void:
             # refractive surfaces leave void child slots (cull code 2): drop them, keeping the order
             is_void = (cull == 2).to(i32)
-            pV, pD, pE, pP, pW, pR, perm = reorder(is_void, 2)
+            pV, pD, pE, pP, pW, pR, pI, perm = reorder(is_void, 2)
             Hc -= n_void
             cull = cull.index_select(0, perm[:Hc].long()).contiguous()
             oV, oD = pV[:, :Hc].contiguous(), pD[:, :Hc].contiguous()
             oE, oP = pE[:Hc].contiguous(), pP[:Hc].contiguous()
             oW = pW[:Hc].contiguous() if pW is not None else None
             oR = pR[:Hc].contiguous() if pR is not None else None
+            oI = pI[:Hc].contiguous()
             if Hc == 0:
                 return None, 0, H
-        rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR)
+        rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR, I=oI)
         if n_cull and n_cull < Hc:
             # survivors first, weak rays at the back (tracer_engine.py:242-245, 268-274)
-            pV, pD, pE, pP, pW, pR, _ = reorder(cull, 2)
-            rec = dict(V=pV, D=pD, E=pE, P=pP, W=pW, R=pR)
+            pV, pD, pE, pP, pW, pR, pI, _ = reorder(cull, 2)
+            rec = dict(V=pV, D=pD, E=pE, P=pP, W=pW, R=pR, I=pI)
         rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR)
         return rec, Hc - n_cull, H
 
-    def _bounce_fused(self, scene, cur, bounce, min_energy, use_bvh):
-        """The same iteration through trc_bounce: the launch sequence, the two count read-backs
-        and the buffer carving happen inside the library; Python allocates two arenas and wraps
-        views.  Philox draws, no two-children optics, bundle resident in HBM."""
+    # ------------------------------------------------- device-driven trace
+    def _plan_block(self, scene, cur, bounce, max_bounces):
+        """How many bounces to enqueue from ``bounce`` on and the hit capacity of each, from what the previous
+        trace of this scene did (``self._hist``).  Without two-children optics a bounce cannot hit more rays
+        than entered it, so the capacity of the bounce before is a hard bound."""
+        n = cur.n
+        hist = self._hist
+        full = n <= FULL_CAP_RAYS
+        caps, n_in_est, bound = [], float(n), n
+        depth_known = bounce in hist
+        for j in range(min(max_bounces, L.TRACE_MAX_BOUNCES)):
+            h = hist.get(bounce + j)
+            if h is None or h[0] == 0:
+                if depth_known and j > 0:
+                    break                       # the last trace ended here; a surprise survivor starts a new block
+                if j >= BLIND_BOUNCES or (j > 0 and not full):
+                    break                       # unknown territory: worst-case buffers, so few bounces at a time
+                est_h = float(bound)            # nothing known: every ray may hit
+                surv = 1.
+            else:
+                est_h = n_in_est * h[1] / h[0]
+                surv = h[2] / float(h[1]) if h[1] else 0.
+            cap = bound if full else min(bound, int(1.3 * est_h) + 4096)
+            cap = _round_cap(max(cap, min(bound, self._cap_floor.get(bounce + j, 0))))
+            caps.append(cap)
+            n_in_est = est_h * surv
+            bound = cap
+            if depth_known and h is not None and h[2] == 0:
+                break                           # nothing survived this bounce last time
+        return caps
+
+    def _count_hits(self, scene, cur, use_bvh):
+        """Hit count of the bundle's first bounce alone (a nearest-hit pass that emits no records): sizes the
+        buffers of a large first trace exactly instead of for the worst case."""
         import torch
         lib = L.load()
         dev = self.device
         st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        n = cur.n
+        n_chunks = (n + L.HIT_CHUNK - 1) // L.HIT_CHUNK
+        chunk = torch.empty(2 * n_chunks, dtype=torch.int32, device=dev)
+        total = torch.zeros(1, dtype=torch.int64, device=dev)
+        L.check(lib.trc_trace_hits(scene.handle, n, L.dptr(cur.V), L.dptr(cur.D), L.dptr(cur.E), cur.V.stride(0),
+                                   1 if use_bvh else 0, None, None, 0, L.dptr(chunk), chunk.data_ptr() + 4 * n_chunks,
+                                   L.dptr(total), st))
+        return int(total.item())
+
+    def _trace_block(self, scene, cur, bounce, max_bounces, min_energy, use_bvh):
+        """Up to ``max_bounces`` iterations of the reference loop body through trc_trace: one foreign call
+        enqueues every kernel, one stream synchronisation, one read-back of all counts.  Returns a list of
+        (record dict or None, survivors, hits, rays in), one entry per bounce that ran on valid data; an
+        overflowing bounce (more hits than planned) ends the list early and raises its capacity floor, so the
+        caller's next block starts with it."""
+        import torch
+        lib = L.load()
+        dev = self.device
+        stream = torch.cuda.current_stream(dev)
+        st = C.c_void_p(stream.cuda_stream)
         n, S = cur.n, scene.num_surfaces
         want = scene.accountant_sources
         if 'wavelengths' in want and cur.W is None:
             raise ValueError("Spectral accountant needs a 'wavelengths' bundle property")
         cols = ((L.COL_NORMALS if 'normals' in want else 0) | (L.COL_E_IN if 'e_in' in want else 0) |
                 (L.COL_DIRS_IN if 'dirs_in' in want else 0) | (L.COL_ATTENUATED if 'attenuated' in want else 0))
-        has_w = 1 if cur.W is not None else 0
-        frac = self._hit_frac.get(bounce)
-        cap = n if frac is None or n <= (1 << 20) else min(n, int(1.3 * frac * n) + 65536)
-        h_seg = np.zeros(S + 1, dtype=np.int64) if scene.has_accountants else None
-        a, r = L.BounceArgs(), L.BounceResult()
+        if bounce not in self._hist and bounce not in self._cap_floor and n > FULL_CAP_RAYS and cur.slices is None:
+            self._cap_floor[bounce] = self._count_hits(scene, cur, use_bvh)
+            self._hist[bounce] = (n, self._cap_floor[bounce], self._cap_floor[bounce])
+        caps = self._plan_block(scene, cur, bounce, max_bounces)
+        nb = len(caps)
+        a, plan = L.TraceArgs(), L.TracePlan()
         a.n, a.ld = n, cur.V.stride(0)
         a.d_vertices, a.d_directions, a.d_energy = cur.V.data_ptr(), cur.D.data_ptr(), cur.E.data_ptr()
-        a.d_wavelengths = cur.W.data_ptr() if has_w else None
-        a.use_bvh, a.bounce, a.seed, a.min_energy = (1 if use_bvh else 0), bounce, self.seed, float(min_energy)
-        a.columns, a.time_trace = cols, (1 if self.kernel_events is not None else 0)
-        a.h_seg = h_seg.ctypes.data if h_seg is not None else None
+        a.d_wavelengths = cur.W.data_ptr() if cur.W is not None else None
+        a.d_ray_ids = cur.I.data_ptr() if cur.I is not None else None
+        a.ray_id_base = cur.id_base
+        a.use_bvh, a.first_bounce, a.n_bounces = (1 if use_bvh else 0), bounce, nb
+        timed = self.kernel_events is not None and bounce == 0 and cur.slices is None
+        a.flags = (L.TRACE_SEG if scene.has_accountants else 0) | (L.TRACE_TIME_WALK if timed else 0)
+        a.seed, a.min_energy, a.columns = self.seed, float(min_energy), cols
+        for j, c in enumerate(caps):
+            a.capacity[j] = c
+        L.check(lib.trc_trace_plan(scene.handle, C.byref(a), C.byref(plan)))
+        keep = torch.empty(int(plan.keep_bytes), dtype=torch.uint8, device=dev)
+        scratch = torch.empty(int(plan.scratch_bytes), dtype=torch.uint8, device=dev)
+        words = int(plan.counts_words)
+        if self._counts_host is None or self._counts_host.numel() < words:
+            self._counts_host = torch.empty(max(words, 64), dtype=torch.int64, pin_memory=True)
+        counts = self._counts_host
+        a.d_keep, a.keep_bytes = keep.data_ptr(), keep.numel()
+        a.d_scratch, a.scratch_bytes = scratch.data_ptr(), scratch.numel()
         a.d_absorbed_per_surface = self.absorbed_per_surface.data_ptr()
         a.d_hits_per_surface = self.hits_per_surface.data_ptr()
-        while True:
-            keep = torch.empty(int(lib.trc_bounce_keep_bytes(cap, cols, has_w, S)), dtype=torch.uint8, device=dev)
-            scratch = torch.empty(int(lib.trc_bounce_scratch_bytes(n, cap, S)), dtype=torch.uint8, device=dev)
-            a.capacity = cap
-            a.d_keep, a.keep_bytes = keep.data_ptr(), keep.numel()
-            a.d_scratch, a.scratch_bytes = scratch.data_ptr(), scratch.numel()
-            rc = lib.trc_bounce(scene.handle, C.byref(a), C.byref(r), st)
-            if a.time_trace and r.ev_start:
-                ev = (r.ev_start, r.ev_stop)
-
-                def elapsed(ev=ev):
-                    ms = C.c_float(0.)
-                    L.check(lib.trc_event_elapsed_ms(ev[0], ev[1], C.byref(ms)))
-                    return ms.value
-                if rc == 0:
-                    self.kernel_events.append((bounce, n, int(r.hits), elapsed))
-                else:
-                    elapsed()              # releases the events of the attempt that overflowed
-            if rc == -4 and r.hits > cap:      # TRC_ERR_CAPACITY: more hits than the arenas hold
-                cap = int(r.hits)
-                continue
-            L.check(rc)
-            break
-        H, n_cull = int(r.hits), int(r.culled)
-        self._hit_frac[bounce] = H / float(n) if n else 0.
-        if H == 0:
-            return None, 0, 0
+        a.h_counts = counts.data_ptr()
+        if cur.slices is not None:
+            # the bundle is still arriving: run the first nearest-hit pass slice by slice, as each copy lands
+            a.flags |= L.TRACE_WALK_DONE
+            L.check(lib.trc_trace_init(scene.handle, C.byref(a), st))
+            sp = scratch.data_ptr()
+            ld = cur.V.stride(0)
+            for lo, hi, ev in cur.slices:
+                stream.wait_event(ev)
+                c0 = lo // L.HIT_CHUNK
+                L.check(lib.trc_trace_hits_slice(
+                    scene.handle, hi - lo, cur.V.data_ptr() + 8 * lo, cur.D.data_ptr() + 8 * lo,
+                    cur.E.data_ptr() + 8 * lo, ld, 1 if use_bvh else 0, None, sp + plan.off_records,
+                    sp + plan.off_keys, caps[0], sp + plan.off_chunk_off + 4 * c0, sp + plan.off_chunk_cnt + 4 * c0,
+                    sp + plan.off_total, lo, st))
+            cur.slices = cur.keep = None       # resident from here on
+        L.check(lib.trc_trace(scene.handle, C.byref(a), st))
+        stream.synchronize()                    # the only synchronisation of the block
+        per = 4 + (S + 1 if scene.has_accountants else 0)
+        host = counts[:nb * per].numpy()
         f64, i64 = torch.float64, torch.int64
+        out = []
+        for j in range(nb):
+            n_in, H, n_surv, reorder = (int(x) for x in host[per * j:per * j + 4])
+            if timed and j == 0:
+                ms = C.c_float(0.)
+                L.check(lib.trc_trace_walk_ms(scene.handle, C.byref(ms)))
+                self.kernel_events.append((0, n_in, H, lambda v=ms.value: v))
+            if H > caps[j]:
+                # more hits than planned: nothing of this bounce is valid; the next block starts here, larger
+                self._cap_floor[bounce + j] = H
+                self._hist[bounce + j] = (n_in, H, H)
+                self.stats_overflows = getattr(self, 'stats_overflows', 0) + 1
+                break
+            self._hist[bounce + j] = (n_in, H, n_surv)
+            self._hit_frac[bounce + j] = H / float(n_in) if n_in else 0.
+            if H == 0:
+                out.append((None, 0, 0, n_in))
+                break
+            lay = plan.bounce[j]
+            ld = int(lay.ld)
 
-        def view(off, dtype, rows):
-            if off < 0:
-                return None
-            nbytes = 8 * H * (rows or 1)
-            t = keep[off:off + nbytes].view(dtype)
-            return t.view(rows, H) if rows else t
-        oV, oD = view(r.off_vertices, f64, 3), view(r.off_directions, f64, 3)
-        oE, oP, oW = view(r.off_energy, f64, 0), view(r.off_parents, i64, 0), view(r.off_wavelengths, f64, 0)
-        if scene.has_accountants:
-            self._account(scene, h_seg, dict(
-                hits=oV, absorbed=view(r.off_absorbed, f64, 0), e_out=oE, normals=view(r.off_normals, f64, 3),
-                e_in=view(r.off_e_in, f64, 0), dirs_in=view(r.off_dirs_in, f64, 3), wavelengths=oW,
-                attenuated=view(r.off_attenuated, f64, 0)), copy=not self._keep_tree)
-        rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
-        if r.off_sorted_vertices >= 0:
-            rec = dict(V=view(r.off_sorted_vertices, f64, 3), D=view(r.off_sorted_directions, f64, 3),
-                       E=view(r.off_sorted_energy, f64, 0), P=view(r.off_sorted_parents, i64, 0),
-                       W=view(r.off_sorted_wavelengths, f64, 0))
-        rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW)
-        return rec, H - n_cull, H
+            def view(off, dtype, rows, lay_ld=ld, h=H):
+                if off < 0:
+                    return None
+                t = keep[off:off + 8 * lay_ld * (rows or 1)].view(dtype)
+                return t.view(rows, lay_ld)[:, :h] if rows else t[:h]
+            first = dict(V=view(lay.off_vertices, f64, 3), D=view(lay.off_directions, f64, 3),
+                         E=view(lay.off_energy, f64, 0), P=view(lay.off_parents, i64, 0),
+                         W=view(lay.off_wavelengths, f64, 0), I=view(lay.off_ray_ids, i64, 0))
+            pre = first
+            if reorder:        # survivors-first copy and slot-order copy differ
+                pre = dict(V=view(lay.off_alt_vertices, f64, 3), D=view(lay.off_alt_directions, f64, 3),
+                           E=view(lay.off_alt_energy, f64, 0), P=view(lay.off_alt_parents, i64, 0),
+                           W=view(lay.off_alt_wavelengths, f64, 0))
+            if scene.has_accountants:
+                seg = host[per * j + 4:per * (j + 1)]
+                self._account(scene, seg, dict(
+                    hits=pre['V'], absorbed=view(lay.off_absorbed, f64, 0), e_out=pre['E'],
+                    normals=view(lay.off_normals, f64, 3), e_in=view(lay.off_e_in, f64, 0),
+                    dirs_in=view(lay.off_dirs_in, f64, 3), wavelengths=pre['W'],
+                    attenuated=view(lay.off_attenuated, f64, 0)), copy=not self._keep_tree)
+            rec = dict(first)
+            rec['pre_cull'] = dict(V=pre['V'], D=pre['D'], E=pre['E'], P=pre['P'], W=pre['W'])
+            out.append((rec, n_surv, H, n_in))
+            if n_surv == 0:
+                break
+        return out
 
     @staticmethod
     def _account(scene, seg, src, child_off=None, copy=True):
@@ -594,6 +697,11 @@ class TracerEngine(object):
         self.tree = RayTree()
         if tree is True:
             self.tree.append(bundle)
+        with torch.cuda.device(self.device):      # scene tables, BVH and every launch on the engine's device
+            return self._ray_tracer(bundle, reps, min_energy, tree, accel, Kd_Tree)
+
+    def _ray_tracer(self, bundle, reps, min_energy, tree, accel, Kd_Tree):
+        import torch
         scene = self.compile()
         self.Kd_Tree = Kd_Tree if Kd_Tree is not None else (scene if accel else None)
         if self.device_accel == 'bvh' or accel:
@@ -605,24 +713,34 @@ class TracerEngine(object):
         if scene.needs_wavelengths and not bundle.has_property('wavelengths'):
             raise ValueError("scene has spectral optics but the bundle carries no 'wavelengths'")
 
-        with torch.cuda.device(self.device):
-            cur = self._to_device(bundle)
-            if scene.has_refractive and cur.R is None:
-                raise ValueError("scene has refractive optics but the bundle carries no 'ref_index'")
-            source_E = cur.E
-            self.absorbed_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.float64, device=self.device)
-            self.hits_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.int64, device=self.device)
-            ray_bounces = 0
-            per_bounce = []
-            last_rec = None
-            for i in range(reps):
-                ray_bounces += cur.n
+        cur = self._to_device(bundle)
+        if scene.has_refractive and cur.R is None:
+            raise ValueError("scene has refractive optics but the bundle carries no 'ref_index'")
+        source_E = cur.E
+        self.absorbed_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.float64, device=self.device)
+        self.hits_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.int64, device=self.device)
+        # device-driven (trc_trace) unless draws are injected or some optics emits two children per hit
+        device_driven = self.fused_bounce and self.rng == 'philox' and not scene.has_split and cur.R is None
+        ray_bounces = 0
+        per_bounce = []
+        last_rec = None
+        i = 0
+        depleted = False
+        while i < reps and not depleted:
+            if device_driven:
+                results = self._trace_block(scene, cur, i, reps - i, min_energy, use_bvh)
+            else:
                 rec, n_surv, H = self._bounce(scene, cur, i, min_energy, use_bvh)
-                per_bounce.append((cur.n, H, n_surv))
+                results = [(rec, n_surv, H, cur.n)]
+            for rec, n_surv, H, n_in in results:
+                i += 1
+                ray_bounces += n_in
+                per_bounce.append((n_in, H, n_surv))
                 if rec is None:
                     last_rec = None
                     cur = _DevBundle(cur.V[:, :0], cur.D[:, :0], cur.E[:0], None if cur.W is None else cur.W[:0])
                     logging.log(self.loglevel, 'Ray bundle depleted')
+                    depleted = True
                     break
                 last_rec = rec
                 if tree:
@@ -631,18 +749,20 @@ class TracerEngine(object):
                     self.tree.append(self._as_bundle(full))
                 W = rec['W'][:n_surv] if rec['W'] is not None else None
                 R = rec['R'][:n_surv] if rec.get('R') is not None else None
-                cur = _DevBundle(rec['V'][:, :n_surv], rec['D'][:, :n_surv], rec['E'][:n_surv], W, R=R)
+                I = rec['I'][:n_surv] if rec.get('I') is not None else None
+                cur = _DevBundle(rec['V'][:, :n_surv], rec['D'][:, :n_surv], rec['E'][:n_surv], W, R=R, I=I)
                 if cur.n == 0:
                     logging.log(self.loglevel, 'Ray bundle depleted')
+                    depleted = True
                     break
-            if not tree:
-                # only the last record, in pre-cull order (tracer_engine.py:288-291)
-                self.tree.append(self._as_bundle(last_rec['pre_cull']) if last_rec is not None
-                                 else RayBundle.empty_bund())
-            self.stats = dict(ray_bounces=ray_bounces, per_bounce=per_bounce, surfaces=scene.num_surfaces,
-                              use_bvh=use_bvh)
-            if cur.n != 0:
-                logging.warning(f'{cur.n} rays left at the end of the simulation')
-                frac = float((cur.E.sum() / source_E.sum()).item()) * 100.
-                logging.warning(f'Remaining energy in last bundle: {frac}%')
-            return self._to_host(cur.V), self._to_host(cur.D)
+        if not tree:
+            # only the last record, in pre-cull order (tracer_engine.py:288-291)
+            self.tree.append(self._as_bundle(last_rec['pre_cull']) if last_rec is not None
+                             else RayBundle.empty_bund())
+        self.stats = dict(ray_bounces=ray_bounces, per_bounce=per_bounce, surfaces=scene.num_surfaces,
+                          use_bvh=use_bvh)
+        if cur.n != 0:
+            logging.warning(f'{cur.n} rays left at the end of the simulation')
+            frac = float((cur.E.sum() / source_E.sum()).item()) * 100.
+            logging.warning(f'Remaining energy in last bundle: {frac}%')
+        return self._to_host(cur.V), self._to_host(cur.D)
