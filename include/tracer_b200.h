@@ -367,10 +367,11 @@ int trc_optics(const TrcScene *scene, const TrcOpticsArgs *args, void *stream);
  * Memory: two caller-owned device arenas sized by trc_trace_plan.  d_scratch is reused by every bounce and may
  * be freed after the synchronisation; d_keep holds the outputs of bounce j at plan.bounce[j] (byte offsets, -1 =
  * absent): rows of `ld` = capacity[j] elements of which the first `hits` are valid.
- *   children, survivors first and weak rays at the back (tracer_engine.py:242-245, 268-274): off_vertices (3,ld),
- *     off_directions (3,ld), off_energy, off_parents (int64), off_ray_ids (int64), off_wavelengths;
- *   off_alt_*: the same children in slot order (surface-major, parent-minor) -- only valid when the bounce's
- *     `reorder` word is 1 (some but not all children weak); otherwise the slot order IS the first copy;
+ *   children in slot order (surface-major, parent-minor): off_vertices (3,ld), off_directions (3,ld), off_energy,
+ *     off_parents (int64), off_ray_ids (int64), off_wavelengths;
+ *   off_alt_*: the same children with survivors first and weak rays at the back (tracer_engine.py:242-245,
+ *     268-274) -- only written when the bounce's `reorder` word is 1 (some but not all children weak); otherwise
+ *     the slot order already IS that order.  The next bounce reads whichever applies (decided on the device);
  *   accountant columns in slot order: off_absorbed, off_normals, off_e_in, off_dirs_in, off_attenuated;
  *   off_seg: int64 (n_surfaces + 1), surface s owns slots [seg[s], seg[s+1]).
  * h_counts (page-locked host memory, plan.counts_words int64): per bounce [rays in, hits, survivors, reorder]
@@ -385,6 +386,7 @@ int trc_optics(const TrcScene *scene, const TrcOpticsArgs *args, void *stream);
                                    (trc_trace_hits_slice on a bundle still arriving from the host) into the scratch
                                    buffers named by the plan */
 #define TRC_TRACE_SEG       4   /* copy seg of every bounce to h_counts (accountants need it on the host) */
+#define TRC_TRACE_ZERO_TALLIES 8 /* zero d_absorbed_per_surface / d_hits_per_surface first (trc_trace_init's kernel) */
 typedef struct TrcTraceArgs {
     int64_t n;                        /* rays entering the first bounce */
     const double *d_vertices;         /* (3,n) rows of stride ld */

@@ -48,6 +48,11 @@ for e in ev:
     a[0] += 1; a[1] += e['dur']
 for k, (c, d) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:25]:
     print('  %-70s %4d  %8.1f us/step' % (k, c // STEPS, d / STEPS))
+if os.environ.get('TRC_PROBE_LIST'):
+    per = len(ev) // STEPS
+    print('launches of the last step (us):')
+    for e in ev[-per:]:
+        print('  %8.1f  %s' % (e['dur'], e['name'][:60]))
 # largest idle gaps of one step
 gaps = []
 end = ev[0]['ts'] + ev[0]['dur']

@@ -73,7 +73,7 @@ COL_NORMALS, COL_E_IN, COL_DIRS_IN, COL_ATTENUATED = 1, 2, 4, 8
 
 
 TRACE_MAX_BOUNCES = 8
-TRACE_TIME_WALK, TRACE_WALK_DONE, TRACE_SEG = 1, 2, 4
+TRACE_TIME_WALK, TRACE_WALK_DONE, TRACE_SEG, TRACE_ZERO_TALLIES = 1, 2, 4, 8
 
 
 class TraceArgs(C.Structure):

@@ -39,13 +39,9 @@ struct OpticsParams {
     int64_t *o_ids;
     // device-driven trace (trace.cu): hit count and bookkeeping live in device memory
     TrcBounceCtl *ctl;            // nullable; when set h = min(ctl->hits, capacity)
-    TrcBounceCtl *ctl_next;       // nullable: receives n_in = survivors
     int64_t capacity;
     uint32_t *cta_surv;           // survivors per CTA -> exclusive scan (last block), read by the partition kernel
-    double *cta_sum;              // absorbed energy per CTA (CTAs whose slots lie on one surface)
-    int32_t *cta_key;             //   its surface, or -1 when the CTA used atomics
     double *absorbed_per_surface;
-    int64_t *d_counts;            // [n_in, hits, survivors, reorder] of this bounce for the final read-back
 };
 
 // Philox draws in the units the reference's numpy calls produce
@@ -156,6 +152,7 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
     if (p.ctl) {                       // device-driven: the hit count never visited the host
         long long hraw = (long long)p.ctl->hits;
         p.h = hraw <= p.capacity ? hraw : 0;       // an overflowed bounce does nothing: the host re-runs it
+        p.wavelengths = p.ctl->in.W; p.ids_in = (const int64_t *)p.ctl->in.ids; p.id_base = p.ctl->in.id_base;
     }
     bool live = q < p.h;
     bool culled = false;
@@ -223,11 +220,13 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
         p.o_energy[c] = e_first;
         p.o_parents[c] = r;
         if (p.o_ref_index) p.o_ref_index[c] = p.ref_index[r];
+#ifndef TRC_OPT_NO_IDS
         if (p.o_ids) {
             int64_t id = p.ids_in ? p.ids_in[r] : p.id_base + r;
             p.o_ids[c] = id;
             if (c2 >= 0) p.o_ids[c2] = id;
         }
+#endif
         a_val = e_in - o.energy; a_key = sidx;
         if (p.absorbed) p.absorbed[q] = e_in - o.energy;
         if (p.normals) { p.normals[q] = n.x; p.normals[p.ld_out + q] = n.y; p.normals[2 * p.ld_out + q] = n.z; }
@@ -244,100 +243,119 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
         if ((threadIdx.x & 31) == 0 && m) atomicAdd(p.n_cull, (unsigned long long)__popc(m));
     }
     if (!p.ctl) return;
-    // ---- device-driven trace: per-CTA survivor counts and per-surface absorbed sums, then the last
-    // block to finish closes the bounce (survivor total, reorder decision, next bounce's ray count).
+    // ---- device-driven trace: survivors per CTA and per-surface absorbed sums with ONE block barrier;
+    // bounce_close_kernel (next launch) turns the per-CTA counts into the bounce's totals.
     __shared__ unsigned s_cnt[8];
     __shared__ double s_sum[8];
-    __shared__ int s_first, s_last;
-    __shared__ bool s_is_last;
+    __shared__ int s_key[8];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t blk0 = (int64_t)blockIdx.x * blockDim.x;
-    const bool blk_live = blk0 < p.h;
-    if (blk_live) {
-        unsigned ms = __ballot_sync(0xffffffffu, live && !culled);
-        if (threadIdx.x == 0) s_first = a_key;
-        if (q == p.h - 1 || (live && threadIdx.x == blockDim.x - 1)) s_last = a_key;
-        // warp-level segmented sum of a_val by key (keys are non-decreasing with the lane: slot order)
+    if (blk0 < p.h) {
+        const unsigned ms = __ballot_sync(0xffffffffu, live && !culled);
+        // warp-level segmented sum of a_val by surface (keys are non-decreasing with the lane: slot order;
+        // dead lanes at the end of the last block carry key -1)
         double acc = a_val;
-        int key = a_key;
+        const int key = a_key;
         for (int o = 1; o < 32; o <<= 1) {
             double other = __shfl_down_sync(0xffffffffu, acc, o);
             int okey = __shfl_down_sync(0xffffffffu, key, o);
             if (lane + o < 32 && okey == key) acc += other;
         }
-        int prev = __shfl_up_sync(0xffffffffu, key, 1);
+        const int prev = __shfl_up_sync(0xffffffffu, key, 1);
         const bool head = key >= 0 && (lane == 0 || prev != key);
-        if (lane == 0) { s_cnt[warp] = __popc(ms); s_sum[warp] = 0.0; }
-        __syncthreads();
-        const bool single = s_first == s_last;          // every slot of the CTA lies on one surface
+        const unsigned heads = __ballot_sync(0xffffffffu, head);
+        // a warp whose live slots lie on ONE surface hands its sum to thread 0; otherwise one atomic per segment
+        const bool one = __popc(heads) == 1;
         if (head) {
-            if (single) s_sum[warp] = acc;              // one head per warp
+            if (one) { s_sum[warp] = acc; s_key[warp] = key; }
             else atomicAdd(&p.absorbed_per_surface[key], acc);
+        }
+        if (lane == 0) {
+            s_cnt[warp] = __popc(ms);
+            if (!one) s_key[warp] = -1;
         }
         __syncthreads();
         if (threadIdx.x == 0) {
             unsigned c = 0;
+            int k = -1;
             double t = 0.0;
-            for (int w = 0; w < 8; ++w) { c += s_cnt[w]; t += s_sum[w]; }      // fixed order: deterministic
-            p.cta_surv[blockIdx.x] = c;
-            p.cta_sum[blockIdx.x] = t;
-            p.cta_key[blockIdx.x] = single ? s_first : -1;
-        }
-    }
-    __threadfence();
-    if (threadIdx.x == 0) s_is_last = atomicAdd(&p.ctl->ticket_optics, 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (!s_is_last) return;
-    __threadfence();
-    const int64_t nb = (p.h + 255) / 256;
-    // (1) exclusive scan of the per-CTA survivor counts, in place
-    __shared__ unsigned s_scan[256];
-    __shared__ unsigned s_carry;
-    if (threadIdx.x == 0) s_carry = 0;
-    __syncthreads();
-    for (int64_t start = 0; start < nb; start += 1024) {
-        int64_t i0 = start + 4 * (int64_t)threadIdx.x;
-        unsigned v[4], t = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { v[k] = i0 + k < nb ? __ldcg(&p.cta_surv[i0 + k]) : 0u; t += v[k]; }
-        unsigned incl = t;
-        for (int o = 1; o < 32; o <<= 1) { unsigned x = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += x; }
-        if (lane == 31) s_scan[warp] = incl;
-        __syncthreads();
-        unsigned wbase = 0;
-        for (int w = 0; w < warp; ++w) wbase += s_scan[w];
-        unsigned run = s_carry + wbase + incl - t;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { if (i0 + k < nb) p.cta_surv[i0 + k] = run; run += v[k]; }
-        __syncthreads();
-        if (threadIdx.x == 255) s_carry = run;
-        __syncthreads();
-    }
-    // (2) per-surface absorbed energy from the single-surface CTAs: each thread folds a contiguous run of CTAs
-    {
-        int64_t per = (nb + 255) / 256;
-        int64_t b0 = per * threadIdx.x, b1 = b0 + per < nb ? b0 + per : nb;
-        int key = -1;
-        double acc = 0.0;
-        for (int64_t b = b0; b < b1; ++b) {
-            int kk = __ldcg(&p.cta_key[b]);
-            if (kk != key) {
-                if (key >= 0) atomicAdd(&p.absorbed_per_surface[key], acc);
-                key = kk; acc = 0.0;
+            for (int w = 0; w < 8; ++w) {                 // runs of warps on the same surface: one atomic per run
+                c += s_cnt[w];
+                const int kw = s_key[w];
+                if (kw != k) {
+                    if (k >= 0) atomicAdd(&p.absorbed_per_surface[k], t);
+                    k = kw; t = 0.0;
+                }
+                if (kw >= 0) t += s_sum[w];
             }
-            if (kk >= 0) acc += __ldcg(&p.cta_sum[b]);
+            if (k >= 0) atomicAdd(&p.absorbed_per_surface[k], t);
+            p.cta_surv[blockIdx.x] = c;
         }
-        if (key >= 0) atomicAdd(&p.absorbed_per_surface[key], acc);
+    }
+}
+
+// Closes a bounce of the device-driven trace (one block, launched right after the optics kernel): survivor
+// total from the per-CTA counts, the reorder decision, the exclusive scan the partition kernel needs when it
+// will run, and the next bounce's ray count and bundle.  A separate launch rather than a "last block" ticket
+// inside the optics kernel: a ticket costs every CTA an atomic round trip before it can retire.
+struct CloseParams {
+    TrcBounceCtl *ctl, *ctl_next;
+    TrcBundleDesc children, children_sorted;
+    int64_t capacity;
+    uint32_t *cta_surv;
+    int64_t *d_counts;
+};
+__global__ void __launch_bounds__(1024)
+bounce_close_kernel(CloseParams p) {
+    __shared__ unsigned long long s_part[32];
+    __shared__ unsigned s_scan[32];
+    __shared__ unsigned s_carry;
+    pdl_wait();
+    pdl_trigger();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long hraw = (long long)p.ctl->hits;
+    const unsigned overflow = hraw > p.capacity ? 1u : 0u;
+    const long long h = overflow ? 0 : hraw;
+    const int64_t nb = (h + 255) / 256;
+    unsigned long long t = 0;
+    for (int64_t i = threadIdx.x; i < nb; i += 1024) t += p.cta_surv[i];
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (lane == 0) s_part[warp] = t;
+    __syncthreads();
+    unsigned long long tot = 0;
+    for (int w = 0; w < 32; ++w) tot += s_part[w];
+    const long long n_surv = (long long)tot;
+    const unsigned reorder = (n_surv > 0 && n_surv < h) ? 1u : 0u;
+    if (reorder) {
+        if (threadIdx.x == 0) s_carry = 0;
+        __syncthreads();
+        for (int64_t start = 0; start < nb; start += 4096) {
+            const int64_t i0 = start + 4 * (int64_t)threadIdx.x;
+            unsigned v[4], s4 = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { v[k] = i0 + k < nb ? p.cta_surv[i0 + k] : 0u; s4 += v[k]; }
+            unsigned incl = s4;
+            for (int o = 1; o < 32; o <<= 1) { unsigned x = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += x; }
+            if (lane == 31) s_scan[warp] = incl;
+            __syncthreads();
+            unsigned wbase = 0;
+            for (int w = 0; w < warp; ++w) wbase += s_scan[w];
+            unsigned run = s_carry + wbase + incl - s4;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { if (i0 + k < nb) p.cta_surv[i0 + k] = run; run += v[k]; }
+            __syncthreads();
+            if (threadIdx.x == 1023) s_carry = run;
+            __syncthreads();
+        }
     }
     if (threadIdx.x == 0) {
-        const long long hraw = (long long)p.ctl->hits;
-        const long long n_surv = (long long)s_carry;
-        const unsigned overflow = hraw > p.capacity ? 1u : 0u;
-        const unsigned reorder = (n_surv > 0 && n_surv < p.h) ? 1u : 0u;
         p.ctl->n_surv = n_surv;
         p.ctl->reorder = reorder;
         p.ctl->overflow = overflow;
-        if (p.ctl_next) p.ctl_next->n_in = overflow ? 0 : n_surv;     // an overflowed bounce feeds nothing forward
+        if (p.ctl_next) {
+            p.ctl_next->n_in = overflow ? 0 : n_surv;     // an overflowed bounce feeds nothing forward
+            p.ctl_next->in = reorder ? p.children_sorted : p.children;
+        }
         p.d_counts[0] = p.ctl->n_in; p.d_counts[1] = hraw; p.d_counts[2] = n_surv; p.d_counts[3] = reorder;
     }
 }
@@ -516,12 +534,11 @@ int trc_optics_dyn(const TrcScene *sc, const TrcOpticsArgs *a, const TrcOpticsDy
     p.ref_index = a->d_ref_index; p.o_ref_index = a->d_out_ref_index;
     p.n_void = reinterpret_cast<unsigned long long *>(a->d_n_void);
     p.ids_in = a->d_ray_ids; p.id_base = a->ray_id_base; p.o_ids = a->d_out_ray_ids;
-    p.ctl = nullptr; p.ctl_next = nullptr; p.capacity = a->h; p.cta_surv = nullptr; p.cta_sum = nullptr;
-    p.cta_key = nullptr; p.absorbed_per_surface = nullptr; p.d_counts = nullptr;
+    p.ctl = nullptr; p.capacity = a->h; p.cta_surv = nullptr; p.absorbed_per_surface = nullptr;
     if (dyn) {
         if (sc->has_split) return fail(TRC_ERR_UNSUPPORTED_KIND, "trc_optics: device-driven trace with two-children optics%s");
-        p.ctl = dyn->ctl; p.ctl_next = dyn->ctl_next; p.cta_surv = dyn->cta_surv; p.cta_sum = dyn->cta_sum;
-        p.cta_key = dyn->cta_key; p.absorbed_per_surface = dyn->absorbed_per_surface; p.d_counts = dyn->d_counts;
+        p.ctl = dyn->ctl; p.cta_surv = dyn->cta_surv;
+        p.absorbed_per_surface = dyn->absorbed_per_surface;
     }
     if ((p.ref_index == nullptr) != (p.o_ref_index == nullptr))
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: d_ref_index and d_out_ref_index go together%s");
@@ -530,10 +547,16 @@ int trc_optics_dyn(const TrcScene *sc, const TrcOpticsArgs *a, const TrcOpticsDy
                     "trc_optics: a scene with TRC_O_REFRACTIVE surfaces needs d_ref_index and d_child_off%s");
     if (p.child_off && !p.seg) return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: d_child_off needs d_seg%s");
     int64_t blocks = (a->h + 255) / 256;
-    if (dyn)
+    if (dyn) {
         TRC_CUDA(launch_pdl(optics_kernel<false>, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream,
                             (const TrcSurfaceRec *)sc->d_surfaces, (const double *)sc->d_tables, p));
-    else if (sc->has_refractive)
+        CloseParams c;
+        c.ctl = dyn->ctl; c.ctl_next = dyn->ctl_next; c.children = dyn->children;
+        c.children_sorted = dyn->children_sorted; c.capacity = a->h; c.cta_surv = dyn->cta_surv;
+        c.d_counts = dyn->d_counts;
+        TRC_CUDA(launch_pdl(bounce_close_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, c));
+        return check_launch("optics", 2);
+    } else if (sc->has_refractive)
         optics_kernel<true><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(sc->d_surfaces, sc->d_tables, p);
     else
         optics_kernel<false><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(sc->d_surfaces, sc->d_tables, p);

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include "../../include/tracer_b200.h"
 
 // thread-local last-error text, defined in tracer_b200.cu
@@ -43,18 +44,25 @@ __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.lau
 template <typename... KArgs, typename... Args>
 static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
                                      Args... args) {
+    static const bool no_pdl = getenv("TRC_NO_PDL") != nullptr;   // profiling: kernels then neither overlap nor wait
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    cfg.attrs = attr; cfg.numAttrs = no_pdl ? 0 : 1;
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 #endif
 
 // ---- device-side control block of the device-driven trace (trace.cu).  One per bounce; the counts
 // never visit the host between the first launch of a trace and its final read-back.
+struct TrcBundleDesc {               // where a bundle lives: SoA rows of stride ld (ray_bundle.py:6-63)
+    const double *V, *D, *E, *W;       // W (wavelengths) nullable
+    const long long *ids;              // source-ray ids, nullable: id = id_base + index
+    long long id_base;
+    long long ld;
+};
 struct TrcBounceCtl {
     long long n_in;                    // rays entering the bounce (bounce 0: host; later: survivors of the previous one)
     unsigned long long chunk_counter;  // dynamic work distribution of the tree walk
@@ -62,11 +70,13 @@ struct TrcBounceCtl {
     long long n_surv;                  // children with energy > min_energy (optics finalize)
     unsigned int ticket_order;         // "last block" tickets
     unsigned int ticket_optics;
-    unsigned int reorder;              // 1: some but not all children are weak -> survivors-first reorder runs
+    unsigned int reorder;              // 1: some but not all children are weak -> the survivors-first copy is made
     unsigned int overflow;             // hits > capacity: results of this and later bounces are void
-    long long pad_[2];
-};                                     // 64 bytes
-static_assert(sizeof(TrcBounceCtl) == 64, "TrcBounceCtl layout");
+    TrcBundleDesc in;                  // the bundle entering the bounce: the children of the bounce before, in slot
+                                       // order or (reorder) the survivors-first copy -- chosen on the device
+    long long pad_[3];
+};                                     // 128 bytes
+static_assert(sizeof(TrcBounceCtl) == 128, "TrcBounceCtl layout");
 
 // The tree as the walk reads it: one 32-byte record per INNER node holding the
 // boxes of its two children quantised to 16 bits on the grid of the root box
@@ -131,21 +141,14 @@ struct TrcScene {
 // Optics launch of the device-driven trace (bounce.cu).
 struct TrcOpticsDyn {
     TrcBounceCtl *ctl, *ctl_next;
+    TrcBundleDesc children, children_sorted;   // where this bounce's children are written: slot order / survivors first
     uint32_t *cta_surv;
-    double *cta_sum;
-    int32_t *cta_key;
     double *absorbed_per_surface;
     int64_t *d_counts;
 };
 int trc_optics_dyn(const TrcScene *sc, const TrcOpticsArgs *a, const TrcOpticsDyn *dyn, void *stream);
 
-// Nearest-hit launch of the device-driven trace (nearest.cu): the ray count, the work counter and the hit
-// total live in device memory; n_cap sizes the grid.
-struct TrcNearestDyn {
-    const long long *n_ptr;
-    unsigned long long *chunk_counter;
-    unsigned long long *total;
-};
-int trc_nearest_dyn(const TrcScene *sc, int64_t n_cap, const double *d_vert, const double *d_dir, const double *d_energy,
-                    int64_t ld, int32_t use_bvh, TrcHitRecord *d_records, int32_t *d_keys, int64_t capacity,
-                    uint32_t *d_chunk_off, uint32_t *d_chunk_cnt, const TrcNearestDyn *dyn, cudaStream_t st);
+// Nearest-hit launch of the device-driven trace (nearest.cu): the bundle (pointers and ray count), the work
+// counter and the hit total live in the control block; n_cap sizes the grid.
+int trc_nearest_dyn(const TrcScene *sc, int64_t n_cap, TrcBounceCtl *ctl, int32_t use_bvh, TrcHitRecord *d_records,
+                    int32_t *d_keys, int64_t capacity, uint32_t *d_chunk_off, uint32_t *d_chunk_cnt, cudaStream_t st);

@@ -73,7 +73,7 @@ static_assert(TRC_HIT_CHUNK == 256, "one brute-force block = one chunk");
 
 __global__ void __launch_bounds__(256)
 nearest_hit_brute_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict__ pool, int n_surf, int64_t n,
-                         const long long *__restrict__ n_ptr,
+                         const TrcBounceCtl *__restrict__ ctl,
                          const double *__restrict__ vert, const double *__restrict__ dir, int64_t ld,
                          HitSink sink) {
     __shared__ TrcSurfaceRec stage[TRC_STAGE_SURFS];
@@ -81,7 +81,9 @@ nearest_hit_brute_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *
     __shared__ unsigned long long block_base;
     pdl_wait();
     pdl_trigger();
-    if (n_ptr) n = *n_ptr;             // device-driven trace: the ray count lives in device memory
+    if (ctl) {                         // device-driven trace: the bundle is described in device memory
+        n = ctl->n_in; vert = ctl->in.V; dir = ctl->in.D; ld = ctl->in.ld; sink.energy = ctl->in.E;
+    }
     if ((int64_t)blockIdx.x * blockDim.x >= n) return;      // grid sized for the capacity of the input bundle
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     bool live = i < n;
@@ -173,6 +175,8 @@ struct WalkWarpShared {
     int q2n;                                  // its fill (warp-uniform, kept here to spare a register)
     long long fifo[4];                        // chunk ids in consumption order (written by the prefetcher)
     double ring[kRing][6][32];                // cp.async landing zone: vertex + direction rows of 32 rays
+    const double *vert, *dir, *energy;        // the bundle (kernel parameters, or the control block of a device-driven
+    long long ld;                             // trace): read from here so that they cost no registers in the walk loop
 };
 
 // Dynamic shared memory of a CTA: the per-warp blocks, then the cached top of the tree,
@@ -201,7 +205,7 @@ struct WalkParams {
     int n_cached;                             // pairs cached in shared memory
     float root_lo[3], root_hi[3], qstep[3], extent[3];
     int64_t n;
-    const long long *n_ptr;                   // non-null: the ray count is read from device memory (device-driven trace)
+    const TrcBounceCtl *ctl;                  // non-null: bundle and ray count are read from device memory (device-driven trace)
     const double *vert, *dir;
     int64_t ld;
     HitSink sink;
@@ -321,8 +325,10 @@ __device__ __forceinline__ int flush_queue_body(WalkWarpShared &sh, const unsign
         int surf = INT_MAX;
         if (has) {
             int64_t ray = chunk_base + slot;
-            V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
-            V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
+            const double *vp = sh.vert + ray, *dp = sh.dir + ray;
+            const long long ld = sh.ld;
+            V3 v = mk(vp[0], vp[ld], vp[2 * ld]);
+            V3 d = mk(dp[0], dp[ld], dp[2 * ld]);
             for (int k = 0; k < cnt; ++k) {
                 int s = cnt == 1 ? first : __ldg(&p.cand[first + k]);     // single-surface entries hold the index
                 const TrcSurfaceRec *sr = &p.surfs[s];
@@ -408,8 +414,10 @@ __device__ __forceinline__ int prefilter_queue(WalkWarpShared &sh, const WalkPar
         bool pass = has;
         if (has && ((e >> 22) & 3u) == 0u) {                     // single-surface entry holds the surface index
             int64_t ray = chunk_base + (int)(e >> 24);
-            V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
-            V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
+            const double *vp = sh.vert + ray, *dp = sh.dir + ray;
+            const long long ld = sh.ld;
+            V3 v = mk(vp[0], vp[ld], vp[2 * ld]);
+            V3 d = mk(dp[0], dp[ld], dp[2 * ld]);
             pass = tri_prefilter(p.tri32 + 3 * (size_t)(e & kCandMask), v, d);
         }
         if (q2n >= 32)                                           // leaves < 32: room for 32 more
@@ -468,10 +476,12 @@ __device__ __forceinline__ void emit_chunk_hits(WalkWarpShared &sh, const WalkPa
         if ((int64_t)pos >= p.sink.capacity) break;       // overflow: the host re-runs with the exact size
         int i = slots[e];
         int64_t ray = chunk_base + i;
-        V3 v = mk(p.vert[ray], p.vert[p.ld + ray], p.vert[2 * p.ld + ray]);
-        V3 d = mk(p.dir[ray], p.dir[p.ld + ray], p.dir[2 * p.ld + ray]);
+        const double *vp = sh.vert + ray, *dp = sh.dir + ray;
+        const long long ld = sh.ld;
+        V3 v = mk(vp[0], vp[ld], vp[2 * ld]);
+        V3 d = mk(dp[0], dp[ld], dp[2 * ld]);
         const int surf = sh.best_s[i];
-        store_record(p.sink.records + pos, v, d, p.sink.energy[ray], p.sink.ray_base + (int)ray, surf);
+        store_record(p.sink.records + pos, v, d, sh.energy[ray], p.sink.ray_base + (int)ray, surf);
         if (p.sink.keys) p.sink.keys[pos] = surf;
     }
     __syncwarp();
@@ -505,7 +515,11 @@ nearest_hit_walk_kernel(WalkParams p) {
     }
     pdl_wait();
     pdl_trigger();
-    if (threadIdx.x == 0) S.n_rays = p.n_ptr ? *p.n_ptr : (long long)p.n;
+    if (threadIdx.x == 0) S.n_rays = p.ctl ? p.ctl->n_in : (long long)p.n;
+    if (lane == 0) {
+        if (p.ctl) { sh.vert = p.ctl->in.V; sh.dir = p.ctl->in.D; sh.energy = p.ctl->in.E; sh.ld = p.ctl->in.ld; }
+        else { sh.vert = p.vert; sh.dir = p.dir; sh.energy = p.sink.energy; sh.ld = p.ld; }
+    }
     __syncthreads();
     unsigned pair_a_smem = (unsigned)__cvta_generic_to_shared(walk_smem + sizeof(WalkShared));
     unsigned pair_b_smem = pair_a_smem + 16u * (unsigned)p.n_cached;             // pair_b follows pair_a
@@ -540,12 +554,14 @@ nearest_hit_walk_kernel(WalkParams p) {
             int64_t ray = pc * kChunk + poff + lane;
             if (poff + lane < pc_n) {
                 double *dst = &sh.ring[ring_w % kRing][0][lane];
-                cp_async8(dst, p.vert + ray);
-                cp_async8(dst + 32, p.vert + p.ld + ray);
-                cp_async8(dst + 64, p.vert + 2 * p.ld + ray);
-                cp_async8(dst + 96, p.dir + ray);
-                cp_async8(dst + 128, p.dir + p.ld + ray);
-                cp_async8(dst + 160, p.dir + 2 * p.ld + ray);
+                const double *vp = sh.vert + ray, *dp = sh.dir + ray;
+                const long long ld = sh.ld;
+                cp_async8(dst, vp);
+                cp_async8(dst + 32, vp + ld);
+                cp_async8(dst + 64, vp + 2 * ld);
+                cp_async8(dst + 96, dp);
+                cp_async8(dst + 128, dp + ld);
+                cp_async8(dst + 160, dp + 2 * ld);
             }
             poff += 32;
             if (poff >= pc_n) { pc = fetch_chunk(); poff = 0; }
@@ -724,19 +740,18 @@ nearest_hit_walk_kernel(WalkParams p) {
 // hit total live in the trace's control block (already zeroed) and the launch carries the PDL attribute.
 static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir, int64_t ld,
                           int32_t use_bvh, HitSink sink, cudaStream_t st, bool zero_total = true,
-                          const TrcNearestDyn *dyn = nullptr) {
+                          TrcBounceCtl *dyn = nullptr) {
     if (!dyn && sink.records && zero_total) TRC_CUDA(cudaMemsetAsync(sink.total, 0, sizeof(unsigned long long), st));
     if (n == 0) return TRC_OK;
     if (n >= 0x7fffffffLL) return fail(TRC_ERR_CAPACITY, "trc_nearest_hit: more than 2^31-1 rays, chunk the bundle%s");
-    const long long *n_ptr = dyn ? dyn->n_ptr : nullptr;
     if (!use_bvh) {
         int64_t blocks = (n + 255) / 256;
         if (dyn) {
             TRC_CUDA(launch_pdl(nearest_hit_brute_kernel, dim3((unsigned)blocks), dim3(256), 0, st, sc->d_surfaces,
-                                sc->d_tables, sc->n_surfaces, n, n_ptr, d_vert, d_dir, ld, sink));
+                                sc->d_tables, sc->n_surfaces, n, dyn, d_vert, d_dir, ld, sink));
         } else {
             nearest_hit_brute_kernel<<<(unsigned)blocks, 256, 0, st>>>(sc->d_surfaces, sc->d_tables, sc->n_surfaces, n,
-                                                                       n_ptr, d_vert, d_dir, ld, sink);
+                                                                       (const TrcBounceCtl *)nullptr, d_vert, d_dir, ld, sink);
         }
         return check_launch("nearest_hit_brute");
     }
@@ -778,8 +793,8 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
         p.root_lo[k] = sc->root_lo[k]; p.root_hi[k] = sc->root_hi[k];
         p.qstep[k] = sc->qstep[k]; p.extent[k] = sc->extent[k];
     }
-    p.n = n; p.n_ptr = n_ptr; p.vert = d_vert; p.dir = d_dir; p.ld = ld; p.sink = sink;
-    p.chunk_counter = dyn ? dyn->chunk_counter : sc->d_chunk_counter;
+    p.n = n; p.ctl = dyn; p.vert = d_vert; p.dir = d_dir; p.ld = ld; p.sink = sink;
+    p.chunk_counter = dyn ? &dyn->chunk_counter : sc->d_chunk_counter;
     int64_t n_chunks = (n + kChunk - 1) / kChunk;
     int64_t blocks = (n_chunks + kWalkWarps - 1) / kWalkWarps;
     int occ = sc->walk_occ[variant];
@@ -799,11 +814,10 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     return check_launch("nearest_hit_walk");
 }
 
-int trc_nearest_dyn(const TrcScene *sc, int64_t n_cap, const double *d_vert, const double *d_dir, const double *d_energy,
-                    int64_t ld, int32_t use_bvh, TrcHitRecord *d_records, int32_t *d_keys, int64_t capacity,
-                    uint32_t *d_chunk_off, uint32_t *d_chunk_cnt, const TrcNearestDyn *dyn, cudaStream_t st) {
-    HitSink sink = {nullptr, d_energy, d_records, capacity, d_chunk_off, d_chunk_cnt, dyn->total, 0, d_keys};
-    return launch_nearest(sc, n_cap, d_vert, d_dir, ld, use_bvh, sink, st, false, dyn);
+int trc_nearest_dyn(const TrcScene *sc, int64_t n_cap, TrcBounceCtl *ctl, int32_t use_bvh, TrcHitRecord *d_records,
+                    int32_t *d_keys, int64_t capacity, uint32_t *d_chunk_off, uint32_t *d_chunk_cnt, cudaStream_t st) {
+    HitSink sink = {nullptr, nullptr, d_records, capacity, d_chunk_off, d_chunk_cnt, &ctl->hits, 0, d_keys};
+    return launch_nearest(sc, n_cap, nullptr, nullptr, n_cap, use_bvh, sink, st, false, ctl);
 }
 
 extern "C" int trc_nearest_hit(const TrcScene *sc, int64_t n, const double *d_vert, const double *d_dir,

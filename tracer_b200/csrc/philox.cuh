@@ -42,16 +42,28 @@ __device__ __forceinline__ void uniform2(uint64_t seed, uint64_t index, uint32_t
     u1 = u53(r.z, r.w);
 }
 
-// Two independent standard normals (Box-Muller on (0,1] x [0,1)).
+// Two independent standard normals (Box-Muller on (0,1] x [0,1)).  These are the production draws (slope
+// errors, conical scattering): they have no parity constraint, only their distribution matters.  The bulk is
+// evaluated in float32 (relative error 1e-7 of a draw whose scale is a milliradian); the far tail, where
+// 1 - u0 would lose its resolution in float32, takes the float64 path so that it is not truncated.
 __device__ __forceinline__ void normal2(uint64_t seed, uint64_t index, uint32_t stream, uint32_t slot,
                                         double &n0, double &n1) {
     double u0, u1;
     uniform2(seed, index, stream, slot, u0, u1);
-    double r = sqrt(-2.0 * log(1.0 - u0));
-    double s, c;
-    sincospi(2.0 * u1, &s, &c);
-    n0 = r * c;
-    n1 = r * s;
+    const double q = 1.0 - u0;                 // in (0, 1]
+    if (q > 1e-3) {
+        float r = sqrtf(-2.0f * logf((float)q));
+        float s, c;
+        sincospif(2.0f * (float)u1, &s, &c);
+        n0 = (double)(r * c);
+        n1 = (double)(r * s);
+    } else {
+        double r = sqrt(-2.0 * log(q));
+        double s, c;
+        sincospi(2.0 * u1, &s, &c);
+        n0 = r * c;
+        n1 = r * s;
+    }
 }
 
 }  // namespace trc

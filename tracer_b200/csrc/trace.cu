@@ -7,14 +7,15 @@
 // Kernels of one bounce (each starts with griddepcontrol.wait and is launched with the programmatic
 // stream-serialisation attribute, so its prologue overlaps the tail of the one before):
 //   1. nearest_hit_walk / nearest_hit_brute (nearest.cu)  ray count read from the control block
-//   2. order_hist      per (warp tile, surface) hit counts from the 4-byte key array written next to
-//                      the hit records; the last block scans them -> slot offsets per surface (seg)
+//   2. order_hist      per (tile, surface) hit counts from the 4-byte key array written next to the hit records
+//      order_scan      one block: scans them over the tiles -> slot offsets per surface (seg), hit totals
 //   3. order_scatter   stable (surface-major, ray-minor) slot -> record index
 //      [scenes with more than 256 surfaces: passes 1.. of the LSD radix sort of sort.cu + segment offsets]
-//   4. optics          (bounce.cu) children in slot order, accountant columns, per-surface absorbed
-//                      sums; the last block closes the bounce (survivors, reorder flag, next ray count)
-//   5. partition, 6. swap   only act when some but not all children are weak: survivors first
-//                      (tracer_engine.py:242-245, 268-274); otherwise they exit at once
+//   4. optics          (bounce.cu) children in slot order, accountant columns, per-surface absorbed sums
+//      bounce_close    one block: survivors, reorder flag, the next bounce's ray count and bundle
+//   5. partition       only acts when some but not all children are weak: a survivors-first copy of the
+//                      children (tracer_engine.py:242-245, 268-274), which the next bounce then reads -- the
+//                      choice is recorded in the next control block, so no pointer passes through the host
 #include <new>
 
 #include "common.cuh"
@@ -28,15 +29,15 @@ inline int64_t up256(int64_t x) { return (x + 255) & ~(int64_t)255; }
 
 constexpr int kOrderWarps = 8;
 constexpr int kMaxBins = 256;
-constexpr int kTargetWarpTiles = 592;      // 4 warp tiles per SM: bounds the (tile, surface) table the last block scans
+constexpr int kTargetTiles = 592;          // 4 CTAs per SM: bounds the (tile, surface) table the last block scans
 
 struct OrderParams {
     TrcBounceCtl *ctl;
     int64_t capacity;               // hit capacity: offsets beyond it were never written
     const uint32_t *chunk_off, *chunk_cnt;
     const int32_t *keys;            // surface index per record
-    int chunks_per_tile;            // chunks of 256 rays handled by one warp, in ray order
-    int n_tiles;                    // warp tiles covering the capacity of the input bundle
+    int chunks_per_tile;            // chunks of 256 rays handled by one CTA, in ray order (an eighth per warp)
+    int n_tiles;                    // tiles covering the capacity of the input bundle
     int nbins;                      // n_keys when <= 256 (single pass), else 256 (low digit of a radix sort)
     int n_keys;
     uint32_t *hist;                 // [n_tiles][nbins]; exclusive-scanned over the tiles by the last block
@@ -46,14 +47,24 @@ struct OrderParams {
     int32_t *out_keys, *out_vals;   // scatter targets: slot -> surface, slot -> record index
 };
 
-// Walk the hits of one warp tile in ray order: chunk after chunk, records of a chunk in ascending ray index.
-// f(key, record index, valid) is called with all 32 lanes converged.
+// Chunk range [w0, w1) of this warp: the tile's chunks split into contiguous eighths, so that
+// (tile, warp, position) order is ray order.
+__device__ __forceinline__ void warp_chunk_range(const OrderParams &p, long long n_chunks, long long &w0, long long &w1) {
+    const int warp = threadIdx.x >> 5;
+    const long long t0 = (long long)blockIdx.x * p.chunks_per_tile;
+    long long t1 = t0 + p.chunks_per_tile;
+    if (t1 > n_chunks) t1 = n_chunks;
+    const int per_warp = (p.chunks_per_tile + kOrderWarps - 1) / kOrderWarps;
+    w0 = t0 + (long long)warp * per_warp;
+    w1 = w0 + per_warp;
+    if (w1 > t1) w1 = t1;
+}
+
+// Walk the hits of the chunks [c0, c1) in ray order: chunk after chunk, records of a chunk in ascending ray
+// index.  f(key, record index, valid) is called with all 32 lanes converged.
 template <typename F>
-__device__ __forceinline__ void for_each_hit_of_tile(const OrderParams &p, int tile, long long n_chunks, F f) {
+__device__ __forceinline__ void for_each_hit(const OrderParams &p, long long c0, long long c1, F f) {
     const int lane = threadIdx.x & 31;
-    const long long c0 = (long long)tile * p.chunks_per_tile;
-    long long c1 = c0 + p.chunks_per_tile;
-    if (c1 > n_chunks) c1 = n_chunks;
     for (long long cb = c0; cb < c1; cb += 32) {
         long long c = cb + lane;
         uint32_t off = 0, cnt = 0;
@@ -72,62 +83,113 @@ __device__ __forceinline__ void for_each_hit_of_tile(const OrderParams &p, int t
     }
 }
 
+// Per-warp digit counts of this warp's chunk range into cnt[warp][*] (zeroed here).
+__device__ __forceinline__ void count_digits(const OrderParams &p, long long n_chunks, uint32_t (*cnt)[kMaxBins]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool single = p.n_keys <= kMaxBins;
+    for (int b = lane; b < p.nbins; b += 32) cnt[warp][b] = 0;
+    __syncwarp();
+    long long w0, w1;
+    warp_chunk_range(p, n_chunks, w0, w1);
+    for_each_hit(p, w0, w1, [&](int32_t key, int32_t, bool valid) {
+        const int dg = valid ? (single ? key : (key & 255)) : -1;
+        const unsigned peers = __match_any_sync(0xffffffffu, dg);
+        if (valid && (peers & ((1u << lane) - 1u)) == 0u) cnt[warp][dg] += __popc(peers);
+        __syncwarp();
+    });
+}
+
 __global__ void __launch_bounds__(kOrderWarps * 32)
 order_hist_kernel(OrderParams p) {
     __shared__ uint32_t cnt[kOrderWarps][kMaxBins];
-    __shared__ long long s_tot[kMaxBins];
-    __shared__ bool s_is_last;
     pdl_wait();
     pdl_trigger();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long long hraw = (long long)p.ctl->hits;
     const bool overflow = hraw > p.capacity;
     const long long n = overflow ? 0 : p.ctl->n_in;
     const long long n_chunks = (n + TRC_HIT_CHUNK - 1) / TRC_HIT_CHUNK;
-    const int tile = blockIdx.x * kOrderWarps + warp;
-    const bool single = p.n_keys <= kMaxBins;
-    if (tile < p.n_tiles) {
-        for (int b = lane; b < p.nbins; b += 32) cnt[warp][b] = 0;
-        __syncwarp();
-        for_each_hit_of_tile(p, tile, n_chunks, [&](int32_t key, int32_t, bool valid) {
-            const int dg = valid ? (single ? key : (key & 255)) : -1;
-            const unsigned peers = __match_any_sync(0xffffffffu, dg);
-            if (valid && (peers & ((1u << lane) - 1u)) == 0u) cnt[warp][dg] += __popc(peers);
-            __syncwarp();
-        });
-        for (int b = lane; b < p.nbins; b += 32) p.hist[(size_t)tile * p.nbins + b] = cnt[warp][b];
+    count_digits(p, n_chunks, cnt);
+    __syncthreads();
+    if ((int)threadIdx.x < p.nbins) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int w = 0; w < kOrderWarps; ++w) t += cnt[w][threadIdx.x];
+        p.hist[(size_t)blockIdx.x * p.nbins + threadIdx.x] = t;
     }
-    __threadfence();
+}
+
+// One block: exclusive scan of every bin's column of the (tile, bin) table over the tiles, then of the bin
+// totals.  Warp w owns a contiguous band of tiles; lanes own bins lane, lane + 32, ... (coalesced rows).
+// Pass 1 sums the bands, pass 2 rewrites them as running prefixes starting from the sum of the bands before.
+__global__ void __launch_bounds__(kOrderWarps * 32)
+order_scan_kernel(OrderParams p) {
+    __shared__ uint32_t cnt[kOrderWarps][kMaxBins];
+    __shared__ long long s_tot[kMaxBins];
+    pdl_wait();
+    pdl_trigger();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool single = p.n_keys <= kMaxBins;
+    const int rows = p.n_tiles;
+    const int band = (rows + kOrderWarps - 1) / kOrderWarps;
+    const int r0 = warp * band, r1 = min(rows, r0 + band);
+    uint32_t acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0;
+    for (int r = r0; r < r1; ++r) {
+        const uint32_t *row = p.hist + (size_t)r * p.nbins;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { int b = lane + 32 * k; if (b < p.nbins) acc[k] += row[b]; }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) cnt[warp][lane + 32 * k] = acc[k];
     __syncthreads();
-    if (threadIdx.x == 0) s_is_last = atomicAdd(&p.ctl->ticket_order, 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (!s_is_last) return;
-    __threadfence();
-    // last block: exclusive scan of every bin's column over the tiles, then of the bin totals
+    uint32_t run[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        uint32_t base = 0;
+        for (int w = 0; w < warp; ++w) base += cnt[w][lane + 32 * k];
+        run[k] = base;
+    }
+    for (int r = r0; r < r1; r += 4) {
+        uint32_t v[4][8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t *row = p.hist + (size_t)(r + q) * p.nbins;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { int b = lane + 32 * k; v[q][k] = (r + q < r1 && b < p.nbins) ? row[b] : 0u; }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t *row = p.hist + (size_t)(r + q) * p.nbins;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                int b = lane + 32 * k;
+                if (r + q < r1 && b < p.nbins) row[b] = run[k];
+                run[k] += v[q][k];
+            }
+        }
+    }
+    // bin totals and their exclusive scan (= slot offsets per surface for a single pass)
     long long tot = 0;
     if ((int)threadIdx.x < p.nbins) {
-        uint32_t run = 0;
-        uint32_t *col = p.hist + threadIdx.x;
-#pragma unroll 8
-        for (int t = 0; t < p.n_tiles; ++t) {
-            uint32_t v = __ldcg(col + (size_t)t * p.nbins);
-            col[(size_t)t * p.nbins] = run;
-            run += v;
-        }
-        tot = run;
+#pragma unroll
+        for (int w = 0; w < kOrderWarps; ++w) tot += cnt[w][threadIdx.x];
     }
     s_tot[threadIdx.x] = tot;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        long long run = 0;
-        for (int b = 0; b < p.nbins; ++b) { long long v = s_tot[b]; s_tot[b] = run; run += v; }
-        p.bin_off[p.nbins] = run;
-        *p.h_eff = run;
+    for (int o = 1; o < kMaxBins; o <<= 1) {          // inclusive Hillis-Steele scan over the 256 bins
+        long long add = (int)threadIdx.x >= o ? s_tot[threadIdx.x - o] : 0;
+        __syncthreads();
+        s_tot[threadIdx.x] += add;
+        __syncthreads();
     }
-    __syncthreads();
     if ((int)threadIdx.x < p.nbins) {
-        p.bin_off[threadIdx.x] = s_tot[threadIdx.x];
+        p.bin_off[threadIdx.x] = s_tot[threadIdx.x] - tot;
         if (single && p.hits_per_surface) p.hits_per_surface[threadIdx.x] += tot;
+    }
+    if (threadIdx.x == kMaxBins - 1) {
+        p.bin_off[p.nbins] = s_tot[threadIdx.x];
+        *p.h_eff = s_tot[threadIdx.x];
     }
 }
 
@@ -141,13 +203,20 @@ order_scatter_kernel(OrderParams p) {
     if (hraw > p.capacity) return;
     const long long n = p.ctl->n_in;
     const long long n_chunks = (n + TRC_HIT_CHUNK - 1) / TRC_HIT_CHUNK;
-    const int tile = blockIdx.x * kOrderWarps + warp;
+    if ((long long)blockIdx.x * p.chunks_per_tile >= n_chunks) return;
     const bool single = p.n_keys <= kMaxBins;
-    if (tile >= p.n_tiles) return;
-    for (int b = lane; b < p.nbins; b += 32)
-        pos[warp][b] = (uint32_t)p.bin_off[b] + p.hist[(size_t)tile * p.nbins + b];
-    __syncwarp();
-    for_each_hit_of_tile(p, tile, n_chunks, [&](int32_t key, int32_t rec, bool valid) {
+    // counts per warp again (4 bytes per hit out of L2), then this warp's first slot of every bin
+    count_digits(p, n_chunks, pos);
+    __syncthreads();
+    if ((int)threadIdx.x < p.nbins) {
+        uint32_t base = (uint32_t)p.bin_off[threadIdx.x] + p.hist[(size_t)blockIdx.x * p.nbins + threadIdx.x];
+#pragma unroll
+        for (int w = 0; w < kOrderWarps; ++w) { uint32_t c = pos[w][threadIdx.x]; pos[w][threadIdx.x] = base; base += c; }
+    }
+    __syncthreads();
+    long long w0, w1;
+    warp_chunk_range(p, n_chunks, w0, w1);
+    for_each_hit(p, w0, w1, [&](int32_t key, int32_t rec, bool valid) {
         const int dg = valid ? (single ? key : (key & 255)) : -1;
         const unsigned peers = __match_any_sync(0xffffffffu, dg);
         const unsigned before = __popc(peers & ((1u << lane) - 1u));
@@ -217,32 +286,20 @@ partition_kernel(PartParams p) {
     if (a.w) b.w[dst] = a.w[q];
 }
 
-// After the partition the second copy holds the survivors-first order; the next bounce reads the FIRST copy
-// (its kernels were enqueued with those addresses), so the two copies trade contents.
-__global__ void __launch_bounds__(256)
-swap_kernel(PartParams p) {
-    pdl_wait();
-    pdl_trigger();
-    if (!p.ctl->reorder) return;
-    const long long hraw = (long long)p.ctl->hits;
-    const long long h = hraw < p.capacity ? hraw : p.capacity;
-    const long long q = (long long)blockIdx.x * 256 + threadIdx.x;
-    if (q >= h) return;
-    const Columns &a = p.a, &b = p.b;
-#define TRC_SWAP(x, y) { auto t_ = (x); (x) = (y); (y) = t_; }
-    TRC_SWAP(a.v[q], b.v[q]); TRC_SWAP(a.v[a.ld + q], b.v[b.ld + q]); TRC_SWAP(a.v[2 * a.ld + q], b.v[2 * b.ld + q]);
-    TRC_SWAP(a.d[q], b.d[q]); TRC_SWAP(a.d[a.ld + q], b.d[b.ld + q]); TRC_SWAP(a.d[2 * a.ld + q], b.d[2 * b.ld + q]);
-    TRC_SWAP(a.e[q], b.e[q]); TRC_SWAP(a.par[q], b.par[q]); TRC_SWAP(a.ids[q], b.ids[q]);
-    if (a.w) TRC_SWAP(a.w[q], b.w[q]);
-#undef TRC_SWAP
-}
-
-__global__ void trace_init_kernel(TrcBounceCtl *ctl, int n_ctl, long long n0, int64_t *counts, int n_counts) {
+__global__ void trace_init_kernel(TrcBounceCtl *ctl, int n_ctl, long long n0, TrcBundleDesc in0, int64_t *counts,
+                                  int n_counts, double *absorbed, int64_t *hits, int n_tally) {
     pdl_wait();
     int i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int k = i; k < n_tally; k += gridDim.x * blockDim.x) { absorbed[k] = 0.0; hits[k] = 0; }
     long long *w = reinterpret_cast<long long *>(ctl);
     const int words = n_ctl * (int)(sizeof(TrcBounceCtl) / 8);
-    if (i < words) w[i] = (i == 0) ? n0 : 0;      // word 0 = ctl[0].n_in
+    const int w_in = (int)(offsetof(TrcBounceCtl, in) / 8), n_in_words = (int)(sizeof(TrcBundleDesc) / 8);
+    if (i < words) {
+        long long v = 0;
+        if (i == 0) v = n0;                                            // ctl[0].n_in
+        else if (i >= w_in && i < w_in + n_in_words) v = reinterpret_cast<const long long *>(&in0)[i - w_in];
+        w[i] = v;
+    }
     if (i < n_counts) counts[i] = 0;
 }
 
@@ -274,15 +331,14 @@ void bounce_layout(int64_t base, int64_t cap, uint32_t columns, int has_w, int32
 
 struct ScratchPlan {
     int64_t off_ctl, off_counts, off_heff, off_records, off_keys, off_chunk_off, off_chunk_cnt, off_slot_surf,
-        off_slot_rec, off_alt_k, off_alt_v, off_hist, off_bin_off, off_sort_work, off_cull, off_cta_surv, off_cta_sum,
-        off_cta_key, total;
+        off_slot_rec, off_alt_k, off_alt_v, off_hist, off_bin_off, off_sort_work, off_cull, off_cta_surv, total;
     int64_t cap_max, in_max;
 };
 
 int tiles_for(int64_t n_in_cap, int *chunks_per_tile) {
     int64_t n_chunks = (n_in_cap + TRC_HIT_CHUNK - 1) / TRC_HIT_CHUNK;
     if (n_chunks < 1) n_chunks = 1;
-    int64_t g = (n_chunks + kTargetWarpTiles - 1) / kTargetWarpTiles;
+    int64_t g = (n_chunks + kTargetTiles - 1) / kTargetTiles;
     if (g < 1) g = 1;
     *chunks_per_tile = (int)g;
     return (int)((n_chunks + g - 1) / g);
@@ -333,8 +389,6 @@ ScratchPlan scratch_plan(const TrcScene *sc, const TrcTraceArgs *a) {
     s.off_sort_work = take(multi ? trc_sort_work_bytes(cap_max, S) : 0);
     s.off_cull = take(4 * cap_max);
     s.off_cta_surv = take(4 * nb);
-    s.off_cta_sum = take(8 * nb);
-    s.off_cta_key = take(4 * nb);
     s.total = off;
     return s;
 }
@@ -369,9 +423,18 @@ extern "C" int trc_trace_init(const TrcScene *sc, const TrcTraceArgs *a, void *s
     if (a->scratch_bytes < s.total) return fail(TRC_ERR_BAD_ARGUMENT, "trc_trace_init: scratch arena smaller than planned%s");
     char *scr = (char *)a->d_scratch;
     const int words = (TRC_TRACE_MAX_BOUNCES + 1) * (int)(sizeof(TrcBounceCtl) / 8);
-    TRC_CUDA(launch_pdl(trace_init_kernel, dim3((words + 255) / 256), dim3(256), 0, (cudaStream_t)stream,
-                        (TrcBounceCtl *)(scr + s.off_ctl), TRC_TRACE_MAX_BOUNCES + 1, (long long)a->n,
-                        (int64_t *)(scr + s.off_counts), 4 * TRC_TRACE_MAX_BOUNCES));
+    TrcBundleDesc in0 = {a->d_vertices, a->d_directions, a->d_energy, a->d_wavelengths,
+                         (const long long *)a->d_ray_ids, (long long)a->ray_id_base, (long long)a->ld};
+    const int n_tally = (a->flags & TRC_TRACE_ZERO_TALLIES) ? sc->n_surfaces : 0;
+    if (n_tally && (!a->d_absorbed_per_surface || !a->d_hits_per_surface))
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_trace_init: TRC_TRACE_ZERO_TALLIES without tally arrays%s");
+    int blocks = (words + 255) / 256;
+    if ((n_tally + 255) / 256 > blocks) blocks = (n_tally + 255) / 256;
+    if (blocks > 1024) blocks = 1024;
+    TRC_CUDA(launch_pdl(trace_init_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream,
+                        (TrcBounceCtl *)(scr + s.off_ctl), TRC_TRACE_MAX_BOUNCES + 1, (long long)a->n, in0,
+                        (int64_t *)(scr + s.off_counts), 4 * TRC_TRACE_MAX_BOUNCES, a->d_absorbed_per_surface,
+                        a->d_hits_per_surface, n_tally));
     return check_launch("trace_init");
 }
 
@@ -406,10 +469,7 @@ extern "C" int trc_trace(const TrcScene *sc, const TrcTraceArgs *a, void *stream
         rc = trc_trace_init(sc, a, stream);
         if (rc != TRC_OK) return rc;
     }
-    // bundle entering the current bounce
-    const double *V = a->d_vertices, *D = a->d_directions, *E = a->d_energy, *W = a->d_wavelengths;
-    const int64_t *ids = a->d_ray_ids;
-    int64_t id_base = a->ray_id_base, ld = a->ld, in_cap = a->n;
+    int64_t in_cap = a->n;            // capacity of the bundle entering the current bounce (it sizes the grids)
     for (int j = 0; j < a->n_bounces; ++j) {
         const int64_t cap = a->capacity[j];
         const TrcTraceBounceLayout &L = plan.bounce[j];
@@ -425,8 +485,7 @@ extern "C" int trc_trace(const TrcScene *sc, const TrcTraceArgs *a, void *stream
                 }
                 TRC_CUDA(cudaEventRecord(scw->ev_walk[0], st));
             }
-            TrcNearestDyn dyn = {&c->n_in, &c->chunk_counter, &c->hits};
-            rc = trc_nearest_dyn(sc, in_cap, V, D, E, ld, a->use_bvh, records, keys, cap, chunk_off, chunk_cnt, &dyn, st);
+            rc = trc_nearest_dyn(sc, in_cap, c, a->use_bvh, records, keys, cap, chunk_off, chunk_cnt, st);
             if (rc != TRC_OK) return rc;
             if (timed) TRC_CUDA(cudaEventRecord(scw->ev_walk[1], st));
         }
@@ -447,10 +506,11 @@ extern "C" int trc_trace(const TrcScene *sc, const TrcTraceArgs *a, void *stream
         const bool first_to_alt = (tail_passes & 1) != 0;
         op.out_keys = first_to_alt ? alt_k : slot_surf;
         op.out_vals = first_to_alt ? alt_v : slot_rec;
-        const unsigned oblocks = (unsigned)((op.n_tiles + kOrderWarps - 1) / kOrderWarps);
+        const unsigned oblocks = (unsigned)op.n_tiles;
         TRC_CUDA(launch_pdl(order_hist_kernel, dim3(oblocks), dim3(kOrderWarps * 32), 0, st, op));
+        TRC_CUDA(launch_pdl(order_scan_kernel, dim3(1), dim3(kOrderWarps * 32), 0, st, op));
         TRC_CUDA(launch_pdl(order_scatter_kernel, dim3(oblocks), dim3(kOrderWarps * 32), 0, st, op));
-        rc = check_launch("order", 2);
+        rc = check_launch("order", 3);
         if (rc != TRC_OK) return rc;
         if (multi) {
             bool in_first = true;
@@ -467,7 +527,7 @@ extern "C" int trc_trace(const TrcScene *sc, const TrcTraceArgs *a, void *stream
         // 4. optics, accountant columns, per-surface sums; its last block closes the bounce
         TrcOpticsArgs o;
         memset(&o, 0, sizeof(o));
-        o.h = cap; o.d_records = records; o.d_slot_rec = slot_rec; o.d_wavelengths = W;
+        o.h = cap; o.d_records = records; o.d_slot_rec = slot_rec;       // wavelengths / ids: from the control block
         o.d_out_vertices = (double *)(keep + L.off_vertices); o.d_out_directions = (double *)(keep + L.off_directions);
         o.d_out_energy = (double *)(keep + L.off_energy); o.d_out_parents = (int64_t *)(keep + L.off_parents);
         o.d_out_ray_ids = (int64_t *)(keep + L.off_ray_ids);
@@ -480,12 +540,20 @@ extern "C" int trc_trace(const TrcScene *sc, const TrcTraceArgs *a, void *stream
         o.d_attenuated = L.off_attenuated >= 0 ? (double *)(keep + L.off_attenuated) : nullptr;
         o.d_out_wavelengths = has_w ? (double *)(keep + L.off_wavelengths) : nullptr;
         o.d_cull = (int32_t *)(scr + sp.off_cull);
-        o.d_ray_ids = ids; o.ray_id_base = id_base;
-        TrcOpticsDyn od = {c, c + 1, (uint32_t *)(scr + sp.off_cta_surv), (double *)(scr + sp.off_cta_sum),
-                           (int32_t *)(scr + sp.off_cta_key), a->d_absorbed_per_surface, d_counts + 4 * j};
+        TrcOpticsDyn od;
+        od.ctl = c; od.ctl_next = c + 1;
+        od.children = {o.d_out_vertices, o.d_out_directions, o.d_out_energy, o.d_out_wavelengths,
+                       (const long long *)o.d_out_ray_ids, 0, (long long)cap};
+        od.children_sorted = {(const double *)(keep + L.off_alt_vertices), (const double *)(keep + L.off_alt_directions),
+                              (const double *)(keep + L.off_alt_energy),
+                              has_w ? (const double *)(keep + L.off_alt_wavelengths) : nullptr,
+                              (const long long *)(keep + L.off_alt_ray_ids), 0, (long long)cap};
+        od.cta_surv = (uint32_t *)(scr + sp.off_cta_surv);
+        od.absorbed_per_surface = a->d_absorbed_per_surface;
+        od.d_counts = d_counts + 4 * j;
         rc = trc_optics_dyn(sc, &o, &od, stream);
         if (rc != TRC_OK) return rc;
-        // 5./6. survivors first (acts only when some but not all children are weak)
+        // 5. survivors-first copy (acts only when some but not all children are weak)
         PartParams pp;
         pp.ctl = c; pp.capacity = cap; pp.cull = o.d_cull; pp.cta_surv = od.cta_surv;
         pp.a = {o.d_out_vertices, o.d_out_directions, o.d_out_energy, o.d_out_parents, o.d_out_ray_ids,
@@ -495,12 +563,9 @@ extern "C" int trc_trace(const TrcScene *sc, const TrcTraceArgs *a, void *stream
                 (int64_t *)(keep + L.off_alt_ray_ids), has_w ? (double *)(keep + L.off_alt_wavelengths) : nullptr, cap};
         const unsigned pblocks = (unsigned)((cap + 255) / 256);
         TRC_CUDA(launch_pdl(partition_kernel, dim3(pblocks), dim3(256), 0, st, pp));
-        TRC_CUDA(launch_pdl(swap_kernel, dim3(pblocks), dim3(256), 0, st, pp));
-        rc = check_launch("partition", 2);
+        rc = check_launch("partition");
         if (rc != TRC_OK) return rc;
-        // the children (survivors first) are the next bundle
-        V = o.d_out_vertices; D = o.d_out_directions; E = o.d_out_energy; W = o.d_out_wavelengths;
-        ids = o.d_out_ray_ids; id_base = 0; ld = cap; in_cap = cap;
+        in_cap = cap;      // the children are the next bundle; which copy, the device decided (TrcBounceCtl::in)
     }
     // one read-back for the whole trace
     const int64_t per = 4 + ((a->flags & TRC_TRACE_SEG) ? S + 1 : 0);

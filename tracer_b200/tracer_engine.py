@@ -108,6 +108,7 @@ class TracerEngine(object):
         self._hist = {}           # bounce -> (rays in, hits, survivors) of the previous trace (plans trc_trace)
         self._cap_floor = {}      # bounce -> smallest capacity that is known to fit (set after an overflow)
         self._counts_host = None  # page-locked int64 words for the one read-back of a trace
+        self._tallies_dirty = False
         self._copy_stream = None
         self._keep_tree = False
         self.fused_bounce = True   # sequence a bounce inside the library (trc_bounce) when the configuration allows
@@ -120,6 +121,8 @@ class TracerEngine(object):
         caching host allocator: ~50 GB/s instead of the ~5 GB/s of a pageable copy, and the
         block is recycled once the caller drops the array)."""
         import torch
+        if t.numel() == 0:
+            return np.zeros(tuple(t.shape))
         t = t.contiguous()
         if t.numel() < (1 << 20):
             return t.cpu().numpy()
@@ -558,6 +561,9 @@ class TracerEngine(object):
         a.use_bvh, a.first_bounce, a.n_bounces = (1 if use_bvh else 0), bounce, nb
         timed = self.kernel_events is not None and bounce == 0 and cur.slices is None
         a.flags = (L.TRACE_SEG if scene.has_accountants else 0) | (L.TRACE_TIME_WALK if timed else 0)
+        if self._tallies_dirty:
+            a.flags |= L.TRACE_ZERO_TALLIES     # the trace's first launch zeroes the per-surface tallies
+            self._tallies_dirty = False
         a.seed, a.min_energy, a.columns = self.seed, float(min_energy), cols
         for j, c in enumerate(caps):
             a.capacity[j] = c
@@ -592,7 +598,8 @@ class TracerEngine(object):
         stream.synchronize()                    # the only synchronisation of the block
         per = 4 + (S + 1 if scene.has_accountants else 0)
         host = counts[:nb * per].numpy()
-        f64, i64 = torch.float64, torch.int64
+        k64, ki64 = keep.view(torch.float64), keep.view(torch.int64)
+        f64, i64 = k64, ki64
         out = []
         for j in range(nb):
             n_in, H, n_surv, reorder = (int(x) for x in host[per * j:per * j + 4])
@@ -614,26 +621,29 @@ class TracerEngine(object):
             lay = plan.bounce[j]
             ld = int(lay.ld)
 
-            def view(off, dtype, rows, lay_ld=ld, h=H):
+            def view(off, base, rows, lay_ld=ld, h=H):
                 if off < 0:
                     return None
-                t = keep[off:off + 8 * lay_ld * (rows or 1)].view(dtype)
-                return t.view(rows, lay_ld)[:, :h] if rows else t[:h]
-            first = dict(V=view(lay.off_vertices, f64, 3), D=view(lay.off_directions, f64, 3),
-                         E=view(lay.off_energy, f64, 0), P=view(lay.off_parents, i64, 0),
-                         W=view(lay.off_wavelengths, f64, 0), I=view(lay.off_ray_ids, i64, 0))
-            pre = first
-            if reorder:        # survivors-first copy and slot-order copy differ
-                pre = dict(V=view(lay.off_alt_vertices, f64, 3), D=view(lay.off_alt_directions, f64, 3),
-                           E=view(lay.off_alt_energy, f64, 0), P=view(lay.off_alt_parents, i64, 0),
-                           W=view(lay.off_alt_wavelengths, f64, 0))
+                if rows:
+                    return torch.as_strided(base, (rows, h), (lay_ld, 1), off >> 3)
+                return torch.as_strided(base, (h,), (1,), off >> 3)
+            pre = dict(V=view(lay.off_vertices, f64, 3), D=view(lay.off_directions, f64, 3),
+                       E=view(lay.off_energy, f64, 0), P=view(lay.off_parents, i64, 0),
+                       W=view(lay.off_wavelengths, f64, 0), I=view(lay.off_ray_ids, i64, 0))
+            first = pre
+            if reorder:        # some but not all children are weak: the survivors-first copy was made
+                first = dict(V=view(lay.off_alt_vertices, f64, 3), D=view(lay.off_alt_directions, f64, 3),
+                             E=view(lay.off_alt_energy, f64, 0), P=view(lay.off_alt_parents, i64, 0),
+                             W=view(lay.off_alt_wavelengths, f64, 0), I=view(lay.off_alt_ray_ids, i64, 0))
             if scene.has_accountants:
                 seg = host[per * j + 4:per * (j + 1)]
-                self._account(scene, seg, dict(
-                    hits=pre['V'], absorbed=view(lay.off_absorbed, f64, 0), e_out=pre['E'],
-                    normals=view(lay.off_normals, f64, 3), e_in=view(lay.off_e_in, f64, 0),
-                    dirs_in=view(lay.off_dirs_in, f64, 3), wavelengths=pre['W'],
-                    attenuated=view(lay.off_attenuated, f64, 0)), copy=not self._keep_tree)
+                src = dict(hits=pre['V'], e_out=pre['E'], wavelengths=pre['W'])
+                for name, off, rows in (('absorbed', lay.off_absorbed, 0), ('normals', lay.off_normals, 3),
+                                        ('e_in', lay.off_e_in, 0), ('dirs_in', lay.off_dirs_in, 3),
+                                        ('attenuated', lay.off_attenuated, 0)):
+                    if name in want:
+                        src[name] = view(off, f64, rows)
+                self._account(scene, seg, src, copy=not self._keep_tree)
             rec = dict(first)
             rec['pre_cull'] = dict(V=pre['V'], D=pre['D'], E=pre['E'], P=pre['P'], W=pre['W'])
             out.append((rec, n_surv, H, n_in))
@@ -717,10 +727,17 @@ class TracerEngine(object):
         if scene.has_refractive and cur.R is None:
             raise ValueError("scene has refractive optics but the bundle carries no 'ref_index'")
         source_E = cur.E
-        self.absorbed_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.float64, device=self.device)
-        self.hits_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.int64, device=self.device)
         # device-driven (trc_trace) unless draws are injected or some optics emits two children per hit
         device_driven = self.fused_bounce and self.rng == 'philox' and not scene.has_split and cur.R is None
+        if device_driven and cur.n > 0 and reps > 0:
+            tall = torch.empty(2 * scene.num_surfaces, dtype=torch.float64, device=self.device)
+            self.absorbed_per_surface = tall[:scene.num_surfaces]
+            self.hits_per_surface = tall[scene.num_surfaces:].view(torch.int64)
+            self._tallies_dirty = True
+        else:
+            self.absorbed_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.float64, device=self.device)
+            self.hits_per_surface = torch.zeros(scene.num_surfaces, dtype=torch.int64, device=self.device)
+            self._tallies_dirty = False
         ray_bounces = 0
         per_bounce = []
         last_rec = None

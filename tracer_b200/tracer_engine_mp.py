@@ -83,6 +83,8 @@ class TracerEngineMP(TracerEngine):
         import torch
         import torch.distributed as dist
         S = self.absorbed_per_surface.shape[0]
+        if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+            return self.absorbed_per_surface, self.hits_per_surface, bins
         parts = [self.absorbed_per_surface, self.hits_per_surface.to(torch.float64)]
         if bins is not None:
             parts.append(bins.reshape(-1))
