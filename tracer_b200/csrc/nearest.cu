@@ -154,10 +154,28 @@ constexpr int kStack = 64;
 #endif
 constexpr int kWalkSteps = TRC_WALK_STEPS;                  // visits per lane between two warp-level collections
 constexpr unsigned kNoEntry = 0xffffffffu;    // (first < 2^22 - 1, so no real entry is all ones)
-#ifndef TRC_WALK_RING
-#define TRC_WALK_RING 3
+// Ray ring of a warp, two interchangeable transports (TRC_WALK_TMA):
+//   1: batches of 64 rays, six 1-D bulk copies (cp.async.bulk -> SASS UBLKCP) issued by one lane, completion on an
+//      mbarrier; the rays bypass L1, so the float64 stage and the record emission re-read them from L2;
+//   0: batches of 32 rays, six 8-byte cp.async.ca per lane (LDGSTS), which also leave the rays in L1.
+#ifndef TRC_WALK_TMA
+#define TRC_WALK_TMA 1
 #endif
-constexpr int kRing = TRC_WALK_RING;                       // ray batches in flight per warp (cp.async), 1.5 KB each
+#if TRC_WALK_TMA
+#ifndef TRC_WALK_BATCH
+#define TRC_WALK_BATCH 64
+#endif
+#ifndef TRC_WALK_AHEAD
+#define TRC_WALK_AHEAD 1
+#endif
+constexpr int kBatch = TRC_WALK_BATCH;        // rays per batch: six rows of 8 * kBatch bytes, one cp.async.bulk each
+constexpr int kAhead = TRC_WALK_AHEAD;        // batches landing while one is consumed
+constexpr int kRing = kAhead < 2 ? 2 : 4;     // slots (a power of two)
+static_assert(kAhead >= 1 && kAhead <= 3 && (kBatch == 32 || kBatch == 64), "ring shape");
+#else
+constexpr int kRing = 4;                      // three batches in flight (a power of two keeps the slot index cheap)
+constexpr int kBatch = 32;
+#endif
 constexpr int kListFields = 10;               // A[3], Bn[3], Bf[3], slot | direction signs << 8
 #ifndef TRC_WALK_SMEM_PAIRS
 #define TRC_WALK_SMEM_PAIRS 512
@@ -174,7 +192,8 @@ struct WalkWarpShared {
     unsigned queue2[64];                      // candidates that passed the float32 triangle pre-test
     int q2n;                                  // its fill (warp-uniform, kept here to spare a register)
     long long fifo[4];                        // chunk ids in consumption order (written by the prefetcher)
-    double ring[kRing][6][32];                // cp.async landing zone: vertex + direction rows of 32 rays
+    alignas(16) double ring[kRing][6][kBatch];   // bulk-copy landing zone (16-byte aligned rows): vertex + direction rows
+    unsigned long long mbar[kRing];           // one mbarrier per landing slot (transaction bytes of its six copies)
     const double *vert, *dir, *energy;        // the bundle (kernel parameters, or the control block of a device-driven
     long long ld;                             // trace): read from here so that they cost no registers in the walk loop
 };
@@ -288,13 +307,32 @@ __device__ __forceinline__ uint4 lds128(unsigned addr) {
 
 // Conservative entry distance into the child box whose axis words are w0, w1, w2;
 // hit = entered before tbest.
+#ifndef TRC_WALK_FFMA2
+#define TRC_WALK_FFMA2 0
+#endif
+// two float32 FMAs in one instruction (fma.rn.f32x2, sm_100+ -> SASS FFMA2): halves the FMA issue slots of a visit
+__device__ __forceinline__ void fma2(float a0, float a1, float b0, float b1, float c0, float c1, float &d0, float &d1) {
+    unsigned long long a, b, c, d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(b) : "f"(b0), "f"(b1));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(c) : "f"(c0), "f"(c1));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
+}
 __device__ __forceinline__ float slab16(unsigned w0, unsigned w1, unsigned w2, const RayF &r, float tbest, bool &hit) {
+#if TRC_WALK_FFMA2
+    float n0, n1, n2, f0, f1, f2;
+    fma2(plane(w0, r.sn[0]), plane(w1, r.sn[1]), r.A[0], r.A[1], r.Bn[0], r.Bn[1], n0, n1);
+    fma2(plane(w0, r.sf[0]), plane(w1, r.sf[1]), r.A[0], r.A[1], r.Bf[0], r.Bf[1], f0, f1);
+    fma2(plane(w2, r.sn[2]), plane(w2, r.sf[2]), r.A[2], r.A[2], r.Bn[2], r.Bf[2], n2, f2);
+#else
     float n0 = fmaf(plane(w0, r.sn[0]), r.A[0], r.Bn[0]);
     float n1 = fmaf(plane(w1, r.sn[1]), r.A[1], r.Bn[1]);
     float n2 = fmaf(plane(w2, r.sn[2]), r.A[2], r.Bn[2]);
     float f0 = fmaf(plane(w0, r.sf[0]), r.A[0], r.Bf[0]);
     float f1 = fmaf(plane(w1, r.sf[1]), r.A[1], r.Bf[1]);
     float f2 = fmaf(plane(w2, r.sf[2]), r.A[2], r.Bf[2]);
+#endif
     float tmin = fmaxf(fmaxf(n0, n1), fmaxf(n2, 0.0f));
     float tmax = fminf(fminf(f0, f1), fminf(f2, tbest));
     hit = tmin <= tmax;
@@ -376,7 +414,7 @@ __device__ __noinline__ int flush_queue_generic(WalkWarpShared &sh, const WalkPa
 // own error band decides nothing.  The plane distance t is not used: the float64 stage rules on it.
 __device__ __forceinline__ bool tri_prefilter(const float4 *tri, V3 v, V3 d) {
     const float4 a = __ldg(tri), b = __ldg(tri + 1), c = __ldg(tri + 2);
-    if (c.y == 0.f) return true;                                 // not a triangle
+    if (c.y == 0.f) return true;                                 // neither a triangle nor a plate: not pre-tested
     const float ox = (float)v.x, oy = (float)v.y, oz = (float)v.z;
     const float dx = (float)d.x, dy = (float)d.y, dz = (float)d.z;
     const float e0x = a.w, e0y = b.x, e0z = b.y, e1x = b.z, e1y = b.w, e1z = c.x;
@@ -394,6 +432,11 @@ __device__ __forceinline__ bool tri_prefilter(const float4 *tri, V3 v, V3 d) {
     const float nd = fabsf(dx) + fabsf(dy) + fabsf(dz);
     const float err_u = keps * A * n1 * nd, err_v = keps * A * n0 * nd, err_d = keps * n0 * n1 * nd;
     if (!(ad > 2.f * err_d)) return true;                        // grazing / degenerate / NaN: undecided
+    if (c.y == 2.f) {                                            // centred parallelogram: |u| <= 1 and |v| <= 1
+        if (fabsf(nu) - ad > err_u + err_d) return false;
+        if (fabsf(nv) - ad > err_v + err_d) return false;
+        return true;
+    }
     if (nu < -err_u || nv < -err_v) return false;
     if (nu + nv - ad > err_u + err_v + err_d) return false;
     return true;
@@ -487,9 +530,31 @@ __device__ __forceinline__ void emit_chunk_hits(WalkWarpShared &sh, const WalkPa
     __syncwarp();
 }
 
+// ---- 1-D bulk copies (TMA engine, sm_90+) into the per-warp ray ring, completion through an mbarrier
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    unsigned done;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+}
 __device__ __forceinline__ void cp_async8(void *smem_dst, const void *gmem_src) {
     unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
 // kAllShared: the whole tree fits the shared-memory cache (no global-memory path in the walk)
@@ -530,14 +595,24 @@ nearest_hit_walk_kernel(WalkParams p) {
                                                 : (unsigned)TRC_META_INDEX(p.root_meta);
     int stack[kStack];
 
-    // ---- ray prefetcher: the warp streams batches of 32 rays (chunk after chunk, chunk
-    // ids from the global counter) into a ring of kRing shared-memory slots with
-    // cp.async, always kRing - 1 batches ahead of stage A, so a ray is read from HBM
-    // exactly once and stage A never waits for DRAM.
+    // ---- ray prefetcher: the warp streams batches of kBatch rays (chunk after chunk, chunk ids from the
+    // global counter) into a two-slot shared-memory ring, one batch ahead of stage A: six 1-D bulk copies
+    // (cp.async.bulk, one per coordinate row) issued by ONE lane and tracked by the slot's mbarrier, so a ray
+    // is read from HBM exactly once, stage A does not wait for DRAM, and no lane computes addresses.
     int64_t pc;            // chunk being prefetched           (warp-uniform)
     int pc_n = 0;          // rays in that chunk (0: past the end of the bundle)
     int poff = 0;          // next ray offset in that chunk
     int fifo_w = 0, fifo_r = 0, ring_w = 0, ring_r = 0;
+#if TRC_WALK_TMA
+    if (lane == 0) {
+        for (int k = 0; k < kRing; ++k) mbar_init(smem_u32(&sh.mbar[k]), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncwarp();
+    // bulk copies need 16-byte aligned rows: otherwise (odd row stride, sliced bundle) lanes copy by hand
+    const bool bulk_ok = ((((unsigned long long)sh.vert | (unsigned long long)sh.dir) & 15ULL) == 0ULL) && ((sh.ld & 1LL) == 0LL);
+#endif
     auto fetch_chunk = [&]() -> int64_t {
         unsigned long long c = 0;
         if (lane == 0) c = atomicAdd(p.chunk_counter, 1ULL);
@@ -549,19 +624,20 @@ nearest_hit_walk_kernel(WalkParams p) {
         pc_n = rem <= 0 ? 0 : (rem < kChunk ? (int)rem : kChunk);
         return (int64_t)c;
     };
+#if !TRC_WALK_TMA
     auto issue_batch = [&]() {
         if (pc_n > 0) {
             int64_t ray = pc * kChunk + poff + lane;
             if (poff + lane < pc_n) {
-                double *dst = &sh.ring[ring_w % kRing][0][lane];
+                double *dst = &sh.ring[ring_w & (kRing - 1)][0][lane];
                 const double *vp = sh.vert + ray, *dp = sh.dir + ray;
                 const long long ld = sh.ld;
                 cp_async8(dst, vp);
-                cp_async8(dst + 32, vp + ld);
-                cp_async8(dst + 64, vp + 2 * ld);
-                cp_async8(dst + 96, dp);
-                cp_async8(dst + 128, dp + ld);
-                cp_async8(dst + 160, dp + 2 * ld);
+                cp_async8(dst + kBatch, vp + ld);
+                cp_async8(dst + 2 * kBatch, vp + 2 * ld);
+                cp_async8(dst + 3 * kBatch, dp);
+                cp_async8(dst + 4 * kBatch, dp + ld);
+                cp_async8(dst + 5 * kBatch, dp + 2 * ld);
             }
             poff += 32;
             if (poff >= pc_n) { pc = fetch_chunk(); poff = 0; }
@@ -570,8 +646,48 @@ nearest_hit_walk_kernel(WalkParams p) {
         ++ring_w;
     };
     pc = fetch_chunk();
+    issue_batch();
+    issue_batch();
+#else
+    auto issue_batch = [&]() {
+        if (pc_n <= 0) return;                    // past the end of the bundle: nobody will wait for this batch
+        const int cnt = min(kBatch, pc_n - poff);
+        const int slot = ring_w & (kRing - 1);
+        const int64_t ray0 = pc * kChunk + poff;
+        if (bulk_ok && (cnt & 1) == 0) {
+            if (lane == 0) {
+                const unsigned bar = smem_u32(&sh.mbar[slot]);
+                const unsigned dst = smem_u32(&sh.ring[slot][0][0]);
+                const unsigned bytes = 8u * (unsigned)cnt;
+                const double *vp = sh.vert + ray0, *dp = sh.dir + ray0;
+                const long long ld = sh.ld;
+                mbar_arrive_expect_tx(bar, 6u * bytes);
+                bulk_g2s(dst, vp, bytes, bar);
+                bulk_g2s(dst + 8u * kBatch, vp + ld, bytes, bar);
+                bulk_g2s(dst + 16u * kBatch, vp + 2 * ld, bytes, bar);
+                bulk_g2s(dst + 24u * kBatch, dp, bytes, bar);
+                bulk_g2s(dst + 32u * kBatch, dp + ld, bytes, bar);
+                bulk_g2s(dst + 40u * kBatch, dp + 2 * ld, bytes, bar);
+            }
+        } else {
+            for (int j = lane; j < cnt; j += 32) {
+                const double *vp = sh.vert + ray0 + j, *dp = sh.dir + ray0 + j;
+                const long long ld = sh.ld;
+                double *dst = &sh.ring[slot][0][j];
+                dst[0] = vp[0]; dst[kBatch] = vp[ld]; dst[2 * kBatch] = vp[2 * ld];
+                dst[3 * kBatch] = dp[0]; dst[4 * kBatch] = dp[ld]; dst[5 * kBatch] = dp[2 * ld];
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&sh.mbar[slot]));
+        }
+        poff += cnt;
+        if (poff >= pc_n) { pc = fetch_chunk(); poff = 0; }
+        ++ring_w;
+    };
+    pc = fetch_chunk();
 #pragma unroll
-    for (int k = 0; k < kRing - 1; ++k) issue_batch();
+    for (int k = 0; k < kAhead; ++k) issue_batch();
+#endif
 
     for (;;) {
         const int64_t c_cur = (int64_t)sh.fifo[fifo_r & 3];
@@ -599,19 +715,29 @@ nearest_hit_walk_kernel(WalkParams p) {
             while (list_n < 32 && next < chunk_n) {
                 int j = next + lane;
                 bool valid = j < chunk_n;
-                next += 32;
+#if TRC_WALK_TMA
+                if ((next & (kBatch - 1)) == 0) {
+                    // a new batch: start the copy of the one after it, then wait for this one to have landed
+                    __syncwarp();
+                    issue_batch();
+                    mbar_wait(smem_u32(&sh.mbar[ring_r & (kRing - 1)]), (unsigned)(ring_r / kRing) & 1u);
+                    ++ring_r;
+                }
+#else
                 issue_batch();
-                asm volatile("cp.async.wait_group %0;" ::"n"(kRing - 1) : "memory");
+                asm volatile("cp.async.wait_group 2;" ::: "memory");
+                ++ring_r;
+#endif
                 RayF nr;
                 unsigned nsigns = 0u;
                 bool surv = false;
                 if (valid) {
-                    const double *src = &sh.ring[ring_r % kRing][0][lane];   // this lane's own copies
-                    V3 v = mk(src[0], src[32], src[64]);
-                    V3 d = mk(src[96], src[128], src[160]);
+                    const double *src = &sh.ring[(ring_r - 1) & (kRing - 1)][0][(next & (kBatch - 1)) + lane];
+                    V3 v = mk(src[0], src[kBatch], src[2 * kBatch]);
+                    V3 d = mk(src[3 * kBatch], src[4 * kBatch], src[5 * kBatch]);
                     surv = ray_setup(v, d, p, nr, nsigns) && root_count != 7 && !(p.debug & 2);
                 }
-                ++ring_r;
+                next += 32;
                 unsigned m = __ballot_sync(full, surv);
                 if (root_count > 0) {
                     // the whole tree is one leaf: its surfaces are candidates of every surviving ray
@@ -730,7 +856,9 @@ nearest_hit_walk_kernel(WalkParams p) {
         if (p.sink.records) emit_chunk_hits(sh, p, c_cur, chunk_base, lane);
         __syncwarp();
     }
+#if !TRC_WALK_TMA
     asm volatile("cp.async.wait_all;" ::: "memory");
+#endif
 }
 
 }  // namespace

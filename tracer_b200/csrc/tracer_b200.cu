@@ -64,9 +64,13 @@ extern "C" int trc_scene_create(const TrcSurfaceRec *surfaces, int32_t n_surface
         e = cudaMalloc(&sc->d_tables, sizeof(double) * (size_t)n_table);
         if (e == cudaSuccess) e = cudaMemcpy(sc->d_tables, tables, sizeof(double) * (size_t)n_table, cudaMemcpyHostToDevice);
     }
-    for (int32_t i = 0; i < n_surfaces; ++i)
-        if (surfaces[i].gkind == TRC_G_TRIANGLE) ++sc->n_triangles;
-    if (e == cudaSuccess && sc->flat_only && sc->n_triangles > 0 && !getenv("TRC_NO_TRI_PREFILTER")) {
+    int32_t n_prefilter = 0;           // surfaces the walk can pre-test in float32: triangles, rect and round plates
+    for (int32_t i = 0; i < n_surfaces; ++i) {
+        const int k = surfaces[i].gkind;
+        if (k == TRC_G_TRIANGLE) ++sc->n_triangles;
+        if (k == TRC_G_TRIANGLE || k == TRC_G_RECT_PLATE || k == TRC_G_RECT_EXTRUDED || k == TRC_G_ROUND_PLATE) ++n_prefilter;
+    }
+    if (e == cudaSuccess && sc->flat_only && n_prefilter > 0 && !getenv("TRC_NO_TRI_PREFILTER")) {
         e = cudaMalloc(&sc->d_tri32, sizeof(float4) * 3 * (size_t)n_surfaces);
         if (e == cudaSuccess) e = build_tri32(sc);
     }
@@ -105,9 +109,13 @@ extern "C" int trc_scene_destroy(TrcScene *sc) {
 
 extern "C" int32_t trc_scene_num_surfaces(const TrcScene *sc) { return sc ? sc->n_surfaces : 0; }
 
-// Float32 copy of every triangle for the tree walk's pre-test (nearest.cu, tri_prefilter):
-// [p0.x p0.y p0.z e0.x] [e0.y e0.z e1.x e1.y] [e1.z flag - -], p0 = frame origin, e = R * verts
-// (triangular_face.py:60-61), flag = 1 for a triangle, 0 for any other kind (never pre-tested).
+// Float32 copy of every triangle / plate for the tree walk's pre-test (nearest.cu, tri_prefilter):
+// [p0.x p0.y p0.z e0.x] [e0.y e0.z e1.x e1.y] [e1.z flag - -], p0 = frame origin.
+//   flag 1: triangle p0 + u e0 + v e1, u, v >= 0, u + v <= 1, e = R * verts (triangular_face.py:60-61);
+//   flag 2: centred parallelogram |u|, |v| <= 1 -- a rect plate (e = half sides along the frame's x, y;
+//           flat_surface.py:202-211; the hole of an extruded plate is left to the float64 test) or the
+//           bounding square of a round plate (e = Re along x, y; :484-492);
+//   flag 0: any other kind (never pre-tested).
 __global__ void build_tri32_kernel(const TrcSurfaceRec *s, float4 *out, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -122,6 +130,11 @@ __global__ void build_tri32_kernel(const TrcSurfaceRec *s, float4 *out, int n) {
         a = make_float4((float)f[3], (float)f[7], (float)f[11], (float)e0[0]);
         b = make_float4((float)e0[1], (float)e0[2], (float)e1[0], (float)e1[1]);
         c = make_float4((float)e1[2], 1.f, 0.f, 0.f);
+    } else if (s[i].gkind == TRC_G_RECT_PLATE || s[i].gkind == TRC_G_RECT_EXTRUDED || s[i].gkind == TRC_G_ROUND_PLATE) {
+        const double hx = gp[0], hy = s[i].gkind == TRC_G_ROUND_PLATE ? gp[0] : gp[1];
+        a = make_float4((float)f[3], (float)f[7], (float)f[11], (float)(f[0] * hx));
+        b = make_float4((float)(f[4] * hx), (float)(f[8] * hx), (float)(f[1] * hy), (float)(f[5] * hy));
+        c = make_float4((float)(f[9] * hy), 2.f, 0.f, 0.f);
     }
     out[3 * (size_t)i] = a; out[3 * (size_t)i + 1] = b; out[3 * (size_t)i + 2] = c;
 }
