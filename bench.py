@@ -1,19 +1,23 @@
 """bench.py -- ray-bounces/s of the NSTTF heliostat-field trace (BASELINE.json).
 
-A step = one ``TracerEngine.ray_tracer`` pass (reps=3, tree=True) over one
-synthetic Buie-sunshape bundle aimed at the 218-heliostat Sandia NSTTF field +
-tower receiver, followed by on-device flux-map binning
-of the receiver hits and (N>1) the NCCL all-reduce of the tallies.  Weak
-scaling: every GPU traces its own ``--rays`` bundle (default 1e8).
+A step = one ``TracerEngine.ray_tracer`` pass (reps=3, tree=True) over one synthetic Buie-sunshape bundle aimed
+at the 218-heliostat Sandia NSTTF field + tower receiver, followed by on-device
+flux-map binning of the receiver hits and (N>1) the NCCL all-reduce of the tallies.
 
-  value   : device-resident bundle, CUDA-event timed, max over ranks
-  e2e     : same step through the public API with a HOST bundle in pinned
-            memory (H2D inside the timed region) and the flux map read back
-  roofline: dominant kernel (nearest-hit BVH walk over the source bundle) timed
-            by CUDA events around its launch inside the timed region;
-            algorithmic bytes = 48 B/ray + 72 B/hit
-  cpu_baseline / --impl reference: the NumPy oracle port of the reference
-            engine on the host cores, bounded sample of the same workload
+The metric's own configuration is ONE source of 1e8 rays sharded over the N GPUs (BASELINE.json configs[2],
+the reference's ``.../procs`` scheme: tracer_engine_mp.py:19-35, sources.py:238), so the headline is
+strong scaling: every rank traces 1e8 / N rays of the same source (global Philox ray ids).
+
+  value    : device-resident shards, CUDA-event timed, max over ranks, aggregate ray-bounces/s
+  e2e      : same step through the public API with HOST bundles in pinned memory (H2D inside the timed
+             region) and the flux map read back; next to it the bare concurrent H2D rate of the same bytes
+  roofline : dominant kernel (nearest-hit BVH walk over the source shard) timed by CUDA events around its
+             launch inside the timed region; algorithmic bytes = 48 B/ray + 72 B/hit; DRAM traffic
+             and instructions per ray from the committed ncu capture when it matches the kernel source
+  weak     : (N>1) every rank traces its own 1e8 rays -- the round-1 line, kept for comparison
+  configs  : (N=1) short device-timed rates of the other BASELINE configurations (C1, C2, C3-dense, C4, C5)
+  cpu_baseline / --impl reference: the NumPy oracle port of the reference engine on the host cores,
+             bounded sample of the same workload
 """
 import os
 os.environ.setdefault("OMP_NUM_THREADS", "1")       # CPU baseline: one BLAS thread per process
@@ -21,7 +25,6 @@ os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")
 import argparse
 import json
 import multiprocessing as mp
-import os
 import subprocess
 import sys
 import threading
@@ -34,7 +37,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-from tests import scenes  # noqa: E402  (scene builders only; no oracle import here)
+from tracer_b200.models import scenes  # noqa: E402  (scene builders; no oracle import here)
 
 METRIC = "ray-bounces/sec, NSTTF field 1e8 rays"
 UNIT = "ray-bounces/s"
@@ -43,7 +46,7 @@ FLUX_RES = 50
 FLUX_CMP_RES = 10                       # bins per side of the flux-map comparison with the CPU reference
 ALGO_BYTES_PER_RAY_HIT_KERNEL = 48      # vertex + direction read once per ray
 ALGO_BYTES_PER_HIT_HIT_KERNEL = 72      # per hit: 8 B energy read + 64 B hit record written
-TRAFFIC_BYTES_PER_RAY_NCU = 57.8        # (dram read + write) / rays of the ncu --set full capture in profiles/
+WORKLOAD = "C3 NSTTF heliostat field (218 heliostats + receiver), Buie CSR 0.01, reps=3"
 
 
 class ClockSampler(object):
@@ -173,10 +176,9 @@ def run_reference(args, rank):
     sample = "%d processes x %d rays of the NSTTF scene (219 surfaces), reps=%d" % (procs, rays, REPS)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "impl": "reference",
-        "config": {"workload": "C3 NSTTF heliostat field (218 heliostats + receiver), Buie CSR 0.01, reps=3",
-                   "rays_per_step": procs * rays, "surfaces": 219},
+        "config": {"workload": WORKLOAD, "rays_per_step": procs * rays, "surfaces": 219},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -190,12 +192,14 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--rays", type=float, default=1e8, help="rays per GPU per step")
+    ap.add_argument("--rays", type=float, default=1e8, help="rays of the whole source per step (sharded over the GPUs)")
     ap.add_argument("--cpu-rays", type=float, default=2e5, help="rays per host process for the CPU baseline")
     ap.add_argument("--accel", default="bvh", choices=["bvh", "brute"])
     ap.add_argument("--leaf-size", type=int, default=1)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-configs", action="store_true")
+    ap.add_argument("--no-weak", action="store_true")
     args = ap.parse_args()
     args.rays, args.cpu_rays = int(args.rays), int(args.cpu_rays)
     rank = int(os.environ.get("RANK", "0"))

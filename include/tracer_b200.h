@@ -522,6 +522,11 @@ int trc_fluxmap_binned(int32_t coord, int64_t n, const double *d_hits, int64_t l
 int trc_segment_sums(int64_t h, const int32_t *d_sorted_keys, const double *d_values,
                      double *d_totals, void *stream);
 
+/* Measurement aid, not part of the path: sustained FMA rate of the float32 (fp64 = 0) or float64 (fp64 = 1)
+ * pipe of the current device in TFLOP/s (2 flop per FMA) -- the roofline denominator SURVEY.md 8(d) asks the
+ * builder to measure for the brute-force nearest-hit kernel.  Synchronous. */
+int trc_fma_peak(int32_t fp64, double *tflops);
+
 #ifdef __cplusplus
 }
 #endif

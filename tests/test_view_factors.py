@@ -95,6 +95,35 @@ def test_closed_cylinder_view_factors():
     assert (sd <= 0.005 + 1e-12).all()
 
 
+@pytest.mark.gpu
+def test_holman_cavity_view_factors():
+    """BASELINE config 5's only reference-held vector: the 5x5 matrix of Holman's example 8.17
+    (emissive_losses/emissive_losses_test.py:37-44; geometry view_factors_3D.py:359-475: aperture disc, three
+    FiniteCylinder bands, back disc).  The textbook prints 2-3 digits (its rows deviate from the closed forms
+    by up to 0.0154), so the trace is held to the closed forms within Monte-Carlo error (4 binomial standard
+    errors per entry) and to the textbook matrix within the textbook's precision."""
+    from tracer_b200.view_factors import AssemblyRTVF
+    asm, elems, areas, emit = scenes.c5_holman(T)
+    state = {'k': 0}
+
+    def em(i, n):
+        state['k'] += 1
+        return emit(i, n, seed=state['k'])
+    vf = AssemblyRTVF(asm, elems, areas, em, num_rays=100000, precision=0.005, seed=3)
+    F, sd = vf.run(max_passes=40)
+    exact, ex_areas = scenes.holman_exact()
+    np.testing.assert_allclose(areas, ex_areas)
+    assert vf.passes >= 2 and not vf.progress.any()
+    # every entry is a binomial proportion of the rays its row cast (the reference's own interval, `sd`, measures
+    # the spread between passes and is far narrower after two equal passes, so it is not the yardstick here)
+    sigma = np.sqrt(exact * (1. - exact) / np.vstack(vf.p))
+    assert (np.abs(F - exact) <= 4. * sigma + 1e-12).all(), (F, exact, sigma)
+    assert np.abs(F - scenes.HOLMAN_VF).max() < 0.02, F
+    assert np.abs(F.sum(axis=1) - 1.).max() < 0.005
+    AF = F * np.vstack(areas)
+    assert np.abs(AF - AF.T).max() < 0.005 * areas.max()
+
+
 def _cylinder_vf(r=1., h=2.):
     R = r / h
     X = 1. + (1. + R ** 2) / R ** 2

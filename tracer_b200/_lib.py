@@ -153,6 +153,7 @@ SIGNATURES = {
     "trc_trace_walk_ms": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "trc_fluxmap_binned": (C.c_int, [_I32, _I64, _P, _I64, _P, _DP, _D, _P, _I32, _P, _I32, _P, _P]),
     "trc_segment_sums": (C.c_int, [_I64, _P, _P, _P, _P]),
+    "trc_fma_peak": (C.c_int, [_I32, C.POINTER(C.c_double)]),
 }
 
 

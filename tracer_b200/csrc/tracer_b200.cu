@@ -301,3 +301,50 @@ extern "C" int trc_scene_set_bvh(TrcScene *sc, const TrcBvhNode *nodes, int32_t 
     return TRC_OK;
 }
 
+
+// ------------------------------------------------------------ pipe peaks
+// FMA micro-benchmark (MEASURED_PEAKS.json has no scalar-pipe figure): every thread runs eight
+// independent chains of dependent fused multiply-adds; returns the sustained rate in TFLOP/s (2 flop per FMA).
+template <typename T>
+__global__ void __launch_bounds__(256)
+fma_peak_kernel(T *out, int iters, T a, T b) {
+    T x0 = (T)threadIdx.x, x1 = x0 + (T)1, x2 = x0 + (T)2, x3 = x0 + (T)3;
+    T x4 = x0 + (T)4, x5 = x0 + (T)5, x6 = x0 + (T)6, x7 = x0 + (T)7;
+#pragma unroll 4
+    for (int i = 0; i < iters; ++i) {
+        x0 = x0 * a + b; x1 = x1 * a + b; x2 = x2 * a + b; x3 = x3 * a + b;
+        x4 = x4 * a + b; x5 = x5 * a + b; x6 = x6 * a + b; x7 = x7 * a + b;
+    }
+    T s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+    if (s == (T)123456789) out[0] = s;          // never true in practice: keeps the chains alive
+}
+
+extern "C" int trc_fma_peak(int32_t fp64, double *tflops) {
+    if (!tflops) return fail(TRC_ERR_BAD_ARGUMENT, "trc_fma_peak: bad argument%s");
+    int dev = 0, sms = 0;
+    TRC_CUDA(cudaGetDevice(&dev));
+    TRC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    void *out = nullptr;
+    TRC_CUDA(cudaMalloc(&out, 64));
+    cudaEvent_t e0, e1;
+    TRC_CUDA(cudaEventCreate(&e0));
+    TRC_CUDA(cudaEventCreate(&e1));
+    const int blocks = sms * 8, iters = fp64 ? 1 << 14 : 1 << 16;
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {           // first repetition warms up
+        cudaEventRecord(e0);
+        if (fp64) fma_peak_kernel<double><<<blocks, 256>>>((double *)out, iters, 1.0000001, 1e-9);
+        else fma_peak_kernel<float><<<blocks, 256>>>((float *)out, iters, 1.0000001f, 1e-9f);
+        cudaEventRecord(e1);
+        cudaError_t e = cudaEventSynchronize(e1);
+        if (e != cudaSuccess) { cudaFree(out); return fail(TRC_ERR_CUDA, "trc_fma_peak: %s", cudaGetErrorString(e)); }
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (rep > 0 && ms < best) best = ms;
+    }
+    trc_note_launches(4);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out);
+    const double flop = 2.0 * 8.0 * (double)iters * 256.0 * (double)blocks;
+    *tflops = flop / ((double)best * 1e-3) / 1e12;
+    return TRC_OK;
+}

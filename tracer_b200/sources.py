@@ -122,6 +122,18 @@ def oblique_solar_rect_bundle(num_rays, center, source_direction, rays_direction
     return rayb
 
 
+def _rotz_each(phi, v, then=None):
+    """rotz(phi[t])[:3, :3] applied to column t of ``v`` for every t at once (the reference loops over the
+    rays, sources.py:676-678, 741-743): batched 3x3 products, bit-identical to the per-ray numpy.dot.
+    ``then``: a fixed 3x3 matrix folded in first as (rotz . then) . v, the association of vf_cylinder_bundle."""
+    c, s = np.cos(phi), np.sin(phi)
+    R = np.zeros((len(phi), 3, 3))
+    R[:, 0, 0], R[:, 0, 1], R[:, 1, 0], R[:, 1, 1], R[:, 2, 2] = c, -s, s, c, 1.
+    if then is not None:
+        R = np.matmul(R, then)
+    return np.matmul(R, v.T[:, :, None])[:, :, 0].T
+
+
 def vf_frustum_bundle(num_rays, r0, r1, depth, center, direction, flux=None, rays_in=True,
                       angular_span=[0., 2. * np.pi], angular_range=np.pi / 2.):
     """Lambertian emission from the lateral surface of a conical frustum, for view-factor
@@ -136,9 +148,7 @@ def vf_frustum_bundle(num_rays, r0, r1, depth, center, direction, flux=None, ray
     phi_s = np.random.uniform(low=angular_span[0], high=angular_span[1], size=num_rays)
     xs, ys = rs * np.cos(phi_s), rs * np.sin(phi_s)
     yrot = roty(-np.pi / 2. + np.arctan(c))[:3, :3]
-    local_unit = np.zeros(np.shape(dir_flat))
-    for t in range(num_rays):
-        local_unit[:, t] = np.dot(rotz(phi_s[t])[:3, :3], np.dot(yrot, dir_flat[:, t]))
+    local_unit = _rotz_each(phi_s, np.dot(yrot, dir_flat))
     if rays_in == False:  # noqa: E712 (reference spelling)
         local_unit = -1. * local_unit
     perp_rot = rotation_to_z(direction)
@@ -163,9 +173,7 @@ def vf_cylinder_bundle(num_rays, rc, lc, center, direction, flux=None, rays_in=T
     xs, ys = rc * np.cos(phi_s), rc * np.sin(phi_s)
     dir_flat = pillbox_sunshape_directions(num_rays, ang_range)
     yrot = roty(-np.pi / 2.)[:3, :3]
-    local_unit = np.zeros(np.shape(dir_flat))
-    for t in range(num_rays):
-        local_unit[:, t] = np.dot(np.dot(rotz(phi_s[t])[:3, :3], yrot), dir_flat[:, t])
+    local_unit = _rotz_each(phi_s, dir_flat, then=yrot)
     if rays_in == False:  # noqa: E712
         local_unit = -local_unit
     perp_rot = rotation_to_z(direction)
