@@ -223,6 +223,20 @@ int trc_sort_pairs(int64_t n, int32_t n_keys,
                    int32_t *d_keys_out, int32_t *d_vals_out,
                    int64_t *d_count, void *d_work, void *stream);
 
+/* trc_sort_pairs without a caller-provided work buffer and without any allocation: the work area is a
+ * file-scope device array of the library (about 2 MB, held by every GPU that loads the library until exit).
+ * No counterpart in the reference; added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same results as
+ * trc_sort_pairs.  Limits: n <= TRC_SORT_STATIC_MAX_PAIRS, n_keys <= TRC_SORT_STATIC_MAX_KEYS, otherwise
+ * TRC_ERR_CAPACITY.  All calls share the array: calls that overlap on the GPU race; the array keeps the last
+ * call's contents (harmless: every cell is written before it is read). */
+#define TRC_SORT_STATIC_MAX_PAIRS 4194304
+#define TRC_SORT_STATIC_MAX_KEYS 256
+int trc_sort_pairs_static(int64_t n, int32_t n_keys,
+                          const int32_t *d_keys_in, const int32_t *d_vals_in,
+                          int32_t *d_keys_out, int32_t *d_vals_out,
+                          int64_t *d_count, void *stream);
+
 /* Segment offsets of a sorted key array holding *d_count (<= n_max) entries:
  * d_offsets[k] = first position whose key >= k, for k in [0, n_keys]; i.e.
  * surface k owns slots [off[k], off[k+1]).  This is what the optics loop's

@@ -136,6 +136,7 @@ SIGNATURES = {
     "trc_order_hits": (C.c_int, [_I64, _P, _P, _P, _I64, _I32, _P, _P, _P, _P, _P]),
     "trc_sort_work_bytes": (_I64, [_I64, _I32]),
     "trc_sort_pairs": (C.c_int, [_I64, _I32, _P, _P, _P, _P, _P, _P, _P]),
+    "trc_sort_pairs_static": (C.c_int, [_I64, _I32, _P, _P, _P, _P, _P, _P]),
     "trc_segment_offsets_dyn": (C.c_int, [_P, _I64, _I32, _P, _P, _P]),
     "trc_optics": (C.c_int, [_P, C.POINTER(OpticsArgs), _P]),
     "trc_gather_rows": (C.c_int, [_I64, _P, _I32, _P, _I64, _P, _I64, _P, _P, _P]),

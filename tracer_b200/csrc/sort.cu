@@ -398,3 +398,40 @@ extern "C" int trc_order_hits(int64_t n_chunks, const uint32_t *d_chunk_off, con
     if (rc != TRC_OK) return rc;
     return trc_segment_offsets_dyn(count, h, n_keys, d_slot_surf, d_offsets, stream);
 }
+
+// ------------------------------------------------------- allocation-free variant
+// trc_sort_pairs for callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc): the work area is a file-scope device array instead of a caller-provided buffer.  No counterpart in
+// the reference.  Limits: n <= TRC_SORT_STATIC_MAX_PAIRS and
+// n_keys <= TRC_SORT_STATIC_MAX_KEYS (one radix pass, so no ping-pong pair arrays are needed).  Every GPU that
+// loads the library holds the array (about 2 MB) until exit.  All calls share it: calls that overlap on the GPU
+// (different streams, or different host threads) race.  Nothing in it has to start at zero -- the histogram
+// kernel writes every (bin, tile) cell, empty tiles included, and the scan kernels write every block sum before
+// it is read -- so the contents a previous call left behind are harmless.
+namespace {
+constexpr size_t kStaticScratchBytes = 2u * 1024u * 1024u + 4096u;
+constexpr int kStaticMaxDevices = 64;
+}  // namespace
+static __device__ __align__(256) unsigned char g_sort_static_scratch[kStaticScratchBytes];
+static void *g_sort_static_ptr[kStaticMaxDevices];      // device address of the array, per device (host code must
+                                                         // not pass the symbol itself: it is a host-side stand-in)
+
+extern "C" int trc_sort_pairs_static(int64_t n, int32_t n_keys, const int32_t *d_keys_in, const int32_t *d_vals_in,
+                                     int32_t *d_keys_out, int32_t *d_vals_out, int64_t *d_count, void *stream) {
+    if (n < 0 || n_keys < 1) return fail(TRC_ERR_BAD_ARGUMENT, "trc_sort_pairs_static: bad argument%s");
+    if (n > TRC_SORT_STATIC_MAX_PAIRS)
+        return fail(TRC_ERR_CAPACITY, "trc_sort_pairs_static: more than TRC_SORT_STATIC_MAX_PAIRS (4194304) pairs; use trc_sort_pairs%s");
+    if (n_keys > TRC_SORT_STATIC_MAX_KEYS)
+        return fail(TRC_ERR_CAPACITY, "trc_sort_pairs_static: more than TRC_SORT_STATIC_MAX_KEYS (256) keys; use trc_sort_pairs%s");
+    if (layout(n > 0 ? n : 1, n_keys).total > kStaticScratchBytes)
+        return fail(TRC_ERR_CAPACITY, "trc_sort_pairs_static: work area larger than the static scratch%s");
+    int dev = 0;
+    TRC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kStaticMaxDevices) return fail(TRC_ERR_BAD_ARGUMENT, "trc_sort_pairs_static: device index out of range%s");
+    if (!g_sort_static_ptr[dev]) {          // set-up, once per device, with that device current
+        void *ptr = nullptr;
+        TRC_CUDA(cudaGetSymbolAddress(&ptr, g_sort_static_scratch));
+        g_sort_static_ptr[dev] = ptr;
+    }
+    return trc_sort_pairs(n, n_keys, d_keys_in, d_vals_in, d_keys_out, d_vals_out, d_count, g_sort_static_ptr[dev], stream);
+}
