@@ -304,6 +304,8 @@ struct CloseParams {
     int64_t capacity;
     uint32_t *cta_surv;
     int64_t *d_counts;
+    const int64_t *seg;
+    int n_seg;
 };
 __global__ void __launch_bounds__(1024)
 bounce_close_kernel(CloseParams p) {
@@ -317,6 +319,8 @@ bounce_close_kernel(CloseParams p) {
     const unsigned overflow = hraw > p.capacity ? 1u : 0u;
     const long long h = overflow ? 0 : hraw;
     const int64_t nb = (h + 255) / 256;
+    if (p.seg)                         // the slot offsets travel with the counts: one device-to-host copy per trace
+        for (int k = threadIdx.x; k < p.n_seg; k += 1024) p.d_counts[4 + k] = p.seg[k];
     unsigned long long t = 0;
     for (int64_t i = threadIdx.x; i < nb; i += 1024) t += p.cta_surv[i];
     for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
@@ -553,7 +557,7 @@ int trc_optics_dyn(const TrcScene *sc, const TrcOpticsArgs *a, const TrcOpticsDy
         CloseParams c;
         c.ctl = dyn->ctl; c.ctl_next = dyn->ctl_next; c.children = dyn->children;
         c.children_sorted = dyn->children_sorted; c.capacity = a->h; c.cta_surv = dyn->cta_surv;
-        c.d_counts = dyn->d_counts;
+        c.d_counts = dyn->d_counts; c.seg = dyn->seg; c.n_seg = dyn->n_seg;
         TRC_CUDA(launch_pdl(bounce_close_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, c));
         return check_launch("optics", 2);
     } else if (sc->has_refractive)

@@ -145,6 +145,8 @@ struct TrcOpticsDyn {
     uint32_t *cta_surv;
     double *absorbed_per_surface;
     int64_t *d_counts;
+    const int64_t *seg;            // nullable: per-surface slot offsets to append to d_counts (n_seg words)
+    int n_seg;
 };
 int trc_optics_dyn(const TrcScene *sc, const TrcOpticsArgs *a, const TrcOpticsDyn *dyn, void *stream);
 

@@ -339,9 +339,20 @@ int tiles_for(int64_t n_in_cap, int *chunks_per_tile) {
     int64_t n_chunks = (n_in_cap + TRC_HIT_CHUNK - 1) / TRC_HIT_CHUNK;
     if (n_chunks < 1) n_chunks = 1;
     int64_t g = (n_chunks + kTargetTiles - 1) / kTargetTiles;
-    if (g < 1) g = 1;
+    if (g < kOrderWarps) g = kOrderWarps;      // at least a chunk per warp: small bundles get few tiles (short scan)
     *chunks_per_tile = (int)g;
     return (int)((n_chunks + g - 1) / g);
+}
+
+// Words of the read-back per bounce: [rays in, hits, survivors, reorder] and, when asked for, seg -- gathered
+// next to the counts on the device (bounce_close) so that ONE copy brings everything back.  Scenes with many
+// surfaces (meshes) keep seg where it is and copy it separately.
+constexpr int kInlineSegMax = 4096;
+inline bool seg_inline(const TrcScene *sc, const TrcTraceArgs *a) {
+    return (a->flags & TRC_TRACE_SEG) && sc->n_surfaces + 1 <= kInlineSegMax;
+}
+inline int64_t counts_per_bounce(const TrcScene *sc, const TrcTraceArgs *a) {
+    return 4 + (seg_inline(sc, a) ? sc->n_surfaces + 1 : 0);
 }
 
 int validate(const TrcScene *sc, const TrcTraceArgs *a, const char *who) {
@@ -373,7 +384,7 @@ ScratchPlan scratch_plan(const TrcScene *sc, const TrcTraceArgs *a) {
     int64_t off = 0;
     auto take = [&](int64_t bytes) { int64_t r = off; off = up256(off + bytes); return r; };
     s.off_ctl = take((int64_t)sizeof(TrcBounceCtl) * (TRC_TRACE_MAX_BOUNCES + 1));
-    s.off_counts = take(8 * 4 * TRC_TRACE_MAX_BOUNCES);
+    s.off_counts = take(8 * counts_per_bounce(sc, a) * TRC_TRACE_MAX_BOUNCES);
     s.off_heff = take(8 * TRC_TRACE_MAX_BOUNCES);
     s.off_records = take(64 * cap_max);
     s.off_keys = take(4 * cap_max);
@@ -384,7 +395,8 @@ ScratchPlan scratch_plan(const TrcScene *sc, const TrcTraceArgs *a) {
     const bool multi = S > kMaxBins;
     s.off_alt_k = take(multi ? 4 * cap_max : 0);
     s.off_alt_v = take(multi ? 4 * cap_max : 0);
-    s.off_hist = take(4 * tiles * nbins);
+    (void)tiles;
+    s.off_hist = take(4 * (int64_t)kTargetTiles * nbins);      // tiles_for never exceeds kTargetTiles, but is not monotonic in n
     s.off_bin_off = take(8 * (nbins + 1));
     s.off_sort_work = take(multi ? trc_sort_work_bytes(cap_max, S) : 0);
     s.off_cull = take(4 * cap_max);
@@ -433,7 +445,7 @@ extern "C" int trc_trace_init(const TrcScene *sc, const TrcTraceArgs *a, void *s
     if (blocks > 1024) blocks = 1024;
     TRC_CUDA(launch_pdl(trace_init_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream,
                         (TrcBounceCtl *)(scr + s.off_ctl), TRC_TRACE_MAX_BOUNCES + 1, (long long)a->n, in0,
-                        (int64_t *)(scr + s.off_counts), 4 * TRC_TRACE_MAX_BOUNCES, a->d_absorbed_per_surface,
+                        (int64_t *)(scr + s.off_counts), (int)(counts_per_bounce(sc, a) * TRC_TRACE_MAX_BOUNCES), a->d_absorbed_per_surface,
                         a->d_hits_per_surface, n_tally));
     return check_launch("trace_init");
 }
@@ -456,6 +468,7 @@ extern "C" int trc_trace(const TrcScene *sc, const TrcTraceArgs *a, void *stream
     char *scr = (char *)a->d_scratch, *keep = (char *)a->d_keep;
     TrcBounceCtl *ctl = (TrcBounceCtl *)(scr + sp.off_ctl);
     int64_t *d_counts = (int64_t *)(scr + sp.off_counts);
+    const int64_t cpb = counts_per_bounce(sc, a);
     int64_t *d_heff = (int64_t *)(scr + sp.off_heff);
     TrcHitRecord *records = (TrcHitRecord *)(scr + sp.off_records);
     int32_t *keys = (int32_t *)(scr + sp.off_keys);
@@ -550,7 +563,9 @@ extern "C" int trc_trace(const TrcScene *sc, const TrcTraceArgs *a, void *stream
                               (const long long *)(keep + L.off_alt_ray_ids), 0, (long long)cap};
         od.cta_surv = (uint32_t *)(scr + sp.off_cta_surv);
         od.absorbed_per_surface = a->d_absorbed_per_surface;
-        od.d_counts = d_counts + 4 * j;
+        od.d_counts = d_counts + cpb * j;
+        od.seg = seg_inline(sc, a) ? seg : nullptr;
+        od.n_seg = S + 1;
         rc = trc_optics_dyn(sc, &o, &od, stream);
         if (rc != TRC_OK) return rc;
         // 5. survivors-first copy (acts only when some but not all children are weak)
@@ -569,11 +584,11 @@ extern "C" int trc_trace(const TrcScene *sc, const TrcTraceArgs *a, void *stream
     }
     // one read-back for the whole trace
     const int64_t per = 4 + ((a->flags & TRC_TRACE_SEG) ? S + 1 : 0);
-    if (per == 4) {
-        TRC_CUDA(cudaMemcpyAsync(a->h_counts, d_counts, sizeof(int64_t) * 4 * (size_t)a->n_bounces, cudaMemcpyDeviceToHost, st));
+    if (per == cpb) {
+        TRC_CUDA(cudaMemcpyAsync(a->h_counts, d_counts, sizeof(int64_t) * (size_t)(per * a->n_bounces), cudaMemcpyDeviceToHost, st));
     } else {
         for (int j = 0; j < a->n_bounces; ++j) {
-            TRC_CUDA(cudaMemcpyAsync(a->h_counts + per * j, d_counts + 4 * j, sizeof(int64_t) * 4, cudaMemcpyDeviceToHost, st));
+            TRC_CUDA(cudaMemcpyAsync(a->h_counts + per * j, d_counts + cpb * j, sizeof(int64_t) * 4, cudaMemcpyDeviceToHost, st));
             TRC_CUDA(cudaMemcpyAsync(a->h_counts + per * j + 4, keep + plan.bounce[j].off_seg,
                                      sizeof(int64_t) * (size_t)(S + 1), cudaMemcpyDeviceToHost, st));
         }
