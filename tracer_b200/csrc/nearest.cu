@@ -185,8 +185,13 @@ constexpr int kSmemPairs = TRC_WALK_SMEM_PAIRS;               // top of the tree
 constexpr unsigned kCandMask = 0x003fffffu;
 
 struct WalkWarpShared {
+#ifdef TRC_WALK_EXPERIMENT_NO_F64
+    unsigned long long best_t[1];
+    int best_s[2];
+#else
     unsigned long long best_t[kChunk];        // bits of the best float64 t (+inf = none)
     int best_s[kChunk];                       // its surface index (INT_MAX = none)
+#endif
     float list[kListFields][kListCap];        // SoA: lanes read consecutive entries conflict-free
     unsigned queue[kQueueCap];                // packed (slot, leaf)
     unsigned queue2[64];                      // candidates that passed the float32 triangle pre-test
@@ -480,6 +485,9 @@ __device__ __forceinline__ int prefilter_queue(WalkWarpShared &sh, const WalkPar
 template <bool kFlatOnly>
 __device__ __forceinline__ int flush_queue(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
                                            int qn, bool all) {
+#ifdef TRC_WALK_EXPERIMENT_NO_F64      // timing experiment only: what the walk costs without the float64 stage
+    if (kFlatOnly) return (qn >= 32 || all) ? 0 : qn;
+#endif
     if (kFlatOnly) {
         if (p.tri32) return prefilter_queue(sh, p, chunk_base, lane, qn, all);
         return flush_queue_body<true>(sh, sh.queue, p, chunk_base, lane, qn, all);
@@ -696,7 +704,9 @@ nearest_hit_walk_kernel(WalkParams p) {
         if (chunk_base >= S.n_rays) break;
         const int chunk_n = (int)min((int64_t)kChunk, (int64_t)S.n_rays - chunk_base);
 
+#ifndef TRC_WALK_EXPERIMENT_NO_F64
         for (int i = lane; i < kChunk; i += 32) { sh.best_t[i] = TRC_INF_BITS; sh.best_s[i] = INT_MAX; }
+#endif
         if (lane == 0) sh.q2n = 0;
         __syncwarp();
 
@@ -785,7 +795,11 @@ nearest_hit_walk_kernel(WalkParams p) {
                     set_selectors(r, (unsigned)word >> 8);
                     tag = (unsigned)slot << 24;
                     cur = 0; sp = 0;
+#ifdef TRC_WALK_EXPERIMENT_NO_F64
+                    tbest = TRC_FINF;
+#else
                     tbest = best_as_float(sh.best_t[slot]);
+#endif
                 }
                 list_n -= min(__popc(idle), list_n);
                 __syncwarp();
@@ -839,7 +853,9 @@ nearest_hit_walk_kernel(WalkParams p) {
                     pend0 = pend1 = kNoEntry;
                     if (qn >= 32) {
                         qn = flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, false);
+#ifndef TRC_WALK_EXPERIMENT_NO_F64
                         if (cur >= 0) tbest = best_as_float(sh.best_t[tag >> 24]);
+#endif
                     }
                 }
                 int n_active = __popc(__ballot_sync(full, cur >= 0));
@@ -851,8 +867,15 @@ nearest_hit_walk_kernel(WalkParams p) {
         __syncwarp();
         if (p.sink.hit_surf) {
             for (int i = lane; i < chunk_n; i += 32)
+#ifndef TRC_WALK_EXPERIMENT_NO_F64
                 p.sink.hit_surf[chunk_base + i] = sh.best_t[i] == TRC_INF_BITS ? -1 : sh.best_s[i];
+#else
+                p.sink.hit_surf[chunk_base + i] = -1;
+#endif
         }
+#ifdef TRC_WALK_EXPERIMENT_NO_F64
+        if (!kFlatOnly)
+#endif
         if (p.sink.records) emit_chunk_hits(sh, p, c_cur, chunk_base, lane);
         __syncwarp();
     }
