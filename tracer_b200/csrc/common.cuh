@@ -127,11 +127,13 @@ struct TrcScene {
     int32_t *d_cand = nullptr;         // leaf surfaces followed by unbounded surfaces (the walk's candidate list)
     int num_sms = 148;
     int device = 0;                    // CUDA device the tables live on
-    int walk_occ[4] = {0, 0, 0, 0};    // resident CTAs per SM of each tree-walk instantiation (cached query)
+    int walk_occ[6] = {0, 0, 0, 0, 0, 0};    // resident CTAs per SM of each tree-walk instantiation (cached query)
     bool flat_only = false;            // every surface is of the flat family (kinds <= TRC_G_TRIANGLE)
     float4 *d_tri32 = nullptr;         // float32 copies of the triangles (3 x float4 per surface) for the walk's
                                        // conservative pre-test; null unless the scene is flat-only and has triangles
     int32_t n_triangles = 0;
+    double *d_tri64 = nullptr;         // compact float64 triangle table (TRC_TRI_REC_DOUBLES per surface) for the walk's
+                                       // float64 stage; null unless the scene is flat-only and has triangles
     bool has_refractive = false;       // some surface is TRC_O_REFRACTIVE: the optics need the ref_index column
     bool has_split = false;
     int64_t *h_pinned = nullptr;       // page-locked host words for the count read-backs of trc_bounce: [hits, culled, seg(S+1)]

@@ -89,6 +89,39 @@ __device__ __forceinline__ double isect_flat(const TrcSurfaceRec *s, int kind, V
     return t;
 }
 
+// The terms of the triangle test that depend on the face only, written exactly as isect_flat's triangle branch
+// writes them (same expressions, hence the same fused multiply-adds): the tree walk of a mesh scene evaluates
+// them once per scene into a compact table (128 bytes per face instead of the 384-byte surface record).
+struct TriTerms { V3 e0, e1; double uv, n0, n1, den; };
+__device__ __forceinline__ TriTerms tri_terms(const double *f, const double *gp) {
+    TriTerms r;
+    r.e0 = rot_to_global(f, mk(gp[0], gp[1], gp[2]));
+    r.e1 = rot_to_global(f, mk(gp[3], gp[4], gp[5]));
+    r.uv = gp[0] * gp[3] + gp[1] * gp[4] + gp[2] * gp[5];
+    r.n0 = gp[0] * gp[0] + gp[1] * gp[1] + gp[2] * gp[2];
+    r.n1 = gp[3] * gp[3] + gp[4] * gp[4] + gp[5] * gp[5];
+    r.den = r.uv * r.uv - r.n0 * r.n1;
+    return r;
+}
+// One record of the compact table: [c(3) n(3) e0(3) e1(3) uv n0 n1 den]; den == 0 marks "not a triangle"
+// (the walk then reads the full surface record).
+#define TRC_TRI_REC_DOUBLES 16
+// isect_flat for a triangle given by its compact record: c = frame origin, n = frame z axis.
+__device__ __forceinline__ double isect_triangle(V3 c, V3 n, const TriTerms &tt, V3 v, V3 d) {
+    double dt = dot(d, n);
+    if (!(fabs(dt) > 1e-7)) return TRC_INF;
+    double vt = dot(n, mk(v.x - c.x, v.y - c.y, v.z - c.z));
+    double t = -vt / dt;
+    if (t < 1e-7) return TRC_INF;
+    V3 g = axpy(v, t, d);
+    V3 w = mk(g.x - c.x, g.y - c.y, g.z - c.z);
+    double r0 = dot(w, tt.e0), r1 = dot(w, tt.e1);
+    double b0 = (tt.uv * r1 - tt.n1 * r0) / tt.den;
+    double b1 = (tt.uv * r0 - tt.n0 * r1) / tt.den;
+    if (b0 < 0.0 || b1 < 0.0 || (b0 + b1) > 1.0) return TRC_INF;
+    return t;
+}
+
 // Circular perforations: the hit is void when strictly inside any hole
 // (flat_surface.py:372-373, polygon.py:155-158).  h = (cx, cy, r) triples.
 __device__ __forceinline__ bool in_a_hole(const double *h, int n, double lx, double ly) {

@@ -217,6 +217,7 @@ struct WalkParams {
     const TrcSurfaceRec *surfs;
     const double *pool;                       // scene table pool (apertures of the pool-based flat kinds)
     const float4 *tri32;                      // float32 triangles for the pre-test, or null (see tri_prefilter)
+    const double *tri64;                      // compact float64 triangle table (geom.cuh), or null
     const uint4 *pair_a, *pair_b;
     const uint4 *pair_ab;                     // interleaved copy for the walk outside the shared-memory cache
     int n_pairs;
@@ -350,7 +351,7 @@ __device__ __forceinline__ float best_as_float(unsigned long long bits) {
 
 // Stage C: test queued (slot, leaf) candidates in float64, 32 at a time, and
 // fold them into the per-slot best (t, surface).  `all` drains the queue.
-template <bool kFlatOnly>
+template <int kFlatOnly>     // 0 generic scene, 1 flat-family surfaces only, 2 the same with the compact triangle table
 __device__ __forceinline__ int flush_queue_body(WalkWarpShared &sh, const unsigned *queue, const WalkParams &p,
                                                 int64_t chunk_base, int lane, int qn, bool all) {
     __syncwarp();
@@ -377,7 +378,21 @@ __device__ __forceinline__ int flush_queue_body(WalkWarpShared &sh, const unsign
                 const TrcSurfaceRec *sr = &p.surfs[s];
                 double tk;
                 if (kFlatOnly) {              // scene of flat-family surfaces only: no quadric code, few registers
-                    tk = isect_flat(sr, sr->gkind, v, d);
+                    const double2 *tr = reinterpret_cast<const double2 *>(p.tri64 + (size_t)TRC_TRI_REC_DOUBLES * s);
+                    double2 h7;
+                    if (kFlatOnly == 2 && (h7 = __ldg(tr + 7)).y != 0.0) {
+                        // a triangle: one 128-byte line instead of the 384-byte surface record
+                        const double2 h0 = __ldg(tr), h1 = __ldg(tr + 1), h2 = __ldg(tr + 2), h3 = __ldg(tr + 3);
+                        const double2 h4 = __ldg(tr + 4), h5 = __ldg(tr + 5), h6 = __ldg(tr + 6);
+                        const double4 q0 = make_double4(h0.x, h0.y, h1.x, h1.y), q1 = make_double4(h2.x, h2.y, h3.x, h3.y);
+                        const double4 q2 = make_double4(h4.x, h4.y, h5.x, h5.y), q3 = make_double4(h6.x, h6.y, h7.x, h7.y);
+                        TriTerms tt;
+                        tt.e0 = mk(q1.z, q1.w, q2.x); tt.e1 = mk(q2.y, q2.z, q2.w);
+                        tt.uv = q3.x; tt.n0 = q3.y; tt.n1 = q3.z; tt.den = q3.w;
+                        tk = isect_triangle(mk(q0.x, q0.y, q0.z), mk(q0.w, q1.x, q1.y), tt, v, d);
+                    } else {
+                        tk = isect_flat(sr, sr->gkind, v, d);
+                    }
                     if (tk == 0.0) tk = TRC_INF;
                 } else {
                     tk = intersect(sr, v, d, p.pool);
@@ -449,6 +464,7 @@ __device__ __forceinline__ bool tri_prefilter(const float4 *tri, V3 v, V3 d) {
 
 // Flat-only scenes with triangles: queue entries first take the float32 pre-test, 32 at a time;
 // the few that pass wait in queue2 for the float64 stage.
+template <int kFlatOnly>
 __device__ __forceinline__ int prefilter_queue(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
                                                int qn, bool all) {
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -469,28 +485,28 @@ __device__ __forceinline__ int prefilter_queue(WalkWarpShared &sh, const WalkPar
             pass = tri_prefilter(p.tri32 + 3 * (size_t)(e & kCandMask), v, d);
         }
         if (q2n >= 32)                                           // leaves < 32: room for 32 more
-            q2n = flush_queue_body<true>(sh, sh.queue2, p, chunk_base, lane, q2n, false);
+            q2n = flush_queue_body<kFlatOnly>(sh, sh.queue2, p, chunk_base, lane, q2n, false);
         unsigned m = __ballot_sync(0xffffffffu, pass);
         if (pass) sh.queue2[q2n + __popc(m & lt_mask)] = e;
         q2n += __popc(m);
         __syncwarp();
         qn = base;
     }
-    if (q2n >= 32 || (all && q2n > 0)) q2n = flush_queue_body<true>(sh, sh.queue2, p, chunk_base, lane, q2n, all);
+    if (q2n >= 32 || (all && q2n > 0)) q2n = flush_queue_body<kFlatOnly>(sh, sh.queue2, p, chunk_base, lane, q2n, all);
     if (lane == 0) sh.q2n = q2n;
     __syncwarp();
     return qn;
 }
 
-template <bool kFlatOnly>
+template <int kFlatOnly>     // 0 generic scene, 1 flat-family surfaces only, 2 the same with the compact triangle table
 __device__ __forceinline__ int flush_queue(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
                                            int qn, bool all) {
 #ifdef TRC_WALK_EXPERIMENT_NO_F64      // timing experiment only: what the walk costs without the float64 stage
     if (kFlatOnly) return (qn >= 32 || all) ? 0 : qn;
 #endif
     if (kFlatOnly) {
-        if (p.tri32) return prefilter_queue(sh, p, chunk_base, lane, qn, all);
-        return flush_queue_body<true>(sh, sh.queue, p, chunk_base, lane, qn, all);
+        if (p.tri32) return prefilter_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, all);
+        return flush_queue_body<kFlatOnly>(sh, sh.queue, p, chunk_base, lane, qn, all);
     }
     return flush_queue_generic(sh, p, chunk_base, lane, qn, all);
 }
@@ -566,7 +582,7 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
 }
 
 // kAllShared: the whole tree fits the shared-memory cache (no global-memory path in the walk)
-template <bool kAllShared, bool kFlatOnly>
+template <bool kAllShared, int kFlatOnly>
 __global__ void __launch_bounds__(kWalkWarps * 32, kFlatOnly ? TRC_WALK_MIN_CTAS_FLAT : TRC_WALK_MIN_CTAS)
 nearest_hit_walk_kernel(WalkParams p) {
     extern __shared__ __align__(16) unsigned char walk_smem[];
@@ -909,8 +925,9 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     if ((sc->n_nodes == 0 && sc->n_unbounded == 0) || !sc->d_chunk_counter || !sc->d_cand)
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: use_bvh set but no BVH uploaded%s");
     typedef void (*WalkKernel)(WalkParams);
-    static const WalkKernel kernels[4] = {nearest_hit_walk_kernel<false, false>, nearest_hit_walk_kernel<true, false>,
-                                          nearest_hit_walk_kernel<false, true>, nearest_hit_walk_kernel<true, true>};
+    static const WalkKernel kernels[6] = {nearest_hit_walk_kernel<false, 0>, nearest_hit_walk_kernel<true, 0>,
+                                          nearest_hit_walk_kernel<false, 1>, nearest_hit_walk_kernel<true, 1>,
+                                          nearest_hit_walk_kernel<false, 2>, nearest_hit_walk_kernel<true, 2>};
     static int g_refill_at = -1;
     static bool attr_set[64] = {};       // cudaFuncSetAttribute is per device
     if (sc->device < 0 || sc->device >= 64) return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: device index out of range%s");
@@ -918,19 +935,21 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
         const char *env = getenv("TRC_WALK_REFILL_AT");      // tuning knob (0..31)
         g_refill_at = 24;
         if (env) { int v = atoi(env); if (v >= 0 && v < 32) g_refill_at = v; }
-        for (int k = 0; k < 4; ++k)
+        for (int k = 0; k < 6; ++k)
             TRC_CUDA(cudaFuncSetAttribute(kernels[k], cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)(sizeof(WalkShared) + 32 * kSmemPairs)));
         attr_set[sc->device] = true;
     }
-    int n_cached = sc->n_pairs < kSmemPairs ? sc->n_pairs : kSmemPairs;
+    // a tree that fits is cached whole; of a larger one only the top 256 pairs, so that two CTAs still fit an SM
+    int n_cached = sc->n_pairs <= kSmemPairs ? sc->n_pairs : kSmemPairs / 2;
     n_cached = (n_cached + 7) & ~7;
     const size_t smem = sizeof(WalkShared) + 32 * (size_t)n_cached;
-    const int variant = (sc->n_pairs <= kSmemPairs ? 1 : 0) | (sc->flat_only ? 2 : 0);
+    const int variant = (sc->n_pairs <= kSmemPairs ? 1 : 0) | (sc->flat_only ? (sc->d_tri64 ? 4 : 2) : 0);
     WalkParams p;
     p.surfs = sc->d_surfaces;
     p.pool = sc->d_tables;
     p.tri32 = sc->d_tri32;
+    p.tri64 = sc->d_tri64;
     p.pair_a = reinterpret_cast<const uint4 *>(sc->d_pair_a);
     p.pair_b = reinterpret_cast<const uint4 *>(sc->d_pair_b);
     p.pair_ab = reinterpret_cast<const uint4 *>(sc->d_pair_ab);

@@ -70,8 +70,11 @@ extern "C" int trc_scene_create(const TrcSurfaceRec *surfaces, int32_t n_surface
         if (k == TRC_G_TRIANGLE) ++sc->n_triangles;
         if (k == TRC_G_TRIANGLE || k == TRC_G_RECT_PLATE || k == TRC_G_RECT_EXTRUDED || k == TRC_G_ROUND_PLATE) ++n_prefilter;
     }
-    if (e == cudaSuccess && sc->flat_only && n_prefilter > 0 && !getenv("TRC_NO_TRI_PREFILTER")) {
-        e = cudaMalloc(&sc->d_tri32, sizeof(float4) * 3 * (size_t)n_surfaces);
+    if (e == cudaSuccess && sc->flat_only) {
+        if (n_prefilter > 0 && !getenv("TRC_NO_TRI_PREFILTER"))
+            e = cudaMalloc(&sc->d_tri32, sizeof(float4) * 3 * (size_t)n_surfaces);
+        if (e == cudaSuccess && sc->n_triangles > 0)      // the walk of a flat-only scene with triangles relies on it
+            e = cudaMalloc(&sc->d_tri64, sizeof(double) * TRC_TRI_REC_DOUBLES * (size_t)n_surfaces);
         if (e == cudaSuccess) e = build_tri32(sc);
     }
     if (e == cudaSuccess) e = cudaHostAlloc((void **)&sc->h_pinned, sizeof(int64_t) * (size_t)(n_surfaces + 3), cudaHostAllocDefault);
@@ -92,6 +95,7 @@ extern "C" int trc_scene_destroy(TrcScene *sc) {
     cudaFree(sc->d_surfaces);
     cudaFree(sc->d_tables);
     cudaFree(sc->d_tri32);
+    cudaFree(sc->d_tri64);
     cudaFree(sc->d_nodes);
     cudaFree(sc->d_pair_a);
     cudaFree(sc->d_pair_b);
@@ -116,10 +120,22 @@ extern "C" int32_t trc_scene_num_surfaces(const TrcScene *sc) { return sc ? sc->
 //           flat_surface.py:202-211; the hole of an extruded plate is left to the float64 test) or the
 //           bounding square of a round plate (e = Re along x, y; :484-492);
 //   flag 0: any other kind (never pre-tested).
-__global__ void build_tri32_kernel(const TrcSurfaceRec *s, float4 *out, int n) {
+__global__ void build_tri32_kernel(const TrcSurfaceRec *s, float4 *out, double *out64, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const double *f = s[i].frame, *gp = s[i].gp;
+    if (out64) {
+        double *o = out64 + (size_t)TRC_TRI_REC_DOUBLES * i;
+        if (s[i].gkind == TRC_G_TRIANGLE) {
+            TriTerms tt = tri_terms(f, gp);
+            o[0] = f[3]; o[1] = f[7]; o[2] = f[11]; o[3] = f[2]; o[4] = f[6]; o[5] = f[10];
+            o[6] = tt.e0.x; o[7] = tt.e0.y; o[8] = tt.e0.z; o[9] = tt.e1.x; o[10] = tt.e1.y; o[11] = tt.e1.z;
+            o[12] = tt.uv; o[13] = tt.n0; o[14] = tt.n1; o[15] = tt.den;
+        } else {
+            for (int k = 0; k < TRC_TRI_REC_DOUBLES; ++k) o[k] = 0.0;
+        }
+    }
+    if (!out) return;
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a, c = a;
     if (s[i].gkind == TRC_G_TRIANGLE) {
         double e0[3], e1[3];
@@ -140,8 +156,8 @@ __global__ void build_tri32_kernel(const TrcSurfaceRec *s, float4 *out, int n) {
 }
 
 static cudaError_t build_tri32(TrcScene *sc) {
-    if (!sc->d_tri32) return cudaSuccess;
-    build_tri32_kernel<<<(sc->n_surfaces + 255) / 256, 256>>>(sc->d_surfaces, sc->d_tri32, sc->n_surfaces);
+    if (!sc->d_tri32 && !sc->d_tri64) return cudaSuccess;
+    build_tri32_kernel<<<(sc->n_surfaces + 255) / 256, 256>>>(sc->d_surfaces, sc->d_tri32, sc->d_tri64, sc->n_surfaces);
     return cudaDeviceSynchronize();
 }
 

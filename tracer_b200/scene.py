@@ -552,6 +552,22 @@ class CompiledScene(object):
             leaf_surfs.ctypes.data_as(C.c_void_p) if len(leaf_surfs) else None, len(leaf_surfs),
             unb.ctypes.data_as(C.c_void_p) if len(unb) else None, len(unb)))
 
+    def seg_entries_needed(self, device):
+        """(host list, device index tensor) of the slot-offset entries the engine reads on the host after a
+        bounce: both ends of every mesh and of every surface with accountants."""
+        import torch
+        cached = getattr(self, '_seg_needed', None)
+        if cached is None or cached[1].device != device:
+            idx = set()
+            for i0, i1, _ in self.mesh_segments:
+                idx.update((i0, i1))
+            for s_ in self.account_list:
+                idx.update((int(s_), int(s_) + 1))
+            idx = sorted(idx)
+            cached = (idx, torch.tensor(idx, dtype=torch.int64, device=device))
+            self._seg_needed = cached
+        return cached
+
     @property
     def num_surfaces(self):
         return len(self.records)

@@ -49,6 +49,38 @@ class _LazyRows(object):
         return self._host if dtype is None else self._host.astype(dtype)
 
 
+class _DeviceSeg(object):
+    """Per-surface slot offsets of a bounce that stay in HBM (scenes with very many surfaces, e.g. a 1e6-face
+    mesh: 8 MB per bounce): the few entries the engine needs arrive with one small gather, the whole array is
+    only copied when somebody asks for it (``TriangleMeshObject.face_of_hits``)."""
+
+    def __init__(self, tensor, known=None):
+        self.t = tensor
+        self.known = known or {}
+        self._host = None
+
+    def __len__(self):
+        return int(self.t.shape[0]) if self._host is None else len(self._host)
+
+    def __array__(self, dtype=None, copy=None):
+        if self._host is None:
+            self._host = self.t.cpu().numpy()
+            self.t = None
+        return self._host if dtype is None else self._host.astype(dtype)
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            if self._host is not None:
+                return self._host[i]
+            return _DeviceSeg(self.t[i].clone())
+        if self._host is None and i in self.known:
+            return self.known[i]
+        return self.__array__()[i]
+
+
+INLINE_SEG_MAX = 4096          # scenes with more surfaces keep the slot offsets of a bounce on the device
+
+
 class _DevBundle(object):
     """Engine-internal view of a bundle living in HBM.  ``slices`` is set while a
     host bundle is still arriving: [(first ray, end ray, CUDA event of its copy)]."""
@@ -560,7 +592,8 @@ class TracerEngine(object):
         a.ray_id_base = cur.id_base
         a.use_bvh, a.first_bounce, a.n_bounces = (1 if use_bvh else 0), bounce, nb
         timed = self.kernel_events is not None and bounce == 0 and cur.slices is None
-        a.flags = (L.TRACE_SEG if scene.has_accountants else 0) | (L.TRACE_TIME_WALK if timed else 0)
+        seg_on_host = scene.has_accountants and S + 1 <= INLINE_SEG_MAX
+        a.flags = (L.TRACE_SEG if seg_on_host else 0) | (L.TRACE_TIME_WALK if timed else 0)
         if self._tallies_dirty:
             a.flags |= L.TRACE_ZERO_TALLIES     # the trace's first launch zeroes the per-surface tallies
             self._tallies_dirty = False
@@ -596,7 +629,7 @@ class TracerEngine(object):
             cur.slices = cur.keep = None       # resident from here on
         L.check(lib.trc_trace(scene.handle, C.byref(a), st))
         stream.synchronize()                    # the only synchronisation of the block
-        per = 4 + (S + 1 if scene.has_accountants else 0)
+        per = 4 + (S + 1 if seg_on_host else 0)
         host = counts[:nb * per].numpy()
         k64, ki64 = keep.view(torch.float64), keep.view(torch.int64)
         f64, i64 = k64, ki64
@@ -636,7 +669,13 @@ class TracerEngine(object):
                              E=view(lay.off_alt_energy, f64, 0), P=view(lay.off_alt_parents, i64, 0),
                              W=view(lay.off_alt_wavelengths, f64, 0), I=view(lay.off_alt_ray_ids, i64, 0))
             if scene.has_accountants:
-                seg = host[per * j + 4:per * (j + 1)]
+                if seg_on_host:
+                    seg = host[per * j + 4:per * (j + 1)]
+                else:
+                    seg_dev = torch.as_strided(ki64, (S + 1,), (1,), lay.off_seg >> 3)
+                    need = scene.seg_entries_needed(dev)
+                    vals = seg_dev.index_select(0, need[1]).cpu().tolist()
+                    seg = _DeviceSeg(seg_dev, dict(zip(need[0], vals)))
                 src = dict(hits=pre['V'], e_out=pre['E'], wavelengths=pre['W'])
                 for name, off, rows in (('absorbed', lay.off_absorbed, 0), ('normals', lay.off_normals, 3),
                                         ('e_in', lay.off_e_in, 0), ('dirs_in', lay.off_dirs_in, 3),
@@ -667,7 +706,10 @@ class TracerEngine(object):
                 continue
             if child_off is not None:
                 raise NotImplementedError("TriangleMeshObject in a scene with two-children optics")
-            mesh._add_chunk(np.array(seg[i0:i1 + 1], dtype=np.int64), {k: take(src[k][..., a:b]) for k in names})
+            part = seg[i0:i1 + 1]
+            if not isinstance(part, _DeviceSeg):
+                part = np.array(part, dtype=np.int64)
+            mesh._add_chunk(part, {k: take(src[k][..., a:b]) for k in names})
         for s in scene.account_list:
             orec = scene.optics[s]
             a, b = int(seg[s]), int(seg[s + 1])
