@@ -63,8 +63,10 @@ typedef enum TrcGeomKind {
     TRC_G_CYL_RECT = 20,       /* RectCutCylinder            cylinder.py:161      gp: R, half_h, hw, hh */
     TRC_G_QUADRIC_FLAT = 21,   /* FlatQuadricSurfaceGM       quadratic_surface.py:4   gp: a b c d e f */
     TRC_G_QUADRIC_RECT = 22,   /* RectFlatQuadricSurfaceGM   quadratic_surface.py:63  gp: a b c d e f hw hh */
-    TRC_G_SPHERE_CUT = 23,     /* CutSphereGM + BoundarySphere sphere_surface.py:168, boundary_shape.py:89-111
-                                  gp: r, cx, cy, cz (bound centre, global), R_bound */
+    TRC_G_SPHERE_CUT = 23,     /* CutSphereGM sphere_surface.py:168 bounded by a BoundarySphere (boundary_shape.py:89-111)
+                                  gp: r, cx, cy, cz (bound centre, global), R_bound, 0
+                                  or by a BoundaryPlane (:151-165) gp: r, a, b, c, d, 1 with (a, b, c, d) = row 2 of the
+                                  inverse of (surface frame . bound transform): valid where a x + b y + c z + d >= 0 */
     TRC_G_ELLIPSOID = 24,      /* EllipsoidGM                ellipsoid.py:5,63    gp: 1/a^2, 1/b^2, 1/c^2, xlo, xhi, ylo,
                                   yhi, zlo, zhi (-inf / +inf where there is no limit) */
     TRC_G_RECT_PERFORATED = 25,/* PerforatedRectPlateGM      flat_surface.py:357  gp: hx, hy, pool offset, n_holes;

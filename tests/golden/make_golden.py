@@ -106,6 +106,11 @@ def fluxmap_reference():
 def main():
     ref_import.enable()
     only = sys.argv[1:]          # optional: names of the trace cases to (re)generate, nothing else
+    if only == ['--zoo']:        # only the geometry zoo
+        z = zoo_reference()
+        np.savez_compressed(os.path.join(HERE, 'gm_zoo.npz'), **z)
+        print('gm_zoo', {k[:-7]: int(np.isfinite(v).sum()) for k, v in z.items() if k.endswith('_params')})
+        return
     for name in (only or TRACE_CASES):
         data = trace_reference(name)
         np.savez_compressed(os.path.join(HERE, name + '.npz'), **data)

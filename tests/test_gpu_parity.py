@@ -75,6 +75,27 @@ def test_geometry_kinds_against_oracle(name):
     assert np.array_equal(eng2.tree[1].get_parents(), hit)
 
 
+@pytest.mark.parametrize('name', ['hemisphere', 'cut_sphere', 'cut_sphere_plane', 'sphere_rect'])
+@pytest.mark.parametrize('accel', ['brute', 'bvh'])
+def test_sphere_family_against_reference_ray_by_ray(name, accel):
+    """CUDA path against the REAL reference for the sphere-family classes, on the behaviour the reference has
+    where its root selection is well defined: one ray at a time (tests/golden/sphere_family.npz)."""
+    from tests.golden.make_sphere_family import N_RAYS, SEED
+    gold = load_golden('sphere_family')
+    opt = T.optics_callables.ReflectiveNormalReceiver(0.1)
+    asm = scenes.zoo_scene(T, name, opt)
+    rays = scenes.zoo_rays(T, N_RAYS, SEED)
+    ref = gold[name + '_params'].copy()
+    ref[ref == 0.] = np.inf
+    hit = np.nonzero(np.isfinite(ref))[0]
+    eng = _engine(asm, device_accel=accel)
+    eng.ray_tracer(rays, reps=1, min_energy=-1., tree=True)
+    child = eng.tree[1]
+    assert np.array_equal(child.get_parents(), hit), 'hit/miss pattern differs from the reference'
+    close(child.get_vertices(), gold[name + '_points'], TIGHT, 'hit points')
+    close(opt.get_all_hits()[2], gold[name + '_normals'], TIGHT, 'normals')
+
+
 def test_culling_and_parent_bookkeeping():
     """Survivors first, culled rays at the back, parents index the previous record
     (tests/test_tracer_tree.py:106-153 of the reference)."""

@@ -1,2 +1,2 @@
 """Drop-in module name for the reference's tracer/boundary_shape.py; see scenegraph.py."""
-from .scenegraph import BoundaryShape, BoundaryBox, BoundarySphere  # noqa: F401
+from .scenegraph import BoundaryShape, BoundaryBox, BoundarySphere, BoundaryCylinder, BoundaryPlane  # noqa: F401

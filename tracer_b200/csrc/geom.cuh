@@ -203,6 +203,8 @@ __device__ __forceinline__ bool quadric_root_ok(const TrcSurfaceRec *s, int kind
     default: break;
     }
     if (kind == TRC_G_SPHERE_CUT) {
+        if (gp[5] != 0.0)      // BoundaryPlane.in_bounds (boundary_shape.py:151-165): gp[1..4] = row 2 of the inverse frame
+            return t > 1e-6 && (gp[1] * p.x + gp[2] * p.y + gp[3] * p.z + gp[4]) >= 0.0;
         // BoundarySphere.in_bounds (boundary_shape.py:104-111)
         double dx = p.x - gp[1], dy = p.y - gp[2], dz = p.z - gp[3];
         return t > 1e-6 && gp[4] * gp[4] >= dx * dx + dy * dy + dz * dz;

@@ -366,6 +366,8 @@ def gm_zoo(T):
         'sphere': (lambda: S.SphericalGM(0.8), tilt),
         'hemisphere': (lambda: S.HemisphereGM(0.8), tilt),
         'cut_sphere': (lambda: S.CutSphereGM(0.8, T.boundary_shape.BoundarySphere(radius=1.6, location=np.r_[0.1, -0.2, -1.1])), tilt),
+        'cut_sphere_plane': (lambda: S.CutSphereGM(0.8, T.boundary_shape.BoundaryPlane(
+            location=np.r_[0.05, 0., -0.2], rotation=sg.rotx(0.4)[:3, :3])), tilt),
         'sphere_rect': (lambda: S.SphericalRectFacet(0.8, 0.9, 0.7), tilt),
         'cone_inf': (lambda: C.InfiniteCone(0.5, 0.1), tilt),
         'cone': (lambda: C.FiniteCone(0.7, 1.2), tilt),

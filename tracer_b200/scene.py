@@ -118,14 +118,24 @@ def _geom_record(gm, surface):
             bound = gm._bound
             if bound is None:
                 return L.G_SPHERE, [r], box(r, r, -r, r)
-            if 'BoundarySphere' not in _mro_names(bound):
+            bnames = _mro_names(bound)
+            if 'BoundaryPlane' in bnames:
+                # CutSphereGM.find_intersections moves the bound into the surface's frame first (:184-186);
+                # in_bounds is inv(frame)[2] . [p; 1] >= 0 (boundary_shape.py:161-164)
+                row = np.linalg.inv(np.dot(np.asarray(surface._temp_frame, float), np.asarray(bound.get_transform(), float)))[2]
+                return L.G_SPHERE_CUT, [r] + list(row) + [1.], box(r, r, -r, r)
+            if 'BoundaryCylinder' in bnames:
+                raise NotImplementedError(
+                    "CutSphereGM bounded by a BoundaryCylinder: the reference itself raises ValueError there "
+                    "(boundary_shape.py:146-147 stacks a (3, 2) array on 3 ones), there is no behaviour to reproduce")
+            if 'BoundarySphere' not in bnames:
                 raise NotImplementedError(
                     f"CutSphereGM bounding volume {type(bound).__name__} is not supported on the GPU "
-                    "(only BoundarySphere)")
+                    "(BoundarySphere and BoundaryPlane are)")
             # BoundarySphere never moves its centre with the frame (boundary_shape.py:101)
             c = np.asarray(bound._temp_loc, float)[:3]
             rb = float(bound._radius)
-            return L.G_SPHERE_CUT, [r] + list(c) + [rb], ('global', c - rb, c + rb)
+            return L.G_SPHERE_CUT, [r] + list(c) + [rb, 0.], ('global', c - rb, c + rb)
         if name == 'SphericalGM':
             r = float(gm._rad)
             return L.G_SPHERE, [r], box(r, r, -r, r)

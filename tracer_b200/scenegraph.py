@@ -206,6 +206,29 @@ class BoundarySphere(BoundaryShape):
         return self._radius ** 2 >= ((bund_vertices - self._temp_loc[:3]) ** 2).sum(axis=1)
 
 
+class BoundaryCylinder(BoundaryShape):
+    """Infinite cylinder along the local z axis (boundary_shape.py:130-149).  Kept as the reference writes it:
+    ``in_bounds`` projects with the frame itself, and stacks ``vertices.T`` on ``vertices.shape[1]`` ones, which
+    only works for a (3, 3) argument -- CutSphereGM passes (2, 3) and the reference raises ValueError there, so
+    the GPU engine refuses a CutSphereGM bounded by a cylinder instead of inventing a behaviour."""
+
+    def __init__(self, diameter=1., location=None, rotation=None):
+        self._R = diameter / 2.
+        BoundaryShape.__init__(self, location, None)
+
+    def in_bounds(self, vertices):
+        local_xy = np.dot(self._temp_frame[:2], np.vstack((vertices.T, np.ones(vertices.shape[1]))))
+        return np.sum(local_xy ** 2, axis=0) <= self._R ** 2
+
+
+class BoundaryPlane(BoundaryShape):
+    """Half space on the positive local z side of the frame's xy plane (boundary_shape.py:151-165)."""
+
+    def in_bounds(self, vertices):
+        local_z = np.dot(np.linalg.inv(self._temp_frame)[2], np.vstack((vertices.T, np.ones(vertices.shape[0]))))
+        return local_z >= 0
+
+
 # Bumped by every structural change made through the API of any Assembly / AssembledObject;
 # get_surfaces() results are cached against it (a heliostat field is ~650 objects and the
 # engine asks for the surface list at the start of every trace).
