@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 12
+#define TRC_ABI_VERSION 13
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -198,13 +198,27 @@ int trc_bvh_build(const double *lo3, const double *hi3, int32_t n, int32_t leaf_
 int trc_scene_set_bvh(TrcScene *scene, const TrcBvhNode *nodes, int32_t n_nodes,
                       const int32_t *leaf_surfaces, int32_t n_leaf_surfaces,
                       const int32_t *unbounded, int32_t n_unbounded);
+/* Shadow grid for a directionally coherent bundle (every direction within `half_angle` radians of `direction`:
+ * the first bounce of a solar source, sources.py:88-117, 330-464).  The nearest-hit entry points called with
+ * use_bvh == 2 then find the candidates of such rays with one lookup in a plane grid of the surfaces' shadows
+ * instead of the tree walk (KdTree.traversal, accel_tree.py:213-312, is what both replace); rays outside the cone
+ * take the walk, and every candidate takes the same float64 test, so results do not change.  box_lo / box_hi:
+ * global AABBs (n_boxes x 3 float64) of the bounded surfaces, surface_ids their indices.  *enabled = 0 when no
+ * grid was made (cone too wide or grazing every axis, too many surfaces per cell, no shared memory to spare):
+ * use_bvh == 2 is then an ordinary walk.  A NULL direction or negative half_angle removes the grid.  Host-built;
+ * synchronises the device (call it between traces). */
+int trc_scene_set_shadow_grid(TrcScene *scene, int32_t n_boxes, const double *box_lo, const double *box_hi,
+                              const int32_t *surface_ids, const double *direction, double half_angle,
+                              int32_t *enabled);
 int trc_scene_destroy(TrcScene *scene);
 int32_t trc_scene_num_surfaces(const TrcScene *scene);
 
 /* Nearest hit across all surfaces for every ray.  Replaces
  * TracerEngine.intersect_ray (tracer_engine.py:27-64) together with every
  * GeometryManager.find_intersections it calls and,
- * when use_bvh != 0, KdTree.traversal (accel_tree.py:213-312).
+ * when use_bvh != 0, KdTree.traversal (accel_tree.py:213-312).  use_bvh: 0 = every surface for every ray,
+ * 1 = tree walk, 2 = tree walk with the scene's shadow grid for the rays it covers (trc_scene_set_shadow_grid;
+ * the same in trc_trace_hits, trc_trace_hits_slice and TrcTraceArgs, where 2 applies to the bundle passed in).
  * d_hit_surf[i] = index of the first surface hit by ray i (lowest index wins
  * ties, strict '<' at tracer_engine.py:59), or -1. */
 int trc_nearest_hit(const TrcScene *scene, int64_t n_rays,

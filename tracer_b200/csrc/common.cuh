@@ -101,6 +101,25 @@ struct TrcPairHalf { uint32_t w[4]; };
 #define TRC_CHILD_LEAF 0x80000000u
 #define TRC_CHILD_ENTRY_MASK 0x00ffffffu
 
+// Shadow grid of a directionally coherent bundle (built by trc_scene_set_shadow_grid, shadow_grid.cu; read by the
+// tree-walk kernel's stage A).  A ray whose slopes (d_a / d_n, d_b / d_n) lie in the slope box is keyed by the point
+// where it crosses the reference plane x_n = h0; the cell of that point lists every surface whose box the ray can
+// touch (the builder widened each shadow by the slope box and by the float32 rounding of the kernel's arithmetic),
+// so such a ray needs no tree walk.  Rays outside the slope box, too far out (|v| > rmax) or with d_n of the other
+// sign take the walk: the grid only prunes, results are those of the walk bit for bit.
+struct TrcShadowGrid {
+    const uint32_t *bits;          // one bit per cell: some surface's shadow covers it (copied to shared memory)
+    const uint32_t *cells;         // payload << 8 | count; count == 1: payload = the surface index, else list offset
+    const int32_t *list;           // surface indices of the cells with more than one candidate
+    int n_words;                   // 32-bit words of `bits`
+    int axis_n, axis_a, axis_b;
+    int nx, ny;
+    float h0, sgn;                 // reference plane, sign of d_n inside the slope box
+    float t0a, t0b, da, db;        // slope box centre and half widths
+    float ga0, gb0, inv_ca, inv_cb;   // grid origin and 1 / cell size
+    float rmax;
+};
+
 // Device-side scene tables; owned by the library (trc_scene_create/destroy).
 struct TrcScene {
     int32_t n_surfaces = 0;
@@ -127,7 +146,7 @@ struct TrcScene {
     int32_t *d_cand = nullptr;         // leaf surfaces followed by unbounded surfaces (the walk's candidate list)
     int num_sms = 148;
     int device = 0;                    // CUDA device the tables live on
-    int walk_occ[6] = {0, 0, 0, 0, 0, 0};    // resident CTAs per SM of each tree-walk instantiation (cached query)
+    int walk_occ[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};    // resident CTAs per SM of each tree-walk instantiation (cached query)
     bool flat_only = false;            // every surface is of the flat family (kinds <= TRC_G_TRIANGLE)
     float4 *d_tri32 = nullptr;         // float32 copies of the triangles (3 x float4 per surface) for the walk's
                                        // conservative pre-test; null unless the scene is flat-only and has triangles
@@ -136,6 +155,10 @@ struct TrcScene {
                                        // float64 stage; null unless the scene is flat-only and has triangles
     bool has_refractive = false;       // some surface is TRC_O_REFRACTIVE: the optics need the ref_index column
     bool has_split = false;
+    bool has_grid = false;             // a shadow grid is set (use_bvh == 2 routes coherent rays through it)
+    TrcShadowGrid grid = {};
+    uint32_t *d_grid_bits = nullptr, *d_grid_cells = nullptr;
+    int32_t *d_grid_list = nullptr;
     int64_t *h_pinned = nullptr;       // page-locked host words for the count read-backs of trc_bounce: [hits, culled, seg(S+1)]
     cudaEvent_t ev_walk[2] = {nullptr, nullptr};   // reusable event pair around the bounce-0 nearest-hit kernel (time_trace)
 };
@@ -151,6 +174,10 @@ struct TrcOpticsDyn {
     int n_seg;
 };
 int trc_optics_dyn(const TrcScene *sc, const TrcOpticsArgs *a, const TrcOpticsDyn *dyn, void *stream);
+
+// 32-bit words of shared memory the tree-walk kernel can spare for a shadow grid's occupancy bits (nearest.cu)
+int trc_walk_grid_word_budget(const TrcScene *sc);
+void trc_scene_free_shadow_grid(TrcScene *sc);
 
 // Nearest-hit launch of the device-driven trace (nearest.cu): the bundle (pointers and ray count), the work
 // counter and the hit total live in the control block; n_cap sizes the grid.

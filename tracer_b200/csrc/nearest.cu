@@ -27,6 +27,7 @@
 #include <stdint.h>
 #include <stdlib.h>
 
+#include <algorithm>
 #include "common.cuh"
 #include "geom.cuh"
 
@@ -180,6 +181,7 @@ constexpr int kListFields = 10;               // A[3], Bn[3], Bf[3], slot | dire
 #ifndef TRC_WALK_SMEM_PAIRS
 #define TRC_WALK_SMEM_PAIRS 512
 #endif
+constexpr int kGridMaxWords = 8192;           // occupancy bits of a shadow grid in shared memory: at most 32 KB
 constexpr int kSmemPairs = TRC_WALK_SMEM_PAIRS;               // top of the tree (breadth-first) cached per CTA: 16 KB
 // queue entry = slot << 24 | (count - 1) << 22 | first candidate-list index: one entry per leaf
 constexpr unsigned kCandMask = 0x003fffffu;
@@ -213,7 +215,10 @@ struct WalkShared {
     long long pad_;                           // here so that it costs no registers in the walk loop
 };
 
+typedef TrcShadowGrid GridParams;      // shadow grid of a directionally coherent bundle (common.cuh)
+
 struct WalkParams {
+    GridParams g;
     const TrcSurfaceRec *surfs;
     const double *pool;                       // scene table pool (apertures of the pool-based flat kinds)
     const float4 *tri32;                      // float32 triangles for the pre-test, or null (see tri_prefilter)
@@ -582,7 +587,7 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
 }
 
 // kAllShared: the whole tree fits the shared-memory cache (no global-memory path in the walk)
-template <bool kAllShared, int kFlatOnly>
+template <bool kAllShared, int kFlatOnly, bool kGrid>
 __global__ void __launch_bounds__(kWalkWarps * 32, kFlatOnly ? TRC_WALK_MIN_CTAS_FLAT : TRC_WALK_MIN_CTAS)
 nearest_hit_walk_kernel(WalkParams p) {
     extern __shared__ __align__(16) unsigned char walk_smem[];
@@ -601,6 +606,10 @@ nearest_hit_walk_kernel(WalkParams p) {
             cache[k] = __ldg(p.pair_a + k);
             cache[p.n_cached + k] = __ldg(p.pair_b + k);
         }
+        if (kGrid) {                          // the grid's occupancy bits follow the pair cache (constant data too)
+            uint32_t *gb = reinterpret_cast<uint32_t *>(walk_smem + sizeof(WalkShared) + 32 * (size_t)p.n_cached);
+            for (int k = threadIdx.x; k < p.g.n_words; k += blockDim.x) gb[k] = __ldg(p.g.bits + k);
+        }
     }
     pdl_wait();
     pdl_trigger();
@@ -613,6 +622,7 @@ nearest_hit_walk_kernel(WalkParams p) {
     unsigned pair_a_smem = (unsigned)__cvta_generic_to_shared(walk_smem + sizeof(WalkShared));
     unsigned pair_b_smem = pair_a_smem + 16u * (unsigned)p.n_cached;             // pair_b follows pair_a
     asm volatile("" : "+r"(pair_a_smem), "+r"(pair_b_smem));   // keep them in registers (else recomputed per visit)
+    const uint32_t *grid_bits = reinterpret_cast<const uint32_t *>(walk_smem + sizeof(WalkShared) + 32 * (size_t)p.n_cached);
     const int root_count = p.has_tree ? (int)TRC_META_COUNT(p.root_meta) : 7;   // 0 inner, 1..4 leaf, 7 nothing
     // entry payload of a tree that is a single leaf: list position, or the surface index itself for one surface
     const unsigned root_first = root_count == 1 ? (unsigned)__ldg(&p.cand[TRC_META_INDEX(p.root_meta)])
@@ -757,11 +767,56 @@ nearest_hit_walk_kernel(WalkParams p) {
                 RayF nr;
                 unsigned nsigns = 0u;
                 bool surv = false;
-                if (valid) {
-                    const double *src = &sh.ring[(ring_r - 1) & (kRing - 1)][0][(next & (kBatch - 1)) + lane];
-                    V3 v = mk(src[0], src[kBatch], src[2 * kBatch]);
-                    V3 d = mk(src[3 * kBatch], src[4 * kBatch], src[5 * kBatch]);
-                    surv = ray_setup(v, d, p, nr, nsigns) && root_count != 7 && !(p.debug & 2);
+                const double *src = &sh.ring[(ring_r - 1) & (kRing - 1)][0][(next & (kBatch - 1)) + lane];
+                bool walk_it = valid;          // the ray takes the tree walk (always, without a shadow grid)
+                if (kGrid) {
+                    // ---- shadow grid: rays inside the slope box are keyed by their crossing of the plane x_n = h0
+                    bool look = false;
+                    unsigned cell = 0u;
+                    if (valid) {
+                        const float vn = (float)src[p.g.axis_n * kBatch], va = (float)src[p.g.axis_a * kBatch],
+                                    vb = (float)src[p.g.axis_b * kBatch];
+                        const float dn = (float)src[(3 + p.g.axis_n) * kBatch], da = (float)src[(3 + p.g.axis_a) * kBatch],
+                                    db = (float)src[(3 + p.g.axis_b) * kBatch];
+                        const float inv = rcp_approx(dn);
+                        const bool in_box = dn * p.g.sgn > 0.0f && fabsf(fmaf(da, inv, -p.g.t0a)) <= p.g.da &&
+                                            fabsf(fmaf(db, inv, -p.g.t0b)) <= p.g.db &&
+                                            fmaxf(fmaxf(fabsf(va), fabsf(vb)), fabsf(vn)) <= p.g.rmax;
+                        if (in_box) {
+                            walk_it = false;
+                            const float t = (p.g.h0 - vn) * inv;
+                            const float ca = (fmaf(t, da, va) - p.g.ga0) * p.g.inv_ca;
+                            const float cb = (fmaf(t, db, vb) - p.g.gb0) * p.g.inv_cb;
+                            if (ca >= 0.0f && cb >= 0.0f && ca < (float)p.g.nx && cb < (float)p.g.ny) {
+                                cell = (unsigned)((int)cb * p.g.nx + (int)ca);
+                                look = (grid_bits[cell >> 5] >> (cell & 31u)) & 1u;
+                            }
+                        }
+                    }
+                    const unsigned ml = __ballot_sync(full, look);
+                    if (ml) {
+                        const unsigned ent = look ? __ldg(p.g.cells + cell) : 0u;
+                        const int cnt = (int)(ent & 255u);
+                        const unsigned pay = ent >> 8;
+                        const int maxc = __reduce_max_sync(full, cnt);
+                        for (int k = 0; k < maxc; ++k) {
+                            const bool has = k < cnt;
+                            const unsigned m = __ballot_sync(full, has);
+                            if (has) {
+                                const unsigned s_c = cnt == 1 ? pay : (unsigned)__ldg(p.g.list + pay + k);
+                                sh.queue[qn + __popc(m & lt_mask)] = ((unsigned)j << 24) | s_c;
+                            }
+                            qn += __popc(m);
+                            if (qn >= 32) qn = flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, false);
+                        }
+                    }
+                }
+                if (!kGrid || __any_sync(full, walk_it)) {
+                    if (walk_it) {
+                        V3 v = mk(src[0], src[kBatch], src[2 * kBatch]);
+                        V3 d = mk(src[3 * kBatch], src[4 * kBatch], src[5 * kBatch]);
+                        surv = ray_setup(v, d, p, nr, nsigns) && root_count != 7 && !(p.debug & 2);
+                    }
                 }
                 next += 32;
                 unsigned m = __ballot_sync(full, surv);
@@ -902,6 +957,22 @@ nearest_hit_walk_kernel(WalkParams p) {
 
 }  // namespace
 
+// pairs of the tree cached in shared memory: a tree that fits is cached whole; of a larger one only the top 256
+// pairs, so that two CTAs still fit an SM
+static int walk_cached_pairs(const TrcScene *sc) {
+    int n_cached = sc->n_pairs <= kSmemPairs ? sc->n_pairs : kSmemPairs / 2;
+    return (n_cached + 7) & ~7;
+}
+
+// Shared memory left for a shadow grid's occupancy bits next to this scene's per-warp blocks and tree cache, with
+// two CTAs per SM (228 KB per SM, 1 KB reserved per CTA)
+int trc_walk_grid_word_budget(const TrcScene *sc) {
+    const long per_cta = (228 * 1024) / TRC_WALK_MIN_CTAS_FLAT - 1024 - 256;
+    long spare = per_cta - (long)sizeof(WalkShared) - 32L * walk_cached_pairs(sc);
+    if (spare < 0) spare = 0;
+    return (int)std::min<long>(spare / 4, kGridMaxWords);
+}
+
 // dyn != nullptr: device-driven trace (trace.cu).  `n` is then the CAPACITY of the input bundle (it
 // sizes the grid), the real count is read from dyn->n_ptr by the kernels, the work counter and the
 // hit total live in the trace's control block (already zeroed) and the launch carries the PDL attribute.
@@ -925,9 +996,13 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     if ((sc->n_nodes == 0 && sc->n_unbounded == 0) || !sc->d_chunk_counter || !sc->d_cand)
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: use_bvh set but no BVH uploaded%s");
     typedef void (*WalkKernel)(WalkParams);
-    static const WalkKernel kernels[6] = {nearest_hit_walk_kernel<false, 0>, nearest_hit_walk_kernel<true, 0>,
-                                          nearest_hit_walk_kernel<false, 1>, nearest_hit_walk_kernel<true, 1>,
-                                          nearest_hit_walk_kernel<false, 2>, nearest_hit_walk_kernel<true, 2>};
+    static const WalkKernel kernels[12] = {
+        nearest_hit_walk_kernel<false, 0, false>, nearest_hit_walk_kernel<true, 0, false>,
+        nearest_hit_walk_kernel<false, 1, false>, nearest_hit_walk_kernel<true, 1, false>,
+        nearest_hit_walk_kernel<false, 2, false>, nearest_hit_walk_kernel<true, 2, false>,
+        nearest_hit_walk_kernel<false, 0, true>, nearest_hit_walk_kernel<true, 0, true>,
+        nearest_hit_walk_kernel<false, 1, true>, nearest_hit_walk_kernel<true, 1, true>,
+        nearest_hit_walk_kernel<false, 2, true>, nearest_hit_walk_kernel<true, 2, true>};
     static int g_refill_at = -1;
     static bool attr_set[64] = {};       // cudaFuncSetAttribute is per device
     if (sc->device < 0 || sc->device >= 64) return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: device index out of range%s");
@@ -935,17 +1010,20 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
         const char *env = getenv("TRC_WALK_REFILL_AT");      // tuning knob (0..31)
         g_refill_at = 24;
         if (env) { int v = atoi(env); if (v >= 0 && v < 32) g_refill_at = v; }
-        for (int k = 0; k < 6; ++k)
+        for (int k = 0; k < 12; ++k)
             TRC_CUDA(cudaFuncSetAttribute(kernels[k], cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)(sizeof(WalkShared) + 32 * kSmemPairs)));
+                                          (int)(sizeof(WalkShared) + 32 * kSmemPairs + (k >= 6 ? 4 * kGridMaxWords : 0))));
         attr_set[sc->device] = true;
     }
     // a tree that fits is cached whole; of a larger one only the top 256 pairs, so that two CTAs still fit an SM
-    int n_cached = sc->n_pairs <= kSmemPairs ? sc->n_pairs : kSmemPairs / 2;
-    n_cached = (n_cached + 7) & ~7;
-    const size_t smem = sizeof(WalkShared) + 32 * (size_t)n_cached;
-    const int variant = (sc->n_pairs <= kSmemPairs ? 1 : 0) | (sc->flat_only ? (sc->d_tri64 ? 4 : 2) : 0);
+    const int n_cached = walk_cached_pairs(sc);
+    // use_bvh == 2: rays inside the slope box of the scene's shadow grid skip the walk (a request without a grid
+    // set is an ordinary walk)
+    const bool grid = use_bvh == 2 && sc->has_grid;
+    const size_t smem = sizeof(WalkShared) + 32 * (size_t)n_cached + (grid ? 4 * (size_t)sc->grid.n_words : 0);
+    const int variant = ((sc->n_pairs <= kSmemPairs ? 1 : 0) | (sc->flat_only ? (sc->d_tri64 ? 4 : 2) : 0)) + (grid ? 6 : 0);
     WalkParams p;
+    p.g = grid ? sc->grid : TrcShadowGrid();
     p.surfs = sc->d_surfaces;
     p.pool = sc->d_tables;
     p.tri32 = sc->d_tri32;

@@ -498,7 +498,9 @@ extern "C" int trc_trace(const TrcScene *sc, const TrcTraceArgs *a, void *stream
                 }
                 TRC_CUDA(cudaEventRecord(scw->ev_walk[0], st));
             }
-            rc = trc_nearest_dyn(sc, in_cap, c, a->use_bvh, records, keys, cap, chunk_off, chunk_cnt, st);
+            // use_bvh == 2 (shadow grid of a coherent bundle) concerns the bundle the caller passed: bounce j == 0
+            rc = trc_nearest_dyn(sc, in_cap, c, (j == 0 || a->use_bvh < 2) ? a->use_bvh : 1, records, keys, cap,
+                                 chunk_off, chunk_cnt, st);
             if (rc != TRC_OK) return rc;
             if (timed) TRC_CUDA(cudaEventRecord(scw->ev_walk[1], st));
         }

@@ -562,6 +562,31 @@ class CompiledScene(object):
             leaf_surfs.ctypes.data_as(C.c_void_p) if len(leaf_surfs) else None, len(leaf_surfs),
             unb.ctypes.data_as(C.c_void_p) if len(unb) else None, len(unb)))
 
+    GRID_MAX_SURFACES = 1 << 16       # larger scenes keep the tree walk (cells would list dozens of faces)
+
+    def set_shadow_grid(self, direction, half_angle):
+        """Shadow grid for bundles whose directions lie within ``half_angle`` of ``direction`` (the first bounce
+        of a solar source): trc_scene_set_shadow_grid.  Cached per (direction, angle); returns whether the
+        nearest-hit kernel may be called with use_bvh = 2."""
+        import ctypes as C
+        key = None if direction is None else (tuple(np.round(np.asarray(direction, float), 12)), float(half_angle))
+        if key == getattr(self, '_grid_key', ('unset',)):
+            return self._grid_on
+        lib = L.load()
+        on = C.c_int32(0)
+        if key is None or len(self.bounded) == 0 or len(self.bounded) > self.GRID_MAX_SURFACES:
+            L.check(lib.trc_scene_set_shadow_grid(self.handle, 0, None, None, None, None, -1., C.byref(on)))
+        else:
+            lo = np.ascontiguousarray(self.aabb_lo[self.bounded], dtype=np.float64)
+            hi = np.ascontiguousarray(self.aabb_hi[self.bounded], dtype=np.float64)
+            ids = np.ascontiguousarray(self.bounded, dtype=np.int32)
+            d = np.ascontiguousarray(direction, dtype=np.float64)
+            L.check(lib.trc_scene_set_shadow_grid(
+                self.handle, len(ids), lo.ctypes.data_as(C.c_void_p), hi.ctypes.data_as(C.c_void_p),
+                ids.ctypes.data_as(C.c_void_p), d.ctypes.data_as(C.c_void_p), float(half_angle), C.byref(on)))
+        self._grid_key, self._grid_on = key, bool(on.value)
+        return self._grid_on
+
     def seg_entries_needed(self, device):
         """(host list, device index tensor) of the slot-offset entries the engine reads on the host after a
         bounce: both ends of every mesh and of every surface with accountants."""

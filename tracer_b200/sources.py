@@ -275,12 +275,19 @@ def _device_bundle_buffers(num_rays, device):
     return dev, V, D, E
 
 
-def _wrap(V, D, E, first_ray=0):
+MAX_CONE_HINT = 0.25     # rad: wider sources are not worth a shadow grid
+
+
+def _wrap(V, D, E, first_ray=0, cone=None):
     """Device-backed bundle.  ``_ray_id_base`` is the global index of its first ray: the engine keys the
     optics draws of every descendant by (seed, global source-ray index, bounce), so the shards of one source
     traced on several GPUs draw exactly what the whole source draws."""
     b = RayBundle(vertices=_DeviceColumns([V]), directions=_DeviceColumns([D]), energy=_DeviceColumns([E]))
     b.__dict__['_ray_id_base'] = int(first_ray)
+    if cone is not None and cone[1] <= MAX_CONE_HINT:
+        # every direction lies within cone[1] radians of cone[0]: lets the engine trace the first bounce through the
+        # scene's shadow grid (scene.py set_shadow_grid); the kernel re-checks each ray, so the hint only prunes
+        b.__dict__['_dir_cone'] = (np.asarray(cone[0], float).reshape(3).copy(), float(cone[1]) * (1. + 1e-9) + 1e-12)
     return b
 
 
@@ -315,7 +322,7 @@ def disk_bundle_device(num_rays, center, direction, radius, ang_range, flux=None
         L.check(lib.trc_source_pillbox_disk(num_rays, first_ray, seed, c, rd, rd, float(radius_in), float(radius),
                                             float(angular_span[0]), float(angular_span[1]), float(ang_range),
                                             float(e), L.dptr(V), L.dptr(D), L.dptr(E), num_rays, st))
-    return _wrap(V, D, E, first_ray)
+    return _wrap(V, D, E, first_ray, cone=(np.asarray(rot)[:, 2], float(ang_range)))
 
 
 def buie_sunshape_device(num_rays, center, direction, radius, CSR, flux=None, pre_process_CSR=True,
@@ -347,7 +354,7 @@ def buie_sunshape_device(num_rays, center, direction, radius, CSR, flux=None, pr
         st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         L.check(lib.trc_source_buie_disk(num_rays, first_ray, seed, C.byref(t), c, rd, rp, float(radius), float(e),
                                          L.dptr(V), L.dptr(D), L.dptr(E), num_rays, st))
-    return _wrap(V, D, E, first_ray)
+    return _wrap(V, D, E, first_ray, cone=(rotation_to_z(rays_direction)[:, 2], THETA_TOT))
 
 
 def _rect_local_half_extents(x, y, plane_normal):
@@ -385,7 +392,7 @@ def rect_bundle_device(num_rays, center, direction, x, y, ang_range, flux=None, 
         st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         L.check(lib.trc_source_pillbox_rect(num_rays, first_ray, seed, c, rd, rp, float(hx), float(hy),
                                             float(ang_range), float(e), L.dptr(V), L.dptr(D), L.dptr(E), num_rays, st))
-    return _wrap(V, D, E, first_ray)
+    return _wrap(V, D, E, first_ray, cone=(rotation_to_z(rays_direction)[:, 2], float(ang_range)))
 
 
 def oblique_solar_rect_bundle_device(num_rays, center, source_direction, rays_direction, x, y, ang_range, flux=None,
@@ -422,4 +429,4 @@ def rect_buie_sunshape_device(num_rays, center, direction, width, height, CSR, f
         st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         L.check(lib.trc_source_buie_rect(num_rays, first_ray, seed, C.byref(t), c, rd, rp, float(width) / 2.,
                                          float(height) / 2., float(e), L.dptr(V), L.dptr(D), L.dptr(E), num_rays, st))
-    return _wrap(V, D, E, first_ray)
+    return _wrap(V, D, E, first_ray, cone=(rotation_to_z(rays_direction)[:, 2], THETA_TOT))

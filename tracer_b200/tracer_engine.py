@@ -102,6 +102,37 @@ FULL_CAP_RAYS = 1 << 18       # bundles up to this size get buffers for "every r
 BLIND_BOUNCES = 4             # bounces enqueued per call while the depth of the trace is unknown
 
 
+GRID_MIN_RAYS = 1 << 16       # bundles at least this large with a narrow direction cone use the scene's shadow grid
+CONE_SAMPLE = 1 << 16         # rays of a host bundle looked at to estimate its cone
+MAX_CONE = 0.25               # rad
+
+
+def _direction_cone(bundle):
+    """(axis, half angle) of a cone holding the bundle's directions, or None.  Device sources state it
+    (sources._wrap); for a large host bundle it is estimated from the first CONE_SAMPLE rays with a margin.
+    It is a pruning hint only: the kernel checks every ray against the cone's slope box and walks the tree
+    for those outside."""
+    cone = getattr(bundle, '_dir_cone', None)
+    if cone is not None:
+        return cone
+    props = getattr(bundle, '_props', None)
+    d = props.get('directions') if props is not None else None
+    if not isinstance(d, np.ndarray) or d.ndim != 2 or d.shape[0] != 3 or d.shape[1] < (1 << 20):
+        return None
+    sample = np.asarray(d[:, :CONE_SAMPLE], dtype=float)
+    norm = np.sqrt(np.sum(sample ** 2, axis=0))
+    if not np.all(norm > 0.):
+        return None
+    unit = sample / norm
+    axis = unit.mean(axis=1)
+    length = np.sqrt(np.sum(axis ** 2))
+    if not length > 0.5:
+        return None
+    axis = axis / length
+    half = float(np.arccos(np.clip(np.min(np.dot(axis, unit)), -1., 1.))) * 1.05 + 1e-4
+    return (axis, half) if half <= MAX_CONE else None
+
+
 def _round_cap(x):
     return max(256, (int(x) + 255) // 256 * 256)
 
@@ -143,6 +174,7 @@ class TracerEngine(object):
         self._tallies_dirty = False
         self._copy_stream = None
         self._keep_tree = False
+        self.shadow_grid = True    # first bounce of a narrow-cone bundle through the scene's shadow grid (results equal)
         self.fused_bounce = True   # sequence a bounce inside the library (trc_bounce) when the configuration allows
         self.kernel_events = None  # set to a list to collect (bounce, n, H, start, end) CUDA events of trc_trace_hits
         self.stats = {}
@@ -175,7 +207,11 @@ class TracerEngine(object):
             frames = [s._global_frames if hasattr(s, '_global_frames') else s._temp_frame for s in surfaces]
         else:
             frames = [s._temp_frame for s in surfaces]
-        key = (tuple(map(id, surfaces)), tuple(map(id, frames)))
+        # Optics and geometry managers are part of the key by identity as well: replacing one (surf._opt = ...)
+        # recompiles.  Editing a parameter IN PLACE (opt._abs = 0.5, gm._half_dims[0] = 2.) is not seen --
+        # call compile(force=True) after such an edit (the reference re-reads the live objects every trace).
+        managers = [(getattr(s, '_opt', None), getattr(s, '_geom', None)) for s in surfaces]
+        key = (tuple(map(id, surfaces)), tuple(map(id, frames)), tuple((id(o), id(g)) for o, g in managers))
         if force or self._scene is None or key != self._frames_key:
             if self._scene is not None:
                 self._scene.close()
@@ -183,7 +219,7 @@ class TracerEngine(object):
             self._hit_frac = {}
             self._hist, self._cap_floor = {}, {}
             self._frames_key = key
-            self._frames_ref = (surfaces, frames)
+            self._frames_ref = (surfaces, frames, managers)
         return self._scene
 
     # ----------------------------------------------------------- bundles
@@ -366,7 +402,7 @@ class TracerEngine(object):
                     c0 = a // L.HIT_CHUNK
                     L.check(lib.trc_trace_hits_slice(
                         scene.handle, b - a, cur.V.data_ptr() + 8 * a, cur.D.data_ptr() + 8 * a,
-                        cur.E.data_ptr() + 8 * a, ld, 1 if use_bvh else 0, None, L.dptr(records), None, cap,
+                        cur.E.data_ptr() + 8 * a, ld, int(use_bvh), None, L.dptr(records), None, cap,
                         chunk_off.data_ptr() + 4 * c0, chunk_cnt.data_ptr() + 4 * c0, L.dptr(counters), a, st))
                 cur.slices = cur.keep = None   # resident from here on (an overflow re-runs the plain call)
                 H = int(counters[0].item())
@@ -379,7 +415,7 @@ class TracerEngine(object):
                 ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 ev0.record()
             L.check(lib.trc_trace_hits(scene.handle, n, L.dptr(cur.V), L.dptr(cur.D), L.dptr(cur.E),
-                                       cur.V.stride(0), 1 if use_bvh else 0, None, L.dptr(records), cap,
+                                       cur.V.stride(0), int(use_bvh), None, L.dptr(records), cap,
                                        L.dptr(chunk_off), L.dptr(chunk_cnt), L.dptr(counters), st))
             if self.kernel_events is not None:
                 ev1.record()
@@ -558,7 +594,7 @@ class TracerEngine(object):
         chunk = torch.empty(2 * n_chunks, dtype=torch.int32, device=dev)
         total = torch.zeros(1, dtype=torch.int64, device=dev)
         L.check(lib.trc_trace_hits(scene.handle, n, L.dptr(cur.V), L.dptr(cur.D), L.dptr(cur.E), cur.V.stride(0),
-                                   1 if use_bvh else 0, None, None, 0, L.dptr(chunk), chunk.data_ptr() + 4 * n_chunks,
+                                   int(use_bvh), None, None, 0, L.dptr(chunk), chunk.data_ptr() + 4 * n_chunks,
                                    L.dptr(total), st))
         return int(total.item())
 
@@ -590,7 +626,7 @@ class TracerEngine(object):
         a.d_wavelengths = cur.W.data_ptr() if cur.W is not None else None
         a.d_ray_ids = cur.I.data_ptr() if cur.I is not None else None
         a.ray_id_base = cur.id_base
-        a.use_bvh, a.first_bounce, a.n_bounces = (1 if use_bvh else 0), bounce, nb
+        a.use_bvh, a.first_bounce, a.n_bounces = int(use_bvh), bounce, nb
         timed = self.kernel_events is not None and bounce == 0 and cur.slices is None
         seg_on_host = scene.has_accountants and S + 1 <= INLINE_SEG_MAX
         a.flags = (L.TRACE_SEG if seg_on_host else 0) | (L.TRACE_TIME_WALK if timed else 0)
@@ -623,7 +659,7 @@ class TracerEngine(object):
                 c0 = lo // L.HIT_CHUNK
                 L.check(lib.trc_trace_hits_slice(
                     scene.handle, hi - lo, cur.V.data_ptr() + 8 * lo, cur.D.data_ptr() + 8 * lo,
-                    cur.E.data_ptr() + 8 * lo, ld, 1 if use_bvh else 0, None, sp + plan.off_records,
+                    cur.E.data_ptr() + 8 * lo, ld, int(use_bvh), None, sp + plan.off_records,
                     sp + plan.off_keys, caps[0], sp + plan.off_chunk_off + 4 * c0, sp + plan.off_chunk_cnt + 4 * c0,
                     sp + plan.off_total, lo, st))
             cur.slices = cur.keep = None       # resident from here on
@@ -766,6 +802,11 @@ class TracerEngine(object):
             raise ValueError("scene has spectral optics but the bundle carries no 'wavelengths'")
 
         cur = self._to_device(bundle)
+        # a bundle of nearly parallel rays (a solar source) finds its candidates in the scene's shadow grid
+        grid = False
+        if use_bvh and self.shadow_grid and cur.n >= GRID_MIN_RAYS:
+            cone = _direction_cone(bundle)
+            grid = cone is not None and scene.set_shadow_grid(cone[0], cone[1])
         if scene.has_refractive and cur.R is None:
             raise ValueError("scene has refractive optics but the bundle carries no 'ref_index'")
         source_E = cur.E
@@ -786,10 +827,11 @@ class TracerEngine(object):
         i = 0
         depleted = False
         while i < reps and not depleted:
+            how = (2 if grid and i == 0 else 1) if use_bvh else 0      # the use_bvh argument of the C entry points
             if device_driven:
-                results = self._trace_block(scene, cur, i, reps - i, min_energy, use_bvh)
+                results = self._trace_block(scene, cur, i, reps - i, min_energy, how)
             else:
-                rec, n_surv, H = self._bounce(scene, cur, i, min_energy, use_bvh)
+                rec, n_surv, H = self._bounce(scene, cur, i, min_energy, how)
                 results = [(rec, n_surv, H, cur.n)]
             for rec, n_surv, H, n_in in results:
                 i += 1
@@ -819,7 +861,7 @@ class TracerEngine(object):
             self.tree.append(self._as_bundle(last_rec['pre_cull']) if last_rec is not None
                              else RayBundle.empty_bund())
         self.stats = dict(ray_bounces=ray_bounces, per_bounce=per_bounce, surfaces=scene.num_surfaces,
-                          use_bvh=use_bvh)
+                          use_bvh=use_bvh, shadow_grid=bool(grid))
         if cur.n != 0:
             logging.warning(f'{cur.n} rays left at the end of the simulation')
             frac = float((cur.E.sum() / source_E.sum()).item()) * 100.
