@@ -9,11 +9,14 @@ from .numpy_engine import (_names, find_intersections, reflections, rotation_to_
 
 
 class Bundle(object):
-    """Minimal SoA bundle of the oracle (tracer/ray_bundle.py:6-63)."""
+    """Minimal SoA bundle of the oracle (tracer/ray_bundle.py:6-63).  ``wavelengths`` is (n,) for monochromatic
+    rays or (W, n) next to ``spectra`` (W, n) for polychromatic ones: the ray index is the last axis of every
+    property (ray_bundle.py:84-90)."""
 
-    def __init__(self, vertices, directions, energy, parents=None, wavelengths=None, ref_index=None):
+    def __init__(self, vertices, directions, energy, parents=None, wavelengths=None, ref_index=None, spectra=None):
         self.vertices, self.directions, self.energy = vertices, directions, energy
         self.parents, self.wavelengths, self.ref_index = parents, wavelengths, ref_index
+        self.spectra = spectra
 
     @property
     def n(self):
@@ -22,8 +25,9 @@ class Bundle(object):
     def take(self, idx):
         return Bundle(self.vertices[:, idx], self.directions[:, idx], self.energy[idx],
                       None if self.parents is None else self.parents[idx],
-                      None if self.wavelengths is None else self.wavelengths[idx],
-                      None if self.ref_index is None else self.ref_index[idx])
+                      None if self.wavelengths is None else self.wavelengths[..., idx],
+                      None if self.ref_index is None else self.ref_index[idx],
+                      None if self.spectra is None else self.spectra[..., idx])
 
     @staticmethod
     def concat(bs):
@@ -31,8 +35,9 @@ class Bundle(object):
             return Bundle(N.zeros((3, 0)), N.zeros((3, 0)), N.array([]), N.array([], dtype=int))
         wl = None if bs[0].wavelengths is None else N.hstack([b.wavelengths for b in bs])
         ri = None if bs[0].ref_index is None else N.hstack([b.ref_index for b in bs])
+        sp = None if bs[0].spectra is None else N.hstack([b.spectra for b in bs])
         return Bundle(N.hstack([b.vertices for b in bs]), N.hstack([b.directions for b in bs]),
-                      N.hstack([b.energy for b in bs]), N.hstack([b.parents for b in bs]), wl, ri)
+                      N.hstack([b.energy for b in bs]), N.hstack([b.parents for b in bs]), wl, ri, sp)
 
     # reference-style getters so tests can treat oracle and engine bundles alike
     def get_vertices(self):
@@ -49,6 +54,12 @@ class Bundle(object):
 
     def get_ref_index(self):
         return self.ref_index
+
+    def get_wavelengths(self):
+        return self.wavelengths
+
+    def get_spectra(self):
+        return self.spectra
 
     def get_num_rays(self):
         return self.n
@@ -78,7 +89,7 @@ _KNOWN = ('Transparent', 'OneSidedReflective', 'Reflective', 'OneSidedRealReflec
           'Lambertian_directional_axisymmetric_piecewise_spectral', 'Reflective_spectral',
           'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM', 'LambertianAbsorbant',
           'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise', 'PeriodicBoundary',
-          'FresnelConductorHomogenous')
+          'FresnelConductorHomogenous', 'Lambertian_directional_axisymmetric_piecewise_Polychromatic')
 
 
 def fresnel(ray_dirs, normals, n1, n2):
@@ -165,15 +176,17 @@ def _iam(base, d, normals, energy):
     return energy * (1. - base._abs) * (1. - N.exp(-cos_aoi ** base.c / base.a_r)) / (1. - N.exp(-1. / base.a_r))
 
 
-def apply_optics(opt, d, normals, energy, wavelengths, up, v_parent=None, hit=None):
+def apply_optics(opt, d, normals, energy, wavelengths, up, v_parent=None, hit=None, spectra=None):
     """One optics callable on the selected rays of one surface.
     Returns (directions (3,h), energy (h,)); apply_optics.attenuations holds the
-    attenuated energy of the last call (LambertianAbsorbant) or None."""
+    attenuated energy of the last call (LambertianAbsorbant) or None, apply_optics.spectra_out the
+    outgoing spectra of a polychromatic callable or None (then the child inherits the parent's)."""
     base, _ = _unwrap(opt)
     names = _names(base)
     h = d.shape[1]
     one_sided = False
     apply_optics.attenuations = None
+    apply_optics.spectra_out = None
     for cls in type(base).__mro__:          # a subclass with its own __call__ is not its parent
         if cls.__name__ in _KNOWN:
             break
@@ -270,6 +283,19 @@ def apply_optics(opt, d, normals, energy, wavelengths, up, v_parent=None, hit=No
                 ab = RegularGridInterpolator((base.thetas, base.wavelengths), base.absorptance)(
                     N.array([th, wavelengths]).T)
             out = _lambert(normals, N.pi / 2., h), energy * (1. - ab)
+        elif name == 'Lambertian_directional_axisymmetric_piecewise_Polychromatic':   # :403-425
+            th = _theta_in(d, normals)
+            pts = N.array([N.tile(th, (wavelengths.shape[0], 1)), wavelengths]).T      # (h, W, 2)
+            if hasattr(base, 'interpolator'):
+                ab = base.interpolator(pts)
+            else:
+                from scipy.interpolate import RegularGridInterpolator
+                ab = RegularGridInterpolator((base.thetas, base.wavelengths), base.absorptance)(pts)
+            sp = spectra * (1. - ab.T)
+            dx = N.diff(wavelengths, axis=0)                            # N.trapz(sp, wavelengths, axis=0)
+            e_out = N.sum(dx * (sp[1:] + sp[:-1]) / 2.0, axis=0)
+            apply_optics.spectra_out = sp
+            out = _lambert(normals, N.pi / 2., h), e_out
         elif name == 'Reflective_spectral':                         # :183-193
             ab = N.interp(wavelengths, base._wavelengths, base._absorptances)
             out = reflections(d, normals), energy * (1. - ab)
@@ -341,11 +367,17 @@ class OracleEngine(object):
                 ri = N.asarray(bundle.get_ref_index(), float)
             except (KeyError, AttributeError):
                 ri = None
+        sp = None
+        if hasattr(bundle, 'has_property') and bundle.has_property('spectra'):
+            try:
+                sp = N.asarray(bundle.get_spectra(), float)
+            except (KeyError, AttributeError):
+                sp = None
         bund = Bundle(N.asarray(bundle.get_vertices(), float), N.asarray(bundle.get_directions(), float),
-                      N.asarray(bundle.get_energy(), float), None, wl, ri)
+                      N.asarray(bundle.get_energy(), float), None, wl, ri, sp)
         self.tree = [bund] if tree else []
         self.front_surfs = []
-        self.tallies = [dict() for _ in surfaces]
+        self.tallies = {}
         self.ray_bounces = 0
         record = []
         for i in range(reps):
@@ -362,7 +394,17 @@ class OracleEngine(object):
                 normals = normals_fn(sel)
                 d_in = bund.directions[:, sel]
                 e_in = bund.energy[sel]
-                wl_in = None if bund.wavelengths is None else bund.wavelengths[sel]
+                wl_in = None if bund.wavelengths is None else bund.wavelengths[..., sel]
+                sp_in = None if bund.spectra is None else bund.spectra[..., sel]
+                ri_sel = None if bund.ref_index is None else bund.ref_index[sel]
+                if 'BiFacial' in _names(surf._opt):                 # optics_callables.py:1877-1924
+                    child = self._bifacial(s_idx, surf, hit, normals, d_in, e_in, wl_in, sp_in, ri_sel, sel,
+                                           bund.vertices[:, sel])
+                    record.append(child)
+                    delete = child.energy <= min_energy
+                    weak.append(delete)
+                    outg.append(child.take(N.nonzero(~delete)[0]) if delete.any() else child)
+                    continue
                 base_opt, _ = _unwrap(surf._opt)
                 if 'PeriodicBoundary' in _names(base_opt):          # optics_callables.py:703-721
                     ri_in = None if bund.ref_index is None else bund.ref_index[sel]
@@ -384,9 +426,11 @@ class OracleEngine(object):
                     outg.append(child.take(N.nonzero(~delete)[0]) if delete.any() else child)
                     continue
                 dirs, e_out = apply_optics(surf._opt, d_in, normals, e_in, wl_in, surf._temp_frame[:3, 2],
-                                           v_parent=bund.vertices[:, sel], hit=hit)
-                child = Bundle(hit, dirs, e_out, sel, wl_in, None if bund.ref_index is None else bund.ref_index[sel])
-                self._count(s_idx, surf, hit, d_in, normals, e_in, e_out, wl_in, apply_optics.attenuations)
+                                           v_parent=bund.vertices[:, sel], hit=hit, spectra=sp_in)
+                sp_out = sp_in if apply_optics.spectra_out is None else apply_optics.spectra_out
+                child = Bundle(hit, dirs, e_out, sel, wl_in, ri_sel, sp_out)
+                self._count(s_idx, surf._opt, hit, d_in, normals, e_in, e_out, wl_in, apply_optics.attenuations,
+                            sp_in, sp_out)
                 record.append(child)
                 delete = e_out <= min_energy
                 weak.append(delete)
@@ -403,29 +447,80 @@ class OracleEngine(object):
             self.tree.append(Bundle.concat(record))
         return bund.vertices, bund.directions
 
-    def _count(self, s_idx, surf, hit, d_in, normals, e_in, e_out, wl_in, attenuated=None):
-        """Accountant.count for each accountant (optics_callables.py:1597-1790)."""
-        _, accs = _unwrap(surf._opt)
+    def _bifacial(self, s_idx, surf, hit, normals, d_in, e_in, wl_in, sp_in, ri_sel, sel, v_parent):
+        """BiFacial.__call__ (optics_callables.py:1885-1901): rays travelling along +z of the surface ("up",
+        geometry_manager.py:29-34) hit the back.  Each side's callable runs on ALL the selected rays when at least
+        one ray is on its side (its draws and its accountants see all of them) and keeps its own side's children;
+        the back children come first."""
+        opt = surf._opt
+        up = surf._temp_frame[:3, 2]
+        proj = N.around(N.sum(d_in * up[:, None], axis=0), decimals=6)
+        back = proj > 0.
+        parts = []
+        for side, side_opt, mask in (('back', opt.OpticsCallable_back, back), ('front', opt.OpticsCallable_front, ~back)):
+            if not mask.any():
+                continue
+            base, _ = _unwrap(side_opt)
+            if any(nm in ('PeriodicBoundary', 'RefractiveHomogenous', 'BiFacial') for nm in _names(base)):
+                raise NotImplementedError("oracle: two-children optics inside BiFacial")
+            dirs, e_out = apply_optics(side_opt, d_in, normals, e_in, wl_in, up, v_parent=v_parent, hit=hit,
+                                       spectra=sp_in)
+            sp_out = sp_in if apply_optics.spectra_out is None else apply_optics.spectra_out
+            self._count((s_idx, side), side_opt, hit, d_in, normals, e_in, e_out, wl_in, apply_optics.attenuations,
+                        sp_in, sp_out)
+            parts.append(Bundle(hit, dirs, e_out, sel, wl_in, ri_sel, sp_out).take(N.nonzero(mask)[0]))
+        return Bundle.concat(parts)
+
+    def _count(self, key, opt, hit, d_in, normals, e_in, e_out, wl_in, attenuated=None, sp_in=None, sp_out=None):
+        """Accountant.count for each accountant (optics_callables.py:1597-1848)."""
+        _, accs = _unwrap(opt)
         data = {'_absorbed': e_in - e_out, '_attenuated': attenuated, '_received': e_in, '_scattered': e_out, '_hits': hit,
                 '_directions': d_in, '_normals': normals, '_wavelengths': wl_in}
-        t = self.tallies[s_idx]
+        t = self.tallies.setdefault(key, {})
         for a in accs:
-            field = _ACC.get(getattr(a, 'shorthand', None))
+            sh = getattr(a, 'shorthand', None)
+            if sh == 'Polychromatic':                   # :1825-1838: the child's wavelengths, spectra lost at the hit
+                t.setdefault('_wavelengths', []).append(wl_in)
+                t.setdefault('_spectra', []).append(sp_in - sp_out)
+                continue
+            field = _ACC.get(sh)
             if field is None:
                 raise NotImplementedError("oracle: accountant %s" % type(a).__name__)
             t.setdefault(field, []).append(data[field])
             if self.write_accountants:
                 getattr(a, field).append(data[field])
 
-    def get_all_hits(self, s_idx):
-        """Same list the surface's optics manager would return from get_all_hits()."""
-        _, accs = _unwrap(self._asm.get_surfaces()[s_idx]._opt)
+    def _hits_of(self, key, opt):
+        _, accs = _unwrap(opt)
         out = []
         for a in accs:
+            if a.shorthand == 'Polychromatic':
+                # PolychromaticAccountant.get_data reads self._absorbed, which its reset() never creates (:1840-1848)
+                raise AttributeError("'PolychromaticAccountant' object has no attribute '_absorbed'")
             field = _ACC[a.shorthand]
-            chunks = self.tallies[s_idx].get(field, [])
+            chunks = self.tallies.get(key, {}).get(field, [])
             if field in ('_hits', '_directions', '_normals'):
                 out.append(N.hstack(chunks) if chunks else N.zeros((3, 0)))
             else:
                 out.append(N.hstack(chunks) if chunks else N.array([]))
         return out
+
+    def get_all_hits(self, s_idx):
+        """Same list the surface's optics manager would return from get_all_hits(); a BiFacial manager returns
+        (front, back), each the list of that side's callable or [] when it has no accountants (:1903-1914)."""
+        opt = self._asm.get_surfaces()[s_idx]._opt
+        if 'BiFacial' in _names(opt):
+            sides = []
+            for side, side_opt in (('front', opt.OpticsCallable_front), ('back', opt.OpticsCallable_back)):
+                try:                                    # the reference swallows every error here (:1905-1912)
+                    sides.append(self._hits_of((s_idx, side), side_opt) if _unwrap(side_opt)[1] else [])
+                except AttributeError:
+                    sides.append([])
+            return tuple(sides)
+        return self._hits_of(s_idx, opt)
+
+    def get_polychromatic(self, key):
+        """(wavelengths (W, h), absorbed spectra (W, h)) a PolychromaticAccountant holds in its lists; ``key`` is a
+        surface index or (surface index, 'front' | 'back')."""
+        t = self.tallies.get(key, {})
+        return N.hstack(t['_wavelengths']), N.hstack(t['_spectra'])

@@ -33,7 +33,12 @@ TRACE_CASES = {
     'c7_periodic_cell': (scenes.c7_periodic_cell, dict(n_rays=2000), 20, 6, 1e-10),
     'c8_fresnel_conductor': (scenes.c8_fresnel_conductor, dict(n_rays=2000), 21, 6, 1e-10),
     'c9_refractive': (scenes.c9_refractive, dict(n_rays=2000), 22, 7, 1e-3 * 1000. * np.pi * 1.21 / 2000),
+    'c10_polychromatic': (scenes.c10_polychromatic, dict(n_rays=2000), 23, 5, 1e-3 * 1000. * np.pi * 1.44 / 2000),
+    'c11_bifacial': (scenes.c11_bifacial, dict(n_rays=3000), 24, 6, 1e-3 * 1000. * np.pi * 2.56 / 3000),
 }
+# raw lists of the accountants (get_all_hits() raises in the reference when a PolychromaticAccountant is there)
+_ACC_LISTS = ('_absorbed', '_attenuated', '_received', '_scattered', '_wavelengths', '_spectra', '_hits',
+              '_directions', '_normals')
 ZOO_RAYS = 4000
 ZOO_SEED = 99
 
@@ -60,11 +65,27 @@ def trace_reference(name):
             out['p%d' % k] = b.get_parents()
         if name == 'c9_refractive':
             out['r%d' % k] = b.get_ref_index()
+        if name == 'c10_polychromatic':
+            out['w%d' % k] = b.get_wavelengths()
+            out['s%d' % k] = b.get_spectra()
     for s, surf in enumerate(asm.get_surfaces()):
         opt = surf.get_optics_manager()
-        if hasattr(opt, 'get_all_hits'):
-            for j, arr in enumerate(opt.get_all_hits()):
-                out['acc_%d_%d' % (s, j)] = arr
+        if type(opt).__name__ == 'BiFacial':
+            # (front, back) lists; a side without accountants gives []
+            for side, arrays in zip(('front', 'back'), opt.get_all_hits()):
+                for j, arr in enumerate(arrays):
+                    out['accb_%d_%s_%d' % (s, side, j)] = arr
+        elif hasattr(opt, 'get_all_hits'):
+            try:
+                for j, arr in enumerate(opt.get_all_hits()):
+                    out['acc_%d_%d' % (s, j)] = arr
+            except AttributeError:
+                # PolychromaticAccountant.get_data raises (optics_callables.py:1840-1848): record the raw lists
+                for j, acc in enumerate(opt.accountants):
+                    for field in _ACC_LISTS:
+                        chunks = getattr(acc, field, None)
+                        if chunks:
+                            out['accl_%d_%d%s' % (s, j, field)] = np.hstack(chunks)
     return out
 
 

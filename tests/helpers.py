@@ -39,6 +39,9 @@ def compare_tree(gold, tree, n_levels=None, rtol=RTOL):
         close(b.get_energy(), gold['e%d' % k], rtol, f'level {k} energy')
         if 'r%d' % k in gold.files:
             assert np.array_equal(np.asarray(b.get_ref_index()), gold['r%d' % k]), f'level {k}: ref_index differs'
+        if 'w%d' % k in gold.files:                 # polychromatic bundles: (W, n) wavelengths and spectra
+            close(b.get_wavelengths(), gold['w%d' % k], rtol, f'level {k} wavelengths')
+            close(b.get_spectra(), gold['s%d' % k], rtol, f'level {k} spectra')
 
 
 def golden_accountants(gold):
@@ -48,6 +51,28 @@ def golden_accountants(gold):
             _, s, j = key.split('_')
             out.setdefault(int(s), {})[int(j)] = gold[key]
     return {s: [v[j] for j in sorted(v)] for s, v in out.items()}
+
+
+def golden_bifacial(gold):
+    """{surface: {'front': [arrays], 'back': [arrays]}} of the BiFacial managers of a golden trace."""
+    out = {}
+    for key in gold.files:
+        if key.startswith('accb_'):
+            _, s, side, j = key.split('_')
+            out.setdefault(int(s), {}).setdefault(side, {})[int(j)] = gold[key]
+    return {s: {side: [v[j] for j in sorted(v)] for side, v in d.items()} for s, d in out.items()}
+
+
+def golden_accountant_lists(gold):
+    """{surface: {(accountant index, list attribute): array}} of managers whose get_all_hits() raises in the
+    reference (PolychromaticAccountant): the accountants' raw lists, stacked over the bounces."""
+    out = {}
+    for key in gold.files:
+        if key.startswith('accl_'):
+            _, s, rest = key.split('_', 2)
+            j, field = rest.split('_', 1)
+            out.setdefault(int(s), {})[(int(j), '_' + field)] = gold[key]
+    return out
 
 
 def fluxmap_agreement(mean_a, sem_a, mean_b, sem_b):

@@ -9,7 +9,8 @@ from oracle.numpy_engine import find_intersections
 from oracle.numpy_trace import OracleEngine
 from tests import scenes
 from tests.golden.make_golden import TRACE_CASES, ZOO_RAYS, ZOO_SEED
-from tests.helpers import close, compare_tree, golden_accountants, load_golden
+from tests.helpers import (close, compare_tree, golden_accountant_lists, golden_accountants, golden_bifacial,
+                           load_golden)
 
 T = scenes.NS('tracer_b200')
 
@@ -31,6 +32,19 @@ def test_trace_matches_reference(name):
         assert len(mine) == len(arrays)
         for a, b in zip(mine, arrays):
             close(a, b, 1e-12, f'accountant of surface {s}')
+    for s, sides in golden_bifacial(gold).items():
+        front, back = eng.get_all_hits(s)
+        for side, mine in (('front', front), ('back', back)):
+            arrays = sides.get(side, [])
+            assert len(mine) == len(arrays), f'BiFacial surface {s} {side}'
+            for a, b in zip(mine, arrays):
+                close(a, b, 1e-12, f'BiFacial surface {s} {side}')
+    for s, lists in golden_accountant_lists(gold).items():
+        with pytest.raises(AttributeError):      # as in the reference (optics_callables.py:1840-1848)
+            eng.get_all_hits(s)
+        tall = eng.tallies[s]
+        for (j, field), ref in lists.items():
+            close(np.hstack(tall[field]), ref, 1e-12, f'accountant {j} list {field} of surface {s}')
 
 
 @pytest.mark.parametrize('name', sorted(scenes.gm_zoo(T)))

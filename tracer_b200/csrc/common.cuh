@@ -146,7 +146,7 @@ struct TrcScene {
     int32_t *d_cand = nullptr;         // leaf surfaces followed by unbounded surfaces (the walk's candidate list)
     int num_sms = 148;
     int device = 0;                    // CUDA device the tables live on
-    int walk_occ[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};    // resident CTAs per SM of each tree-walk instantiation (cached query)
+    int walk_occ[6] = {0, 0, 0, 0, 0, 0};    // resident CTAs per SM of each tree-walk instantiation (cached query)
     bool flat_only = false;            // every surface is of the flat family (kinds <= TRC_G_TRIANGLE)
     float4 *d_tri32 = nullptr;         // float32 copies of the triangles (3 x float4 per surface) for the walk's
                                        // conservative pre-test; null unless the scene is flat-only and has triangles
@@ -159,6 +159,10 @@ struct TrcScene {
     TrcShadowGrid grid = {};
     uint32_t *d_grid_bits = nullptr, *d_grid_cells = nullptr;
     int32_t *d_grid_list = nullptr;
+    int grid_occ[3] = {0, 0, 0};       // resident CTAs per SM of the shadow-grid kernel's instantiations (cached query)
+    uint32_t *d_dirty = nullptr;       // chunks the shadow-grid kernel leaves to the tree walk (dirty_cap entries)
+    int64_t dirty_cap = 0;
+    unsigned long long *d_dirty_counters = nullptr;   // [entries of d_dirty, work counter of the walk over them]
     int64_t *h_pinned = nullptr;       // page-locked host words for the count read-backs of trc_bounce: [hits, culled, seg(S+1)]
     cudaEvent_t ev_walk[2] = {nullptr, nullptr};   // reusable event pair around the bounce-0 nearest-hit kernel (time_trace)
 };

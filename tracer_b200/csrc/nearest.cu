@@ -27,7 +27,6 @@
 #include <stdint.h>
 #include <stdlib.h>
 
-#include <algorithm>
 #include "common.cuh"
 #include "geom.cuh"
 
@@ -181,7 +180,8 @@ constexpr int kListFields = 10;               // A[3], Bn[3], Bf[3], slot | dire
 #ifndef TRC_WALK_SMEM_PAIRS
 #define TRC_WALK_SMEM_PAIRS 512
 #endif
-constexpr int kGridMaxWords = 8192;           // occupancy bits of a shadow grid in shared memory: at most 32 KB
+constexpr int kGridQueue = 512;               // candidate queue of the shadow-grid kernel (entries per warp)
+constexpr int kGridMaxWords = 6144;           // occupancy bits of a shadow grid in shared memory: at most 24 KB
 constexpr int kSmemPairs = TRC_WALK_SMEM_PAIRS;               // top of the tree (breadth-first) cached per CTA: 16 KB
 // queue entry = slot << 24 | (count - 1) << 22 | first candidate-list index: one entry per leaf
 constexpr unsigned kCandMask = 0x003fffffu;
@@ -215,10 +215,34 @@ struct WalkShared {
     long long pad_;                           // here so that it costs no registers in the walk loop
 };
 
-typedef TrcShadowGrid GridParams;      // shadow grid of a directionally coherent bundle (common.cuh)
+// Per-warp shared memory of the shadow-grid kernel (nearest_hit_grid_kernel): the per-slot best (t, surface) of a
+// chunk and the candidate queues; same member names as WalkWarpShared where the float64 stage reads them.
+struct GridWarpShared {
+    unsigned long long best_t[kChunk];
+    int best_s[kChunk];
+    unsigned queue[kGridQueue];               // packed (slot, surface); lends its storage to the hit-slot list
+    unsigned queue2[64];
+    int q2n;
+    const double *vert, *dir, *energy;
+    long long ld;
+};
+__device__ __forceinline__ unsigned char *slot_scratch(WalkWarpShared &sh) {
+    static_assert(sizeof(float) * kListFields * kListCap >= kChunk, "slot list borrows the active list");
+    return reinterpret_cast<unsigned char *>(&sh.list[0][0]);
+}
+__device__ __forceinline__ unsigned char *slot_scratch(GridWarpShared &sh) {
+    static_assert(sizeof(unsigned) * kGridQueue >= kChunk, "slot list borrows the candidate queue");
+    return reinterpret_cast<unsigned char *>(&sh.queue[0]);
+}
+
+typedef TrcShadowGrid GridParams;             // shadow grid of a directionally coherent bundle (common.cuh)
 
 struct WalkParams {
-    GridParams g;
+    GridParams g;                             // shadow-grid kernel only
+    uint32_t *dirty_list;                     // shadow-grid kernel: chunks it leaves to the walk (some ray outside the
+    unsigned long long *dirty_count;          //   grid's slope box) ...
+    const uint32_t *chunk_list;               // ... and the walk kernel launched after it: the chunk ids to process
+    const unsigned long long *chunk_list_n;   //   (null: every chunk of the bundle)
     const TrcSurfaceRec *surfs;
     const double *pool;                       // scene table pool (apertures of the pool-based flat kinds)
     const float4 *tri32;                      // float32 triangles for the pre-test, or null (see tri_prefilter)
@@ -356,8 +380,8 @@ __device__ __forceinline__ float best_as_float(unsigned long long bits) {
 
 // Stage C: test queued (slot, leaf) candidates in float64, 32 at a time, and
 // fold them into the per-slot best (t, surface).  `all` drains the queue.
-template <int kFlatOnly>     // 0 generic scene, 1 flat-family surfaces only, 2 the same with the compact triangle table
-__device__ __forceinline__ int flush_queue_body(WalkWarpShared &sh, const unsigned *queue, const WalkParams &p,
+template <int kFlatOnly, class Sh>     // 0 generic scene, 1 flat-family surfaces only, 2 the same with the compact triangle table
+__device__ __forceinline__ int flush_queue_body(Sh &sh, const unsigned *queue, const WalkParams &p,
                                                 int64_t chunk_base, int lane, int qn, bool all) {
     __syncwarp();
     if (p.debug & 1) qn = 0;
@@ -428,6 +452,10 @@ __device__ __noinline__ int flush_queue_generic(WalkWarpShared &sh, const WalkPa
                                                 int qn, bool all) {
     return flush_queue_body<false>(sh, sh.queue, p, chunk_base, lane, qn, all);
 }
+__device__ __noinline__ int flush_queue_generic(GridWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
+                                                int qn, bool all) {
+    return flush_queue_body<false>(sh, sh.queue, p, chunk_base, lane, qn, all);
+}
 
 // Conservative float32 ray/triangle test (Moeller-Trumbore with running error bounds): false only
 // when the ray certainly misses the triangle, so that the float64 test of the reference
@@ -469,8 +497,8 @@ __device__ __forceinline__ bool tri_prefilter(const float4 *tri, V3 v, V3 d) {
 
 // Flat-only scenes with triangles: queue entries first take the float32 pre-test, 32 at a time;
 // the few that pass wait in queue2 for the float64 stage.
-template <int kFlatOnly>
-__device__ __forceinline__ int prefilter_queue(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
+template <int kFlatOnly, class Sh>
+__device__ __forceinline__ int prefilter_queue(Sh &sh, const WalkParams &p, int64_t chunk_base, int lane,
                                                int qn, bool all) {
     const unsigned lt_mask = (1u << lane) - 1u;
     __syncwarp();
@@ -503,8 +531,8 @@ __device__ __forceinline__ int prefilter_queue(WalkWarpShared &sh, const WalkPar
     return qn;
 }
 
-template <int kFlatOnly>     // 0 generic scene, 1 flat-family surfaces only, 2 the same with the compact triangle table
-__device__ __forceinline__ int flush_queue(WalkWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane,
+template <int kFlatOnly, class Sh>     // 0 generic scene, 1 flat-family surfaces only, 2 the same with the compact triangle table
+__device__ __forceinline__ int flush_queue(Sh &sh, const WalkParams &p, int64_t chunk_base, int lane,
                                            int qn, bool all) {
 #ifdef TRC_WALK_EXPERIMENT_NO_F64      // timing experiment only: what the walk costs without the float64 stage
     if (kFlatOnly) return (qn >= 32 || all) ? 0 : qn;
@@ -520,12 +548,12 @@ __device__ __forceinline__ int flush_queue(WalkWarpShared &sh, const WalkParams 
 // The hit slots are first compacted into shared memory (the active list is empty at this
 // point and lends its storage), so the dependent global loads of the records run once for
 // 32 hits at a time instead of once per 32 slots.
-__device__ __forceinline__ void emit_chunk_hits(WalkWarpShared &sh, const WalkParams &p, int64_t c_cur,
+template <class Sh>
+__device__ __forceinline__ void emit_chunk_hits(Sh &sh, const WalkParams &p, int64_t c_cur,
                                              int64_t chunk_base, int lane) {
     const unsigned full = 0xffffffffu;
     const unsigned lt_mask = (1u << lane) - 1u;
-    unsigned char *slots = reinterpret_cast<unsigned char *>(&sh.list[0][0]);
-    static_assert(sizeof(float) * kListFields * kListCap >= kChunk, "slot list borrows the active list");
+    unsigned char *slots = slot_scratch(sh);
     int h_c = 0;
 #pragma unroll
     for (int k = 0; k < kChunk / 32; ++k) {
@@ -587,7 +615,7 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
 }
 
 // kAllShared: the whole tree fits the shared-memory cache (no global-memory path in the walk)
-template <bool kAllShared, int kFlatOnly, bool kGrid>
+template <bool kAllShared, int kFlatOnly>
 __global__ void __launch_bounds__(kWalkWarps * 32, kFlatOnly ? TRC_WALK_MIN_CTAS_FLAT : TRC_WALK_MIN_CTAS)
 nearest_hit_walk_kernel(WalkParams p) {
     extern __shared__ __align__(16) unsigned char walk_smem[];
@@ -606,10 +634,6 @@ nearest_hit_walk_kernel(WalkParams p) {
             cache[k] = __ldg(p.pair_a + k);
             cache[p.n_cached + k] = __ldg(p.pair_b + k);
         }
-        if (kGrid) {                          // the grid's occupancy bits follow the pair cache (constant data too)
-            uint32_t *gb = reinterpret_cast<uint32_t *>(walk_smem + sizeof(WalkShared) + 32 * (size_t)p.n_cached);
-            for (int k = threadIdx.x; k < p.g.n_words; k += blockDim.x) gb[k] = __ldg(p.g.bits + k);
-        }
     }
     pdl_wait();
     pdl_trigger();
@@ -622,7 +646,6 @@ nearest_hit_walk_kernel(WalkParams p) {
     unsigned pair_a_smem = (unsigned)__cvta_generic_to_shared(walk_smem + sizeof(WalkShared));
     unsigned pair_b_smem = pair_a_smem + 16u * (unsigned)p.n_cached;             // pair_b follows pair_a
     asm volatile("" : "+r"(pair_a_smem), "+r"(pair_b_smem));   // keep them in registers (else recomputed per visit)
-    const uint32_t *grid_bits = reinterpret_cast<const uint32_t *>(walk_smem + sizeof(WalkShared) + 32 * (size_t)p.n_cached);
     const int root_count = p.has_tree ? (int)TRC_META_COUNT(p.root_meta) : 7;   // 0 inner, 1..4 leaf, 7 nothing
     // entry payload of a tree that is a single leaf: list position, or the surface index itself for one surface
     const unsigned root_first = root_count == 1 ? (unsigned)__ldg(&p.cand[TRC_META_INDEX(p.root_meta)])
@@ -649,7 +672,11 @@ nearest_hit_walk_kernel(WalkParams p) {
 #endif
     auto fetch_chunk = [&]() -> int64_t {
         unsigned long long c = 0;
-        if (lane == 0) c = atomicAdd(p.chunk_counter, 1ULL);
+        if (lane == 0) {
+            c = atomicAdd(p.chunk_counter, 1ULL);
+            // after the shadow-grid kernel: only the chunks it left over, by id (past the list: past the bundle)
+            if (p.chunk_list) c = c < *p.chunk_list_n ? (unsigned long long)p.chunk_list[c] : (1ULL << 40);
+        }
         c = __shfl_sync(full, c, 0);
         if (lane == 0) sh.fifo[fifo_w & 3] = (long long)c;
         ++fifo_w;
@@ -767,56 +794,11 @@ nearest_hit_walk_kernel(WalkParams p) {
                 RayF nr;
                 unsigned nsigns = 0u;
                 bool surv = false;
-                const double *src = &sh.ring[(ring_r - 1) & (kRing - 1)][0][(next & (kBatch - 1)) + lane];
-                bool walk_it = valid;          // the ray takes the tree walk (always, without a shadow grid)
-                if (kGrid) {
-                    // ---- shadow grid: rays inside the slope box are keyed by their crossing of the plane x_n = h0
-                    bool look = false;
-                    unsigned cell = 0u;
-                    if (valid) {
-                        const float vn = (float)src[p.g.axis_n * kBatch], va = (float)src[p.g.axis_a * kBatch],
-                                    vb = (float)src[p.g.axis_b * kBatch];
-                        const float dn = (float)src[(3 + p.g.axis_n) * kBatch], da = (float)src[(3 + p.g.axis_a) * kBatch],
-                                    db = (float)src[(3 + p.g.axis_b) * kBatch];
-                        const float inv = rcp_approx(dn);
-                        const bool in_box = dn * p.g.sgn > 0.0f && fabsf(fmaf(da, inv, -p.g.t0a)) <= p.g.da &&
-                                            fabsf(fmaf(db, inv, -p.g.t0b)) <= p.g.db &&
-                                            fmaxf(fmaxf(fabsf(va), fabsf(vb)), fabsf(vn)) <= p.g.rmax;
-                        if (in_box) {
-                            walk_it = false;
-                            const float t = (p.g.h0 - vn) * inv;
-                            const float ca = (fmaf(t, da, va) - p.g.ga0) * p.g.inv_ca;
-                            const float cb = (fmaf(t, db, vb) - p.g.gb0) * p.g.inv_cb;
-                            if (ca >= 0.0f && cb >= 0.0f && ca < (float)p.g.nx && cb < (float)p.g.ny) {
-                                cell = (unsigned)((int)cb * p.g.nx + (int)ca);
-                                look = (grid_bits[cell >> 5] >> (cell & 31u)) & 1u;
-                            }
-                        }
-                    }
-                    const unsigned ml = __ballot_sync(full, look);
-                    if (ml) {
-                        const unsigned ent = look ? __ldg(p.g.cells + cell) : 0u;
-                        const int cnt = (int)(ent & 255u);
-                        const unsigned pay = ent >> 8;
-                        const int maxc = __reduce_max_sync(full, cnt);
-                        for (int k = 0; k < maxc; ++k) {
-                            const bool has = k < cnt;
-                            const unsigned m = __ballot_sync(full, has);
-                            if (has) {
-                                const unsigned s_c = cnt == 1 ? pay : (unsigned)__ldg(p.g.list + pay + k);
-                                sh.queue[qn + __popc(m & lt_mask)] = ((unsigned)j << 24) | s_c;
-                            }
-                            qn += __popc(m);
-                            if (qn >= 32) qn = flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, false);
-                        }
-                    }
-                }
-                if (!kGrid || __any_sync(full, walk_it)) {
-                    if (walk_it) {
-                        V3 v = mk(src[0], src[kBatch], src[2 * kBatch]);
-                        V3 d = mk(src[3 * kBatch], src[4 * kBatch], src[5 * kBatch]);
-                        surv = ray_setup(v, d, p, nr, nsigns) && root_count != 7 && !(p.debug & 2);
-                    }
+                if (valid) {
+                    const double *src = &sh.ring[(ring_r - 1) & (kRing - 1)][0][(next & (kBatch - 1)) + lane];
+                    V3 v = mk(src[0], src[kBatch], src[2 * kBatch]);
+                    V3 d = mk(src[3 * kBatch], src[4 * kBatch], src[5 * kBatch]);
+                    surv = ray_setup(v, d, p, nr, nsigns) && root_count != 7 && !(p.debug & 2);
                 }
                 next += 32;
                 unsigned m = __ballot_sync(full, surv);
@@ -955,23 +937,174 @@ nearest_hit_walk_kernel(WalkParams p) {
 #endif
 }
 
+
+// ------------------------------------------------------------------ shadow grid (coherent bundles)
+// Nearest hit of a bundle whose rays lie in the slope box of the scene's shadow grid (common.cuh TrcShadowGrid,
+// built by shadow_grid.cu): no tree, no per-ray walk state.  A warp owns a chunk of 256 consecutive rays; a lane
+// keys its ray by the point where it crosses the grid's reference plane, tests the cell's bit in shared memory
+// (two thirds of the rays of a heliostat field end here), fetches the cell's candidates and queues them; the
+// queue is tested 32 at a time in float64 by the same code as the tree walk's stage C, and the chunk's hits are
+// emitted in ascending ray order.  A chunk with a ray outside the slope box (or too far out for the float32 key) is
+// left untouched and listed for the tree-walk kernel, which is launched right after over that list -- so a wrong
+// or partial hint costs time, never correctness.
+#ifndef TRC_GRID_MIN_CTAS
+#define TRC_GRID_MIN_CTAS 2
+#endif
+struct GridShared {
+    GridWarpShared w[kWalkWarps];
+    long long n_rays;
+    long long pad_;
+};
+
+// the float64 stage as ONE out-of-line call site: the key / lookup loop below stays small and keeps its registers
+template <int kFlatOnly>
+__device__ __noinline__ int grid_flush(GridWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane, int qn) {
+    return flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, true);
+}
+
+struct GridRay { double vn, va, vb, dn, da, db; };
+
+template <int kFlatOnly>
+__global__ void __launch_bounds__(kWalkWarps * 32, TRC_GRID_MIN_CTAS)
+nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
+    extern __shared__ __align__(16) unsigned char grid_smem[];
+    GridShared &S = *reinterpret_cast<GridShared *>(grid_smem);
+    GridWarpShared &sh = S.w[threadIdx.x >> 5];
+    const uint32_t *bits = reinterpret_cast<const uint32_t *>(grid_smem + sizeof(GridShared));
+    const int lane = threadIdx.x & 31;
+    const unsigned full = 0xffffffffu;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    {
+        uint32_t *dst = reinterpret_cast<uint32_t *>(grid_smem + sizeof(GridShared));
+        for (int k = threadIdx.x; k < p.g.n_words; k += blockDim.x) dst[k] = __ldg(p.g.bits + k);   // constant data
+    }
+    pdl_wait();
+    pdl_trigger();
+    if (threadIdx.x == 0) S.n_rays = p.ctl ? p.ctl->n_in : (long long)p.n;
+    if (lane == 0) {
+        if (p.ctl) { sh.vert = p.ctl->in.V; sh.dir = p.ctl->in.D; sh.energy = p.ctl->in.E; sh.ld = p.ctl->in.ld; }
+        else { sh.vert = p.vert; sh.dir = p.dir; sh.energy = p.sink.energy; sh.ld = p.ld; }
+    }
+    __syncthreads();
+    const long long n_rays = S.n_rays;
+    // the six rows in the grid's axis order (normal, a, b)
+    const double *vn_p = sh.vert + p.g.axis_n * sh.ld, *va_p = sh.vert + p.g.axis_a * sh.ld, *vb_p = sh.vert + p.g.axis_b * sh.ld;
+    const double *dn_p = sh.dir + p.g.axis_n * sh.ld, *da_p = sh.dir + p.g.axis_a * sh.ld, *db_p = sh.dir + p.g.axis_b * sh.ld;
+    auto load_ray = [&](int64_t ray, bool ok) {
+        GridRay r = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        if (ok) { r.vn = vn_p[ray]; r.va = va_p[ray]; r.vb = vb_p[ray]; r.dn = dn_p[ray]; r.da = da_p[ray]; r.db = db_p[ray]; }
+        return r;
+    };
+    unsigned long long c_next = 0;
+    if (lane == 0) c_next = atomicAdd(p.chunk_counter, 1ULL);
+    c_next = __shfl_sync(full, c_next, 0);
+    for (;;) {
+        const unsigned long long c = c_next;
+        const int64_t chunk_base = (int64_t)c * kChunk;
+        if (chunk_base >= n_rays) break;
+        const int chunk_n = (int)min((int64_t)kChunk, (int64_t)n_rays - chunk_base);
+        GridRay cur = load_ray(chunk_base + lane, lane < chunk_n);
+        if (lane == 0) c_next = atomicAdd(p.chunk_counter, 1ULL);      // the next chunk's id arrives while this one runs
+        for (int i = lane; i < kChunk; i += 32) { sh.best_t[i] = TRC_INF_BITS; sh.best_s[i] = INT_MAX; }
+        if (lane == 0) sh.q2n = 0;
+        __syncwarp();
+        int qn = 0;
+        bool dirty = false;
+        unsigned ent_prev = 0u;            // cell entry fetched for the previous group's ray of this lane
+        int next = 0;
+        // software pipeline over the chunk's groups of 32 rays: [load rays of g+1] [key + cell fetch of g] [queue g-1].
+        // The float64 stage is called from OUTSIDE the pipelined loop (which leaves when the queue cannot take another
+        // group), so that the loop carries no call and keeps its state in registers.
+        for (;;) {
+            bool need_flush = false;
+#pragma unroll 1
+            for (; next < chunk_n + 32; next += 32) {
+                // room for the previous group's candidates (and the unbounded surfaces of this one)?
+                const int cnt = (int)(ent_prev & 255u);
+                int incl = cnt;
+                const unsigned mq = __ballot_sync(full, cnt != 0);
+                const bool simple = __all_sync(full, cnt <= 1);
+                if (mq && !simple) {
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) { const int x = __shfl_up_sync(full, incl, o); if (lane >= o) incl += x; }
+                }
+                const int tot = !mq ? 0 : (simple ? __popc(mq) : __shfl_sync(full, incl, 31));
+                const int want = tot + 32 * p.n_unbounded;
+                if (want > kGridQueue) { dirty = true; break; }        // absurdly crowded cells: leave it to the walk
+                if (qn + want > kGridQueue) { need_flush = true; break; }
+                const int j = next + lane;
+                const bool valid = j < chunk_n;
+                const GridRay nxt = load_ray(chunk_base + j + 32, j + 32 < chunk_n);
+                unsigned ent = 0u;
+                bool out = false;
+                if (valid) {
+                    const float vn = (float)cur.vn, va = (float)cur.va, vb = (float)cur.vb;
+                    const float dn = (float)cur.dn, da = (float)cur.da, db = (float)cur.db;
+                    const float inv = rcp_approx(dn);
+                    const bool in_box = dn * p.g.sgn > 0.0f && fabsf(fmaf(da, inv, -p.g.t0a)) <= p.g.da &&
+                                        fabsf(fmaf(db, inv, -p.g.t0b)) <= p.g.db &&
+                                        fmaxf(fmaxf(fabsf(va), fabsf(vb)), fabsf(vn)) <= p.g.rmax;
+                    out = !in_box;
+                    const float t = (p.g.h0 - vn) * inv;
+                    const float ca = (fmaf(t, da, va) - p.g.ga0) * p.g.inv_ca;
+                    const float cb = (fmaf(t, db, vb) - p.g.gb0) * p.g.inv_cb;
+                    // float -> int saturates and NaN gives 0: a ray outside the grid fails the unsigned compare
+                    const unsigned ia = (unsigned)__float2int_rd(ca), ib = (unsigned)__float2int_rd(cb);
+                    if (in_box && ia < (unsigned)p.g.nx && ib < (unsigned)p.g.ny) {
+                        const unsigned cell = ib * (unsigned)p.g.nx + ia;
+                        if ((bits[cell >> 5] >> (cell & 31u)) & 1u) ent = __ldg(p.g.cells + cell);
+                    }
+                }
+                if (__any_sync(full, out)) { dirty = true; break; }
+                // ---- queue the candidates of the previous group (its cell entries have landed by now)
+                if (mq) {
+                    const unsigned tag = (unsigned)(j - 32) << 24;
+                    const unsigned pay = ent_prev >> 8;
+                    const int pos = qn + (simple ? __popc(mq & lt_mask) : incl - cnt);
+                    if (cnt == 1) sh.queue[pos] = tag | pay;                 // the surface index itself
+                    else {
+#pragma unroll 1
+                        for (int k = 0; k < cnt; ++k) sh.queue[pos + k] = tag | (unsigned)__ldg(p.g.list + pay + k);
+                    }
+                    qn += tot;
+                }
+                // surfaces without a finite box are candidates of every ray (accel_tree.py:59-73)
+                if (p.n_unbounded && next < chunk_n) {
+                    const unsigned mv = __ballot_sync(full, valid);
+#pragma unroll 1
+                    for (int k = 0; k < p.n_unbounded; ++k) {
+                        const unsigned s_unb = (unsigned)__ldg(&p.cand[p.unbounded_first + k]);
+                        if (valid) sh.queue[qn + __popc(mv & lt_mask)] = ((unsigned)j << 24) | s_unb;
+                        qn += __popc(mv);
+                    }
+                }
+                ent_prev = ent;
+                cur = nxt;
+            }
+            if (!need_flush) break;
+            qn = grid_flush<kFlatOnly>(sh, p, chunk_base, lane, qn);
+        }
+        c_next = __shfl_sync(full, c_next, 0);
+        if (dirty) {
+            // leave the whole chunk to the tree walk (its kernel follows on the stream and writes the chunk's tables)
+            if (lane == 0) p.dirty_list[atomicAdd(p.dirty_count, 1ULL)] = (uint32_t)c;
+            __syncwarp();
+            continue;
+        }
+        grid_flush<kFlatOnly>(sh, p, chunk_base, lane, qn);
+        __syncwarp();
+        if (p.sink.hit_surf)
+            for (int i = lane; i < chunk_n; i += 32)
+                p.sink.hit_surf[chunk_base + i] = sh.best_t[i] == TRC_INF_BITS ? -1 : sh.best_s[i];
+        if (p.sink.records) emit_chunk_hits(sh, p, (int64_t)c, chunk_base, lane);
+        __syncwarp();
+    }
+}
+
 }  // namespace
 
-// pairs of the tree cached in shared memory: a tree that fits is cached whole; of a larger one only the top 256
-// pairs, so that two CTAs still fit an SM
-static int walk_cached_pairs(const TrcScene *sc) {
-    int n_cached = sc->n_pairs <= kSmemPairs ? sc->n_pairs : kSmemPairs / 2;
-    return (n_cached + 7) & ~7;
-}
-
-// Shared memory left for a shadow grid's occupancy bits next to this scene's per-warp blocks and tree cache, with
-// two CTAs per SM (228 KB per SM, 1 KB reserved per CTA)
-int trc_walk_grid_word_budget(const TrcScene *sc) {
-    const long per_cta = (228 * 1024) / TRC_WALK_MIN_CTAS_FLAT - 1024 - 256;
-    long spare = per_cta - (long)sizeof(WalkShared) - 32L * walk_cached_pairs(sc);
-    if (spare < 0) spare = 0;
-    return (int)std::min<long>(spare / 4, kGridMaxWords);
-}
+// 32-bit words of shared memory the shadow-grid kernel can give to a grid's occupancy bits
+int trc_walk_grid_word_budget(const TrcScene *) { return kGridMaxWords; }
 
 // dyn != nullptr: device-driven trace (trace.cu).  `n` is then the CAPACITY of the input bundle (it
 // sizes the grid), the real count is read from dyn->n_ptr by the kernels, the work counter and the
@@ -996,13 +1129,9 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     if ((sc->n_nodes == 0 && sc->n_unbounded == 0) || !sc->d_chunk_counter || !sc->d_cand)
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: use_bvh set but no BVH uploaded%s");
     typedef void (*WalkKernel)(WalkParams);
-    static const WalkKernel kernels[12] = {
-        nearest_hit_walk_kernel<false, 0, false>, nearest_hit_walk_kernel<true, 0, false>,
-        nearest_hit_walk_kernel<false, 1, false>, nearest_hit_walk_kernel<true, 1, false>,
-        nearest_hit_walk_kernel<false, 2, false>, nearest_hit_walk_kernel<true, 2, false>,
-        nearest_hit_walk_kernel<false, 0, true>, nearest_hit_walk_kernel<true, 0, true>,
-        nearest_hit_walk_kernel<false, 1, true>, nearest_hit_walk_kernel<true, 1, true>,
-        nearest_hit_walk_kernel<false, 2, true>, nearest_hit_walk_kernel<true, 2, true>};
+    static const WalkKernel kernels[6] = {nearest_hit_walk_kernel<false, 0>, nearest_hit_walk_kernel<true, 0>,
+                                          nearest_hit_walk_kernel<false, 1>, nearest_hit_walk_kernel<true, 1>,
+                                          nearest_hit_walk_kernel<false, 2>, nearest_hit_walk_kernel<true, 2>};
     static int g_refill_at = -1;
     static bool attr_set[64] = {};       // cudaFuncSetAttribute is per device
     if (sc->device < 0 || sc->device >= 64) return fail(TRC_ERR_BAD_ARGUMENT, "trc_nearest_hit: device index out of range%s");
@@ -1010,20 +1139,19 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
         const char *env = getenv("TRC_WALK_REFILL_AT");      // tuning knob (0..31)
         g_refill_at = 24;
         if (env) { int v = atoi(env); if (v >= 0 && v < 32) g_refill_at = v; }
-        for (int k = 0; k < 12; ++k)
+        for (int k = 0; k < 6; ++k)
             TRC_CUDA(cudaFuncSetAttribute(kernels[k], cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)(sizeof(WalkShared) + 32 * kSmemPairs + (k >= 6 ? 4 * kGridMaxWords : 0))));
+                                          (int)(sizeof(WalkShared) + 32 * kSmemPairs)));
         attr_set[sc->device] = true;
     }
     // a tree that fits is cached whole; of a larger one only the top 256 pairs, so that two CTAs still fit an SM
-    const int n_cached = walk_cached_pairs(sc);
-    // use_bvh == 2: rays inside the slope box of the scene's shadow grid skip the walk (a request without a grid
-    // set is an ordinary walk)
-    const bool grid = use_bvh == 2 && sc->has_grid;
-    const size_t smem = sizeof(WalkShared) + 32 * (size_t)n_cached + (grid ? 4 * (size_t)sc->grid.n_words : 0);
-    const int variant = ((sc->n_pairs <= kSmemPairs ? 1 : 0) | (sc->flat_only ? (sc->d_tri64 ? 4 : 2) : 0)) + (grid ? 6 : 0);
+    int n_cached = sc->n_pairs <= kSmemPairs ? sc->n_pairs : kSmemPairs / 2;
+    n_cached = (n_cached + 7) & ~7;
+    const size_t smem = sizeof(WalkShared) + 32 * (size_t)n_cached;
+    const int variant = (sc->n_pairs <= kSmemPairs ? 1 : 0) | (sc->flat_only ? (sc->d_tri64 ? 4 : 2) : 0);
     WalkParams p;
-    p.g = grid ? sc->grid : TrcShadowGrid();
+    p.g = TrcShadowGrid();
+    p.dirty_list = nullptr; p.dirty_count = nullptr; p.chunk_list = nullptr; p.chunk_list_n = nullptr;
     p.surfs = sc->d_surfaces;
     p.pool = sc->d_tables;
     p.tri32 = sc->d_tri32;
@@ -1045,6 +1173,63 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
     p.chunk_counter = dyn ? &dyn->chunk_counter : sc->d_chunk_counter;
     int64_t n_chunks = (n + kChunk - 1) / kChunk;
     int64_t blocks = (n_chunks + kWalkWarps - 1) / kWalkWarps;
+    if (use_bvh == 2 && sc->has_grid) {
+        // ---- coherent bundle: the shadow-grid kernel takes every chunk whose rays all lie in the grid's slope box and
+        // lists the others; the tree walk below then runs over that list only (a request without a grid set is an
+        // ordinary walk)
+        typedef void (*GridKernel)(WalkParams);
+        static const GridKernel gkernels[3] = {nearest_hit_grid_kernel<0>, nearest_hit_grid_kernel<1>,
+                                               nearest_hit_grid_kernel<2>};
+        static bool gattr_set[64] = {};
+        if (!gattr_set[sc->device]) {
+            for (int k = 0; k < 3; ++k)
+                TRC_CUDA(cudaFuncSetAttribute(gkernels[k], cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)(sizeof(GridShared) + 4 * kGridMaxWords)));
+            gattr_set[sc->device] = true;
+        }
+        TrcScene *scw = const_cast<TrcScene *>(sc);
+        if (!scw->d_dirty_counters) TRC_CUDA(cudaMalloc(&scw->d_dirty_counters, 2 * sizeof(unsigned long long)));
+        if (scw->dirty_cap < n_chunks) {
+            TRC_CUDA(cudaStreamSynchronize(st));             // an earlier launch on this stream may still use the list
+            cudaFree(scw->d_dirty);
+            scw->d_dirty = nullptr; scw->dirty_cap = 0;
+            TRC_CUDA(cudaMalloc(&scw->d_dirty, (size_t)n_chunks * sizeof(uint32_t)));
+            scw->dirty_cap = n_chunks;
+        }
+        TRC_CUDA(cudaMemsetAsync(scw->d_dirty_counters, 0, 2 * sizeof(unsigned long long), st));
+        const int gvariant = sc->flat_only ? (sc->d_tri64 ? 2 : 1) : 0;
+        const size_t gsmem = sizeof(GridShared) + 4 * (size_t)sc->grid.n_words;
+        int gocc = sc->grid_occ[gvariant];
+        if (gocc <= 0) {
+            TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&gocc, gkernels[gvariant], kWalkWarps * 32, gsmem));
+            if (gocc < 1) gocc = 1;
+            scw->grid_occ[gvariant] = gocc;
+        }
+        WalkParams g = p;
+        g.g = sc->grid;
+        g.dirty_list = scw->d_dirty; g.dirty_count = scw->d_dirty_counters;
+        int64_t gblocks = std::min<int64_t>(blocks, (int64_t)sc->num_sms * gocc);
+        if (dyn) {
+            TRC_CUDA(launch_pdl(gkernels[gvariant], dim3((unsigned)gblocks), dim3(kWalkWarps * 32), gsmem, st, g));
+        } else {
+            TRC_CUDA(cudaMemsetAsync(sc->d_chunk_counter, 0, sizeof(unsigned long long), st));
+            gkernels[gvariant]<<<(unsigned)gblocks, kWalkWarps * 32, gsmem, st>>>(g);
+        }
+        int rc = check_launch("nearest_hit_grid");
+        if (rc != TRC_OK) return rc;
+        // the walk that follows: chunk ids from the list, its own work counter
+        p.chunk_list = scw->d_dirty; p.chunk_list_n = scw->d_dirty_counters;
+        p.chunk_counter = scw->d_dirty_counters + 1;
+        int occ2 = sc->walk_occ[variant];
+        if (occ2 <= 0) {
+            TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, kernels[variant], kWalkWarps * 32, smem));
+            if (occ2 < 1) occ2 = 1;
+            scw->walk_occ[variant] = occ2;
+        }
+        int64_t wblocks = std::min<int64_t>(blocks, (int64_t)sc->num_sms * occ2);
+        TRC_CUDA(launch_pdl(kernels[variant], dim3((unsigned)wblocks), dim3(kWalkWarps * 32), smem, st, p));
+        return check_launch("nearest_hit_walk");
+    }
     int occ = sc->walk_occ[variant];
     if (occ <= 0) {
         TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernels[variant], kWalkWarps * 32, smem));

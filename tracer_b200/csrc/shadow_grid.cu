@@ -89,7 +89,7 @@ void free_grid(TrcScene *sc) {
     sc->d_grid_list = nullptr;
     sc->has_grid = false;
     sc->grid = TrcShadowGrid();
-    for (int k = 6; k < 12; ++k) sc->walk_occ[k] = 0;      // occupancy depends on the grid's shared-memory share
+    for (int k = 0; k < 3; ++k) sc->grid_occ[k] = 0;       // occupancy depends on the grid's shared-memory share
 }
 
 }  // namespace
@@ -111,7 +111,7 @@ extern "C" int trc_scene_set_shadow_grid(TrcScene *sc, int32_t n_boxes, const do
     len = std::sqrt(len);
     if (!(len > 0.0) || !std::isfinite(len)) return TRC_OK;
     for (int k = 0; k < 3; ++k) d0[k] = direction[k] / len;
-    const int max_words = std::min(trc_walk_grid_word_budget(sc), 8192);
+    const int max_words = trc_walk_grid_word_budget(sc);
     if (max_words < 64) return TRC_OK;           // no shared memory to spare next to this scene's tree cache
     for (int i = 0; i < n_boxes; ++i)
         if (surface_ids[i] < 0 || surface_ids[i] >= (1 << 22))

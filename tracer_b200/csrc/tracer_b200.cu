@@ -105,6 +105,8 @@ extern "C" int trc_scene_destroy(TrcScene *sc) {
     cudaFree(sc->d_leaf_surfaces);
     cudaFree(sc->d_unbounded);
     trc_scene_free_shadow_grid(sc);
+    cudaFree(sc->d_dirty);
+    cudaFree(sc->d_dirty_counters);
     if (sc->h_pinned) cudaFreeHost(sc->h_pinned);
     if (sc->ev_walk[0]) cudaEventDestroy(sc->ev_walk[0]);
     if (sc->ev_walk[1]) cudaEventDestroy(sc->ev_walk[1]);

@@ -311,6 +311,68 @@ def c9_refractive(T, n_rays=2000):
     return asm, source
 
 
+def c10_polychromatic(T, n_rays=2000, n_samples=5):
+    """Rays carrying spectra (bundle properties ``wavelengths`` and ``spectra``, both (W, n)): a floor with the
+    polychromatic directional optics and Absorber + Polychromatic + Location accountants, a wall with the same
+    optics and the Polychromatic accountant alone, a specular plate and a diffuse lid that pass the spectra on
+    unchanged (optics_callables.py:393-425, 1825-1848)."""
+    oc = T.optics_callables
+    thetas = np.linspace(0., np.pi / 2., 9)
+    wls = np.linspace(0.25e-6, 3.0e-6, 14)
+    table = 0.15 + 0.7 * np.outer(np.cos(thetas) ** 0.5, np.linspace(1., 0.35, 14))
+    poly = oc.Lambertian_directional_axisymmetric_piecewise_PolychromaticAbsorberPolychromaticLocation
+    poly2 = oc.Lambertian_directional_axisymmetric_piecewise_PolychromaticPolychromatic
+    objs = [
+        T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(4., 4.), poly(thetas, table, wls))]),
+        T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(4., 2.), poly2(thetas, table[::-1], wls))],
+                                 transform=np.dot(T.spatial_geometry.translate(2., 0., 1.), T.spatial_geometry.roty(-np.pi / 2.))),
+        T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(4., 2.), oc.ReflectiveReceiver(0.2))],
+                                 transform=np.dot(T.spatial_geometry.translate(-2., 0., 1.), T.spatial_geometry.roty(np.pi / 2.))),
+        T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(4., 4.), oc.LambertianPolychromatic(0.3))],
+                                 transform=np.dot(T.spatial_geometry.translate(0., 0., 2.), T.spatial_geometry.rotx(np.pi))),
+    ]
+    asm = T.assembly.Assembly(objects=objs)
+
+    def source():
+        direction = np.r_[0.35, 0.1, -1.]
+        direction = direction / np.sqrt(np.sum(direction ** 2))
+        b = T.sources.disk_bundle(n_rays, np.c_[[-0.3, 0., 1.9]], direction, 1.2, 0.05, flux=1000.)
+        # every ray samples its own wavelengths (sorted, inside the table's range) and a smooth spectrum
+        wl = np.sort(np.random.uniform(0.3e-6, 2.8e-6, size=(n_samples, n_rays)), axis=0)
+        spectra = (1. + 0.5 * np.sin(wl * 3e6)) * np.random.uniform(0.5, 1.5, size=n_rays) * b.get_energy() / 2.5e-6
+        return T.ray_bundle.RayBundle(vertices=b.get_vertices(), directions=b.get_directions(),
+                                      energy=b.get_energy(), wavelengths=wl, spectra=spectra)
+    return asm, source
+
+
+def c11_bifacial(T, n_rays=2000):
+    """BiFacial optics managers (optics_callables.py:1877-1924) on plates that are hit from both sides: a tilted
+    plate diffuse in front / specular with slope error at the back (both sides with accountants), a plate
+    specular in front / absorbing at the back, inside a diffuse box (floor + lid)."""
+    oc = T.optics_callables
+    thetas = np.linspace(0., np.pi / 2., 6)
+    abs_th = np.linspace(0.1, 0.6, 6)
+    two_a = oc.BiFacial(oc.LambertianReceiver(0.25), oc.RealReflectiveReceiver(0.1, 3e-3, True))
+    two_b = oc.BiFacial(oc.ReflectiveDetector(0.15), oc.Lambertian_directional_axisymmetric_piecewiseAbsorber(thetas, abs_th))
+    two_c = oc.BiFacial(oc.Reflective(0.05), oc.LambertianSpecular(0.3, 0.4))
+    objs = [
+        T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(2., 2.), two_a)],
+                                 transform=np.dot(T.spatial_geometry.translate(-0.8, 0., 1.), T.spatial_geometry.roty(0.9))),
+        T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(2., 2.), two_b)],
+                                 transform=np.dot(T.spatial_geometry.translate(0.9, 0., 1.1), T.spatial_geometry.roty(-1.1))),
+        T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RoundPlateGM(0.7), two_c)],
+                                 transform=np.dot(T.spatial_geometry.translate(0., 0.2, 1.55), T.spatial_geometry.rotx(0.3))),
+        T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(6., 6.), oc.LambertianReceiver(0.2))]),
+        T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(6., 6.), oc.LambertianReceiver(0.2))],
+                                 transform=np.dot(T.spatial_geometry.translate(0., 0., 2.2), T.spatial_geometry.rotx(np.pi))),
+    ]
+    asm = T.assembly.Assembly(objects=objs)
+
+    def source():
+        return T.sources.disk_bundle(n_rays, np.c_[[0., 0., 0.05]], np.r_[0., 0., 1.], 1.6, np.pi / 3., flux=1000.)
+    return asm, source
+
+
 def _optical_constants(T):
     """The reference keeps its materials outside the tracer package."""
     if T.pkg == 'tracer':

@@ -121,6 +121,45 @@ class Lambertian_directional_axisymmetric_piecewise_spectral(_OpticsDescription)
         self.absorptance = np.reshape(absorptance, (len(self.thetas), len(self.wavelengths)))
 
 
+class Lambertian_directional_axisymmetric_piecewise_Polychromatic(_OpticsDescription):
+    """Diffuse; every ray carries a spectrum (bundle properties ``wavelengths`` and ``spectra``, both (W, n)) whose
+    W samples are each absorbed with the absorptance bilinear in (incidence angle, wavelength); the outgoing energy
+    is the trapezoid integral of the outgoing spectrum over the ray's wavelengths (:393-425)."""
+
+    def __init__(self, thetas, absorptance, wavelengths):
+        self.thetas, self.wavelengths = np.unique(thetas), np.unique(wavelengths)
+        self.absorptance = np.reshape(absorptance, (len(self.thetas), len(self.wavelengths)))
+
+
+class BiFacial(object):
+    """Two optics managers on one surface: rays travelling along the surface's +z ("up", geometry_manager.py:29-34)
+    meet ``OpticsCallable_back``, the others ``OpticsCallable_front`` (:1877-1924).  As in the reference, each
+    side's manager processes ALL the rays that hit the surface whenever one of them is on its side -- so its
+    accountants record every hit with that side's optics -- and only its own side's children are kept, the back
+    ones first.  Not part of the accountant class factory (:2086)."""
+
+    def __init__(self, OpticsCallable_front, OpticsCallable_back):
+        self.OpticsCallable_front = OpticsCallable_front
+        self.OpticsCallable_back = OpticsCallable_back
+
+    def __call__(self, geometry, rays, selector):
+        raise TypeError("BiFacial is a description; optics run on the GPU through TracerEngine.ray_tracer (no CPU path)")
+
+    def get_all_hits(self):
+        out = []
+        for side in (self.OpticsCallable_front, self.OpticsCallable_back):
+            try:
+                out.append(side.get_all_hits())
+            except Exception:                       # the reference's bare except (:1905-1912)
+                out.append([])
+        return tuple(out)
+
+    def reset(self):
+        # the reference calls side.reset(self) -- one argument too many -- inside try/except (:1916-1924): the
+        # sides are never reset through the BiFacial manager.  Reset them directly between traces.
+        pass
+
+
 class Lambertian_IAM(Lambertian):
     """Lambertian whose energy follows the Martin-Ruiz incidence-angle modifier (:303-318)."""
 
@@ -230,7 +269,8 @@ _BASE_OPTICS = {c.__name__: c for c in (
     Transparent, Reflective, Lambertian, Reflective_spectral, OneSidedReflective, RealReflective,
     OneSidedRealReflective, LambertianSpecular, Lambertian_directional_axisymmetric_piecewise,
     LambertianSpecular_directional_axisymmetric_piecewise,
-    Lambertian_directional_axisymmetric_piecewise_spectral)}
+    Lambertian_directional_axisymmetric_piecewise_spectral,
+    Lambertian_directional_axisymmetric_piecewise_Polychromatic)}
 
 # Optics of the reference without a GPU counterpart (DESIGN.md 4.4 gives the reason for each: the
 # scattering family, Reflective_IAM and SemiLambertian raise inside the reference itself; the others
@@ -239,8 +279,7 @@ _BASE_OPTICS = {c.__name__: c for c in (
 _UNSUPPORTED = (
     'Refractive', 'RefractiveAbsorbantHomogenous', 'RefractiveScattering',
     'RefractiveScatteringHomogenous', 'Scattering', 'ScatteringPeriodicBoundary',
-    'Absorbant', 'SemiLambertian', 'BiFacial', 'Reflective_IAM',
-    'Lambertian_directional_axisymmetric_piecewise_Polychromatic')
+    'Absorbant', 'SemiLambertian', 'Reflective_IAM')
 
 
 # ------------------------------------------------------------ accountants
@@ -283,7 +322,17 @@ class ScatteringAccountant(Accountant):
 
 
 class PolychromaticAccountant(Accountant):
+    """Per bounce: the (W, h) wavelengths of the outgoing rays in ``_wavelengths`` and the spectral power lost at the
+    hit (incoming minus outgoing spectra) in ``_spectra`` (:1825-1838).  ``get_data`` raises as the reference's does
+    (it reads ``_absorbed``, which ``reset`` never creates, :1840-1848): read the two lists."""
     shorthand, field = 'Polychromatic', '_spectra'
+
+    def reset(self):
+        self._wavelengths = []
+        self._spectra = []
+
+    def get_data(self):
+        raise AttributeError("'PolychromaticAccountant' object has no attribute '_absorbed'")
 
 
 class SpectralAccountant(Accountant):
