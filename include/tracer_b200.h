@@ -126,6 +126,10 @@ typedef enum TrcOpticsKind {
 /* Surface flag bits. */
 #define TRC_F_ONE_SIDED   1u   /* OneSidedReflective / OneSidedRealReflective (:195,:492): E'=0 where d.up>0 */
 #define TRC_F_UNBOUNDED   2u   /* no finite AABB: tested for every ray, outside the BVH */
+#define TRC_F_POLY        8u   /* Lambertian_directional_axisymmetric_piecewise_Polychromatic (:393-425): the optics
+                                  kernel treats the surface as a Lambertian that absorbs nothing; trc_spectra then absorbs
+                                  each ray's spectrum sample by sample (table = thetas, then wavelengths and the
+                                  absorptance grid; op[6] = number of wavelengths) and integrates the energy */
 #define TRC_F_IAM         4u   /* Martin-Ruiz incidence-angle modifier (IAM.__call__ :277-282) replaces the
                                   energy of Lambertian_IAM :303 / RealReflective_IAM :320:
                                   E' = E (1 - abs) (1 - exp(-cos^c / a_r)) / (1 - exp(-1 / a_r)),
@@ -382,6 +386,36 @@ typedef struct TrcOpticsArgs {
     int64_t *d_out_ray_ids;
 } TrcOpticsArgs;
 int trc_optics(const TrcScene *scene, const TrcOpticsArgs *args, void *stream);
+
+/* Polychromatic rays: bundle properties `wavelengths` and `spectra`, both (W, n) (optics_callables.py:393-425,
+ * ray_bundle.py:65-100).  Runs after trc_optics on a scene without two-children optics and finishes each child
+ * slot q (child index == slot): copies the parent's W wavelengths, and writes the child's spectrum
+ *   - TRC_F_POLY surfaces: spectrum * (1 - absorptance(theta_in, wavelength_w)), bilinear as scipy's
+ *     RegularGridInterpolator (:403-412); the slot's energy becomes the trapezoid integral of the new spectrum
+ *     over the ray's wavelengths (numpy.trapz, :413), d_absorbed[q] the energy lost, d_cull[q] is re-decided;
+ *   - Reflective, RealReflective (and their one-sided forms), Lambertian: spectrum * (1 - absorptivity)
+ *     (:137, :173, :266); Lambertian_directional_axisymmetric_piecewise: spectrum * (1 - absorptance(theta_in)) (:358);
+ *   - every other kind: the parent's spectrum.
+ * d_lost_spectra (nullable, (W, ld_out)) receives parent minus child spectrum: what PolychromaticAccountant.count
+ * stores (:1835-1838).  d_normals / d_dirs_in: the accountant columns trc_optics wrote for the same slots.
+ * *d_n_cull must be zero on entry; it counts every slot whose final energy is <= min_energy. */
+typedef struct TrcSpectraArgs {
+    int64_t h;                        /* child slots */
+    int32_t n_samples;                /* W */
+    const int32_t *d_slot_surf;       /* (h,) surface of each slot */
+    const int64_t *d_parents;         /* (h,) parent ray of each slot */
+    const double *d_in_wavelengths, *d_in_spectra; int64_t ld_in;   /* (W, ld_in) of the incoming bundle */
+    const double *d_normals, *d_dirs_in; int64_t ld_cols;           /* (3, ld_cols) per slot */
+    double *d_out_wavelengths, *d_out_spectra; int64_t ld_out;      /* (W, ld_out) of the children */
+    double *d_energy;                 /* (h,) child energy: read (== parent energy on TRC_F_POLY surfaces), rewritten there */
+    double *d_absorbed;               /* (h,) nullable */
+    double *d_lost_spectra;           /* (W, ld_out) nullable */
+    int32_t *d_cull;                  /* (h,) */
+    int64_t *d_n_cull;
+    double min_energy;
+} TrcSpectraArgs;
+int trc_spectra(const TrcScene *scene, const TrcSpectraArgs *args, void *stream);
+
 
 /* The reference loop (tracer_engine.py:193-274) for up to TRC_TRACE_MAX_BOUNCES iterations, enqueued back to
  * back on the stream with NO host synchronisation in between: trc_trace_hits -> child order -> trc_optics

@@ -302,6 +302,17 @@ def apply_optics(opt, d, normals, energy, wavelengths, up, v_parent=None, hit=No
         else:
             continue
         one_sided = any(nm in ('OneSidedReflective', 'OneSidedRealReflective') for nm in names)
+        if spectra is not None and apply_optics.spectra_out is None:
+            # polychromatic bundle through a grey optics: the classes below scale the spectra like the energy
+            # (optics_callables.py:137, 173, 266, 358), the IAM classes are not restated, the others pass them on
+            if name in ('Reflective', 'OneSidedReflective', 'RealReflective', 'OneSidedRealReflective', 'Lambertian'):
+                apply_optics.spectra_out = spectra * (1. - base._abs)
+            elif name == 'Lambertian_directional_axisymmetric_piecewise':
+                apply_optics.spectra_out = spectra * (1. - N.interp(_theta_in(d, normals), base.thetas, base.abs_th))
+            elif name.endswith('_IAM') or name in ('LambertianAbsorbant', 'FresnelConductorHomogenous',
+                                                   'Reflective_spectral',
+                                                   'Lambertian_directional_axisymmetric_piecewise_spectral'):
+                raise NotImplementedError("oracle: %s with a polychromatic bundle" % name)
         break
     else:
         raise NotImplementedError("oracle: optics %s" % type(base).__name__)

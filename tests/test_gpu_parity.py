@@ -13,7 +13,8 @@ import pytest
 
 from tests import scenes
 from tests.golden.make_golden import TRACE_CASES, ZOO_RAYS, ZOO_SEED
-from tests.helpers import close, compare_tree, golden_accountants, load_golden
+from tests.helpers import (close, compare_tree, golden_accountant_lists, golden_accountants, golden_bifacial,
+                           load_golden)
 
 pytestmark = pytest.mark.gpu
 
@@ -42,6 +43,19 @@ def test_trace_matches_reference_golden(name, accel):
         assert len(mine) == len(arrays)
         for a, b in zip(mine, arrays):
             close(a, b, TIGHT, f'accountant of surface {s}')
+    for s, sides in golden_bifacial(gold).items():          # BiFacial managers: (front, back) lists
+        front, back = asm.get_surfaces()[s].get_optics_manager().get_all_hits()
+        for side, mine in (('front', front), ('back', back)):
+            arrays = sides.get(side, [])
+            assert len(mine) == len(arrays), f'BiFacial surface {s} {side}'
+            for a, b in zip(mine, arrays):
+                close(a, b, TIGHT, f'BiFacial surface {s} {side}')
+    for s, lists in golden_accountant_lists(gold).items():  # managers with a PolychromaticAccountant: raw lists
+        opt = asm.get_surfaces()[s].get_optics_manager()
+        with pytest.raises(AttributeError):                 # as in the reference (optics_callables.py:1840-1848)
+            opt.get_all_hits()
+        for (j, field), ref in lists.items():
+            close(np.hstack(getattr(opt.accountants[j], field)), ref, TIGHT, f'accountant {j} list {field} of surface {s}')
 
 
 @pytest.mark.parametrize('name', sorted(scenes.gm_zoo(T)))

@@ -28,6 +28,7 @@ ABI_VERSION = 13
 F_ONE_SIDED = 1
 F_UNBOUNDED = 2
 F_IAM = 4
+F_POLY = 8
 # enum TrcFluxCoord
 (FLUX_XY, FLUX_R_ATAN_XY, FLUX_R_ATAN_YX, FLUX_Z_PHI, FLUX_THETA_PHI) = range(5)
 BVH_MAX_LEAF = 4
@@ -66,6 +67,18 @@ class OpticsArgs(C.Structure):
         ("d_slot_surf", C.c_void_p), ("d_seg", C.c_void_p), ("d_child_off", C.c_void_p),
         ("d_ref_index", C.c_void_p), ("d_out_ref_index", C.c_void_p), ("d_n_void", C.c_void_p),
         ("d_ray_ids", C.c_void_p), ("ray_id_base", C.c_int64), ("d_out_ray_ids", C.c_void_p),
+    ]
+
+
+class SpectraArgs(C.Structure):
+    _fields_ = [
+        ("h", C.c_int64), ("n_samples", C.c_int32),
+        ("d_slot_surf", C.c_void_p), ("d_parents", C.c_void_p),
+        ("d_in_wavelengths", C.c_void_p), ("d_in_spectra", C.c_void_p), ("ld_in", C.c_int64),
+        ("d_normals", C.c_void_p), ("d_dirs_in", C.c_void_p), ("ld_cols", C.c_int64),
+        ("d_out_wavelengths", C.c_void_p), ("d_out_spectra", C.c_void_p), ("ld_out", C.c_int64),
+        ("d_energy", C.c_void_p), ("d_absorbed", C.c_void_p), ("d_lost_spectra", C.c_void_p),
+        ("d_cull", C.c_void_p), ("d_n_cull", C.c_void_p), ("min_energy", C.c_double),
     ]
 
 
@@ -128,6 +141,7 @@ SIGNATURES = {
     "trc_bvh_build": (C.c_int, [_P, _P, _I32, _I32, _P, _I32, C.POINTER(_I32), _P]),
     "trc_scene_set_bvh": (C.c_int, [_P, _P, _I32, _P, _I32, _P, _I32]),
     "trc_scene_set_shadow_grid": (C.c_int, [_P, _I32, _P, _P, _P, _P, C.c_double, C.POINTER(_I32)]),
+    "trc_spectra": (C.c_int, [_P, _P, _P]),
     "trc_scene_destroy": (C.c_int, [_P]),
     "trc_scene_num_surfaces": (_I32, [_P]),
     "trc_nearest_hit": (C.c_int, [_P, _I64, _P, _P, _I64, _I32, _P, _P]),

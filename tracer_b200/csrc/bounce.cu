@@ -364,6 +364,57 @@ bounce_close_kernel(CloseParams p) {
     }
 }
 
+// Polychromatic rays (trc_spectra): one thread per child slot, W samples each; see the header for the rules.
+__global__ void __launch_bounds__(256)
+spectra_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict__ tables, TrcSpectraArgs a) {
+    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool culled = false;
+    if (q < a.h) {
+        const TrcSurfaceRec *s = &surfs[a.d_slot_surf[q]];
+        const int64_t r = a.d_parents[q];
+        const int W = a.n_samples;
+        double factor = 1.0;
+        bool poly = (s->flags & TRC_F_POLY) != 0;
+        double th = 0.0;
+        if (poly || s->okind == TRC_O_LAMB_DIRECTIONAL) {
+            // incidence angle as the optics compute it: acos(|(d.n) n|)  (optics_callables.py:341-345, :405-409)
+            V3 n = mk(a.d_normals[q], a.d_normals[a.ld_cols + q], a.d_normals[2 * a.ld_cols + q]);
+            V3 d = mk(a.d_dirs_in[q], a.d_dirs_in[a.ld_cols + q], a.d_dirs_in[2 * a.ld_cols + q]);
+            double k = dot(d, n);
+            V3 vert = mk(k * n.x, k * n.y, k * n.z);
+            th = acos(sqrt(vert.x * vert.x + vert.y * vert.y + vert.z * vert.z));
+        }
+        if (!poly && !(s->flags & TRC_F_IAM)) {
+            if (s->okind == TRC_O_REFLECTIVE || s->okind == TRC_O_REAL_REFLECTIVE || s->okind == TRC_O_LAMBERTIAN)
+                factor = 1.0 - s->op[0];
+            else if (s->okind == TRC_O_LAMB_DIRECTIONAL)
+                factor = 1.0 - interp1(th, tables + s->table_off, tables + s->table_off + s->table_len, s->table_len);
+        }
+        double energy = 0.0, wl_prev = 0.0, sp_prev = 0.0;
+        for (int w = 0; w < W; ++w) {
+            const double wl = a.d_in_wavelengths[(int64_t)w * a.ld_in + r];
+            const double sp_in = a.d_in_spectra[(int64_t)w * a.ld_in + r];
+            double sp = sp_in * factor;
+            if (poly) sp = sp_in * (1.0 - interp2(th, wl, tables + s->table_off, s->table_len, (int)s->op[6]));
+            a.d_out_wavelengths[(int64_t)w * a.ld_out + q] = wl;
+            a.d_out_spectra[(int64_t)w * a.ld_out + q] = sp;
+            if (a.d_lost_spectra) a.d_lost_spectra[(int64_t)w * a.ld_out + q] = sp_in - sp;
+            if (w > 0) energy += (wl - wl_prev) * (sp + sp_prev) / 2.0;      // numpy.trapz: sum(diff(x) * (y[1:] + y[:-1]) / 2)
+            wl_prev = wl; sp_prev = sp;
+        }
+        double e = a.d_energy[q];
+        if (poly) {
+            if (a.d_absorbed) a.d_absorbed[q] = e - energy;
+            a.d_energy[q] = energy;
+            e = energy;
+        }
+        culled = e <= a.min_energy;
+        a.d_cull[q] = culled ? 1 : 0;
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, culled);
+    if ((threadIdx.x & 31) == 0 && m) atomicAdd(reinterpret_cast<unsigned long long *>(a.d_n_cull), (unsigned long long)__popc(m));
+}
+
 __global__ void __launch_bounds__(256)
 gather_rows_kernel(int64_t n_out, const int32_t *__restrict__ idx, int n_rows,
                    const double *__restrict__ in, int64_t ld_in, double *__restrict__ out, int64_t ld_out,
@@ -569,6 +620,18 @@ int trc_optics_dyn(const TrcScene *sc, const TrcOpticsArgs *a, const TrcOpticsDy
 
 extern "C" int trc_optics(const TrcScene *sc, const TrcOpticsArgs *a, void *stream) {
     return trc_optics_dyn(sc, a, nullptr, stream);
+}
+
+extern "C" int trc_spectra(const TrcScene *sc, const TrcSpectraArgs *a, void *stream) {
+    if (!sc || !a || a->h < 0 || a->n_samples < 1) return fail(TRC_ERR_BAD_ARGUMENT, "trc_spectra: bad argument%s");
+    if (a->h == 0) return TRC_OK;
+    if (!a->d_slot_surf || !a->d_parents || !a->d_in_wavelengths || !a->d_in_spectra || !a->d_normals || !a->d_dirs_in ||
+        !a->d_out_wavelengths || !a->d_out_spectra || !a->d_energy || !a->d_cull || !a->d_n_cull ||
+        a->ld_out < a->h || a->ld_cols < a->h)
+        return fail(TRC_ERR_BAD_ARGUMENT, "trc_spectra: null buffer or bad stride%s");
+    if (sc->has_split) return fail(TRC_ERR_UNSUPPORTED_KIND, "trc_spectra: scene with two-children optics%s");
+    spectra_kernel<<<(unsigned)((a->h + 255) / 256), 256, 0, (cudaStream_t)stream>>>(sc->d_surfaces, sc->d_tables, *a);
+    return check_launch("spectra");
 }
 
 extern "C" int trc_gather_rows(int64_t n_out, const int32_t *d_idx, int32_t n_rows, const double *d_in,

@@ -199,6 +199,8 @@ _ACC_FIELDS = {  # shorthand -> (list attribute on the accountant, source)
     'Directional': ('_directions', 'dirs_in'),
     'Normal': ('_normals', 'normals'),
     'Spectral': ('_wavelengths', 'wavelengths'),
+    # PolychromaticAccountant keeps two lists: the children's wavelengths and the spectra lost at the hit
+    'Polychromatic': ('_spectra', 'lost_spectra'),
 }
 
 
@@ -222,7 +224,24 @@ def _material_table(material):
 
 
 def _optics_record(opt):
-    """-> dict(okind, op, flags, table, accountants, draws)"""
+    """-> dict(okind, op, flags, table, accountants, draws); a BiFacial manager gives its front side's record
+    with the back side's under 'back'."""
+    if 'BiFacial' in _mro_names(opt):
+        sides = []
+        for side in (opt.OpticsCallable_front, opt.OpticsCallable_back):
+            if 'BiFacial' in _mro_names(side):
+                raise NotImplementedError("BiFacial inside BiFacial")
+            r = _optics_record(side)
+            if r['okind'] in (L.O_PERIODIC, L.O_REFRACTIVE):
+                raise NotImplementedError("two-children optics (periodic, refractive) inside BiFacial")
+            if r['okind'] == L.O_LAMB_PIECEWISE_SPEC:
+                raise NotImplementedError(
+                    "Lambertian_piecewise_Specular_directional_axisymmetric_piecewise inside BiFacial")
+            sides.append(r)
+        rec = dict(sides[0])
+        rec['back'] = sides[1]
+        rec['instance'] = opt
+        return rec
     accountants = []
     base = opt
     if hasattr(opt, 'accountants') and hasattr(opt, '_opt'):
@@ -233,6 +252,8 @@ def _optics_record(opt):
                 raise NotImplementedError(
                     f"accountant {type(a).__name__} of {type(opt).__name__} has no GPU counterpart")
             accountants.append((a,) + _ACC_FIELDS[sh])
+            if sh == 'Polychromatic':
+                accountants.append((a, '_wavelengths', 'wavelengths'))
     elif hasattr(opt, 'get_all_hits'):
         raise NotImplementedError(f"optics manager {type(opt).__name__}: unknown accounting wrapper")
     rec = dict(okind=None, op=[0.] * 8, flags=0, table=None, table_len=None, accountants=accountants,
@@ -246,7 +267,8 @@ def _optics_record(opt):
              'Lambertian_directional_axisymmetric_piecewise_spectral', 'Reflective_spectral',
              'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM', 'LambertianAbsorbant',
              'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise', 'PeriodicBoundary',
-             'FresnelConductorHomogenous', 'RefractiveHomogenous', 'RefractiveTransmissiveHomogenous')
+             'FresnelConductorHomogenous', 'RefractiveHomogenous', 'RefractiveTransmissiveHomogenous',
+             'Lambertian_directional_axisymmetric_piecewise_Polychromatic')
     for cls in type(base).__mro__:
         if cls.__name__ in known:
             break
@@ -355,6 +377,20 @@ def _optics_record(opt):
             rec['op'][1] = float(len(wl))
             rec['table'] = (np.asarray(th, float), np.concatenate([np.asarray(wl, float), np.ravel(val)]))
             rec['needs_wavelengths'] = True
+        elif name == 'Lambertian_directional_axisymmetric_piecewise_Polychromatic':
+            # the optics kernel sees a Lambertian that absorbs nothing (same draws, :415-416); trc_spectra absorbs
+            # the spectrum and integrates the energy
+            rec['okind'] = L.O_LAMBERTIAN
+            rec['op'][:2] = [0., np.pi / 2.]
+            rec['flags'] |= L.F_POLY
+            if hasattr(base, 'interpolator'):      # reference object: scipy RegularGridInterpolator
+                th, wl = [np.asarray(g, float) for g in base.interpolator.grid]
+                val = np.asarray(base.interpolator.values, float)
+            else:
+                th, wl, val = base.thetas, base.wavelengths, base.absorptance
+            rec['op'][6] = float(len(wl))
+            rec['table'] = (np.asarray(th, float), np.concatenate([np.asarray(wl, float), np.ravel(val)]))
+            rec['needs_spectra'] = True
         elif name == 'Reflective_spectral':
             rec['okind'] = L.O_REFLECTIVE_SPECTRAL
             rec['table'] = (np.asarray(base._wavelengths, float), np.asarray(base._absorptances, float))
@@ -403,6 +439,7 @@ class CompiledScene(object):
         self.surfaces = surfaces
         S = len(surfaces)
         recs = np.zeros(S, dtype=L.SURFACE_DTYPE)
+        self._back = {}                  # surface -> (okind, op, flags, table_off, table_len) of a BiFacial back side
         self._tables = []
         self._table_len = 0
         self.optics = []
@@ -432,18 +469,36 @@ class CompiledScene(object):
         for a, b, _ in self.mesh_segments:
             in_mesh[a:b] = True
         # surfaces whose accountants are fed one by one (TracerEngine._account); a mesh gets one chunk per bounce
-        self.account_list = [i for i in np.nonzero(~in_mesh)[0] if self.optics[i]['accountants']]
+        self.account_list = [i for i in np.nonzero(~in_mesh)[0]
+                             if self.optics[i]['accountants'] or self.optics[i].get('back', {}).get('accountants')]
         self.records = recs
+        # BiFacial managers: a second table of the same scene with the back sides' optics (same geometry, same pool)
+        self.has_bifacial = bool(self._back)
+        self.records_back = None
+        self.handle_back = None
+        if self.has_bifacial:
+            self.records_back = recs.copy()
+            self.bifacial_mask = np.zeros(S, dtype=bool)
+            for i, (okind, op, flags, toff, tlen) in self._back.items():
+                rb = self.records_back[i]
+                rb['okind'], rb['op'], rb['table_off'], rb['table_len'] = okind, op, toff, tlen
+                rb['flags'] = (int(recs[i]['flags']) & L.F_UNBOUNDED) | flags
+                self.bifacial_mask[i] = True
         self.tables = np.concatenate(tables) if tables else np.zeros(0)
         uniq = list({id(o): o for o in self.optics}.values())        # a mesh shares one record
+        uniq = uniq + [o['back'] for o in uniq if o.get('back')]
         self.needs_wavelengths = any(o['needs_wavelengths'] for o in uniq)
+        self.needs_spectra = any(o.get('needs_spectra') for o in uniq)
         self.has_accountants = any(o['accountants'] for o in uniq)
         self.children_per_hit = np.where((recs['okind'] == L.O_PERIODIC) | (recs['okind'] == L.O_REFRACTIVE),
                                          2, 1).astype(np.int64)
         self.has_refractive = bool((recs['okind'] == L.O_REFRACTIVE).any())
         self.has_split = bool((self.children_per_hit > 1).any())
+        if self.has_split and self.has_bifacial:
+            raise NotImplementedError("BiFacial managers in a scene with two-children optics (periodic, refractive)")
         self.needs_theta_for_draws = any(o['okind'] == L.O_LAMB_PIECEWISE_SPEC for o in uniq)
         self.accountant_sources = set(src for o in uniq for (_, _, src) in o['accountants'])
+        self.has_poly_accountant = 'lost_spectra' in self.accountant_sources
         self.unbounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) != 0)[0].astype(np.int32)
         self.bounded = np.nonzero((recs['flags'] & L.F_UNBOUNDED) == 0)[0].astype(np.int32)
         self.leaf_size = leaf_size
@@ -495,6 +550,17 @@ class CompiledScene(object):
             x, y = orec['table']
             r['table_off'], r['table_len'] = self._add_table(x), len(x)
             self._add_table(y)
+        back = orec.get('back')
+        if back is not None:
+            toff, tlen = -1, 0
+            if back['table'] is not None:
+                x, y = back['table']
+                toff, tlen = self._add_table(x), len(x)
+                self._add_table(y)
+            self._back[i] = (back['okind'], back['op'], back['flags'], toff, tlen)
+            if back['accountants'] and id(back['instance']) in seen_opt:
+                raise NotImplementedError("optics manager instance shared between BiFacial sides / surfaces")
+            seen_opt[id(back['instance'])] = i
         self.optics.append(orec)
 
     def _fill_mesh(self, recs, i0, mesh):
@@ -504,6 +570,8 @@ class CompiledScene(object):
         verts = np.asarray(mesh.mesh_vertices(), dtype=float)
         n = len(frames)
         orec = _optics_record(mesh.mesh_optics())
+        if orec.get('back') is not None:
+            raise NotImplementedError("BiFacial optics on a TriangleMeshObject")
         if orec['okind'] in (L.O_PERIODIC, L.O_REFRACTIVE):
             raise NotImplementedError("two-children optics (periodic, refractive) on a TriangleMeshObject")
         orec['mesh'] = mesh
@@ -551,6 +619,12 @@ class CompiledScene(object):
                                      C.byref(h)))
         self.handle = h
         self._upload_bvh()
+        if self.has_bifacial:              # optics-only copy: trc_optics reads its surface table and the shared pool
+            hb = C.c_void_p()
+            L.check(lib.trc_scene_create(self.records_back.ctypes.data_as(C.c_void_p), len(self.records_back),
+                                         tab.ctypes.data_as(C.c_void_p) if tab.size else None, int(tab.size),
+                                         C.byref(hb)))
+            self.handle_back = hb
 
     def _upload_bvh(self):
         import ctypes as C
@@ -587,6 +661,16 @@ class CompiledScene(object):
         self._grid_key, self._grid_on = key, bool(on.value)
         return self._grid_on
 
+    def bifacial_tensors(self, device):
+        """(up (S, 3): +z of every surface frame in global coordinates, mask (S,) of the BiFacial surfaces) on device."""
+        import torch
+        cached = getattr(self, '_bifacial_dev', None)
+        if cached is None or cached[0].device != device:
+            up = np.ascontiguousarray(self.records['frame'][:, [2, 6, 10]], dtype=np.float64)
+            cached = (torch.from_numpy(up).to(device), torch.from_numpy(self.bifacial_mask.copy()).to(device))
+            self._bifacial_dev = cached
+        return cached
+
     def seg_entries_needed(self, device):
         """(host list, device index tensor) of the slot-offset entries the engine reads on the host after a
         bounce: both ends of every mesh and of every surface with accountants."""
@@ -611,6 +695,9 @@ class CompiledScene(object):
         if self.handle is not None:
             L.load().trc_scene_destroy(self.handle)
             self.handle = None
+        if getattr(self, 'handle_back', None) is not None:
+            L.load().trc_scene_destroy(self.handle_back)
+            self.handle_back = None
 
     def __del__(self):
         try:

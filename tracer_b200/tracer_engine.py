@@ -84,10 +84,11 @@ INLINE_SEG_MAX = 4096          # scenes with more surfaces keep the slot offsets
 class _DevBundle(object):
     """Engine-internal view of a bundle living in HBM.  ``slices`` is set while a
     host bundle is still arriving: [(first ray, end ray, CUDA event of its copy)]."""
-    __slots__ = ('V', 'D', 'E', 'W', 'R', 'I', 'id_base', 'n', 'slices', 'keep')
+    __slots__ = ('V', 'D', 'E', 'W', 'R', 'I', 'SP', 'id_base', 'n', 'slices', 'keep')
 
-    def __init__(self, V, D, E, W=None, slices=None, keep=None, R=None, I=None, id_base=0):
+    def __init__(self, V, D, E, W=None, slices=None, keep=None, R=None, I=None, id_base=0, SP=None):
         self.V, self.D, self.E, self.W = V, D, E, W
+        self.SP = SP              # spectra (W, n) of polychromatic rays; W is then (W, n) too
         self.R = R                # ref_index column (refractive scenes), else None
         self.I = I                # source-ray id of each ray (int64), None: id_base + index
         self.id_base = int(id_base)
@@ -251,13 +252,20 @@ class TracerEngine(object):
             return streamed
         V, D, E = col('vertices'), col('directions'), col('energy')
         W = col('wavelengths', required=False) if bundle.has_property('wavelengths') else None
+        SP = col('spectra', required=False) if bundle.has_property('spectra') else None
+        if SP is not None:
+            if W is None or SP.dim() != 2 or W.shape != SP.shape or SP.shape[1] != E.shape[0]:
+                raise ValueError("polychromatic bundle: 'wavelengths' and 'spectra' must both be (W, n)")
+        elif W is not None and W.shape != E.shape:
+            raise ValueError("bundle wavelengths must be (n,) (or (W, n) next to 'spectra')")
         R = col('ref_index', required=False) if bundle.has_property('ref_index') else None
         if R is not None and R.shape != E.shape:
             raise ValueError("bundle ref_index must be (n,)")
         if V.dim() != 2 or V.shape[0] != 3 or D.shape != V.shape or E.shape[0] != V.shape[1]:
             raise ValueError("bundle arrays must be vertices (3,n), directions (3,n), energy (n,)")
         return _DevBundle(V.contiguous(), D.contiguous(), E.contiguous(), None if W is None else W.contiguous(),
-                          R=None if R is None else R.contiguous(), id_base=id_base)
+                          R=None if R is None else R.contiguous(), id_base=id_base,
+                          SP=None if SP is None else SP.contiguous())
 
     def _upload_in_slices(self, bundle):
         """Large host bundle: allocate it in HBM and enqueue the host->device copy in
@@ -304,69 +312,82 @@ class TracerEngine(object):
         return _DevBundle(V, D, E, None, slices, keep=(tV, tD, tE))
 
     # ------------------------------------------------------------ draws
-    def _numpy_draws(self, scene, seg, H, theta_in=None):
-        """Host draws in the reference's consumption order; returns 3 device arrays or None.
-        ``theta_in`` (host, slot order) is needed by optics whose specular/diffuse split
-        depends on the incidence angle."""
+    @staticmethod
+    def _draws_for(rec, table, n, theta):
+        """numpy.random draws of one optics callable on n hits, in the order its __call__ consumes them."""
+        k = rec['okind']
+        vals = [None, None, None]
+        if k == L.O_REAL_REFLECTIVE:
+            sig = rec['op'][1]
+            if sig > 0.:
+                if rec['op'][2] != 0.:
+                    vals[0] = np.random.normal(scale=sig, size=(n,))
+                    vals[1] = np.random.normal(scale=sig, size=(n,))
+                else:
+                    vals[0] = np.random.normal(scale=sig, size=(n,))
+                    vals[1] = np.random.uniform(low=0., high=2. * np.pi, size=(n,))
+        elif k == L.O_LAMB_PIECEWISE_SPEC:
+            th_tab, rest = table
+            spec = np.interp(theta, th_tab, rest[len(th_tab):])
+            r = np.random.rand(n)
+            diffuse = ~(r < spec)
+            nd = int(diffuse.sum())
+            vals[0] = r
+            vals[1], vals[2] = np.zeros(n), np.zeros(n)
+            vals[1][diffuse] = np.random.uniform(low=0., high=2. * np.pi, size=nd)
+            vals[2][diffuse] = np.random.uniform(size=nd)
+        elif k == L.O_REFRACTIVE:
+            # _refract_dirs (:1229-1231) then _make_output_refraction_bundles (:1255)
+            if rec['op'][3] >= 0.:
+                vals[0] = np.random.normal(scale=rec['op'][3], size=n)
+                vals[1] = np.random.uniform(low=0., high=2. * np.pi, size=n)
+            if rec['op'][2] != 0.:
+                vals[2] = np.random.uniform(size=n)
+        elif k in (L.O_LAMBERTIAN, L.O_LAMB_DIRECTIONAL, L.O_LAMB_DIRECTIONAL_SPECTRAL,
+                   L.O_LAMBERTIAN_ABSORBANT):
+            ang = rec['op'][1] if k in (L.O_LAMBERTIAN, L.O_LAMBERTIAN_ABSORBANT) else np.pi / 2.
+            vals[0] = np.random.uniform(low=0., high=2. * np.pi, size=n)
+            if ang != 0.:
+                vals[1] = np.random.uniform(size=n)
+        elif k in (L.O_LAMBERTIAN_SPECULAR, L.O_LAMBSPEC_DIRECTIONAL):
+            spec = rec['op'][1] if k == L.O_LAMBERTIAN_SPECULAR else rec['op'][0]
+            r = np.random.rand(n)
+            diffuse = ~(r < spec)
+            nd = int(diffuse.sum())
+            vals[0] = r
+            vals[1], vals[2] = np.zeros(n), np.zeros(n)
+            vals[1][diffuse] = np.random.uniform(low=0., high=2. * np.pi, size=nd)
+            vals[2][diffuse] = np.random.uniform(size=nd)
+        return vals
+
+    def _numpy_draws(self, scene, seg, H, theta_in=None, back=None):
+        """Host draws in the reference's consumption order; returns the (3, H) device array of the surfaces'
+        (front) optics and, for scenes with BiFacial managers, a second one for the back sides (else None).
+        ``theta_in`` (host, slot order) is needed by optics whose specular/diffuse split depends on the incidence
+        angle; ``back`` (host bool, slot order) marks the hits on the back of a BiFacial surface: a side draws
+        (for ALL the surface's hits) only when some hit is on it, the back side first (optics_callables.py:1891-1894)."""
         import torch
-        draws = None
+        draws = np.zeros((3, H))
+        draws_b = np.zeros((3, H)) if scene.has_bifacial else None
         counts = np.diff(seg)
         for s in np.nonzero(counts)[0]:
             n = int(counts[s])
             a, b = int(seg[s]), int(seg[s + 1])
-            rec = scene.records[s]
-            k = rec['okind']
-            vals = [None, None, None]
-            if k == L.O_REAL_REFLECTIVE:
-                sig = rec['op'][1]
-                if sig > 0.:
-                    if rec['op'][2] != 0.:
-                        vals[0] = np.random.normal(scale=sig, size=(n,))
-                        vals[1] = np.random.normal(scale=sig, size=(n,))
-                    else:
-                        vals[0] = np.random.normal(scale=sig, size=(n,))
-                        vals[1] = np.random.uniform(low=0., high=2. * np.pi, size=(n,))
-            elif k == L.O_LAMB_PIECEWISE_SPEC:
-                th_tab, rest = scene.optics[s]['table']
-                spec = np.interp(theta_in[a:b], th_tab, rest[len(th_tab):])
-                r = np.random.rand(n)
-                diffuse = ~(r < spec)
-                nd = int(diffuse.sum())
-                vals[0] = r
-                vals[1], vals[2] = np.zeros(n), np.zeros(n)
-                vals[1][diffuse] = np.random.uniform(low=0., high=2. * np.pi, size=nd)
-                vals[2][diffuse] = np.random.uniform(size=nd)
-            elif k == L.O_REFRACTIVE:
-                # _refract_dirs (:1229-1231) then _make_output_refraction_bundles (:1255)
-                if rec['op'][3] >= 0.:
-                    vals[0] = np.random.normal(scale=rec['op'][3], size=n)
-                    vals[1] = np.random.uniform(low=0., high=2. * np.pi, size=n)
-                if rec['op'][2] != 0.:
-                    vals[2] = np.random.uniform(size=n)
-            elif k in (L.O_LAMBERTIAN, L.O_LAMB_DIRECTIONAL, L.O_LAMB_DIRECTIONAL_SPECTRAL,
-                       L.O_LAMBERTIAN_ABSORBANT):
-                ang = rec['op'][1] if k in (L.O_LAMBERTIAN, L.O_LAMBERTIAN_ABSORBANT) else np.pi / 2.
-                vals[0] = np.random.uniform(low=0., high=2. * np.pi, size=n)
-                if ang != 0.:
-                    vals[1] = np.random.uniform(size=n)
-            elif k in (L.O_LAMBERTIAN_SPECULAR, L.O_LAMBSPEC_DIRECTIONAL):
-                spec = rec['op'][1] if k == L.O_LAMBERTIAN_SPECULAR else rec['op'][0]
-                r = np.random.rand(n)
-                diffuse = ~(r < spec)
-                nd = int(diffuse.sum())
-                vals[0] = r
-                vals[1], vals[2] = np.zeros(n), np.zeros(n)
-                vals[1][diffuse] = np.random.uniform(low=0., high=2. * np.pi, size=nd)
-                vals[2][diffuse] = np.random.uniform(size=nd)
-            if any(v is not None for v in vals):
-                if draws is None:
-                    draws = np.zeros((3, H))
+            theta = None if theta_in is None else theta_in[a:b]
+            passes = [(scene.records[s], scene.optics[s]['table'], draws)]
+            if scene.has_bifacial and scene.bifacial_mask[s]:
+                passes = []
+                if back[a:b].any():
+                    passes.append((scene.records_back[s], scene.optics[s]['back']['table'], draws_b))
+                if not back[a:b].all():
+                    passes.append((scene.records[s], scene.optics[s]['table'], draws))
+            for rec, table, dest in passes:
+                vals = self._draws_for(rec, table, n, theta)
                 for j in range(3):
                     if vals[j] is not None:
-                        draws[j, a:b] = vals[j]
-        if draws is None:
-            draws = np.zeros((3, H))
-        return torch.from_numpy(draws).to(self.device)
+                        dest[j, a:b] = vals[j]
+        to_dev = (lambda x: torch.from_numpy(x).to(self.device))
+        return to_dev(draws), (to_dev(draws_b) if draws_b is not None else None)
 
     # ------------------------------------------------------------ bounce
     def _bounce(self, scene, cur, bounce, min_energy, use_bvh):
@@ -444,70 +465,136 @@ class TracerEngine(object):
             Hc = int(child_off_host[-1])
             child_off = torch.from_numpy(child_off_host).to(dev)
 
-        oV = torch.empty((3, Hc), dtype=f64, device=dev)
-        oD = torch.empty((3, Hc), dtype=f64, device=dev)
-        oE = torch.empty(Hc, dtype=f64, device=dev)
-        oP = torch.empty(Hc, dtype=i64, device=dev)
-        cull = torch.empty(Hc, dtype=i32, device=dev)
-        want = scene.accountant_sources
-        absorbed = torch.empty(H, dtype=f64, device=dev)   # always: feeds the per-surface totals
-        normals = torch.empty((3, Hc), dtype=f64, device=dev) if 'normals' in want else None   # row stride = ld_out
-        e_in = torch.empty(H, dtype=f64, device=dev) if 'e_in' in want else None
-        dirs_in = torch.empty((3, Hc), dtype=f64, device=dev) if 'dirs_in' in want else None
-        attenuated = torch.empty(H, dtype=f64, device=dev) if 'attenuated' in want else None
+        want = set(scene.accountant_sources)
+        poly = cur.SP is not None
+        if poly:
+            want.update(('normals', 'dirs_in'))          # trc_spectra reads the incidence angle from them
         if 'wavelengths' in want and cur.W is None:
             raise ValueError("Spectral accountant needs a 'wavelengths' bundle property")
-        oW = torch.empty(Hc, dtype=f64, device=dev) if cur.W is not None else None
-        oR = torch.empty(Hc, dtype=f64, device=dev) if cur.R is not None else None
-        oI = torch.empty(Hc, dtype=i64, device=dev)
-        a = L.OpticsArgs()
-        a.h = H
-        a.d_records, a.d_slot_rec = records.data_ptr(), slot_rec.data_ptr()
-        a.d_wavelengths = cur.W.data_ptr() if cur.W is not None else None
-        a.d_out_vertices, a.d_out_directions = oV.data_ptr(), oD.data_ptr()
-        a.d_out_energy, a.d_out_parents, a.ld_out = oE.data_ptr(), oP.data_ptr(), Hc
-        if child_off is not None:
-            a.d_slot_surf, a.d_seg, a.d_child_off = slot_surf.data_ptr(), seg.data_ptr(), child_off.data_ptr()
-        a.seed, a.bounce, a.min_energy = self.seed, bounce, float(min_energy)
-        if cur.R is not None:
-            a.d_ref_index, a.d_out_ref_index = cur.R.data_ptr(), oR.data_ptr()
-        a.d_ray_ids = cur.I.data_ptr() if cur.I is not None else None
-        a.ray_id_base, a.d_out_ray_ids = cur.id_base, oI.data_ptr()
-        draws = None
+        n_w = int(cur.SP.shape[0]) if poly else 0
+
+        def outputs():
+            """One set of child columns + accountant columns (slot order) for an optics pass."""
+            o = dict(V=torch.empty((3, Hc), dtype=f64, device=dev), D=torch.empty((3, Hc), dtype=f64, device=dev),
+                     E=torch.empty(Hc, dtype=f64, device=dev), P=torch.empty(Hc, dtype=i64, device=dev),
+                     cull=torch.empty(Hc, dtype=i32, device=dev),
+                     absorbed=torch.empty(H, dtype=f64, device=dev),   # always: feeds the per-surface totals
+                     normals=torch.empty((3, Hc), dtype=f64, device=dev) if 'normals' in want else None,   # row stride = ld_out
+                     e_in=torch.empty(H, dtype=f64, device=dev) if 'e_in' in want else None,
+                     dirs_in=torch.empty((3, Hc), dtype=f64, device=dev) if 'dirs_in' in want else None,
+                     attenuated=torch.empty(H, dtype=f64, device=dev) if 'attenuated' in want else None,
+                     W=None, SP=None, lost_spectra=None,
+                     R=torch.empty(Hc, dtype=f64, device=dev) if cur.R is not None else None,
+                     I=torch.empty(Hc, dtype=i64, device=dev))
+            if poly:
+                o['W'] = torch.empty((n_w, Hc), dtype=f64, device=dev)
+                o['SP'] = torch.empty((n_w, Hc), dtype=f64, device=dev)
+                if 'lost_spectra' in want:
+                    o['lost_spectra'] = torch.empty((n_w, Hc), dtype=f64, device=dev)
+            elif cur.W is not None:
+                o['W'] = torch.empty(Hc, dtype=f64, device=dev)
+            return o
+
+        def optics_args(o, draws):
+            a = L.OpticsArgs()
+            a.h = H
+            a.d_records, a.d_slot_rec = records.data_ptr(), slot_rec.data_ptr()
+            a.d_wavelengths = cur.W.data_ptr() if (cur.W is not None and not poly) else None
+            a.d_out_vertices, a.d_out_directions = o['V'].data_ptr(), o['D'].data_ptr()
+            a.d_out_energy, a.d_out_parents, a.ld_out = o['E'].data_ptr(), o['P'].data_ptr(), Hc
+            if child_off is not None:
+                a.d_slot_surf, a.d_seg, a.d_child_off = slot_surf.data_ptr(), seg.data_ptr(), child_off.data_ptr()
+            a.seed, a.bounce, a.min_energy = self.seed, bounce, float(min_energy)
+            if cur.R is not None:
+                a.d_ref_index, a.d_out_ref_index = cur.R.data_ptr(), o['R'].data_ptr()
+            a.d_ray_ids = cur.I.data_ptr() if cur.I is not None else None
+            a.ray_id_base, a.d_out_ray_ids = cur.id_base, o['I'].data_ptr()
+            for j in range(3):
+                a.d_draws[j] = draws[j].data_ptr() if draws is not None else None
+            a.d_absorbed = o['absorbed'].data_ptr()
+            for name, field in (('normals', 'd_normals'), ('e_in', 'd_e_in'), ('dirs_in', 'd_dirs_in'),
+                                ('attenuated', 'd_attenuated')):
+                setattr(a, field, o[name].data_ptr() if o[name] is not None else None)
+            a.d_out_wavelengths = o['W'].data_ptr() if (o['W'] is not None and not poly) else None
+            a.d_cull = o['cull'].data_ptr()
+            a.d_n_cull = counters[1:].data_ptr()
+            a.d_n_void = counters[2:].data_ptr()
+            return a
+
+        def optics_pass(handle, o, draws):
+            """trc_optics (+ trc_spectra for polychromatic rays) with the surface table behind ``handle``."""
+            L.check(lib.trc_optics(handle, C.byref(optics_args(o, draws)), st))
+            if poly:
+                counters[1:2].zero_()                       # trc_spectra re-decides every slot's cull flag
+                sa = L.SpectraArgs()
+                sa.h, sa.n_samples = H, n_w
+                sa.d_slot_surf, sa.d_parents = slot_surf.data_ptr(), o['P'].data_ptr()
+                sa.d_in_wavelengths, sa.d_in_spectra, sa.ld_in = cur.W.data_ptr(), cur.SP.data_ptr(), cur.W.stride(0)
+                sa.d_normals, sa.d_dirs_in, sa.ld_cols = o['normals'].data_ptr(), o['dirs_in'].data_ptr(), Hc
+                sa.d_out_wavelengths, sa.d_out_spectra, sa.ld_out = o['W'].data_ptr(), o['SP'].data_ptr(), Hc
+                sa.d_energy, sa.d_absorbed = o['E'].data_ptr(), o['absorbed'].data_ptr()
+                sa.d_lost_spectra = o['lost_spectra'].data_ptr() if o['lost_spectra'] is not None else None
+                sa.d_cull, sa.d_n_cull, sa.min_energy = o['cull'].data_ptr(), counters[1:].data_ptr(), float(min_energy)
+                L.check(lib.trc_spectra(handle, C.byref(sa), st))
+
+        # BiFacial managers (optics_callables.py:1885-1901): which hits are on the back of their surface
+        back = back_host = back_counts = None
+        if scene.has_bifacial:
+            up, bif = scene.bifacial_tensors(dev)
+            d_in = records.index_select(0, slot_rec.long())[:, 3:6]
+            proj = (d_in * up.index_select(0, slot_surf.long())).sum(dim=1)
+            back = (torch.round(proj, decimals=6) > 0.) & bif.index_select(0, slot_surf.long())
+            back_counts = torch.bincount(slot_surf[back].long(), minlength=S).cpu().numpy()
+
+        draws = draws_back = None
         if self.rng == 'numpy':
             theta_in = None
             if scene.needs_theta_for_draws:
                 # the specular/diffuse split of these optics follows the incidence angle: a first
                 # pass of the kernel (draws unused for normals) provides it to the host
-                tn = torch.empty((3, Hc), dtype=f64, device=dev)
-                td = torch.empty((3, Hc), dtype=f64, device=dev)
-                a.d_normals, a.d_dirs_in = tn.data_ptr(), td.data_ptr()
-                L.check(lib.trc_optics(scene.handle, C.byref(a), st))
+                tmp = outputs()
+                tn = tmp['normals'] if tmp['normals'] is not None else torch.empty((3, Hc), dtype=f64, device=dev)
+                td = tmp['dirs_in'] if tmp['dirs_in'] is not None else torch.empty((3, Hc), dtype=f64, device=dev)
+                tmp['normals'], tmp['dirs_in'] = tn, td
+                L.check(lib.trc_optics(scene.handle, C.byref(optics_args(tmp, None)), st))
+                counters[1:].zero_()
                 hn, hd = tn[:, :H].cpu().numpy(), td[:, :H].cpu().numpy()
                 vertical = np.sum(hd * hn, axis=0) * hn          # optics_callables.py:469-472
                 theta_in = np.arccos(np.sqrt(np.sum(vertical ** 2, axis=0)))
-            draws = self._numpy_draws(scene, seg_host, H, theta_in)
-        for j in range(3):
-            a.d_draws[j] = draws[j].data_ptr() if draws is not None else None
-        a.d_absorbed = absorbed.data_ptr()
-        a.d_normals = normals.data_ptr() if normals is not None else None
-        a.d_e_in = e_in.data_ptr() if e_in is not None else None
-        a.d_dirs_in = dirs_in.data_ptr() if dirs_in is not None else None
-        a.d_attenuated = attenuated.data_ptr() if attenuated is not None else None
-        a.d_out_wavelengths = oW.data_ptr() if oW is not None else None
-        a.d_cull = cull.data_ptr()
-        a.d_n_cull = counters[1:].data_ptr()
-        a.d_n_void = counters[2:].data_ptr()
-        L.check(lib.trc_optics(scene.handle, C.byref(a), st))
+                del tmp
+            back_host = back.cpu().numpy() if back is not None else None
+            draws, draws_back = self._numpy_draws(scene, seg_host, H, theta_in, back_host)
 
+        out = outputs()
+        optics_pass(scene.handle, out, draws)
+        src_back = None
+        if scene.has_bifacial:
+            # the back sides' optics on every slot (same geometry, second surface table), then slot by slot the
+            # side the ray is on.  Each side's accountants still see ALL the hits of their surface (below).
+            out_b = outputs()
+            optics_pass(scene.handle_back, out_b, draws_back)
+            src_back = out_b
+            merged = {}
+            for k, t in out.items():
+                merged[k] = None if t is None else torch.where(back, out_b[k], t)
+            src_front, out = out, merged
+            counters[1] = (out['cull'] == 1).sum()
+
+        oV, oD, oE, oP, cull, oW, oR, oI, oS = (out[k] for k in ('V', 'D', 'E', 'P', 'cull', 'W', 'R', 'I', 'SP'))
+        absorbed = out['absorbed']
         # per-surface absorbed energy and hit counts, kept on device: the payload of
         # the multi-GPU all-reduce (tracer_engine_mp.py) and a tally for 'fast' optics
         L.check(lib.trc_segment_sums(H, L.dptr(slot_surf), L.dptr(absorbed), L.dptr(self.absorbed_per_surface), st))
         self.hits_per_surface += seg[1:] - seg[:-1]
         if scene.has_accountants:
-            self._account(scene, seg_host, dict(hits=oV, absorbed=absorbed, e_out=oE, normals=normals, e_in=e_in,
-                                                dirs_in=dirs_in, wavelengths=oW, attenuated=attenuated),
-                          child_off_host)
+            def columns(o):
+                return dict(hits=o['V'], absorbed=o['absorbed'], e_out=o['E'], normals=o['normals'], e_in=o['e_in'],
+                            dirs_in=o['dirs_in'], wavelengths=o['W'], attenuated=o['attenuated'],
+                            lost_spectra=o['lost_spectra'])
+            if scene.has_bifacial:
+                self._account(scene, seg_host, columns(src_front), child_off_host, back=(columns(src_back), back_counts))
+            else:
+                self._account(scene, seg_host, columns(out), child_off_host)
 
         n_cull, n_void = (int(x) for x in counters[1:].tolist())
         del records, work
@@ -525,30 +612,38 @@ class TracerEngine(object):
             L.check(lib.trc_gather_rows(Hc, L.dptr(perm), 3, L.dptr(oV), Hc, L.dptr(pV), Hc, None, None, st))
             L.check(lib.trc_gather_rows(Hc, L.dptr(perm), 3, L.dptr(oD), Hc, L.dptr(pD), Hc, None, None, st))
             L.check(lib.trc_gather_rows(Hc, L.dptr(perm), 1, L.dptr(oE), Hc, L.dptr(pE), Hc, L.dptr(oP), L.dptr(pP), st))
-            pW = oW.index_select(0, perm.long()) if oW is not None else None
-            pR = oR.index_select(0, perm.long()) if oR is not None else None
-            pI = oI.index_select(0, perm.long())
-            return pV, pD, pE, pP, pW, pR, pI, perm
+            pl = perm.long()
+            pW = oW.index_select(-1, pl) if oW is not None else None
+            pS = oS.index_select(-1, pl) if oS is not None else None
+            pR = oR.index_select(0, pl) if oR is not None else None
+            pI = oI.index_select(0, pl)
+            return pV, pD, pE, pP, pW, pR, pI, pS, perm
 
+        if scene.has_bifacial:
+            # children of a BiFacial surface: the back side's first, each side in hit order (:1891-1899)
+            key = 2 * slot_surf + (~back).to(i32) * scene.bifacial_tensors(dev)[1].index_select(0, slot_surf.long()).to(i32)
+            oV, oD, oE, oP, oW, oR, oI, oS, perm = reorder(key.contiguous(), 2 * S)
+            cull = cull.index_select(0, perm.long()).contiguous()
         if n_void:
             # refractive surfaces leave void child slots (cull code 2): drop them, keeping the order
             is_void = (cull == 2).to(i32)
-            pV, pD, pE, pP, pW, pR, pI, perm = reorder(is_void, 2)
+            pV, pD, pE, pP, pW, pR, pI, pS, perm = reorder(is_void, 2)
             Hc -= n_void
             cull = cull.index_select(0, perm[:Hc].long()).contiguous()
             oV, oD = pV[:, :Hc].contiguous(), pD[:, :Hc].contiguous()
             oE, oP = pE[:Hc].contiguous(), pP[:Hc].contiguous()
-            oW = pW[:Hc].contiguous() if pW is not None else None
+            oW = pW[..., :Hc].contiguous() if pW is not None else None
+            oS = pS[..., :Hc].contiguous() if pS is not None else None
             oR = pR[:Hc].contiguous() if pR is not None else None
             oI = pI[:Hc].contiguous()
             if Hc == 0:
                 return None, 0, H
-        rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR, I=oI)
+        rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR, I=oI, SP=oS)
         if n_cull and n_cull < Hc:
             # survivors first, weak rays at the back (tracer_engine.py:242-245, 268-274)
-            pV, pD, pE, pP, pW, pR, pI, _ = reorder(cull, 2)
-            rec = dict(V=pV, D=pD, E=pE, P=pP, W=pW, R=pR, I=pI)
-        rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR)
+            pV, pD, pE, pP, pW, pR, pI, pS, _ = reorder(cull, 2)
+            rec = dict(V=pV, D=pD, E=pE, P=pP, W=pW, R=pR, I=pI, SP=pS)
+        rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR, SP=oS)
         return rec, Hc - n_cull, H
 
     # ------------------------------------------------- device-driven trace
@@ -727,7 +822,7 @@ class TracerEngine(object):
         return out
 
     @staticmethod
-    def _account(scene, seg, src, child_off=None, copy=True):
+    def _account(scene, seg, src, child_off=None, copy=True, back=None):
         """What Accountant.count() stores, one chunk per surface per bounce
         (optics_callables.py:1597-1790), kept in HBM until read.  ``src`` maps a
         source name to the tensor the optics kernel filled: slot order, except the
@@ -751,13 +846,20 @@ class TracerEngine(object):
             a, b = int(seg[s]), int(seg[s + 1])
             if b == a:
                 continue
-            for acc, field, name in orec['accountants']:
-                t = src[name]
-                if child_off is not None and name in ('hits', 'e_out', 'wavelengths'):
-                    lo = int(child_off[s])
-                    getattr(acc, field).append(_LazyRows(take(t[..., lo:lo + (b - a)])))
-                else:
-                    getattr(acc, field).append(_LazyRows(take(t[..., a:b])))
+            feeds = [(orec['accountants'], src)]
+            if orec.get('back') is not None:
+                # BiFacial: a side's manager ran (on every hit of the surface) iff some hit was on that side
+                n_back = int(back[1][s])
+                feeds = ([(orec['back']['accountants'], back[0])] if n_back > 0 else []) + \
+                        ([(orec['accountants'], src)] if n_back < b - a else [])
+            for accs, cols in feeds:
+                for acc, field, name in accs:
+                    t = cols[name]
+                    if child_off is not None and name in ('hits', 'e_out', 'wavelengths'):
+                        lo = int(child_off[s])
+                        getattr(acc, field).append(_LazyRows(take(t[..., lo:lo + (b - a)])))
+                    else:
+                        getattr(acc, field).append(_LazyRows(take(t[..., a:b])))
 
     @staticmethod
     def _as_bundle(rec, n=None):
@@ -770,6 +872,8 @@ class TracerEngine(object):
             kw['wavelengths'] = cols(rec['W'])
         if rec.get('R') is not None:
             kw['ref_index'] = cols(rec['R'])
+        if rec.get('SP') is not None:
+            kw['spectra'] = cols(rec['SP'])
         return RayBundle(vertices=cols(rec['V']), directions=cols(rec['D']), energy=cols(rec['E']),
                          parents=cols(rec['P']), **kw)
 
@@ -811,7 +915,14 @@ class TracerEngine(object):
             raise ValueError("scene has refractive optics but the bundle carries no 'ref_index'")
         source_E = cur.E
         # device-driven (trc_trace) unless draws are injected or some optics emits two children per hit
-        device_driven = self.fused_bounce and self.rng == 'philox' and not scene.has_split and cur.R is None
+        if scene.needs_spectra and cur.SP is None:
+            raise ValueError("scene has polychromatic optics but the bundle carries no 'spectra' (with 'wavelengths', both (W, n))")
+        if cur.SP is not None and (scene.needs_wavelengths or scene.has_split or
+                                   bool((scene.records['flags'] & L.F_IAM).any())):
+            raise NotImplementedError("polychromatic bundle (a 'spectra' property) in a scene with spectral, IAM, periodic "
+                                      "or refractive optics")
+        device_driven = (self.fused_bounce and self.rng == 'philox' and not scene.has_split and cur.R is None
+                         and cur.SP is None and not scene.has_bifacial)
         if device_driven and cur.n > 0 and reps > 0:
             tall = torch.empty(2 * scene.num_surfaces, dtype=torch.float64, device=self.device)
             self.absorbed_per_surface = tall[:scene.num_surfaces]
@@ -839,7 +950,7 @@ class TracerEngine(object):
                 per_bounce.append((n_in, H, n_surv))
                 if rec is None:
                     last_rec = None
-                    cur = _DevBundle(cur.V[:, :0], cur.D[:, :0], cur.E[:0], None if cur.W is None else cur.W[:0])
+                    cur = _DevBundle(cur.V[:, :0], cur.D[:, :0], cur.E[:0], None if cur.W is None else cur.W[..., :0])
                     logging.log(self.loglevel, 'Ray bundle depleted')
                     depleted = True
                     break
@@ -848,10 +959,11 @@ class TracerEngine(object):
                     full = dict(rec)
                     full.pop('pre_cull')
                     self.tree.append(self._as_bundle(full))
-                W = rec['W'][:n_surv] if rec['W'] is not None else None
+                W = rec['W'][..., :n_surv] if rec['W'] is not None else None
+                SP = rec['SP'][..., :n_surv] if rec.get('SP') is not None else None
                 R = rec['R'][:n_surv] if rec.get('R') is not None else None
                 I = rec['I'][:n_surv] if rec.get('I') is not None else None
-                cur = _DevBundle(rec['V'][:, :n_surv], rec['D'][:, :n_surv], rec['E'][:n_surv], W, R=R, I=I)
+                cur = _DevBundle(rec['V'][:, :n_surv], rec['D'][:, :n_surv], rec['E'][:n_surv], W, R=R, I=I, SP=SP)
                 if cur.n == 0:
                     logging.log(self.loglevel, 'Ray bundle depleted')
                     depleted = True
