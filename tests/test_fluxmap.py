@@ -36,16 +36,18 @@ def _local_uv(coord, param, local):
 
 @pytest.mark.parametrize('name', CASES)
 def test_mesh_and_areas_match_reference_cpu(name):
-    from tracer_b200.fluxmap import _mesh
+    from tracer_b200.fluxmap import _mesh_regions
     gm, frame, res, _ = scenes.fluxmap_cases(T)[name]
-    coord, param, eu, ev, areas = _mesh(gm, res)
     proj = np.round(np.linalg.inv(frame), decimals=9)
     hits = GOLD[name + '_hits']
     local = np.dot(proj, np.vstack([hits, np.ones(hits.shape[1])]))[:3]
-    u, v = _local_uv(coord, param, local)
-    en = np.histogram2d(u, v, bins=[eu, ev], weights=GOLD[name + '_eners'])[0]
-    with np.errstate(divide='ignore', invalid='ignore'):
-        flux = np.hstack(en / areas)
+    maps = []
+    for coord, param, eu, ev, areas in _mesh_regions(gm, res):
+        u, v = _local_uv(coord, param, local)
+        en = np.histogram2d(u, v, bins=[eu, ev], weights=GOLD[name + '_eners'])[0]
+        with np.errstate(divide='ignore', invalid='ignore'):
+            maps.append(np.hstack(en / areas))
+    flux = maps[0] if len(maps) == 1 else np.array(maps)        # a multi-mesh class returns one map per mesh
     np.testing.assert_allclose(flux, GOLD[name + '_flux'], rtol=1e-12, atol=0., equal_nan=True)
 
 
@@ -59,9 +61,13 @@ def test_device_binning_matches_reference(name):
     surf._temp_frame = frame
     hits = torch.from_numpy(GOLD[name + '_hits']).cuda()
     en = torch.from_numpy(GOLD[name + '_eners']).cuda()
-    bins, areas = binned_energy(surf, hits, en, res)
-    with np.errstate(divide='ignore', invalid='ignore'):
-        flux = np.hstack(bins.cpu().numpy() / areas)
+    from tracer_b200.fluxmap import _mesh_regions
+    maps = []
+    for region in range(len(_mesh_regions(gm, res))):
+        bins, areas = binned_energy(surf, hits, en, res, region=region)
+        with np.errstate(divide='ignore', invalid='ignore'):
+            maps.append(np.hstack(bins.cpu().numpy() / areas))
+    flux = maps[0] if len(maps) == 1 else np.array(maps)
     np.testing.assert_allclose(flux, GOLD[name + '_flux'], rtol=1e-11, atol=0., equal_nan=True)
     # chunked input gives the same map; energy inside the mesh is conserved
     half = hits.shape[1] // 2

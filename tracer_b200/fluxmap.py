@@ -63,8 +63,12 @@ def _mesh(gm, resolution):
     reference's ``get_fluxmap`` of this geometry manager uses."""
     N = np
     names = [c.__name__ for c in type(gm).__mro__]
-    if 'StraightCutRoundPlateGM' in names or 'ExtrudedRectPlateGM' in names:
-        raise NotImplementedError(f"flux map of {type(gm).__name__}: multi-region mesh not implemented")
+    if 'StraightCutRoundPlateGM' in names and getattr(gm, 'x_cut', None) is not None:
+        # the reference's own get_fluxmap raises TypeError here (flat_surface.py:620-632 slices and sizes arrays
+        # with resolution / 3, a float): there is no map to reproduce
+        raise NotImplementedError("flux map of StraightCutRoundPlateGM: the reference's get_fluxmap raises TypeError")
+    if 'ExtrudedRectPlateGM' in names:
+        raise NotImplementedError("ExtrudedRectPlateGM has four meshes: use _mesh_regions / surface_fluxmap")
     if 'RectPlateGM' in names:                                        # flat_surface.py:237-251
         xs = N.linspace(-gm._half_dims[0, 0], gm._half_dims[0, 0], resolution + 1)
         ys = N.linspace(-gm._half_dims[1, 0], gm._half_dims[1, 0], resolution + 1)
@@ -108,14 +112,36 @@ def _mesh(gm, resolution):
     raise NotImplementedError(f"{type(gm).__name__} has no get_fluxmap in the reference")
 
 
-def binned_energy(surface, hits, energy, resolution, device=None):
+def _mesh_regions(gm, resolution):
+    """The meshes of ``gm.get_fluxmap`` as a list of (coord kind, param, u edges, v edges, bin areas): one entry
+    for every class but ExtrudedRectPlateGM, whose plate is cut in four rectangles around the hole -- bottom,
+    middle left, middle right, top, each resolution x resolution (flat_surface.py:321-356)."""
+    N = np
+    names = [c.__name__ for c in type(gm).__mro__]
+    if 'ExtrudedRectPlateGM' not in names:
+        return [_mesh(gm, resolution)]
+    hx, hy = gm._half_dims[0, 0], gm._half_dims[1, 0]
+    cx, cy = gm.extr_center[0], gm.extr_center[1]
+    ex, ey = gm.extr_half_dims[0, 0], gm.extr_half_dims[1, 0]
+    spans = [((-hx, hx), (-hy, cy - ey)), ((-hx, cx - ex), (cy - ey, cy + ey)),
+             ((cx + ex, hx), (cy - ey, cy + ey)), ((-hx, hx), (cy + ey, hy))]
+    out = []
+    for (x0, x1), (y0, y1) in spans:
+        xs, ys = N.linspace(x0, x1, resolution + 1), N.linspace(y0, y1, resolution + 1)
+        dxs = N.tile(N.abs(xs[1:] - xs[:-1]), (len(ys) - 1, 1))
+        dys = N.tile(N.abs(ys[1:] - ys[:-1]), (len(xs) - 1, 1)).T
+        out.append((L.FLUX_XY, 0., xs, ys, dxs * dys))
+    return out
+
+
+def binned_energy(surface, hits, energy, resolution, device=None, region=0):
     """Energy per mesh bin, (nu, nv) float64 CUDA tensor, of hit points (3,n, global
     coordinates) weighted by ``energy`` (n,), both CUDA tensors or host arrays.
-    Returns (bins, areas)."""
+    Returns (bins, areas).  ``region`` picks one of the meshes of a multi-mesh class (_mesh_regions)."""
     import torch
     lib = L.load()
     dev = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
-    coord, param, eu, ev, areas = _mesh(surface.get_geometry_manager(), resolution)
+    coord, param, eu, ev, areas = _mesh_regions(surface.get_geometry_manager(), resolution)[region]
     proj = np.round(np.linalg.inv(surface._temp_frame), decimals=9)[:3]   # surface.py:125
     _, pp = L.host_doubles(proj, 12)
     nu, nv = len(eu) - 1, len(ev) - 1
@@ -151,6 +177,8 @@ def surface_fluxmap(surface, resolution, device=None):
     hits = [c.t if getattr(c, 't', None) is not None else np.asarray(c) for c in _chunks(accs['Location']._hits)]
     ener = [c.t if getattr(c, 't', None) is not None else np.asarray(c)
             for c in _chunks(getattr(en, _ACC_FIELDS[en.shorthand][0]))]
-    bins, areas = binned_energy(surface, hits, ener, resolution, device)
-    flux = bins.cpu().numpy() / areas
-    return np.hstack(flux)
+    out = []
+    for region in range(len(_mesh_regions(surface.get_geometry_manager(), resolution))):
+        bins, areas = binned_energy(surface, hits, ener, resolution, device, region=region)
+        out.append(np.hstack(bins.cpu().numpy() / areas))
+    return out[0] if len(out) == 1 else tuple(out)      # ExtrudedRectPlateGM returns its four maps (flat_surface.py:356)

@@ -501,6 +501,9 @@ def fluxmap_cases(T):
     d = rng.normal(size=(3, n))
     d /= np.sqrt(np.sum(d ** 2, axis=0))
     cases['sphere'] = (T.sphere_surface.SphericalGM(0.7), frame, 6, 0.7 * d)
+    # four meshes around a rectangular hole (flat_surface.py:321-356)
+    cases['rect_extruded'] = (T.flat_surface.ExtrudedRectPlateGM(3., 2., np.array([0.3, -0.2]), 1., 0.8), frame, 6,
+                              np.vstack([xy, np.zeros(n)]))
     return cases
 
 
