@@ -71,7 +71,8 @@ def test_device_binning_matches_reference(name):
     np.testing.assert_allclose(flux, GOLD[name + '_flux'], rtol=1e-11, atol=0., equal_nan=True)
     # chunked input gives the same map; energy inside the mesh is conserved
     half = hits.shape[1] // 2
-    b2, _ = binned_energy(surf, [hits[:, :half].contiguous(), hits[:, half:].contiguous()], [en[:half], en[half:]], res)
+    b2, _ = binned_energy(surf, [hits[:, :half].contiguous(), hits[:, half:].contiguous()], [en[:half], en[half:]], res,
+                          region=region)
     np.testing.assert_allclose(b2.cpu().numpy(), bins.cpu().numpy(), rtol=1e-12)
 
 
