@@ -958,8 +958,9 @@ struct GridShared {
 
 // the float64 stage as ONE out-of-line call site: the key / lookup loop below stays small and keeps its registers
 template <int kFlatOnly>
-__device__ __noinline__ int grid_flush(GridWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane, int qn) {
-    return flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, true);
+__device__ __noinline__ int grid_flush(GridWarpShared &sh, const WalkParams &p, int64_t chunk_base, int lane, int qn,
+                                       bool all) {
+    return flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, all);
 }
 
 struct GridRay { double vn, va, vb, dn, da, db; };
@@ -998,12 +999,14 @@ nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
     unsigned long long c_next = 0;
     if (lane == 0) c_next = atomicAdd(p.chunk_counter, 1ULL);
     c_next = __shfl_sync(full, c_next, 0);
+    // the first group of the NEXT chunk is requested before a chunk's float64 stage and record emission, which hide
+    // its latency
+    GridRay cur = load_ray((long long)c_next * kChunk + lane, (long long)c_next * kChunk + lane < n_rays);
     for (;;) {
         const unsigned long long c = c_next;
         const int64_t chunk_base = (int64_t)c * kChunk;
         if (chunk_base >= n_rays) break;
         const int chunk_n = (int)min((int64_t)kChunk, (int64_t)n_rays - chunk_base);
-        GridRay cur = load_ray(chunk_base + lane, lane < chunk_n);
         if (lane == 0) c_next = atomicAdd(p.chunk_counter, 1ULL);      // the next chunk's id arrives while this one runs
         for (int i = lane; i < kChunk; i += 32) { sh.best_t[i] = TRC_INF_BITS; sh.best_s[i] = INT_MAX; }
         if (lane == 0) sh.q2n = 0;
@@ -1030,8 +1033,8 @@ nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
                 }
                 const int tot = !mq ? 0 : (simple ? __popc(mq) : __shfl_sync(full, incl, 31));
                 const int want = tot + 32 * p.n_unbounded;
-                if (want > kGridQueue) { dirty = true; break; }        // absurdly crowded cells: leave it to the walk
-                if (qn + want > kGridQueue) { need_flush = true; break; }
+                if (want > kGridQueue - 64) { dirty = true; break; }   // absurdly crowded cells: leave it to the walk
+                if (qn + want > kGridQueue - 32) { need_flush = true; break; }
                 const int j = next + lane;
                 const bool valid = j < chunk_n;
                 const GridRay nxt = load_ray(chunk_base + j + 32, j + 32 < chunk_n);
@@ -1082,16 +1085,17 @@ nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
                 cur = nxt;
             }
             if (!need_flush) break;
-            qn = grid_flush<kFlatOnly>(sh, p, chunk_base, lane, qn);
+            qn = grid_flush<kFlatOnly>(sh, p, chunk_base, lane, qn, false);     // whole batches of 32; the rest stays queued
         }
         c_next = __shfl_sync(full, c_next, 0);
+        cur = load_ray((long long)c_next * kChunk + lane, (long long)c_next * kChunk + lane < n_rays);
         if (dirty) {
             // leave the whole chunk to the tree walk (its kernel follows on the stream and writes the chunk's tables)
             if (lane == 0) p.dirty_list[atomicAdd(p.dirty_count, 1ULL)] = (uint32_t)c;
             __syncwarp();
             continue;
         }
-        grid_flush<kFlatOnly>(sh, p, chunk_base, lane, qn);
+        grid_flush<kFlatOnly>(sh, p, chunk_base, lane, qn, true);
         __syncwarp();
         if (p.sink.hit_surf)
             for (int i = lane; i < chunk_n; i += 32)
