@@ -29,7 +29,10 @@ inline int64_t up256(int64_t x) { return (x + 255) & ~(int64_t)255; }
 
 constexpr int kOrderWarps = 8;
 constexpr int kMaxBins = 256;
-constexpr int kTargetTiles = 592;          // 4 CTAs per SM: bounds the (tile, surface) table the last block scans
+#ifndef TRC_ORDER_TILES
+#define TRC_ORDER_TILES 592
+#endif
+constexpr int kTargetTiles = TRC_ORDER_TILES;   // 4 CTAs per SM: bounds the (tile, surface) table the scan block walks
 
 struct OrderParams {
     TrcBounceCtl *ctl;

@@ -211,8 +211,11 @@ class TracerEngine(object):
         # Optics and geometry managers are part of the key by identity as well: replacing one (surf._opt = ...)
         # recompiles.  Editing a parameter IN PLACE (opt._abs = 0.5, gm._half_dims[0] = 2.) is not seen --
         # call compile(force=True) after such an edit (the reference re-reads the live objects every trace).
-        managers = [(getattr(s, '_opt', None), getattr(s, '_geom', None)) for s in surfaces]
-        key = (tuple(map(id, surfaces)), tuple(map(id, frames)), tuple((id(o), id(g)) for o, g in managers))
+        try:
+            managers = [s._opt for s in surfaces], [s._geom for s in surfaces]
+        except AttributeError:              # a mesh object stands for its faces: no managers of its own
+            managers = ([getattr(s, '_opt', None) for s in surfaces], [getattr(s, '_geom', None) for s in surfaces])
+        key = (tuple(map(id, surfaces)), tuple(map(id, frames)), tuple(map(id, managers[0])), tuple(map(id, managers[1])))
         if force or self._scene is None or key != self._frames_key:
             if self._scene is not None:
                 self._scene.close()
