@@ -13,7 +13,8 @@ from tracer_b200.models import scenes
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 WALK_NCU_JSON = os.path.join(ROOT, "profiles", "walk_ncu.json")
-WALK_SOURCES = ("tracer_b200/csrc/nearest.cu", "tracer_b200/csrc/geom.cuh", "tracer_b200/csrc/common.cuh")
+WALK_SOURCES = ("tracer_b200/csrc/nearest.cu", "tracer_b200/csrc/geom.cuh", "tracer_b200/csrc/common.cuh",
+                "tracer_b200/csrc/shadow_grid.cu")
 
 
 def _peaks():
@@ -301,7 +302,9 @@ def run_gpu(args):
         sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": ncu["dram_bytes_per_ray"] * n if ncu else None,
-                    "kernel": "nearest_hit_walk_kernel (bounce 1)" if args.accel == "bvh" else "nearest_hit_brute_kernel (bounce 1)",
+                    "kernel": (("nearest_hit_grid_kernel (bounce 1: shadow grid of the coherent source bundle; + the tree walk "
+                                "over the chunks it leaves)" if eng.stats.get("shadow_grid") else "nearest_hit_walk_kernel (bounce 1)")
+                               if args.accel == "bvh" else "nearest_hit_brute_kernel (bounce 1)"),
                     "kernel_ms": k_ms, "launches_timed": len(ev), "algorithmic_bytes": algo_bytes,
                     "bytes_per_ray": ALGO_BYTES_PER_RAY_HIT_KERNEL, "bytes_per_hit": ALGO_BYTES_PER_HIT_HIT_KERNEL,
                     "hits": k_hits, "rays": n, "peak_source": peak_src + ", burst (kernel timed by its own events)",

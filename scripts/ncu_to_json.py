@@ -20,7 +20,9 @@ which = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 out = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 hdr = rows[0]
-walks = [r for r in rows[2:] if 'nearest_hit_walk' in r[hdr.index('Kernel Name')]]
+# the first-bounce nearest-hit kernel of the bench: the shadow-grid kernel when the capture has it, else the tree walk
+walks = [r for r in rows[2:] if 'nearest_hit_grid' in r[hdr.index('Kernel Name')]] or \
+        [r for r in rows[2:] if 'nearest_hit_walk' in r[hdr.index('Kernel Name')]]
 r = walks[which]
 
 
