@@ -950,8 +950,12 @@ nearest_hit_walk_kernel(WalkParams p) {
 #ifndef TRC_GRID_MIN_CTAS
 #define TRC_GRID_MIN_CTAS 2
 #endif
+#ifndef TRC_GRID_WARPS
+#define TRC_GRID_WARPS 8
+#endif
+constexpr int kGridWarps = TRC_GRID_WARPS;    // warps per CTA of the shadow-grid kernel
 struct GridShared {
-    GridWarpShared w[kWalkWarps];
+    GridWarpShared w[kGridWarps];
     long long n_rays;
     long long pad_;
 };
@@ -963,10 +967,15 @@ __device__ __noinline__ int grid_flush(GridWarpShared &sh, const WalkParams &p, 
     return flush_queue<kFlatOnly>(sh, p, chunk_base, lane, qn, all);
 }
 
+// record emission out of line as well: the pipelined loop then shares its registers with nothing
+__device__ __noinline__ void grid_emit(GridWarpShared &sh, const WalkParams &p, int64_t c_cur, int64_t chunk_base, int lane) {
+    emit_chunk_hits(sh, p, c_cur, chunk_base, lane);
+}
+
 struct GridRay { double vn, va, vb, dn, da, db; };
 
 template <int kFlatOnly>
-__global__ void __launch_bounds__(kWalkWarps * 32, TRC_GRID_MIN_CTAS)
+__global__ void __launch_bounds__(kGridWarps * 32, TRC_GRID_MIN_CTAS)
 nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
     extern __shared__ __align__(16) unsigned char grid_smem[];
     GridShared &S = *reinterpret_cast<GridShared *>(grid_smem);
@@ -1100,7 +1109,7 @@ nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
         if (p.sink.hit_surf)
             for (int i = lane; i < chunk_n; i += 32)
                 p.sink.hit_surf[chunk_base + i] = sh.best_t[i] == TRC_INF_BITS ? -1 : sh.best_s[i];
-        if (p.sink.records) emit_chunk_hits(sh, p, (int64_t)c, chunk_base, lane);
+        if (p.sink.records) grid_emit(sh, p, (int64_t)c, chunk_base, lane);
         __syncwarp();
     }
 }
@@ -1205,19 +1214,19 @@ static int launch_nearest(const TrcScene *sc, int64_t n, const double *d_vert, c
         const size_t gsmem = sizeof(GridShared) + 4 * (size_t)sc->grid.n_words;
         int gocc = sc->grid_occ[gvariant];
         if (gocc <= 0) {
-            TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&gocc, gkernels[gvariant], kWalkWarps * 32, gsmem));
+            TRC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&gocc, gkernels[gvariant], kGridWarps * 32, gsmem));
             if (gocc < 1) gocc = 1;
             scw->grid_occ[gvariant] = gocc;
         }
         WalkParams g = p;
         g.g = sc->grid;
         g.dirty_list = scw->d_dirty; g.dirty_count = scw->d_dirty_counters;
-        int64_t gblocks = std::min<int64_t>(blocks, (int64_t)sc->num_sms * gocc);
+        int64_t gblocks = std::min<int64_t>((n_chunks + kGridWarps - 1) / kGridWarps, (int64_t)sc->num_sms * gocc);
         if (dyn) {
-            TRC_CUDA(launch_pdl(gkernels[gvariant], dim3((unsigned)gblocks), dim3(kWalkWarps * 32), gsmem, st, g));
+            TRC_CUDA(launch_pdl(gkernels[gvariant], dim3((unsigned)gblocks), dim3(kGridWarps * 32), gsmem, st, g));
         } else {
             TRC_CUDA(cudaMemsetAsync(sc->d_chunk_counter, 0, sizeof(unsigned long long), st));
-            gkernels[gvariant]<<<(unsigned)gblocks, kWalkWarps * 32, gsmem, st>>>(g);
+            gkernels[gvariant]<<<(unsigned)gblocks, kGridWarps * 32, gsmem, st>>>(g);
         }
         int rc = check_launch("nearest_hit_grid");
         if (rc != TRC_OK) return rc;

@@ -29,6 +29,9 @@ inline int64_t up256(int64_t x) { return (x + 255) & ~(int64_t)255; }
 
 constexpr int kOrderWarps = 8;
 constexpr int kMaxBins = 256;
+#ifndef TRC_ORDER_MIN_CHUNKS
+#define TRC_ORDER_MIN_CHUNKS 1
+#endif
 #ifndef TRC_ORDER_TILES
 #define TRC_ORDER_TILES 592
 #endif
@@ -342,7 +345,8 @@ int tiles_for(int64_t n_in_cap, int *chunks_per_tile) {
     int64_t n_chunks = (n_in_cap + TRC_HIT_CHUNK - 1) / TRC_HIT_CHUNK;
     if (n_chunks < 1) n_chunks = 1;
     int64_t g = (n_chunks + kTargetTiles - 1) / kTargetTiles;
-    if (g < kOrderWarps) g = kOrderWarps;      // at least a chunk per warp: small bundles get few tiles (short scan)
+    // at least TRC_ORDER_MIN_CHUNKS chunks per warp: small bundles get few tiles (short scan, fuller CTAs)
+    if (g < kOrderWarps * TRC_ORDER_MIN_CHUNKS) g = kOrderWarps * TRC_ORDER_MIN_CHUNKS;
     *chunks_per_tile = (int)g;
     return (int)((n_chunks + g - 1) / g);
 }
