@@ -124,20 +124,22 @@ order_hist_kernel(OrderParams p) {
     }
 }
 
-// One block: exclusive scan of every bin's column of the (tile, bin) table over the tiles, then of the bin
-// totals.  Warp w owns a contiguous band of tiles; lanes own bins lane, lane + 32, ... (coalesced rows).
+// One block of kScanWarps warps: exclusive scan of every bin's column of the (tile, bin) table over the tiles, then
+// of the bin totals.  Warp w owns a contiguous band of tiles; lanes own bins lane, lane + 32, ... (coalesced rows).
 // Pass 1 sums the bands, pass 2 rewrites them as running prefixes starting from the sum of the bands before.
-__global__ void __launch_bounds__(kOrderWarps * 32)
+// 32 warps: the bands are short (19 rows of 592), the kernel's ~50 us at 8 warps were a serial row walk.
+constexpr int kScanWarps = 32;
+__global__ void __launch_bounds__(kScanWarps * 32)
 order_scan_kernel(OrderParams p) {
-    __shared__ uint32_t cnt[kOrderWarps][kMaxBins];
+    __shared__ uint32_t cnt[kScanWarps][kMaxBins];
     __shared__ long long s_tot[kMaxBins];
     pdl_wait();
     pdl_trigger();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool single = p.n_keys <= kMaxBins;
     const int rows = p.n_tiles;
-    const int band = (rows + kOrderWarps - 1) / kOrderWarps;
-    const int r0 = warp * band, r1 = min(rows, r0 + band);
+    const int band = (rows + kScanWarps - 1) / kScanWarps;
+    const int r0 = min(rows, warp * band), r1 = min(rows, r0 + band);
     uint32_t acc[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k] = 0;
@@ -175,21 +177,22 @@ order_scan_kernel(OrderParams p) {
             }
         }
     }
-    // bin totals and their exclusive scan (= slot offsets per surface for a single pass)
+    // bin totals and their exclusive scan (= slot offsets per surface for a single pass): the first 256 threads
+    const bool low = threadIdx.x < kMaxBins;
     long long tot = 0;
-    if ((int)threadIdx.x < p.nbins) {
-#pragma unroll
-        for (int w = 0; w < kOrderWarps; ++w) tot += cnt[w][threadIdx.x];
+    if (low && (int)threadIdx.x < p.nbins) {
+#pragma unroll 8
+        for (int w = 0; w < kScanWarps; ++w) tot += cnt[w][threadIdx.x];
     }
-    s_tot[threadIdx.x] = tot;
+    if (low) s_tot[threadIdx.x] = tot;
     __syncthreads();
     for (int o = 1; o < kMaxBins; o <<= 1) {          // inclusive Hillis-Steele scan over the 256 bins
-        long long add = (int)threadIdx.x >= o ? s_tot[threadIdx.x - o] : 0;
+        long long add = (low && (int)threadIdx.x >= o) ? s_tot[threadIdx.x - o] : 0;
         __syncthreads();
-        s_tot[threadIdx.x] += add;
+        if (low) s_tot[threadIdx.x] += add;
         __syncthreads();
     }
-    if ((int)threadIdx.x < p.nbins) {
+    if (low && (int)threadIdx.x < p.nbins) {
         p.bin_off[threadIdx.x] = s_tot[threadIdx.x] - tot;
         if (single && p.hits_per_surface) p.hits_per_surface[threadIdx.x] += tot;
     }
@@ -530,7 +533,7 @@ extern "C" int trc_trace(const TrcScene *sc, const TrcTraceArgs *a, void *stream
         op.out_vals = first_to_alt ? alt_v : slot_rec;
         const unsigned oblocks = (unsigned)op.n_tiles;
         TRC_CUDA(launch_pdl(order_hist_kernel, dim3(oblocks), dim3(kOrderWarps * 32), 0, st, op));
-        TRC_CUDA(launch_pdl(order_scan_kernel, dim3(1), dim3(kOrderWarps * 32), 0, st, op));
+        TRC_CUDA(launch_pdl(order_scan_kernel, dim3(1), dim3(kScanWarps * 32), 0, st, op));
         TRC_CUDA(launch_pdl(order_scatter_kernel, dim3(oblocks), dim3(kOrderWarps * 32), 0, st, op));
         rc = check_launch("order", 3);
         if (rc != TRC_OK) return rc;
