@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 13
+#define TRC_ABI_VERSION 14
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -130,6 +130,15 @@ typedef enum TrcOpticsKind {
                                   kernel treats the surface as a Lambertian that absorbs nothing; trc_spectra then absorbs
                                   each ray's spectrum sample by sample (table = thetas, then wavelengths and the
                                   absorptance grid; op[6] = number of wavelengths) and integrates the energy */
+#define TRC_F_TABULATED   16u  /* TRC_O_REFRACTIVE between media given by material tables (Refractive :726-858,
+                                  RefractiveAbsorbant :908-944): the indices are complex, m(lambda) = n + i k interpolated
+                                  linearly from knots in the table pool -- material 1 at table_off (table_len knots:
+                                  lambdas, then n, then k), material 2 at op[0] (op[1] knots).  The ray's index (columns
+                                  d_ref_index + d_ref_index_im) equal to material 1's at its wavelength enters material 2
+                                  and vice versa; Snell with the real parts, Fresnel with the complex ones (real part of
+                                  R kept, :839); op[4] != 0: every child is attenuated by exp(-4 pi k path / lambda)
+                                  with its own k and wavelength (optics.attenuations, optics.py:205-212), path scaled by
+                                  op[7].  Needs d_wavelengths. */
 #define TRC_F_IAM         4u   /* Martin-Ruiz incidence-angle modifier (IAM.__call__ :277-282) replaces the
                                   energy of Lambertian_IAM :303 / RealReflective_IAM :320:
                                   E' = E (1 - abs) (1 - exp(-cos^c / a_r)) / (1 - exp(-1 / a_r)),
@@ -384,6 +393,9 @@ typedef struct TrcOpticsArgs {
     const int64_t *d_ray_ids;
     int64_t ray_id_base;
     int64_t *d_out_ray_ids;
+    /* imaginary part of ref_index, per ray / per child (nullable: zero): scenes with TRC_F_TABULATED surfaces */
+    const double *d_ref_index_im;
+    double *d_out_ref_index_im;
 } TrcOpticsArgs;
 int trc_optics(const TrcScene *scene, const TrcOpticsArgs *args, void *stream);
 

@@ -134,10 +134,19 @@ def refractive_children(base, hit, d, normals, energy, sel, wl, m1, v_parent, al
             rots = [rots]
         for i in range(h):
             normals[:, i] = N.dot(rots[i], errors[:, i])
-    n2 = N.where(m1 == base._ref_idxs[0], base._ref_idxs[1], base._ref_idxs[0])     # :1217-1218
-    refr, out_dirs = refractions(m1, n2, d, normals)
+    tabulated = not hasattr(base, '_ref_idxs')      # Refractive / RefractiveAbsorbant: materials m(lambda), complex
+    if tabulated:                                   # toggle_ref_idx :744-756, _refract_dirs :781-785
+        mat_0 = base._materials[0].m(wl)
+        n2 = N.where(m1 == mat_0, base._materials[1].m(wl), mat_0)
+        refr, out_dirs = refractions(N.real(m1), N.real(n2), d, normals)
+    else:
+        n2 = N.where(m1 == base._ref_idxs[0], base._ref_idxs[1], base._ref_idxs[0])     # :1217-1218
+        refr, out_dirs = refractions(m1, n2, d, normals)
     R = N.ones(h)
-    R[refr] = fresnel(d[:, refr], normals[:, refr], m1[refr], n2[refr])             # :841-843
+    import warnings as _w
+    with _w.catch_warnings():                       # complex reflectance into the float array: the real part (:839)
+        _w.simplefilter('ignore')
+        R[refr] = fresnel(d[:, refr], normals[:, refr], m1[refr], n2[refr])         # :841-843
     take = (lambda a, m: None if a is None else a[m])
     if base._single_ray:                                           # :1252-1281
         refl = N.random.uniform(size=R.shape) <= R
@@ -155,7 +164,13 @@ def refractive_children(base, hit, d, normals, energy, sel, wl, m1, v_parent, al
         parts = [Bundle(hit, reflections(d, normals), energy * R, sel, wl, m1),
                  Bundle(hit[:, refr], out_dirs, energy[refr] * (1. - R[refr]), sel[refr], take(wl, refr), n2[refr])]
     child = Bundle.concat(parts)
-    if getattr(base, 'a_c', None) is not None:                     # attenuate :874-889
+    if tabulated and hasattr(base, 'a_c') and base.a_c is None:    # RefractiveAbsorbant: attenuate :874-881 with k
+        pos = N.searchsorted(sel, child.parents)
+        path = N.sqrt(N.sum((child.vertices - v_parent[:, pos]) ** 2, axis=0))
+        if base._scaling != 1.:
+            path = path * base._scaling
+        child.energy = N.exp(-4. * N.pi * path * N.imag(child.ref_index) / child.wavelengths) * child.energy   # optics.py:205-212
+    elif getattr(base, 'a_c', None) is not None:                   # attenuate :874-889
         # parents index the incoming bundle; v_parent / m1 are given per selected ray, so map back
         pos = N.searchsorted(sel, child.parents)
         path = N.sqrt(N.sum((child.vertices - v_parent[:, pos]) ** 2, axis=0))
@@ -375,7 +390,8 @@ class OracleEngine(object):
         ri = None
         if hasattr(bundle, 'has_property') and bundle.has_property('ref_index'):
             try:
-                ri = N.asarray(bundle.get_ref_index(), float)
+                ri = N.asarray(bundle.get_ref_index())
+                ri = ri if N.iscomplexobj(ri) else ri.astype(float)
             except (KeyError, AttributeError):
                 ri = None
         sp = None
@@ -427,7 +443,7 @@ class OracleEngine(object):
                     weak.append(delete)
                     outg.append(child.take(N.nonzero(~delete)[0]) if delete.any() else child)
                     continue
-                if 'RefractiveHomogenous' in _names(base_opt):      # row O8
+                if 'RefractiveHomogenous' in _names(base_opt) or 'Refractive' in _names(base_opt):      # row O8
                     child = refractive_children(base_opt, hit, d_in, normals, e_in, sel, wl_in,
                                                 bund.ref_index[sel], bund.vertices[:, sel],
                                                 bund.wavelengths, bund.ref_index)

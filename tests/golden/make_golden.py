@@ -35,6 +35,7 @@ TRACE_CASES = {
     'c9_refractive': (scenes.c9_refractive, dict(n_rays=2000), 22, 7, 1e-3 * 1000. * np.pi * 1.21 / 2000),
     'c10_polychromatic': (scenes.c10_polychromatic, dict(n_rays=2000), 23, 5, 1e-3 * 1000. * np.pi * 1.44 / 2000),
     'c11_bifacial': (scenes.c11_bifacial, dict(n_rays=3000), 24, 6, 1e-3 * 1000. * np.pi * 2.56 / 3000),
+    'c12_refractive_materials': (scenes.c12_refractive_materials, dict(n_rays=2000), 25, 8, 1e-4 * 1000. * np.pi * 0.81 / 2000),
 }
 # raw lists of the accountants (get_all_hits() raises in the reference when a PolychromaticAccountant is there)
 _ACC_LISTS = ('_absorbed', '_attenuated', '_received', '_scattered', '_wavelengths', '_spectra', '_hits',
@@ -65,6 +66,10 @@ def trace_reference(name):
             out['p%d' % k] = b.get_parents()
         if name == 'c9_refractive':
             out['r%d' % k] = b.get_ref_index()
+        if name == 'c12_refractive_materials':          # complex indices: real and imaginary parts, compared as floats
+            out['rr%d' % k] = np.real(b.get_ref_index())
+            out['ri%d' % k] = np.imag(b.get_ref_index())
+            out['wl%d' % k] = b.get_wavelengths()
         if name == 'c10_polychromatic':
             out['w%d' % k] = b.get_wavelengths()
             out['s%d' % k] = b.get_spectra()

@@ -39,6 +39,12 @@ def compare_tree(gold, tree, n_levels=None, rtol=RTOL):
         close(b.get_energy(), gold['e%d' % k], rtol, f'level {k} energy')
         if 'r%d' % k in gold.files:
             assert np.array_equal(np.asarray(b.get_ref_index()), gold['r%d' % k]), f'level {k}: ref_index differs'
+        if 'rr%d' % k in gold.files:                # complex refractive indices from material tables
+            ri = np.asarray(b.get_ref_index())
+            close(np.real(ri), gold['rr%d' % k], rtol, f'level {k} Re(ref_index)')
+            im, ref_im = np.imag(ri), gold['ri%d' % k]          # k ~ 1e-8: relative, not absolute
+            assert np.all(np.abs(im - ref_im) <= max(rtol, 1e-12) * np.abs(ref_im)), f'level {k} Im(ref_index)'
+            close(b.get_wavelengths(), gold['wl%d' % k], rtol, f'level {k} wavelengths')
         if 'w%d' % k in gold.files:                 # polychromatic bundles: (W, n) wavelengths and spectra
             close(b.get_wavelengths(), gold['w%d' % k], rtol, f'level {k} wavelengths')
             close(b.get_spectra(), gold['s%d' % k], rtol, f'level {k} spectra')

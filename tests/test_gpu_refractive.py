@@ -216,3 +216,60 @@ def test_refractive_needs_ref_index_and_refuses_accountants():
     asm = T.assembly.Assembly(objects=[T.object.AssembledObject(surfs=[surf])])
     with pytest.raises(NotImplementedError):
         _engine(asm).compile()
+
+
+def test_tabulated_media_snell_fresnel_and_k_attenuation():
+    """Refractive / RefractiveAbsorbant with material tables (optics_callables.py:726-858, 908-944), device draws:
+    Snell's law with Re m(lambda), energy split R + T = 1 with the complex-index Fresnel reflectance, the child's
+    complex index = the material's at its wavelength, attenuation exp(-4 pi k path / lambda) of the children."""
+    import os
+    from tracer_b200.tracer_engine import TracerEngine
+    oc, ocn, sg = T.optics_callables, T.optical_constants, T.spatial_geometry
+    from tracer_b200.models import scenes as ms
+    glass = ocn.OpticalMaterialFromFile(os.path.join(os.path.dirname(os.path.abspath(ms.__file__)), 'data', 'glass_nk.csv'))
+    air = ocn.Air()
+    n = 20000
+    rng = np.random.RandomState(4)
+    wl = rng.uniform(4e-7, 2.3e-6, n)
+    d = np.tile(np.c_[[0.5, 0.2, -1.]] / np.sqrt(1.29), (1, n))
+    v = np.vstack([rng.uniform(-0.5, 0.5, n), rng.uniform(-0.5, 0.5, n), np.ones(n)])
+    for cls, kw in ((oc.Refractive, {}), (oc.RefractiveAbsorbant, dict(attenuation_coefficient_1=1., scaling=3.))):
+        surf = T.surface.Surface(T.flat_surface.RectPlateGM(6., 6.), cls(air, glass, single_ray=False, **kw))
+        asm = T.assembly.Assembly(objects=[T.object.AssembledObject(surfs=[surf])])
+        b = T.ray_bundle.RayBundle(vertices=v, directions=d, energy=np.ones(n), wavelengths=wl, ref_index=air.m(wl))
+        eng = TracerEngine(asm, rng='philox', seed=2)
+        eng.ray_tracer(b, reps=1, min_energy=1e-12, tree=True)
+        child = eng.tree[1]
+        assert child.get_num_rays() == 2 * n
+        par = child.get_parents()
+        assert np.array_equal(par[:n], np.arange(n)) and np.array_equal(par[n:], np.arange(n))
+        m2 = glass.m(wl)
+        ri = child.get_ref_index()
+        close(np.real(ri[n:]), m2.real, 1e-12, 'Re m2')
+        assert np.allclose(np.imag(ri[n:]), m2.imag, rtol=1e-9, atol=0.)
+        assert np.all(ri[:n] == 1.)                                   # reflected rays stay in air
+        close(child.get_wavelengths(), np.r_[wl, wl], 1e-15, 'wavelengths')
+        # Snell: sin(theta_2) = sin(theta_1) / Re m2
+        dr = child.get_directions()[:, n:]
+        sin1 = np.sqrt(1. - d[2] ** 2)
+        sin2 = np.sqrt(dr[0] ** 2 + dr[1] ** 2)
+        close(sin2, sin1 / m2.real, 1e-12, 'Snell')
+        # Fresnel with complex indices, real part kept
+        th = np.arccos(np.abs(d[2]))
+        bar = np.sqrt(1 - (1. / m2 * np.sin(th)) ** 2)
+        rs = ((np.cos(th) - m2 * bar) / (np.cos(th) + m2 * bar)) ** 2
+        rp = ((bar - m2 * np.cos(th)) / (bar + m2 * np.cos(th))) ** 2
+        R = ((rs + rp) / 2).real
+        e = child.get_energy()
+        if cls is oc.Refractive:
+            close(e[:n], R, 1e-12, 'reflected energy')
+            close(e[n:], 1. - R, 1e-12, 'refracted energy')
+        else:
+            path = 3. * np.sqrt(np.sum((child.get_vertices()[:, n:] - v) ** 2, axis=0))
+            close(e[:n], R, 1e-12, 'reflected energy (k = 0 in air)')
+            close(e[n:], (1. - R) * np.exp(-4. * np.pi * path * m2.imag / wl), 1e-12, 'attenuated refracted energy')
+    # without a coefficient the reference raises AttributeError on the first hit: refused at compile time
+    surf = T.surface.Surface(T.flat_surface.RectPlateGM(6., 6.), oc.RefractiveAbsorbant(air, glass))
+    asm = T.assembly.Assembly(objects=[T.object.AssembledObject(surfs=[surf])])
+    with pytest.raises(NotImplementedError):
+        TracerEngine(asm).ray_tracer(b, reps=1, min_energy=1e-12)

@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtracer_b200.so")
 
-ABI_VERSION = 13
+ABI_VERSION = 14
 
 # enum TrcGeomKind
 (G_FLAT_INFINITE, G_RECT_PLATE, G_RECT_EXTRUDED, G_ROUND_PLATE, G_TRIANGLE, G_PARABOLOID,
@@ -29,6 +29,7 @@ F_ONE_SIDED = 1
 F_UNBOUNDED = 2
 F_IAM = 4
 F_POLY = 8
+F_TABULATED = 16
 # enum TrcFluxCoord
 (FLUX_XY, FLUX_R_ATAN_XY, FLUX_R_ATAN_YX, FLUX_Z_PHI, FLUX_THETA_PHI) = range(5)
 BVH_MAX_LEAF = 4
@@ -67,6 +68,7 @@ class OpticsArgs(C.Structure):
         ("d_slot_surf", C.c_void_p), ("d_seg", C.c_void_p), ("d_child_off", C.c_void_p),
         ("d_ref_index", C.c_void_p), ("d_out_ref_index", C.c_void_p), ("d_n_void", C.c_void_p),
         ("d_ray_ids", C.c_void_p), ("ray_id_base", C.c_int64), ("d_out_ray_ids", C.c_void_p),
+        ("d_ref_index_im", C.c_void_p), ("d_out_ref_index_im", C.c_void_p),
     ]
 
 

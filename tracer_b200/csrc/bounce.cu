@@ -37,6 +37,8 @@ struct OpticsParams {
     const int64_t *ids_in;
     int64_t id_base;
     int64_t *o_ids;
+    const double *ref_index_im;    // imaginary parts of ref_index (scenes with tabulated refractive media), nullable
+    double *o_ref_index_im;
     // device-driven trace (trace.cu): hit count and bookkeeping live in device memory
     TrcBounceCtl *ctl;            // nullable; when set h = min(ctl->hits, capacity)
     int64_t capacity;
@@ -89,6 +91,62 @@ __device__ __forceinline__ void philox_draws(const TrcSurfaceRec *s, uint64_t se
 
 // TRC_O_REFRACTIVE: two child slots per hit (block A reflected, block B refracted), either of
 // which may be void (d_cull = 2).  Out of line: keeps the common optics path at its register count.
+// TRC_F_TABULATED: the two media are material tables, the indices complex (optics.cuh apply_refractive_tab).
+__device__ __noinline__ void refractive_tab_slot(const OpticsParams &p, const TrcSurfaceRec *s, const double *tables,
+                                                 int64_t q, int sidx, int64_t r, V3 v, V3 d, double e_in, double wl,
+                                                 V3 hit, V3 n, const double *u) {
+    const Cx m1 = cx(p.ref_index[r], p.ref_index_im ? p.ref_index_im[r] : 0.0);
+    RefractTabOut ro = apply_refractive_tab(s, tables, d, n, e_in, m1, wl, u);
+    const int64_t first = p.seg[sidx];
+    // single_ray mode inherits the columns it does not set (the reflected ray's ref_index, both rays' wavelengths)
+    // from bundle position = rank of the hit among the surface's hits (rays.inherit(argwhere(refl), ...), :797-815)
+    Cx m_inherit = m1;
+    if (s->op[2] != 0.0) {
+        m_inherit = cx(p.ref_index[q - first], p.ref_index_im ? p.ref_index_im[q - first] : 0.0);
+        wl = p.wavelengths[q - first];
+    }
+    double att_path = 0.0;
+    if (s->op[4] != 0.0) {          // Absorbant.attenuate :874-881: path from the parent vertex, scaled
+        double dx = hit.x - v.x, dy = hit.y - v.y, dz = hit.z - v.z;
+        att_path = sqrt(dx * dx + dy * dy + dz * dz);
+        if (s->op[7] != 1.0) att_path *= s->op[7];
+    }
+    const int64_t ca = p.child_off[sidx] + (q - first), cb = ca + (p.seg[sidx + 1] - first);
+    int n_weak = 0, n_gone = 0;
+    double e_out = 0.0;
+    for (int side = 0; side < 2; ++side) {
+        const int64_t c = side ? cb : ca;
+        const bool has = side ? ro.has_refr : ro.has_refl;
+        const V3 od = side ? ro.dir_refr : ro.dir_refl;
+        const Cx mc = side ? ro.m2 : m_inherit;
+        double oe = has ? (side ? ro.e_refr : ro.e_refl) : 0.0;
+        if (s->op[4] != 0.0) oe = exp(-4.0 * M_PI * att_path * mc.im / wl) * oe;      // optics.attenuations, optics.py:205-212
+        p.o_vert[c] = hit.x; p.o_vert[p.ld_out + c] = hit.y; p.o_vert[2 * p.ld_out + c] = hit.z;
+        p.o_dir[c] = od.x; p.o_dir[p.ld_out + c] = od.y; p.o_dir[2 * p.ld_out + c] = od.z;
+        p.o_energy[c] = oe;
+        p.o_parents[c] = r;
+        p.o_ref_index[c] = mc.re;
+        if (p.o_ref_index_im) p.o_ref_index_im[c] = mc.im;
+        if (p.o_ids) {
+            uint64_t id = (uint64_t)(p.ids_in ? p.ids_in[r] : p.id_base + r);
+            p.o_ids[c] = (int64_t)((id << 1) | (uint64_t)side);
+        }
+        if (p.o_wavelengths) p.o_wavelengths[c] = wl;
+        const bool weak = has && oe <= p.min_energy;
+        if (p.cull) p.cull[c] = has ? (weak ? 1 : 0) : 2;
+        n_weak += weak ? 1 : 0;
+        n_gone += has ? 0 : 1;
+        e_out += has ? oe : 0.0;
+    }
+    if (p.absorbed) p.absorbed[q] = e_in - e_out;
+    if (p.normals) { p.normals[q] = n.x; p.normals[p.ld_out + q] = n.y; p.normals[2 * p.ld_out + q] = n.z; }
+    if (p.e_in) p.e_in[q] = e_in;
+    if (p.attenuated) p.attenuated[q] = 0.0;
+    if (p.dirs_in) { p.dirs_in[q] = d.x; p.dirs_in[p.ld_out + q] = d.y; p.dirs_in[2 * p.ld_out + q] = d.z; }
+    if (n_weak && p.n_cull) atomicAdd(p.n_cull, (unsigned long long)n_weak);
+    if (n_gone && p.n_void) atomicAdd(p.n_void, (unsigned long long)n_gone);
+}
+
 __device__ __noinline__ void refractive_slot(const OpticsParams &p, const TrcSurfaceRec *s, int64_t q, int sidx,
                                              int64_t r, V3 v, V3 d, double e_in, double wl, V3 hit, V3 n,
                                              const double *u) {
@@ -115,6 +173,7 @@ __device__ __noinline__ void refractive_slot(const OpticsParams &p, const TrcSur
         p.o_energy[c] = oe;
         p.o_parents[c] = r;
         p.o_ref_index[c] = side ? ro.m2 : m_inherit;
+        if (p.o_ref_index_im) p.o_ref_index_im[c] = 0.0;
         if (p.o_ids) {                  // the two children of a split get distinct ids: (id << 1) | side
             uint64_t id = (uint64_t)(p.ids_in ? p.ids_in[r] : p.id_base + r);
             p.o_ids[c] = (int64_t)((id << 1) | (uint64_t)side);
@@ -182,7 +241,8 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
             philox_draws(s, p.seed, p.bounce, (uint64_t)(p.ids_in ? p.ids_in[r] : p.id_base + r), u);
         }
         if (kRefractive && s->okind == TRC_O_REFRACTIVE) {
-            refractive_slot(p, s, q, sidx, r, v, d, e_in, wl, hit, n, u);
+            if (s->flags & TRC_F_TABULATED) refractive_tab_slot(p, s, tables, q, sidx, r, v, d, e_in, wl, hit, n, u);
+            else refractive_slot(p, s, q, sidx, r, v, d, e_in, wl, hit, n, u);
         } else {
         OpticsOut o = apply_optics(s, tables, d, n, e_in, wl, u, v, hit);
         if (s->flags & TRC_F_ONE_SIDED) {
@@ -220,6 +280,11 @@ optics_kernel(const TrcSurfaceRec *__restrict__ surfs, const double *__restrict_
         p.o_energy[c] = e_first;
         p.o_parents[c] = r;
         if (p.o_ref_index) p.o_ref_index[c] = p.ref_index[r];
+        if (kRefractive && p.o_ref_index_im) {
+            const double im = p.ref_index_im ? p.ref_index_im[r] : 0.0;
+            p.o_ref_index_im[c] = im;
+            if (c2 >= 0) p.o_ref_index_im[c2] = im;
+        }
 #ifndef TRC_OPT_NO_IDS
         if (p.o_ids) {
             int64_t id = p.ids_in ? p.ids_in[r] : p.id_base + r;
@@ -589,6 +654,7 @@ int trc_optics_dyn(const TrcScene *sc, const TrcOpticsArgs *a, const TrcOpticsDy
     p.ref_index = a->d_ref_index; p.o_ref_index = a->d_out_ref_index;
     p.n_void = reinterpret_cast<unsigned long long *>(a->d_n_void);
     p.ids_in = a->d_ray_ids; p.id_base = a->ray_id_base; p.o_ids = a->d_out_ray_ids;
+    p.ref_index_im = a->d_ref_index_im; p.o_ref_index_im = a->d_out_ref_index_im;
     p.ctl = nullptr; p.capacity = a->h; p.cta_surv = nullptr; p.absorbed_per_surface = nullptr;
     if (dyn) {
         if (sc->has_split) return fail(TRC_ERR_UNSUPPORTED_KIND, "trc_optics: device-driven trace with two-children optics%s");
@@ -601,6 +667,9 @@ int trc_optics_dyn(const TrcScene *sc, const TrcOpticsArgs *a, const TrcOpticsDy
         return fail(TRC_ERR_BAD_ARGUMENT,
                     "trc_optics: a scene with TRC_O_REFRACTIVE surfaces needs d_ref_index and d_child_off%s");
     if (p.child_off && !p.seg) return fail(TRC_ERR_BAD_ARGUMENT, "trc_optics: d_child_off needs d_seg%s");
+    if (sc->has_tabulated && (!p.wavelengths || !p.o_ref_index_im))
+        return fail(TRC_ERR_BAD_ARGUMENT,
+                    "trc_optics: refractive media from material tables need d_wavelengths and d_out_ref_index_im%s");
     int64_t blocks = (a->h + 255) / 256;
     if (dyn) {
         TRC_CUDA(launch_pdl(optics_kernel<false>, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream,

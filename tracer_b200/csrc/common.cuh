@@ -155,6 +155,7 @@ struct TrcScene {
                                        // float64 stage; null unless the scene is flat-only and has triangles
     bool has_refractive = false;       // some surface is TRC_O_REFRACTIVE: the optics need the ref_index column
     bool has_split = false;
+    bool has_tabulated = false;        // some TRC_O_REFRACTIVE surface takes its indices from material tables
     bool has_grid = false;             // a shadow grid is set (use_bvh == 2 routes coherent rays through it)
     TrcShadowGrid grid = {};
     uint32_t *d_grid_bits = nullptr, *d_grid_cells = nullptr;

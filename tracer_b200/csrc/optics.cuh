@@ -161,6 +161,84 @@ __device__ __forceinline__ RefractOut apply_refractive(const TrcSurfaceRec *s, V
     return r;
 }
 
+// ---- refraction between media given by material tables (TRC_F_TABULATED): complex indices
+struct Cx { double re, im; };
+__device__ __forceinline__ Cx cx(double re, double im) { Cx z; z.re = re; z.im = im; return z; }
+__device__ __forceinline__ Cx cadd(Cx a, Cx b) { return cx(a.re + b.re, a.im + b.im); }
+__device__ __forceinline__ Cx csub(Cx a, Cx b) { return cx(a.re - b.re, a.im - b.im); }
+__device__ __forceinline__ Cx cmul(Cx a, Cx b) { return cx(a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re); }
+__device__ __forceinline__ Cx cscale(Cx a, double k) { return cx(a.re * k, a.im * k); }
+__device__ __forceinline__ Cx cdiv(Cx a, Cx b) {
+    double den = b.re * b.re + b.im * b.im;
+    return cx((a.re * b.re + a.im * b.im) / den, (a.im * b.re - a.re * b.im) / den);
+}
+__device__ __forceinline__ Cx csqrt(Cx z) {          // principal branch, as numpy.sqrt of a complex array
+    double r = hypot(z.re, z.im);
+    if (r == 0.0) return cx(0.0, 0.0);
+    double a = sqrt(0.5 * (r + fabs(z.re)));
+    double b = 0.5 * z.im / a;
+    if (z.re >= 0.0) return cx(a, b);
+    return cx(fabs(b), z.im < 0.0 ? -a : a);
+}
+// m(lambda) of a material: knots at `t` = lambdas[n], then n[n], then k[n]; linear, clamped at the ends
+__device__ __forceinline__ Cx material_m(const double *t, int n, double wl) {
+    return cx(interp1(wl, t, t + n, n), interp1(wl, t, t + 2 * n, n));
+}
+struct RefractTabOut {
+    V3 dir_refl, dir_refr;
+    double e_refl, e_refr;
+    Cx m2;
+    bool has_refl, has_refr;
+};
+// Refractive._make_refraction_bundle (:836-842) for one hit: m1 the ray's complex index, wl its wavelength.
+__device__ __forceinline__ RefractTabOut apply_refractive_tab(const TrcSurfaceRec *s, const double *tables, V3 d, V3 n,
+                                                                double e_in, Cx m1, double wl, const double *u) {
+    const double *op = s->op;
+    RefractTabOut r;
+    if (op[3] >= 0.0) {        // _refract_dirs :765-777
+        double st = sin(u[0]);
+        n = rotation_to_z_apply(n, mk(st * cos(u[1]), st * sin(u[1]), cos(u[0])));
+    }
+    // toggle_ref_idx :744-756.  The reference compares m1 == material_1.m(wavelength) exactly; the ray's index was
+    // produced by the same linear interpolation on the host or on the device, which may differ in the last bits
+    // (fused multiply-add), so "equal" is taken to 1e-9 relative here.
+    const Cx ma = material_m(tables + s->table_off, s->table_len, wl);
+    const Cx mb = material_m(tables + (int)op[0], (int)op[1], wl);
+    const bool in_a = fabs(m1.re - ma.re) <= 1e-9 * fabs(ma.re) && fabs(m1.im - ma.im) <= 1e-9 * fabs(ma.im) + 1e-300;
+    const Cx m2 = in_a ? mb : ma;
+    r.m2 = m2;
+    const double nn = m2.re / m1.re;                     // optics.refractions(m1.real, m2.real, ...) :785
+    const double cos1 = n.x * d.x + n.y * d.y + n.z * d.z;
+    const bool refr = cos1 * cos1 >= 1.0 - nn * nn;
+    double R = 1.0;
+    r.dir_refr = mk(0.0, 0.0, 0.0);
+    if (refr) {
+        double cos2 = sqrt(1.0 - 1.0 / (nn * nn) * (1.0 - cos1 * cos1));
+        double sg = cos1 < 0.0 ? -1.0 : 1.0;
+        r.dir_refr = mk((d.x - cos1 * n.x) / nn + n.x * cos2 * sg,
+                        (d.y - cos1 * n.y) / nn + n.y * cos2 * sg,
+                        (d.z - cos1 * n.z) / nn + n.z * cos2 * sg);
+        // optics.fresnel (optics.py:13-39) in complex arithmetic; the float array R keeps the real part (:839)
+        const double th = acos(fabs(cos1));
+        const double foo = cos(th), sn = sin(th);
+        const Cx q = cscale(cdiv(m1, m2), sn);
+        const Cx bar = csqrt(csub(cx(1.0, 0.0), cmul(q, q)));
+        const Cx rs = cdiv(csub(cscale(m1, foo), cmul(m2, bar)), cadd(cscale(m1, foo), cmul(m2, bar)));
+        const Cx rp = cdiv(csub(cmul(m1, bar), cscale(m2, foo)), cadd(cmul(m1, bar), cscale(m2, foo)));
+        R = 0.5 * (cmul(rs, rs).re + cmul(rp, rp).re);
+    }
+    r.dir_refl = reflect(d, n);
+    if (op[2] != 0.0) {        // single_ray :792-823
+        bool refl = u[2] <= R;
+        r.has_refl = refl; r.has_refr = !refl;
+        r.e_refl = e_in; r.e_refr = e_in;
+    } else {                   // :826-834
+        r.has_refl = true; r.has_refr = refr;
+        r.e_refl = e_in * R; r.e_refr = e_in * (1.0 - R);
+    }
+    return r;
+}
+
 struct OpticsOut { V3 dir; double energy; double attenuated; };
 
 // |(d.n) n|: the cosine of the incidence angle as the reference forms it

@@ -54,6 +54,7 @@ extern "C" int trc_scene_create(const TrcSurfaceRec *surfaces, int32_t n_surface
     for (int32_t i = 0; i < n_surfaces; ++i) {
         if (surfaces[i].gkind > TRC_G_TRIANGLE) sc->flat_only = false;
         if (surfaces[i].okind == TRC_O_REFRACTIVE) sc->has_refractive = sc->has_split = true;
+        if (surfaces[i].okind == TRC_O_REFRACTIVE && (surfaces[i].flags & TRC_F_TABULATED)) sc->has_tabulated = true;
         if (surfaces[i].okind == TRC_O_PERIODIC) sc->has_split = true;
     }
     cudaError_t e = cudaMalloc(&sc->d_surfaces, sizeof(TrcSurfaceRec) * (size_t)n_surfaces);

@@ -373,6 +373,42 @@ def c11_bifacial(T, n_rays=2000):
     return asm, source
 
 
+def c12_refractive_materials(T, n_rays=2000):
+    """Refraction between media given by material objects (complex m(lambda) from a table; optics_callables.py
+    :726-858, :908-944): a glass slab split in the two modes of ``Refractive`` (both children | one child drawn from
+    the Fresnel reflectance, rough surface), under it an absorbing slab (``RefractiveAbsorbant``: attenuation from
+    the imaginary index), a diffuse receiver below.  The rays carry one wavelength each and start in air."""
+    oc = T.optics_callables
+    ocn = _optical_constants(T)
+    here = os.path.dirname(os.path.abspath(__file__))
+    glass = ocn.OpticalMaterialFromFile(os.path.join(here, 'data', 'glass_nk.csv'))
+    air = ocn.Air()
+    sg = T.spatial_geometry
+
+    def plate(opt, z, flip=False, w=3., h=3.):
+        tr = sg.translate(0., 0., z)
+        if flip:
+            tr = np.dot(tr, sg.rotx(np.pi))
+        return T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(w, h), opt)], transform=tr)
+    objs = [
+        plate(oc.Refractive(air, glass, single_ray=False), 1.0),
+        plate(oc.Refractive(air, glass, single_ray=True, sigma=3e-3), 0.7, flip=True),
+        plate(oc.RefractiveAbsorbant(air, glass, single_ray=False, attenuation_coefficient_1=1., scaling=2.), 0.4),
+        plate(oc.RefractiveAbsorbant(air, glass, single_ray=True, attenuation_coefficient_2=1.), 0.1, flip=True),
+        plate(oc.LambertianReceiver(0.6), -0.3, w=8., h=8.),
+    ]
+    asm = T.assembly.Assembly(objects=objs)
+
+    def source():
+        direction = np.r_[0.25, 0.1, -1.]
+        direction = direction / np.sqrt(np.sum(direction ** 2))
+        b = T.sources.disk_bundle(n_rays, np.c_[[-0.2, 0., 1.6]], direction, 0.9, 0.1, flux=1000.)
+        wl = np.random.uniform(3.5e-7, 2.4e-6, size=n_rays)
+        return T.ray_bundle.RayBundle(vertices=b.get_vertices(), directions=b.get_directions(), energy=b.get_energy(),
+                                      wavelengths=wl, ref_index=air.m(wl))
+    return asm, source
+
+
 def _optical_constants(T):
     """The reference keeps its materials outside the tracer package."""
     if T.pkg == 'tracer':

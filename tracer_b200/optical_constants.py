@@ -42,3 +42,11 @@ class OpticalMaterialFromFile(OpticalMaterialTable):
         except KeyError:
             raise ValueError("Invalid wavelength unit. Use 'nm', 'um', or 'm'.")
         OpticalMaterialTable.__init__(self, data[:, 0] * factor, data[:, 1], data[:, 2])
+
+
+class Air(object):
+    """Vacuum / air placeholder: m = 1 at every wavelength (optical_constants.py:143-155)."""
+
+    def m(self, lambdas):
+        return np.ones(len(lambdas))
+

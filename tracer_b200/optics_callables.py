@@ -259,10 +259,41 @@ class RefractiveTransmissiveHomogenous(RefractiveHomogenous):
             self.a_c = np.array(attenuation_coefficients)
 
 
+class Refractive(_OpticsDescription):
+    """Interface between two media whose complex refractive indices come from material objects of the
+    optical_constants module (``material.m(wavelengths)`` = n + i k, :726-858).  The rays carry ``wavelengths`` and a
+    (complex) ``ref_index``; a ray whose index equals material_1's at its wavelength enters material_2 and vice
+    versa.  Snell's law uses the real parts, the Fresnel reflectance the complex indices (its real part is kept)."""
+
+    def __init__(self, material_1, material_2, single_ray=True, sigma=None):
+        self._materials = [material_1, material_2]
+        self._single_ray = single_ray
+        self._sigma = sigma
+
+
+class RefractiveAbsorbant(Refractive):
+    """Refractive followed by Absorbant.attenuate (:908-944, :874-881): the outgoing rays are attenuated over the path
+    from the parent vertex by exp(-4 pi k path / lambda), k the imaginary part of their own index.  As in the
+    reference the constructor's logic is inverted: that happens when an attenuation coefficient IS given (its value
+    is discarded, :920-924); with none given the reference raises AttributeError on the first hit."""
+
+    def __init__(self, material_1, material_2, single_ray=True, sigma=None, attenuation_coefficient_1=None,
+                 attenuation_coefficient_2=None, scaling=1.):
+        Refractive.__init__(self, material_1, material_2, single_ray, sigma)
+        if (attenuation_coefficient_1 is None) and (attenuation_coefficient_2 is None):
+            attenuation_coefficients = [attenuation_coefficient_1, attenuation_coefficient_2]
+        else:
+            attenuation_coefficients = None
+        self._scaling = scaling
+        self.a_c = attenuation_coefficients
+        if self.a_c is not None:
+            self.a_c = np.array(attenuation_coefficients)
+
+
 perfect_mirror = Reflective(0)
 
 _BASE_OPTICS = {c.__name__: c for c in (
-    RefractiveHomogenous, RefractiveTransmissiveHomogenous,
+    Refractive, RefractiveAbsorbant, RefractiveHomogenous, RefractiveTransmissiveHomogenous,
     PeriodicBoundary, FresnelConductorHomogenous,
     Lambertian_IAM, RealReflective_IAM, LambertianSpecular_IAM, LambertianAbsorbant,
     Lambertian_piecewise_Specular_directional_axisymmetric_piecewise,
@@ -277,7 +308,7 @@ _BASE_OPTICS = {c.__name__: c for c in (
 # need complex indices, per-ray spectra or two optics per surface): constructing them says so
 # instead of silently mis-tracing.
 _UNSUPPORTED = (
-    'Refractive', 'RefractiveAbsorbantHomogenous', 'RefractiveScattering',
+    'RefractiveAbsorbantHomogenous', 'RefractiveScattering',
     'RefractiveScatteringHomogenous', 'Scattering', 'ScatteringPeriodicBoundary',
     'Absorbant', 'SemiLambertian', 'Reflective_IAM')
 

@@ -208,6 +208,8 @@ def _material_table(material):
     """(wavelengths, [n..., k...]) knots of a material's complex index.  Materials that
     interpolate a table (scipy interp1d in the reference, OpticalMaterialTable here) give
     their own knots, so the kernel reproduces them exactly; analytic models are sampled."""
+    if type(material).__name__ == 'Air':           # m = 1 at every wavelength (optical_constants.py:143-155)
+        return np.array([0., 1.]), np.array([1., 1., 0., 0.])
     if hasattr(material, 'lambdas') and hasattr(material, 'n') and hasattr(material, 'k'):
         wl, n, k = material.lambdas, material.n, material.k
     elif hasattr(material, 'm_func') and hasattr(material.m_func, 'x'):
@@ -268,7 +270,7 @@ def _optics_record(opt):
              'Lambertian_IAM', 'RealReflective_IAM', 'LambertianSpecular_IAM', 'LambertianAbsorbant',
              'Lambertian_piecewise_Specular_directional_axisymmetric_piecewise', 'PeriodicBoundary',
              'FresnelConductorHomogenous', 'RefractiveHomogenous', 'RefractiveTransmissiveHomogenous',
-             'Lambertian_directional_axisymmetric_piecewise_Polychromatic')
+             'Lambertian_directional_axisymmetric_piecewise_Polychromatic', 'Refractive', 'RefractiveAbsorbant')
     for cls in type(base).__mro__:
         if cls.__name__ in known:
             break
@@ -312,6 +314,31 @@ def _optics_record(opt):
             rec['op'][0] = _scalar(base._n1, 'n1')
             rec['table'] = _material_table(base._material)
             rec['needs_wavelengths'] = True
+        elif name in ('RefractiveAbsorbant', 'Refractive') and not hasattr(base, '_ref_idxs'):
+            # media given by material tables, complex indices (:726-858, :908-944)
+            if accountants:
+                raise NotImplementedError("refractive optics with accountants (see RefractiveHomogenous)")
+            rec['okind'] = L.O_REFRACTIVE
+            rec['flags'] |= L.F_TABULATED
+            sigma = base._sigma
+            if sigma is not None and sigma < 0.:
+                raise ValueError("sigma must not be negative")
+            rec['op'][2] = 1.0 if base._single_ray else 0.0
+            rec['op'][3] = -1.0 if sigma is None else _scalar(sigma, 'sigma')
+            wl_a, nk_a = _material_table(base._materials[0])
+            wl_b, nk_b = _material_table(base._materials[1])
+            rec['table'] = (wl_a, nk_a)                     # material 1: lambdas, then n, then k
+            rec['table2'] = np.concatenate([wl_b, nk_b])    # material 2 goes to the pool too: op[0] = offset, op[1] = knots
+            rec['table2_len'] = len(wl_b)
+            rec['needs_wavelengths'] = True
+            if name == 'RefractiveAbsorbant':
+                if base.a_c is not None:
+                    raise NotImplementedError(
+                        "RefractiveAbsorbant without attenuation coefficients: the reference raises AttributeError on "
+                        "the first hit (Absorbant.attenuate reads self._ref_idxs, optics_callables.py:883); give "
+                        "attenuation_coefficient_1 (any value: the attenuation then comes from the imaginary indices)")
+                rec['op'][4] = 1.0
+                rec['op'][7] = _scalar(base._scaling, 'scaling')
         elif name in ('RefractiveTransmissiveHomogenous', 'RefractiveHomogenous'):
             if accountants:
                 raise NotImplementedError(
@@ -493,6 +520,7 @@ class CompiledScene(object):
         self.children_per_hit = np.where((recs['okind'] == L.O_PERIODIC) | (recs['okind'] == L.O_REFRACTIVE),
                                          2, 1).astype(np.int64)
         self.has_refractive = bool((recs['okind'] == L.O_REFRACTIVE).any())
+        self.has_tabulated = bool(((recs['okind'] == L.O_REFRACTIVE) & ((recs['flags'] & L.F_TABULATED) != 0)).any())
         self.has_split = bool((self.children_per_hit > 1).any())
         if self.has_split and self.has_bifacial:
             raise NotImplementedError("BiFacial managers in a scene with two-children optics (periodic, refractive)")
@@ -550,6 +578,8 @@ class CompiledScene(object):
             x, y = orec['table']
             r['table_off'], r['table_len'] = self._add_table(x), len(x)
             self._add_table(y)
+        if orec.get('table2') is not None:
+            r['op'][0], r['op'][1] = float(self._add_table(orec['table2'])), float(orec['table2_len'])
         back = orec.get('back')
         if back is not None:
             toff, tlen = -1, 0

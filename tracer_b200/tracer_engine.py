@@ -84,10 +84,11 @@ INLINE_SEG_MAX = 4096          # scenes with more surfaces keep the slot offsets
 class _DevBundle(object):
     """Engine-internal view of a bundle living in HBM.  ``slices`` is set while a
     host bundle is still arriving: [(first ray, end ray, CUDA event of its copy)]."""
-    __slots__ = ('V', 'D', 'E', 'W', 'R', 'I', 'SP', 'id_base', 'n', 'slices', 'keep')
+    __slots__ = ('V', 'D', 'E', 'W', 'R', 'RI', 'I', 'SP', 'id_base', 'n', 'slices', 'keep')
 
-    def __init__(self, V, D, E, W=None, slices=None, keep=None, R=None, I=None, id_base=0, SP=None):
+    def __init__(self, V, D, E, W=None, slices=None, keep=None, R=None, I=None, id_base=0, SP=None, RI=None):
         self.V, self.D, self.E, self.W = V, D, E, W
+        self.RI = RI              # imaginary part of ref_index (media given by material tables), else None
         self.SP = SP              # spectra (W, n) of polychromatic rays; W is then (W, n) too
         self.R = R                # ref_index column (refractive scenes), else None
         self.I = I                # source-ray id of each ray (int64), None: id_base + index
@@ -261,14 +262,35 @@ class TracerEngine(object):
                 raise ValueError("polychromatic bundle: 'wavelengths' and 'spectra' must both be (W, n)")
         elif W is not None and W.shape != E.shape:
             raise ValueError("bundle wavelengths must be (n,) (or (W, n) next to 'spectra')")
-        R = col('ref_index', required=False) if bundle.has_property('ref_index') else None
+        R, RI = self._ref_index_columns(bundle)
         if R is not None and R.shape != E.shape:
             raise ValueError("bundle ref_index must be (n,)")
         if V.dim() != 2 or V.shape[0] != 3 or D.shape != V.shape or E.shape[0] != V.shape[1]:
             raise ValueError("bundle arrays must be vertices (3,n), directions (3,n), energy (n,)")
         return _DevBundle(V.contiguous(), D.contiguous(), E.contiguous(), None if W is None else W.contiguous(),
                           R=None if R is None else R.contiguous(), id_base=id_base,
-                          SP=None if SP is None else SP.contiguous())
+                          SP=None if SP is None else SP.contiguous(), RI=None if RI is None else RI.contiguous())
+
+    def _ref_index_columns(self, bundle):
+        """(real, imaginary) device columns of the bundle's ref_index; the imaginary one is None for a real index."""
+        import torch
+        if not bundle.has_property('ref_index') or not getattr(bundle, 'is_set', lambda n: True)('ref_index'):
+            return None, None
+        raw = bundle._props.get('ref_index') if hasattr(bundle, '_props') else None
+        if isinstance(raw, _DeviceColumns):
+            t = raw.pieces[0] if len(raw.pieces) == 1 else torch.cat(raw.pieces, dim=-1)
+            t = t.to(self.device)
+            if t.is_complex():
+                return t.real.contiguous(), t.imag.contiguous()
+            return t, None
+        try:
+            arr = np.asarray(bundle.get_ref_index())
+        except (KeyError, AttributeError):
+            return None, None
+        to_dev = (lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(self.device, non_blocking=True))
+        if np.iscomplexobj(arr):
+            return to_dev(arr.real), to_dev(arr.imag)
+        return to_dev(arr), None
 
     def _upload_in_slices(self, bundle):
         """Large host bundle: allocate it in HBM and enqueue the host->device copy in
@@ -488,6 +510,7 @@ class TracerEngine(object):
                      attenuated=torch.empty(H, dtype=f64, device=dev) if 'attenuated' in want else None,
                      W=None, SP=None, lost_spectra=None,
                      R=torch.empty(Hc, dtype=f64, device=dev) if cur.R is not None else None,
+                     RI=torch.empty(Hc, dtype=f64, device=dev) if (cur.R is not None and scene.has_tabulated) else None,
                      I=torch.empty(Hc, dtype=i64, device=dev))
             if poly:
                 o['W'] = torch.empty((n_w, Hc), dtype=f64, device=dev)
@@ -510,6 +533,8 @@ class TracerEngine(object):
             a.seed, a.bounce, a.min_energy = self.seed, bounce, float(min_energy)
             if cur.R is not None:
                 a.d_ref_index, a.d_out_ref_index = cur.R.data_ptr(), o['R'].data_ptr()
+                a.d_ref_index_im = cur.RI.data_ptr() if cur.RI is not None else None
+                a.d_out_ref_index_im = o['RI'].data_ptr() if o['RI'] is not None else None
             a.d_ray_ids = cur.I.data_ptr() if cur.I is not None else None
             a.ray_id_base, a.d_out_ray_ids = cur.id_base, o['I'].data_ptr()
             for j in range(3):
@@ -584,6 +609,7 @@ class TracerEngine(object):
             counters[1] = (out['cull'] == 1).sum()
 
         oV, oD, oE, oP, cull, oW, oR, oI, oS = (out[k] for k in ('V', 'D', 'E', 'P', 'cull', 'W', 'R', 'I', 'SP'))
+        oRI = out['RI']
         absorbed = out['absorbed']
         # per-surface absorbed energy and hit counts, kept on device: the payload of
         # the multi-GPU all-reduce (tracer_engine_mp.py) and a tally for 'fast' optics
@@ -620,12 +646,16 @@ class TracerEngine(object):
             pS = oS.index_select(-1, pl) if oS is not None else None
             pR = oR.index_select(0, pl) if oR is not None else None
             pI = oI.index_select(0, pl)
+            if oRI is not None:
+                reorder.RI = oRI.index_select(0, pl)
             return pV, pD, pE, pP, pW, pR, pI, pS, perm
+        reorder.RI = None
 
         if scene.has_bifacial:
             # children of a BiFacial surface: the back side's first, each side in hit order (:1891-1899)
             key = 2 * slot_surf + (~back).to(i32) * scene.bifacial_tensors(dev)[1].index_select(0, slot_surf.long()).to(i32)
             oV, oD, oE, oP, oW, oR, oI, oS, perm = reorder(key.contiguous(), 2 * S)
+            oRI = reorder.RI
             cull = cull.index_select(0, perm.long()).contiguous()
         if n_void:
             # refractive surfaces leave void child slots (cull code 2): drop them, keeping the order
@@ -638,15 +668,16 @@ class TracerEngine(object):
             oW = pW[..., :Hc].contiguous() if pW is not None else None
             oS = pS[..., :Hc].contiguous() if pS is not None else None
             oR = pR[:Hc].contiguous() if pR is not None else None
+            oRI = reorder.RI[:Hc].contiguous() if reorder.RI is not None else None
             oI = pI[:Hc].contiguous()
             if Hc == 0:
                 return None, 0, H
-        rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR, I=oI, SP=oS)
+        rec = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR, I=oI, SP=oS, RI=oRI)
         if n_cull and n_cull < Hc:
             # survivors first, weak rays at the back (tracer_engine.py:242-245, 268-274)
             pV, pD, pE, pP, pW, pR, pI, pS, _ = reorder(cull, 2)
-            rec = dict(V=pV, D=pD, E=pE, P=pP, W=pW, R=pR, I=pI, SP=pS)
-        rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR, SP=oS)
+            rec = dict(V=pV, D=pD, E=pE, P=pP, W=pW, R=pR, I=pI, SP=pS, RI=reorder.RI)
+        rec['pre_cull'] = dict(V=oV, D=oD, E=oE, P=oP, W=oW, R=oR, SP=oS, RI=oRI)
         return rec, Hc - n_cull, H
 
     # ------------------------------------------------- device-driven trace
@@ -874,7 +905,11 @@ class TracerEngine(object):
         if rec.get('W') is not None:
             kw['wavelengths'] = cols(rec['W'])
         if rec.get('R') is not None:
-            kw['ref_index'] = cols(rec['R'])
+            if rec.get('RI') is not None:       # complex index (media given by material tables)
+                import torch
+                kw['ref_index'] = cols(torch.complex(rec['R'], rec['RI']))
+            else:
+                kw['ref_index'] = cols(rec['R'])
         if rec.get('SP') is not None:
             kw['spectra'] = cols(rec['SP'])
         return RayBundle(vertices=cols(rec['V']), directions=cols(rec['D']), energy=cols(rec['E']),
@@ -916,6 +951,9 @@ class TracerEngine(object):
             grid = cone is not None and scene.set_shadow_grid(cone[0], cone[1])
         if scene.has_refractive and cur.R is None:
             raise ValueError("scene has refractive optics but the bundle carries no 'ref_index'")
+        if scene.has_tabulated and cur.RI is None:
+            import torch as _t
+            cur.RI = _t.zeros_like(cur.R)
         source_E = cur.E
         # device-driven (trc_trace) unless draws are injected or some optics emits two children per hit
         if scene.needs_spectra and cur.SP is None:
@@ -965,8 +1003,9 @@ class TracerEngine(object):
                 W = rec['W'][..., :n_surv] if rec['W'] is not None else None
                 SP = rec['SP'][..., :n_surv] if rec.get('SP') is not None else None
                 R = rec['R'][:n_surv] if rec.get('R') is not None else None
+                RI = rec['RI'][:n_surv] if rec.get('RI') is not None else None
                 I = rec['I'][:n_surv] if rec.get('I') is not None else None
-                cur = _DevBundle(rec['V'][:, :n_surv], rec['D'][:, :n_surv], rec['E'][:n_surv], W, R=R, I=I, SP=SP)
+                cur = _DevBundle(rec['V'][:, :n_surv], rec['D'][:, :n_surv], rec['E'][:n_surv], W, R=R, I=I, SP=SP, RI=RI)
                 if cur.n == 0:
                     logging.log(self.loglevel, 'Ray bundle depleted')
                     depleted = True
