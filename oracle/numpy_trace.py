@@ -447,6 +447,11 @@ class OracleEngine(object):
                     child = refractive_children(base_opt, hit, d_in, normals, e_in, sel, wl_in,
                                                 bund.ref_index[sel], bund.vertices[:, sel],
                                                 bund.wavelengths, bund.ref_index)
+                    if _unwrap(surf._opt)[1]:
+                        # Accountant.count on the child bundle AS RETURNED, [reflected][refracted]: one ray per hit in
+                        # single_ray mode, subtracted in that order from the hit-ordered incoming energies (:1638-1643);
+                        # otherwise the shapes differ and numpy raises ValueError, as in the reference
+                        self._count(s_idx, surf._opt, hit, d_in, normals, e_in, child.energy, wl_in)
                     record.append(child)
                     delete = child.energy <= min_energy
                     weak.append(delete)

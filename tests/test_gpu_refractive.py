@@ -212,10 +212,39 @@ def test_refractive_needs_ref_index_and_refuses_accountants():
     with pytest.raises(ValueError):
         eng.ray_tracer(bund, reps=1, min_energy=0.)
     oc = T.optics_callables
-    surf = T.surface.Surface(T.flat_surface.FlatGeometryManager(), oc.RefractiveHomogenousReceiver(1., 1.5))
+    # accountants need one child per hit (single_ray): with two the reference's count() raises ValueError
+    surf = T.surface.Surface(T.flat_surface.FlatGeometryManager(), oc.RefractiveHomogenousReceiver(1., 1.5, single_ray=False))
     asm = T.assembly.Assembly(objects=[T.object.AssembledObject(surfs=[surf])])
     with pytest.raises(NotImplementedError):
         _engine(asm).compile()
+
+
+def test_accountants_on_a_single_ray_refractive_surface():
+    """The reference's accountants see the child bundle as the callable returns it, [reflected][refracted]
+    (optics_callables.py:1638-1643): Location in hit order, Scatterer the children's energies in child order, Absorber
+    their difference to the hit-ordered incoming energies -- zero for a source of equal energies, a permutation
+    artefact otherwise.  (Bundle-by-bundle parity with the reference: golden c12, surface 1.)"""
+    oc = T.optics_callables
+    opt = oc.RefractiveHomogenousAbsorberScattererLocation(1., 1.5, single_ray=True)
+    surf = T.surface.Surface(T.flat_surface.RectPlateGM(4., 4.), opt)
+    asm = T.assembly.Assembly(objects=[T.object.AssembledObject(surfs=[surf])])
+    n = 5000
+    rng = np.random.RandomState(1)
+    v = np.vstack([rng.uniform(-1, 1, n), rng.uniform(-1, 1, n), np.ones(n)])
+    d = np.tile(np.c_[[0.6, 0., -0.8]], (1, n))
+    e = rng.uniform(0.5, 1.5, n)
+    bund = T.ray_bundle.RayBundle(vertices=v, directions=d, energy=e, ref_index=np.ones(n))
+    eng = _engine(asm, rng='philox', seed=3)
+    eng.ray_tracer(bund, reps=1, min_energy=0., tree=True)
+    child = eng.tree[1]
+    absorbed, scattered, hits = opt.get_all_hits()
+    assert child.get_num_rays() == n and hits.shape == (3, n)
+    close(hits[:2], v[:2] + 0.75 * np.r_[1., 0.][:, None], 1e-12, 'hit points in hit order')
+    close(scattered, child.get_energy(), 0., 'Scatterer = child energies in child order')
+    close(absorbed, e - child.get_energy(), 1e-15, 'Absorber = hit-ordered e_in - child-ordered e_out')
+    par = child.get_parents()
+    assert not np.array_equal(par, np.arange(n))          # reflected rays first: the child order is not the hit order
+    close(child.get_energy(), e[par], 0., 'single_ray children keep their parent energy')
 
 
 def test_tabulated_media_snell_fresnel_and_k_attenuation():

@@ -392,7 +392,8 @@ def c12_refractive_materials(T, n_rays=2000):
         return T.object.AssembledObject(surfs=[T.surface.Surface(T.flat_surface.RectPlateGM(w, h), opt)], transform=tr)
     objs = [
         plate(oc.Refractive(air, glass, single_ray=False), 1.0),
-        plate(oc.Refractive(air, glass, single_ray=True, sigma=3e-3), 0.7, flip=True),
+        plate(oc.RefractiveDetector(air, glass, single_ray=True, sigma=3e-3), 0.7, flip=True),     # accountants see the
+                                                                         # [reflected][refracted] child bundle as it is
         plate(oc.RefractiveAbsorbant(air, glass, single_ray=False, attenuation_coefficient_1=1., scaling=2.), 0.4),
         plate(oc.RefractiveAbsorbant(air, glass, single_ray=True, attenuation_coefficient_2=1.), 0.1, flip=True),
         plate(oc.LambertianReceiver(0.6), -0.3, w=8., h=8.),

@@ -225,6 +225,22 @@ def _material_table(material):
     return wl[order], np.concatenate([np.asarray(n, float)[order], np.asarray(k, float)[order]])
 
 
+def _check_refractive_accountants(base, accountants):
+    """Accountants on a refractive surface.  Accountant.count works on the child bundle as the callable returns it,
+    [reflected][refracted]: in ``single_ray`` mode it has one ray per hit and the reference subtracts it, in that order,
+    from the hit-ordered incoming energies (optics_callables.py:1638-1643) -- reproduced as it is; when every hit
+    emits two children the shapes differ and the reference raises ValueError."""
+    if not accountants:
+        return
+    if not base._single_ray:
+        raise NotImplementedError(
+            "refractive optics with accountants and single_ray=False: the reference raises ValueError there "
+            "(Accountant.count subtracts a child bundle of another length, optics_callables.py:1638-1643)")
+    for _, _, src in accountants:
+        if src not in ('absorbed', 'e_in', 'e_out', 'hits', 'dirs_in'):
+            raise NotImplementedError(f"accountant column {src!r} on a refractive surface")
+
+
 def _optics_record(opt):
     """-> dict(okind, op, flags, table, accountants, draws); a BiFacial manager gives its front side's record
     with the back side's under 'back'."""
@@ -316,8 +332,7 @@ def _optics_record(opt):
             rec['needs_wavelengths'] = True
         elif name in ('RefractiveAbsorbant', 'Refractive') and not hasattr(base, '_ref_idxs'):
             # media given by material tables, complex indices (:726-858, :908-944)
-            if accountants:
-                raise NotImplementedError("refractive optics with accountants (see RefractiveHomogenous)")
+            _check_refractive_accountants(base, accountants)
             rec['okind'] = L.O_REFRACTIVE
             rec['flags'] |= L.F_TABULATED
             sigma = base._sigma
@@ -340,11 +355,7 @@ def _optics_record(opt):
                 rec['op'][4] = 1.0
                 rec['op'][7] = _scalar(base._scaling, 'scaling')
         elif name in ('RefractiveTransmissiveHomogenous', 'RefractiveHomogenous'):
-            if accountants:
-                raise NotImplementedError(
-                    "refractive optics with accountants: Accountant.count compares the incoming rays with a "
-                    "child bundle in [reflected][refracted] order (and of another length when rays split); "
-                    "not reproduced")
+            _check_refractive_accountants(base, accountants)
             n_a, n_b = base._ref_idxs
             if np.iscomplexobj(np.asarray([n_a, n_b])):
                 raise NotImplementedError("refractive optics: complex refractive indices (attenuation from the "

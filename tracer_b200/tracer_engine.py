@@ -491,6 +491,8 @@ class TracerEngine(object):
             child_off = torch.from_numpy(child_off_host).to(dev)
 
         want = set(scene.accountant_sources)
+        if scene.has_refractive and scene.has_accountants:
+            want.add('e_in')                             # accountants of refractive surfaces re-derive their columns
         poly = cur.SP is not None
         if poly:
             want.update(('normals', 'dirs_in'))          # trc_spectra reads the incidence angle from them
@@ -619,7 +621,7 @@ class TracerEngine(object):
             def columns(o):
                 return dict(hits=o['V'], absorbed=o['absorbed'], e_out=o['E'], normals=o['normals'], e_in=o['e_in'],
                             dirs_in=o['dirs_in'], wavelengths=o['W'], attenuated=o['attenuated'],
-                            lost_spectra=o['lost_spectra'])
+                            lost_spectra=o['lost_spectra'], cull=o['cull'])
             if scene.has_bifacial:
                 self._account(scene, seg_host, columns(src_front), child_off_host, back=(columns(src_back), back_counts))
             else:
@@ -886,6 +888,24 @@ class TracerEngine(object):
                 n_back = int(back[1][s])
                 feeds = ([(orec['back']['accountants'], back[0])] if n_back > 0 else []) + \
                         ([(orec['accountants'], src)] if n_back < b - a else [])
+            if orec['okind'] == L.O_REFRACTIVE:
+                # single_ray refraction (one child per hit): the child bundle as the callable returns it is
+                # [reflected in hit order][refracted in hit order]; count() subtracts it AS IS from the hit-ordered
+                # incoming energies (optics_callables.py:1638-1643)
+                lo, h = int(child_off[s]), b - a
+                blk = src['e_out'][lo:lo + 2 * h]
+                e_child = blk[src['cull'][lo:lo + 2 * h] != 2]
+                for acc, field, name in orec['accountants']:
+                    if name == 'absorbed':
+                        t = src['e_in'][a:b] - e_child
+                    elif name == 'e_out':
+                        t = e_child
+                    elif name == 'hits':
+                        t = src['hits'][:, lo:lo + h]
+                    else:                                   # e_in, dirs_in: slot order
+                        t = src[name][..., a:b]
+                    getattr(acc, field).append(_LazyRows(t.clone()))
+                continue
             for accs, cols in feeds:
                 for acc, field, name in accs:
                     t = cols[name]
