@@ -309,10 +309,22 @@ def test_refractive_records():
     assert list(r['op'][2]) == [1., 1.45, 1., -1., 2., 0.05, 2.5, 10.]
     assert list(sc.children_per_hit) == [2, 2, 2, 1] and sc.has_split and sc.has_refractive
     assert not scene(oc.Reflective(0.1)).has_refractive
-    with pytest.raises(NotImplementedError):
-        scene(oc.RefractiveHomogenousReceiver(1., 1.5))
+    assert scene(oc.RefractiveHomogenousReceiver(1., 1.5)).has_accountants       # one child per hit: count() is defined
+    with pytest.raises(NotImplementedError):                                     # two: the reference raises ValueError
+        scene(oc.RefractiveHomogenousReceiver(1., 1.5, single_ray=False))
     with pytest.raises(NotImplementedError):
         scene(oc.RefractiveHomogenous(1., 1.5 + 0.1j))
+    # media given by material tables: knots of both materials in the pool, flag TRC_F_TABULATED
+    ocn = T.optical_constants
+    glass = ocn.OpticalMaterialTable([3e-7, 1e-6, 2.5e-6], [1.55, 1.52, 1.5], [1e-8, 2e-8, 4e-8])
+    tab = scene(oc.RefractiveAbsorbant(ocn.Air(), glass, single_ray=False, attenuation_coefficient_1=1., scaling=2.))
+    r0 = tab.records[0]
+    assert r0['okind'] == L.O_REFRACTIVE and r0['flags'] & L.F_TABULATED and tab.has_tabulated
+    assert r0['table_len'] == 2 and int(r0['op'][1]) == 3 and r0['op'][4] == 1. and r0['op'][7] == 2.
+    off_b = int(r0['op'][0])
+    assert list(tab.tables[off_b:off_b + 9]) == [3e-7, 1e-6, 2.5e-6, 1.55, 1.52, 1.5, 1e-8, 2e-8, 4e-8]
+    with pytest.raises(NotImplementedError):                                     # the reference raises AttributeError
+        scene(oc.RefractiveAbsorbant(ocn.Air(), glass))
     with pytest.raises(NotImplementedError):
         scene(oc.RefractiveTransmissiveHomogenous(1., 1.5, None))
 
