@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TRC_ABI_VERSION 14
+#define TRC_ABI_VERSION 15
 
 typedef enum TrcStatus {
     TRC_OK = 0,
@@ -221,6 +221,11 @@ int trc_scene_set_bvh(TrcScene *scene, const TrcBvhNode *nodes, int32_t n_nodes,
  * use_bvh == 2 is then an ordinary walk.  A NULL direction or negative half_angle removes the grid.  Host-built;
  * synchronises the device (call it between traces). */
 int trc_scene_set_shadow_grid(TrcScene *scene, int32_t n_boxes, const double *box_lo, const double *box_hi,
+                              const double *quads /* nullable: n_boxes x 4 corners x 3, global coordinates, of the
+                                                     surfaces that lie inside a planar quadrilateral (plates,
+                                                     triangles: last corner repeated); NaN in the first entry = none.
+                                                     Their shadow is then the hull of the corners' shadows instead of
+                                                     the box's, which halves the candidates of a tilted plate */,
                               const int32_t *surface_ids, const double *direction, double half_angle,
                               int32_t *enabled);
 int trc_scene_destroy(TrcScene *scene);
@@ -602,6 +607,14 @@ int trc_segment_sums(int64_t h, const int32_t *d_sorted_keys, const double *d_va
  * pipe of the current device in TFLOP/s (2 flop per FMA) -- the roofline denominator SURVEY.md 8(d) asks the
  * builder to measure for the brute-force nearest-hit kernel.  Synchronous. */
 int trc_fma_peak(int32_t fp64, double *tflops);
+/* Instrumentation (no counterpart in the reference): time, in ms, to stream n rays of a bundle (vertices and
+ * directions, six float64 rows of stride ld) through persistent warps that own chunks of 256 rays, as the shadow-grid
+ * kernel reads them.  variant 1, 2, 4: that many 32-ray groups in flight per warp by register prefetch (16 warps per
+ * SM), chunk ids from one atomic counter; 11, 12, 14: the same with the chunks dealt round robin; 108: one
+ * cp.async.bulk per row and chunk into a two-chunk shared-memory ring, 8 warps per SM.  Allocates a few bytes,
+ * synchronises; scripts/stream_probe.py. */
+int trc_stream_probe(int32_t variant, const double *d_vertices, const double *d_directions, int64_t ld, int64_t n,
+                     float *ms_out);
 
 #ifdef __cplusplus
 }

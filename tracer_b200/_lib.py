@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libtracer_b200.so")
 
-ABI_VERSION = 14
+ABI_VERSION = 15
 
 # enum TrcGeomKind
 (G_FLAT_INFINITE, G_RECT_PLATE, G_RECT_EXTRUDED, G_ROUND_PLATE, G_TRIANGLE, G_PARABOLOID,
@@ -142,8 +142,9 @@ SIGNATURES = {
     "trc_scene_update_frames": (C.c_int, [_P, _P, _P, _I32]),
     "trc_bvh_build": (C.c_int, [_P, _P, _I32, _I32, _P, _I32, C.POINTER(_I32), _P]),
     "trc_scene_set_bvh": (C.c_int, [_P, _P, _I32, _P, _I32, _P, _I32]),
-    "trc_scene_set_shadow_grid": (C.c_int, [_P, _I32, _P, _P, _P, _P, C.c_double, C.POINTER(_I32)]),
+    "trc_scene_set_shadow_grid": (C.c_int, [_P, _I32, _P, _P, _P, _P, _P, C.c_double, C.POINTER(_I32)]),
     "trc_spectra": (C.c_int, [_P, _P, _P]),
+    "trc_stream_probe": (C.c_int, [_I32, _P, _P, _I64, _I64, C.POINTER(C.c_float)]),
     "trc_scene_destroy": (C.c_int, [_P]),
     "trc_scene_num_surfaces": (_I32, [_P]),
     "trc_nearest_hit": (C.c_int, [_P, _I64, _P, _P, _I64, _I32, _P, _P]),

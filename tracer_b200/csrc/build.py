@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.dirname(HERE)
 LIB = os.path.join(PKG, "libtracer_b200.so")
 OBJ_DIR = os.path.join(HERE, "build")
-SOURCES = ["tracer_b200.cu", "nearest.cu", "bvh_build.cu", "sort.cu", "bounce.cu", "sources.cu", "trace.cu", "shadow_grid.cu"]
+SOURCES = ["tracer_b200.cu", "nearest.cu", "bvh_build.cu", "sort.cu", "bounce.cu", "sources.cu", "trace.cu", "shadow_grid.cu", "probe.cu"]
 HEADERS = ["common.cuh", "geom.cuh", "optics.cuh", "philox.cuh",
            os.path.join("..", "..", "include", "tracer_b200.h")]
 NVCC_FLAGS = [

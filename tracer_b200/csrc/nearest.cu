@@ -1011,6 +1011,12 @@ nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
     // the first group of the NEXT chunk is requested before a chunk's float64 stage and record emission, which hide
     // its latency
     GridRay cur = load_ray((long long)c_next * kChunk + lane, (long long)c_next * kChunk + lane < n_rays);
+#ifndef TRC_GRID_DEPTH
+#define TRC_GRID_DEPTH 1
+#endif
+#if TRC_GRID_DEPTH == 2
+    GridRay nx1 = load_ray((long long)c_next * kChunk + 32 + lane, (long long)c_next * kChunk + 32 + lane < n_rays);
+#endif
     for (;;) {
         const unsigned long long c = c_next;
         const int64_t chunk_base = (int64_t)c * kChunk;
@@ -1046,9 +1052,16 @@ nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
                 if (qn + want > kGridQueue - 32) { need_flush = true; break; }
                 const int j = next + lane;
                 const bool valid = j < chunk_n;
+#if TRC_GRID_DEPTH == 2
+                const GridRay nx2 = load_ray(chunk_base + j + 64, j + 64 < chunk_n);     // two groups ahead
+#else
                 const GridRay nxt = load_ray(chunk_base + j + 32, j + 32 < chunk_n);
+#endif
                 unsigned ent = 0u;
                 bool out = false;
+                if (p.debug & 4) {      // experiment (TRC_WALK_DEBUG=4): stream the rays, do nothing with them
+                    if (valid && cur.vn + cur.va + cur.vb + cur.dn + cur.da + cur.db == 1.2345e300) ent = 1u;
+                } else
                 if (valid) {
                     const float vn = (float)cur.vn, va = (float)cur.va, vb = (float)cur.vb;
                     const float dn = (float)cur.dn, da = (float)cur.da, db = (float)cur.db;
@@ -1091,13 +1104,20 @@ nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
                     }
                 }
                 ent_prev = ent;
+#if TRC_GRID_DEPTH == 2
+                cur = nx1; nx1 = nx2;
+#else
                 cur = nxt;
+#endif
             }
             if (!need_flush) break;
             qn = grid_flush<kFlatOnly>(sh, p, chunk_base, lane, qn, false);     // whole batches of 32; the rest stays queued
         }
         c_next = __shfl_sync(full, c_next, 0);
         cur = load_ray((long long)c_next * kChunk + lane, (long long)c_next * kChunk + lane < n_rays);
+#if TRC_GRID_DEPTH == 2
+        nx1 = load_ray((long long)c_next * kChunk + 32 + lane, (long long)c_next * kChunk + 32 + lane < n_rays);
+#endif
         if (dirty) {
             // leave the whole chunk to the tree walk (its kernel follows on the stream and writes the chunk's tables)
             if (lane == 0) p.dirty_list[atomicAdd(p.dirty_count, 1ULL)] = (uint32_t)c;

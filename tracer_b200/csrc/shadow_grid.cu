@@ -83,6 +83,35 @@ Rect shadow(const AxisChoice &c, const double *lo, const double *hi, double pad_
     return r;
 }
 
+struct P2 { double x, y; };
+
+// convex hull (counter-clockwise, monotone chain) of n points; returns the number of hull points written to `out`
+int convex_hull(P2 *pts, int n, P2 *out) {
+    std::sort(pts, pts + n, [](const P2 &a, const P2 &b) { return a.x < b.x || (a.x == b.x && a.y < b.y); });
+    auto cross = [](const P2 &o, const P2 &a, const P2 &b) { return (a.x - o.x) * (b.y - o.y) - (a.y - o.y) * (b.x - o.x); };
+    int k = 0;
+    for (int i = 0; i < n; ++i) { while (k >= 2 && cross(out[k - 2], out[k - 1], pts[i]) <= 0) --k; out[k++] = pts[i]; }
+    for (int i = n - 2, t = k + 1; i >= 0; --i) { while (k >= t && cross(out[k - 2], out[k - 1], pts[i]) <= 0) --k; out[k++] = pts[i]; }
+    return k > 1 ? k - 1 : k;
+}
+
+// Shadow of a planar quad (4 corners, global coordinates): the hull of every corner's key under the four corners of
+// the slope box -- the key is affine in the point for a fixed slope and affine in the slope for a fixed point, so the
+// keys of all (point of the quad, slope of the box) pairs lie in the hull of these 16.
+int quad_shadow(const AxisChoice &c, const double *quad, double pad_slope, P2 *hull) {
+    P2 pts[16];
+    int n = 0;
+    const double ta[2] = {c.t0a - c.da - pad_slope, c.t0a + c.da + pad_slope};
+    const double tb[2] = {c.t0b - c.db - pad_slope, c.t0b + c.db + pad_slope};
+    for (int k = 0; k < 4; ++k) {
+        const double *p = quad + 3 * k;
+        const double h = p[c.n] - c.h0;
+        for (int i = 0; i < 2; ++i)
+            for (int j = 0; j < 2; ++j) { pts[n].x = p[c.a] - h * ta[i]; pts[n].y = p[c.b] - h * tb[j]; ++n; }
+    }
+    return convex_hull(pts, n, hull);
+}
+
 void free_grid(TrcScene *sc) {
     cudaFree(sc->d_grid_bits); cudaFree(sc->d_grid_cells); cudaFree(sc->d_grid_list);
     sc->d_grid_bits = sc->d_grid_cells = nullptr;
@@ -97,8 +126,8 @@ void free_grid(TrcScene *sc) {
 void trc_scene_free_shadow_grid(TrcScene *sc) { free_grid(sc); }
 
 extern "C" int trc_scene_set_shadow_grid(TrcScene *sc, int32_t n_boxes, const double *box_lo, const double *box_hi,
-                                         const int32_t *surface_ids, const double *direction, double half_angle,
-                                         int32_t *enabled) {
+                                         const double *quads, const int32_t *surface_ids, const double *direction,
+                                         double half_angle, int32_t *enabled) {
     if (!sc || n_boxes < 0 || (n_boxes > 0 && (!box_lo || !box_hi || !surface_ids)) || !enabled)
         return fail(TRC_ERR_BAD_ARGUMENT, "trc_scene_set_shadow_grid: bad argument%s");
     *enabled = 0;
@@ -166,18 +195,49 @@ extern "C" int trc_scene_set_shadow_grid(TrcScene *sc, int32_t n_boxes, const do
     const double cell_pad = 2e-3 * cell;                            // rounding of (key - origin) / cell in float32
     const int64_t n_cells = (int64_t)nx * ny;
     std::vector<uint32_t> count(n_cells, 0u);
-    auto range = [&](double x0, double x1, double g0, int nmax, int &i0, int &i1) {
-        i0 = (int)std::floor((x0 - cell_pad - g0) / cell); i1 = (int)std::floor((x1 + cell_pad - g0) / cell);
-        i0 = std::max(i0, 0); i1 = std::min(i1, nmax - 1);
+    const double m = key_err + cell_pad;                            // outward margin of a hull shadow
+    // Cells of surface i's shadow: the rectangle of its box, or -- a planar surface whose corners are known -- the hull
+    // of its corners' keys, rasterised row by row (the x extent of the hull over the widened row band).
+    auto for_each_cell = [&](int i, auto &&fn) {
+        const double *quad = quads ? quads + 12 * (size_t)i : nullptr;
+        if (!quad || !std::isfinite(quad[0])) {
+            int a0 = (int)std::floor((rects[i].a0 - cell_pad - ga0) / cell), a1 = (int)std::floor((rects[i].a1 + cell_pad - ga0) / cell);
+            int b0 = (int)std::floor((rects[i].b0 - cell_pad - gb0) / cell), b1 = (int)std::floor((rects[i].b1 + cell_pad - gb0) / cell);
+            a0 = std::max(a0, 0); a1 = std::min(a1, nx - 1); b0 = std::max(b0, 0); b1 = std::min(b1, ny - 1);
+            for (int b = b0; b <= b1; ++b)
+                for (int a = a0; a <= a1; ++a) fn((int64_t)b * nx + a);
+            return;
+        }
+        P2 hull[17];
+        const int nh = quad_shadow(c, quad, pad_slope, hull);
+        double ylo = 1e300, yhi = -1e300;
+        for (int k = 0; k < nh; ++k) { ylo = std::min(ylo, hull[k].y); yhi = std::max(yhi, hull[k].y); }
+        int b0 = std::max(0, (int)std::floor((ylo - m - gb0) / cell)), b1 = std::min(ny - 1, (int)std::floor((yhi + m - gb0) / cell));
+        for (int b = b0; b <= b1; ++b) {
+            const double ya = gb0 + b * cell - m, yb = gb0 + (b + 1) * cell + m;
+            double xlo = 1e300, xhi = -1e300;
+            for (int k = 0; k < nh; ++k) {
+                const P2 p = hull[k], q = hull[(k + 1) % nh];
+                // the part of edge p-q inside the band ya <= y <= yb
+                double t0 = 0.0, t1 = 1.0;
+                const double dy = q.y - p.y;
+                if (dy == 0.0) { if (p.y < ya || p.y > yb) continue; }
+                else {
+                    double ta_ = (ya - p.y) / dy, tb_ = (yb - p.y) / dy;
+                    if (ta_ > tb_) std::swap(ta_, tb_);
+                    t0 = std::max(t0, ta_); t1 = std::min(t1, tb_);
+                    if (t0 > t1) continue;
+                }
+                const double x0 = p.x + t0 * (q.x - p.x), x1 = p.x + t1 * (q.x - p.x);
+                xlo = std::min(xlo, std::min(x0, x1)); xhi = std::max(xhi, std::max(x0, x1));
+            }
+            if (xlo > xhi) continue;
+            int a0 = std::max(0, (int)std::floor((xlo - m - ga0) / cell)), a1 = std::min(nx - 1, (int)std::floor((xhi + m - ga0) / cell));
+            for (int a = a0; a <= a1; ++a) fn((int64_t)b * nx + a);
+        }
     };
     int64_t total = 0;
-    for (int i = 0; i < n_boxes; ++i) {
-        int a0, a1, b0, b1;
-        range(rects[i].a0, rects[i].a1, ga0, nx, a0, a1);
-        range(rects[i].b0, rects[i].b1, gb0, ny, b0, b1);
-        for (int b = b0; b <= b1; ++b)
-            for (int a = a0; a <= a1; ++a) { ++count[(int64_t)b * nx + a]; ++total; }
-    }
+    for (int i = 0; i < n_boxes; ++i) for_each_cell(i, [&](int64_t k) { ++count[k]; ++total; });
     if (total >= (1 << 24)) return TRC_OK;                          // list offsets are 24 bits
     std::vector<uint32_t> cells(n_cells, 0u), bits((n_cells + 31) / 32, 0u);
     std::vector<uint32_t> first(n_cells, 0u);
@@ -189,20 +249,14 @@ extern "C" int trc_scene_set_shadow_grid(TrcScene *sc, int32_t n_boxes, const do
     }
     std::vector<int32_t> list(std::max<uint32_t>(run, 1u), 0);
     std::vector<uint32_t> fill(n_cells, 0u);
-    for (int i = 0; i < n_boxes; ++i) {
-        int a0, a1, b0, b1;
-        range(rects[i].a0, rects[i].a1, ga0, nx, a0, a1);
-        range(rects[i].b0, rects[i].b1, gb0, ny, b0, b1);
-        for (int b = b0; b <= b1; ++b)
-            for (int a = a0; a <= a1; ++a) {
-                const int64_t k = (int64_t)b * nx + a;
-                if (count[k] == 1u) cells[k] = ((uint32_t)surface_ids[i] << 8) | 1u;
-                else {
-                    list[first[k] + fill[k]++] = surface_ids[i];
-                    cells[k] = (first[k] << 8) | count[k];
-                }
+    for (int i = 0; i < n_boxes; ++i)
+        for_each_cell(i, [&](int64_t k) {
+            if (count[k] == 1u) cells[k] = ((uint32_t)surface_ids[i] << 8) | 1u;
+            else {
+                list[first[k] + fill[k]++] = surface_ids[i];
+                cells[k] = (first[k] << 8) | count[k];
             }
-    }
+        });
     TRC_CUDA(cudaMalloc(&sc->d_grid_bits, bits.size() * sizeof(uint32_t)));
     TRC_CUDA(cudaMalloc(&sc->d_grid_cells, cells.size() * sizeof(uint32_t)));
     TRC_CUDA(cudaMalloc(&sc->d_grid_list, list.size() * sizeof(int32_t)));

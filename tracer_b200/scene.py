@@ -690,15 +690,17 @@ class CompiledScene(object):
         lib = L.load()
         on = C.c_int32(0)
         if key is None or len(self.bounded) == 0 or len(self.bounded) > self.GRID_MAX_SURFACES:
-            L.check(lib.trc_scene_set_shadow_grid(self.handle, 0, None, None, None, None, -1., C.byref(on)))
+            L.check(lib.trc_scene_set_shadow_grid(self.handle, 0, None, None, None, None, None, -1., C.byref(on)))
         else:
             lo = np.ascontiguousarray(self.aabb_lo[self.bounded], dtype=np.float64)
             hi = np.ascontiguousarray(self.aabb_hi[self.bounded], dtype=np.float64)
+            quads = np.ascontiguousarray(self.planar_quads()[self.bounded], dtype=np.float64)
             ids = np.ascontiguousarray(self.bounded, dtype=np.int32)
             d = np.ascontiguousarray(direction, dtype=np.float64)
             L.check(lib.trc_scene_set_shadow_grid(
                 self.handle, len(ids), lo.ctypes.data_as(C.c_void_p), hi.ctypes.data_as(C.c_void_p),
-                ids.ctypes.data_as(C.c_void_p), d.ctypes.data_as(C.c_void_p), float(half_angle), C.byref(on)))
+                quads.ctypes.data_as(C.c_void_p), ids.ctypes.data_as(C.c_void_p), d.ctypes.data_as(C.c_void_p),
+                float(half_angle), C.byref(on)))
         self._grid_key, self._grid_on = key, bool(on.value)
         return self._grid_on
 
@@ -711,6 +713,32 @@ class CompiledScene(object):
             cached = (torch.from_numpy(up).to(device), torch.from_numpy(self.bifacial_mask.copy()).to(device))
             self._bifacial_dev = cached
         return cached
+
+    def planar_quads(self):
+        """(S, 4, 3) corners, global coordinates, of the quadrilateral every flat plate / triangle lies in (NaN rows for
+        the other kinds): their shadow in the shadow grid is the hull of the corners' shadows, not the box's."""
+        r = self.records
+        S = len(r)
+        out = np.full((S, 4, 3), np.nan)
+        frame = r['frame'].reshape(S, 3, 4)
+        gp = r['gp']
+        kind = r['gkind']
+        local = np.zeros((S, 4, 3))
+        rect = np.isin(kind, (L.G_RECT_PLATE, L.G_RECT_EXTRUDED, L.G_RECT_PERFORATED))
+        sx, sy = np.array([-1., 1., 1., -1.]), np.array([-1., -1., 1., 1.])
+        local[rect, :, 0] = gp[rect, 0:1] * sx
+        local[rect, :, 1] = gp[rect, 1:2] * sy
+        rnd = kind == L.G_ROUND_PLATE
+        local[rnd, :, 0] = gp[rnd, 0:1] * sx
+        local[rnd, :, 1] = gp[rnd, 0:1] * sy
+        tri = kind == L.G_TRIANGLE
+        # TriangularFace: p = p0 + u e0 + v e1 with e = R * verts (gp[0:3] = verts[:, 0], gp[3:6] = verts[:, 1])
+        local[tri, 1, :] = gp[tri, 0:3]
+        local[tri, 2, :] = gp[tri, 3:6]
+        local[tri, 3, :] = gp[tri, 3:6]
+        sel = rect | rnd | tri
+        out[sel] = np.einsum('sij,skj->ski', frame[sel][:, :, :3], local[sel]) + frame[sel][:, None, :, 3]
+        return out
 
     def seg_entries_needed(self, device):
         """(host list, device index tensor) of the slot-offset entries the engine reads on the host after a
