@@ -180,7 +180,10 @@ constexpr int kListFields = 10;               // A[3], Bn[3], Bf[3], slot | dire
 #ifndef TRC_WALK_SMEM_PAIRS
 #define TRC_WALK_SMEM_PAIRS 512
 #endif
-constexpr int kGridQueue = 512;               // candidate queue of the shadow-grid kernel (entries per warp)
+#ifndef TRC_GRID_QUEUE
+#define TRC_GRID_QUEUE 512
+#endif
+constexpr int kGridQueue = TRC_GRID_QUEUE;               // candidate queue of the shadow-grid kernel (entries per warp)
 constexpr int kGridMaxWords = 6144;           // occupancy bits of a shadow grid in shared memory: at most 24 KB
 constexpr int kSmemPairs = TRC_WALK_SMEM_PAIRS;               // top of the tree (breadth-first) cached per CTA: 16 KB
 // queue entry = slot << 24 | (count - 1) << 22 | first candidate-list index: one entry per leaf
@@ -217,7 +220,13 @@ struct WalkShared {
 
 // Per-warp shared memory of the shadow-grid kernel (nearest_hit_grid_kernel): the per-slot best (t, surface) of a
 // chunk and the candidate queues; same member names as WalkWarpShared where the float64 stage reads them.
+#ifndef TRC_GRID_AHEAD
+#define TRC_GRID_AHEAD 1
+#endif
+constexpr int kGridAhead = TRC_GRID_AHEAD;    // groups of 32 rays a warp has in flight ahead of the one it keys
+constexpr int kGridRing = kGridAhead + 1;
 struct GridWarpShared {
+    double ring[kGridRing][6][32];            // ray groups arriving by cp.async: rows (vn, va, vb, dn, da, db) x lane
     unsigned long long best_t[kChunk];
     int best_s[kChunk];
     unsigned queue[kGridQueue];               // packed (slot, surface); lends its storage to the hit-slot list
@@ -432,6 +441,9 @@ __device__ __forceinline__ int flush_queue_body(Sh &sh, const unsigned *queue, c
         unsigned long long tb = (unsigned long long)__double_as_longlong(t);
         bool cand = has && tb < TRC_INF_BITS;
         unsigned long long before = cand ? sh.best_t[slot] : 0ULL;
+        // a slot's first hit: its energy will be wanted by the record emission, and only hits read that row
+        if (cand && before == TRC_INF_BITS && p.sink.records)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(sh.energy + chunk_base + slot));
         __syncwarp();
         if (cand) atomicMin(&sh.best_t[slot], tb);
         __syncwarp();
@@ -563,25 +575,41 @@ __device__ __forceinline__ void emit_chunk_hits(Sh &sh, const WalkParams &p, int
         if (hit) slots[h_c + __popc(m & lt_mask)] = (unsigned char)i;
         h_c += __popc(m);
     }
+    __syncwarp();
+    // the first 32 hits' rays are requested BEFORE the reservation of record space: the atomic's round trip and the
+    // loads (the energy comes from DRAM: it is read for hits only) then overlap instead of adding up, once per chunk
+    const long long ld = sh.ld;
+    V3 v = mk(0.0, 0.0, 0.0), d = v;
+    double en = 0.0;
+    int i = 0;
+    if (lane < h_c) {
+        i = slots[lane];
+        const int64_t ray = chunk_base + i;
+        const double *vp = sh.vert + ray, *dp = sh.dir + ray;
+        v = mk(vp[0], vp[ld], vp[2 * ld]);
+        d = mk(dp[0], dp[ld], dp[2 * ld]);
+        en = sh.energy[ray];
+    }
     unsigned long long base = 0;
     if (lane == 0) {
-        base = atomicAdd(p.sink.total, (unsigned long long)h_c);
+        if (h_c) base = atomicAdd(p.sink.total, (unsigned long long)h_c);    // one address: not for nothing
         p.sink.chunk_off[c_cur] = (uint32_t)base;
         p.sink.chunk_cnt[c_cur] = (uint32_t)h_c;
     }
     base = __shfl_sync(full, base, 0);
-    __syncwarp();
     for (int e = lane; e < h_c; e += 32) {
         unsigned long long pos = base + e;
         if ((int64_t)pos >= p.sink.capacity) break;       // overflow: the host re-runs with the exact size
-        int i = slots[e];
-        int64_t ray = chunk_base + i;
-        const double *vp = sh.vert + ray, *dp = sh.dir + ray;
-        const long long ld = sh.ld;
-        V3 v = mk(vp[0], vp[ld], vp[2 * ld]);
-        V3 d = mk(dp[0], dp[ld], dp[2 * ld]);
+        if (e >= 32) {
+            i = slots[e];
+            const int64_t ray = chunk_base + i;
+            const double *vp = sh.vert + ray, *dp = sh.dir + ray;
+            v = mk(vp[0], vp[ld], vp[2 * ld]);
+            d = mk(dp[0], dp[ld], dp[2 * ld]);
+            en = sh.energy[ray];
+        }
         const int surf = sh.best_s[i];
-        store_record(p.sink.records + pos, v, d, sh.energy[ray], p.sink.ray_base + (int)ray, surf);
+        store_record(p.sink.records + pos, v, d, en, p.sink.ray_base + (int)(chunk_base + i), surf);
         if (p.sink.keys) p.sink.keys[pos] = surf;
     }
     __syncwarp();
@@ -948,10 +976,10 @@ nearest_hit_walk_kernel(WalkParams p) {
 // left untouched and listed for the tree-walk kernel, which is launched right after over that list -- so a wrong
 // or partial hint costs time, never correctness.
 #ifndef TRC_GRID_MIN_CTAS
-#define TRC_GRID_MIN_CTAS 2
+#define TRC_GRID_MIN_CTAS 1
 #endif
 #ifndef TRC_GRID_WARPS
-#define TRC_GRID_WARPS 8
+#define TRC_GRID_WARPS 16
 #endif
 constexpr int kGridWarps = TRC_GRID_WARPS;    // warps per CTA of the shadow-grid kernel
 struct GridShared {
@@ -959,6 +987,9 @@ struct GridShared {
     long long n_rays;
     long long pad_;
 };
+
+static_assert(sizeof(GridShared) + 4 * kGridMaxWords <= (TRC_GRID_MIN_CTAS == 1 ? 232448 : 232448 / TRC_GRID_MIN_CTAS - 1024),
+              "shadow-grid kernel: per-warp state + occupancy bits exceed the shared memory of its CTAs per SM");
 
 // the float64 stage as ONE out-of-line call site: the key / lookup loop below stays small and keeps its registers
 template <int kFlatOnly>
@@ -1000,33 +1031,37 @@ nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
     // the six rows in the grid's axis order (normal, a, b)
     const double *vn_p = sh.vert + p.g.axis_n * sh.ld, *va_p = sh.vert + p.g.axis_a * sh.ld, *vb_p = sh.vert + p.g.axis_b * sh.ld;
     const double *dn_p = sh.dir + p.g.axis_n * sh.ld, *da_p = sh.dir + p.g.axis_a * sh.ld, *db_p = sh.dir + p.g.axis_b * sh.ld;
-    auto load_ray = [&](int64_t ray, bool ok) {
-        GridRay r = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-        if (ok) { r.vn = vn_p[ray]; r.va = va_p[ray]; r.vb = vb_p[ray]; r.dn = dn_p[ray]; r.da = da_p[ray]; r.db = db_p[ray]; }
-        return r;
+    // Chunks are dealt round robin (warp w of the grid takes chunks w, w + W, ...), so a warp's rays form one known
+    // sequence of groups of 32; the groups arrive in a shared-memory ring by cp.async, kGridAhead of them in flight
+    // per warp ahead of the one being keyed -- across the float64 stage, the record emission and chunk boundaries.
+    // (Registers cannot hold that much: one group in flight per warp streams at half the HBM rate at 16 warps per SM.)
+    const unsigned long long c_stride = (unsigned long long)gridDim.x * kGridWarps;
+    unsigned long long c_next = (unsigned long long)blockIdx.x * kGridWarps + (threadIdx.x >> 5);
+    unsigned long long c_iss = c_next;        // chunk, group and ring slot of the next group to request
+    int g_iss = 0, slot_iss = 0, slot_con = 0;
+    auto issue = [&]() {
+        const long long ray = (long long)c_iss * kChunk + 32 * g_iss + lane;
+        if (ray < n_rays) {
+            double (*dst)[32] = sh.ring[slot_iss];
+            cp_async8(&dst[0][lane], vn_p + ray); cp_async8(&dst[1][lane], va_p + ray); cp_async8(&dst[2][lane], vb_p + ray);
+            cp_async8(&dst[3][lane], dn_p + ray); cp_async8(&dst[4][lane], da_p + ray); cp_async8(&dst[5][lane], db_p + ray);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        if (++g_iss == kChunk / 32) { g_iss = 0; c_iss += c_stride; }
+        slot_iss = slot_iss + 1 == kGridRing ? 0 : slot_iss + 1;
     };
-    unsigned long long c_next = 0;
-    if (lane == 0) c_next = atomicAdd(p.chunk_counter, 1ULL);
-    c_next = __shfl_sync(full, c_next, 0);
-    // the first group of the NEXT chunk is requested before a chunk's float64 stage and record emission, which hide
-    // its latency
-    GridRay cur = load_ray((long long)c_next * kChunk + lane, (long long)c_next * kChunk + lane < n_rays);
-#ifndef TRC_GRID_DEPTH
-#define TRC_GRID_DEPTH 1
-#endif
-#if TRC_GRID_DEPTH == 2
-    GridRay nx1 = load_ray((long long)c_next * kChunk + 32 + lane, (long long)c_next * kChunk + 32 + lane < n_rays);
-#endif
+#pragma unroll
+    for (int k = 0; k < kGridAhead; ++k) issue();
     for (;;) {
         const unsigned long long c = c_next;
         const int64_t chunk_base = (int64_t)c * kChunk;
         if (chunk_base >= n_rays) break;
         const int chunk_n = (int)min((int64_t)kChunk, (int64_t)n_rays - chunk_base);
-        if (lane == 0) c_next = atomicAdd(p.chunk_counter, 1ULL);      // the next chunk's id arrives while this one runs
+        c_next = c + c_stride;
         for (int i = lane; i < kChunk; i += 32) { sh.best_t[i] = TRC_INF_BITS; sh.best_s[i] = INT_MAX; }
         if (lane == 0) sh.q2n = 0;
         __syncwarp();
-        int qn = 0;
+        int qn = 0, done_g = 0;           // done_g: groups of this chunk taken from the ring
         bool dirty = false;
         unsigned ent_prev = 0u;            // cell entry fetched for the previous group's ray of this lane
         int next = 0;
@@ -1052,11 +1087,18 @@ nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
                 if (qn + want > kGridQueue - 32) { need_flush = true; break; }
                 const int j = next + lane;
                 const bool valid = j < chunk_n;
-#if TRC_GRID_DEPTH == 2
-                const GridRay nx2 = load_ray(chunk_base + j + 64, j + 64 < chunk_n);     // two groups ahead
-#else
-                const GridRay nxt = load_ray(chunk_base + j + 32, j + 32 < chunk_n);
-#endif
+                GridRay cur = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+                if (next < chunk_n) {
+                    issue();
+                    asm volatile("cp.async.wait_group %0;" ::"n"(kGridAhead) : "memory");
+                    if (valid) {
+                        const double (*src)[32] = sh.ring[slot_con];
+                        cur.vn = src[0][lane]; cur.va = src[1][lane]; cur.vb = src[2][lane];
+                        cur.dn = src[3][lane]; cur.da = src[4][lane]; cur.db = src[5][lane];
+                    }
+                    slot_con = slot_con + 1 == kGridRing ? 0 : slot_con + 1;
+                    ++done_g;
+                }
                 unsigned ent = 0u;
                 bool out = false;
                 if (p.debug & 4) {      // experiment (TRC_WALK_DEBUG=4): stream the rays, do nothing with them
@@ -1077,7 +1119,7 @@ nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
                     const unsigned ia = (unsigned)__float2int_rd(ca), ib = (unsigned)__float2int_rd(cb);
                     if (in_box && ia < (unsigned)p.g.nx && ib < (unsigned)p.g.ny) {
                         const unsigned cell = ib * (unsigned)p.g.nx + ia;
-                        if ((bits[cell >> 5] >> (cell & 31u)) & 1u) ent = __ldg(p.g.cells + cell);
+                        if (((bits[cell >> 5] >> (cell & 31u)) & 1u) && !(p.debug & 32)) ent = __ldg(p.g.cells + cell);
                     }
                 }
                 if (__any_sync(full, out)) { dirty = true; break; }
@@ -1104,32 +1146,27 @@ nearest_hit_grid_kernel(const __grid_constant__ WalkParams p) {
                     }
                 }
                 ent_prev = ent;
-#if TRC_GRID_DEPTH == 2
-                cur = nx1; nx1 = nx2;
-#else
-                cur = nxt;
-#endif
             }
             if (!need_flush) break;
             qn = grid_flush<kFlatOnly>(sh, p, chunk_base, lane, qn, false);     // whole batches of 32; the rest stays queued
         }
-        c_next = __shfl_sync(full, c_next, 0);
-        cur = load_ray((long long)c_next * kChunk + lane, (long long)c_next * kChunk + lane < n_rays);
-#if TRC_GRID_DEPTH == 2
-        nx1 = load_ray((long long)c_next * kChunk + 32 + lane, (long long)c_next * kChunk + 32 + lane < n_rays);
-#endif
         if (dirty) {
             // leave the whole chunk to the tree walk (its kernel follows on the stream and writes the chunk's tables)
             if (lane == 0) p.dirty_list[atomicAdd(p.dirty_count, 1ULL)] = (uint32_t)c;
+            // step over the groups of this chunk that were requested or due but not keyed
+            for (int k = done_g; k < kChunk / 32; ++k) {
+                issue();
+                slot_con = slot_con + 1 == kGridRing ? 0 : slot_con + 1;
+            }
             __syncwarp();
             continue;
         }
-        grid_flush<kFlatOnly>(sh, p, chunk_base, lane, qn, true);
+        if (!(p.debug & 16)) grid_flush<kFlatOnly>(sh, p, chunk_base, lane, qn, true);
         __syncwarp();
         if (p.sink.hit_surf)
             for (int i = lane; i < chunk_n; i += 32)
                 p.sink.hit_surf[chunk_base + i] = sh.best_t[i] == TRC_INF_BITS ? -1 : sh.best_s[i];
-        if (p.sink.records) grid_emit(sh, p, (int64_t)c, chunk_base, lane);
+        if (p.sink.records && !(p.debug & 8)) grid_emit(sh, p, (int64_t)c, chunk_base, lane);
         __syncwarp();
     }
 }
