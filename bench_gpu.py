@@ -175,27 +175,35 @@ def run_gpu(args):
         asm.reset_all_optics()
         eng.ray_tracer(bundle, reps=REPS, min_energy=1e-10, tree=True)
         bins = receiver_energy_bins(recv, FLUX_RES, device=dev)
-        absorbed, hits, bins = eng.reduce_tallies(bins)
+        # the all-reduce of the step's tallies and flux map is enqueued on the process group's stream; this rank's
+        # next trace does not wait for the slowest rank (every collective is waited for before the timed region ends)
+        pend = eng.reduce_tallies(bins, async_op=True)
         if read_back:
-            return bins.cpu().numpy(), eng.stats["ray_bounces"]
-        return bins, eng.stats["ray_bounces"]
+            return pend.result()[2].cpu().numpy(), eng.stats["ray_bounces"]
+        return pend, eng.stats["ray_bounces"]
 
     sampler = ClockSampler(local)
     sampler.start()                  # nvidia-smi needs ~1 s to start; it samples every timed region
 
     def timed(bundle, steps, warmup, read_back=False, after_warmup=None):
         for _ in range(warmup):
-            step(bundle, read_back)
+            w, _ = step(bundle, read_back)
+            if not read_back:
+                w.result()
         if after_warmup:
             after_warmup()
         barrier()
         l0 = lib.trc_launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        bounces, last = 0, None
+        bounces, last, pending = 0, None, []
         for _ in range(steps):
             last, b = step(bundle, read_back)
             bounces += b
+            if not read_back:
+                pending.append(last)
+        for pend in pending:
+            last = pend.result()[2]             # the stream waits for every step's collective: inside the timed region
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)

@@ -31,6 +31,11 @@ def _worker(rank, world, port, out):
     eng.hits_per_surface = torch.arange(S, dtype=torch.int64) + 10 * rank
     bins = torch.full((4, 4), float(rank + 1), dtype=torch.float64)
     absorbed, hits, b = eng.reduce_tallies(bins)
+    # the enqueue-only form gives the same sums when its handle is read
+    pend = eng.reduce_tallies(bins, async_op=True)
+    a2, h2, b2 = pend.result()
+    assert torch.equal(a2, absorbed) and torch.equal(h2, hits) and torch.equal(b2, b)
+    assert pend.result()[0] is a2
     out[rank] = (absorbed.numpy().copy(), hits.numpy().copy(), b.numpy().copy())
     dist.destroy_process_group()
 

@@ -76,21 +76,42 @@ class TracerEngineMP(TracerEngine):
             self.tree = merge_trees(trees)
         return out
 
-    def reduce_tallies(self, bins=None, group=None):
+    def reduce_tallies(self, bins=None, group=None, async_op=False):
         """All-reduce(sum) [absorbed per surface | hits per surface | bins] over the
         ranks; returns (absorbed (S,), hits (S,), bins or None) as tensors on the
-        device they were on.  Without an initialised process group it is a no-op."""
+        device they were on.  Without an initialised process group it is a no-op.
+        With ``async_op`` the collective is only enqueued (on the process group's own stream) and a handle is
+        returned whose ``result()`` gives the same triple: the caller's stream -- the next trace -- does not wait
+        for the slowest rank until somebody reads the sums."""
         import torch
         import torch.distributed as dist
         S = self.absorbed_per_surface.shape[0]
         if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
-            return self.absorbed_per_surface, self.hits_per_surface, bins
+            out = (self.absorbed_per_surface, self.hits_per_surface, bins)
+            return _PendingTallies(None, out) if async_op else out
         parts = [self.absorbed_per_surface, self.hits_per_surface.to(torch.float64)]
         if bins is not None:
             parts.append(bins.reshape(-1))
         packed = torch.cat(parts)
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-            dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
-        absorbed, hits = packed[:S], packed[S:2 * S].round().to(torch.int64)
-        out_bins = packed[2 * S:].reshape(bins.shape) if bins is not None else None
-        return absorbed, hits, out_bins
+        work = dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+
+        def unpack():
+            absorbed, hits = packed[:S], packed[S:2 * S].round().to(torch.int64)
+            out_bins = packed[2 * S:].reshape(bins.shape) if bins is not None else None
+            return absorbed, hits, out_bins
+        return _PendingTallies(work, unpack) if async_op else unpack()
+
+
+class _PendingTallies(object):
+    """An enqueued all-reduce of the tallies (TracerEngineMP.reduce_tallies(async_op=True))."""
+
+    def __init__(self, work, out):
+        self._work, self._out = work, out
+
+    def result(self):
+        if self._work is not None:
+            self._work.wait()                   # the current stream waits for the collective, the host does not
+            self._work = None
+        if callable(self._out):
+            self._out = self._out()
+        return self._out
