@@ -166,3 +166,47 @@ def test_prebuilt_kdtree_handle_selects_the_walk():
     for k in range(1, a.tree.num_bunds()):
         assert np.array_equal(a.tree[k].get_parents(), b.tree[k].get_parents())
         assert np.array_equal(a.tree[k].get_vertices(), b.tree[k].get_vertices())
+
+
+def test_reflected_bundle_walk_equals_brute():
+    """The second bounce of a heliostat field: child bundles are surface-major, so consecutive rays leave one mirror
+    towards the receiver, every ray starts ON a surface (its own mirror is a candidate that must lose) and nearly all
+    reach the receiver.  Same hit indices as brute force -- for the reflected bundle itself, with the origins moved
+    back behind the mirrors (the own mirror and its neighbours become real candidates), reversed, with the order of
+    half the rays scrambled and with non-finite rays mixed in."""
+    from tracer_b200.scene import CompiledScene
+    from tracer_b200.tracer_engine import TracerEngine
+    from tests.test_gpu_shadow_grid import _nsttf_source
+    asm, _ = scenes.c3_nsttf(T, n_rays=10)
+    src, _ = _nsttf_source(2000000, 7)
+    eng = TracerEngine(asm, rng='philox', seed=3, device_accel='bvh')
+    eng.ray_tracer(src, reps=1, min_energy=1e-10, tree=True)
+    b = eng.tree[1]
+    V, D = np.ascontiguousarray(b.get_vertices()), np.ascontiguousarray(b.get_directions())
+    n = V.shape[1]
+    assert n > 100000
+    sc = CompiledScene(asm)
+
+    def same(V, D, frac_lo=None):
+        brute, walk = _hits(sc, V, D, 0), _hits(sc, V, D, 1)
+        bad = np.nonzero(walk != brute)[0]
+        assert bad.size == 0, 'walk != brute at rays %s: %s vs %s' % (bad[:5], walk[bad[:5]], brute[bad[:5]])
+        if frac_lo is not None:
+            assert (brute >= 0).mean() > frac_lo
+        return brute
+    same(V, D, 0.9)                                   # nearly all reach the receiver
+    back = same(V - 30. * D, D, 0.9)                  # from 30 m behind: the own mirror (or a neighbour) comes first
+    assert (back < 218).mean() > 0.5
+    same(V, -D)                                       # away from the tower
+    rng = np.random.RandomState(4)
+    perm = np.arange(n)
+    half = rng.permutation(n // 2)
+    perm[:n // 2] = half
+    same(V[:, perm], D[:, perm], 0.9)
+    V2, D2 = V.copy(), D.copy()
+    V2[0, 1000::7777] = np.nan
+    D2[2, 5000::9999] = np.inf
+    same(V2, D2)
+    # a short bundle whose last batch is partial and odd
+    same(V[:, :64 * 37 + 13], D[:, :64 * 37 + 13])
+    sc.close()
