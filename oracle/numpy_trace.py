@@ -529,6 +529,8 @@ class OracleEngine(object):
             if a.shorthand == 'Polychromatic':
                 # PolychromaticAccountant.get_data reads self._absorbed, which its reset() never creates (:1840-1848)
                 raise AttributeError("'PolychromaticAccountant' object has no attribute '_absorbed'")
+            if a.shorthand == 'Spectral':               # the same slip in SpectralAccountant.get_data (:1813-1823)
+                raise AttributeError("'SpectralAccountant' object has no attribute '_absorbed'")
             field = _ACC[a.shorthand]
             chunks = self.tallies.get(key, {}).get(field, [])
             if field in ('_hits', '_directions', '_normals'):

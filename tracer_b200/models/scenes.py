@@ -395,7 +395,9 @@ def c12_refractive_materials(T, n_rays=2000):
         plate(oc.RefractiveDetector(air, glass, single_ray=True, sigma=3e-3), 0.7, flip=True),     # accountants see the
                                                                          # [reflected][refracted] child bundle as it is
         plate(oc.RefractiveAbsorbant(air, glass, single_ray=False, attenuation_coefficient_1=1., scaling=2.), 0.4),
-        plate(oc.RefractiveAbsorbant(air, glass, single_ray=True, attenuation_coefficient_2=1.), 0.1, flip=True),
+        # smooth single_ray surface with accountants of the incoming rays: wavelengths and normals in hit order
+        plate(oc.RefractiveAbsorbantSpectralNormal(air, glass, single_ray=True, attenuation_coefficient_2=1.), 0.1,
+              flip=True),
         plate(oc.LambertianReceiver(0.6), -0.3, w=8., h=8.),
     ]
     asm = T.assembly.Assembly(objects=objs)

@@ -367,7 +367,13 @@ class PolychromaticAccountant(Accountant):
 
 
 class SpectralAccountant(Accountant):
+    """Per bounce: the wavelengths of the incoming rays that hit, in hit order (:1801-1811).  ``get_data`` raises as
+    the reference's does (it tests ``self._absorbed``, which this accountant never creates, :1813-1823): read
+    ``_wavelengths``."""
     shorthand, field = 'Spectral', '_wavelengths'
+
+    def get_data(self):
+        raise AttributeError("'SpectralAccountant' object has no attribute '_absorbed'")
 
 
 class LocationAccountant(Accountant):

@@ -237,7 +237,11 @@ def _check_refractive_accountants(base, accountants):
             "refractive optics with accountants and single_ray=False: the reference raises ValueError there "
             "(Accountant.count subtracts a child bundle of another length, optics_callables.py:1638-1643)")
     for _, _, src in accountants:
-        if src not in ('absorbed', 'e_in', 'e_out', 'hits', 'dirs_in'):
+        if src == 'normals' and getattr(base, '_sigma', None) is not None:
+            raise NotImplementedError(
+                "NormalAccountant on a rough refractive surface: the reference's _refract_dirs perturbs the geometry "
+                "manager's normals in place before the accountant reads them")
+        if src not in ('absorbed', 'e_in', 'e_out', 'hits', 'dirs_in', 'normals', 'wavelengths'):
             raise NotImplementedError(f"accountant column {src!r} on a refractive surface")
 
 

@@ -621,7 +621,7 @@ class TracerEngine(object):
             def columns(o):
                 return dict(hits=o['V'], absorbed=o['absorbed'], e_out=o['E'], normals=o['normals'], e_in=o['e_in'],
                             dirs_in=o['dirs_in'], wavelengths=o['W'], attenuated=o['attenuated'],
-                            lost_spectra=o['lost_spectra'], cull=o['cull'])
+                            lost_spectra=o['lost_spectra'], cull=o['cull'], parents=o['P'], w_in=cur.W)
             if scene.has_bifacial:
                 self._account(scene, seg_host, columns(src_front), child_off_host, back=(columns(src_back), back_counts))
             else:
@@ -902,7 +902,11 @@ class TracerEngine(object):
                         t = e_child
                     elif name == 'hits':
                         t = src['hits'][:, lo:lo + h]
-                    else:                                   # e_in, dirs_in: slot order
+                    elif name == 'wavelengths':
+                        # SpectralAccountant.count reads the INCOMING rays' wavelengths in hit order (:1811); the
+                        # children's differ in single_ray mode (inherited by rank, :797-815)
+                        t = src['w_in'].index_select(0, src['parents'][lo:lo + h])
+                    else:                                   # e_in, dirs_in, normals: slot order
                         t = src[name][..., a:b]
                     getattr(acc, field).append(_LazyRows(t.clone()))
                 continue
