@@ -314,6 +314,15 @@ def test_refractive_records():
         scene(oc.RefractiveHomogenousReceiver(1., 1.5, single_ray=False))
     with pytest.raises(NotImplementedError):
         scene(oc.RefractiveHomogenous(1., 1.5 + 0.1j))
+    # accountants of the incoming rays (wavelengths, normals): fine on a smooth surface; on a rough one the reference
+    # perturbs the geometry manager's normals in place before NormalAccountant reads them -- refused
+    smooth = scene(oc.RefractiveHomogenousSpectralNormal(1., 1.5))
+    assert smooth.has_accountants and {'wavelengths', 'normals'} <= set(smooth.accountant_sources)
+    scene(oc.RefractiveHomogenousSpectral(1., 1.5, sigma=1e-3))
+    with pytest.raises(NotImplementedError):
+        scene(oc.RefractiveHomogenousNormal(1., 1.5, sigma=1e-3))
+    with pytest.raises(AttributeError):                     # SpectralAccountant.get_data, as the reference's (:1813-1823)
+        oc.RefractiveHomogenousSpectralNormal(1., 1.5).get_all_hits()
     # media given by material tables: knots of both materials in the pool, flag TRC_F_TABULATED
     ocn = T.optical_constants
     glass = ocn.OpticalMaterialTable([3e-7, 1e-6, 2.5e-6], [1.55, 1.52, 1.5], [1e-8, 2e-8, 4e-8])
